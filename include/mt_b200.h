@@ -1,0 +1,117 @@
+/* mt_b200.h — C ABI of the B200-native hot path of kartikkadur/MasterThesis.
+ *
+ * The reference has no FFI: its hot path is torch.nn modules (src/models/core/blocks.py,
+ * norm.py, networks.py). Each entry point below replaces one family of torch.nn calls on
+ * that path; the file:line after each declaration is the reference call site it stands in
+ * for. All pointers are DEVICE pointers unless a name ends in _host; all activation
+ * tensors are NHWC bf16 ("stored" channel counts are multiples of 8); `stream` is a
+ * cudaStream_t passed as void*. Every function returns 0 on success or a negative error
+ * code (-cudaError_t, or <= -1000 for argument errors) and never allocates or
+ * synchronises. There is no CPU fallback: without a CUDA device every call fails.
+ */
+#ifndef MT_B200_H
+#define MT_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { MT_ACT_NONE = 0, MT_ACT_RELU = 1, MT_ACT_LRELU = 2, MT_ACT_TANH = 3 };
+enum { MT_NORM_INSTANCE = 0, MT_NORM_ADAIN = 1, MT_NORM_LAYER = 2 };
+
+/* One convolution-shaped contraction.  The input buffer is [N, Hin, Win, Cin_s]; reflection
+ * borders are already materialised in it (blocks.py:29-31 folds all padding into
+ * ReflectionPad2d), `zpad` is additional logical ZERO padding realised by TMA out-of-bounds
+ * fill.  The result is written at offset (out_pad, out_pad) of an [N, out_H, out_W, Cout_s]
+ * buffer so that the consumer's reflection border can be filled in place. */
+typedef struct MtConv2d {
+  int N;
+  int Hin, Win, Cin, Cin_s;
+  int Hout, Wout, Cout, Cout_s;
+  int kh, kw, stride, zpad;
+  int out_H, out_W, out_pad;
+  int act;      /* MT_ACT_* fused into the epilogue */
+  float slope;  /* LeakyReLU slope (functions.py:34 -> 0.01) */
+} MtConv2d;
+
+/* ---- library --------------------------------------------------------------------- */
+int mt_version(void);
+const char* mt_error_string(int code);
+/* stored channel count for a logical one (multiple of 8) */
+int mt_stored_channels(int c);
+/* 1 if a (Cin_s, kw) stem runs in row-window mode (K = kh x 64 window elements) */
+int mt_conv_window_mode(int Cin_s, int kw);
+
+/* ---- weight packing (fp32 OIHW master -> bf16 GEMM operands) ------------------------
+ * nn.Conv2d weight [Cout, Cin, kh, kw] (blocks.py:36) or nn.ConvTranspose2d weight
+ * [Cin, Cout, kh, kw] (blocks.py:72), fp32.  `transposed`=1 for ConvTranspose2d.
+ *  w_fwd : forward operand  [taps][Cout_s'][Cin_s]   (window mode: [kh][Cout][64])
+ *  w_bwd : data-grad operand [taps][Cin_s'][Cout_s]
+ * Either output may be NULL. Sizes in elements are returned by mt_packed_weight_elems. */
+long long mt_packed_weight_elems(int Cout, int Cin, int kh, int kw, int window, int bwd);
+int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, int kw, int transposed,
+                        int window, void* w_fwd, void* w_bwd, void* stream);
+
+/* ---- convolutions (implicit GEMM, tcgen05/TMEM, TMA) -------------------------------- */
+/* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
+int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,
+                  void* y, void* stream);
+/* d(loss)/d(input buffer), including the reflection border rows/cols (folded later) */
+int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx, void* stream);
+/* d(loss)/d(weight) accumulated (+=) into fp32 dw_packed[taps][Cout][Cin_s] (window mode:
+ * [kh][Cout][64]); mt_unpack_conv_wgrad scatters it back to OIHW. */
+int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+                    void* stream);
+int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
+                         int transposed, int window, float* dw, void* stream);
+/* nn.ConvTranspose2d(k=3, s=2, p=1, op=1) forward / dgrad / wgrad     blocks.py:69-73.
+ * Descriptor: Hin/Win = input dims, Hout/Wout = 2*Hin, 2*Win; kh=kw=3, stride=2, zpad=1. */
+int mt_conv_transpose2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
+                            const float* bias, void* y, void* stream);
+int mt_conv_transpose2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
+                              void* stream);
+int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+                              void* stream);
+
+/* ---- layout / padding ------------------------------------------------------------------ */
+/* NCHW fp32 image (+ one-hot domain code tiled over H,W: networks.py:136-140) -> NHWC bf16 with
+ * the consumer's reflection border (blocks.py:29-31); channels >= Ci+nd are zero. */
+int mt_image_to_nhwc(const float* img, const float* onehot, int N, int Ci, int nd, int H, int W,
+                     int pad, int Cs, void* out, void* stream);
+/* adjoint of the above w.r.t. the image channels: folds border gradients back. Cs must be 8. */
+int mt_image_grad_from_nhwc(const void* dpad, int N, int Ci, int H, int W, int pad, int Cs,
+                            float* dimg, void* stream);
+/* nn.ReflectionPad2d(pad) in place on [N,H+2p,W+2p,C] whose interior is already written */
+int mt_reflect_border(void* buf, int N, int H, int W, int C, int pad, void* stream);
+/* ReflectionPad2d backward: padded gradient -> dense [N,H,W,C] */
+int mt_reflect_fold(const void* dpad, int N, int H, int W, int C, int pad, void* dense,
+                    void* stream);
+/* dpad[interior] += dense   (residual fan-in, blocks.py:137,166) */
+int mt_add_interior(void* dpad, const void* dense, int N, int H, int W, int C, int pad,
+                    void* stream);
+
+/* ---- normalisation (InstanceNorm2d / AdaptiveInstanceNorm / LayerNorm) ---------------------
+ * functions.py:17, norm.py:5-33.  stats/sums: [N][C][2] fp32; ss: (scale, shift) per (n,c);
+ * mr: (mean, rstd); coef: [N][C][3]; gb: fc(s) output [N][2C] (weight | bias). */
+int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream);
+int mt_norm_finalize(const float* stats, int mode, int N, int C, int HW, float eps,
+                     const float* gb, const float* ln_w, const float* ln_b, float* ss, float* mr,
+                     void* stream);
+/* out_pad[interior] = act(x*scale+shift) (+ residual) (+ noise, misc.py:25); ss may be NULL */
+int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C, int act,
+                      float slope, const void* res_pad, int res_p, const float* noise,
+                      void* out_pad, int out_p, void* stream);
+int mt_norm_bwd_reduce(const void* g, const void* x, const float* ss, int N, int HW, int C,
+                       int act, float slope, float* sums, void* stream);
+int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C, int HW,
+                         const float* gb, const float* ln_w, float* coef, float* dgb,
+                         float* dln_w, float* dln_b, void* stream);
+int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float* coef, int N,
+                      int HW, int C, int act, float slope, void* dx, void* stream);
+/* backward of conv+bias+activation written into a padded buffer: fold + act' */
+int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C, int pad,
+                    int act, float slope, void* dy, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MT_B200_H */

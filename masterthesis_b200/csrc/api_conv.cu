@@ -1,0 +1,242 @@
+// Host side of the convolution entry points of include/mt_b200.h: builds the TMA tensor maps
+// and the tap maps that turn conv forward / data-grad / transposed-conv phases into launches of
+// the one implicit-GEMM kernel (igemm_fwd.cu), and weight-grad into igemm_wgrad.cu.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cudaTypedefs.h>
+#include <string.h>
+#include <mutex>
+
+#include "../../include/mt_b200.h"
+#include "igemm.cuh"
+
+namespace mt {
+
+// ------------------------------------------------------------------ tensor maps
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static void load_encode() {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) ==
+          cudaSuccess &&
+      qres == cudaDriverEntryPointSuccess)
+    g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+}
+
+int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr) {
+  std::call_once(g_encode_once, load_encode);
+  if (!g_encode) return -1001;
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+                        const_cast<void*>(base), dims, strides_bytes, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -(2000 + (int)r);
+}
+
+// Generic description of one launch of the conv-shaped GEMM.
+struct ConvLike {
+  const void* a;            // activation operand, [An][Ah][Aw][Ac_s]
+  int An, Ah, Aw, Ac, Ac_s; // logical/stored channels of A (K extent = Ac)
+  int a_mul;                // TMA traversal stride on h, w (1 or 2)
+  bool window;              // row-window stem mode
+  int win_stride;           // pixel stride baked into the window map
+  int win_cols;             // number of valid output columns in window mode
+  const void* b;            // packed weights [taps_total][Bn][Bk_s]
+  int taps_total, Bn, Bk, Bk_s;
+  int Wt, Ht, Nt;           // pixel space
+  int kh, kw, off_h, off_w, step_h, step_w, w_base, w_step_r, w_step_s;
+  int n_store, n_bias;
+  long long out_n_stride, out_h_stride, out_w_stride, out_off;
+  int act; float slope; const float* bias; void* out;
+};
+
+static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  const int mul = c.window ? 1 : c.a_mul;
+  pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul, &p.TW, &p.TH, &p.TN);
+  p.tiles_w = cdiv(c.Wt, p.TW); p.tiles_h = cdiv(c.Ht, p.TH); p.tiles_n = cdiv(c.Nt, p.TN);
+  p.Wt = c.Wt; p.Ht = c.Ht; p.Nt = c.Nt;
+  p.kh = c.kh; p.kw = c.kw;
+  p.mul_h = c.a_mul; p.mul_w = mul;
+  p.off_h = c.off_h; p.off_w = c.off_w; p.step_h = c.step_h; p.step_w = c.step_w;
+  p.w_base = c.w_base; p.w_step_r = c.w_step_r; p.w_step_s = c.w_step_s;
+  p.BN = pick_bn(c.Bn);
+  p.n_tiles = cdiv(c.Bn, p.BN);
+  p.k_chunks = c.window ? 1 : cdiv(c.Ac, 64);
+  p.n_store = c.n_store; p.n_bias = c.bias ? c.n_bias : 0;
+  const int stage_bytes = 16384 + p.BN * 128;
+  p.stages = (200 * 1024) / stage_bytes;
+  if (p.stages > 8) p.stages = 8;
+  const int iters = p.kh * p.kw * p.k_chunks;
+  if (p.stages > iters) p.stages = iters < 2 ? 2 : iters;
+  p.tmem_cols = pow2_cols(p.BN);
+  p.out_n_stride = c.out_n_stride; p.out_h_stride = c.out_h_stride;
+  p.out_w_stride = c.out_w_stride; p.out_off = c.out_off;
+  p.act = c.act; p.slope = c.slope; p.bias = c.bias;
+  p.out = reinterpret_cast<__nv_bfloat16*>(c.out);
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!c.window) {
+    uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
+    uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
+                       (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
+    uint32_t box[4] = {64, (uint32_t)(p.TW * c.a_mul), (uint32_t)(p.TH * c.a_mul), (uint32_t)p.TN};
+    uint32_t es[4] = {1, (uint32_t)c.a_mul, (uint32_t)c.a_mul, 1};
+    rc = make_tmap(&tmA, c.a, 4, dims, str, box, es);
+  } else {
+    // dim0: 64-element window starting at pixel (w*win_stride); dim1: output column.
+    uint64_t dims[4] = {64, (uint64_t)c.win_cols, (uint64_t)c.Ah, (uint64_t)c.An};
+    uint64_t str[3] = {(uint64_t)c.win_stride * c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
+                       (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)(p.TH * c.a_mul), (uint32_t)p.TN};
+    uint32_t es[4] = {1, 1, (uint32_t)c.a_mul, 1};
+    rc = make_tmap(&tmA, c.a, 4, dims, str, box, es);
+  }
+  if (rc) return rc;
+  {
+    uint64_t dims[3] = {(uint64_t)c.Bk, (uint64_t)c.Bn, (uint64_t)c.taps_total};
+    uint64_t str[2] = {(uint64_t)c.Bk_s * 2, (uint64_t)c.Bn * c.Bk_s * 2};
+    uint32_t box[3] = {64, (uint32_t)p.BN, 1};
+    uint32_t es[3] = {1, 1, 1};
+    rc = make_tmap(&tmB, c.b, 3, dims, str, box, es);
+  }
+  if (rc) return rc;
+  return launch_igemm(tmA, tmB, p, stream);
+}
+
+static int check_desc(const MtConv2d* d) {
+  if (!d) return -1002;
+  if (d->Cin_s % 8 || d->Cout_s % 8 || d->Cin > d->Cin_s || d->Cout > d->Cout_s) return -1003;
+  if (d->stride != 1 && d->stride != 2) return -1004;
+  if (d->N <= 0 || d->kh <= 0 || d->kw <= 0) return -1005;
+  return 0;
+}
+
+}  // namespace mt
+
+using namespace mt;
+
+extern "C" int mt_stored_channels(int c) { return round_up(c, 8); }
+extern "C" int mt_conv_window_mode(int Cin_s, int kw) { return (Cin_s * kw <= 64) ? 1 : 0; }
+
+extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
+                             const float* bias, void* y, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  ConvLike c;
+  memset(&c, 0, sizeof(c));
+  const bool win = mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0;
+  c.a = x; c.An = d->N; c.Ah = d->Hin; c.Aw = d->Win; c.Ac = d->Cin; c.Ac_s = d->Cin_s;
+  c.a_mul = d->stride; c.window = win; c.win_stride = d->stride; c.win_cols = d->Wout;
+  c.b = w_fwd;
+  c.Wt = d->Wout; c.Ht = d->Hout; c.Nt = d->N;
+  if (win) {
+    c.taps_total = d->kh; c.Bn = d->Cout; c.Bk = 64; c.Bk_s = 64;
+    c.kh = d->kh; c.kw = 1; c.off_h = 0; c.off_w = 0; c.step_h = 1; c.step_w = 0;
+    c.w_base = 0; c.w_step_r = 1; c.w_step_s = 0;
+  } else {
+    c.taps_total = d->kh * d->kw; c.Bn = d->Cout; c.Bk = d->Cin; c.Bk_s = d->Cin_s;
+    c.kh = d->kh; c.kw = d->kw; c.off_h = -d->zpad; c.off_w = -d->zpad;
+    c.step_h = 1; c.step_w = 1; c.w_base = 0; c.w_step_r = d->kw; c.w_step_s = 1;
+  }
+  c.n_store = d->Cout_s; c.n_bias = d->Cout;
+  c.out_w_stride = d->Cout_s;
+  c.out_h_stride = (long long)d->out_W * d->Cout_s;
+  c.out_n_stride = (long long)d->out_H * d->out_W * d->Cout_s;
+  c.out_off = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
+  c.act = d->act; c.slope = d->slope; c.bias = bias; c.out = y;
+  return run_conv_like(c, (cudaStream_t)stream);
+}
+
+// Sub-pixel phase launcher shared by stride-2 dgrad and ConvTranspose2d forward:
+//   out[2a+ph, 2b+pw] = sum_{r == (ph+zp) mod 2, s == (pw+zp) mod 2} A[a + (ph+zp-r)/2, ...] W[r,s]
+static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, long long row_pitch,
+                      long long pix_pitch, long long base_off, cudaStream_t stream) {
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      const int r0 = (ph + zp) & 1, s0 = (pw + zp) & 1;
+      const int nr = (kh - r0 + 1) / 2, ns = (kw - s0 + 1) / 2;
+      const int Ht = (OutH - ph + 1) / 2, Wt = (OutW - pw + 1) / 2;
+      if (Ht <= 0 || Wt <= 0) continue;
+      if (nr <= 0 || ns <= 0) return -1006;  // phase without taps: caller must not use k<2
+      ConvLike q = c;
+      q.Ht = Ht; q.Wt = Wt;
+      q.kh = nr; q.kw = ns;
+      q.off_h = (ph + zp - r0) / 2; q.off_w = (pw + zp - s0) / 2;
+      q.step_h = -1; q.step_w = -1;
+      q.w_base = r0 * kw + s0; q.w_step_r = 2 * kw; q.w_step_s = 2;
+      q.out_h_stride = 2 * row_pitch; q.out_w_stride = 2 * pix_pitch;
+      q.out_off = base_off + ph * row_pitch + pw * pix_pitch;
+      int rc = run_conv_like(q, stream);
+      if (rc) return rc;
+    }
+  return 0;
+}
+
+extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
+                               void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  ConvLike c;
+  memset(&c, 0, sizeof(c));
+  // A = dy [N, Hout, Wout, Cout_s] (dense: the producer of dy writes an unpadded buffer)
+  c.a = dy; c.An = d->N; c.Ah = d->Hout; c.Aw = d->Wout; c.Ac = d->Cout; c.Ac_s = d->Cout_s;
+  c.a_mul = 1; c.window = false;
+  c.b = w_bwd; c.taps_total = d->kh * d->kw; c.Bn = d->Cin; c.Bk = d->Cout; c.Bk_s = d->Cout_s;
+  c.Nt = d->N;
+  c.n_store = d->Cin_s; c.n_bias = 0; c.bias = nullptr; c.act = MT_ACT_NONE; c.out = dx;
+  const long long pix = d->Cin_s, row = (long long)d->Win * d->Cin_s;
+  c.out_n_stride = (long long)d->Hin * row;
+  if (d->stride == 1) {
+    c.Wt = d->Win; c.Ht = d->Hin;
+    c.kh = d->kh; c.kw = d->kw; c.off_h = d->zpad; c.off_w = d->zpad; c.step_h = -1; c.step_w = -1;
+    c.w_base = 0; c.w_step_r = d->kw; c.w_step_s = 1;
+    c.out_h_stride = row; c.out_w_stride = pix; c.out_off = 0;
+    return run_conv_like(c, (cudaStream_t)stream);
+  }
+  return run_phases(c, d->kh, d->kw, d->zpad, d->Hin, d->Win, row, pix, 0, (cudaStream_t)stream);
+}
+
+extern "C" int mt_conv_transpose2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
+                                       const float* bias, void* y, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  if (d->stride != 2) return -1004;
+  ConvLike c;
+  memset(&c, 0, sizeof(c));
+  c.a = x; c.An = d->N; c.Ah = d->Hin; c.Aw = d->Win; c.Ac = d->Cin; c.Ac_s = d->Cin_s;
+  c.a_mul = 1; c.window = false;
+  c.b = w_fwd; c.taps_total = d->kh * d->kw; c.Bn = d->Cout; c.Bk = d->Cin; c.Bk_s = d->Cin_s;
+  c.Nt = d->N;
+  c.n_store = d->Cout_s; c.n_bias = d->Cout; c.bias = bias; c.act = d->act; c.slope = d->slope;
+  c.out = y;
+  const long long pix = d->Cout_s, row = (long long)d->out_W * d->Cout_s;
+  c.out_n_stride = (long long)d->out_H * row;
+  const long long base = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
+  return run_phases(c, d->kh, d->kw, d->zpad, d->Hout, d->Wout, row, pix, base,
+                    (cudaStream_t)stream);
+}
+
+extern "C" int mt_conv_transpose2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd,
+                                         void* dx, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  // dx[hi] = sum_r dy[2*hi - zpad + r] W[ci, co, r]  == stride-2 zero-padded conv over dy.
+  ConvLike c;
+  memset(&c, 0, sizeof(c));
+  c.a = dy; c.An = d->N; c.Ah = d->Hout; c.Aw = d->Wout; c.Ac = d->Cout; c.Ac_s = d->Cout_s;
+  c.a_mul = 2; c.window = false;
+  c.b = w_bwd; c.taps_total = d->kh * d->kw; c.Bn = d->Cin; c.Bk = d->Cout; c.Bk_s = d->Cout_s;
+  c.Wt = d->Win; c.Ht = d->Hin; c.Nt = d->N;
+  c.kh = d->kh; c.kw = d->kw; c.off_h = -d->zpad; c.off_w = -d->zpad; c.step_h = 1; c.step_w = 1;
+  c.w_base = 0; c.w_step_r = d->kw; c.w_step_s = 1;
+  c.n_store = d->Cin_s; c.n_bias = 0; c.act = MT_ACT_NONE; c.out = dx;
+  c.out_w_stride = d->Cin_s; c.out_h_stride = (long long)d->Win * d->Cin_s;
+  c.out_n_stride = (long long)d->Hin * d->Win * d->Cin_s; c.out_off = 0;
+  return run_conv_like(c, (cudaStream_t)stream);
+}

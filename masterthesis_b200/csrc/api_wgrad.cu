@@ -1,0 +1,211 @@
+// Weight-gradient entry points and the fp32-master <-> bf16-operand weight (un)packers.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include "../../include/mt_b200.h"
+#include "igemm.cuh"
+
+namespace mt {
+
+struct WgradLike {
+  const void* p; int Pn, Ph, Pw, Pc, Pc_s;   // un-shifted tensor -> M
+  const void* q; int Qn, Qh, Qw, Qc, Qc_s;   // tap-shifted tensor -> N
+  int q_mul; bool window; int win_stride, win_cols;
+  int kh, kw, off_h, off_w, step_h, step_w;
+  float* out; int N_store;                   // row pitch of out (fp32 elements)
+};
+
+static int run_wgrad_like(const WgradLike& c, cudaStream_t stream) {
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  pick_tile(64, c.Pw, c.Ph, c.Pn, c.q_mul, &p.TW, &p.TH, &p.TN);
+  p.tiles_w = cdiv(c.Pw, p.TW); p.tiles_h = cdiv(c.Ph, p.TH); p.tiles_n = cdiv(c.Pn, p.TN);
+  p.kh = c.kh; p.kw = c.kw;
+  p.mul_h = c.q_mul; p.mul_w = c.window ? 1 : c.q_mul;
+  p.off_h = c.off_h; p.off_w = c.off_w; p.step_h = c.step_h; p.step_w = c.step_w;
+  const int n_logical = c.window ? 64 : c.Qc;
+  p.BN = n_logical >= 256 ? 256 : (n_logical > 64 ? 128 : 64);
+  p.m_tiles = cdiv(c.Pc, 128);
+  p.n_tiles = cdiv(n_logical, p.BN);
+  const int total_kt = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int items = p.kh * p.kw * p.m_tiles * p.n_tiles;
+  int splits = cdiv(4 * 148, items);          // aim at ~4 CTAs per SM worth of work items
+  const int max_splits = cdiv(total_kt, 4);   // at least 4 pixel tiles per split
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  const int per = cdiv(total_kt, splits);
+  p.splits = cdiv(total_kt, per);
+  const int stage_bytes = (2 + p.BN / 64) * 8192;
+  p.stages = (200 * 1024) / stage_bytes;
+  if (p.stages > 8) p.stages = 8;
+  p.tmem_cols = pow2_cols(p.BN);
+  p.M_valid = c.Pc;
+  p.N_valid = c.N_store;
+  p.out_m_stride = c.N_store;
+  p.out_tap_stride = (long long)c.Pc * c.N_store;
+  p.out = c.out;
+
+  CUtensorMap tmP, tmQ;
+  {
+    uint64_t dims[4] = {(uint64_t)c.Pc, (uint64_t)c.Pw, (uint64_t)c.Ph, (uint64_t)c.Pn};
+    uint64_t str[3] = {(uint64_t)c.Pc_s * 2, (uint64_t)c.Pw * c.Pc_s * 2,
+                       (uint64_t)c.Ph * c.Pw * c.Pc_s * 2};
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)p.TH, (uint32_t)p.TN};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = make_tmap(&tmP, c.p, 4, dims, str, box, es);
+    if (rc) return rc;
+  }
+  if (!c.window) {
+    uint64_t dims[4] = {(uint64_t)c.Qc, (uint64_t)c.Qw, (uint64_t)c.Qh, (uint64_t)c.Qn};
+    uint64_t str[3] = {(uint64_t)c.Qc_s * 2, (uint64_t)c.Qw * c.Qc_s * 2,
+                       (uint64_t)c.Qh * c.Qw * c.Qc_s * 2};
+    uint32_t box[4] = {64, (uint32_t)(p.TW * c.q_mul), (uint32_t)(p.TH * c.q_mul), (uint32_t)p.TN};
+    uint32_t es[4] = {1, (uint32_t)c.q_mul, (uint32_t)c.q_mul, 1};
+    int rc = make_tmap(&tmQ, c.q, 4, dims, str, box, es);
+    if (rc) return rc;
+  } else {
+    uint64_t dims[4] = {64, (uint64_t)c.win_cols, (uint64_t)c.Qh, (uint64_t)c.Qn};
+    uint64_t str[3] = {(uint64_t)c.win_stride * c.Qc_s * 2, (uint64_t)c.Qw * c.Qc_s * 2,
+                       (uint64_t)c.Qh * c.Qw * c.Qc_s * 2};
+    uint32_t box[4] = {64, (uint32_t)p.TW, (uint32_t)(p.TH * c.q_mul), (uint32_t)p.TN};
+    uint32_t es[4] = {1, 1, (uint32_t)c.q_mul, 1};
+    int rc = make_tmap(&tmQ, c.q, 4, dims, str, box, es);
+    if (rc) return rc;
+  }
+  return launch_wgrad(tmP, tmQ, p, stream);
+}
+
+// ------------------------------------------------------------------ pack / unpack
+// Source weight element for (n_idx -> out channel of the packed row, k_idx, r, s):
+//   Conv2d          W[co][ci][r][s]   ConvTranspose2d  W[ci][co][r][s]
+__device__ __forceinline__ long long w_index(int co, int ci, int r, int s, int Cout, int Cin,
+                                             int kh, int kw, int transposed) {
+  return transposed ? (((long long)ci * Cout + co) * kh + r) * kw + s
+                    : (((long long)co * Cin + ci) * kh + r) * kw + s;
+}
+
+__global__ void pack_weight_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw,
+                                   int transposed, int window, __nv_bfloat16* __restrict__ wf,
+                                   __nv_bfloat16* __restrict__ wb) {
+  const int Cin_s = (Cin + 7) & ~7, Cout_s = (Cout + 7) & ~7;
+  const long long nf = window ? (long long)kh * Cout * 64 : (long long)kh * kw * Cout * Cin_s;
+  const long long nb = (long long)kh * kw * Cin * Cout_s;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nf + nb; i += stride) {
+    if (i < nf) {
+      if (!wf) continue;
+      float v = 0.f;
+      if (window) {
+        const int e = (int)(i % 64); long long t = i / 64;
+        const int co = (int)(t % Cout); const int r = (int)(t / Cout);
+        const int s = e / Cin_s, ci = e % Cin_s;
+        if (s < kw && ci < Cin) v = w[w_index(co, ci, r, s, Cout, Cin, kh, kw, transposed)];
+      } else {
+        const int ci = (int)(i % Cin_s); long long t = i / Cin_s;
+        const int co = (int)(t % Cout); const int tap = (int)(t / Cout);
+        if (ci < Cin) v = w[w_index(co, ci, tap / kw, tap % kw, Cout, Cin, kh, kw, transposed)];
+      }
+      wf[i] = __float2bfloat16(v);
+    } else {
+      if (!wb) continue;
+      const long long j = i - nf;
+      const int co = (int)(j % Cout_s); long long t = j / Cout_s;
+      const int ci = (int)(t % Cin); const int tap = (int)(t / Cin);
+      float v = 0.f;
+      if (co < Cout) v = w[w_index(co, ci, tap / kw, tap % kw, Cout, Cin, kh, kw, transposed)];
+      wb[j] = __float2bfloat16(v);
+    }
+  }
+}
+
+// dw_packed -> dw (OIHW / IOHW fp32). Conv2d: [tap][Cout][Cin_s] (window: [kh][Cout][64]);
+// ConvTranspose2d: [tap][Cin][Cout_s].
+__global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout, int Cin, int kh, int kw,
+                                    int transposed, int window, float* __restrict__ dw) {
+  const int Cin_s = (Cin + 7) & ~7, Cout_s = (Cout + 7) & ~7;
+  const long long n = (long long)Cout * Cin * kh * kw;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int s = (int)(i % kw); long long t = i / kw;
+    const int r = (int)(t % kh); t /= kh;
+    int co, ci;
+    if (transposed) { co = (int)(t % Cout); ci = (int)(t / Cout); }
+    else            { ci = (int)(t % Cin);  co = (int)(t / Cin); }
+    long long src;
+    if (transposed) src = ((long long)(r * kw + s) * Cin + ci) * Cout_s + co;
+    else if (window) src = ((long long)r * Cout + co) * 64 + s * Cin_s + ci;
+    else src = ((long long)(r * kw + s) * Cout + co) * Cin_s + ci;
+    dw[i] = g[src];
+  }
+}
+
+}  // namespace mt
+
+using namespace mt;
+
+extern "C" long long mt_packed_weight_elems(int Cout, int Cin, int kh, int kw, int window,
+                                            int bwd) {
+  const int Cin_s = round_up(Cin, 8), Cout_s = round_up(Cout, 8);
+  if (bwd) return (long long)kh * kw * Cin * Cout_s;
+  return window ? (long long)kh * Cout * 64 : (long long)kh * kw * Cout * Cin_s;
+}
+
+extern "C" int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, int kw,
+                                   int transposed, int window, void* w_fwd, void* w_bwd,
+                                   void* stream) {
+  const long long n = mt_packed_weight_elems(Cout, Cin, kh, kw, window, 0) +
+                      mt_packed_weight_elems(Cout, Cin, kh, kw, window, 1);
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      w, Cout, Cin, kh, kw, transposed, window, (__nv_bfloat16*)w_fwd, (__nv_bfloat16*)w_bwd);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
+                                    int transposed, int window, float* dw, void* stream) {
+  const long long n = (long long)Cout * Cin * kh * kw;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  unpack_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, Cout, Cin, kh, kw,
+                                                                transposed, window, dw);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+                               void* stream) {
+  if (!d || d->Cin_s % 8 || d->Cout_s % 8) return -1003;
+  WgradLike c;
+  memset(&c, 0, sizeof(c));
+  const bool win = mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0;
+  c.p = dy; c.Pn = d->N; c.Ph = d->Hout; c.Pw = d->Wout; c.Pc = d->Cout; c.Pc_s = d->Cout_s;
+  c.q = x; c.Qn = d->N; c.Qh = d->Hin; c.Qw = d->Win; c.Qc = d->Cin; c.Qc_s = d->Cin_s;
+  c.q_mul = d->stride; c.window = win; c.win_stride = d->stride; c.win_cols = d->Wout;
+  if (win) {
+    c.kh = d->kh; c.kw = 1; c.off_h = 0; c.off_w = 0; c.step_h = 1; c.step_w = 0;
+    c.N_store = 64;
+  } else {
+    c.kh = d->kh; c.kw = d->kw; c.off_h = -d->zpad; c.off_w = -d->zpad; c.step_h = 1; c.step_w = 1;
+    c.N_store = d->Cin_s;
+  }
+  c.out = dw_packed;
+  return run_wgrad_like(c, (cudaStream_t)stream);
+}
+
+extern "C" int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const void* dy,
+                                         float* dw_packed, void* stream) {
+  if (!d || d->Cin_s % 8 || d->Cout_s % 8) return -1003;
+  WgradLike c;
+  memset(&c, 0, sizeof(c));
+  // dW[ci][co][r][s] = sum x[hi, wi, ci] * dy[2hi - zpad + r, 2wi - zpad + s, co]
+  c.p = x; c.Pn = d->N; c.Ph = d->Hin; c.Pw = d->Win; c.Pc = d->Cin; c.Pc_s = d->Cin_s;
+  c.q = dy; c.Qn = d->N; c.Qh = d->Hout; c.Qw = d->Wout; c.Qc = d->Cout; c.Qc_s = d->Cout_s;
+  c.q_mul = 2; c.window = false;
+  c.kh = d->kh; c.kw = d->kw; c.off_h = -d->zpad; c.off_w = -d->zpad; c.step_h = 1; c.step_w = 1;
+  c.N_store = d->Cout_s;
+  c.out = dw_packed;
+  return run_wgrad_like(c, (cudaStream_t)stream);
+}

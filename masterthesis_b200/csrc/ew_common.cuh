@@ -1,0 +1,83 @@
+// Shared helpers of the HBM-bound kernels: 16-byte (8 x bf16) vector access, reflection index
+// maps, launch sizing.  All activation tensors are NHWC bf16 with C % 8 == 0.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace mt {
+
+static constexpr int NUM_SMS = 148;
+
+struct alignas(16) bf16x8 {
+  __nv_bfloat162 v[4];
+};
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 r = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+  uint4 r;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = r;
+}
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+  f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// nn.ReflectionPad2d index map: padded coordinate j in [0, L+2p) -> interior index in [0, L)
+__device__ __forceinline__ int reflect_src(int j, int L, int p) {
+  int i = j - p;
+  if (i < 0) i = -i;
+  if (i >= L) i = 2 * (L - 1) - i;
+  return i;
+}
+// Adjoint of the map above: padded coordinates whose value came from interior index i.
+// Returns the count (1..3) and fills src[] with padded coordinates.
+__device__ __forceinline__ int reflect_fold_sources(int i, int L, int p, int (&src)[3]) {
+  int n = 0;
+  src[n++] = i + p;
+  if (i >= 1 && i <= p) src[n++] = p - i;                      // top / left border
+  const int k = L - 2 - i;                                     // bottom / right border offset
+  if (k >= 0 && k < p) src[n++] = L + p + k;
+  return n;
+}
+
+__device__ __forceinline__ float act_fwd(float v, int act, float slope) {
+  if (act == 1) return fmaxf(v, 0.f);
+  if (act == 2) return v > 0.f ? v : v * slope;
+  if (act == 3) return tanhf(v);
+  return v;
+}
+// derivative expressed through the PRE-activation sign (relu / lrelu) — y is the pre-activation
+__device__ __forceinline__ float act_grad_pre(float y, int act, float slope) {
+  if (act == 1) return y > 0.f ? 1.f : 0.f;
+  if (act == 2) return y > 0.f ? 1.f : slope;
+  return 1.f;
+}
+
+static inline int grid_for(long long work_items, int block, int max_waves = 8) {
+  long long b = (work_items + block - 1) / block;
+  const long long cap = (long long)NUM_SMS * max_waves;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+static inline int cuda_rc() {
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
+
+}  // namespace mt

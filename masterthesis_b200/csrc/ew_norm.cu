@@ -1,0 +1,366 @@
+// InstanceNorm2d / AdaptiveInstanceNorm / LayerNorm, forward and backward, as a plane-statistics
+// pass + per-(n,c) coefficient finalisation + one fused affine/activation/residual/noise pass.
+// Reference semantics: functions.py:17 (InstanceNorm2d affine=False, eps 1e-5, biased var),
+// norm.py:23-33 ((1+w)*IN(x)+b with w,b = chunk(fc(s),2)), norm.py:5-21 (F.layer_norm over
+// (C,H,W), per-channel affine), misc.py:18-26 (x + noise), blocks.py:137,166 (residual add).
+#include "../../include/mt_b200.h"
+#include "ew_common.cuh"
+
+namespace mt {
+
+// ---------------------------------------------------------------- statistics
+// x [N, HW, C] -> stats [N][C][2] += (sum, sumsq).  One CTA = (n, pixel chunk); thread = one
+// 8-channel vector x a pixel lane; warp reads are 512 contiguous bytes.
+template <bool kBackward>
+__global__ void __launch_bounds__(256)
+plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ g,
+                    const float* __restrict__ ss, int HW, int C, int chunks, int act, float slope,
+                    float* __restrict__ out) {
+  extern __shared__ float red[];  // [lanes][V*16]
+  const int V = C / 8;
+  const int lanes = blockDim.x / V;
+  const int n = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
+  const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  const int per = (HW + chunks - 1) / chunks;
+  const int p0 = chunk * per, p1 = min(HW, p0 + per);
+  float a0[8], a1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a0[j] = a1[j] = 0.f;
+  float sc[8], sh[8];
+  if (kBackward) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = ss[((long long)n * C + v * 8 + j) * 2];
+      sh[j] = ss[((long long)n * C + v * 8 + j) * 2 + 1];
+    }
+  }
+  if (pl < lanes) {
+    for (int p = p0 + pl; p < p1; p += lanes) {
+      const long long off = ((long long)n * HW + p) * C + v * 8;
+      float xv[8];
+      load8(x + off, xv);
+      if (!kBackward) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { a0[j] += xv[j]; a1[j] += xv[j] * xv[j]; }
+      } else {
+        float gv[8];
+        load8(g + off, gv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float y = xv[j] * sc[j] + sh[j];           // pre-activation (A*xhat + B)
+          const float gg = gv[j] * act_grad_pre(y, act, slope);
+          a0[j] += gg;                                      // sum g
+          a1[j] += gg * xv[j];                              // sum g*x  (xhat folded in finalize)
+        }
+      }
+    }
+  }
+  if (pl < lanes) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      red[(pl * V + v) * 16 + j] = a0[j];
+      red[(pl * V + v) * 16 + 8 + j] = a1[j];
+    }
+  }
+  __syncthreads();
+  // thread t < V*16 sums over lanes
+  for (int t = threadIdx.x; t < V * 16; t += blockDim.x) {
+    float s = 0.f;
+    for (int l = 0; l < lanes; ++l) s += red[l * V * 16 + t];
+    const int vv = t / 16, k = t % 16;
+    const int c = vv * 8 + (k & 7);
+    atomicAdd(out + ((long long)n * C + c) * 2 + (k >> 3), s);
+  }
+}
+
+// ---------------------------------------------------------------- forward finalize
+// stats -> ss[n][c] = (scale, shift) with y = x*scale + shift, mr[n][c] = (mean, rstd)
+__global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, int N, int C,
+                                     int HW, float eps, const float* __restrict__ gb,
+                                     const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+                                     float* __restrict__ ss, float* __restrict__ mr) {
+  const int n = blockIdx.x;
+  __shared__ float tot[2];
+  if (mode == MT_NORM_LAYER) {
+    float s0 = 0.f, s1 = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      s0 += stats[((long long)n * C + c) * 2];
+      s1 += stats[((long long)n * C + c) * 2 + 1];
+    }
+    __shared__ float r0[32], r1[32];
+    for (int o = 16; o; o >>= 1) {
+      s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    }
+    if ((threadIdx.x & 31) == 0) { r0[threadIdx.x >> 5] = s0; r1[threadIdx.x >> 5] = s1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t0 = 0.f, t1 = 0.f;
+      for (int i = 0; i < (blockDim.x + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
+      tot[0] = t0; tot[1] = t1;
+    }
+    __syncthreads();
+  }
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float mean, var, A = 1.f, B = 0.f;
+    if (mode == MT_NORM_LAYER) {
+      const float cnt = (float)C * (float)HW;
+      mean = tot[0] / cnt;
+      var = tot[1] / cnt - mean * mean;
+      if (ln_w) { A = ln_w[c]; B = ln_b[c]; }
+    } else {
+      mean = stats[((long long)n * C + c) * 2] / (float)HW;
+      var = stats[((long long)n * C + c) * 2 + 1] / (float)HW - mean * mean;
+      if (mode == MT_NORM_ADAIN) {
+        A = 1.f + gb[(long long)n * 2 * C + c];
+        B = gb[(long long)n * 2 * C + C + c];
+      }
+    }
+    const float rstd = rsqrtf(fmaxf(var, 0.f) + eps);
+    ss[((long long)n * C + c) * 2] = A * rstd;
+    ss[((long long)n * C + c) * 2 + 1] = B - A * mean * rstd;
+    mr[((long long)n * C + c) * 2] = mean;
+    mr[((long long)n * C + c) * 2 + 1] = rstd;
+  }
+}
+
+// ---------------------------------------------------------------- forward apply
+// out_pad[n, h+po, w+po, :] = act(x*scale + shift) (+ res_pad[n, h+pr, w+pr, :]) (+ noise)
+__global__ void __launch_bounds__(256)
+affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ss, int N,
+                      int H, int W, int C, int act, float slope,
+                      const __nv_bfloat16* __restrict__ res, int pr,
+                      const float* __restrict__ noise, __nv_bfloat16* __restrict__ out, int po) {
+  const int V = C / 8;
+  const long long total = (long long)N * H * W * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H); const int n = (int)(t / H);
+    float f[8];
+    load8(x + i * 8, f);
+    if (ss) {
+      const float4* s4 = reinterpret_cast<const float4*>(ss + ((long long)n * C + v * 8) * 2);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 q = __ldg(s4 + j);
+        f[2 * j] = f[2 * j] * q.x + q.y;
+        f[2 * j + 1] = f[2 * j + 1] * q.z + q.w;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = act_fwd(f[j], act, slope);
+    if (res) {
+      float r[8];
+      load8(res + (((long long)n * (H + 2 * pr) + h + pr) * (W + 2 * pr) + w + pr) * C + v * 8, r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    }
+    if (noise) {
+      float r[8];
+      load8f(noise + i * 8, r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    }
+    store8(out + (((long long)n * (H + 2 * po) + h + po) * (W + 2 * po) + w + po) * C + v * 8, f);
+  }
+}
+
+// ---------------------------------------------------------------- backward finalize
+// sums[n][c] = (sum g, sum g*x) with g already masked by act'.  Produces coef[n][c][3] such that
+//   dx = c0*g + c1*x + c2, and the parameter gradients.
+__global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const float* __restrict__ mr,
+                                         int mode, int N, int C, int HW,
+                                         const float* __restrict__ gb, const float* __restrict__ ln_w,
+                                         float* __restrict__ coef, float* __restrict__ dgb,
+                                         float* __restrict__ dln_w, float* __restrict__ dln_b) {
+  const int n = blockIdx.x;
+  __shared__ float tot[2];
+  __shared__ float r0[32], r1[32];
+  if (mode == MT_NORM_LAYER) {
+    // mean_n(A g) and mean_n(A g xhat) over all (c, hw)
+    float s0 = 0.f, s1 = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const float mean = mr[((long long)n * C + c) * 2], rstd = mr[((long long)n * C + c) * 2 + 1];
+      const float sg = sums[((long long)n * C + c) * 2], sgx = sums[((long long)n * C + c) * 2 + 1];
+      const float sgxh = (sgx - mean * sg) * rstd;
+      const float A = ln_w ? ln_w[c] : 1.f;
+      s0 += A * sg; s1 += A * sgxh;
+      if (dln_w) { atomicAdd(dln_w + c, sgxh); atomicAdd(dln_b + c, sg); }
+    }
+    for (int o = 16; o; o >>= 1) {
+      s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    }
+    if ((threadIdx.x & 31) == 0) { r0[threadIdx.x >> 5] = s0; r1[threadIdx.x >> 5] = s1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t0 = 0.f, t1 = 0.f;
+      for (int i = 0; i < (blockDim.x + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
+      const float cnt = (float)C * (float)HW;
+      tot[0] = t0 / cnt; tot[1] = t1 / cnt;
+    }
+    __syncthreads();
+  }
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = mr[((long long)n * C + c) * 2], rstd = mr[((long long)n * C + c) * 2 + 1];
+    const float sg = sums[((long long)n * C + c) * 2], sgx = sums[((long long)n * C + c) * 2 + 1];
+    const float sgxh = (sgx - mean * sg) * rstd;   // sum g*xhat
+    float A = 1.f, mg, mgx;
+    if (mode == MT_NORM_LAYER) {
+      A = ln_w ? ln_w[c] : 1.f;
+      mg = tot[0]; mgx = tot[1];                    // already include A
+      // dx = rstd*(A g - mg - xhat*mgx)
+      coef[((long long)n * C + c) * 3 + 0] = rstd * A;
+      coef[((long long)n * C + c) * 3 + 1] = -rstd * rstd * mgx;
+      coef[((long long)n * C + c) * 3 + 2] = -rstd * (mg - mean * rstd * mgx);
+    } else {
+      if (mode == MT_NORM_ADAIN) {
+        A = 1.f + gb[(long long)n * 2 * C + c];
+        dgb[(long long)n * 2 * C + c] = sgxh;       // d(weight) = sum g*xhat
+        dgb[(long long)n * 2 * C + C + c] = sg;     // d(bias)   = sum g
+      }
+      mg = sg / (float)HW; mgx = sgxh / (float)HW;
+      // dx = A*rstd*(g - mg - xhat*mgx)
+      coef[((long long)n * C + c) * 3 + 0] = A * rstd;
+      coef[((long long)n * C + c) * 3 + 1] = -A * rstd * rstd * mgx;
+      coef[((long long)n * C + c) * 3 + 2] = -A * rstd * (mg - mean * rstd * mgx);
+    }
+  }
+}
+
+// dx = c0*(g*act'(y)) + c1*x + c2
+__global__ void __launch_bounds__(256)
+norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
+                      const float* __restrict__ ss, const float* __restrict__ coef, int N, int HW,
+                      int C, int act, float slope, __nv_bfloat16* __restrict__ dx) {
+  const int V = C / 8;
+  const long long total = (long long)N * HW * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    const int n = (int)(i / ((long long)HW * V));
+    float xv[8], gv[8], o[8];
+    load8(x + i * 8, xv);
+    load8(g + i * 8, gv);
+    const float* s = ss + ((long long)n * C + v * 8) * 2;
+    const float* cf = coef + ((long long)n * C + v * 8) * 3;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float y = xv[j] * __ldg(s + 2 * j) + __ldg(s + 2 * j + 1);
+      const float gg = gv[j] * act_grad_pre(y, act, slope);
+      o[j] = __ldg(cf + 3 * j) * gg + __ldg(cf + 3 * j + 1) * xv[j] + __ldg(cf + 3 * j + 2);
+    }
+    store8(dx + i * 8, o);
+  }
+}
+
+// dy[n,h,w,:] = fold(dpad)[n,h,w,:] * act'(out_pad interior)  — for conv+bias+act layers whose
+// activated output was written straight into the consumer's padded buffer (D, style encoder).
+__global__ void __launch_bounds__(256)
+act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16* __restrict__ outp,
+                    int N, int H, int W, int C, int p, int act, float slope,
+                    __nv_bfloat16* __restrict__ dy) {
+  const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
+  const long long total = (long long)N * H * W * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H); const int n = (int)(t / H);
+    int hs[3], ws[3];
+    const int nh = reflect_fold_sources(h, H, p, hs), nw = reflect_fold_sources(w, W, p, ws);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int a = 0; a < nh; ++a)
+      for (int b = 0; b < nw; ++b) {
+        float f[8];
+        load8(dpad + (((long long)n * Hp + hs[a]) * Wp + ws[b]) * C + v * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    float o[8];
+    load8(outp + (((long long)n * Hp + h + p) * Wp + w + p) * C + v * 8, o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= act_grad_pre(o[j], act, slope);
+    store8(dy + i * 8, acc);
+  }
+}
+
+}  // namespace mt
+
+using namespace mt;
+#define ST(s) ((cudaStream_t)(s))
+
+static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int HW,
+                         int C, int act, float slope, float* out, cudaStream_t st) {
+  if (C % 8 || C / 8 > 256) return -1003;
+  cudaError_t e = cudaMemsetAsync(out, 0, (size_t)N * C * 2 * sizeof(float), st);
+  if (e != cudaSuccess) return -(int)e;
+  const int V = C / 8;
+  const int lanes = 256 / V;
+  int chunks = (4 * NUM_SMS + N - 1) / N;
+  const int max_chunks = (HW + lanes * 4 - 1) / (lanes * 4);
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  const size_t smem = (size_t)lanes * V * 16 * sizeof(float);
+  if (bwd)
+    plane_reduce_kernel<true><<<N * chunks, 256, smem, st>>>(
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, HW, C, chunks, act, slope, out);
+  else
+    plane_reduce_kernel<false><<<N * chunks, 256, smem, st>>>(
+        (const __nv_bfloat16*)x, nullptr, nullptr, HW, C, chunks, 0, 0.f, out);
+  return cuda_rc();
+}
+
+extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream) {
+  return reduce_launch(false, x, nullptr, nullptr, N, HW, C, 0, 0.f, stats, ST(stream));
+}
+extern "C" int mt_norm_finalize(const float* stats, int mode, int N, int C, int HW, float eps,
+                                const float* gb, const float* ln_w, const float* ln_b, float* ss,
+                                float* mr, void* stream) {
+  if (mode == MT_NORM_ADAIN && !gb) return -1008;
+  norm_finalize_kernel<<<N, 256, 0, ST(stream)>>>(stats, mode, N, C, HW, eps, gb, ln_w, ln_b, ss, mr);
+  return cuda_rc();
+}
+extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,
+                                 int act, float slope, const void* res_pad, int res_p,
+                                 const float* noise, void* out_pad, int out_p, void* stream) {
+  if (C % 8) return -1003;
+  const long long total = (long long)N * H * W * (C / 8);
+  affine_act_fwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)x, ss, N, H, W, C, act, slope, (const __nv_bfloat16*)res_pad, res_p,
+      noise, (__nv_bfloat16*)out_pad, out_p);
+  return cuda_rc();
+}
+extern "C" int mt_norm_bwd_reduce(const void* g, const void* x, const float* ss, int N, int HW,
+                                  int C, int act, float slope, float* sums, void* stream) {
+  return reduce_launch(true, x, g, ss, N, HW, C, act, slope, sums, ST(stream));
+}
+extern "C" int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C,
+                                    int HW, const float* gb, const float* ln_w, float* coef,
+                                    float* dgb, float* dln_w, float* dln_b, void* stream) {
+  if (mode == MT_NORM_ADAIN && (!gb || !dgb)) return -1008;
+  norm_bwd_finalize_kernel<<<N, 256, 0, ST(stream)>>>(sums, mr, mode, N, C, HW, gb, ln_w, coef,
+                                                      dgb, dln_w, dln_b);
+  return cuda_rc();
+}
+extern "C" int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float* coef,
+                                 int N, int HW, int C, int act, float slope, void* dx,
+                                 void* stream) {
+  if (C % 8) return -1003;
+  const long long total = (long long)N * HW * (C / 8);
+  norm_bwd_apply_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, N, HW, C, act, slope,
+      (__nv_bfloat16*)dx);
+  return cuda_rc();
+}
+extern "C" int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C,
+                               int pad, int act, float slope, void* dy, void* stream) {
+  if (C % 8) return -1003;
+  const long long total = (long long)N * H * W * (C / 8);
+  act_bwd_fold_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)dpad, (const __nv_bfloat16*)out_pad, N, H, W, C, pad, act, slope,
+      (__nv_bfloat16*)dy);
+  return cuda_rc();
+}

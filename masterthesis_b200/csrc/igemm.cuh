@@ -1,0 +1,96 @@
+// Host-visible parameter blocks of the implicit-GEMM kernels (igemm_fwd.cu, igemm_wgrad.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace mt {
+
+enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_LRELU = 2, ACT_TANH = 3 };
+
+// D[pixels, Cout] = sum_taps A_tap[pixels, Cin] * W_tap[Cin, Cout]
+// A tile: TN x TH x TW pixels (=128 rows) x 64 channels, fetched by one 4-D TMA box.
+struct IgemmParams {
+  int tiles_w, tiles_h, tiles_n, n_tiles;  // tile grid (pixels) and Cout tiles
+  int TW, TH, TN;                          // pixel tile, TW*TH*TN == 128
+  int Wt, Ht, Nt;                          // valid extents of the pixel space
+  int kh, kw;                              // tap grid
+  int mul_h, mul_w;                        // TMA coord = pix*mul + off + tap*step
+  int off_h, off_w, step_h, step_w;
+  int w_base, w_step_r, w_step_s;          // weight tap index = base + r*step_r + s*step_s
+  int k_chunks;                            // ceil(K per tap / 64)
+  int BN;                                  // Cout tile (16..256, multiple of 16)
+  int n_store;                             // channels to store per pixel (multiple of 8)
+  int n_bias;                              // number of valid bias entries (0: no bias)
+  int stages;
+  int tmem_cols;
+  long long out_n_stride, out_h_stride, out_w_stride, out_off;  // elements
+  int act;
+  float slope;
+  const float* bias;
+  __nv_bfloat16* out;
+  float* stats;        // optional [N][n_stat_c][2] fp32 (sum, sumsq) accumulated with atomics
+  int n_stat_c;
+};
+
+// dW_tap[Cout, Cin] = sum_pixels dY[pix, Cout]^T * X_tap[pix, Cin]   (both operands MN-major)
+struct WgradParams {
+  int tiles_w, tiles_h, tiles_n;  // pixel (K) tiles
+  int TW, TH, TN;                 // pixel tile: TW*TH*TN == 64 (one K block)
+  int kh, kw;
+  int mul_h, mul_w, off_h, off_w, step_h, step_w;  // X coord = pix*mul + off + tap*step
+  int m_tiles, n_tiles;           // Cout tiles of 128, Cin tiles of BN
+  int BN;
+  int splits;                     // split-K factor over pixel tiles
+  int stages;
+  int tmem_cols;
+  int M_valid, N_valid;           // Cout, Cin(stored) extents to write
+  long long out_tap_stride, out_m_stride;  // fp32 element strides of dW[tap][m][n]
+  float* out;                     // accumulated with atomics (must be zeroed by caller)
+};
+
+int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr);
+
+int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p,
+                 cudaStream_t stream);
+int launch_wgrad(const CUtensorMap& tmA, const CUtensorMap& tmB, const WgradParams& p,
+                 cudaStream_t stream);
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+static inline int round_up(int a, int b) { return cdiv(a, b) * b; }
+
+// Pick the pixel tile (TW x TH x TN == P) with least padded volume; prefer wide tiles.
+static inline void pick_tile(int P, int Wt, int Ht, int Nt, int box_mul, int* TW, int* TH, int* TN) {
+  long long best = -1;
+  for (int tw = P; tw >= 1; tw >>= 1) {
+    if (tw * box_mul > 256) continue;
+    for (int th = P / tw; th >= 1; th >>= 1) {
+      if (th * box_mul > 256) continue;
+      int tn = P / (tw * th);
+      if (tn > 256) continue;
+      long long vol = (long long)round_up(Wt, tw) * round_up(Ht, th) * round_up(Nt, tn);
+      if (best < 0 || vol < best) {
+        best = vol;
+        *TW = tw; *TH = th; *TN = tn;
+      }
+    }
+  }
+}
+
+static inline int pick_bn(int n_logical) {
+  if (n_logical >= 256) return 256;
+  if (n_logical > 64) return 128;
+  if (n_logical > 32) return 64;
+  if (n_logical > 16) return 32;
+  return 16;
+}
+static inline int pow2_cols(int bn) {
+  int c = 32;
+  while (c < bn) c <<= 1;
+  return c;
+}
+
+
+}  // namespace mt

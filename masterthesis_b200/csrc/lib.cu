@@ -1,0 +1,24 @@
+// Library-level entry points: version and error strings.
+#include <cuda_runtime.h>
+#include "../../include/mt_b200.h"
+
+extern "C" int mt_version(void) { return 100; }
+
+extern "C" const char* mt_error_string(int code) {
+  if (code == 0) return "ok";
+  if (code <= -2000) return "cuTensorMapEncodeTiled rejected the tensor map (code = -(2000+CUresult))";
+  switch (code) {
+    case -1000: return "launch grid out of range";
+    case -1001: return "cuTensorMapEncodeTiled driver entry point unavailable (no CUDA driver?)";
+    case -1002: return "null descriptor";
+    case -1003: return "channel counts must be stored as multiples of 8 / unsupported channel count";
+    case -1004: return "unsupported stride";
+    case -1005: return "bad dimensions";
+    case -1006: return "stride-2 phase without taps";
+    case -1007: return "reflection pad must be smaller than the spatial size";
+    case -1008: return "missing parameter tensor for this norm mode";
+    default: break;
+  }
+  if (code < 0 && code > -1000) return cudaGetErrorString((cudaError_t)(-code));
+  return "unknown error";
+}

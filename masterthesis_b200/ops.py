@@ -1,0 +1,276 @@
+"""Tensor-level wrappers over the C ABI (include/mt_b200.h).
+
+Everything here takes/returns torch CUDA tensors purely as device-memory handles: allocation and
+stream come from torch, arithmetic happens in libmt_b200.so.  Activations are NHWC bf16 with the
+stored channel count rounded up to 8; a "padded" buffer is [N, H+2p, W+2p, C] with the reflection
+border materialised.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import MtConv2d, check
+
+ACT = {None: 0, "none": 0, "relu": 1, "lrelu": 2, "tanh": 3}
+NORM = {"instance": 0, "adain": 1, "layer": 2}
+LRELU_SLOPE = 0.01  # nn.LeakyReLU default (reference functions.py:34)
+EPS = 1e-5
+
+_launches = 0  # number of kernels of OURS launched (bench.py reports it)
+
+
+def launches() -> int:
+    return _launches
+
+
+def _count(n=1):
+    global _launches
+    _launches += n
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def cs(c: int) -> int:
+    """stored channel count"""
+    return (c + 7) // 8 * 8
+
+
+def _require_cuda(t: torch.Tensor):
+    if not t.is_cuda:
+        raise RuntimeError("masterthesis_b200 has no CPU path: tensors must live on a CUDA device")
+
+
+def empty_act(N, H, W, C, device, slack=False):
+    """bf16 NHWC buffer; with `slack` 64 zeroed elements follow (row-window TMA over-read)."""
+    n = N * H * W * C
+    if not slack:
+        return torch.empty((N, H, W, C), dtype=torch.bfloat16, device=device)
+    flat = torch.empty(n + 64, dtype=torch.bfloat16, device=device)
+    flat[n:].zero_()
+    return flat[:n].view(N, H, W, C)
+
+
+@dataclass(frozen=True)
+class ConvGeom:
+    """Static geometry of one Conv2d / ConvTranspose2d call site."""
+    Cin: int
+    Cout: int
+    kh: int
+    kw: int
+    stride: int = 1
+    zpad: int = 0          # logical zero padding (reflection padding lives in the input buffer)
+    transposed: bool = False
+
+    @property
+    def Cin_s(self):
+        return cs(self.Cin)
+
+    @property
+    def Cout_s(self):
+        return cs(self.Cout)
+
+    @property
+    def window(self) -> bool:
+        return (not self.transposed) and self.zpad == 0 and self.Cin_s * self.kw <= 64
+
+    def out_hw(self, Hin, Win):
+        if self.transposed:
+            return Hin * 2, Win * 2
+        return ((Hin + 2 * self.zpad - self.kh) // self.stride + 1,
+                (Win + 2 * self.zpad - self.kw) // self.stride + 1)
+
+    def desc(self, N, Hin, Win, out_pad=0, act=None) -> MtConv2d:
+        Ho, Wo = self.out_hw(Hin, Win)
+        return MtConv2d(N, Hin, Win, self.Cin, self.Cin_s, Ho, Wo, self.Cout, self.Cout_s,
+                        self.kh, self.kw, self.stride, self.zpad, Ho + 2 * out_pad, Wo + 2 * out_pad,
+                        out_pad, ACT[act], LRELU_SLOPE)
+
+
+# ----------------------------------------------------------------------------- weights
+def pack_weight(w: torch.Tensor, g: ConvGeom):
+    """fp32 master weight (OIHW, or IOHW for transposed) -> (w_fwd, w_bwd) bf16 GEMM operands."""
+    _require_cuda(w)
+    L = _lib.lib()
+    w = w.detach().contiguous().float()
+    nf = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0)
+    nb = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 1)
+    wf = torch.empty(nf, dtype=torch.bfloat16, device=w.device)
+    wb = torch.empty(nb, dtype=torch.bfloat16, device=w.device)
+    check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed), int(g.window),
+                                _p(wf), _p(wb), _stream()), "mt_pack_conv_weight")
+    _count()
+    return wf, wb
+
+
+# ----------------------------------------------------------------------------- convolutions
+def conv_fwd(x, wf, bias, g: ConvGeom, act=None, out_pad=0, out=None):
+    """x: [N,Hin,Win,Cin_s] -> [N,Ho+2op,Wo+2op,Cout_s]; border of `out` is NOT filled here."""
+    _require_cuda(x)
+    N, Hin, Win, C = x.shape
+    assert C == g.Cin_s and x.dtype == torch.bfloat16 and x.is_contiguous()
+    d = g.desc(N, Hin, Win, out_pad, act)
+    if out is None:
+        out = empty_act(N, d.out_H, d.out_W, g.Cout_s, x.device)
+    fn = _lib.lib().mt_conv_transpose2d_fwd if g.transposed else _lib.lib().mt_conv2d_fwd
+    check(fn(ctypes.byref(d), _p(x), _p(wf), _p(bias), _p(out), _stream()), "conv_fwd")
+    _count(4 if g.transposed else 1)
+    return out
+
+
+def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
+    """dy: dense [N,Ho,Wo,Cout_s] -> dx [N,Hin,Win,Cin_s] (gradient of the padded input buffer)."""
+    _require_cuda(dy)
+    N = dy.shape[0]
+    assert dy.is_contiguous() and dy.shape[3] == g.Cout_s
+    d = g.desc(N, Hin, Win)
+    assert (d.Hout, d.Wout) == tuple(dy.shape[1:3]), (d.Hout, d.Wout, dy.shape)
+    dx = empty_act(N, Hin, Win, g.Cin_s, dy.device)
+    fn = _lib.lib().mt_conv_transpose2d_dgrad if g.transposed else _lib.lib().mt_conv2d_dgrad
+    check(fn(ctypes.byref(d), _p(dy), _p(wb), _p(dx), _stream()), "conv_dgrad")
+    _count(4 if (g.stride == 2 and not g.transposed) else 1)
+    return dx
+
+
+def conv_wgrad(x, dy, g: ConvGeom):
+    """-> fp32 weight gradient in the master layout (OIHW, or IOHW for transposed)."""
+    _require_cuda(x)
+    N, Hin, Win, _ = x.shape
+    L = _lib.lib()
+    d = g.desc(N, Hin, Win)
+    if g.transposed:
+        n = g.kh * g.kw * g.Cin * g.Cout_s
+    elif g.window:
+        n = g.kh * g.Cout * 64
+    else:
+        n = g.kh * g.kw * g.Cout * g.Cin_s
+    packed = torch.zeros(n, dtype=torch.float32, device=x.device)
+    fn = L.mt_conv_transpose2d_wgrad if g.transposed else L.mt_conv2d_wgrad
+    check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), _stream()), "conv_wgrad")
+    shape = (g.Cin, g.Cout, g.kh, g.kw) if g.transposed else (g.Cout, g.Cin, g.kh, g.kw)
+    dw = torch.empty(shape, dtype=torch.float32, device=x.device)
+    check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
+                                 int(g.window), _p(dw), _stream()), "unpack_wgrad")
+    _count(2)
+    return dw
+
+
+# ----------------------------------------------------------------------------- layout
+def image_to_nhwc(img, onehot, pad, Cs=None):
+    _require_cuda(img)
+    N, Ci, H, W = img.shape
+    nd = 0 if onehot is None else onehot.shape[1]
+    Cs = Cs or cs(Ci + nd)
+    out = empty_act(N, H + 2 * pad, W + 2 * pad, Cs, img.device, slack=True)
+    img = img.contiguous().float()
+    oh = None if onehot is None else onehot.contiguous().float()
+    check(_lib.lib().mt_image_to_nhwc(_p(img), _p(oh), N, Ci, nd, H, W, pad, Cs, _p(out), _stream()),
+          "image_to_nhwc")
+    _count()
+    return out
+
+
+def image_grad_from_nhwc(dpad, Ci, H, W, pad):
+    N, _, _, Cs = dpad.shape
+    dimg = torch.empty((N, Ci, H, W), dtype=torch.float32, device=dpad.device)
+    check(_lib.lib().mt_image_grad_from_nhwc(_p(dpad), N, Ci, H, W, pad, Cs, _p(dimg), _stream()),
+          "image_grad_from_nhwc")
+    _count()
+    return dimg
+
+
+def reflect_border_(buf, pad):
+    if pad == 0:
+        return buf
+    N, Hp, Wp, C = buf.shape
+    check(_lib.lib().mt_reflect_border(_p(buf), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _stream()),
+          "reflect_border")
+    _count()
+    return buf
+
+
+def reflect_fold(dpad, pad):
+    N, Hp, Wp, C = dpad.shape
+    if pad == 0:
+        return dpad
+    H, W = Hp - 2 * pad, Wp - 2 * pad
+    dense = empty_act(N, H, W, C, dpad.device)
+    check(_lib.lib().mt_reflect_fold(_p(dpad), N, H, W, C, pad, _p(dense), _stream()), "reflect_fold")
+    _count()
+    return dense
+
+
+def add_interior_(dpad, dense, pad):
+    N, H, W, C = dense.shape
+    check(_lib.lib().mt_add_interior(_p(dpad), _p(dense), N, H, W, C, pad, _stream()), "add_interior")
+    _count()
+    return dpad
+
+
+# ----------------------------------------------------------------------------- norms
+def plane_stats(x):
+    N, H, W, C = x.shape
+    stats = torch.empty((N, C, 2), dtype=torch.float32, device=x.device)
+    check(_lib.lib().mt_plane_stats(_p(x), N, H * W, C, _p(stats), _stream()), "plane_stats")
+    _count()
+    return stats
+
+
+def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None):
+    N, C, _ = stats.shape
+    ss = torch.empty_like(stats)
+    mr = torch.empty_like(stats)
+    check(_lib.lib().mt_norm_finalize(_p(stats), NORM[mode], N, C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
+                                      _p(ss), _p(mr), _stream()), "norm_finalize")
+    _count()
+    return ss, mr
+
+
+def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, out=None):
+    N, H, W, C = x.shape
+    if out is None:
+        out = empty_act(N, H + 2 * out_p, W + 2 * out_p, C, x.device)
+    check(_lib.lib().mt_affine_act_fwd(_p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(res_pad),
+                                       res_p, _p(noise), _p(out), out_p, _stream()), "affine_act_fwd")
+    _count()
+    return out
+
+
+def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None):
+    """g, x dense [N,H,W,C].  Returns (dx, dgb | None, dln_w | None, dln_b | None)."""
+    N, H, W, C = x.shape
+    L = _lib.lib()
+    dev = x.device
+    sums = torch.empty((N, C, 2), dtype=torch.float32, device=dev)
+    check(L.mt_norm_bwd_reduce(_p(g), _p(x), _p(ss), N, H * W, C, ACT[act], LRELU_SLOPE, _p(sums),
+                               _stream()), "norm_bwd_reduce")
+    coef = torch.empty((N, C, 3), dtype=torch.float32, device=dev)
+    dgb = torch.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
+    dlw = torch.zeros(C, dtype=torch.float32, device=dev) if (mode == "layer" and ln_w is not None) else None
+    dlb = torch.zeros(C, dtype=torch.float32, device=dev) if dlw is not None else None
+    check(L.mt_norm_bwd_finalize(_p(sums), _p(mr), NORM[mode], N, C, H * W, _p(gb), _p(ln_w), _p(coef),
+                                 _p(dgb), _p(dlw), _p(dlb), _stream()), "norm_bwd_finalize")
+    dx = torch.empty_like(x)
+    check(L.mt_norm_bwd_apply(_p(g), _p(x), _p(ss), _p(coef), N, H * W, C, ACT[act], LRELU_SLOPE,
+                              _p(dx), _stream()), "norm_bwd_apply")
+    _count(3)
+    return dx, dgb, dlw, dlb
+
+
+def act_bwd_fold(dpad, out_pad, pad, act):
+    N, Hp, Wp, C = out_pad.shape
+    H, W = Hp - 2 * pad, Wp - 2 * pad
+    dy = empty_act(N, H, W, C, dpad.device)
+    check(_lib.lib().mt_act_bwd_fold(_p(dpad), _p(out_pad), N, H, W, C, pad, ACT[act], LRELU_SLOPE,
+                                     _p(dy), _stream()), "act_bwd_fold")
+    _count()
+    return dy

@@ -1,0 +1,211 @@
+"""Op-level parity cases: each CUDA entry point vs the same op in plain PyTorch fp32 on the same
+bf16-rounded inputs (reference call sites: src/models/core/blocks.py:30-42,69-73, norm.py:5-33).
+Used by tests/test_kernels_gpu.py and tools/gpu_probe.py.  Returns relative errors
+max|a-b| / max|b|; bf16 storage + fp32 accumulate bounds them by ~2^-8.
+"""
+import torch
+import torch.nn.functional as F
+
+from masterthesis_b200 import ops
+from masterthesis_b200.ops import ConvGeom
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-12)).item()
+
+
+def bf(x):
+    return x.to(torch.bfloat16).float()
+
+
+def to_nhwc(x, Cs=None):
+    """NCHW fp32 -> NHWC bf16 with channels zero-padded to the stored count."""
+    N, C, H, W = x.shape
+    Cs = Cs or ops.cs(C)
+    out = torch.zeros(N, H, W, Cs, dtype=torch.bfloat16, device=x.device)
+    out[..., :C] = x.permute(0, 2, 3, 1).to(torch.bfloat16)
+    return out
+
+
+def from_nhwc(x, C):
+    return x[..., :C].permute(0, 3, 1, 2).float()
+
+
+def conv_case(N, Cin, Cout, H, W, k, stride, rpad, zpad=0, bias=True, act=None, out_pad=0, seed=0):
+    """Conv2d forward + dgrad + wgrad.  rpad: reflection padding materialised in the input."""
+    torch.manual_seed(seed)
+    g = ConvGeom(Cin, Cout, k, k, stride, zpad)
+    x = bf(torch.randn(N, Cin, H, W, device=DEV))
+    xp = F.pad(x, (rpad,) * 4, mode="reflect") if rpad else x
+    w = bf(torch.randn(Cout, Cin, k, k, device=DEV) * 0.05)
+    b = torch.randn(Cout, device=DEV) if bias else None
+    xp_ref = xp.clone().requires_grad_(True)
+    w_ref = w.clone().requires_grad_(True)
+    y_ref = F.conv2d(xp_ref, w_ref, b, stride=stride, padding=zpad)
+    if act == "lrelu":
+        y_ref = F.leaky_relu(y_ref, 0.01)
+    elif act == "relu":
+        y_ref = F.relu(y_ref)
+    dy = bf(torch.randn_like(y_ref))
+    y_ref.backward(dy)
+
+    if g.window:
+        xn = ops.image_to_nhwc(x, None, rpad)          # slack-padded buffer for the row-window TMA
+    else:
+        xn = to_nhwc(xp)
+    wf, wb = ops.pack_weight(w, g)
+    y = ops.conv_fwd(xn, wf, b, g, act=act, out_pad=out_pad)
+    if out_pad:
+        y = y[:, out_pad:-out_pad, out_pad:-out_pad, :].contiguous()
+    res = {"fwd": rel(from_nhwc(y, Cout), y_ref.detach())}
+    if act is None:
+        dyn = to_nhwc(dy)
+        dx = ops.conv_dgrad(dyn, wb, g, xn.shape[1], xn.shape[2])
+        res["dgrad"] = rel(from_nhwc(dx, Cin), xp_ref.grad)
+        dw = ops.conv_wgrad(xn, dyn, g)
+        res["wgrad"] = rel(dw, w_ref.grad)
+    return res
+
+
+def convT_case(N, Cin, Cout, H, W, bias=True, act=None, seed=0):
+    torch.manual_seed(seed)
+    g = ConvGeom(Cin, Cout, 3, 3, 2, 1, transposed=True)
+    x = bf(torch.randn(N, Cin, H, W, device=DEV))
+    w = bf(torch.randn(Cin, Cout, 3, 3, device=DEV) * 0.05)
+    b = torch.randn(Cout, device=DEV) if bias else None
+    x_ref = x.clone().requires_grad_(True)
+    w_ref = w.clone().requires_grad_(True)
+    y_ref = F.conv_transpose2d(x_ref, w_ref, b, stride=2, padding=1, output_padding=1)
+    dy = bf(torch.randn_like(y_ref))
+    y_ref.backward(dy)
+    xn = to_nhwc(x)
+    wf, wb = ops.pack_weight(w, g)
+    y = ops.conv_fwd(xn, wf, b, g)
+    dyn = to_nhwc(dy)
+    dx = ops.conv_dgrad(dyn, wb, g, H, W)
+    dw = ops.conv_wgrad(xn, dyn, g)
+    return {"fwd": rel(from_nhwc(y, Cout), y_ref.detach()),
+            "dgrad": rel(from_nhwc(dx, Cin), x_ref.grad),
+            "wgrad": rel(dw, w_ref.grad)}
+
+
+def norm_case(mode, N, C, H, W, act, residual=False, noise=False, seed=0):
+    torch.manual_seed(seed)
+    x = bf(torch.randn(N, C, H, W, device=DEV) * 2 + 0.5)
+    x_ref = x.clone().requires_grad_(True)
+    gb = lw = lb = None
+    params = []
+    if mode == "adain":
+        gb = (torch.randn(N, 2 * C, device=DEV) * 0.5).requires_grad_(True)
+        params = [gb]
+        y_ref = (1 + gb[:, :C, None, None]) * F.instance_norm(x_ref) + gb[:, C:, None, None]
+    elif mode == "instance":
+        y_ref = F.instance_norm(x_ref)
+    else:
+        lw = (torch.rand(C, device=DEV) + 0.5).requires_grad_(True)
+        lb = torch.randn(C, device=DEV).requires_grad_(True)
+        params = [lw, lb]
+        y_ref = F.layer_norm(x_ref, x_ref.shape[1:], lw.view(C, 1, 1).expand(C, H, W),
+                             lb.view(C, 1, 1).expand(C, H, W))
+    if act == "relu":
+        y_ref = F.relu(y_ref)
+    elif act == "lrelu":
+        y_ref = F.leaky_relu(y_ref, 0.01)
+    res_t = nz = None
+    if residual:
+        res_t = bf(torch.randn(N, C, H, W, device=DEV))
+        y_ref = y_ref + res_t
+    if noise:
+        nz = torch.randn(N, C, H, W, device=DEV)
+        y_ref = y_ref + nz
+    g = bf(torch.randn_like(y_ref))
+    y_ref.backward(g)
+
+    xn = to_nhwc(x)
+    stats = ops.plane_stats(xn)
+    ss, mr = ops.norm_finalize(stats, mode, H * W, None if gb is None else gb.detach(),
+                               None if lw is None else lw.detach(), None if lb is None else lb.detach())
+    res_pad = None
+    if residual:
+        res_pad = to_nhwc(F.pad(res_t, (1, 1, 1, 1), mode="reflect"))
+    out = ops.affine_act_fwd(xn, ss, act=act, res_pad=res_pad, res_p=1,
+                             noise=None if nz is None else nz.permute(0, 2, 3, 1).contiguous(),
+                             out_p=1)
+    ops.reflect_border_(out, 1)
+    out_ref = F.pad(y_ref.detach(), (1, 1, 1, 1), mode="reflect")
+    r = {"fwd": rel(from_nhwc(out, C), out_ref)}
+    dx, dgb, dlw, dlb = ops.norm_bwd(to_nhwc(g), xn, ss, mr, mode, act=act,
+                                     gb=None if gb is None else gb.detach(),
+                                     ln_w=None if lw is None else lw.detach())
+    r["dx"] = rel(from_nhwc(dx, C), x_ref.grad)
+    if mode == "adain":
+        r["dgb"] = rel(dgb, gb.grad)
+    if mode == "layer":
+        r["dlw"] = rel(dlw, lw.grad)
+        r["dlb"] = rel(dlb, lb.grad)
+    return r
+
+
+def pad_case(N, C, H, W, p, seed=0):
+    """reflect border / fold / add_interior / act_bwd_fold / image pack + grad."""
+    torch.manual_seed(seed)
+    x = bf(torch.randn(N, C, H, W, device=DEV))
+    x_ref = x.clone().requires_grad_(True)
+    xp_ref = F.pad(x_ref, (p,) * 4, mode="reflect")
+    gpad = bf(torch.randn_like(xp_ref))
+    xp_ref.backward(gpad)
+    buf = torch.zeros(N, H + 2 * p, W + 2 * p, C, dtype=torch.bfloat16, device=DEV)
+    buf[:, p:H + p, p:W + p, :] = to_nhwc(x)
+    ops.reflect_border_(buf, p)
+    r = {"border": rel(from_nhwc(buf, C), xp_ref.detach())}
+    dense = ops.reflect_fold(to_nhwc(gpad), p)
+    r["fold"] = rel(from_nhwc(dense, C), x_ref.grad)
+    acc = to_nhwc(gpad).clone()
+    ops.add_interior_(acc, to_nhwc(x), p)
+    ref = gpad.clone()
+    ref[:, :, p:H + p, p:W + p] += x
+    r["add_interior"] = rel(from_nhwc(acc, C), ref)
+    dy = ops.act_bwd_fold(to_nhwc(gpad), buf, p, "lrelu")
+    r["act_bwd_fold"] = rel(from_nhwc(dy, C), x_ref.grad * torch.where(x > 0, 1.0, 0.01))
+    # image edge
+    img = torch.rand(N, 3, H, W, device=DEV) * 2 - 1
+    onehot = torch.eye(4, device=DEV)[torch.arange(N) % 4]
+    packed = ops.image_to_nhwc(img, onehot, p)
+    full = torch.cat([img, onehot[:, :, None, None].expand(N, 4, H, W)], 1)
+    r["image_pack"] = rel(from_nhwc(packed, 7), F.pad(bf(full), (p,) * 4, mode="reflect"))
+    img_ref = img.clone().requires_grad_(True)
+    F.pad(img_ref, (p,) * 4, mode="reflect").backward(gpad[:, :3])
+    gp8 = to_nhwc(gpad[:, :3], 8)
+    r["image_grad"] = rel(ops.image_grad_from_nhwc(gp8, 3, H, W, p), img_ref.grad)
+    return r
+
+
+CASES = {
+    # the hot shape: ResnetBlock / AdaINResnetBlock conv (blocks.py:131-134,150-151)
+    "conv3x3_256": lambda: conv_case(2, 256, 256, 64, 64, 3, 1, 1, bias=False),
+    "conv3x3_s2": lambda: conv_case(2, 64, 128, 64, 64, 3, 2, 1),
+    "conv3x3_s2_act_pad": lambda: conv_case(2, 64, 128, 32, 32, 3, 2, 1, act="lrelu", out_pad=1),
+    "stem7x7": lambda: conv_case(2, 3, 64, 64, 64, 7, 1, 3),
+    "stem4x4_s2": lambda: conv_case(2, 7, 64, 64, 64, 4, 2, 1),
+    "stem3x3_s2": lambda: conv_case(2, 3, 64, 64, 64, 3, 2, 1),
+    "conv1x1": lambda: conv_case(2, 128, 256, 16, 16, 1, 1, 0),
+    "dis_tail": lambda: conv_case(3, 1024, 1024, 8, 8, 3, 2, 1),
+    "odd_channels": lambda: conv_case(1, 32, 48, 20, 12, 3, 1, 1),
+    "conv4x4_s2_zpad": lambda: conv_case(2, 64, 128, 32, 32, 4, 2, 0, zpad=1),
+    "conv7x7_s2_256": lambda: conv_case(1, 256, 256, 32, 32, 7, 2, 1),
+    "convT_256_128": lambda: convT_case(2, 256, 128, 16, 16),
+    "convT_128_64": lambda: convT_case(1, 128, 64, 24, 40, bias=False),
+    "in_relu": lambda: norm_case("instance", 2, 256, 32, 32, "relu"),
+    "in_res_noise": lambda: norm_case("instance", 2, 128, 16, 24, None, residual=True, noise=True),
+    "adain_relu": lambda: norm_case("adain", 3, 256, 16, 16, "relu"),
+    "adain_res": lambda: norm_case("adain", 2, 64, 16, 16, None, residual=True),
+    "ln_relu": lambda: norm_case("layer", 2, 128, 32, 32, "relu"),
+    "in_lrelu_c1024": lambda: norm_case("instance", 2, 1024, 8, 8, "lrelu"),
+    "pad1": lambda: pad_case(2, 64, 16, 24, 1),
+    "pad3": lambda: pad_case(2, 8, 32, 32, 3),
+}
+
+TOL = 1e-2
