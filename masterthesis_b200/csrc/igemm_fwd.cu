@@ -173,8 +173,8 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmPara
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(igemm_conv_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return -(int)e;
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    if (e != cudaSuccess) return -(3000 + (int)e);
     attr_set = true;
   }
   const long long grid = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.n_tiles;

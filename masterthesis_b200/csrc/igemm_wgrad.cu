@@ -152,8 +152,8 @@ int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradPara
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(igemm_wgrad_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return -(int)e;
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    if (e != cudaSuccess) return -(3000 + (int)e);
     attr_set = true;
   }
   const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;

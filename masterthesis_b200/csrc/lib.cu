@@ -6,6 +6,7 @@ extern "C" int mt_version(void) { return 100; }
 
 extern "C" const char* mt_error_string(int code) {
   if (code == 0) return "ok";
+  if (code <= -3000) return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed (code = -(3000+cudaError))";
   if (code <= -2000) return "cuTensorMapEncodeTiled rejected the tensor map (code = -(2000+CUresult))";
   switch (code) {
     case -1000: return "launch grid out of range";

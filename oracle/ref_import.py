@@ -1,0 +1,84 @@
+"""TEST INFRASTRUCTURE — import the UNMODIFIED reference (/root/reference/src) as a library.
+
+Only usable where /root/reference exists (the build container), i.e. by
+oracle/make_golden.py and by CPU tests that pin the oracle against the reference directly.
+Nothing on the GPU box imports this.  Two modules the reference imports but that are absent
+here and never touch arithmetic are stubbed (tensorboardX: model.py:13, matplotlib.cm:
+utils.py:7), and the two CPU-incompatible `.get_device()` lines (misc.py:25, loss.py:60-62)
+are patched harness-side to `.device` so the training step can run on CPU.
+"""
+import os
+import sys
+import types
+
+REF_SRC = "/root/reference/src"
+
+
+def available() -> bool:
+    return os.path.isdir(REF_SRC)
+
+
+def import_reference():
+    if not available():
+        raise RuntimeError("reference sources not present on this machine")
+    if "tensorboardX" not in sys.modules:
+        tb = types.ModuleType("tensorboardX")
+
+        class SummaryWriter:  # noqa: D401 - stub
+            def __init__(self, *a, **k):
+                pass
+
+            def add_scalar(self, *a, **k):
+                pass
+        tb.SummaryWriter = SummaryWriter
+        sys.modules["tensorboardX"] = tb
+    if "matplotlib" not in sys.modules:
+        mpl = types.ModuleType("matplotlib")
+        cm = types.ModuleType("matplotlib.cm")
+        mpl.cm = cm
+        sys.modules["matplotlib"] = mpl
+        sys.modules["matplotlib.cm"] = cm
+    # the reference's top-level module names (models, utils, dataset) must win the import
+    for name in ("models", "utils", "dataset"):
+        mod = sys.modules.get(name)
+        if mod is not None and not getattr(mod, "__file__", "").startswith(REF_SRC):
+            raise RuntimeError(f"module name clash: {name} already imported from {mod.__file__}")
+    if REF_SRC not in sys.path:
+        sys.path.insert(0, REF_SRC)
+    import torch
+    import models  # noqa: F401  (reference package)
+    from models.core import misc, loss
+
+    def noise_forward(self, x):
+        if not self.training:
+            return x
+        return x + torch.randn(x.size()).to(x.device)
+
+    def gan_forward(self, inp, trg_is_real, is_dis=None):
+        if "wgangp" in self.loss_type:
+            return -inp.mean() if trg_is_real else inp.mean()
+        trg = (self.ones if trg_is_real else self.zeros).expand_as(inp).to(inp.device)
+        return self.loss(inp, trg)
+
+    misc.GaussianNoiseLayer.forward = noise_forward
+    loss.GANLoss.forward = gan_forward
+    return models
+
+
+def default_args(**over):
+    """argparse.Namespace with the reference's defaults (arguments.py:20-46,85-118)."""
+    import argparse
+    d = dict(
+        input_dim=3, output_dim=3, dim=64, init_type="normal", init_gain=0.02, use_dropout=False,
+        num_domains=4, mode="train", concat=False, reparam=False, use_dis_content=False,
+        latent_dim=8, up_type="transpose", dec_norm="layer", enc_norm="instance", batch_size=1,
+        crop_size=256, resume=None, resume_opt=None, gpu_ids=[], dis_norm=None, norm_feat=False,
+        lr=1e-4, wd=1e-4, beta1=0.5, beta2=0.999, lr_policy="step", n_iters=1000000, last_iter=-1,
+        n_iter_decay=600000, d_iter=3, lambda_rec=10.0, lambda_cls=1.0, lambda_cls_G=5.0,
+        lambda_style=5.0, gan_mode="vanilla", ms_dis=False, dis_sn=False, num_scales=3,
+        use_ragan=False, lambda_perceptual=1.0, vgg_type="vgg19", vgg_loss=None,
+        vgg_layers=["conv5_4"], layer_weights=[1.0], logdir="/tmp/mt_logs",
+        checkpoint_dir="/tmp/mt_ckpt", display_dir="/tmp/mt_disp",
+    )
+    d.update(over)
+    return argparse.Namespace(**d)
