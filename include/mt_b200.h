@@ -111,6 +111,33 @@ int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float
 int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C, int pad,
                     int act, float slope, void* dy, void* stream);
 
+/* ---- style-encoder pooling algebra, RGB head, content regulariser --------------------------- */
+/* nn.AvgPool2d(2,2) over the interior of a padded buffer -> dense [N,H/2,W/2,C]  blocks.py:113 */
+int mt_avgpool2_fwd(const void* x_pad, int pad, int N, int H, int W, int C, void* out,
+                    void* stream);
+/* dpad[interior] += 0.25 * upsample(dpooled) */
+int mt_avgpool2_bwd_add(const void* dpooled, void* dpad, int pad, int N, int H, int W, int C,
+                        void* stream);
+/* out_pad[interior] = act(avgpool2(c) + d): DownResnetBlock sum (blocks.py:118-119) fused with
+ * the in-place LeakyReLU that is the only consumer of the sum (blocks.py:107, networks.py:123) */
+int mt_pool_add_act_fwd(const void* c, const void* d, int N, int H, int W, int C, int act,
+                        float slope, void* out_pad, int out_p, void* stream);
+int mt_pool_add_act_bwd(const void* dout_pad, const void* out_pad, int N, int H, int W, int C,
+                        int out_p, int act, float slope, void* dd, void* dc, void* stream);
+/* nn.AdaptiveAvgPool2d(1)  networks.py:124 */
+int mt_gap_fwd(const void* x, int N, int HW, int C, float* out, void* stream);
+int mt_gap_bwd(const float* dout, int N, int HW, int C, void* dx, void* stream);
+/* ConvTranspose2d(C -> Co<=4, k=1, no bias) + tanh, NHWC bf16 -> NCHW fp32  networks.py:248-251 */
+int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int C, int Co, float* y,
+                    void* stream);
+int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, const float* w, int N, int HW,
+                    int C, int Co, void* dx, float* dw, void* stream);
+/* sum(x^2) over the interior (adain_model.py:396-399) and dx = scale * x on the interior */
+int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, int pad, float* out,
+                      void* stream);
+int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C, int pad,
+                      void* dx_pad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,377 @@
+// Remaining HBM-bound pieces of the path: the style encoder's pooling / shortcut algebra
+// (blocks.py:93-119, networks.py:123-124), the RGB head (ConvTranspose2d 1x1 -> tanh,
+// networks.py:248-251) and the content-code L2 regulariser (adain_model.py:396-399).
+#include "../../include/mt_b200.h"
+#include "ew_common.cuh"
+
+namespace mt {
+
+// out[n,h2,w2,:] = mean of the 2x2 window of the interior of x_pad        (nn.AvgPool2d(2,2))
+__global__ void __launch_bounds__(256)
+avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int p, int N, int H, int W, int C,
+                    __nv_bfloat16* __restrict__ out) {
+  const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
+  const long long total = (long long)N * Ho * Wo * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % Wo); t /= Wo;
+    const int h = (int)(t % Ho); const int n = (int)(t / Ho);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        float f[8];
+        load8(x + (((long long)n * Hp + 2 * h + dy + p) * Wp + 2 * w + dx + p) * C + v * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= 0.25f;
+    store8(out + i * 8, acc);
+  }
+}
+
+// dpad[n, h+p, w+p, :] += 0.25 * dpooled[n, h/2, w/2, :]
+__global__ void __launch_bounds__(256)
+avgpool2_bwd_add_kernel(const __nv_bfloat16* __restrict__ dpo, __nv_bfloat16* __restrict__ dpad,
+                        int p, int N, int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
+  const long long total = (long long)N * H * W * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H); const int n = (int)(t / H);
+    if (h / 2 >= Ho || w / 2 >= Wo) continue;
+    float g[8], a[8];
+    load8(dpo + (((long long)n * Ho + h / 2) * Wo + w / 2) * C + v * 8, g);
+    __nv_bfloat16* d = dpad + (((long long)n * Hp + h + p) * Wp + w + p) * C + v * 8;
+    load8(d, a);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] += 0.25f * g[j];
+    store8(d, a);
+  }
+}
+
+// out_pad[interior] = act(avgpool2(c) + d)          (DownResnetBlock tail + next LeakyReLU)
+__global__ void __launch_bounds__(256)
+pool_add_act_fwd_kernel(const __nv_bfloat16* __restrict__ c, const __nv_bfloat16* __restrict__ d,
+                        int N, int H, int W, int C, int act, float slope,
+                        __nv_bfloat16* __restrict__ out, int po) {
+  const int Ho = H / 2, Wo = W / 2, V = C / 8;
+  const long long total = (long long)N * Ho * Wo * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % Wo); t /= Wo;
+    const int h = (int)(t % Ho); const int n = (int)(t / Ho);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        float f[8];
+        load8(c + (((long long)n * H + 2 * h + dy) * W + 2 * w + dx) * C + v * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    float dv[8];
+    load8(d + i * 8, dv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = act_fwd(acc[j] * 0.25f + dv[j], act, slope);
+    store8(out + (((long long)n * (Ho + 2 * po) + h + po) * (Wo + 2 * po) + w + po) * C + v * 8, acc);
+  }
+}
+
+// g = fold(dout_pad) * act'(out);  dd = g (half res);  dc = 0.25 * g upsampled (full res)
+__global__ void __launch_bounds__(256)
+pool_add_act_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
+                        int N, int H, int W, int C, int po, int act, float slope,
+                        __nv_bfloat16* __restrict__ dd, __nv_bfloat16* __restrict__ dc) {
+  const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = Ho + 2 * po, Wp = Wo + 2 * po;
+  const long long total = (long long)N * Ho * Wo * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % Wo); t /= Wo;
+    const int h = (int)(t % Ho); const int n = (int)(t / Ho);
+    int hs[3], ws[3];
+    const int nh = reflect_fold_sources(h, Ho, po, hs), nw = reflect_fold_sources(w, Wo, po, ws);
+    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int a = 0; a < nh; ++a)
+      for (int b = 0; b < nw; ++b) {
+        float f[8];
+        load8(dout + (((long long)n * Hp + hs[a]) * Wp + ws[b]) * C + v * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] += f[j];
+      }
+    float o[8];
+    load8(outp + (((long long)n * Hp + h + po) * Wp + w + po) * C + v * 8, o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= act_grad_pre(o[j], act, slope);
+    store8(dd + i * 8, g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= 0.25f;
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx)
+        store8(dc + (((long long)n * H + 2 * h + dy) * W + 2 * w + dx) * C + v * 8, g);
+  }
+}
+
+// nn.AdaptiveAvgPool2d(1): x [N,HW,C] bf16 -> out [N,C] fp32
+__global__ void __launch_bounds__(256)
+gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C, float* __restrict__ out) {
+  extern __shared__ float red[];
+  const int V = C / 8, lanes = blockDim.x / V, n = blockIdx.x;
+  const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (pl < lanes)
+    for (int p = pl; p < HW; p += lanes) {
+      float f[8];
+      load8(x + ((long long)n * HW + p) * C + v * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+  if (pl < lanes)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[(pl * V + v) * 8 + j] = acc[j];
+  __syncthreads();
+  for (int t = threadIdx.x; t < C; t += blockDim.x) {
+    float s = 0.f;
+    for (int l = 0; l < lanes; ++l) s += red[l * C + t];
+    out[(long long)n * C + t] = s / (float)HW;
+  }
+}
+__global__ void __launch_bounds__(256)
+gap_bwd_kernel(const float* __restrict__ dout, int N, int HW, int C, __nv_bfloat16* __restrict__ dx) {
+  const int V = C / 8;
+  const long long total = (long long)N * HW * V;
+  const float inv = 1.f / (float)HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    const int n = (int)(i / ((long long)HW * V));
+    float g[8];
+    load8f(dout + (long long)n * C + v * 8, g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= inv;
+    store8(dx + i * 8, g);
+  }
+}
+
+// RGB head: y[n,o,h,w] = tanh(sum_c x[n,h,w,c] * w[c][o]),  o < Co <= 4, NCHW fp32 output.
+__global__ void __launch_bounds__(256)
+rgb_head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, int N,
+                    int HW, int C, int Co, float* __restrict__ y) {
+  extern __shared__ float ws[];  // [C][4]
+  for (int i = threadIdx.x; i < C * 4; i += blockDim.x)
+    ws[i] = (i & 3) < Co ? wgt[(i >> 2) * Co + (i & 3)] : 0.f;
+  __syncthreads();
+  const long long total = (long long)N * HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / HW);
+    const int pix = (int)(i % HW);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    for (int v = 0; v < C / 8; ++v) {
+      float f[8];
+      load8(x + i * C + v * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 q = *reinterpret_cast<const float4*>(ws + (v * 8 + j) * 4);
+        a0 += f[j] * q.x; a1 += f[j] * q.y; a2 += f[j] * q.z; a3 += f[j] * q.w;
+      }
+    }
+    const float a[4] = {a0, a1, a2, a3};
+    for (int o = 0; o < Co; ++o) y[((long long)n * Co + o) * HW + pix] = tanhf(a[o]);
+  }
+}
+
+// g_o = dy_o*(1-y_o^2); dx[c] = sum_o g_o w[c][o]; dw[c][o] += sum_pix x[c] g_o
+__global__ void __launch_bounds__(256)
+rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                    const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, int N,
+                    int HW, int C, int Co, __nv_bfloat16* __restrict__ dx, float* __restrict__ dw) {
+  extern __shared__ float sm[];  // ws[C*4] | red[lanes*V*32]
+  float* ws = sm;
+  float* red = sm + C * 4;
+  for (int i = threadIdx.x; i < C * 4; i += blockDim.x)
+    ws[i] = (i & 3) < Co ? wgt[(i >> 2) * Co + (i & 3)] : 0.f;
+  __syncthreads();
+  const int V = C / 8, lanes = blockDim.x / V;
+  const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  float acc[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+  const long long total = (long long)N * HW;
+  if (pl < lanes)
+    for (long long i = (long long)blockIdx.x * lanes + pl; i < total; i += (long long)gridDim.x * lanes) {
+      const int n = (int)(i / HW);
+      const int pix = (int)(i % HW);
+      float g[4] = {0, 0, 0, 0};
+      for (int o = 0; o < Co; ++o) {
+        const long long k = ((long long)n * Co + o) * HW + pix;
+        const float yy = __ldg(y + k);
+        g[o] = __ldg(dy + k) * (1.f - yy * yy);
+      }
+      float f[8], d[8];
+      load8(x + i * C + v * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 q = *reinterpret_cast<const float4*>(ws + (v * 8 + j) * 4);
+        d[j] = g[0] * q.x + g[1] * q.y + g[2] * q.z + g[3] * q.w;
+        acc[j][0] += f[j] * g[0]; acc[j][1] += f[j] * g[1];
+        acc[j][2] += f[j] * g[2]; acc[j][3] += f[j] * g[3];
+      }
+      store8(dx + i * C + v * 8, d);
+    }
+  if (pl < lanes)
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int o = 0; o < 4; ++o) red[(pl * V + v) * 32 + j * 4 + o] = acc[j][o];
+  __syncthreads();
+  for (int t = threadIdx.x; t < V * 32; t += blockDim.x) {
+    float s = 0.f;
+    for (int l = 0; l < lanes; ++l) s += red[l * V * 32 + t];
+    const int c = (t / 32) * 8 + (t % 32) / 4, o = t & 3;
+    if (o < Co) atomicAdd(dw + c * Co + o, s);
+  }
+}
+
+// sum of squares over the interior of a padded buffer (fp32 scalar, atomics) and its gradient
+__global__ void __launch_bounds__(256)
+sumsq_interior_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, int C, int p,
+                      float* __restrict__ out) {
+  const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
+  const long long total = (long long)N * H * W * V;
+  float s = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); long long t = i / V;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H); const int n = (int)(t / H);
+    float f[8];
+    load8(x + (((long long)n * Hp + h + p) * Wp + w + p) * C + v * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += f[j] * f[j];
+  }
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ float r[8];
+  if ((threadIdx.x & 31) == 0) r[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += r[i];
+    atomicAdd(out, t);
+  }
+}
+// dx_pad = scale[0] * x_pad on the interior, 0 on the border
+__global__ void __launch_bounds__(256)
+scale_interior_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale, int N,
+                      int H, int W, int C, int p, __nv_bfloat16* __restrict__ dx) {
+  const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
+  const long long total = (long long)N * Hp * Wp * V;
+  const float sc = __ldg(scale);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long t = i / V;
+    const int wp = (int)(t % Wp); t /= Wp;
+    const int hp = (int)(t % Hp);
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (hp >= p && hp < H + p && wp >= p && wp < W + p) {
+      load8(x + i * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] *= sc;
+    }
+    store8(dx + i * 8, f);
+  }
+}
+
+}  // namespace mt
+
+using namespace mt;
+#define ST(s) ((cudaStream_t)(s))
+#define BF(p) ((__nv_bfloat16*)(p))
+#define CBF(p) ((const __nv_bfloat16*)(p))
+
+extern "C" int mt_avgpool2_fwd(const void* x_pad, int pad, int N, int H, int W, int C, void* out,
+                               void* stream) {
+  if (C % 8) return -1003;
+  avgpool2_fwd_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256), 256, 0,
+                        ST(stream)>>>(CBF(x_pad), pad, N, H, W, C, BF(out));
+  return cuda_rc();
+}
+extern "C" int mt_avgpool2_bwd_add(const void* dpooled, void* dpad, int pad, int N, int H, int W,
+                                   int C, void* stream) {
+  if (C % 8) return -1003;
+  avgpool2_bwd_add_kernel<<<grid_for((long long)N * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
+      CBF(dpooled), BF(dpad), pad, N, H, W, C);
+  return cuda_rc();
+}
+extern "C" int mt_pool_add_act_fwd(const void* c, const void* d, int N, int H, int W, int C,
+                                   int act, float slope, void* out_pad, int out_p, void* stream) {
+  if (C % 8) return -1003;
+  pool_add_act_fwd_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256), 256, 0,
+                            ST(stream)>>>(CBF(c), CBF(d), N, H, W, C, act, slope, BF(out_pad), out_p);
+  return cuda_rc();
+}
+extern "C" int mt_pool_add_act_bwd(const void* dout_pad, const void* out_pad, int N, int H, int W,
+                                   int C, int out_p, int act, float slope, void* dd, void* dc,
+                                   void* stream) {
+  if (C % 8) return -1003;
+  pool_add_act_bwd_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256), 256, 0,
+                            ST(stream)>>>(CBF(dout_pad), CBF(out_pad), N, H, W, C, out_p, act, slope,
+                                          BF(dd), BF(dc));
+  return cuda_rc();
+}
+extern "C" int mt_gap_fwd(const void* x, int N, int HW, int C, float* out, void* stream) {
+  if (C % 8 || C / 8 > 256) return -1003;
+  const int lanes = 256 / (C / 8);
+  gap_fwd_kernel<<<N, 256, (size_t)lanes * C * sizeof(float), ST(stream)>>>(CBF(x), HW, C, out);
+  return cuda_rc();
+}
+extern "C" int mt_gap_bwd(const float* dout, int N, int HW, int C, void* dx, void* stream) {
+  if (C % 8) return -1003;
+  gap_bwd_kernel<<<grid_for((long long)N * HW * (C / 8), 256), 256, 0, ST(stream)>>>(dout, N, HW, C,
+                                                                                     BF(dx));
+  return cuda_rc();
+}
+extern "C" int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int C, int Co,
+                               float* y, void* stream) {
+  if (C % 8 || Co > 4 || Co < 1) return -1003;
+  rgb_head_fwd_kernel<<<grid_for((long long)N * HW, 256), 256, (size_t)C * 4 * sizeof(float),
+                        ST(stream)>>>(CBF(x), w, N, HW, C, Co, y);
+  return cuda_rc();
+}
+extern "C" int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, const float* w, int N,
+                               int HW, int C, int Co, void* dx, float* dw, void* stream) {
+  if (C % 8 || Co > 4 || Co < 1 || C / 8 > 256) return -1003;
+  cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)C * Co * sizeof(float), ST(stream));
+  if (e != cudaSuccess) return -(int)e;
+  const int V = C / 8, lanes = 256 / V;
+  const size_t smem = ((size_t)C * 4 + (size_t)lanes * V * 32) * sizeof(float);
+  int grid = grid_for(((long long)N * HW + lanes - 1) / lanes, 1, 4);
+  rgb_head_bwd_kernel<<<grid, 256, smem, ST(stream)>>>(dy, y, CBF(x), w, N, HW, C, Co, BF(dx), dw);
+  return cuda_rc();
+}
+extern "C" int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, int pad, float* out,
+                                 void* stream) {
+  if (C % 8) return -1003;
+  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float), ST(stream));
+  if (e != cudaSuccess) return -(int)e;
+  sumsq_interior_kernel<<<grid_for((long long)N * H * W * (C / 8), 256, 4), 256, 0, ST(stream)>>>(
+      CBF(x_pad), N, H, W, C, pad, out);
+  return cuda_rc();
+}
+extern "C" int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C,
+                                 int pad, void* dx_pad, void* stream) {
+  if (C % 8) return -1003;
+  scale_interior_kernel<<<grid_for((long long)N * (H + 2 * pad) * (W + 2 * pad) * (C / 8), 256), 256,
+                          0, ST(stream)>>>(CBF(x_pad), scale, N, H, W, C, pad, BF(dx_pad));
+  return cuda_rc();
+}

@@ -1,0 +1,232 @@
+"""torch.autograd glue over the CUDA entry points.
+
+Each Function is one *block* of the reference graph (blocks.py) executed as a static plan of our
+kernels in forward and backward; autograd only stitches blocks, concatenations and losses
+together.  Activations crossing Function boundaries are padded NHWC bf16 buffers whose
+reflection border is materialised for the consumer; their gradients have the same padded shape
+and are folded by the producer's backward.
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from . import ops
+
+
+def _c(t):
+    return t if t is None or t.is_contiguous() else t.contiguous()
+
+
+def _bias_grad(dy, Cout):
+    return ops.channel_sum(dy)[:Cout]
+
+
+class ImageToNHWC(Function):
+    """NCHW fp32 image (+ tiled one-hot code) -> padded NHWC bf16 (networks.py:136-140 + ReflectionPad2d)."""
+
+    @staticmethod
+    def forward(ctx, img, onehot, pad):
+        ctx.meta = (img.shape[1], img.shape[2], img.shape[3], pad)
+        return ops.image_to_nhwc(img, onehot, pad)
+
+    @staticmethod
+    def backward(ctx, dout):
+        Ci, H, W, pad = ctx.meta
+        dimg = ops.image_grad_from_nhwc(_c(dout), Ci, H, W, pad) if ctx.needs_input_grad[0] else None
+        return dimg, None, None
+
+
+class ConvAct(Function):
+    """[pre-padded input] -> Conv2d/ConvTranspose2d (+bias) (+activation) -> padded output
+    (ConvBlock without norm: blocks.py:10-46; used by Discriminator, style encoder, shortcuts)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, wf, wb, geom, act, out_pad):
+        out = ops.conv_fwd(x, wf, bias, geom, act=act, out_pad=out_pad)
+        ops.reflect_border_(out, out_pad)
+        ctx.geom, ctx.act, ctx.out_pad = geom, act, out_pad
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, out if (act is not None) else None, wb)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, out, wb = ctx.saved_tensors
+        g, act, op = ctx.geom, ctx.act, ctx.out_pad
+        dout = _c(dout)
+        if act is None:
+            dy = ops.reflect_fold(dout, op)
+        else:
+            dy = ops.act_bwd_fold(dout, out, op, act)
+        dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
+        dw = ops.conv_wgrad(x, dy, g) if ctx.needs_input_grad[1] else None
+        db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db, None, None, None, None, None
+
+
+class ConvNormAct(Function):
+    """conv -> {InstanceNorm | AdaIN | LayerNorm} -> activation (-> + noise) -> padded output
+    (ConvBlock with norm: blocks.py:38-42; UpsampleBlock: blocks.py:82-90)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, wf, wb, geom, mode, p1, p2, act, out_pad, noise):
+        raw = ops.conv_fwd(x, wf, bias, geom)
+        N, H, W, C = raw.shape
+        stats = ops.plane_stats(raw)
+        gb = p1 if mode == "adain" else None
+        lw, lb = (p1, p2) if mode == "layer" else (None, None)
+        ss, mr = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb)
+        out = ops.affine_act_fwd(raw, ss, act=act, noise=noise, out_p=out_pad)
+        ops.reflect_border_(out, out_pad)
+        ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, raw, ss, mr, p1, wb)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, raw, ss, mr, p1, wb = ctx.saved_tensors
+        g, mode, act, op = ctx.geom, ctx.mode, ctx.act, ctx.out_pad
+        G = ops.reflect_fold(_c(dout), op)
+        dy, dgb, dlw, dlb = ops.norm_bwd(G, raw, ss, mr, mode, act=act,
+                                         gb=_c(p1) if mode == "adain" else None,
+                                         ln_w=p1 if mode == "layer" else None)
+        dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
+        dw = ops.conv_wgrad(x, dy, g) if ctx.needs_input_grad[1] else None
+        db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        dp1 = dgb if mode == "adain" else (dlw.view_as(p1) if mode == "layer" and dlw is not None else None)
+        dp2 = dlb.view_as(p1) if (mode == "layer" and dlb is not None) else None
+        return dx, dw, db, None, None, None, None, dp1, dp2, None, None, None
+
+
+class ResBlock(Function):
+    """x + norm(conv3x3(relu(norm(conv3x3(x)))))  with norm = InstanceNorm2d (ResnetBlock,
+    blocks.py:121-138) or one shared AdaptiveInstanceNorm (AdaINResnetBlock, blocks.py:140-167).
+    Optional Gaussian noise on the block output (ContentEncoder tail, networks.py:38, misc.py:25)."""
+
+    @staticmethod
+    def forward(ctx, x, w1, w2, wf1, wb1, wf2, wb2, geom, mode, gb, act, out_pad, noise):
+        gbc = _c(gb) if mode == "adain" else None
+        raw1 = ops.conv_fwd(x, wf1, None, geom)
+        N, H, W, C = raw1.shape
+        ss1, mr1 = ops.norm_finalize(ops.plane_stats(raw1), mode, H * W, gbc)
+        h = ops.affine_act_fwd(raw1, ss1, act=act, out_p=1)
+        ops.reflect_border_(h, 1)
+        raw2 = ops.conv_fwd(h, wf2, None, geom)
+        ss2, mr2 = ops.norm_finalize(ops.plane_stats(raw2), mode, H * W, gbc)
+        out = ops.affine_act_fwd(raw2, ss2, act=None, res_pad=x, res_p=1, noise=noise, out_p=out_pad)
+        ops.reflect_border_(out, out_pad)
+        ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
+        ctx.save_for_backward(x, raw1, h, raw2, ss1, mr1, ss2, mr2, gbc, wb1, wb2)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, raw1, h, raw2, ss1, mr1, ss2, mr2, gb, wb1, wb2 = ctx.saved_tensors
+        g, mode, act, op = ctx.geom, ctx.mode, ctx.act, ctx.out_pad
+        G = ops.reflect_fold(_c(dout), op)
+        dy2, dgb2, _, _ = ops.norm_bwd(G, raw2, ss2, mr2, mode, act=None, gb=gb)
+        dw2 = ops.conv_wgrad(h, dy2, g) if ctx.needs_input_grad[2] else None
+        dh = ops.conv_dgrad(dy2, wb2, g, h.shape[1], h.shape[2])
+        G1 = ops.reflect_fold(dh, 1)
+        dy1, dgb1, _, _ = ops.norm_bwd(G1, raw1, ss1, mr1, mode, act=act, gb=gb)
+        dw1 = ops.conv_wgrad(x, dy1, g) if ctx.needs_input_grad[1] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.conv_dgrad(dy1, wb1, g, x.shape[1], x.shape[2])
+            if G is dout:  # out_pad == 0: do not alias the incoming gradient
+                G = G.clone()
+            ops.add_interior_(dx, G, 1)
+        dgb = (dgb1 + dgb2) if mode == "adain" else None
+        return dx, dw1, dw2, None, None, None, None, None, None, dgb, None, None, None
+
+
+class DownBlock(Function):
+    """DownResnetBlock (blocks.py:93-119) on a = LeakyReLU(x) (the in-place activation that both
+    branches see), fused with the LeakyReLU that consumes the block's sum:
+        out = lrelu( avgpool2(convB(lrelu(convA(a)))) + conv1x1(avgpool2(a)) )"""
+
+    @staticmethod
+    def forward(ctx, a, wA, bA, wB, bB, wS, bS, packs, geoms, out_pad):
+        (wfA, wbA), (wfB, wbB), (wfS, wbS) = packs
+        gA, gB, gS = geoms
+        b = ops.conv_fwd(a, wfA, bA, gA, act="lrelu", out_pad=1)
+        ops.reflect_border_(b, 1)
+        c = ops.conv_fwd(b, wfB, bB, gB)
+        pa = ops.avgpool2_fwd(a, 1)
+        d = ops.conv_fwd(pa, wfS, bS, gS)
+        out = ops.pool_add_act_fwd(c, d, "lrelu", out_pad)
+        ops.reflect_border_(out, out_pad)
+        ctx.geoms, ctx.out_pad = geoms, out_pad
+        ctx.save_for_backward(a, b, pa, out, wbA, wbB, wbS)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        a, b, pa, out, wbA, wbB, wbS = ctx.saved_tensors
+        gA, gB, gS = ctx.geoms
+        need = ctx.needs_input_grad
+        dd, dc = ops.pool_add_act_bwd(_c(dout), out, ctx.out_pad, "lrelu")
+        dwB = ops.conv_wgrad(b, dc, gB) if need[3] else None
+        dbB = _bias_grad(dc, gB.Cout) if need[4] else None
+        db_pad = ops.conv_dgrad(dc, wbB, gB, b.shape[1], b.shape[2])
+        dyA = ops.act_bwd_fold(db_pad, b, 1, "lrelu")
+        dwA = ops.conv_wgrad(a, dyA, gA) if need[1] else None
+        dbA = _bias_grad(dyA, gA.Cout) if need[2] else None
+        dwS = ops.conv_wgrad(pa, dd, gS) if need[5] else None
+        dbS = _bias_grad(dd, gS.Cout) if need[6] else None
+        da = None
+        if need[0]:
+            da = ops.conv_dgrad(dyA, wbA, gA, a.shape[1], a.shape[2])
+            dpa = ops.conv_dgrad(dd, wbS, gS, pa.shape[1], pa.shape[2])
+            ops.avgpool2_bwd_add_(dpa, da, 1)
+        return da, dwA, dbA, dwB, dbB, dwS, dbS, None, None, None
+
+
+class GlobalAvgPool(Function):
+    """nn.AdaptiveAvgPool2d(1) on a dense NHWC bf16 tensor -> fp32 [N, C]  (networks.py:124)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.hw = (x.shape[1], x.shape[2])
+        return ops.gap_fwd(x)
+
+    @staticmethod
+    def backward(ctx, dout):
+        return ops.gap_bwd(dout.float(), *ctx.hw)
+
+
+class RgbHead(Function):
+    """ConvTranspose2d(C -> 3, k=1, bias=False) + Tanh, NHWC bf16 -> NCHW fp32 (networks.py:248-251)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        Co = weight.shape[1]
+        w2 = weight.detach().reshape(weight.shape[0], Co).contiguous().float()
+        y = ops.rgb_head_fwd(x, w2, Co)
+        ctx.save_for_backward(x, y, w2)
+        ctx.wshape = weight.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, w2 = ctx.saved_tensors
+        dx, dw = ops.rgb_head_bwd(dy.float(), y, x, w2, w2.shape[1])
+        return dx, dw.view(ctx.wshape)
+
+
+class SumSqInterior(Function):
+    """sum(z^2) over the interior of a padded buffer (torch.pow(mu,2) of adain_model.py:396-399)."""
+
+    @staticmethod
+    def forward(ctx, x, pad):
+        ctx.pad = pad
+        ctx.save_for_backward(x)
+        return ops.sumsq_interior(x, pad)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (x,) = ctx.saved_tensors
+        scale = (dout.float() * 2.0).reshape(())
+        return ops.scale_interior(x, scale.contiguous(), ctx.pad), None

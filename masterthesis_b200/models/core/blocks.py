@@ -1,0 +1,342 @@
+"""Blocks of the translation networks, with the reference's constructor signatures, module tree
+and state_dict keys (src/models/core/blocks.py:10-208) — executed as fused CUDA plans.
+
+Every block has two entry points:
+  run(...)      native: padded NHWC bf16 buffers in/out (what the networks use);
+  forward(x)    reference-compatible: NCHW fp32 in/out (layout conversion at the edge).
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ... import functional as Fn
+from ... import ops
+from ...ops import ConvGeom
+from .functions import (act_name, get_activation_layer, get_norm_layer, get_padding_layer,
+                        spectral_norm)
+from .norm import AdaptiveInstanceNorm, LayerNorm
+
+
+# ------------------------------------------------------------------------- parameter holders
+class _ConvParams(nn.Module):
+    transposed = False
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.kernel_size, self.stride, self.padding = kernel_size, stride, padding
+        shape = ((in_channels, out_channels) if self.transposed else (out_channels, in_channels))
+        self.weight = nn.Parameter(torch.empty(*shape, kernel_size, kernel_size))
+        self.bias = nn.Parameter(torch.empty(out_channels)) if bias else None
+        self.reset_parameters()
+        self._pack = None
+
+    def reset_parameters(self):
+        # torch's nn.Conv2d / nn.ConvTranspose2d default init
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        if self.bias is not None:
+            fan_in = self.weight.shape[1] * self.kernel_size * self.kernel_size
+            bound = 1 / math.sqrt(fan_in) if fan_in > 0 else 0
+            nn.init.uniform_(self.bias, -bound, bound)
+
+    def geom(self, zpad=0) -> ConvGeom:
+        return ConvGeom(self.in_channels, self.out_channels, self.kernel_size, self.kernel_size,
+                        self.stride, zpad, self.transposed)
+
+    def packed(self, zpad=0):
+        """bf16 GEMM operands of the fp32 master weight, refreshed when the weight changes."""
+        w = self.weight
+        key = (w._version, w.data_ptr(), zpad)
+        if self._pack is None or self._pack[0] != key:
+            self._pack = (key, ops.pack_weight(w, self.geom(zpad)))
+        return self._pack[1]
+
+    def extra_repr(self):
+        return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
+                f"stride={self.stride}, padding={self.padding}, bias={self.bias is not None}")
+
+
+class Conv2d(_ConvParams):
+    """nn.Conv2d parameters (weight [Cout,Cin,k,k], bias [Cout])."""
+    transposed = False
+
+
+class ConvTranspose2d(_ConvParams):
+    """nn.ConvTranspose2d parameters (weight [Cin,Cout,k,k], bias [Cout])."""
+    transposed = True
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, output_padding=0,
+                 bias=True):
+        self.output_padding = output_padding
+        super().__init__(in_channels, out_channels, kernel_size, stride, padding, bias)
+
+
+# ------------------------------------------------------------------------- layout edges
+def to_padded(x, pad, onehot=None):
+    """NCHW fp32 -> padded NHWC bf16 (reflection border).  Small channel counts use the image
+    packer (autograd-aware); wide tensors go through torch ops (compatibility path only)."""
+    if x.shape[1] + (0 if onehot is None else onehot.shape[1]) <= 8:
+        return Fn.ImageToNHWC.apply(x, onehot, pad)
+    assert onehot is None
+    if pad:
+        x = F.pad(x, (pad,) * 4, mode='reflect')
+    N, C, H, W = x.shape
+    out = x.permute(0, 2, 3, 1)
+    if ops.cs(C) != C:
+        out = F.pad(out, (0, ops.cs(C) - C))
+    return out.to(torch.bfloat16).contiguous()
+
+
+def from_padded(x, C, pad=0):
+    """padded NHWC bf16 -> NCHW fp32 (compatibility path only)."""
+    if pad:
+        x = x[:, pad:-pad, pad:-pad, :]
+    return x[..., :C].permute(0, 3, 1, 2).float().contiguous()
+
+
+def _find(seq, cls):
+    for m in seq:
+        if isinstance(m, cls):
+            return m
+    return None
+
+
+class ConvBlock(nn.Module):
+    """[ReflectionPad2d] -> Conv2d -> [norm] -> [activation]   (reference blocks.py:10-46)."""
+
+    def __init__(self, input_dim: int, output_dim: int, kernel_size: int, stride: int = 1,
+                 padding: int = 0, bias: bool = False, norm_layer: str = None, activation: str = None,
+                 padding_type: str = None, sn: bool = False):
+        super().__init__()
+        layers = []
+        pad_cls = get_padding_layer(padding_type)
+        act_cls = get_activation_layer(activation)
+        norm_cls = get_norm_layer(norm_layer)
+        self.rpad = 0
+        if pad_cls is not None:
+            layers.append(pad_cls(padding))
+            self.rpad, padding = padding, 0
+        if sn:
+            spectral_norm(None)
+        layers.append(Conv2d(input_dim, output_dim, kernel_size, stride, padding, bias=bias))
+        if norm_cls is not None:
+            layers.append(norm_cls(output_dim))
+        if act_cls is not None:
+            layers.append(act_cls())
+        self.block = nn.Sequential(*layers)
+        self.zpad = padding
+
+    # structural lookups -------------------------------------------------
+    @property
+    def conv(self):
+        return _find(self.block, Conv2d)
+
+    @property
+    def norm(self):
+        for m in self.block:
+            if isinstance(m, (nn.InstanceNorm2d, LayerNorm, nn.BatchNorm2d)):
+                return m
+        return None
+
+    @property
+    def act(self):
+        last = self.block[-1]
+        return None if isinstance(last, (Conv2d, nn.InstanceNorm2d, LayerNorm, nn.BatchNorm2d)) else act_name(last)
+
+    def _check(self):
+        if isinstance(self.block[0], nn.ReplicationPad2d):
+            raise NotImplementedError("replicate padding has no CUDA path")
+        if isinstance(self.norm, nn.BatchNorm2d):
+            raise NotImplementedError("batch norm has no CUDA path (not a default of either model)")
+
+    def run(self, x, out_pad=0, noise=None, act_override='keep'):
+        """x: NHWC bf16 with `self.rpad` reflection border.  Returns a buffer padded by out_pad."""
+        self._check()
+        conv = self.conv
+        g = conv.geom(self.zpad)
+        wf, wb = conv.packed(self.zpad)
+        act = self.act if act_override == 'keep' else act_override
+        norm = self.norm
+        if norm is None:
+            assert noise is None
+            return Fn.ConvAct.apply(x, conv.weight, conv.bias, wf, wb, g, act, out_pad)
+        if isinstance(norm, LayerNorm):
+            mode, p1, p2 = 'layer', (norm.weight if norm.affine else None), (norm.bias if norm.affine else None)
+        else:
+            mode, p1, p2 = 'instance', None, None
+        return Fn.ConvNormAct.apply(x, conv.weight, conv.bias, wf, wb, g, mode, p1, p2, act, out_pad, noise)
+
+    def forward(self, x):
+        y = self.run(to_padded(x, self.rpad))
+        return from_padded(y, self.conv.out_channels)
+
+
+class UpsampleBlock(nn.Module):
+    """ConvTranspose2d -> [norm] -> [activation]   (reference blocks.py:48-91, up_type 'transpose')."""
+
+    def __init__(self, input_dim: int, output_dim: int, kernel_size: int, stride: int = 1,
+                 padding: int = 0, output_padding: int = 0, bias: bool = False, norm_layer: str = None,
+                 activation: str = None, padding_type: str = None, sn: bool = False,
+                 up_type: str = 'transpose'):
+        super().__init__()
+        get_padding_layer(padding_type)
+        act_cls = get_activation_layer(activation)
+        norm_cls = get_norm_layer(norm_layer)
+        if sn:
+            spectral_norm(None)
+        layers = []
+        if 'transpose' in up_type:
+            layers.append(ConvTranspose2d(input_dim, output_dim, kernel_size, stride, padding,
+                                          output_padding, bias=bias))
+        elif 'nearest' in up_type or 'pixelshuffle' in up_type:
+            raise NotImplementedError(f"up_type {up_type} is outside the accelerated path (SURVEY.md 8f-4)")
+        else:
+            raise NotImplementedError(f"Mode {up_type} is not supported at the moment")
+        if norm_cls is not None:
+            layers.append(norm_cls(output_dim))
+        if act_cls is not None:
+            layers.append(act_cls())
+        self.block = nn.Sequential(*layers)
+
+    @property
+    def conv(self):
+        return self.block[0]
+
+    @property
+    def norm(self):
+        return _find(self.block, (nn.InstanceNorm2d, LayerNorm))
+
+    @property
+    def act(self):
+        last = self.block[-1]
+        return None if isinstance(last, (ConvTranspose2d, nn.InstanceNorm2d, LayerNorm)) else act_name(last)
+
+    @property
+    def is_rgb_head(self):
+        c = self.conv
+        return (c.kernel_size == 1 and c.stride == 1 and c.padding == 0 and c.bias is None
+                and self.norm is None and self.act == 'tanh' and c.out_channels <= 4)
+
+    def run(self, x, out_pad=0):
+        """x: dense NHWC bf16.  The 1x1 -> tanh head returns the NCHW fp32 image."""
+        c = self.conv
+        if self.is_rgb_head:
+            return Fn.RgbHead.apply(x, c.weight)
+        if not (c.kernel_size == 3 and c.stride == 2 and c.padding == 1 and c.output_padding == 1):
+            raise NotImplementedError("only ConvTranspose2d(k=3,s=2,p=1,op=1) and the 1x1 tanh head are accelerated")
+        g = c.geom(1)
+        wf, wb = c.packed(1)
+        norm = self.norm
+        if norm is None:
+            return Fn.ConvAct.apply(x, c.weight, c.bias, wf, wb, g, self.act, out_pad)
+        if isinstance(norm, LayerNorm):
+            mode, p1, p2 = 'layer', (norm.weight if norm.affine else None), (norm.bias if norm.affine else None)
+        else:
+            mode, p1, p2 = 'instance', None, None
+        return Fn.ConvNormAct.apply(x, c.weight, c.bias, wf, wb, g, mode, p1, p2, self.act, out_pad, None)
+
+    def forward(self, x):
+        y = self.run(to_padded(x, 0))
+        return y if self.is_rgb_head else from_padded(y, self.conv.out_channels)
+
+
+class DownResnetBlock(nn.Module):
+    """[norm] -> act -> ConvBlock(3x3,+act) -> ConvBlock(3x3) -> AvgPool2  +  AvgPool2 -> Conv1x1
+    (reference blocks.py:93-119).  The first activation is in-place in the reference, so BOTH
+    branches consume act(x); the native path therefore takes a = act(x) as its input."""
+
+    def __init__(self, input_dim: int, output_dim: int, norm_layer: str = 'instance',
+                 activation: str = 'lrelu', padding_type: str = 'reflect', bias: bool = True):
+        super().__init__()
+        if isinstance(norm_layer, str):
+            norm_layer = get_norm_layer(norm_layer)
+        if isinstance(activation, str):
+            activation = get_activation_layer(activation)
+        conv = []
+        if norm_layer is not None:
+            conv.append(norm_layer(input_dim))
+        conv.append(activation())
+        conv.append(ConvBlock(input_dim, input_dim, 3, 1, padding=1, padding_type=padding_type,
+                              norm_layer=norm_layer, activation=activation, bias=bias))
+        conv.append(ConvBlock(input_dim, output_dim, 3, 1, padding=1, padding_type=padding_type, bias=bias))
+        conv.append(nn.AvgPool2d(kernel_size=2, stride=2))
+        self.conv = nn.Sequential(*conv)
+        self.shortcut = nn.Sequential(nn.AvgPool2d(kernel_size=2, stride=2),
+                                      Conv2d(input_dim, output_dim, 1, 1, 0, bias=bias))
+        self._has_norm = norm_layer is not None
+
+    def run(self, a, out_pad=1):
+        """a = LeakyReLU(x) padded by 1.  Returns LeakyReLU(block(x)) padded by out_pad."""
+        if self._has_norm or not isinstance(self.conv[0], nn.LeakyReLU):
+            raise NotImplementedError("DownResnetBlock is accelerated for norm_layer=None, activation='lrelu' "
+                                      "(the only configuration the models build, networks.py:117-121)")
+        cA, cB, cS = self.conv[1].conv, self.conv[2].conv, self.shortcut[1]
+        packs = (cA.packed(), cB.packed(), cS.packed())
+        geoms = (cA.geom(), cB.geom(), cS.geom())
+        return Fn.DownBlock.apply(a, cA.weight, cA.bias, cB.weight, cB.bias, cS.weight, cS.bias,
+                                  packs, geoms, out_pad)
+
+    def forward(self, x):
+        # reference semantics on raw x: returns block(x) WITHOUT the consumer's activation, so the
+        # compatibility path undoes the fused LeakyReLU (it is invertible).
+        a = to_padded(F.leaky_relu(x, 0.01), 1)
+        y = from_padded(self.run(a, out_pad=0), self.shortcut[1].out_channels)
+        return torch.where(y > 0, y, y / 0.01)
+
+
+class ResnetBlock(nn.Module):
+    """x + ConvBlock(norm, act) -> ConvBlock(norm) [-> Dropout]   (reference blocks.py:121-138)."""
+
+    def __init__(self, input_dim: int, output_dim: int, dropout: bool = False,
+                 norm_layer: str = 'instance', padding_type: str = 'reflect', activation: str = 'relu'):
+        super().__init__()
+        model = [ConvBlock(input_dim, output_dim, 3, 1, 1, padding_type=padding_type,
+                           norm_layer=norm_layer, activation=activation),
+                 ConvBlock(output_dim, output_dim, 3, 1, 1, padding_type=padding_type, norm_layer=norm_layer)]
+        if dropout:
+            model.append(nn.Dropout(0.5))
+        self.model = nn.Sequential(*model)
+        self.dropout = dropout
+
+    def run(self, x, out_pad=1, noise=None):
+        if self.dropout:
+            raise NotImplementedError("--use_dropout is outside the accelerated path (SURVEY.md 8f-4)")
+        b1, b2 = self.model[0], self.model[1]
+        if not (isinstance(b1.norm, nn.InstanceNorm2d) and b1.rpad == 1):
+            raise NotImplementedError("ResnetBlock is accelerated for instance norm + reflect padding")
+        c1, c2 = b1.conv, b2.conv
+        (wf1, wb1), (wf2, wb2) = c1.packed(), c2.packed()
+        return Fn.ResBlock.apply(x, c1.weight, c2.weight, wf1, wb1, wf2, wb2, c1.geom(), 'instance',
+                                 None, b1.act, out_pad, noise)
+
+    def forward(self, x):
+        return from_padded(self.run(to_padded(x, 1), out_pad=0), self.model[1].conv.out_channels)
+
+
+class AdaINResnetBlock(nn.Module):
+    """x + AdaIN(conv2(relu(AdaIN(conv1(x), z))), z) with ONE shared AdaptiveInstanceNorm
+    (reference blocks.py:140-167)."""
+
+    def __init__(self, input_dim: int, output_dim: int, dropout: bool = False, style_dim: int = 256,
+                 padding_type: str = 'reflect', activation: str = 'relu'):
+        super().__init__()
+        self.activation = get_activation_layer(activation)()
+        self.conv1 = ConvBlock(input_dim, output_dim, 3, 1, 1, padding_type=padding_type)
+        self.conv2 = ConvBlock(output_dim, output_dim, 3, 1, 1, padding_type=padding_type)
+        self.norm = AdaptiveInstanceNorm(output_dim, style_dim)
+        self.dropout = nn.Dropout(0.5) if dropout else nn.Identity()
+        self._dropout = dropout
+
+    def run(self, x, z, out_pad=1):
+        if self._dropout:
+            raise NotImplementedError("--use_dropout is outside the accelerated path (SURVEY.md 8f-4)")
+        gb = self.norm.modulation(z)
+        c1, c2 = self.conv1.conv, self.conv2.conv
+        (wf1, wb1), (wf2, wb2) = c1.packed(), c2.packed()
+        return Fn.ResBlock.apply(x, c1.weight, c2.weight, wf1, wb1, wf2, wb2, c1.geom(), 'adain',
+                                 gb, act_name(self.activation), out_pad, None)
+
+    def forward(self, x, z):
+        return from_padded(self.run(to_padded(x, 1), z, out_pad=0), self.conv2.conv.out_channels)

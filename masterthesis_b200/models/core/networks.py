@@ -1,0 +1,209 @@
+"""The translation networks with the reference's constructor signatures, module trees and
+state_dict keys (src/models/core/networks.py:8-466), executed as fused CUDA plans.
+
+`forward(...)` keeps the reference contract (NCHW fp32 tensors in and out); `run(...)` is the native
+entry the models use: images stay NCHW fp32 (3 channels), the content code stays a padded NHWC
+bf16 buffer so that it feeds the decoder's first convolution without a layout round trip.
+"""
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ... import functional as Fn
+from .blocks import (AdaINResnetBlock, Conv2d, ConvBlock, DownResnetBlock, ResnetBlock,
+                     UpsampleBlock, from_padded, to_padded)
+from .functions import get_activation_layer, get_norm_layer
+from .misc import GaussianNoiseLayer
+
+CONTENT_PAD = 1  # border carried by the content code z_c (its consumers are 3x3 / 7x7-pad-1 convs)
+
+
+class ContentEncoder(nn.Module):
+    """7x7 stem -> num_downs x (3x3 s2) -> n_blocks x ResnetBlock -> + N(0,1)
+    (reference networks.py:8-43)."""
+
+    def __init__(self, input_dim: int, dim: int = 64, num_downs: int = 2, n_blocks: int = 4,
+                 norm_layer: str = 'instance', padding_type: str = 'reflect', bias: bool = True):
+        super().__init__()
+        layers = [ConvBlock(input_dim, dim, 7, 1, 3, padding_type=padding_type, norm_layer=norm_layer,
+                            activation='lrelu', bias=bias)]
+        for _ in range(num_downs):
+            layers.append(ConvBlock(dim, dim * 2, 3, 2, 1, padding_type=padding_type,
+                                    norm_layer=norm_layer, activation='relu', bias=bias))
+            dim *= 2
+        for _ in range(n_blocks):
+            layers.append(ResnetBlock(dim, dim, norm_layer=norm_layer, activation='relu'))
+        layers.append(GaussianNoiseLayer())
+        self.model = nn.Sequential(*layers)
+        self.output_dim = dim
+        self.num_downs, self.n_blocks = num_downs, n_blocks
+
+    def run(self, img, rng=None):
+        """img NCHW fp32 -> z_c padded NHWC bf16 [N, H/4+2, W/4+2, C]."""
+        if self.n_blocks < 1:
+            raise NotImplementedError("ContentEncoder needs >= 1 ResnetBlock on the CUDA path")
+        x = to_padded(img, 3)
+        for i in range(1 + self.num_downs):
+            x = self.model[i].run(x, out_pad=1)
+        first = 1 + self.num_downs
+        for i in range(self.n_blocks):
+            noise = None
+            if i == self.n_blocks - 1:
+                N, Hp, Wp, C = x.shape
+                noise = self.model[-1].draw(N, Hp - 2, Wp - 2, C, x.device, rng)
+            x = self.model[first + i].run(x, out_pad=CONTENT_PAD, noise=noise)
+        return x
+
+    def forward(self, x):
+        return from_padded(self.run(x), self.output_dim, CONTENT_PAD)
+
+
+class ReparameterizedStyleEncoder(nn.Module):
+    """cat(x, one-hot maps) -> 4x4 s2 stem -> DownResnetBlocks -> act -> GAP -> fc, fcVar ->
+    z = mu + eps * exp(logvar / 2)   (reference networks.py:87-146)."""
+
+    def __init__(self, input_dim: int, output_dim: int = 8, dim: int = 64, n_blocks: int = 4,
+                 num_domains: int = 2, norm_layer: str = None, activation: str = None, bias: bool = True):
+        super().__init__()
+        if isinstance(norm_layer, str):
+            norm_layer = get_norm_layer(norm_layer)
+        if isinstance(activation, str):
+            activation = get_activation_layer(activation)
+        max_filter_size = 256
+        layers = [ConvBlock(input_dim + num_domains, dim, 4, 2, 1, padding_type='reflect', bias=bias)]
+        out_dim = dim
+        for _ in range(1, n_blocks):
+            in_dim = min(max_filter_size, dim)
+            out_dim = min(max_filter_size, dim * 2)
+            layers.append(DownResnetBlock(in_dim, out_dim, norm_layer, activation, bias=bias))
+            dim *= 2
+        layers.append(activation())
+        layers.append(nn.AdaptiveAvgPool2d(1))
+        self.model = nn.Sequential(*layers)
+        self.out_nch = out_dim
+        self.fc = nn.Linear(out_dim, output_dim)
+        self.fcVar = nn.Linear(out_dim, output_dim)
+        self.n_blocks = n_blocks
+
+    def reparameterize(self, mu, logvar, rng=None):
+        std = logvar.mul(0.5).exp()
+        if rng is not None:
+            eps = rng(tuple(std.shape)).to(mu.device)
+        else:
+            eps = torch.randn(std.shape, device=mu.device, dtype=mu.dtype)
+        return eps * std + mu
+
+    def run(self, img, c, rng=None):
+        if not isinstance(self.model[-2], nn.LeakyReLU):
+            raise NotImplementedError("style encoder is accelerated for activation='lrelu' (the models' setting)")
+        x = to_padded(img, 1, onehot=c)
+        last = self.n_blocks == 1
+        a = self.model[0].run(x, out_pad=0 if last else 1, act_override='lrelu')
+        for i in range(1, self.n_blocks):
+            a = self.model[i].run(a, out_pad=0 if i == self.n_blocks - 1 else 1)
+        feat = Fn.GlobalAvgPool.apply(a)[:, :self.out_nch]
+        mu = self.fc(feat)
+        logvar = self.fcVar(feat)
+        return self.reparameterize(mu, logvar, rng), mu, logvar
+
+    def forward(self, x, c):
+        return self.run(x, c)
+
+
+class AdaINDecoder(nn.Module):
+    """style MLP -> n_blocks x AdaINResnetBlock -> num_ups x (ConvT 3x3 s2 + LN + ReLU) -> ConvT 1x1
+    + tanh   (reference networks.py:207-270)."""
+
+    def __init__(self, output_dim: int, dim: int = 256, n_blocks: int = 4, num_domains: int = 2,
+                 num_ups: int = 2, latent_dim: int = 8, up_type: str = 'transpose',
+                 res_norm: str = 'adain', dropout: bool = False, norm_layer: str = 'layer',
+                 activation: str = 'relu', bias: bool = True):
+        super().__init__()
+        self.dim_add = dim
+        self.adain = 'adain' in res_norm
+        self.dec1 = nn.ModuleList()
+        for _ in range(n_blocks):
+            if self.adain:
+                self.dec1.append(AdaINResnetBlock(dim, self.dim_add, style_dim=self.dim_add, dropout=dropout))
+            else:
+                self.dec1.append(ResnetBlock(dim, self.dim_add, dropout=dropout))
+        ups = []
+        for _ in range(num_ups):
+            ups.append(UpsampleBlock(dim, dim // 2, 3, 2, 1, 1, norm_layer=norm_layer,
+                                     activation=activation, up_type=up_type, bias=bias))
+            dim = dim // 2
+        if 'transpose' in up_type:
+            ups.append(UpsampleBlock(dim, output_dim, 1, 1, 0, activation='tanh', up_type='transpose'))
+        else:
+            ups.append(ConvBlock(dim, output_dim, 7, 1, 3, activation='tanh'))
+        self.dec2 = nn.Sequential(*ups)
+        if self.adain:
+            self.linear = nn.Sequential(nn.Linear(latent_dim + num_domains, 256), nn.ReLU(inplace=True),
+                                        nn.Linear(256, 256), nn.ReLU(inplace=True),
+                                        nn.Linear(256, self.dim_add))
+
+    def run(self, z_c, z, c):
+        """z_c padded NHWC bf16 (CONTENT_PAD), z [N,latent], c [N,nd] -> NCHW fp32 image."""
+        out = z_c
+        n = len(self.dec1)
+        if self.adain:
+            s = self.linear(torch.cat([c, z], 1))
+            for i, dec in enumerate(self.dec1):
+                out = dec.run(out, s, out_pad=0 if i == n - 1 else 1)
+        else:
+            for i, dec in enumerate(self.dec1):
+                out = dec.run(out, out_pad=0 if i == n - 1 else 1)
+        if n == 0:
+            out = out[:, CONTENT_PAD:-CONTENT_PAD, CONTENT_PAD:-CONTENT_PAD, :].contiguous()
+        for up in self.dec2:
+            out = up.run(out)
+        return out
+
+    def forward(self, x, z, c):
+        return self.run(to_padded(x, CONTENT_PAD), z, c)
+
+
+class Discriminator(nn.Module):
+    """6 x (3x3 s2 + LeakyReLU) -> {1x1 conv with padding=1 (real/fake map), k x k conv + GAP
+    (domain logits)}   (reference networks.py:335-384)."""
+
+    def __init__(self, input_dim: int, dim: int = 64, n_layers: int = 6, num_domains: int = 2,
+                 norm_layer: str = None, activation: str = 'lrelu', padding_type: str = 'reflect',
+                 bias: bool = True, sn: bool = False, image_size: int = 256):
+        super().__init__()
+        layers = [ConvBlock(input_dim, dim, kernel_size=3, stride=2, padding=1, padding_type=padding_type,
+                            norm_layer=norm_layer, sn=sn, activation=activation, bias=bias)]
+        nch = dim
+        for _ in range(n_layers - 2):
+            layers.append(ConvBlock(nch, nch * 2, kernel_size=3, stride=2, padding=1,
+                                    padding_type=padding_type, norm_layer=norm_layer, sn=sn,
+                                    activation=activation, bias=bias))
+            nch *= 2
+        layers.append(ConvBlock(nch, nch, kernel_size=3, stride=2, padding=1, padding_type=padding_type,
+                                sn=sn, activation=activation, bias=bias))
+        self.model = nn.Sequential(*layers)
+        self.conv1 = Conv2d(nch, 1, kernel_size=1, stride=1, padding=1, bias=False)
+        kernal_size = int(image_size / np.power(2, n_layers))
+        self.conv2 = Conv2d(nch, num_domains, kernel_size=kernal_size, bias=False)
+        self.pool = nn.AdaptiveAvgPool2d(1)
+        self.output_dim = nch
+
+    def run(self, img):
+        x = to_padded(img, 1)
+        n = len(self.model)
+        for i, blk in enumerate(self.model):
+            x = blk.run(x, out_pad=0 if i == n - 1 else 1)
+        # heads: 2 x (S*S*C) MACs per logit — host-side glue on the tiny [N,S,S,C] feature map
+        h = x.float()[..., :self.output_dim]
+        out = torch.einsum('nhwc,c->nhw', h, self.conv1.weight[0, :, 0, 0])
+        out = F.pad(out, (1, 1, 1, 1)).unsqueeze(1)           # conv1 has padding=1: exact-zero border
+        w2 = self.conv2.weight
+        if h.shape[1] == w2.shape[2] and h.shape[2] == w2.shape[3]:
+            cls = torch.einsum('nhwc,dchw->nd', h, w2)
+        else:
+            cls = F.conv2d(h.permute(0, 3, 1, 2), w2).mean(dim=(2, 3))
+        return out, cls
+
+    def forward(self, x):
+        return self.run(x)

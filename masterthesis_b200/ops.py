@@ -274,3 +274,100 @@ def act_bwd_fold(dpad, out_pad, pad, act):
                                      _p(dy), _stream()), "act_bwd_fold")
     _count()
     return dy
+
+
+# ----------------------------------------------------------------------------- pooling / heads
+def avgpool2_fwd(x_pad, pad):
+    N, Hp, Wp, C = x_pad.shape
+    H, W = Hp - 2 * pad, Wp - 2 * pad
+    out = empty_act(N, H // 2, W // 2, C, x_pad.device)
+    check(_lib.lib().mt_avgpool2_fwd(_p(x_pad), pad, N, H, W, C, _p(out), _stream()), "avgpool2_fwd")
+    _count()
+    return out
+
+
+def avgpool2_bwd_add_(dpooled, dpad, pad):
+    N, Hp, Wp, C = dpad.shape
+    check(_lib.lib().mt_avgpool2_bwd_add(_p(dpooled), _p(dpad), pad, N, Hp - 2 * pad, Wp - 2 * pad, C,
+                                         _stream()), "avgpool2_bwd_add")
+    _count()
+    return dpad
+
+
+def pool_add_act_fwd(c, d, act, out_p):
+    N, H, W, C = c.shape
+    out = empty_act(N, H // 2 + 2 * out_p, W // 2 + 2 * out_p, C, c.device)
+    check(_lib.lib().mt_pool_add_act_fwd(_p(c), _p(d), N, H, W, C, ACT[act], LRELU_SLOPE, _p(out), out_p,
+                                         _stream()), "pool_add_act_fwd")
+    _count()
+    return out
+
+
+def pool_add_act_bwd(dout_pad, out_pad, out_p, act):
+    N, Hp, Wp, C = out_pad.shape
+    Ho, Wo = Hp - 2 * out_p, Wp - 2 * out_p
+    dd = empty_act(N, Ho, Wo, C, out_pad.device)
+    dc = empty_act(N, Ho * 2, Wo * 2, C, out_pad.device)
+    check(_lib.lib().mt_pool_add_act_bwd(_p(dout_pad), _p(out_pad), N, Ho * 2, Wo * 2, C, out_p, ACT[act],
+                                         LRELU_SLOPE, _p(dd), _p(dc), _stream()), "pool_add_act_bwd")
+    _count()
+    return dd, dc
+
+
+def gap_fwd(x):
+    N, H, W, C = x.shape
+    out = torch.empty((N, C), dtype=torch.float32, device=x.device)
+    check(_lib.lib().mt_gap_fwd(_p(x), N, H * W, C, _p(out), _stream()), "gap_fwd")
+    _count()
+    return out
+
+
+def gap_bwd(dout, H, W):
+    N, C = dout.shape
+    dx = empty_act(N, H, W, C, dout.device)
+    check(_lib.lib().mt_gap_bwd(_p(dout.contiguous()), N, H * W, C, _p(dx), _stream()), "gap_bwd")
+    _count()
+    return dx
+
+
+def rgb_head_fwd(x, w, Co):
+    """x [N,H,W,C] bf16 dense, w fp32 [C, Co] -> NCHW fp32 tanh image."""
+    N, H, W, C = x.shape
+    y = torch.empty((N, Co, H, W), dtype=torch.float32, device=x.device)
+    check(_lib.lib().mt_rgb_head_fwd(_p(x), _p(w), N, H * W, C, Co, _p(y), _stream()), "rgb_head_fwd")
+    _count()
+    return y
+
+
+def rgb_head_bwd(dy, y, x, w, Co):
+    N, H, W, C = x.shape
+    dx = torch.empty_like(x)
+    dw = torch.empty((C, Co), dtype=torch.float32, device=x.device)
+    check(_lib.lib().mt_rgb_head_bwd(_p(dy.contiguous()), _p(y), _p(x), _p(w), N, H * W, C, Co, _p(dx),
+                                     _p(dw), _stream()), "rgb_head_bwd")
+    _count()
+    return dx, dw
+
+
+def sumsq_interior(x_pad, pad):
+    N, Hp, Wp, C = x_pad.shape
+    out = torch.empty((), dtype=torch.float32, device=x_pad.device)
+    check(_lib.lib().mt_sumsq_interior(_p(x_pad), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _p(out),
+                                       _stream()), "sumsq_interior")
+    _count()
+    return out
+
+
+def scale_interior(x_pad, scale, pad):
+    """scale: fp32 0-dim device tensor."""
+    N, Hp, Wp, C = x_pad.shape
+    dx = torch.empty_like(x_pad)
+    check(_lib.lib().mt_scale_interior(_p(x_pad), _p(scale), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _p(dx),
+                                       _stream()), "scale_interior")
+    _count()
+    return dx
+
+
+def channel_sum(dy):
+    """sum over (n, h, w) of a dense bf16 tensor -> fp32 [C] (bias gradients)."""
+    return plane_stats(dy)[:, :, 0].sum(0)

@@ -1,0 +1,172 @@
+"""TEST INFRASTRUCTURE — fp32 restatement of AdaINModel's training iteration and sampling
+forwards (reference src/models/adain_model.py), on top of oracle/nets.py.  Same import rules as
+oracle/nets.py.  Random draws are supplied by the caller (`draw(shape) -> tensor`) in the
+reference's own order so that the CUDA path can consume identical noise.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+from . import nets
+
+NETS = ('content_encoder', 'style_encoder', 'decoder', 'discriminator1', 'discriminator2')
+
+
+class Adam:
+    """torch.optim.Adam with coupled L2 weight decay (adain_model.py:58-61), restated."""
+
+    def __init__(self, params, lr, betas, wd, eps=1e-8):
+        self.params = params
+        self.lr, self.b1, self.b2, self.wd, self.eps = lr, betas[0], float(betas[1]), wd, eps
+        self.t = 0
+        self.m = {k: torch.zeros_like(v) for k, v in params.items()}
+        self.v = {k: torch.zeros_like(v) for k, v in params.items()}
+
+    def zero_grad(self):
+        for p in self.params.values():
+            p.grad = None
+
+    @torch.no_grad()
+    def step(self):
+        self.t += 1
+        for k, p in self.params.items():
+            if p.grad is None:
+                continue
+            g = p.grad + self.wd * p
+            self.m[k].mul_(self.b1).add_(g, alpha=1 - self.b1)
+            self.v[k].mul_(self.b2).addcmul_(g, g, value=1 - self.b2)
+            denom = self.v[k].sqrt() / math.sqrt(1 - self.b2 ** self.t) + self.eps
+            p.addcdiv_(self.m[k], denom, value=-self.lr / (1 - self.b1 ** self.t))
+
+
+def bce_logits(x, target):
+    """nn.BCEWithLogitsLoss (mean) against a constant or tensor target (loss.py:52-64)."""
+    t = torch.full_like(x, float(target)) if not torch.is_tensor(target) else target
+    return F.binary_cross_entropy_with_logits(x, t)
+
+
+class AdaINStep:
+    """State + one iteration of AdaINModel with default flags (no content-D, vanilla GAN, no VGG)."""
+
+    def __init__(self, params, B, lr=1e-4, betas=(0.5, 0.999), wd=1e-4, lambda_rec=10.0,
+                 lambda_cls=1.0, lambda_cls_G=5.0, latent_dim=8):
+        self.P = {n: {k: v.detach().clone().requires_grad_(True) for k, v in params[n].items()}
+                  for n in params}
+        self.opt = {n: Adam(self.P[n], lr, betas, wd) for n in self.P}
+        self.B, self.latent = B, latent_dim
+        self.lrec, self.lcls, self.lclsg = lambda_rec, lambda_cls, lambda_cls_G
+        self.loss = {}
+
+    # -- networks -------------------------------------------------------------------------
+    def Ec(self, x, draw):
+        n = draw((x.size(0), 256, x.size(2) // 4, x.size(3) // 4)) if draw else None
+        return nets.content_encoder(self.P['content_encoder'], x, n)
+
+    def Es(self, x, c, draw):
+        eps = draw((x.size(0), self.latent))
+        return nets.style_encoder_reparam(self.P['style_encoder'], x, c, eps)
+
+    def G(self, zc, zs, c):
+        return nets.adain_decoder(self.P['decoder'], zc, zs, c)
+
+    def D(self, which, x):
+        return nets.discriminator(self.P[which], x)
+
+    # -- phases (adain_model.py:146-180, 225-239, 241-394) ----------------------------------
+    def update_discriminator(self, img, c_org, draw):
+        B = self.B
+        with torch.no_grad():
+            cls_a, cls_b = torch.split(c_org, B)
+            z_ca, z_cb = torch.split(self.Ec(img, draw), B)
+            z_s, _, _ = self.Es(img, c_org, draw)
+            z_sa, z_sb = torch.split(z_s, B)
+            z_sr = draw((B, self.latent))
+            img_ba, img_br = torch.split(self.G(torch.cat((z_cb, z_cb)), torch.cat((z_sa, z_sr)),
+                                                torch.cat((cls_a, cls_a))), B)
+            img_ab, img_ar = torch.split(self.G(torch.cat((z_ca, z_ca)), torch.cat((z_sb, z_sr)),
+                                                torch.cat((cls_b, cls_b))), B)
+            img_fake = torch.cat((img_ba, img_ab))
+            img_random = torch.cat((img_br, img_ar))
+        for which, fake in (('discriminator1', img_fake), ('discriminator2', img_random)):
+            self.opt[which].zero_grad()
+            pred_fake, _ = self.D(which, fake)
+            pred_real, pred_real_cls = self.D(which, img)
+            d_adv = bce_logits(pred_fake, 0) + bce_logits(pred_real, 1)
+            d_cls = bce_logits(pred_real_cls, c_org)
+            d = d_adv + self.lcls * d_cls
+            d.backward()
+            self.loss.update(d_adv=d_adv.item(), d_cls=d_cls.item(), d_total=d.item())
+            self.opt[which].step()
+
+    def backward_generator(self, img, c_org, draw):
+        B = self.B
+        cls_a, cls_b = torch.split(c_org, B)
+        z_c = self.Ec(img, draw)
+        z_ca, z_cb = torch.split(z_c, B)
+        z_s, mu, logvar = self.Es(img, c_org, draw)
+        z_sa, z_sb = torch.split(z_s, B)
+        img_ba, img_aa = torch.split(self.G(torch.cat((z_cb, z_ca)), torch.cat((z_sa, z_sa)),
+                                            torch.cat((cls_a, cls_a))), B)
+        img_ab, img_bb = torch.split(self.G(torch.cat((z_ca, z_cb)), torch.cat((z_sb, z_sb)),
+                                            torch.cat((cls_b, cls_b))), B)
+        img_fake = torch.cat((img_ba, img_ab))
+        img_self = torch.cat((img_aa, img_bb))
+        z_c_rec_b, z_c_rec_a = torch.split(self.Ec(img_fake, draw), B)
+        z_s_rec, _, _ = self.Es(img_fake, c_org, draw)
+        z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B)
+        img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
+                           torch.cat((cls_a, cls_b)))
+        pred_fake, pred_fake_cls = self.D('discriminator1', img_fake)
+        g_adv = bce_logits(pred_fake, 1)
+        g_cls = bce_logits(pred_fake_cls, c_org) * self.lclsg
+        g_self = F.l1_loss(img_self, img) * self.lrec
+        g_cc = F.l1_loss(img_recon, img) * self.lrec
+        kl_zc = torch.mean(z_c ** 2) * 0.01
+        kl_zs = torch.sum(1 + logvar - mu ** 2 - logvar.exp()) * (-0.5) * 0.01
+        total = g_adv + g_cls + g_self + g_cc + kl_zc + kl_zs
+        total.backward()
+        self.loss.update(g_adv=g_adv.item(), g_cls=g_cls.item(), kl_zc=kl_zc.item(), kl_zs=kl_zs.item(),
+                         l1_self_rec=g_self.item(), l1_cc_rec=g_cc.item(), total_g=total.item())
+
+    def backward_decoder_random(self, img, c_org, draw):
+        B = self.B
+        cls_a, cls_b = torch.split(c_org, B)
+        z_ca, z_cb = torch.split(self.Ec(img, draw), B)
+        z_sr = draw((B, self.latent))
+        img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
+        pred_fake, pred_fake_cls = self.D('discriminator2', img_random)
+        g_adv2 = bce_logits(pred_fake, 1)
+        g_cls2 = bce_logits(pred_fake_cls, c_org) * self.lclsg
+        _, mu2, _ = self.Es(img_random, c_org, draw)
+        mu2_a, mu2_b = torch.split(mu2, B)
+        z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
+        (z_l1 + g_adv2 + g_cls2).backward()
+        self.loss.update(l1_recon_z=z_l1.item(), gan2=g_adv2.item(), gan2_cls=g_cls2.item())
+
+    def optimize_parameters(self, img, c_org, draw):
+        """adain_model.py:428-430 (no content discriminator)."""
+        self.update_discriminator(img, c_org, draw)
+        for n in ('content_encoder', 'style_encoder', 'decoder'):
+            self.opt[n].zero_grad()
+        # D1 receives (unused) gradients in this phase; the reference zeroes them at :174
+        self.backward_generator(img, c_org, draw)
+        for n in ('content_encoder', 'style_encoder', 'decoder'):
+            self.opt[n].step()
+        for n in ('content_encoder', 'decoder'):
+            self.opt[n].zero_grad()
+        self.backward_decoder_random(img, c_org, draw)
+        for n in ('content_encoder', 'decoder'):
+            self.opt[n].step()
+        return dict(self.loss)
+
+    # -- sampling (adain_model.py:96-109) ------------------------------------------------------
+    @torch.no_grad()
+    def forward_reference(self, img_src, img_ref, c_trg, draw):
+        z_c = self.Ec(img_src, draw)
+        z_s, _, _ = self.Es(img_ref, c_trg, draw)
+        return self.G(z_c, z_s, c_trg)
+
+    @torch.no_grad()
+    def forward_random(self, img, z_r, c_trg, draw):
+        return self.G(self.Ec(img, draw), z_r, c_trg)
