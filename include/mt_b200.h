@@ -138,6 +138,12 @@ int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, int pad, fl
 int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C, int pad,
                       void* dx_pad, void* stream);
 
+/* ---- optimizer ------------------------------------------------------------------------------ */
+/* torch.optim.Adam step (coupled L2 weight decay, adain_model.py:58-61) over a flat fp32 bucket;
+ * g is multiplied by gscale first (data-parallel averaging). `step` is the 1-based step count. */
+int mt_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1,
+                 float beta2, float eps, float wd, int step, float gscale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

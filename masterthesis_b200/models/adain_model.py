@@ -1,0 +1,272 @@
+"""AdaINModel — same construction, training-step and sampling API as the reference's
+src/models/adain_model.py:9-430, driving the CUDA networks of models/core/networks.py.
+
+Differences that do not change results: the generator forwards of the
+discriminator phase run without an autograd graph (the reference builds one and never uses it,
+:203); weight gradients nobody consumes are skipped (D1 in phase G1, Es in phase G2, item 11);
+the real and fake discriminator passes are batched into one call; the 13 loss scalars are read
+back with ONE host sync per iteration instead of 13 `.item()` calls.
+"""
+import time
+from contextlib import contextmanager
+
+import torch
+import torch.nn.functional as F
+
+from .. import functional as Fn
+from ..optim import FlatAdam
+from .core import networks
+from .core.networks import CONTENT_PAD
+from .model import Model
+
+
+def _bce(x, target):
+    t = torch.full_like(x, float(target)) if not torch.is_tensor(target) else target
+    return F.binary_cross_entropy_with_logits(x, t)
+
+
+class AdaINModel(Model):
+    def __init__(self, args):
+        super().__init__(args)
+        self.latent_dim = args.latent_dim
+        for flag, why in (('ms_dis', 'MultiScaleDiscriminator'), ('use_ragan', 'relativistic GAN'),
+                          ('dis_sn', 'spectral norm'), ('use_dropout', 'dropout')):
+            if getattr(args, flag, False):
+                raise NotImplementedError(f"--{flag} ({why}) is outside the accelerated path (SURVEY.md §8f)")
+        if getattr(args, 'vgg_loss', None) is not None:
+            raise NotImplementedError("VGG perceptual loss needs downloaded weights; not on the accelerated path")
+        m = self.model
+        m.content_encoder = networks.ContentEncoder(args.input_dim, dim=args.dim, norm_layer=args.enc_norm)
+        # --concat / --reparam are ignored exactly as in the reference (adain_model.py:17-22)
+        m.style_encoder = networks.ReparameterizedStyleEncoder(
+            args.input_dim, output_dim=self.latent_dim, dim=args.dim, num_domains=args.num_domains,
+            norm_layer=None, activation='lrelu')
+        m.decoder = networks.AdaINDecoder(args.input_dim, dim=m.content_encoder.output_dim,
+                                          num_domains=args.num_domains, latent_dim=self.latent_dim,
+                                          up_type=args.up_type, norm_layer=args.dec_norm,
+                                          dropout=args.use_dropout)
+        if 'train' in args.mode:
+            for name in ('discriminator1', 'discriminator2'):
+                m[name] = networks.Discriminator(args.input_dim, dim=args.dim, norm_layer=args.dis_norm,
+                                                 sn=args.dis_sn, num_domains=args.num_domains,
+                                                 image_size=args.crop_size)
+            for net in list(m):
+                self.optimizer[net] = FlatAdam(m[net].parameters(), lr=args.lr,
+                                               betas=(args.beta1, float(args.beta2)), weight_decay=args.wd)
+            if args.use_dis_content:
+                m.content_discriminator = networks.ContentDiscriminator(
+                    dim=m.content_encoder.output_dim, num_domains=args.num_domains)
+                self.optimizer.content_discriminator = FlatAdam(
+                    m.content_discriminator.parameters(), lr=args.lr / 2.5,
+                    betas=(args.beta1, float(args.beta2)), weight_decay=args.wd)
+            if args.gan_mode not in ('vanilla', 'lsgan', 'wgangp', 'hinge'):
+                raise NotImplementedError(f'Loss {args.gan_mode} is not implemented')
+            self.print_loss = ['g_adv', 'g_cls', 'l1_cc_rec']
+
+    # ------------------------------------------------------------------ small pieces
+    def gan_loss(self, pred, is_real):
+        """GANLoss.forward (reference loss.py:52-64)."""
+        mode = self.args.gan_mode
+        if mode == 'wgangp':
+            return -pred.mean() if is_real else pred.mean()
+        if mode == 'lsgan':
+            return F.mse_loss(pred, torch.full_like(pred, 1.0 if is_real else 0.0))
+        return _bce(pred, 1.0 if is_real else 0.0)
+
+    def get_z_random(self, bs, latent_dim):
+        if self.rng is not None:
+            return self.rng((bs, latent_dim)).to(self.device)
+        return torch.randn(bs, latent_dim, device=self.device)
+
+    def set_inputs(self, inputs):
+        dev = self.device
+        self.img_a = inputs['x1'].to(dev, non_blocking=True).detach()
+        self.cls_a = inputs['y1'].to(dev, non_blocking=True).detach()
+        self.img_b = inputs['x2'].to(dev, non_blocking=True).detach()
+        self.cls_b = inputs['y2'].to(dev, non_blocking=True).detach()
+        self.img = torch.cat((self.img_a, self.img_b), dim=0)
+        self.c_org = torch.cat((self.cls_a, self.cls_b), dim=0)
+
+    def Ec(self, img):
+        return self.model.content_encoder.run(img, self.rng)
+
+    def Es(self, img, c):
+        return self.model.style_encoder.run(img, c, self.rng)
+
+    def G(self, z_c, z_s, c):
+        return self.model.decoder.run(z_c, z_s, c)
+
+    @contextmanager
+    def _frozen(self, *nets):
+        ps = [p for n in nets for p in self.model[n].parameters() if p.requires_grad]
+        for p in ps:
+            p.requires_grad_(False)
+        try:
+            yield
+        finally:
+            for p in ps:
+                p.requires_grad_(True)
+
+    def _step(self, *nets):
+        """all-reduce (data parallel) + Adam for the given networks."""
+        if self.dp is not None:
+            self.dp.allreduce([self.optimizer[n] for n in nets])
+        for n in nets:
+            self.optimizer[n].step()
+
+    # ------------------------------------------------------------------ sampling (:96-109)
+    def _mem_gib(self):
+        return torch.cuda.memory_reserved(0) / (1024 * 1024 * 1024)
+
+    def forward_random(self, img, z_r, c_trg):
+        start = time.time()
+        img_fake = self.G(self.Ec(img), z_r, c_trg)
+        end = time.time()
+        return img_fake, end - start, self._mem_gib()
+
+    def forward_reference(self, img_src, img_ref, c_trg):
+        start = time.time()
+        z_c = self.Ec(img_src)
+        z_s, _, _ = self.Es(img_ref, c_trg)
+        img_fake = self.G(z_c, z_s, c_trg)
+        end = time.time()
+        return img_fake, end - start, self._mem_gib()
+
+    def forward(self, img, c_org):
+        """the three translations used for visualisation (:111-134)."""
+        B = self.args.batch_size
+        z_ca, z_cb = torch.split(self.Ec(img), B, dim=0)
+        z_s, _, _ = self.Es(img, c_org)
+        z_sa, z_sb = torch.split(z_s, B, dim=0)
+        z_sr = self.get_z_random(B, self.args.latent_dim)
+        cls_a, cls_b = torch.split(c_org, B, dim=0)
+        f = self.G(torch.cat((z_cb, z_ca, z_cb)), torch.cat((z_sa, z_sa, z_sr)), torch.cat((cls_a,) * 3))
+        img_ba, img_aa, img_br = torch.split(f, B, dim=0)
+        f = self.G(torch.cat((z_ca, z_cb, z_ca)), torch.cat((z_sb, z_sb, z_sr)), torch.cat((cls_b,) * 3))
+        img_ab, img_bb, img_ar = torch.split(f, B, dim=0)
+        return torch.cat((img_ba, img_ab)), torch.cat((img_br, img_ar)), torch.cat((img_aa, img_bb))
+
+    # ------------------------------------------------------------------ phase D (:146-223)
+    def update_discriminator(self, img, c_org):
+        B = self.args.batch_size
+        with torch.no_grad():
+            cls_a, cls_b = torch.split(c_org, B, dim=0)
+            z_ca, z_cb = torch.split(self.Ec(img), B, dim=0)
+            z_s, _, _ = self.Es(img, c_org)
+            z_sa, z_sb = torch.split(z_s, B, dim=0)
+            z_sr = self.get_z_random(B, self.args.latent_dim)
+            img_ba, img_br = torch.split(self.G(torch.cat((z_cb, z_cb)), torch.cat((z_sa, z_sr)),
+                                                torch.cat((cls_a, cls_a))), B, dim=0)
+            img_ab, img_ar = torch.split(self.G(torch.cat((z_ca, z_ca)), torch.cat((z_sb, z_sr)),
+                                                torch.cat((cls_b, cls_b))), B, dim=0)
+            img_fake = torch.cat((img_ba, img_ab))
+            img_random = torch.cat((img_br, img_ar))
+        self.optimizer.discriminator1.zero_grad()
+        self.backward_discriminator(self.model.discriminator1, img, img_fake, c_org)
+        self._step('discriminator1')
+        self.optimizer.discriminator2.zero_grad()
+        self.backward_discriminator(self.model.discriminator2, img, img_random, c_org)
+        self._step('discriminator2')
+
+    def backward_discriminator(self, netD, real, fake, c_org):
+        n = real.shape[0]
+        pred, pred_cls = netD.run(torch.cat((fake.detach(), real)))
+        pred_fake, pred_real = pred[:n], pred[n:]
+        if 'hinge' in self.args.gan_mode:
+            loss_d_adv = F.relu(1.0 - pred_real).mean() + F.relu(1.0 + pred_fake).mean()
+        else:
+            loss_d_adv = self.gan_loss(pred_fake, 0) + self.gan_loss(pred_real, 1)
+        loss_d_cls = _bce(pred_cls[n:], c_org)
+        loss_d = loss_d_adv + self.args.lambda_cls * loss_d_cls
+        loss_d.backward()
+        self._scalars.update(d_adv=loss_d_adv.detach(), d_cls=loss_d_cls.detach(), d_total=loss_d.detach())
+
+    # ------------------------------------------------------------------ phases G1 / G2 (:225-394)
+    def update_generator(self, img, c_org):
+        for n in ('content_encoder', 'style_encoder', 'decoder'):
+            self.optimizer[n].zero_grad()
+        self.backward_generator(img, c_org)
+        self._step('content_encoder', 'style_encoder', 'decoder')
+        for n in ('content_encoder', 'decoder'):
+            self.optimizer[n].zero_grad()
+        self.backward_decoder_random(img, c_org)
+        self._step('content_encoder', 'decoder')
+
+    def _g_adv(self, netD, fake, c_org):
+        pred_fake, pred_fake_cls = netD.run(fake)
+        adv = -pred_fake.mean() if 'hinge' in self.args.gan_mode else self.gan_loss(pred_fake, 1)
+        return adv, _bce(pred_fake_cls, c_org) * self.args.lambda_cls_G
+
+    def backward_generator(self, img, c_org):
+        B = self.args.batch_size
+        world = 1 if self.dp is None else self.dp.world
+        cls_a, cls_b = torch.split(c_org, B, dim=0)
+        z_c = self.Ec(img)
+        z_ca, z_cb = torch.split(z_c, B, dim=0)
+        z_s, mu, logvar = self.Es(img, c_org)
+        z_sa, z_sb = torch.split(z_s, B, dim=0)
+        img_ba, img_aa = torch.split(self.G(torch.cat((z_cb, z_ca)), torch.cat((z_sa, z_sa)),
+                                            torch.cat((cls_a, cls_a))), B, dim=0)
+        img_ab, img_bb = torch.split(self.G(torch.cat((z_ca, z_cb)), torch.cat((z_sb, z_sb)),
+                                            torch.cat((cls_b, cls_b))), B, dim=0)
+        img_fake = torch.cat((img_ba, img_ab))
+        img_self = torch.cat((img_aa, img_bb))
+        z_c_rec_b, z_c_rec_a = torch.split(self.Ec(img_fake), B, dim=0)
+        z_s_rec, _, _ = self.Es(img_fake, c_org)
+        z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B, dim=0)
+        img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
+                           torch.cat((cls_a, cls_b)))
+        with self._frozen('discriminator1'):
+            loss_g_adv, loss_g_cls = self._g_adv(self.model.discriminator1, img_fake, c_org)
+        loss_g_self = F.l1_loss(img_self, img) * self.args.lambda_rec
+        loss_g_cc = F.l1_loss(img_recon, img) * self.args.lambda_rec
+        N, Hp, Wp, _ = z_c.shape
+        n_zc = N * (Hp - 2 * CONTENT_PAD) * (Wp - 2 * CONTENT_PAD) * self.model.content_encoder.output_dim
+        loss_kl_zc = Fn.SumSqInterior.apply(z_c, CONTENT_PAD) / n_zc * 0.01
+        # SUM over the batch, not a mean (:313-314): under data parallelism it must add up over
+        # ranks while the gradient all-reduce averages -> pre-scale by the world size.
+        loss_kl_zs = torch.sum(1 + logvar - mu.pow(2) - logvar.exp()) * (-0.5) * 0.01
+        loss_g = loss_g_adv + loss_g_cls + loss_g_self + loss_g_cc + loss_kl_zc + loss_kl_zs
+        (loss_g + (world - 1) * loss_kl_zs if world > 1 else loss_g).backward()
+        self._scalars.update(g_adv=loss_g_adv.detach(), g_cls=loss_g_cls.detach(),
+                             kl_zc=loss_kl_zc.detach(), kl_zs=loss_kl_zs.detach(),
+                             l1_self_rec=loss_g_self.detach(), l1_cc_rec=loss_g_cc.detach(),
+                             total_g=loss_g.detach())
+
+    def backward_decoder_random(self, img, c_org):
+        B = self.args.batch_size
+        cls_a, cls_b = torch.split(c_org, B, dim=0)
+        z_ca, z_cb = torch.split(self.Ec(img), B, dim=0)
+        z_sr = self.get_z_random(B, self.args.latent_dim)
+        img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
+        with self._frozen('discriminator2', 'style_encoder'):
+            loss_g_adv2, loss_g_cls2 = self._g_adv(self.model.discriminator2, img_random, c_org)
+            _, mu2, _ = self.Es(img_random, c_org)
+        mu2_a, mu2_b = torch.split(mu2, B, dim=0)
+        loss_z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
+        (loss_z_l1 + loss_g_adv2 + loss_g_cls2).backward()
+        self._scalars.update(l1_recon_z=loss_z_l1.detach(), gan2=loss_g_adv2.detach(),
+                             gan2_cls=loss_g_cls2.detach())
+
+    # ------------------------------------------------------------------ the iteration (:421-430)
+    def optimize_parameters(self, global_iter):
+        self._scalars = {}
+        if self.args.use_dis_content:
+            raise NotImplementedError("--use_dis_content is the next row of the scope table (SURVEY.md §8f-1)")
+        self.update_discriminator(self.img, self.c_org)
+        self.update_generator(self.img, self.c_org)
+        keys = list(self._scalars)
+        vals = torch.stack([self._scalars[k].float().reshape(()) for k in keys]).tolist()   # one sync
+        for k, v in zip(keys, vals):
+            self.loss[k] = v
+
+    def compute_visuals(self):
+        B = self.args.batch_size
+        with torch.no_grad():
+            img_fake, img_random, img_self = self.forward(self.img, self.c_org)
+        fa, fb = torch.split(img_fake, B, dim=0)
+        ra, rb = torch.split(img_random, B, dim=0)
+        sa, sb = torch.split(img_self, B, dim=0)
+        row1 = torch.cat((self.img_a[0:1], fb[0:1], rb[0:1], sa[0:1]), dim=3)
+        row2 = torch.cat((self.img_b[0:1], fa[0:1], ra[0:1], sb[0:1]), dim=3)
+        return torch.cat((row1, row2), dim=2)

@@ -1,0 +1,133 @@
+"""Base class of the translation models: same public surface as the reference's
+src/models/model.py:15-122 (dicts `.model/.optimizer/.scheduler/.loss`, initialize / update_lr /
+save / load / write_loss / print_losses / save_images / get_current_lr), so that the reference's
+train.py and sample.py drive this implementation unchanged.
+"""
+import os
+from abc import ABC, abstractmethod
+
+import torch
+import torch.nn as nn
+
+from ..utils import AttributeDict
+from .core.functions import get_scheduler, init_net
+
+
+class _NullWriter:
+    """stand-in when tensorboardX is not installed (the reference hard-requires it, model.py:13)"""
+
+    def __init__(self, *a, **k):
+        pass
+
+    def add_scalar(self, *a, **k):
+        pass
+
+
+def _summary_writer(logdir):
+    try:
+        from tensorboardX import SummaryWriter
+        return SummaryWriter(log_dir=logdir)
+    except Exception:
+        return _NullWriter()
+
+
+class Model(ABC, nn.Module):
+    def __init__(self, args):
+        super().__init__()
+        self.args = args
+        self.device = 'cuda' if torch.cuda.is_available() else 'cpu'
+        # AttributeDict is deliberately NOT an nn.Module container: like in the reference
+        # (model.py:24) model.train()/.eval()/.to() do not reach the nets.
+        self.model = AttributeDict()
+        self.optimizer = AttributeDict()
+        self.scheduler = AttributeDict()
+        self.loss = AttributeDict()
+        if 'train' in args.mode:
+            self.writer = _summary_writer(getattr(args, 'logdir', None))
+        self.print_loss = []
+        self.rng = None          # None: device Philox; callable(shape)->cpu tensor: replayed draws
+        self.dp = None           # masterthesis_b200.parallel.DataParallelGroup or None
+
+    @abstractmethod
+    def set_inputs(self, inputs):
+        pass
+
+    @abstractmethod
+    def optimize_parameters(self, global_iter):
+        pass
+
+    # ------------------------------------------------------------------ lifecycle
+    def initialize(self):
+        if self.device != 'cuda':
+            raise RuntimeError("masterthesis_b200 needs a CUDA device (sm_100a); there is no CPU path")
+        init_type = None if self.args.resume else self.args.init_type
+        for net in self.model:
+            self.model[net] = init_net(self.model[net], init_type=init_type,
+                                       init_gain=getattr(self.args, 'init_gain', 0.02),
+                                       gpu_ids=self.args.gpu_ids, device=self.device)
+        if 'train' in self.args.mode:
+            self.args.last_iter = -1 if self.args.resume_opt is None else self.args.last_iter
+            self.init_scheduler()
+            self.load(self.args.resume, self.args.resume_opt)
+        else:
+            self.load(self.args.resume)
+
+    def init_scheduler(self):
+        for opt in self.optimizer:
+            if self.args.last_iter != -1:
+                for g in self.optimizer[opt].param_groups:
+                    g.setdefault('initial_lr', g['lr'])
+            self.scheduler[opt] = get_scheduler(self.optimizer[opt], self.args, self.args.last_iter)
+
+    def get_current_lr(self):
+        return {opt: self.optimizer[opt].param_groups[0]['lr'] for opt in self.optimizer}
+
+    def update_lr(self):
+        for net in self.model:
+            self.scheduler[net].step()
+
+    # ------------------------------------------------------------------ checkpoints
+    # Wire format of the reference (model.py:70-100): model_{it}.ckpt = {net: state_dict},
+    # opt_{it}.ckpt = {net: optimizer.state_dict()}.  DataParallel-trained reference checkpoints
+    # carry a 'module.' prefix (functions.py:101); it is accepted on load.
+    def save(self, it):
+        path = os.path.join(self.args.checkpoint_dir, f"model_{it}.ckpt")
+        torch.save({net: self.model[net].state_dict() for net in self.model}, path)
+        path = os.path.join(self.args.checkpoint_dir, f"opt_{it}.ckpt")
+        torch.save({opt: self.optimizer[opt].state_dict() for opt in self.optimizer}, path)
+
+    def load(self, checkpoint, opt_ckpt=None):
+        if checkpoint is not None:
+            ckpt = torch.load(checkpoint, map_location='cpu')
+            for net in ckpt:
+                if net in self.model.keys():
+                    print(f"Loading checkpoint for : {net}")
+                    sd = {(k[7:] if k.startswith('module.') else k): v for k, v in ckpt[net].items()}
+                    self.model[net].load_state_dict(sd)
+                else:
+                    print(f"Checkpoint for {net} network is not found.")
+        if opt_ckpt is not None:
+            ckpt = torch.load(opt_ckpt, map_location='cpu')
+            for opt in ckpt:
+                if opt in self.optimizer.keys():
+                    print(f"Loading checkpoint for {opt} optimizer.")
+                    self.optimizer[opt].load_state_dict(ckpt[opt])
+                else:
+                    print(f"Checkpoint for {opt} optimizer is not found.")
+
+    # ------------------------------------------------------------------ logging
+    def save_images(self, it):
+        import torchvision
+        visuals = self.compute_visuals()
+        name = os.path.join(self.args.display_dir, f'gen_{it}.jpg')
+        torchvision.utils.save_image(visuals / 2 + 0.5, name, nrow=1)
+
+    def write_loss(self, global_iter):
+        for k in self.loss:
+            self.writer.add_scalar(k, self.loss[k], global_iter)
+
+    def print_losses(self):
+        return {k: self.loss[k] for k in self.loss if k in self.print_loss}
+
+    def compute_metrics(self):
+        pass

@@ -1,0 +1,107 @@
+"""FlatAdam: torch.optim.Adam semantics (coupled L2, bias correction; the reference builds
+torch.optim.Adam(lr, betas, weight_decay) per net, adain_model.py:58-61) over ONE flat fp32 bucket
+per network, stepped by a single CUDA launch (csrc/ew_optim.cu).  Parameters and their .grad are
+re-pointed to views of the flat buffers, so zero_grad is one memset and the data-parallel
+all-reduce is one NCCL call on the gradient bucket.  state_dict() keeps torch.optim.Adam's layout
+(per-parameter step / exp_avg / exp_avg_sq) so opt_{it}.ckpt files stay interchangeable
+(reference model.py:77-82)."""
+import torch
+
+from . import _lib, ops
+
+
+class FlatAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        params = list(params)
+        defaults = dict(lr=lr, betas=(float(betas[0]), float(betas[1])), eps=eps,
+                        weight_decay=weight_decay, amsgrad=False, maximize=False, foreach=None,
+                        capturable=False, differentiable=False, fused=None)
+        super().__init__(params, defaults)
+        self._flat = None
+        self.grad_scale = 1.0      # set to 1/world by the data-parallel wrapper
+
+    # ------------------------------------------------------------------ flat buckets
+    def _params(self):
+        return [p for g in self.param_groups for p in g['params']]
+
+    def _ensure_flat(self):
+        ps = self._params()
+        dev = ps[0].device
+        if self._flat is not None and self._flat['device'] == dev and \
+                all(p.data_ptr() == a for p, a in zip(ps, self._flat['ptrs'])):
+            return
+        if dev.type != 'cuda':
+            raise RuntimeError("FlatAdam has no CPU path: move the network to a CUDA device first")
+        offs, n = [], 0
+        for p in ps:
+            offs.append(n)
+            n += (p.numel() + 3) // 4 * 4           # keep every view 16-byte aligned
+        flat_p = torch.zeros(n, dtype=torch.float32, device=dev)
+        flat_g = torch.zeros(n, dtype=torch.float32, device=dev)
+        flat_m = torch.zeros(n, dtype=torch.float32, device=dev)
+        flat_v = torch.zeros(n, dtype=torch.float32, device=dev)
+        for p, o in zip(ps, offs):
+            k = p.numel()
+            flat_p[o:o + k].copy_(p.data.reshape(-1))
+            old_g = p.grad
+            p.data = flat_p[o:o + k].view(p.shape)
+            p.grad = flat_g[o:o + k].view(p.shape)
+            if old_g is not None:
+                p.grad.copy_(old_g)
+            st = self.state[p]
+            if 'exp_avg' in st:                      # state loaded from a checkpoint
+                flat_m[o:o + k].copy_(st['exp_avg'].reshape(-1))
+                flat_v[o:o + k].copy_(st['exp_avg_sq'].reshape(-1))
+            st['exp_avg'] = flat_m[o:o + k].view(p.shape)
+            st['exp_avg_sq'] = flat_v[o:o + k].view(p.shape)
+            st.setdefault('step', torch.tensor(0.0))
+        self._flat = dict(p=flat_p, g=flat_g, m=flat_m, v=flat_v, n=n, device=dev,
+                          ptrs=[p.data_ptr() for p in ps])
+
+    @property
+    def grad_bucket(self):
+        self._ensure_flat()
+        return self._flat['g']
+
+    def zero_grad(self, set_to_none: bool = False):
+        self._ensure_flat()
+        self._flat['g'].zero_()
+        off = 0
+        for p in self._params():      # re-attach views that were replaced (p.grad = None, ...)
+            k = p.numel()
+            if p.grad is None or p.grad.data_ptr() != self._flat['g'].data_ptr() + 4 * off:
+                p.grad = self._flat['g'][off:off + k].view(p.shape)
+            off += (k + 3) // 4 * 4
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._flat = None                            # rebuild views around the loaded state
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        self._ensure_flat()
+        g0 = self.param_groups[0]
+        ps = self._params()
+        off = 0
+        for p in ps:                                  # gradients that autograd re-allocated
+            k = p.numel()
+            want = self._flat['g'].data_ptr() + 4 * off
+            if p.grad is not None and p.grad.data_ptr() != want:
+                self._flat['g'][off:off + k].copy_(p.grad.reshape(-1))
+                p.grad = self._flat['g'][off:off + k].view(p.shape)
+            off += (k + 3) // 4 * 4
+        st0 = self.state[ps[0]]
+        step = int(st0['step'].item() if torch.is_tensor(st0['step']) else st0['step']) + 1
+        f = self._flat
+        _lib.check(_lib.lib().mt_adam_flat(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
+                                           f['v'].data_ptr(), f['n'], float(g0['lr']), g0['betas'][0],
+                                           g0['betas'][1], g0['eps'], g0['weight_decay'], step,
+                                           float(self.grad_scale), ops._stream()), "mt_adam_flat")
+        ops._count()
+        step_t = torch.tensor(float(step))
+        for p in ps:
+            self.state[p]['step'] = step_t
+        # the kernel wrote through raw pointers: advance autograd's version counters so that the
+        # packed bf16 weight caches (blocks._ConvParams.packed) refresh.
+        torch._C._autograd._unsafe_set_version_counter(ps, [p._version + 1 for p in ps])
+        return None

@@ -1,0 +1,198 @@
+"""Network- and step-level parity cases: CUDA path vs (a) the reference's own outputs committed in
+tests/golden/ and (b) the fp32 oracle run on the same seeded inputs.  GPU only.
+
+Tolerances (bf16 storage / fp32 accumulate vs the reference's fp32):
+  outputs / losses : max|a-b| / max|b| <= 1e-2 ... 3e-2 for the deepest compositions (stated per check)
+  gradients        : cosine similarity >= 0.999 (>= 0.99 for the deepest chains)
+"""
+import json
+import os
+
+import numpy as np
+import torch
+
+from oracle import nets as onets
+from oracle import ref_import, step as ostep, synth
+
+GOLD = os.path.join(os.path.dirname(__file__), 'golden')
+DEV = 'cuda'
+
+
+def rel(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-12)).item()
+
+
+def cos(a, b):
+    a, b = a.double().cpu().flatten(), b.double().cpu().flatten()
+    return (torch.dot(a, b) / (a.norm() * b.norm()).clamp_min(1e-30)).item()
+
+
+def load_gold(name):
+    z = np.load(os.path.join(GOLD, name + '.npz'))
+    return json.loads(str(z['meta'])), {k: torch.from_numpy(z[k]) for k in z.files if k != 'meta'}
+
+
+def build_nets(meta, size):
+    from masterthesis_b200.models.core import networks
+    dim, nd, latent, seed = meta['dim'], meta['nd'], meta['latent'], meta['seed']
+    ns = {
+        'content_encoder': networks.ContentEncoder(3, dim),
+        'style_encoder': networks.ReparameterizedStyleEncoder(3, latent, dim, num_domains=nd,
+                                                              norm_layer=None, activation='lrelu'),
+        'decoder': networks.AdaINDecoder(3, dim * 4, num_domains=nd, latent_dim=latent),
+        'discriminator': networks.Discriminator(3, dim, num_domains=nd, image_size=size),
+    }
+    for n, net in ns.items():
+        net.load_state_dict(synth.synth_params(meta['shapes'][n], seed, n + '.'))
+        net.to(DEV)
+    return ns
+
+
+def nets_vs_golden(name):
+    """Same computation as oracle/make_golden.py:nets_case, on the CUDA path, vs the REFERENCE's
+    recorded outputs and gradients."""
+    meta, gold = load_gold(name)
+    seed, N, nd, size, s = meta['seed'], meta['N'], meta['nd'], meta['size'], meta['sub']
+    ns = build_nets(meta, size)
+    draws = synth.Draws(seed)
+    img = synth.synth_images(N, size, seed).to(DEV).requires_grad_(True)
+    c = synth.synth_onehot(N, nd, seed).to(DEV)
+    z_c = ns['content_encoder'].run(img, draws)
+    z, mu, logvar = ns['style_encoder'].run(img, c, draws)
+    fake = ns['decoder'].run(z_c, z, c)
+    d_out, d_cls = ns['discriminator'].run(fake)
+    proj = synth.synth_tensor('proj', fake.shape, seed).to(DEV)
+    loss = (fake * proj).sum() + d_out.sum() + (d_cls * c).sum() + mu.sum() + 0.5 * logvar.sum()
+    loss.backward()
+    from masterthesis_b200.models.core.blocks import from_padded
+    r = {
+        'z_c': rel(from_padded(z_c.detach(), meta['dim'] * 4, 1)[:, :, ::s, ::s], gold['z_c']),
+        'mu': rel(mu.detach(), gold['mu']), 'logvar': rel(logvar.detach(), gold['logvar']),
+        'fake': rel(fake.detach()[:, :, ::s, ::s], gold['fake']),
+        'd_out': rel(d_out.detach(), gold['d_out']), 'd_cls': rel(d_cls.detach(), gold['d_cls']),
+        'cos_dimg': cos(img.grad[:, :, ::s, ::s], gold['dimg']),
+    }
+    for k, g in gold.items():
+        if not k.startswith('grad.'):
+            continue
+        _, n, key = k.split('.', 2)
+        mine = dict(ns[n].named_parameters())[key].grad
+        if mine.numel() > 20000:
+            mine = mine.flatten()[:: max(1, mine.numel() // 20000)]
+        r['cos_' + k[5:]] = cos(mine, g.flatten())
+    return r
+
+
+def make_model(dim, size, B, nd=4, seed=2, shapes=None):
+    from masterthesis_b200 import models
+    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=B, num_domains=nd, init_type=None)
+    m = models.AdaINModel(args)
+    if shapes is None:
+        shapes = {n: {k: list(v.shape) for k, v in m.model[n].state_dict().items()} for n in m.model}
+    params = {n: synth.synth_params(shapes[n], seed, n + '.') for n in m.model}
+    for n in m.model:
+        m.model[n].load_state_dict(params[n])
+    m.initialize()
+    return m, params
+
+
+def batch(B, size, nd, seed):
+    return {'x1': synth.synth_images(B, size, seed, 'x1'), 'x2': synth.synth_images(B, size, seed, 'x2'),
+            'y1': synth.synth_onehot(B, nd, seed, 'y'), 'y2': synth.synth_onehot(B, nd, seed, 'y', offset=1)}
+
+
+def step_vs_golden(name='step_dim8_64'):
+    """AdaINModel.optimize_parameters on the CUDA path vs the REFERENCE's recorded losses, and its
+    gradients at every optimizer step vs the oracle's."""
+    meta, gold = load_gold(name)
+    seed, B, nd, size, dim = meta['seed'], meta['B'], meta['nd'], meta['size'], meta['dim']
+    m, params = make_model(dim, size, B, nd, seed, meta['shapes'])
+    m.rng = synth.Draws(seed)
+    # oracle twin on the GPU in fp32 (TF32 off) for the gradient comparison
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    st = ostep.AdaINStep({n: {k: v.to(DEV) for k, v in p.items()} for n, p in params.items()}, B)
+    st.Ec = lambda x, draw: onets.content_encoder(
+        st.P['content_encoder'], x, draw((x.size(0), dim * 4, x.size(2) // 4, x.size(3) // 4)).to(DEV))
+    odraw_src = synth.Draws(seed)
+    odraw = lambda shape: odraw_src(shape).to(DEV)  # noqa: E731
+
+    mine_g, ref_g = [], []
+    for n in m.optimizer:
+        opt = m.optimizer[n]
+        orig = opt.step
+
+        def rec(orig=orig, n=n, opt=opt):
+            mine_g.append((n, {k: p.grad.detach().clone() for k, p in m.model[n].named_parameters()
+                               if p.grad is not None}))
+            return orig()
+        opt.step = rec
+    for n in st.opt:
+        o = st.opt[n]
+        orig = o.step
+
+        def rec2(orig=orig, n=n, o=o):
+            ref_g.append((n, {k: p.grad.detach().clone() for k, p in o.params.items() if p.grad is not None}))
+            return orig()
+        o.step = rec2
+
+    b = batch(B, size, nd, seed)
+    r = {}
+    for it in range(meta['iters']):
+        m.set_inputs(b)
+        m.optimize_parameters(it)
+        st.optimize_parameters(m.img.clone(), m.c_org.clone(), odraw)
+        worst = 0.0
+        for k in m.loss:
+            ref = float(gold[f'loss.{it}.{k}'])
+            worst = max(worst, abs(m.loss[k] - ref) / max(1.0, abs(ref)))
+        r[f'loss_it{it}'] = worst
+    assert [list(s) for s in m.rng.log] == meta['draws'], "RNG call order differs from the reference"
+    # gradient cosine per (step point, net): first iteration only (identical weights there)
+    for i, ((n1, g1), (n2, g2)) in enumerate(zip(mine_g[:5], ref_g[:5])):
+        assert n1 == n2
+        a = torch.cat([g1[k].flatten() for k in g2 if k in g1])
+        bb = torch.cat([g2[k].flatten() for k in g2 if k in g1])
+        r[f'cos_step{i}_{n1}'] = cos(a, bb)
+        # discriminator phases in the G steps skip D/Es grads by design; every key of ours must exist in ref
+    return r
+
+
+def sampling_vs_oracle(dim=64, size=256, N=2, nd=4, seed=5):
+    """forward_reference / forward_random (config 2 shape) vs the fp32 oracle on the GPU."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    from masterthesis_b200 import models
+    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=N, num_domains=nd, init_type=None,
+                                   mode='test')
+    m = models.AdaINModel(args)
+    shapes = {n: {k: list(v.shape) for k, v in m.model[n].state_dict().items()} for n in m.model}
+    params = {n: synth.synth_params(shapes[n], seed, n + '.') for n in m.model}
+    for n in m.model:
+        m.model[n].load_state_dict(params[n])
+    m.initialize()
+    m.rng = synth.Draws(seed)
+    st = ostep.AdaINStep({n: {k: v.to(DEV) for k, v in p.items()} for n, p in params.items()}, N)
+    st.Ec = lambda x, draw: onets.content_encoder(
+        st.P['content_encoder'], x, draw((x.size(0), dim * 4, x.size(2) // 4, x.size(3) // 4)).to(DEV))
+    src = synth.Draws(seed)
+    odraw = lambda shape: src(shape).to(DEV)  # noqa: E731
+    a = synth.synth_images(N, size, seed, 'src').to(DEV)
+    b = synth.synth_images(N, size, seed, 'ref').to(DEV)
+    c = synth.synth_onehot(N, nd, seed).to(DEV)
+    z = synth.synth_tensor('zr', (N, 8), seed).to(DEV)
+    with torch.no_grad():
+        y1, secs, gib = m.forward_reference(a, b, c)
+        y2, _, _ = m.forward_random(a, z, c)
+    r1 = st.forward_reference(a, b, c, odraw)
+    r2 = st.forward_random(a, z, c, odraw)
+    return {'forward_reference': rel(y1, r1), 'forward_random': rel(y2, r2)}
+
+
+CASES = {
+    'nets_dim16_64': lambda: nets_vs_golden('nets_dim16_64'),
+    'nets_dim64_256': lambda: nets_vs_golden('nets_dim64_256'),
+    'step_dim8_64': step_vs_golden,
+    'sampling_256': sampling_vs_oracle,
+}

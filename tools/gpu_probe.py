@@ -11,12 +11,16 @@ sys.path.insert(0, ROOT)
 if len(sys.argv) >= 3 and sys.argv[1] == "--one":
     import torch
     from tests.kernel_cases import CASES
+    from tests.model_cases import CASES as MCASES
+    CASES = dict(CASES); CASES.update(MCASES)
     res = CASES[sys.argv[2]]()
     torch.cuda.synchronize()
     print("RESULT " + json.dumps(res))
     sys.exit(0)
 
 from tests.kernel_cases import CASES  # noqa: E402
+from tests.model_cases import CASES as MCASES  # noqa: E402
+CASES = dict(CASES); CASES.update(MCASES)
 
 names = sys.argv[1:] or list(CASES)
 for n in names:
@@ -27,7 +31,7 @@ for n in names:
         if line:
             print(f"{n:24s} {line[0][7:]}", flush=True)
         else:
-            tail = (p.stderr or p.stdout).strip().splitlines()[-6:]
+            tail = (p.stderr or p.stdout).strip().splitlines()[-14:]
             print(f"{n:24s} FAILED rc={p.returncode}\n    " + "\n    ".join(tail), flush=True)
     except subprocess.TimeoutExpired:
         print(f"{n:24s} TIMEOUT", flush=True)
