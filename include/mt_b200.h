@@ -31,6 +31,8 @@ typedef struct MtConv2d {
   int out_H, out_W, out_pad;
   int act;      /* MT_ACT_* fused into the epilogue */
   float slope;  /* LeakyReLU slope (functions.py:34 -> 0.01) */
+  int window;   /* 1: image-stem row-window mode (requires mt_conv_window_mode(Cin_s,kw) and an
+                   input buffer followed by >= 128 B of finite slack, e.g. from the image packer) */
 } MtConv2d;
 
 /* ---- library --------------------------------------------------------------------- */
@@ -38,7 +40,8 @@ int mt_version(void);
 const char* mt_error_string(int code);
 /* stored channel count for a logical one (multiple of 8) */
 int mt_stored_channels(int c);
-/* 1 if a (Cin_s, kw) stem runs in row-window mode (K = kh x 64 window elements) */
+/* 1 if a (Cin_s, kw) stem runs in row-window mode (K = kh x 64 window elements): Cin_s <= 16 and
+ * Cin_s*kw <= 64.  The input buffer of such a conv must be followed by >= 128 B of finite data. */
 int mt_conv_window_mode(int Cin_s, int kw);
 
 /* ---- weight packing (fp32 OIHW master -> bf16 GEMM operands) ------------------------

@@ -28,7 +28,7 @@ NVCC_FLAGS = [
 class MtConv2d(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "N", "Hin", "Win", "Cin", "Cin_s", "Hout", "Wout", "Cout", "Cout_s",
-        "kh", "kw", "stride", "zpad", "out_H", "out_W", "out_pad", "act")] + [("slope", ctypes.c_float)]
+        "kh", "kw", "stride", "zpad", "out_H", "out_W", "out_pad", "act")] + [("slope", ctypes.c_float), ("window", ctypes.c_int)]
 
 
 def sources():

@@ -122,7 +122,11 @@ static int check_desc(const MtConv2d* d) {
 using namespace mt;
 
 extern "C" int mt_stored_channels(int c) { return round_up(c, 8); }
-extern "C" int mt_conv_window_mode(int Cin_s, int kw) { return (Cin_s * kw <= 64) ? 1 : 0; }
+// Row-window mode is for image stems only (Cin_s <= 16): their buffers come from mt_image_to_nhwc
+// callers that append zeroed slack, because a 64-element window over-reads the last pixels.
+extern "C" int mt_conv_window_mode(int Cin_s, int kw) {
+  return (Cin_s <= 16 && Cin_s * kw <= 64) ? 1 : 0;
+}
 
 extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
                              const float* bias, void* y, void* stream) {
@@ -130,7 +134,8 @@ extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd
   if (rc) return rc;
   ConvLike c;
   memset(&c, 0, sizeof(c));
-  const bool win = mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0;
+  if (d->window && !(mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0)) return -1009;
+  const bool win = d->window != 0;
   c.a = x; c.An = d->N; c.Ah = d->Hin; c.Aw = d->Win; c.Ac = d->Cin; c.Ac_s = d->Cin_s;
   c.a_mul = d->stride; c.window = win; c.win_stride = d->stride; c.win_cols = d->Wout;
   c.b = w_fwd;

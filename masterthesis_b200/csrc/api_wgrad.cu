@@ -180,7 +180,8 @@ extern "C" int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy,
   if (!d || d->Cin_s % 8 || d->Cout_s % 8) return -1003;
   WgradLike c;
   memset(&c, 0, sizeof(c));
-  const bool win = mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0;
+  if (d->window && !(mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0)) return -1009;
+  const bool win = d->window != 0;
   c.p = dy; c.Pn = d->N; c.Ph = d->Hout; c.Pw = d->Wout; c.Pc = d->Cout; c.Pc_s = d->Cout_s;
   c.q = x; c.Qn = d->N; c.Qh = d->Hin; c.Qw = d->Win; c.Qc = d->Cin; c.Qc_s = d->Cin_s;
   c.q_mul = d->stride; c.window = win; c.win_stride = d->stride; c.win_cols = d->Wout;

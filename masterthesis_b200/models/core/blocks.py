@@ -41,16 +41,16 @@ class _ConvParams(nn.Module):
             bound = 1 / math.sqrt(fan_in) if fan_in > 0 else 0
             nn.init.uniform_(self.bias, -bound, bound)
 
-    def geom(self, zpad=0) -> ConvGeom:
+    def geom(self, zpad=0, stem=False) -> ConvGeom:
         return ConvGeom(self.in_channels, self.out_channels, self.kernel_size, self.kernel_size,
-                        self.stride, zpad, self.transposed)
+                        self.stride, zpad, self.transposed, stem)
 
-    def packed(self, zpad=0):
+    def packed(self, zpad=0, stem=False):
         """bf16 GEMM operands of the fp32 master weight, refreshed when the weight changes."""
         w = self.weight
-        key = (w._version, w.data_ptr(), zpad)
+        key = (w._version, w.data_ptr(), zpad, stem)
         if self._pack is None or self._pack[0] != key:
-            self._pack = (key, ops.pack_weight(w, self.geom(zpad)))
+            self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem)))
         return self._pack[1]
 
     def extra_repr(self):
@@ -127,6 +127,7 @@ class ConvBlock(nn.Module):
             layers.append(act_cls())
         self.block = nn.Sequential(*layers)
         self.zpad = padding
+        self.stem = False   # set by the networks on layers fed by the image packer (slack buffer)
 
     # structural lookups -------------------------------------------------
     @property
@@ -155,8 +156,8 @@ class ConvBlock(nn.Module):
         """x: NHWC bf16 with `self.rpad` reflection border.  Returns a buffer padded by out_pad."""
         self._check()
         conv = self.conv
-        g = conv.geom(self.zpad)
-        wf, wb = conv.packed(self.zpad)
+        g = conv.geom(self.zpad, self.stem)
+        wf, wb = conv.packed(self.zpad, self.stem)
         act = self.act if act_override == 'keep' else act_override
         norm = self.norm
         if norm is None:

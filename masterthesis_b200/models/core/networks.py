@@ -35,6 +35,7 @@ class ContentEncoder(nn.Module):
         for _ in range(n_blocks):
             layers.append(ResnetBlock(dim, dim, norm_layer=norm_layer, activation='relu'))
         layers.append(GaussianNoiseLayer())
+        layers[0].stem = True
         self.model = nn.Sequential(*layers)
         self.output_dim = dim
         self.num_downs, self.n_blocks = num_downs, n_blocks
@@ -80,6 +81,7 @@ class ReparameterizedStyleEncoder(nn.Module):
             dim *= 2
         layers.append(activation())
         layers.append(nn.AdaptiveAvgPool2d(1))
+        layers[0].stem = True
         self.model = nn.Sequential(*layers)
         self.out_nch = out_dim
         self.fc = nn.Linear(out_dim, output_dim)
@@ -182,6 +184,7 @@ class Discriminator(nn.Module):
             nch *= 2
         layers.append(ConvBlock(nch, nch, kernel_size=3, stride=2, padding=1, padding_type=padding_type,
                                 sn=sn, activation=activation, bias=bias))
+        layers[0].stem = True
         self.model = nn.Sequential(*layers)
         self.conv1 = Conv2d(nch, 1, kernel_size=1, stride=1, padding=1, bias=False)
         kernal_size = int(image_size / np.power(2, n_layers))

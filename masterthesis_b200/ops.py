@@ -22,6 +22,54 @@ EPS = 1e-5
 
 _launches = 0  # number of kernels of OURS launched (bench.py reports it)
 
+# MT_DEBUG_POISON=1: every buffer this module allocates is NaN-filled and every wrapper checks its
+# results, so that a read of unwritten memory shows up at the op that consumed it (debug only).
+import os as _os
+POISON = _os.environ.get("MT_DEBUG_POISON", "0") == "1"
+
+
+class _T:
+    """torch.empty / torch.empty_like that poison their result in debug mode"""
+
+    @staticmethod
+    def empty(*a, **k):
+        t = torch.empty(*a, **k)
+        if POISON and t.is_floating_point():
+            t.fill_(float("nan"))
+        return t
+
+    @staticmethod
+    def empty_like(x):
+        t = torch.empty_like(x)
+        if POISON and t.is_floating_point():
+            t.fill_(float("nan"))
+        return t
+
+
+def _checked(fn):
+    if not POISON:
+        return fn
+    import functools
+
+    @functools.wraps(fn)
+    def wrap(*a, **k):
+        out = fn(*a, **k)
+        outs = out if isinstance(out, tuple) else (out,)
+        pad = k.get("out_pad", k.get("out_p", 0))
+        if fn.__name__ == "pool_add_act_fwd":
+            pad = a[3]
+        if pad:
+            outs = tuple(o[:, pad:-pad, pad:-pad, :] for o in outs)
+        for i, o in enumerate(outs):
+            if torch.is_tensor(o) and o.is_floating_point() and not fn.__name__.startswith("empty"):
+                if not torch.isfinite(o.float()).all():
+                    bad = (~torch.isfinite(o.float())).nonzero()
+                    raise RuntimeError(f"[poison] {fn.__name__} output {i} shape {tuple(o.shape)} has "
+                                       f"{bad.shape[0]} non-finite values, first at {bad[0].tolist()}, "
+                                       f"last at {bad[-1].tolist()}")
+        return out
+    return wrap
+
 
 def launches() -> int:
     return _launches
@@ -51,11 +99,11 @@ def _require_cuda(t: torch.Tensor):
 
 
 def empty_act(N, H, W, C, device, slack=False):
-    """bf16 NHWC buffer; with `slack` 64 zeroed elements follow (row-window TMA over-read)."""
+    """bf16 NHWC buffer; with `slack` 256 zeroed elements follow (row-window TMA over-read)."""
     n = N * H * W * C
     if not slack:
-        return torch.empty((N, H, W, C), dtype=torch.bfloat16, device=device)
-    flat = torch.empty(n + 64, dtype=torch.bfloat16, device=device)
+        return _T.empty((N, H, W, C), dtype=torch.bfloat16, device=device)
+    flat = _T.empty(n + 256, dtype=torch.bfloat16, device=device)
     flat[n:].zero_()
     return flat[:n].view(N, H, W, C)
 
@@ -70,6 +118,7 @@ class ConvGeom:
     stride: int = 1
     zpad: int = 0          # logical zero padding (reflection padding lives in the input buffer)
     transposed: bool = False
+    stem: bool = False     # input is an image buffer with slack -> row-window mode if eligible
 
     @property
     def Cin_s(self):
@@ -81,7 +130,8 @@ class ConvGeom:
 
     @property
     def window(self) -> bool:
-        return (not self.transposed) and self.zpad == 0 and self.Cin_s * self.kw <= 64
+        return (self.stem and not self.transposed and self.zpad == 0 and self.Cin_s <= 16
+                and self.Cin_s * self.kw <= 64)
 
     def out_hw(self, Hin, Win):
         if self.transposed:
@@ -93,10 +143,11 @@ class ConvGeom:
         Ho, Wo = self.out_hw(Hin, Win)
         return MtConv2d(N, Hin, Win, self.Cin, self.Cin_s, Ho, Wo, self.Cout, self.Cout_s,
                         self.kh, self.kw, self.stride, self.zpad, Ho + 2 * out_pad, Wo + 2 * out_pad,
-                        out_pad, ACT[act], LRELU_SLOPE)
+                        out_pad, ACT[act], LRELU_SLOPE, int(self.window))
 
 
 # ----------------------------------------------------------------------------- weights
+@_checked
 def pack_weight(w: torch.Tensor, g: ConvGeom):
     """fp32 master weight (OIHW, or IOHW for transposed) -> (w_fwd, w_bwd) bf16 GEMM operands."""
     _require_cuda(w)
@@ -104,8 +155,8 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
     w = w.detach().contiguous().float()
     nf = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0)
     nb = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 1)
-    wf = torch.empty(nf, dtype=torch.bfloat16, device=w.device)
-    wb = torch.empty(nb, dtype=torch.bfloat16, device=w.device)
+    wf = _T.empty(nf, dtype=torch.bfloat16, device=w.device)
+    wb = _T.empty(nb, dtype=torch.bfloat16, device=w.device)
     check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed), int(g.window),
                                 _p(wf), _p(wb), _stream()), "mt_pack_conv_weight")
     _count()
@@ -113,6 +164,7 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
 
 
 # ----------------------------------------------------------------------------- convolutions
+@_checked
 def conv_fwd(x, wf, bias, g: ConvGeom, act=None, out_pad=0, out=None):
     """x: [N,Hin,Win,Cin_s] -> [N,Ho+2op,Wo+2op,Cout_s]; border of `out` is NOT filled here."""
     _require_cuda(x)
@@ -127,6 +179,7 @@ def conv_fwd(x, wf, bias, g: ConvGeom, act=None, out_pad=0, out=None):
     return out
 
 
+@_checked
 def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
     """dy: dense [N,Ho,Wo,Cout_s] -> dx [N,Hin,Win,Cin_s] (gradient of the padded input buffer)."""
     _require_cuda(dy)
@@ -141,6 +194,7 @@ def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
     return dx
 
 
+@_checked
 def conv_wgrad(x, dy, g: ConvGeom):
     """-> fp32 weight gradient in the master layout (OIHW, or IOHW for transposed)."""
     _require_cuda(x)
@@ -157,7 +211,7 @@ def conv_wgrad(x, dy, g: ConvGeom):
     fn = L.mt_conv_transpose2d_wgrad if g.transposed else L.mt_conv2d_wgrad
     check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), _stream()), "conv_wgrad")
     shape = (g.Cin, g.Cout, g.kh, g.kw) if g.transposed else (g.Cout, g.Cin, g.kh, g.kw)
-    dw = torch.empty(shape, dtype=torch.float32, device=x.device)
+    dw = _T.empty(shape, dtype=torch.float32, device=x.device)
     check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
                                  int(g.window), _p(dw), _stream()), "unpack_wgrad")
     _count(2)
@@ -165,6 +219,7 @@ def conv_wgrad(x, dy, g: ConvGeom):
 
 
 # ----------------------------------------------------------------------------- layout
+@_checked
 def image_to_nhwc(img, onehot, pad, Cs=None):
     _require_cuda(img)
     N, Ci, H, W = img.shape
@@ -179,15 +234,17 @@ def image_to_nhwc(img, onehot, pad, Cs=None):
     return out
 
 
+@_checked
 def image_grad_from_nhwc(dpad, Ci, H, W, pad):
     N, _, _, Cs = dpad.shape
-    dimg = torch.empty((N, Ci, H, W), dtype=torch.float32, device=dpad.device)
+    dimg = _T.empty((N, Ci, H, W), dtype=torch.float32, device=dpad.device)
     check(_lib.lib().mt_image_grad_from_nhwc(_p(dpad), N, Ci, H, W, pad, Cs, _p(dimg), _stream()),
           "image_grad_from_nhwc")
     _count()
     return dimg
 
 
+@_checked
 def reflect_border_(buf, pad):
     if pad == 0:
         return buf
@@ -198,6 +255,7 @@ def reflect_border_(buf, pad):
     return buf
 
 
+@_checked
 def reflect_fold(dpad, pad):
     N, Hp, Wp, C = dpad.shape
     if pad == 0:
@@ -217,24 +275,27 @@ def add_interior_(dpad, dense, pad):
 
 
 # ----------------------------------------------------------------------------- norms
+@_checked
 def plane_stats(x):
     N, H, W, C = x.shape
-    stats = torch.empty((N, C, 2), dtype=torch.float32, device=x.device)
+    stats = _T.empty((N, C, 2), dtype=torch.float32, device=x.device)
     check(_lib.lib().mt_plane_stats(_p(x), N, H * W, C, _p(stats), _stream()), "plane_stats")
     _count()
     return stats
 
 
+@_checked
 def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None):
     N, C, _ = stats.shape
-    ss = torch.empty_like(stats)
-    mr = torch.empty_like(stats)
+    ss = _T.empty_like(stats)
+    mr = _T.empty_like(stats)
     check(_lib.lib().mt_norm_finalize(_p(stats), NORM[mode], N, C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
                                       _p(ss), _p(mr), _stream()), "norm_finalize")
     _count()
     return ss, mr
 
 
+@_checked
 def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, out=None):
     N, H, W, C = x.shape
     if out is None:
@@ -245,27 +306,29 @@ def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, 
     return out
 
 
+@_checked
 def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None):
     """g, x dense [N,H,W,C].  Returns (dx, dgb | None, dln_w | None, dln_b | None)."""
     N, H, W, C = x.shape
     L = _lib.lib()
     dev = x.device
-    sums = torch.empty((N, C, 2), dtype=torch.float32, device=dev)
+    sums = _T.empty((N, C, 2), dtype=torch.float32, device=dev)
     check(L.mt_norm_bwd_reduce(_p(g), _p(x), _p(ss), N, H * W, C, ACT[act], LRELU_SLOPE, _p(sums),
                                _stream()), "norm_bwd_reduce")
-    coef = torch.empty((N, C, 3), dtype=torch.float32, device=dev)
-    dgb = torch.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
+    coef = _T.empty((N, C, 3), dtype=torch.float32, device=dev)
+    dgb = _T.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
     dlw = torch.zeros(C, dtype=torch.float32, device=dev) if (mode == "layer" and ln_w is not None) else None
     dlb = torch.zeros(C, dtype=torch.float32, device=dev) if dlw is not None else None
     check(L.mt_norm_bwd_finalize(_p(sums), _p(mr), NORM[mode], N, C, H * W, _p(gb), _p(ln_w), _p(coef),
                                  _p(dgb), _p(dlw), _p(dlb), _stream()), "norm_bwd_finalize")
-    dx = torch.empty_like(x)
+    dx = _T.empty_like(x)
     check(L.mt_norm_bwd_apply(_p(g), _p(x), _p(ss), _p(coef), N, H * W, C, ACT[act], LRELU_SLOPE,
                               _p(dx), _stream()), "norm_bwd_apply")
     _count(3)
     return dx, dgb, dlw, dlb
 
 
+@_checked
 def act_bwd_fold(dpad, out_pad, pad, act):
     N, Hp, Wp, C = out_pad.shape
     H, W = Hp - 2 * pad, Wp - 2 * pad
@@ -277,6 +340,7 @@ def act_bwd_fold(dpad, out_pad, pad, act):
 
 
 # ----------------------------------------------------------------------------- pooling / heads
+@_checked
 def avgpool2_fwd(x_pad, pad):
     N, Hp, Wp, C = x_pad.shape
     H, W = Hp - 2 * pad, Wp - 2 * pad
@@ -294,6 +358,7 @@ def avgpool2_bwd_add_(dpooled, dpad, pad):
     return dpad
 
 
+@_checked
 def pool_add_act_fwd(c, d, act, out_p):
     N, H, W, C = c.shape
     out = empty_act(N, H // 2 + 2 * out_p, W // 2 + 2 * out_p, C, c.device)
@@ -303,6 +368,7 @@ def pool_add_act_fwd(c, d, act, out_p):
     return out
 
 
+@_checked
 def pool_add_act_bwd(dout_pad, out_pad, out_p, act):
     N, Hp, Wp, C = out_pad.shape
     Ho, Wo = Hp - 2 * out_p, Wp - 2 * out_p
@@ -314,14 +380,16 @@ def pool_add_act_bwd(dout_pad, out_pad, out_p, act):
     return dd, dc
 
 
+@_checked
 def gap_fwd(x):
     N, H, W, C = x.shape
-    out = torch.empty((N, C), dtype=torch.float32, device=x.device)
+    out = _T.empty((N, C), dtype=torch.float32, device=x.device)
     check(_lib.lib().mt_gap_fwd(_p(x), N, H * W, C, _p(out), _stream()), "gap_fwd")
     _count()
     return out
 
 
+@_checked
 def gap_bwd(dout, H, W):
     N, C = dout.shape
     dx = empty_act(N, H, W, C, dout.device)
@@ -330,38 +398,42 @@ def gap_bwd(dout, H, W):
     return dx
 
 
+@_checked
 def rgb_head_fwd(x, w, Co):
     """x [N,H,W,C] bf16 dense, w fp32 [C, Co] -> NCHW fp32 tanh image."""
     N, H, W, C = x.shape
-    y = torch.empty((N, Co, H, W), dtype=torch.float32, device=x.device)
+    y = _T.empty((N, Co, H, W), dtype=torch.float32, device=x.device)
     check(_lib.lib().mt_rgb_head_fwd(_p(x), _p(w), N, H * W, C, Co, _p(y), _stream()), "rgb_head_fwd")
     _count()
     return y
 
 
+@_checked
 def rgb_head_bwd(dy, y, x, w, Co):
     N, H, W, C = x.shape
-    dx = torch.empty_like(x)
-    dw = torch.empty((C, Co), dtype=torch.float32, device=x.device)
+    dx = _T.empty_like(x)
+    dw = _T.empty((C, Co), dtype=torch.float32, device=x.device)
     check(_lib.lib().mt_rgb_head_bwd(_p(dy.contiguous()), _p(y), _p(x), _p(w), N, H * W, C, Co, _p(dx),
                                      _p(dw), _stream()), "rgb_head_bwd")
     _count()
     return dx, dw
 
 
+@_checked
 def sumsq_interior(x_pad, pad):
     N, Hp, Wp, C = x_pad.shape
-    out = torch.empty((), dtype=torch.float32, device=x_pad.device)
+    out = _T.empty((), dtype=torch.float32, device=x_pad.device)
     check(_lib.lib().mt_sumsq_interior(_p(x_pad), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _p(out),
                                        _stream()), "sumsq_interior")
     _count()
     return out
 
 
+@_checked
 def scale_interior(x_pad, scale, pad):
     """scale: fp32 0-dim device tensor."""
     N, Hp, Wp, C = x_pad.shape
-    dx = torch.empty_like(x_pad)
+    dx = _T.empty_like(x_pad)
     check(_lib.lib().mt_scale_interior(_p(x_pad), _p(scale), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _p(dx),
                                        _stream()), "scale_interior")
     _count()

@@ -53,7 +53,9 @@ def patch_rng(models, draws):
 
 
 def nets_case(name, dim, size, N, nd=4, latent=8, seed=1, sub=1):
-    """Forward of each AdaINModel network + gradients of a fixed linear functional."""
+    """Each AdaINModel network on its own: forward outputs and the gradients of a fixed linear
+    functional of them (independent per net, so that a check of one net does not inherit the
+    rounding noise of the others)."""
     from models.core import networks
     torch.manual_seed(0)
     draws = synth.Draws(seed)
@@ -66,38 +68,50 @@ def nets_case(name, dim, size, N, nd=4, latent=8, seed=1, sub=1):
             'shapes': {}}
     for n, net in (('content_encoder', Ec), ('style_encoder', Es), ('decoder', G), ('discriminator', D)):
         meta['shapes'][n] = load_synth(net, seed, n + '.')
-    img = synth.synth_images(N, size, seed).requires_grad_(True)
-    c = synth.synth_onehot(N, nd, seed)
-    out = {}
-    z_c = Ec(img)                                    # training mode: draw 0 = noise
-    z, mu, logvar = Es(img, c)                       # draw 1 = eps
-    fake = G(z_c, z, c)
-    d_out, d_cls = D(fake)
-    proj = synth.synth_tensor('proj', fake.shape, seed)
-    loss = (fake * proj).sum() + d_out.sum() + (d_cls * c).sum() + mu.sum() + 0.5 * logvar.sum()
-    loss.backward()
     s = sub
-    out['z_c'] = z_c.detach()[:, :, ::s, ::s]
+    out = {}
+    c = synth.synth_onehot(N, nd, seed)
+    # content encoder (training mode: draw 0 = noise)
+    img = synth.synth_images(N, size, seed).requires_grad_(True)
+    z_c = Ec(img)
+    (z_c * synth.synth_tensor('proj_zc', z_c.shape, seed)).sum().backward()
+    out['z_c'], out['Ec.dimg'] = z_c.detach()[:, :, ::s, ::s], img.grad[:, :, ::s, ::s]
+    # style encoder (draw 1 = eps)
+    img2 = synth.synth_images(N, size, seed, 'img2').requires_grad_(True)
+    z, mu, logvar = Es(img2, c)
+    (z.sum() + 2 * mu.sum() + 0.5 * logvar.sum()).backward()
     out['z'], out['mu'], out['logvar'] = z.detach(), mu.detach(), logvar.detach()
+    out['Es.dimg'] = img2.grad[:, :, ::s, ::s]
+    # decoder on a synthetic unit-variance content code
+    zc_in = synth.synth_tensor('zc_in', (N, dim * 4, size // 4, size // 4), seed) * (dim * 4 * (size // 4) ** 2) ** 0.5
+    zc_in = zc_in.to(torch.bfloat16).float().requires_grad_(True)
+    zs_in = synth.synth_tensor('zs_in', (N, latent), seed) * latent ** 0.5
+    zs_in.requires_grad_(True)
+    fake = G(zc_in, zs_in, c)
+    (fake * synth.synth_tensor('proj', fake.shape, seed)).sum().backward()
     out['fake'] = fake.detach()[:, :, ::s, ::s]
-    out['d_out'], out['d_cls'] = d_out.detach(), d_cls.detach()
-    out['loss'] = loss.detach()
-    out['dimg'] = img.grad[:, :, ::s, ::s]
-    # a few parameter gradients (first/last layers of each net)
-    for n, net, keys in (('content_encoder', Ec, ['model.0.block.1.weight', 'model.6.model.1.block.1.weight']),
-                         ('style_encoder', Es, ['model.0.block.1.weight', 'model.3.shortcut.1.weight', 'fc.weight']),
+    out['G.dzc'], out['G.dzs'] = zc_in.grad[:, :, ::max(1, s // 4), ::max(1, s // 4)], zs_in.grad
+    # discriminator
+    img3 = synth.synth_images(N, size, seed, 'img3').requires_grad_(True)
+    d_out, d_cls = D(img3)
+    (d_out * synth.synth_tensor('proj_d', d_out.shape, seed)).sum().add((d_cls * c).sum()).backward()
+    out['d_out'], out['d_cls'], out['D.dimg'] = d_out.detach(), d_cls.detach(), img3.grad[:, :, ::s, ::s]
+    for n, net, keys in (('content_encoder', Ec, ['model.0.block.1.weight', 'model.2.block.1.weight',
+                                                 'model.6.model.1.block.1.weight']),
+                         ('style_encoder', Es, ['model.0.block.1.weight', 'model.2.conv.1.block.1.weight',
+                                                'model.3.shortcut.1.weight', 'fc.weight']),
                          ('decoder', G, ['dec1.0.conv1.block.1.weight', 'dec1.3.norm.fc.weight',
                                          'dec2.0.block.0.weight', 'dec2.1.block.1.weight', 'dec2.2.block.0.weight',
                                          'linear.0.weight']),
-                         ('discriminator', D, ['model.0.block.1.weight', 'model.5.block.1.bias', 'conv1.weight',
-                                               'conv2.weight'])):
+                         ('discriminator', D, ['model.0.block.1.weight', 'model.3.block.1.weight',
+                                               'model.5.block.1.bias', 'conv1.weight', 'conv2.weight'])):
         sd = dict(net.named_parameters())
         for k in keys:
             g = sd[k].grad
             out[f'grad.{n}.{k}'] = g if g.numel() <= 20000 else g.flatten()[:: max(1, g.numel() // 20000)]
     np.savez_compressed(os.path.join(OUT, name + '.npz'), meta=json.dumps(meta),
                         **{k: v.numpy().astype(np.float32) for k, v in out.items()})
-    print(name, 'loss', float(loss), 'draws', draws.log)
+    print(name, 'draws', draws.log, {k: float(v.abs().max()) for k, v in out.items() if not k.startswith('grad')})
 
 
 def step_case(name, dim, size, B, iters=2, nd=4, seed=2):

@@ -20,6 +20,8 @@ def synth_tensor(name, shape, seed=0):
         fan_in = 1
         for s in shape[1:]:
             fan_in *= s
+        if len(shape) == 4 and '.dec2.' in name:     # ConvTranspose2d weights are [Cin, Cout, k, k]
+            fan_in = shape[0] * shape[2] * shape[3] // (4 if shape[2] == 3 else 1)
         # variance-preserving scale keeps activations O(1) through the deep stacks, which makes
         # the parity check sensitive; (the reference's N(0,0.02) init gives tiny, flat signals)
         return torch.randn(shape, generator=g) * (1.0 / fan_in) ** 0.5

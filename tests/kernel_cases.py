@@ -34,10 +34,11 @@ def from_nhwc(x, C):
     return x[..., :C].permute(0, 3, 1, 2).float()
 
 
-def conv_case(N, Cin, Cout, H, W, k, stride, rpad, zpad=0, bias=True, act=None, out_pad=0, seed=0):
+def conv_case(N, Cin, Cout, H, W, k, stride, rpad, zpad=0, bias=True, act=None, out_pad=0, seed=0,
+              stem=False):
     """Conv2d forward + dgrad + wgrad.  rpad: reflection padding materialised in the input."""
     torch.manual_seed(seed)
-    g = ConvGeom(Cin, Cout, k, k, stride, zpad)
+    g = ConvGeom(Cin, Cout, k, k, stride, zpad, False, stem)
     x = bf(torch.randn(N, Cin, H, W, device=DEV))
     xp = F.pad(x, (rpad,) * 4, mode="reflect") if rpad else x
     w = bf(torch.randn(Cout, Cin, k, k, device=DEV) * 0.05)
@@ -188,9 +189,10 @@ CASES = {
     "conv3x3_256": lambda: conv_case(2, 256, 256, 64, 64, 3, 1, 1, bias=False),
     "conv3x3_s2": lambda: conv_case(2, 64, 128, 64, 64, 3, 2, 1),
     "conv3x3_s2_act_pad": lambda: conv_case(2, 64, 128, 32, 32, 3, 2, 1, act="lrelu", out_pad=1),
-    "stem7x7": lambda: conv_case(2, 3, 64, 64, 64, 7, 1, 3),
-    "stem4x4_s2": lambda: conv_case(2, 7, 64, 64, 64, 4, 2, 1),
-    "stem3x3_s2": lambda: conv_case(2, 3, 64, 64, 64, 3, 2, 1),
+    "stem7x7": lambda: conv_case(2, 3, 64, 64, 64, 7, 1, 3, stem=True),
+    "stem4x4_s2": lambda: conv_case(2, 7, 64, 64, 64, 4, 2, 1, stem=True),
+    "stem3x3_s2": lambda: conv_case(2, 3, 64, 64, 64, 3, 2, 1, stem=True),
+    "c3_generic": lambda: conv_case(2, 3, 64, 32, 32, 3, 2, 1),
     "conv1x1": lambda: conv_case(2, 128, 256, 16, 16, 1, 1, 0),
     "dis_tail": lambda: conv_case(3, 1024, 1024, 8, 8, 3, 2, 1),
     "odd_channels": lambda: conv_case(1, 32, 48, 20, 12, 3, 1, 1),
@@ -204,6 +206,10 @@ CASES = {
     "adain_res": lambda: norm_case("adain", 2, 64, 16, 16, None, residual=True),
     "ln_relu": lambda: norm_case("layer", 2, 128, 32, 32, "relu"),
     "in_lrelu_c1024": lambda: norm_case("instance", 2, 1024, 8, 8, "lrelu"),
+    "small_1x1_c32": lambda: conv_case(2, 32, 32, 8, 8, 1, 1, 0),
+    "small_1x1_c64": lambda: conv_case(2, 64, 64, 8, 8, 1, 1, 0),
+    "small_3x3_c32": lambda: conv_case(2, 32, 32, 8, 8, 3, 1, 1),
+    "small_1x1_c32_n1": lambda: conv_case(1, 32, 32, 8, 16, 1, 1, 0),
     "pad1": lambda: pad_case(2, 64, 16, 24, 1),
     "pad3": lambda: pad_case(2, 8, 32, 32, 3),
 }
