@@ -1,0 +1,273 @@
+"""Benchmark of the hot path: AdaINModel.optimize_parameters (full GAN+VAE training iteration,
+reference src/models/adain_model.py:421-430) on synthetic 256x256 images.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (oracle port)
+
+Prints ONE JSON line (rank 0).  `value` = images/s of the whole job with the batch already resident
+in HBM; `e2e` = the same through the public API with pinned HOST buffers (H2D of the batch and D2H
+of the 13 loss scalars inside the timed region); `roofline` = the implicit-GEMM conv kernels'
+algorithmic FLOP/s against the measured bf16 peak; `cpu_baseline` = the fp32 CPU port of the same
+iteration on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "train_images_per_sec"
+UNIT = "images/s"
+SIZE, ND, LATENT = 256, 4, 8
+B_PER_GPU = 8                      # BASELINE.json configs[2]: batch 8 -> 16 images per iteration
+GFLOP_PER_B = 2414.0               # algorithmic GFLOP per unit batch at 256^2
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"bf16_tflops": d.get("bf16_tflops_sustained", d.get("bf16_tflops")), "hbm_gbs": d.get("hbm_gbs"),
+                "source": "MEASURED_PEAKS.json (sustained bf16)"}
+    return {"bf16_tflops": 1590.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def make_args(B, mode="train"):
+    from oracle import ref_import      # default_args only: a plain Namespace, no reference import
+    return ref_import.default_args(dim=64, crop_size=SIZE, batch_size=B, num_domains=ND,
+                                   latent_dim=LATENT, mode=mode, init_type="normal")
+
+
+def synth_batch(B, seed, pinned):
+    g = torch.Generator().manual_seed(seed)
+    x1 = torch.rand((B, 3, SIZE, SIZE), generator=g) * 2 - 1
+    x2 = torch.rand((B, 3, SIZE, SIZE), generator=g) * 2 - 1
+    d1 = torch.randint(0, ND, (B,), generator=g)
+    d2 = (d1 + 1 + torch.randint(0, ND - 1, (B,), generator=g)) % ND      # a different domain
+    b = {"x1": x1, "x2": x2, "y1": torch.eye(ND)[d1], "y2": torch.eye(ND)[d2]}
+    if pinned:
+        b = {k: v.pin_memory() for k, v in b.items()}
+    return b
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_iteration_port(steps, warmup, threads):
+    """The reference's CPU path for this metric: oracle/step.py (fp32 restatement, pinned against
+    the reference in tests/test_oracle_golden.py) — one B=1 iteration (2 images) per step."""
+    from oracle import step as ostep, synth
+    torch.set_num_threads(threads)
+    B = 1
+    import numpy as np
+    meta = json.loads(str(np.load(os.path.join(ROOT, "tests", "golden", "nets_dim64_256.npz"))["meta"]))
+    sh = meta["shapes"]                     # state_dict shapes of the dim=64 / 256x256 architecture
+    sh = {"content_encoder": sh["content_encoder"], "style_encoder": sh["style_encoder"],
+          "decoder": sh["decoder"], "discriminator1": sh["discriminator"], "discriminator2": sh["discriminator"]}
+    params = {n: synth.synth_params(s_, 0, n + ".") for n, s_ in sh.items()}
+    st = ostep.AdaINStep(params, B)
+    b = synth_batch(B, 0, False)
+    img, c = torch.cat((b["x1"], b["x2"])), torch.cat((b["y1"], b["y2"]))
+    draws = synth.Draws(0)
+    ts = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        st.optimize_parameters(img, c, draws)
+        ts.append(time.perf_counter() - t0)
+    ts = ts[warmup:]
+    sec = sum(ts) / len(ts)
+    return 2 * B / sec, sec
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count()
+    steps, warmup = max(1, min(a.steps, 3)), max(0, min(a.warmup, 1))
+    ips, sec = cpu_iteration_port(steps, warmup, threads)
+    line = {"impl": "reference", "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": 0,
+            "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "AdaINModel.optimize_parameters, 256x256, 4 domains (CPU sample: batch 1 = 2 images/iteration)"},
+            "cpu_baseline": {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"{steps} iteration(s) at batch 1 (2 images), 256x256, fp32 torch CPU"},
+            "e2e": {"value": ips, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def conv_roofline(model, batch, pk):
+    """One instrumented iteration: CUDA events around every implicit-GEMM launch on the launching
+    stream; aggregate algorithmic FLOPs / device time per kernel class."""
+    from masterthesis_b200 import ops
+    ops.PROFILE = []
+    model.set_inputs(batch)
+    model.optimize_parameters(0)
+    torch.cuda.synchronize()
+    recs, ops.PROFILE = ops.PROFILE, None
+    by_kind, by_label = {}, {}
+    for kind, label, flops, e0, e1 in recs:
+        ms = e0.elapsed_time(e1)
+        k = by_kind.setdefault(kind, [0.0, 0.0, 0])
+        k[0] += flops; k[1] += ms; k[2] += 1
+        l = by_label.setdefault((kind, label), [0.0, 0.0, 0])
+        l[0] += flops; l[1] += ms; l[2] += 1
+    tot_f = sum(v[0] for v in by_kind.values())
+    tot_ms = sum(v[1] for v in by_kind.values())
+    peak = pk["bf16_tflops"]
+    top = sorted(by_label.items(), key=lambda kv: -kv[1][1])[:8]
+    roof = {"bound": "tensor", "kernel": "igemm_conv_kernel + igemm_wgrad_kernel (all conv launches of one iteration)",
+            "achieved": tot_f / (tot_ms * 1e-3) / 1e12 if tot_ms else None, "peak": peak, "unit": "TFLOP/s",
+            "frac": (tot_f / (tot_ms * 1e-3) / 1e12 / peak) if tot_ms else None, "traffic": None,
+            "peak_source": pk["source"], "launches": sum(v[2] for v in by_kind.values()),
+            "conv_ms_per_iter": tot_ms,
+            "by_kind": {k: {"tflops": v[0] / (v[1] * 1e-3) / 1e12, "ms": v[1], "launches": v[2]} for k, v in by_kind.items()},
+            "top_classes": [{"kind": k[0], "shape": k[1], "tflops": v[0] / (v[1] * 1e-3) / 1e12, "ms": v[1], "launches": v[2]}
+                            for k, v in top]}
+    return roof
+
+
+def run_ours(a):
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the CUDA path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    from masterthesis_b200 import models, ops
+    from masterthesis_b200.parallel import DataParallelGroup
+    dp = DataParallelGroup.from_env()
+    world = 1 if dp is None else dp.world
+    rank = 0 if dp is None else dp.rank
+    if dp is None:
+        torch.cuda.set_device(0)
+    dev_index = torch.cuda.current_device()
+    B = B_PER_GPU
+    torch.manual_seed(1234)
+    model = models.AdaINModel(make_args(B))
+    model.initialize()
+    model.dp = dp
+    if dp is not None:
+        dp.broadcast_parameters([model.model[n] for n in model.model])
+    host = synth_batch(B, 100 + rank, pinned=True)
+    resident = {k: v.cuda() for k, v in host.items()}
+
+    def sync():
+        if dp is not None:
+            dp.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput
+    model.set_inputs(resident)
+    for _ in range(a.warmup):
+        model.optimize_parameters(0)
+    sync()
+    clocks = ClockSampler(dev_index)
+    clocks.start()
+    l0 = ops.launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        model.optimize_parameters(i)
+    e1.record()
+    sync()
+    ms = e0.elapsed_time(e1)
+    launches = ops.launches() - l0
+    clk = clocks.stop()
+    if dp is not None:
+        ms = dp.max_over_ranks(ms)
+    ms_per_step = ms / a.steps
+    value = world * 2 * B / (ms_per_step * 1e-3)
+
+    # ---- end to end through the public API: pinned host batch -> set_inputs (H2D) -> iteration -> losses (D2H)
+    for _ in range(min(2, a.warmup)):
+        model.set_inputs(host); model.optimize_parameters(0)
+    sync()
+    e0.record()
+    for i in range(a.steps):
+        model.set_inputs(host)
+        model.optimize_parameters(i)
+        _ = dict(model.loss)
+    e1.record()
+    sync()
+    ms2 = e0.elapsed_time(e1)
+    if dp is not None:
+        ms2 = dp.max_over_ranks(ms2)
+    e2e = world * 2 * B / (ms2 / a.steps * 1e-3)
+    h2d = sum(v.numel() * v.element_size() for v in host.values())
+    d2h = 13 * 4
+
+    if rank != 0:
+        return
+    pk = peaks()
+    roof = conv_roofline(model, resident, pk)
+    try:
+        steps_cpu = 1
+        cpu_ips, cpu_sec = cpu_iteration_port(steps_cpu, 0, os.cpu_count())
+        cpu = {"value": cpu_ips, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+               "sample": f"{steps_cpu} iteration at batch 1 (2 images), 256x256, fp32 torch CPU, {cpu_sec:.1f} s"}
+    except Exception as ex:  # the GPU numbers must still be printed
+        cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"AdaINModel.optimize_parameters (full GAN+VAE iteration, default flags), "
+                                   f"batch {B} per GPU = {2 * B} images/iteration/GPU, 256x256, 4 domains",
+                       "iters_per_sec": world and 1e3 / ms_per_step,
+                       "l2_policy": "per-iteration working set (GBs of activations) exceeds the 126 MB L2",
+                       "algorithmic_tflop_per_iter_per_gpu": GFLOP_PER_B * B / 1e3,
+                       "model_tflops_per_gpu": GFLOP_PER_B * B / 1e3 / (ms_per_step * 1e-3)},
+            "clocks": clk, "gpu_launches": launches,
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "roofline": roof, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()

@@ -84,6 +84,37 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+# Optional per-launch timing of the implicit-GEMM kernels (bench.py's roofline leg): when a list is
+# installed here, every conv launch is bracketed by CUDA events on the launching stream and
+# (kind, label, algorithmic_flops, start_event, end_event) is appended.
+PROFILE = None
+
+
+class _timed:
+    def __init__(self, kind, g, N, Hin, Win):
+        self.on = PROFILE is not None
+        if self.on:
+            Ho, Wo = g.out_hw(Hin, Win)
+            px = N * (Hin * Win if g.transposed else Ho * Wo)
+            self.flops = 2.0 * px * g.Cin * g.Cout * g.kh * g.kw     # logical channels
+            self.kind = kind
+            self.label = (f"{'convT' if g.transposed else 'conv'}{g.kh}x{g.kw}s{g.stride}"
+                          f"_{g.Cin}->{g.Cout}@{Ho}x{Wo}")
+
+    def __enter__(self):
+        if self.on:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *a):
+        if self.on:
+            self.e1.record()
+            PROFILE.append((self.kind, self.label, self.flops, self.e0, self.e1))
+        return False
+
+
 def _p(t):
     return None if t is None else t.data_ptr()
 
@@ -174,7 +205,8 @@ def conv_fwd(x, wf, bias, g: ConvGeom, act=None, out_pad=0, out=None):
     if out is None:
         out = empty_act(N, d.out_H, d.out_W, g.Cout_s, x.device)
     fn = _lib.lib().mt_conv_transpose2d_fwd if g.transposed else _lib.lib().mt_conv2d_fwd
-    check(fn(ctypes.byref(d), _p(x), _p(wf), _p(bias), _p(out), _stream()), "conv_fwd")
+    with _timed("fwd", g, N, Hin, Win):
+        check(fn(ctypes.byref(d), _p(x), _p(wf), _p(bias), _p(out), _stream()), "conv_fwd")
     _count(4 if g.transposed else 1)
     return out
 
@@ -189,7 +221,8 @@ def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
     assert (d.Hout, d.Wout) == tuple(dy.shape[1:3]), (d.Hout, d.Wout, dy.shape)
     dx = empty_act(N, Hin, Win, g.Cin_s, dy.device)
     fn = _lib.lib().mt_conv_transpose2d_dgrad if g.transposed else _lib.lib().mt_conv2d_dgrad
-    check(fn(ctypes.byref(d), _p(dy), _p(wb), _p(dx), _stream()), "conv_dgrad")
+    with _timed("dgrad", g, N, Hin, Win):
+        check(fn(ctypes.byref(d), _p(dy), _p(wb), _p(dx), _stream()), "conv_dgrad")
     _count(4 if (g.stride == 2 and not g.transposed) else 1)
     return dx
 
@@ -209,7 +242,8 @@ def conv_wgrad(x, dy, g: ConvGeom):
         n = g.kh * g.kw * g.Cout * g.Cin_s
     packed = torch.zeros(n, dtype=torch.float32, device=x.device)
     fn = L.mt_conv_transpose2d_wgrad if g.transposed else L.mt_conv2d_wgrad
-    check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), _stream()), "conv_wgrad")
+    with _timed("wgrad", g, N, Hin, Win):
+        check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), _stream()), "conv_wgrad")
     shape = (g.Cin, g.Cout, g.kh, g.kw) if g.transposed else (g.Cout, g.Cin, g.kh, g.kw)
     dw = _T.empty(shape, dtype=torch.float32, device=x.device)
     check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
