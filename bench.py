@@ -153,6 +153,10 @@ def conv_roofline(model, batch, pk):
     tot_ms = sum(v[1] for v in by_kind.values())
     peak = pk["bf16_tflops"]
     top = sorted(by_label.items(), key=lambda kv: -kv[1][1])[:8]
+    if os.environ.get('MT_BENCH_DUMP'):
+        with open(os.environ['MT_BENCH_DUMP'], 'w') as f:
+            for k, v in sorted(by_label.items(), key=lambda kv: -kv[1][1]):
+                f.write(f"{k[0]:6s} {k[1]:40s} launches {v[2]:3d}  ms {v[1]:8.3f}  TFLOP/s {v[0] / (v[1] * 1e-3) / 1e12:8.1f}\n")
     roof = {"bound": "tensor", "kernel": "igemm_conv_kernel + igemm_wgrad_kernel (all conv launches of one iteration)",
             "achieved": tot_f / (tot_ms * 1e-3) / 1e12 if tot_ms else None, "peak": peak, "unit": "TFLOP/s",
             "frac": (tot_f / (tot_ms * 1e-3) / 1e12 / peak) if tot_ms else None, "traffic": None,

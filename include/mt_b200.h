@@ -147,6 +147,9 @@ int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W
 int mt_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1,
                  float beta2, float eps, float wd, int step, float gscale, void* stream);
 
+/* debug: clock64 stamps of CTA 0 of the last conv launch when MT_IGEMM_DBG&32 (64 x int64, host) */
+int mt_debug_timestamps(void* out_host);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,23 +57,36 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   IgemmParams p;
   memset(&p, 0, sizeof(p));
   const int mul = c.window ? 1 : c.a_mul;
-  pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul, &p.TW, &p.TH, &p.TN);
+  p.BN = pick_bn(c.Bn);
+  p.n_tiles = cdiv(c.Bn, p.BN);
+  // Two 128-row accumulators per CTA share one B tile (-33 % L2->SM bytes per FLOP at BN=256):
+  // used whenever the 256-pixel tiling still yields enough CTAs to occupy the machine.
+  p.mt = 1;
+  if (2 * p.BN <= 512) {
+    int tw, th, tn;
+    pick_tile(256, c.Wt, c.Ht, c.Nt, c.a_mul, &tw, &th, &tn);
+    const long long ctas = (long long)cdiv(c.Wt, tw) * cdiv(c.Ht, th) * cdiv(c.Nt, tn) * p.n_tiles;
+    long long vol1, vol2;
+    { int a1, b1, c1; pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul, &a1, &b1, &c1);
+      vol1 = (long long)round_up(c.Wt, a1) * round_up(c.Ht, b1) * round_up(c.Nt, c1); }
+    vol2 = (long long)round_up(c.Wt, tw) * round_up(c.Ht, th) * round_up(c.Nt, tn);
+    if (ctas >= 96 && vol2 <= vol1 + vol1 / 8) p.mt = 2;
+  }
+  pick_tile(128 * p.mt, c.Wt, c.Ht, c.Nt, c.a_mul, &p.TW, &p.TH, &p.TN);
   p.tiles_w = cdiv(c.Wt, p.TW); p.tiles_h = cdiv(c.Ht, p.TH); p.tiles_n = cdiv(c.Nt, p.TN);
   p.Wt = c.Wt; p.Ht = c.Ht; p.Nt = c.Nt;
   p.kh = c.kh; p.kw = c.kw;
   p.mul_h = c.a_mul; p.mul_w = mul;
   p.off_h = c.off_h; p.off_w = c.off_w; p.step_h = c.step_h; p.step_w = c.step_w;
   p.w_base = c.w_base; p.w_step_r = c.w_step_r; p.w_step_s = c.w_step_s;
-  p.BN = pick_bn(c.Bn);
-  p.n_tiles = cdiv(c.Bn, p.BN);
   p.k_chunks = c.window ? 1 : cdiv(c.Ac, 64);
   p.n_store = c.n_store; p.n_bias = c.bias ? c.n_bias : 0;
-  const int stage_bytes = 16384 + p.BN * 128;
+  const int stage_bytes = 16384 * p.mt + p.BN * 128;
   p.stages = (200 * 1024) / stage_bytes;
   if (p.stages > 8) p.stages = 8;
   const int iters = p.kh * p.kw * p.k_chunks;
   if (p.stages > iters) p.stages = iters < 2 ? 2 : iters;
-  p.tmem_cols = pow2_cols(p.BN);
+  p.tmem_cols = pow2_cols(p.BN * p.mt);
   p.out_n_stride = c.out_n_stride; p.out_h_stride = c.out_h_stride;
   p.out_w_stride = c.out_w_stride; p.out_off = c.out_off;
   p.act = c.act; p.slope = c.slope; p.bias = c.bias;

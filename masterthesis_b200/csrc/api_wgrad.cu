@@ -30,8 +30,9 @@ static int run_wgrad_like(const WgradLike& c, cudaStream_t stream) {
   p.n_tiles = cdiv(n_logical, p.BN);
   const int total_kt = p.tiles_w * p.tiles_h * p.tiles_n;
   const int items = p.kh * p.kw * p.m_tiles * p.n_tiles;
-  int splits = cdiv(4 * 148, items);          // aim at ~4 CTAs per SM worth of work items
-  const int max_splits = cdiv(total_kt, 4);   // at least 4 pixel tiles per split
+  // one wave of CTAs: every split pays a full fp32 red.add epilogue, so prefer long main loops
+  int splits = 148 / items;
+  const int max_splits = cdiv(total_kt, 8);   // at least 8 pixel tiles per split
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
   const int per = cdiv(total_kt, splits);

@@ -126,44 +126,48 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, 
 
 // ---------------------------------------------------------------- forward apply
 // out_pad[n, h+po, w+po, :] = act(x*scale + shift) (+ res_pad[n, h+pr, w+pr, :]) (+ noise)
+// grid = (pixel chunks, N); a thread owns ONE 8-channel vector (its scale/shift live in registers)
+// and walks pixels, so a warp reads/writes 512 contiguous bytes per pixel row.
 __global__ void __launch_bounds__(256)
-affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ss, int N,
-                      int H, int W, int C, int act, float slope,
-                      const __nv_bfloat16* __restrict__ res, int pr,
+affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ss, int H, int W,
+                      int C, int act, float slope, const __nv_bfloat16* __restrict__ res, int pr,
                       const float* __restrict__ noise, __nv_bfloat16* __restrict__ out, int po) {
-  const int V = C / 8;
-  const long long total = (long long)N * H * W * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
-    const int w = (int)(t % W); t /= W;
-    const int h = (int)(t % H); const int n = (int)(t / H);
-    float f[8];
-    load8(x + i * 8, f);
-    if (ss) {
-      const float4* s4 = reinterpret_cast<const float4*>(ss + ((long long)n * C + v * 8) * 2);
+  const int V = C / 8, lanes = blockDim.x / V;
+  const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  if (pl >= lanes) return;
+  const int n = blockIdx.y, HW = H * W;
+  float sc[8], sh[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float4 q = __ldg(s4 + j);
-        f[2 * j] = f[2 * j] * q.x + q.y;
-        f[2 * j + 1] = f[2 * j + 1] * q.z + q.w;
-      }
+  for (int j = 0; j < 8; ++j) { sc[j] = 1.f; sh[j] = 0.f; }
+  if (ss) {
+    const float4* s4 = reinterpret_cast<const float4*>(ss + ((long long)n * C + v * 8) * 2);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float4 q = __ldg(s4 + j);
+      sc[2 * j] = q.x; sh[2 * j] = q.y; sc[2 * j + 1] = q.z; sh[2 * j + 1] = q.w;
     }
+  }
+  const int Hr = H + 2 * pr, Wr = W + 2 * pr, Ho = H + 2 * po, Wo = W + 2 * po;
+  for (int p = blockIdx.x * lanes + pl; p < HW; p += gridDim.x * lanes) {
+    const int h = p / W, w = p - h * W;
+    const long long i = ((long long)n * HW + p) * C + v * 8;
+    float f[8];
+    load8(x + i, f);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = act_fwd(f[j], act, slope);
+    for (int j = 0; j < 8; ++j) f[j] = act_fwd(f[j] * sc[j] + sh[j], act, slope);
     if (res) {
       float r[8];
-      load8(res + (((long long)n * (H + 2 * pr) + h + pr) * (W + 2 * pr) + w + pr) * C + v * 8, r);
+      load8(res + (((long long)n * Hr + h + pr) * Wr + w + pr) * C + v * 8, r);
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] += r[j];
     }
     if (noise) {
       float r[8];
-      load8f(noise + i * 8, r);
+      load8f(noise + i, r);
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] += r[j];
     }
-    store8(out + (((long long)n * (H + 2 * po) + h + po) * (W + 2 * po) + w + po) * C + v * 8, f);
+    store8(out + (((long long)n * Ho + h + po) * Wo + w + po) * C + v * 8, f);
   }
 }
 
@@ -230,29 +234,34 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
   }
 }
 
-// dx = c0*(g*act'(y)) + c1*x + c2
+// dx = c0*(g*act'(y)) + c1*x + c2      grid = (pixel chunks, N), coefficients in registers
 __global__ void __launch_bounds__(256)
 norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
-                      const float* __restrict__ ss, const float* __restrict__ coef, int N, int HW,
-                      int C, int act, float slope, __nv_bfloat16* __restrict__ dx) {
-  const int V = C / 8;
-  const long long total = (long long)N * HW * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V);
-    const int n = (int)(i / ((long long)HW * V));
+                      const float* __restrict__ ss, const float* __restrict__ coef, int HW, int C,
+                      int act, float slope, __nv_bfloat16* __restrict__ dx) {
+  const int V = C / 8, lanes = blockDim.x / V;
+  const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  if (pl >= lanes) return;
+  const int n = blockIdx.y;
+  float sc[8], sh[8], c0[8], c1[8], c2[8];
+  const float* s = ss + ((long long)n * C + v * 8) * 2;
+  const float* cf = coef + ((long long)n * C + v * 8) * 3;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = __ldg(s + 2 * j); sh[j] = __ldg(s + 2 * j + 1);
+    c0[j] = __ldg(cf + 3 * j); c1[j] = __ldg(cf + 3 * j + 1); c2[j] = __ldg(cf + 3 * j + 2);
+  }
+  for (int p = blockIdx.x * lanes + pl; p < HW; p += gridDim.x * lanes) {
+    const long long i = ((long long)n * HW + p) * C + v * 8;
     float xv[8], gv[8], o[8];
-    load8(x + i * 8, xv);
-    load8(g + i * 8, gv);
-    const float* s = ss + ((long long)n * C + v * 8) * 2;
-    const float* cf = coef + ((long long)n * C + v * 8) * 3;
+    load8(x + i, xv);
+    load8(g + i, gv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float y = xv[j] * __ldg(s + 2 * j) + __ldg(s + 2 * j + 1);
-      const float gg = gv[j] * act_grad_pre(y, act, slope);
-      o[j] = __ldg(cf + 3 * j) * gg + __ldg(cf + 3 * j + 1) * xv[j] + __ldg(cf + 3 * j + 2);
+      const float y = xv[j] * sc[j] + sh[j];
+      o[j] = c0[j] * (gv[j] * act_grad_pre(y, act, slope)) + c1[j] * xv[j] + c2[j];
     }
-    store8(dx + i * 8, o);
+    store8(dx + i, o);
   }
 }
 
@@ -292,6 +301,16 @@ act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16*
 using namespace mt;
 #define ST(s) ((cudaStream_t)(s))
 
+// grid (pixel chunks, N) for the per-plane kernels: ~8 CTAs per SM, >= 4 pixels per pixel lane
+static dim3 plane_grid(int N, int HW, int C) {
+  const int lanes = 256 / (C / 8);
+  int chunks = (8 * NUM_SMS + N - 1) / N;
+  const int max_chunks = (HW + lanes * 4 - 1) / (lanes * 4);
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  return dim3((unsigned)chunks, (unsigned)N);
+}
+
 static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int HW,
                          int C, int act, float slope, float* out, cudaStream_t st) {
   if (C % 8 || C / 8 > 256) return -1003;
@@ -326,10 +345,9 @@ extern "C" int mt_norm_finalize(const float* stats, int mode, int N, int C, int 
 extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,
                                  int act, float slope, const void* res_pad, int res_p,
                                  const float* noise, void* out_pad, int out_p, void* stream) {
-  if (C % 8) return -1003;
-  const long long total = (long long)N * H * W * (C / 8);
-  affine_act_fwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
-      (const __nv_bfloat16*)x, ss, N, H, W, C, act, slope, (const __nv_bfloat16*)res_pad, res_p,
+  if (C % 8 || C / 8 > 256) return -1003;
+  affine_act_fwd_kernel<<<plane_grid(N, H * W, C), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)x, ss, H, W, C, act, slope, (const __nv_bfloat16*)res_pad, res_p,
       noise, (__nv_bfloat16*)out_pad, out_p);
   return cuda_rc();
 }
@@ -348,10 +366,9 @@ extern "C" int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode
 extern "C" int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float* coef,
                                  int N, int HW, int C, int act, float slope, void* dx,
                                  void* stream) {
-  if (C % 8) return -1003;
-  const long long total = (long long)N * HW * (C / 8);
-  norm_bwd_apply_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
-      (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, N, HW, C, act, slope,
+  if (C % 8 || C / 8 > 256) return -1003;
+  norm_bwd_apply_kernel<<<plane_grid(N, HW, C), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, HW, C, act, slope,
       (__nv_bfloat16*)dx);
   return cuda_rc();
 }
