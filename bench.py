@@ -138,9 +138,11 @@ def conv_roofline(model, batch, pk):
     stream; aggregate algorithmic FLOPs / device time per kernel class."""
     from masterthesis_b200 import ops
     ops.PROFILE = []
+    graph_mode, model.use_graph = model.use_graph, False     # events between launches: eager iteration
     model.set_inputs(batch)
     model.optimize_parameters(0)
     torch.cuda.synchronize()
+    model.use_graph = graph_mode
     recs, ops.PROFILE = ops.PROFILE, None
     by_kind, by_label = {}, {}
     for kind, label, flops, e0, e1 in recs:
@@ -253,6 +255,7 @@ def run_ours(a):
                                    f"batch {B} per GPU = {2 * B} images/iteration/GPU, 256x256, 4 domains",
                        "iters_per_sec": world and 1e3 / ms_per_step,
                        "l2_policy": "per-iteration working set (GBs of activations) exceeds the 126 MB L2",
+                       "execution": "whole iteration replayed as one CUDA graph" if model._graph else "eager launches",
                        "algorithmic_tflop_per_iter_per_gpu": GFLOP_PER_B * B / 1e3,
                        "model_tflops_per_gpu": GFLOP_PER_B * B / 1e3 / (ms_per_step * 1e-3)},
             "clocks": clk, "gpu_launches": launches,

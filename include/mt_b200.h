@@ -146,6 +146,11 @@ int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W
  * g is multiplied by gscale first (data-parallel averaging). `step` is the 1-based step count. */
 int mt_adam_flat(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1,
                  float beta2, float eps, float wd, int step, float gscale, void* stream);
+/* Same step with the scalars read from DEVICE memory, so that the launch can live in a CUDA graph
+ * that is replayed with new learning rates / step counts:
+ * hyper[0..6] = {lr / (1 - beta1^step), 1 / sqrt(1 - beta2^step), beta1, beta2, eps, wd, gscale}. */
+int mt_adam_flat_dev(float* p, const float* g, float* m, float* v, long long n, const float* hyper,
+                     void* stream);
 
 /* debug: clock64 stamps of CTA 0 of the last conv launch when MT_IGEMM_DBG&32 (64 x int64, host) */
 int mt_debug_timestamps(void* out_host);

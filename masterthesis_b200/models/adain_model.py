@@ -79,13 +79,7 @@ class AdaINModel(Model):
         return torch.randn(bs, latent_dim, device=self.device)
 
     def set_inputs(self, inputs):
-        dev = self.device
-        self.img_a = inputs['x1'].to(dev, non_blocking=True).detach()
-        self.cls_a = inputs['y1'].to(dev, non_blocking=True).detach()
-        self.img_b = inputs['x2'].to(dev, non_blocking=True).detach()
-        self.cls_b = inputs['y2'].to(dev, non_blocking=True).detach()
-        self.img = torch.cat((self.img_a, self.img_b), dim=0)
-        self.c_org = torch.cat((self.cls_a, self.cls_b), dim=0)
+        self._static_inputs(inputs['x1'], inputs['y1'], inputs['x2'], inputs['y2'])
 
     def Ec(self, img):
         return self.model.content_encoder.run(img, self.rng)
@@ -250,15 +244,13 @@ class AdaINModel(Model):
 
     # ------------------------------------------------------------------ the iteration (:421-430)
     def optimize_parameters(self, global_iter):
-        self._scalars = {}
         if self.args.use_dis_content:
             raise NotImplementedError("--use_dis_content is the next row of the scope table (SURVEY.md §8f-1)")
+        self._run_iteration(self._iteration)
+
+    def _iteration(self):
         self.update_discriminator(self.img, self.c_org)
         self.update_generator(self.img, self.c_org)
-        keys = list(self._scalars)
-        vals = torch.stack([self._scalars[k].float().reshape(()) for k in keys]).tolist()   # one sync
-        for k, v in zip(keys, vals):
-            self.loss[k] = v
 
     def compute_visuals(self):
         B = self.args.batch_size

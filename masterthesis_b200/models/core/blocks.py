@@ -20,6 +20,16 @@ from .norm import AdaptiveInstanceNorm, LayerNorm
 
 
 # ------------------------------------------------------------------------- parameter holders
+_PACK_EPOCH = [0]
+
+
+def invalidate_packs():
+    """Drop every cached bf16 weight pack (Model does this before capturing an iteration in a CUDA
+    graph: a replayed iteration must re-pack every weight at its first use, because the weights were
+    stepped by the previous replay)."""
+    _PACK_EPOCH[0] += 1
+
+
 class _ConvParams(nn.Module):
     transposed = False
 
@@ -48,7 +58,7 @@ class _ConvParams(nn.Module):
     def packed(self, zpad=0, stem=False):
         """bf16 GEMM operands of the fp32 master weight, refreshed when the weight changes."""
         w = self.weight
-        key = (w._version, w.data_ptr(), zpad, stem)
+        key = (w._version, w.data_ptr(), zpad, stem, _PACK_EPOCH[0])
         if self._pack is None or self._pack[0] != key:
             self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem)))
         return self._pack[1]

@@ -47,6 +47,15 @@ class Model(ABC, nn.Module):
         self.print_loss = []
         self.rng = None          # None: device Philox; callable(shape)->cpu tensor: replayed draws
         self.dp = None           # masterthesis_b200.parallel.DataParallelGroup or None
+        # The whole training iteration (4 phases, ~2800 kernel launches) is captured once into a CUDA
+        # graph and replayed: the host then costs one launch per iteration instead of ~47 ms of
+        # enqueueing.  args.cuda_graph=False or MT_CUDA_GRAPH=0 keeps the eager path; replayed CPU
+        # draws (self.rng, parity tests) always run eagerly.
+        self.use_graph = bool(getattr(args, 'cuda_graph', True)) and os.environ.get('MT_CUDA_GRAPH', '1') != '0'
+        self.graph_warmup = 2    # eager iterations before capture (lazy init, allocator warm-up)
+        self._graph = None
+        self._eager_iters = 0
+        self._scalars = {}
 
     @abstractmethod
     def set_inputs(self, inputs):
@@ -55,6 +64,76 @@ class Model(ABC, nn.Module):
     @abstractmethod
     def optimize_parameters(self, global_iter):
         pass
+
+    # ------------------------------------------------------------------ iteration driver
+    def reset_graph(self):
+        """forget the captured iteration (call after changing loss weights, batch shape, ...)"""
+        self._graph = None
+        self._eager_iters = 0
+
+    def _static_inputs(self, x1, y1, x2, y2):
+        """Keep the stacked batch in persistent device buffers (a captured iteration reads them in
+        place; reference adain_model.py:87-94 builds `img`, `c_org` by torch.cat)."""
+        dev, B = self.device, x1.shape[0]
+        shape = (2 * B,) + tuple(x1.shape[1:])
+        if getattr(self, 'img', None) is None or tuple(self.img.shape) != shape or \
+                tuple(self.c_org.shape) != (2 * B, y1.shape[1]):
+            self.img = torch.empty(shape, dtype=torch.float32, device=dev)
+            self.c_org = torch.empty((2 * B, y1.shape[1]), dtype=torch.float32, device=dev)
+            self.reset_graph()
+        self.img[:B].copy_(x1, non_blocking=True)
+        self.img[B:].copy_(x2, non_blocking=True)
+        self.c_org[:B].copy_(y1, non_blocking=True)
+        self.c_org[B:].copy_(y2, non_blocking=True)
+        self.img_a, self.img_b = self.img[:B], self.img[B:]
+        self.cls_a, self.cls_b = self.c_org[:B], self.c_org[B:]
+
+    def _loss_vector(self):
+        keys = list(self._scalars)
+        return keys, torch.stack([self._scalars[k].float().reshape(()) for k in keys])
+
+    def _run_iteration(self, body):
+        """Run `body()` (enqueues one full training iteration and fills self._scalars with 0-dim
+        device tensors) eagerly or as a CUDA-graph replay, then read all losses with ONE host sync."""
+        from .. import ops
+        from ..optim import GraphHyper
+        from .core import blocks
+        if not self.use_graph or self.rng is not None:
+            self._scalars = {}
+            body()
+            keys, vec = self._loss_vector()
+        elif self._graph is None and self._eager_iters < self.graph_warmup:
+            self._eager_iters += 1
+            self._scalars = {}
+            body()
+            keys, vec = self._loss_vector()
+        else:
+            if self._graph is None:
+                blocks.invalidate_packs()
+                ctx = GraphHyper(self.device)
+                for opt in self.optimizer.values():
+                    opt.graph_ctx = ctx
+                graph = torch.cuda.CUDAGraph()
+                l0 = ops.launches()
+                torch.cuda.synchronize()
+                try:
+                    with torch.cuda.graph(graph):
+                        self._scalars = {}
+                        body()
+                        keys, vec = self._loss_vector()
+                finally:
+                    for opt in self.optimizer.values():
+                        opt.graph_ctx = None
+                self._graph = dict(graph=graph, ctx=ctx, keys=keys, vec=vec, launches=ops.launches() - l0)
+            else:
+                self._graph['ctx'].advance()
+                ops._count(self._graph['launches'])
+            g = self._graph
+            g['ctx'].upload()
+            g['graph'].replay()
+            keys, vec = g['keys'], g['vec']
+        for k, v in zip(keys, vec.tolist()):     # the one host sync of the iteration
+            self.loss[k] = v
 
     # ------------------------------------------------------------------ lifecycle
     def initialize(self):

@@ -5,9 +5,38 @@ re-pointed to views of the flat buffers, so zero_grad is one memset and the data
 all-reduce is one NCCL call on the gradient bucket.  state_dict() keeps torch.optim.Adam's layout
 (per-parameter step / exp_avg / exp_avg_sq) so opt_{it}.ckpt files stay interchangeable
 (reference model.py:77-82)."""
+import math
+
 import torch
 
 from . import _lib, ops
+
+
+class GraphHyper:
+    """Device-resident Adam scalars for an iteration captured in a CUDA graph: one 8-float slot per
+    FlatAdam.step() call site of the captured iteration, refreshed from the host (learning-rate
+    schedule, step counts) by one small H2D copy before every replay."""
+
+    def __init__(self, device, max_calls=32):
+        self.host = torch.zeros(max_calls, 8, dtype=torch.float32).pin_memory()
+        self.dev = torch.zeros(max_calls, 8, dtype=torch.float32, device=device)
+        self.calls = []
+
+    def slot(self, opt, values):
+        i = len(self.calls)
+        if i >= self.host.shape[0]:
+            raise RuntimeError("GraphHyper: too many optimizer steps in one captured iteration")
+        self.calls.append(opt)
+        self.host[i, :7] = torch.tensor(values, dtype=torch.float32)
+        return self.dev[i].data_ptr()
+
+    def advance(self):
+        """host bookkeeping of every captured step() for the next replay"""
+        for i, opt in enumerate(self.calls):
+            self.host[i, :7] = torch.tensor(opt._host_advance(), dtype=torch.float32)
+
+    def upload(self):
+        self.dev.copy_(self.host, non_blocking=True)
 
 
 class FlatAdam(torch.optim.Optimizer):
@@ -19,6 +48,7 @@ class FlatAdam(torch.optim.Optimizer):
         super().__init__(params, defaults)
         self._flat = None
         self.grad_scale = 1.0      # set to 1/world by the data-parallel wrapper
+        self.graph_ctx = None      # GraphHyper while an iteration is being captured
 
     # ------------------------------------------------------------------ flat buckets
     def _params(self):
@@ -90,18 +120,39 @@ class FlatAdam(torch.optim.Optimizer):
                 self._flat['g'][off:off + k].copy_(p.grad.reshape(-1))
                 p.grad = self._flat['g'][off:off + k].view(p.shape)
             off += (k + 3) // 4 * 4
-        st0 = self.state[ps[0]]
-        step = int(st0['step'].item() if torch.is_tensor(st0['step']) else st0['step']) + 1
         f = self._flat
-        _lib.check(_lib.lib().mt_adam_flat(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
-                                           f['v'].data_ptr(), f['n'], float(g0['lr']), g0['betas'][0],
-                                           g0['betas'][1], g0['eps'], g0['weight_decay'], step,
-                                           float(self.grad_scale), ops._stream()), "mt_adam_flat")
+        hyper = self._host_advance()
+        L = _lib.lib()
+        if self.graph_ctx is not None:
+            slot = self.graph_ctx.slot(self, hyper)
+            _lib.check(L.mt_adam_flat_dev(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
+                                          f['v'].data_ptr(), f['n'], slot, ops._stream()), "mt_adam_flat_dev")
+        else:
+            g0 = self.param_groups[0]
+            _lib.check(L.mt_adam_flat(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
+                                      f['v'].data_ptr(), f['n'], float(g0['lr']), g0['betas'][0],
+                                      g0['betas'][1], g0['eps'], g0['weight_decay'], self._step_count(),
+                                      float(self.grad_scale), ops._stream()), "mt_adam_flat")
         ops._count()
+        return None
+
+    def _step_count(self):
+        st0 = self.state[self._params()[0]]
+        return int(st0['step'].item() if torch.is_tensor(st0['step']) else st0['step'])
+
+    def _host_advance(self):
+        """Host half of one step: advance the step count and autograd's version counters (the kernel
+        writes through raw pointers; the packed bf16 weight caches of blocks._ConvParams.packed key on
+        the version).  Returns the 7 scalars of mt_adam_flat_dev's `hyper` block."""
+        ps = self._params()
+        g0 = self.param_groups[0]
+        step = self._step_count() + 1
         step_t = torch.tensor(float(step))
         for p in ps:
             self.state[p]['step'] = step_t
-        # the kernel wrote through raw pointers: advance autograd's version counters so that the
-        # packed bf16 weight caches (blocks._ConvParams.packed) refresh.
         torch._C._autograd._unsafe_set_version_counter(ps, [p._version + 1 for p in ps])
-        return None
+        b1, b2 = g0['betas']
+        bc1 = 1.0 - b1 ** step
+        bc2 = 1.0 - b2 ** step
+        return (float(g0['lr']) / bc1, 1.0 / math.sqrt(bc2), b1, b2, g0['eps'], g0['weight_decay'],
+                float(self.grad_scale))

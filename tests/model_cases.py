@@ -229,7 +229,39 @@ def sampling_vs_oracle(dim=64, size=256, N=2, nd=4, seed=5):
             'emu_forward_reference': rel(e1, r1), 'emu_forward_random': rel(e2, r2)}
 
 
+def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6):
+    """The CUDA-graph replay of the iteration (Model._run_iteration) vs the eager launch sequence:
+    same weights, same batch, same torch seed (device Philox draws), `iters` iterations including
+    the 2 eager warm-up iterations, the capture and several replays, with a changing learning rate."""
+    out = {}
+    for mode in ('eager', 'graph'):
+        m, _ = make_model(dim, size, B, nd, seed)
+        m.use_graph = mode == 'graph'
+        b = {k: v.to(DEV) for k, v in batch(B, size, nd, seed).items()}
+        torch.manual_seed(77)
+        hist = []
+        for it in range(iters):
+            for opt in m.optimizer.values():          # what update_lr() does through the schedulers
+                opt.param_groups[0]['lr'] = 1e-4 * (1.0 - 0.1 * it)
+            m.set_inputs(b)
+            m.optimize_parameters(it)
+            hist.append(dict(m.loss))
+        torch.cuda.synchronize()
+        out[mode] = (hist, {n: torch.cat([p.detach().flatten() for p in m.model[n].parameters()]).clone()
+                            for n in m.model}, m._graph is not None)
+    assert out['graph'][2] and not out['eager'][2]
+    r = {}
+    for it, (he, hg) in enumerate(zip(out['eager'][0], out['graph'][0])):
+        for k in he:
+            r[f'loss_it{it}.{k}'] = abs(he[k] - hg[k]) / max(1.0, abs(he[k]))
+    for n in out['eager'][1]:
+        r[f'cos_params.{n}'] = cos(out['graph'][1][n] - 0, out['eager'][1][n])
+        r[f'params.{n}'] = rel(out['graph'][1][n], out['eager'][1][n])
+    return r
+
+
 CASES = {
+    'graph_vs_eager': graph_vs_eager,
     'nets_dim16_64': lambda: nets_vs_golden('nets_dim16_64'),
     'nets_dim64_256': lambda: nets_vs_golden('nets_dim64_256'),
     'step_dim8_64': step_vs_golden,
