@@ -4,6 +4,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 
@@ -58,21 +59,11 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   memset(&p, 0, sizeof(p));
   const int mul = c.window ? 1 : c.a_mul;
   p.BN = pick_bn(c.Bn);
+  static int force_bn = -1;
+  if (force_bn < 0) { const char* e = getenv("MT_IGEMM_BN"); force_bn = e ? atoi(e) : 0; }
+  if (force_bn > 0 && force_bn < p.BN) p.BN = force_bn;
   p.n_tiles = cdiv(c.Bn, p.BN);
-  // Two 128-row accumulators per CTA share one B tile (-33 % L2->SM bytes per FLOP at BN=256):
-  // used whenever the 256-pixel tiling still yields enough CTAs to occupy the machine.
-  p.mt = 1;
-  if (2 * p.BN <= 512) {
-    int tw, th, tn;
-    pick_tile(256, c.Wt, c.Ht, c.Nt, c.a_mul, &tw, &th, &tn);
-    const long long ctas = (long long)cdiv(c.Wt, tw) * cdiv(c.Ht, th) * cdiv(c.Nt, tn) * p.n_tiles;
-    long long vol1, vol2;
-    { int a1, b1, c1; pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul, &a1, &b1, &c1);
-      vol1 = (long long)round_up(c.Wt, a1) * round_up(c.Ht, b1) * round_up(c.Nt, c1); }
-    vol2 = (long long)round_up(c.Wt, tw) * round_up(c.Ht, th) * round_up(c.Nt, tn);
-    if (ctas >= 96 && vol2 <= vol1 + vol1 / 8) p.mt = 2;
-  }
-  pick_tile(128 * p.mt, c.Wt, c.Ht, c.Nt, c.a_mul, &p.TW, &p.TH, &p.TN);
+  pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul, &p.TW, &p.TH, &p.TN);
   p.tiles_w = cdiv(c.Wt, p.TW); p.tiles_h = cdiv(c.Ht, p.TH); p.tiles_n = cdiv(c.Nt, p.TN);
   p.Wt = c.Wt; p.Ht = c.Ht; p.Nt = c.Nt;
   p.kh = c.kh; p.kw = c.kw;
@@ -81,12 +72,17 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   p.w_base = c.w_base; p.w_step_r = c.w_step_r; p.w_step_s = c.w_step_s;
   p.k_chunks = c.window ? 1 : cdiv(c.Ac, 64);
   p.n_store = c.n_store; p.n_bias = c.bias ? c.n_bias : 0;
-  const int stage_bytes = 16384 * p.mt + p.BN * 128;
-  p.stages = (200 * 1024) / stage_bytes;
-  if (p.stages > 8) p.stages = 8;
-  const int iters = p.kh * p.kw * p.k_chunks;
-  if (p.stages > iters) p.stages = iters < 2 ? 2 : iters;
-  p.tmem_cols = pow2_cols(p.BN * p.mt);
+  // CTA pairs (one M = 256 MMA per two pixel tiles, half of the weight tile staged per CTA) whenever
+  // the Cout tile is wide enough for the operand fetch to be the limiter and there is work for them.
+  const int pix_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  static int force_cg = -1;
+  if (force_cg < 0) { const char* e = getenv("MT_IGEMM_CG"); force_cg = e ? atoi(e) : 0; }
+  p.cg = (p.BN >= 128 && pix_tiles >= 8) ? 2 : 1;
+  if (force_cg == 1 || (force_cg == 2 && p.BN >= 128)) p.cg = force_cg;
+  p.work_items = cdiv(pix_tiles, p.cg) * p.n_tiles;
+  p.stages = 0;   // fixed per (cg, BN) instantiation in igemm_fwd.cu
+  p.acc_cols = p.BN < 32 ? 32 : p.BN;
+  p.tmem_cols = pow2_cols(2 * p.acc_cols);
   p.out_n_stride = c.out_n_stride; p.out_h_stride = c.out_h_stride;
   p.out_w_stride = c.out_w_stride; p.out_off = c.out_off;
   p.act = c.act; p.slope = c.slope; p.bias = c.bias;
@@ -114,7 +110,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   {
     uint64_t dims[3] = {(uint64_t)c.Bk, (uint64_t)c.Bn, (uint64_t)c.taps_total};
     uint64_t str[2] = {(uint64_t)c.Bk_s * 2, (uint64_t)c.Bn * c.Bk_s * 2};
-    uint32_t box[3] = {64, (uint32_t)p.BN, 1};
+    uint32_t box[3] = {64, (uint32_t)(p.BN / p.cg), 1};   // a CTA of a pair stages half of the tile
     uint32_t es[3] = {1, 1, 1};
     rc = make_tmap(&tmB, c.b, 3, dims, str, box, es);
   }

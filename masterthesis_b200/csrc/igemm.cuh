@@ -13,9 +13,11 @@ enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_LRELU = 2, ACT_TANH = 3 };
 // A tile: TN x TH x TW pixels (=128 rows) x 64 channels, fetched by one 4-D TMA box.
 struct IgemmParams {
   int tiles_w, tiles_h, tiles_n, n_tiles;  // tile grid (pixels) and Cout tiles
-  int TW, TH, TN;                          // pixel tile, TW*TH*TN == 128*mt
-  int dbg;                                 // debug: 1 = no TMA after the first pass, 2 = no MMA
-  int mt;                                  // 128-row accumulators per CTA (1 or 2) sharing one B tile
+  int TW, TH, TN;                          // pixel tile, TW*TH*TN == 128
+  int dbg;                                 // debug: 32 = clock64 stamps of CTA 0 (mt_debug_timestamps)
+  int cg;                                  // 1: one CTA per 128-pixel tile; 2: CTA pair, M = 256 MMA
+  int work_items;                          // ceil(pixel tiles / cg) * n_tiles, walked round-robin
+  int acc_cols;                            // TMEM columns between the two accumulator stages
   int Wt, Ht, Nt;                          // valid extents of the pixel space
   int kh, kw;                              // tap grid
   int mul_h, mul_w;                        // TMA coord = pix*mul + off + tap*step

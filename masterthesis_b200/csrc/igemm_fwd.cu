@@ -1,13 +1,30 @@
-// Implicit-GEMM convolution for sm_100a: TMA-staged NHWC bf16 tiles, tcgen05.mma with the
-// fp32 accumulator in TMEM, warp-specialised (TMA producer / MMA issuer / 4 epilogue warps).
+// Implicit-GEMM convolution for sm_100a: persistent, warp-specialised, TMA-staged NHWC bf16 tiles,
+// tcgen05.mma with fp32 accumulators double-buffered in TMEM.
 //
 // One launch computes  out[pix, co] = act( sum_{tap, ci} A[pix (+) tap, ci] * W[tap][co][ci] + b[co] )
 // for every conv-shaped contraction of the hot path (reference call sites:
 // src/models/core/blocks.py:30-42 Conv2d, :69-73 ConvTranspose2d): forward, data-gradient and
 // the sub-pixel phases of the transposed convolutions are all expressed through the affine
 // tap -> (dh, dw, weight index) maps in IgemmParams.
+//
+// Roles per CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-9 = epilogue.
+// The CTAs are persistent: each walks a static round-robin list of (pixel tile, Cout tile) work
+// items, the shared-memory ring never drains between items, and while the epilogue warps drain
+// accumulator stage `a` the MMA warp already fills stage `a ^ 1` with the next item.
+//
+// CG = 2 (CTA pair, cta_group::2): two CTAs of a cluster own two neighbouring 128-pixel tiles and
+// one Cout tile; each loads its own A tile and HALF of the weight tile, and the leader issues one
+// M = 256 MMA for both (half the weight bytes per SM through L2 and shared memory).
+//
+// Issue-rate rule (tools/micro/mma_pipe.cu, measured on B200): a tcgen05.mma whose shared-memory
+// descriptors reach the uniform datapath through R2UR (i.e. were computed in vector registers, which
+// is what ptxas does with a run-time stage index) issues at ~190 cycles per instruction whatever its
+// shape; with descriptors of the form "uniform base + compile-time constant" the same loop runs at
+// the tensor-pipe floor (128 cycles for 128 x 256 x 16).  Hence BN and the stage count are template
+// parameters and the ring is walked by a loop that is unrolled over the stages.
 #include <stdlib.h>
 #include <stdio.h>
+#include <string.h>
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -17,109 +34,166 @@ static constexpr int BM = 128;
 static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 static constexpr int MAX_STAGES = 8;
+static constexpr int NUM_EPI_WARPS = 8;
+static constexpr int NUM_THREADS = 64 + 32 * NUM_EPI_WARPS;
 __device__ long long g_ts[64];   // debug timestamps of CTA 0 (MT_IGEMM_DBG & 32)
 
-__device__ __forceinline__ float apply_act(float v, int act, float slope) {
-  if (act == ACT_RELU) return fmaxf(v, 0.f);
-  if (act == ACT_LRELU) return v > 0.f ? v : v * slope;
-  if (act == ACT_TANH) return tanhf(v);
-  return v;
-}
-
-static constexpr int NUM_THREADS = 320;   // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue (2 per lane quadrant)
-
-// Epilogue of one warp: TMEM lane quadrant q, columns [col_begin, col_end) of every 128-row
-// sub-tile.  Activation / bias are compile-time so the per-element code is cvt + pack only: with a
-// lone warp per scheduler the epilogue is issue-bound (measured: 75 k cycles for a 256x256 tile with
-// the generic per-element code), hence the slim inner loop, x32 TMEM loads and 8 epilogue warps.
+// Epilogue of one warp: TMEM lane quadrant q, columns [col_begin, col_end) of one 128-row
+// accumulator.  Activation / bias are compile-time so the per-element code is cvt + pack only.
 template <int ACT, bool BIAS>
-__device__ __forceinline__ void epilogue_warp(const IgemmParams& p, uint32_t tmem_base, int q, int lane,
+__device__ __forceinline__ void epilogue_warp(const IgemmParams& p, uint32_t tmem_acc, int q, int lane,
                                               int col_begin, int col_end, int c_base, int w0, int h0,
                                               int n0) {
-  for (int t = 0; t < p.mt; ++t) {
-    const int m = t * BM + q * 32 + lane;
-    const int w_i = m % p.TW;
-    const int h_i = (m / p.TW) % p.TH;
-    const int n_i = m / (p.TW * p.TH);
-    const int w = w0 + w_i, h = h0 + h_i, n = n0 + n_i;
-    const bool row_ok = (w < p.Wt) && (h < p.Ht) && (n < p.Nt);
-    __nv_bfloat16* orow = p.out + p.out_off + (long long)n * p.out_n_stride +
-                          (long long)h * p.out_h_stride + (long long)w * p.out_w_stride;
-    for (int c0 = col_begin; c0 < col_end; c0 += 32) {
-      if (c_base + c0 >= p.n_store) break;  // warp-uniform
-      uint32_t v[32];
-      tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + t * p.BN + c0, v);
-      tmem_ld_wait();
-      if (!row_ok) continue;
+  const int m = q * 32 + lane;
+  const int w_i = m % p.TW;
+  const int h_i = (m / p.TW) % p.TH;
+  const int n_i = m / (p.TW * p.TH);
+  const int w = w0 + w_i, h = h0 + h_i, n = n0 + n_i;
+  const bool row_ok = (w < p.Wt) && (h < p.Ht) && (n < p.Nt);
+  __nv_bfloat16* orow = p.out + p.out_off + (long long)n * p.out_n_stride +
+                        (long long)h * p.out_h_stride + (long long)w * p.out_w_stride;
+  for (int c0 = col_begin; c0 < col_end; c0 += 32) {
+    if (c_base + c0 >= p.n_store) break;  // warp-uniform
+    uint32_t v[32];
+    tmem_ld32(tmem_acc + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+    tmem_ld_wait();
+    if (!row_ok) continue;
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const int c = c_base + c0 + g * 8;
-        if (c < p.n_store) {
-          float f[8];
+    for (int g = 0; g < 4; ++g) {
+      const int c = c_base + c0 + g * 8;
+      if (c < p.n_store) {
+        float f[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
-          if (BIAS) {
-            if (c + 8 <= p.n_bias) {
-              const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
-              const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
-              f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-              f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
-            } else {
+        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
+        if (BIAS) {
+          if (c + 8 <= p.n_bias) {
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
+            f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+            f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+          } else {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                if (c + j < p.n_bias) f[j] += __ldg(p.bias + c + j);
-            }
+            for (int j = 0; j < 8; ++j)
+              if (c + j < p.n_bias) f[j] += __ldg(p.bias + c + j);
           }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            if (ACT == ACT_RELU) f[j] = fmaxf(f[j], 0.f);
-            if (ACT == ACT_LRELU) f[j] = f[j] > 0.f ? f[j] : f[j] * p.slope;
-            if (ACT == ACT_TANH) f[j] = tanhf(f[j]);
-          }
-          uint4 pk;
-          __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
-          __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
-          __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
-          __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
-          pk.x = *reinterpret_cast<uint32_t*>(&t0);
-          pk.y = *reinterpret_cast<uint32_t*>(&t1);
-          pk.z = *reinterpret_cast<uint32_t*>(&t2);
-          pk.w = *reinterpret_cast<uint32_t*>(&t3);
-          *reinterpret_cast<uint4*>(orow + c) = pk;
         }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (ACT == ACT_RELU) f[j] = fmaxf(f[j], 0.f);
+          if (ACT == ACT_LRELU) f[j] = f[j] > 0.f ? f[j] : f[j] * p.slope;
+          if (ACT == ACT_TANH) f[j] = tanhf(f[j]);
+        }
+        uint4 pk;
+        __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
+        __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
+        __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
+        __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
+        pk.x = *reinterpret_cast<uint32_t*>(&t0);
+        pk.y = *reinterpret_cast<uint32_t*>(&t1);
+        pk.z = *reinterpret_cast<uint32_t*>(&t2);
+        pk.w = *reinterpret_cast<uint32_t*>(&t3);
+        *reinterpret_cast<uint4*>(orow + c) = pk;
       }
     }
   }
 }
 
+// Work item -> (Cout tile, pixel-tile origin of THIS CTA).  Pixel tiles are numbered w-fastest; a
+// pair owns tiles 2j and 2j+1 (an out-of-range tile loads zeros and stores nothing).
+struct WorkCoord { int n_tile, w0, h0, n0; };
+template <int CG>
+__device__ __forceinline__ WorkCoord decode_work(const IgemmParams& p, int item, int rank) {
+  WorkCoord c;
+  c.n_tile = item % p.n_tiles;
+  int pt = (item / p.n_tiles) * CG + rank;
+  const int tw = pt % p.tiles_w;
+  pt /= p.tiles_w;
+  const int th = pt % p.tiles_h;
+  const int tn = pt / p.tiles_h;
+  c.w0 = tw * p.TW; c.h0 = th * p.TH; c.n0 = tn * p.TN;
+  return c;
+}
+
+// 4 MMAs = one 64-wide K block.  `a_addr` / `b_addr` must be "uniform base + constant" (see above).
+// Shared-memory matrix descriptor (K-major, SWIZZLE_128B) as a compile-time constant: only the low
+// 18 bits of the CTA-relative address enter it, and the operand ring starts at offset SMEM_RING
+// (checked at kernel start), so no descriptor ever needs a run-time register.
+static constexpr uint32_t SMEM_RING = 2048;   // 1 KB reserved by the system + static barriers, rounded up
+__host__ __device__ constexpr uint64_t const_smem_desc(uint32_t off) {
+  return static_cast<uint64_t>((off & 0x3FFFF) >> 4) | (static_cast<uint64_t>(16 >> 4) << 16) |
+         (static_cast<uint64_t>(1024 >> 4) << 32) | (static_cast<uint64_t>(1) << 46) |
+         (static_cast<uint64_t>(2) << 61);
+}
+
+// 4 MMAs = one 64-wide K block of ring stage STAGE into the accumulator at column ACC_OFF.
+template <int CG, int STAGE, uint32_t STAGE_BYTES, int ACC_OFF>
+__device__ __forceinline__ void mma_kblock(uint32_t tmem_base, uint32_t idesc, uint32_t acc_first) {
+  const uint32_t tmem_acc = tmem_base + ACC_OFF;
+#pragma unroll
+  for (int k = 0; k < BK / 16; ++k) {
+    constexpr uint32_t a_off = SMEM_RING + STAGE * STAGE_BYTES;
+    const uint64_t ad = const_smem_desc(a_off + k * 32);
+    const uint64_t bd = const_smem_desc(a_off + A_STAGE_BYTES + k * 32);
+    const uint32_t acc = k > 0 ? 1u : acc_first;
+    if (CG == 2) umma_bf16_2sm(tmem_acc, ad, bd, idesc, acc);
+    else umma_bf16(tmem_acc, ad, bd, idesc, acc);
+  }
+}
+
+// One pass of the MMA thread over the ring (k-iterations kb .. kb+S-1 of the current work item),
+// as a compile-time recursion so that the stage index is a template constant.
+struct MmaCtx {
+  uint32_t bar_full, bar_empty;   // shared-memory addresses of the barrier arrays
+  uint32_t tmem_base, idesc, phase_bits;
+  int k_iters, acc, dbg;
+};
+template <int CG, int S, uint32_t STAGE_BYTES, int ACC_COLS, int STAGE>
+__device__ __forceinline__ void mma_round(MmaCtx& c, int kb) {
+  if constexpr (STAGE < S) {
+    if (kb + STAGE < c.k_iters) {
+      mbar_wait(c.bar_full + 8 * STAGE, (c.phase_bits >> STAGE) & 1);
+      c.phase_bits ^= 1u << STAGE;
+      tc_fence_after();
+      const uint32_t acc_first = STAGE > 0 ? 1u : (kb != 0 ? 1u : 0u);
+      if (!(c.dbg & 2)) {
+        if (c.acc == 0) mma_kblock<CG, STAGE, STAGE_BYTES, 0>(c.tmem_base, c.idesc, acc_first);
+        else mma_kblock<CG, STAGE, STAGE_BYTES, ACC_COLS>(c.tmem_base, c.idesc, acc_first);
+      }
+      if (CG == 2) umma_commit_2sm(c.bar_empty + 8 * STAGE);
+      else umma_commit(c.bar_empty + 8 * STAGE);
+    }
+    mma_round<CG, S, STAGE_BYTES, ACC_COLS, STAGE + 1>(c, kb);
+  }
+}
+
+template <int CG, int BN, int S>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const IgemmParams p) {
+  constexpr int B_ROWS = BN / CG;                           // weight rows staged by this CTA
+  constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_ROWS * BK * 2;
+  constexpr int ACC_COLS = BN < 32 ? 32 : BN;               // TMEM columns per accumulator stage
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_full[MAX_STAGES];
-  __shared__ __align__(8) uint64_t bar_empty[MAX_STAGES];
-  __shared__ __align__(8) uint64_t bar_tmem_full;
+  __shared__ __align__(8) uint64_t bar_full[S];
+  __shared__ __align__(8) uint64_t bar_empty[S];
+  __shared__ __align__(8) uint64_t bar_tfull[2];
+  __shared__ __align__(8) uint64_t bar_tempty[2];
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
+  const int cluster_id = blockIdx.x / CG;
+  const int n_clusters = gridDim.x / CG;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_bytes = A_STAGE_BYTES * p.mt;
-  const uint32_t stage_bytes = a_bytes + p.BN * BK * 2;
-  const int S = p.stages;
-
-  // ---- tile coordinates
-  int tile = blockIdx.x;
-  const int n_tile = tile % p.n_tiles;
-  tile /= p.n_tiles;
-  const int tw = tile % p.tiles_w;
-  tile /= p.tiles_w;
-  const int th = tile % p.tiles_h;
-  const int tn = tile / p.tiles_h;
-  const int w0 = tw * p.TW, h0 = th * p.TH, n0 = tn * p.TN;
-  const int total_iters = p.kh * p.kw * p.k_chunks;
-
+  if ((smem_base & 0x3FFFFu) != SMEM_RING) {            // const_smem_desc() relies on this offset
+    if (threadIdx.x == 0) g_ts[63] = -(long long)(smem_base & 0x3FFFFu);   // reported by the launcher
+    return;
+  }
+  const int k_iters = p.kh * p.kw * p.k_chunks;
+  const bool stamp = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
   const long long T0 = clock64();
+
   // ---- one-time setup
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -128,123 +202,221 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(smem_u32(&bar_full[i]), 1);
       mbar_init(smem_u32(&bar_empty[i]), 1);
     }
-    mbar_init(smem_u32(&bar_tmem_full), 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&bar_tfull[i]), 1);
+      mbar_init(smem_u32(&bar_tempty[i]), CG * NUM_EPI_WARPS);
+    }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+  if (warp == 1) {
+    if (CG == 2) tmem_alloc_2sm(smem_u32(&tmem_base_slot), p.tmem_cols);
+    else tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+  }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();     // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
-  const long long T1 = clock64();
+  if (stamp && warp == 0) g_ts[7] = clock64() - T0;
 
   if (warp == 0) {
-    // ================= TMA producer =================
-    int it = 0;
-    for (int r = 0; r < p.kh; ++r) {
-      for (int s = 0; s < p.kw; ++s) {
-        const int ch = h0 * p.mul_h + p.off_h + r * p.step_h;
-        const int cw = w0 * p.mul_w + p.off_w + s * p.step_w;
-        const int widx = p.w_base + r * p.w_step_r + s * p.w_step_s;
-        for (int kc = 0; kc < p.k_chunks; ++kc, ++it) {
-          const int stage = it % S;
-          const uint32_t ph = (it / S) & 1;
-          mbar_wait(smem_u32(&bar_empty[stage]), ph ^ 1);
-          if (lane == 0 && (p.dbg & 1) && it >= S) {
-            mbar_arrive(smem_u32(&bar_full[stage]));
-          } else if (lane == 0) {
-            const uint32_t full = smem_u32(&bar_full[stage]);
-            const uint32_t a_dst = smem_base + stage * stage_bytes;
-            mbar_expect_tx(full, stage_bytes);
-            tma_load_4d(a_dst, &tmA, full, kc * BK, cw, ch, n0);
-            tma_load_3d(a_dst + a_bytes, &tmB, full, kc * BK, n_tile * p.BN, widx);
-          }
-          __syncwarp();
-        }
-      }
-    }
-    if ((p.dbg & 32) && blockIdx.x == 0 && lane == 0) g_ts[6] = clock64() - T0;
-  } else if (warp == 1) {
-    // ================= MMA issuer =================
-    const uint32_t idesc = umma_idesc_bf16(BM, p.BN, 0, 0);
-    for (int it = 0; it < total_iters; ++it) {
-      const int stage = it % S;
-      const uint32_t ph = (it / S) & 1;
-      mbar_wait(smem_u32(&bar_full[stage]), ph);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t a_addr = smem_base + stage * stage_bytes;
-        const uint32_t b_addr = a_addr + a_bytes;
+    // ================= TMA producer (one thread; both CTAs of a pair) =================
+    // Every work item starts at ring stage 0 (stage = k-iteration mod S), so that the stage index is
+    // a compile-time constant of the unrolled loop; the per-stage phase parities live in a bit mask.
+    if (lane == 0) {
+      uint32_t phase_bits = 0;
+      for (int item = cluster_id; item < p.work_items; item += n_clusters) {
+        const WorkCoord wc = decode_work<CG>(p, item, rank);
+        int r = 0, s = 0, kc = 0;
+        for (int kb = 0; kb < k_iters; kb += S) {
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t bd = umma_smem_desc(b_addr + k * 32, 16, 1024);
-          for (int t = 0; t < ((p.dbg & 2) ? 0 : p.mt); ++t) {   // the 128-row sub-tiles share the B tile
-            const uint64_t ad = umma_smem_desc(a_addr + t * A_STAGE_BYTES + k * 32, 16, 1024);
-            umma_bf16(tmem_base + t * p.BN, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+          for (int stage = 0; stage < S; ++stage) {
+            if (kb + stage < k_iters) {
+              mbar_wait(smem_u32(&bar_empty[stage]), ((phase_bits >> stage) & 1) ^ 1);
+              phase_bits ^= 1u << stage;
+              const int ch = wc.h0 * p.mul_h + p.off_h + r * p.step_h;
+              const int cw = wc.w0 * p.mul_w + p.off_w + s * p.step_w;
+              const int widx = p.w_base + r * p.w_step_r + s * p.w_step_s;
+              const uint32_t a_dst = smem_base + stage * STAGE_BYTES;
+              if (CG == 2) {
+                // the leader's barrier counts the bytes of BOTH CTAs
+                const uint32_t full = smem_u32(&bar_full[stage]) & PEER_BIT_MASK;
+                if (rank == 0) mbar_expect_tx(full, 2 * STAGE_BYTES);
+                tma_load_4d_2sm(a_dst, &tmA, full, kc * BK, cw, ch, wc.n0);
+                tma_load_3d_2sm(a_dst + A_STAGE_BYTES, &tmB, full, kc * BK,
+                                wc.n_tile * BN + rank * B_ROWS, widx);
+              } else {
+                const uint32_t full = smem_u32(&bar_full[stage]);
+                if ((p.dbg & 1) && item != cluster_id) {
+                  mbar_arrive(full);          // debug: handshake only, no TMA traffic
+                } else {
+                  mbar_expect_tx(full, STAGE_BYTES);
+                  tma_load_4d(a_dst, &tmA, full, kc * BK, cw, ch, wc.n0);
+                  tma_load_3d(a_dst + A_STAGE_BYTES, &tmB, full, kc * BK, wc.n_tile * BN, widx);
+                }
+              }
+              if (++kc == p.k_chunks) {
+                kc = 0;
+                if (++s == p.kw) { s = 0; ++r; }
+              }
+            }
           }
         }
-        umma_commit(smem_u32(&bar_empty[stage]));
-        if (it == total_iters - 1) umma_commit(smem_u32(&bar_tmem_full));
       }
-      __syncwarp();
-      if ((p.dbg & 32) && blockIdx.x == 0 && lane == 0 && it < 40) g_ts[8 + it] = clock64() - T0;
     }
+    __syncwarp();
+    if (stamp) g_ts[6] = clock64() - T0;
+  } else if (warp == 1) {
+    // ================= MMA issuer (one thread of the leader CTA) =================
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) |
+                                 (static_cast<uint32_t>(BN >> 3) << 17) |
+                                 (static_cast<uint32_t>((BM * CG) >> 4) << 24);
+      MmaCtx c;
+      c.bar_full = smem_u32(&bar_full[0]); c.bar_empty = smem_u32(&bar_empty[0]);
+      c.tmem_base = tmem_base; c.idesc = IDESC; c.phase_bits = 0;
+      c.k_iters = k_iters; c.dbg = p.dbg;
+      int tile_i = 0;
+      for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
+        const int acc = tile_i & 1;
+        c.acc = acc;
+        mbar_wait(smem_u32(&bar_tempty[acc]), ((tile_i >> 1) & 1) ^ 1);   // both CTAs drained it
+        tc_fence_after();
+        if (stamp && tile_i < 8) g_ts[8 + 2 * tile_i] = clock64() - T0;
+        for (int kb = 0; kb < k_iters; kb += S)
+          mma_round<CG, S, STAGE_BYTES, ACC_COLS, 0>(c, kb);
+        if (CG == 2) umma_commit_2sm(smem_u32(&bar_tfull[acc]));
+        else umma_commit(smem_u32(&bar_tfull[acc]));
+        if (stamp && tile_i < 8) g_ts[9 + 2 * tile_i] = clock64() - T0;
+      }
+    }
+    __syncwarp();
   } else {
     // ================= epilogue: TMEM -> regs -> bias/act -> bf16 -> HBM =================
     const int q = warp & 3;            // TMEM lane quadrant this warp may access
     const int grp = (warp - 2) >> 2;   // which half of the columns
-    int per = p.BN / 2;
-    if (per < 32) per = 32;
-    const int col_begin = grp * per, col_end = min(p.BN, col_begin + per);
-    const int c_base = n_tile * p.BN;
-    mbar_wait(smem_u32(&bar_tmem_full), 0);
-    tc_fence_after();
-    const long long T2 = clock64();
-    if ((p.dbg & 32) && blockIdx.x == 0 && lane == 0 && warp < 6) g_ts[48 + warp] = T2 - T0;
-    if (col_begin < col_end) {
-      const bool hb = p.n_bias > 0;
-#define MT_EPI(A, B) epilogue_warp<A, B>(p, tmem_base, q, lane, col_begin, col_end, c_base, w0, h0, n0)
-      switch (p.act) {
-        case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
-        case ACT_LRELU: if (hb) MT_EPI(ACT_LRELU, true); else MT_EPI(ACT_LRELU, false); break;
-        case ACT_TANH:  if (hb) MT_EPI(ACT_TANH, true);  else MT_EPI(ACT_TANH, false);  break;
-        default:        if (hb) MT_EPI(ACT_NONE, true);  else MT_EPI(ACT_NONE, false);  break;
-      }
+    constexpr int PER = BN / 2 < 32 ? 32 : BN / 2;
+    const int col_begin = grp * PER, col_end = min(BN, col_begin + PER);
+    const bool hb = p.n_bias > 0;
+    int tile_i = 0;
+    for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
+      const WorkCoord wc = decode_work<CG>(p, item, rank);
+      const int acc = tile_i & 1;
+      const uint32_t acc_ph = (tile_i >> 1) & 1;
+      mbar_wait(smem_u32(&bar_tfull[acc]), acc_ph);
+      tc_fence_after();
+      if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
+      if (col_begin < col_end) {
+        const uint32_t tmem_acc = tmem_base + acc * ACC_COLS;
+        const int c_base = wc.n_tile * BN;
+#define MT_EPI(A, B) epilogue_warp<A, B>(p, tmem_acc, q, lane, col_begin, col_end, c_base, wc.w0, wc.h0, wc.n0)
+        switch (p.act) {
+          case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
+          case ACT_LRELU: if (hb) MT_EPI(ACT_LRELU, true); else MT_EPI(ACT_LRELU, false); break;
+          case ACT_TANH:  if (hb) MT_EPI(ACT_TANH, true);  else MT_EPI(ACT_TANH, false);  break;
+          default:        if (hb) MT_EPI(ACT_NONE, true);  else MT_EPI(ACT_NONE, false);  break;
+        }
 #undef MT_EPI
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {                 // hand the accumulator back to the (leader's) MMA thread
+        if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
+        else mbar_arrive(smem_u32(&bar_tempty[acc]));
+      }
+      if (stamp && warp == 2 && tile_i < 8) g_ts[25 + 2 * tile_i] = clock64() - T0;
     }
   }
 
   // ---- teardown
-  const long long T3 = clock64();
-  if ((p.dbg & 32) && blockIdx.x == 0 && (threadIdx.x % 32 == 0) && warp < 6) {
-    g_ts[warp] = T3 - T0;
-    if (warp == 0) g_ts[7] = T1 - T0;
-  }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+  if (CG == 2) cluster_sync_all();     // the leader's MMAs read the peer's smem / write its TMEM
+  if (warp == 1) {
+    if (CG == 2) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+  if (stamp && warp == 0) g_ts[0] = clock64() - T0;
 }
 
-int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p,
-                 cudaStream_t stream) {
-  const int stage_bytes = A_STAGE_BYTES * p.mt + p.BN * BK * 2;
-  const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+static int g_num_sms = 0;
+
+template <int CG, int BN>
+struct StageCfg {
+  static constexpr int kStageBytes = A_STAGE_BYTES + (BN / CG) * BK * 2;
+  static constexpr int kFit = (208 * 1024) / kStageBytes;
+  static constexpr int kStages = kFit > 8 ? 8 : kFit;
+  static constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024;
+};
+
+template <int CG, int BN>
+static cudaError_t launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p,
+                              cudaStream_t stream) {
+  using Cfg = StageCfg<CG, BN>;
+  auto* kern = igemm_conv_kernel<CG, BN, Cfg::kStages>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_conv_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-    if (e != cudaSuccess) return -(3000 + (int)e);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)Cfg::kSmem);
+    if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const long long grid = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.n_tiles;
-  if (grid <= 0 || grid > 0x7fffffffLL) return -1000;
+  int clusters = g_num_sms / CG;
+  if (clusters > p.work_items) clusters = p.work_items;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(clusters * CG), 1, 1);
+  cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p);
+}
+
+int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p_in,
+                 cudaStream_t stream) {
+  IgemmParams p = p_in;
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
   static int dbg = -1;
   if (dbg < 0) { const char* e = getenv("MT_IGEMM_DBG"); dbg = e ? atoi(e) : 0; }
-  if (dbg) { IgemmParams q = p; q.dbg = dbg; igemm_conv_kernel<<<(unsigned)grid, NUM_THREADS, smem, stream>>>(tmA, tmB, q); }
-  else
-  igemm_conv_kernel<<<(unsigned)grid, NUM_THREADS, smem, stream>>>(tmA, tmB, p);
-  cudaError_t e = cudaGetLastError();
-  return e == cudaSuccess ? 0 : -(int)e;
+  p.dbg = dbg;
+  if (p.work_items <= 0) return -1000;
+  cudaError_t e = cudaErrorInvalidValue;
+  const int key = p.cg * 1000 + p.BN;
+  switch (key) {
+    case 2256: e = launch_cfg<2, 256>(tmA, tmB, p, stream); break;
+    case 2128: e = launch_cfg<2, 128>(tmA, tmB, p, stream); break;
+    case 1256: e = launch_cfg<1, 256>(tmA, tmB, p, stream); break;
+    case 1128: e = launch_cfg<1, 128>(tmA, tmB, p, stream); break;
+    case 1064: e = launch_cfg<1, 64>(tmA, tmB, p, stream); break;
+    case 1032: e = launch_cfg<1, 32>(tmA, tmB, p, stream); break;
+    case 1016: e = launch_cfg<1, 16>(tmA, tmB, p, stream); break;
+    default: return -1010;
+  }
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) return -(int)e;
+  // One-time self check of the shared-memory layout assumption behind const_smem_desc().
+  static bool ring_checked = false;
+  if (!ring_checked) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) {
+      long long flag = 0;
+      if (cudaStreamSynchronize(stream) != cudaSuccess) return -1011;
+      if (cudaMemcpyFromSymbol(&flag, g_ts, sizeof(flag), 63 * sizeof(long long)) != cudaSuccess)
+        return -1011;
+      if (flag < 0) return -1011;        // operand ring is not at SMEM_RING: nothing was computed
+      ring_checked = true;
+    }
+  }
+  return 0;
 }
 
 }  // namespace mt

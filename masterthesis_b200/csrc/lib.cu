@@ -17,6 +17,8 @@ extern "C" const char* mt_error_string(int code) {
     case -1005: return "bad dimensions";
     case -1006: return "stride-2 phase without taps";
     case -1007: return "reflection pad must be smaller than the spatial size";
+    case -1010: return "unsupported (cg, BN) implicit-GEMM tile";
+    case -1011: return "implicit-GEMM shared-memory ring is not at the expected offset";
     case -1009: return "row-window mode requested for an ineligible convolution";
     case -1008: return "missing parameter tensor for this norm mode";
     default: break;
