@@ -33,7 +33,6 @@ namespace mt {
 static constexpr int BM = 128;
 static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
-static constexpr int MAX_STAGES = 8;
 static constexpr int NUM_EPI_WARPS = 8;
 static constexpr int NUM_THREADS = 64 + 32 * NUM_EPI_WARPS;
 __device__ long long g_ts[64];   // debug timestamps of CTA 0 (MT_IGEMM_DBG & 32)
@@ -114,17 +113,6 @@ __device__ __forceinline__ WorkCoord decode_work(const IgemmParams& p, int item,
   return c;
 }
 
-// 4 MMAs = one 64-wide K block.  `a_addr` / `b_addr` must be "uniform base + constant" (see above).
-// Shared-memory matrix descriptor (K-major, SWIZZLE_128B) as a compile-time constant: only the low
-// 18 bits of the CTA-relative address enter it, and the operand ring starts at offset SMEM_RING
-// (checked at kernel start), so no descriptor ever needs a run-time register.
-static constexpr uint32_t SMEM_RING = 2048;   // 1 KB reserved by the system + static barriers, rounded up
-__host__ __device__ constexpr uint64_t const_smem_desc(uint32_t off) {
-  return static_cast<uint64_t>((off & 0x3FFFF) >> 4) | (static_cast<uint64_t>(16 >> 4) << 16) |
-         (static_cast<uint64_t>(1024 >> 4) << 32) | (static_cast<uint64_t>(1) << 46) |
-         (static_cast<uint64_t>(2) << 61);
-}
-
 // 4 MMAs = one 64-wide K block of ring stage STAGE into the accumulator at column ACC_OFF.
 template <int CG, int STAGE, uint32_t STAGE_BYTES, int ACC_OFF>
 __device__ __forceinline__ void mma_kblock(uint32_t tmem_base, uint32_t idesc, uint32_t acc_first) {
@@ -132,8 +120,8 @@ __device__ __forceinline__ void mma_kblock(uint32_t tmem_base, uint32_t idesc, u
 #pragma unroll
   for (int k = 0; k < BK / 16; ++k) {
     constexpr uint32_t a_off = SMEM_RING + STAGE * STAGE_BYTES;
-    const uint64_t ad = const_smem_desc(a_off + k * 32);
-    const uint64_t bd = const_smem_desc(a_off + A_STAGE_BYTES + k * 32);
+    const uint64_t ad = const_smem_desc(a_off + k * 32, 16, 1024);
+    const uint64_t bd = const_smem_desc(a_off + A_STAGE_BYTES + k * 32, 16, 1024);
     const uint32_t acc = k > 0 ? 1u : acc_first;
     if (CG == 2) umma_bf16_2sm(tmem_acc, ad, bd, idesc, acc);
     else umma_bf16(tmem_acc, ad, bd, idesc, acc);

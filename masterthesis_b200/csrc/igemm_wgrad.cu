@@ -15,7 +15,6 @@ namespace mt {
 static constexpr int WG_BM = 128;
 static constexpr int WG_BK = 64;           // pixels per stage
 static constexpr int WG_CHUNK = 64 * 128;  // one (64 ch x 64 pix) slab in bytes
-static constexpr int WG_MAX_STAGES = 8;
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b),
@@ -23,21 +22,88 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                : "memory");
 }
 
+// One pass over the ring (k-iterations kb .. kb+S-1) as a compile-time recursion: the stage index and
+// with it every shared-memory descriptor is a constant (MMA issue-rate rule, see igemm_fwd.cu).
+struct WgCtx {
+  uint32_t bar_full, bar_empty, smem_base, tmem_base, phase_bits;
+  int iters, kt_begin, m_tile, n_tile, r, s;
+};
+
+template <int BN, int S, int STAGE>
+__device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const CUtensorMap* tmQ,
+                                                 const WgradParams& p, WgCtx& c, int kb) {
+  constexpr uint32_t STAGE_BYTES = (2 + BN / 64) * WG_CHUNK;
+  if constexpr (STAGE < S) {
+    if (kb + STAGE < c.iters) {
+      int kt = c.kt_begin + kb + STAGE;
+      const int tw = kt % p.tiles_w; kt /= p.tiles_w;
+      const int th = kt % p.tiles_h;
+      const int tn = kt / p.tiles_h;
+      const int w0 = tw * p.TW, h0 = th * p.TH, n0 = tn * p.TN;
+      mbar_wait(c.bar_empty + 8 * STAGE, ((c.phase_bits >> STAGE) & 1) ^ 1);
+      c.phase_bits ^= 1u << STAGE;
+      const uint32_t full = c.bar_full + 8 * STAGE;
+      const uint32_t a_dst = c.smem_base + STAGE * STAGE_BYTES;
+      const uint32_t b_dst = a_dst + 2 * WG_CHUNK;
+      mbar_expect_tx(full, STAGE_BYTES);
+      tma_load_4d(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
+      tma_load_4d(a_dst + WG_CHUNK, tmP, full, c.m_tile * WG_BM + 64, w0, h0, n0);
+      const int qw = w0 * p.mul_w + p.off_w + c.s * p.step_w;
+      const int qh = h0 * p.mul_h + p.off_h + c.r * p.step_h;
+#pragma unroll
+      for (int ch = 0; ch < BN / 64; ++ch)
+        tma_load_4d(b_dst + ch * WG_CHUNK, tmQ, full, c.n_tile * BN + ch * 64, qw, qh, n0);
+    }
+    wg_produce_round<BN, S, STAGE + 1>(tmP, tmQ, p, c, kb);
+  }
+}
+
+template <int BN, int S, int STAGE>
+__device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
+  constexpr uint32_t STAGE_BYTES = (2 + BN / 64) * WG_CHUNK;
+  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+                             (static_cast<uint32_t>(BN >> 3) << 17) |
+                             (static_cast<uint32_t>(WG_BM >> 4) << 24);
+  if constexpr (STAGE < S) {
+    if (kb + STAGE < c.iters) {
+      mbar_wait(c.bar_full + 8 * STAGE, (c.phase_bits >> STAGE) & 1);
+      c.phase_bits ^= 1u << STAGE;
+      tc_fence_after();
+      constexpr uint32_t a_off = SMEM_RING + STAGE * STAGE_BYTES;
+      constexpr uint32_t b_off = a_off + 2 * WG_CHUNK;
+#pragma unroll
+      for (int k = 0; k < WG_BK / 16; ++k) {
+        // 16 pixels = two 8-row groups of 1024 B; chunks of 64 channels are WG_CHUNK apart.
+        const uint64_t ad = const_smem_desc(a_off + k * 2048, WG_CHUNK, 1024);
+        const uint64_t bd = const_smem_desc(b_off + k * 2048, WG_CHUNK, 1024);
+        const uint32_t acc = (STAGE > 0 || k > 0) ? 1u : (kb != 0 ? 1u : 0u);
+        umma_bf16(c.tmem_base, ad, bd, IDESC, acc);
+      }
+      umma_commit(c.bar_empty + 8 * STAGE);
+    }
+    wg_mma_round<BN, S, STAGE + 1>(c, kb);
+  }
+}
+
+__device__ long long g_wg_flag;   // < 0: shared-memory ring not at SMEM_RING (checked by the launcher)
+
+template <int BN, int S>
 __global__ void __launch_bounds__(192, 1)
 igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ,
                    const WgradParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_full[WG_MAX_STAGES];
-  __shared__ __align__(8) uint64_t bar_empty[WG_MAX_STAGES];
+  __shared__ __align__(8) uint64_t bar_full[S];
+  __shared__ __align__(8) uint64_t bar_empty[S];
   __shared__ __align__(8) uint64_t bar_tmem_full;
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int n_chunks = p.BN / 64;
-  const uint32_t stage_bytes = (2 + n_chunks) * WG_CHUNK;
-  const int S = p.stages;
+  if ((smem_base & 0x3FFFFu) != SMEM_RING) {
+    if (threadIdx.x == 0) g_wg_flag = -(long long)(smem_base & 0x3FFFFu);
+    return;
+  }
 
   // ---- work item
   int item = blockIdx.x;
@@ -69,61 +135,29 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
+  WgCtx c;
+  c.bar_full = smem_u32(&bar_full[0]); c.bar_empty = smem_u32(&bar_empty[0]);
+  c.smem_base = smem_base; c.tmem_base = tmem_base; c.phase_bits = 0;
+  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.r = r; c.s = s;
   if (warp == 0) {
-    for (int it = 0; it < iters; ++it) {
-      int kt = kt_begin + it;
-      const int tw = kt % p.tiles_w; kt /= p.tiles_w;
-      const int th = kt % p.tiles_h;
-      const int tn = kt / p.tiles_h;
-      const int w0 = tw * p.TW, h0 = th * p.TH, n0 = tn * p.TN;
-      const int stage = it % S;
-      const uint32_t ph = (it / S) & 1;
-      mbar_wait(smem_u32(&bar_empty[stage]), ph ^ 1);
-      if (lane == 0) {
-        const uint32_t full = smem_u32(&bar_full[stage]);
-        const uint32_t a_dst = smem_base + stage * stage_bytes;
-        const uint32_t b_dst = a_dst + 2 * WG_CHUNK;
-        mbar_expect_tx(full, stage_bytes);
-        tma_load_4d(a_dst, &tmP, full, m_tile * WG_BM, w0, h0, n0);
-        tma_load_4d(a_dst + WG_CHUNK, &tmP, full, m_tile * WG_BM + 64, w0, h0, n0);
-        const int qw = w0 * p.mul_w + p.off_w + s * p.step_w;
-        const int qh = h0 * p.mul_h + p.off_h + r * p.step_h;
-        for (int c = 0; c < n_chunks; ++c)
-          tma_load_4d(b_dst + c * WG_CHUNK, &tmQ, full, n_tile * p.BN + c * 64, qw, qh, n0);
-      }
-      __syncwarp();
-    }
+    if (lane == 0)
+      for (int kb = 0; kb < iters; kb += S) wg_produce_round<BN, S, 0>(&tmP, &tmQ, p, c, kb);
+    __syncwarp();
   } else if (warp == 1) {
-    const uint32_t idesc = umma_idesc_bf16(WG_BM, p.BN, 1, 1);
-    for (int it = 0; it < iters; ++it) {
-      const int stage = it % S;
-      const uint32_t ph = (it / S) & 1;
-      mbar_wait(smem_u32(&bar_full[stage]), ph);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t a_addr = smem_base + stage * stage_bytes;
-        const uint32_t b_addr = a_addr + 2 * WG_CHUNK;
-#pragma unroll
-        for (int k = 0; k < WG_BK / 16; ++k) {
-          // 16 pixels = two 8-row groups of 1024 B; chunks of 64 channels are WG_CHUNK apart.
-          const uint64_t ad = umma_smem_desc(a_addr + k * 2048, WG_CHUNK, 1024);
-          const uint64_t bd = umma_smem_desc(b_addr + k * 2048, WG_CHUNK, 1024);
-          umma_bf16(tmem_base, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
-        }
-        umma_commit(smem_u32(&bar_empty[stage]));
-        if (it == iters - 1) umma_commit(smem_u32(&bar_tmem_full));
-      }
-      __syncwarp();
+    if (lane == 0) {
+      for (int kb = 0; kb < iters; kb += S) wg_mma_round<BN, S, 0>(c, kb);
+      umma_commit(smem_u32(&bar_tmem_full));
     }
+    __syncwarp();
   } else {
     const int q = warp & 3;
     const int m = m_tile * WG_BM + q * 32 + lane;
     const bool row_ok = m < p.M_valid;
     float* orow = p.out + (long long)tap * p.out_tap_stride + (long long)m * p.out_m_stride;
-    const int n_base = n_tile * p.BN;
+    const int n_base = n_tile * BN;
     mbar_wait(smem_u32(&bar_tmem_full), 0);
     tc_fence_after();
-    for (int c0 = 0; c0 < p.BN; c0 += 16) {
+    for (int c0 = 0; c0 < BN; c0 += 16) {
       if (n_base + c0 >= p.N_valid) break;
       uint32_t v[16];
       tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
@@ -145,22 +179,49 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
-int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradParams& p,
-                 cudaStream_t stream) {
-  const int stage_bytes = (2 + p.BN / 64) * WG_CHUNK;
-  const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+template <int BN>
+static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& tmQ,
+                                    const WgradParams& p, cudaStream_t stream) {
+  constexpr int kStageBytes = (2 + BN / 64) * WG_CHUNK;
+  constexpr int kFit = (200 * 1024) / kStageBytes;
+  constexpr int kStages = kFit > 8 ? 8 : kFit;
+  constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024;
+  auto* kern = igemm_wgrad_kernel<BN, kStages>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_wgrad_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-    if (e != cudaSuccess) return -(3000 + (int)e);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
+    if (e != cudaSuccess) return e;
     attr_set = true;
   }
   const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;
+  kern<<<(unsigned)grid, 192, kSmem, stream>>>(tmP, tmQ, p);
+  return cudaGetLastError();
+}
+
+int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradParams& p,
+                 cudaStream_t stream) {
+  const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;
   if (grid <= 0 || grid > 0x7fffffffLL) return -1000;
-  igemm_wgrad_kernel<<<(unsigned)grid, 192, smem, stream>>>(tmP, tmQ, p);
-  cudaError_t e = cudaGetLastError();
-  return e == cudaSuccess ? 0 : -(int)e;
+  cudaError_t e;
+  switch (p.BN) {
+    case 256: e = launch_wgrad_cfg<256>(tmP, tmQ, p, stream); break;
+    case 128: e = launch_wgrad_cfg<128>(tmP, tmQ, p, stream); break;
+    case 64: e = launch_wgrad_cfg<64>(tmP, tmQ, p, stream); break;
+    default: return -1010;
+  }
+  if (e != cudaSuccess) return -(int)e;
+  static bool ring_checked = false;
+  if (!ring_checked) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) {
+      long long flag = 0;
+      if (cudaStreamSynchronize(stream) != cudaSuccess) return -1011;
+      if (cudaMemcpyFromSymbol(&flag, g_wg_flag, sizeof(flag)) != cudaSuccess) return -1011;
+      if (flag < 0) return -1011;
+      ring_checked = true;
+    }
+  }
+  return 0;
 }
 
 }  // namespace mt

@@ -227,6 +227,20 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_
   d |= static_cast<uint64_t>(2) << 61;  // SWIZZLE_128B
   return d;
 }
+// The same descriptor as a compile-time constant of the CTA-relative byte offset (only the low 18
+// address bits enter it).  MMA operands must be immediates / uniform registers: a descriptor that
+// reaches the uniform datapath through R2UR costs ~40 cycles per move and caps the issue rate at
+// ~190 cycles per tcgen05.mma (tools/micro/mma_pipe.cu).
+__host__ __device__ constexpr uint64_t const_smem_desc(uint32_t off, uint32_t lbo_bytes,
+                                                       uint32_t sbo_bytes) {
+  return static_cast<uint64_t>((off & 0x3FFFF) >> 4) |
+         (static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16) |
+         (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32) |
+         (static_cast<uint64_t>(1) << 46) | (static_cast<uint64_t>(2) << 61);
+}
+// Offset of the 1024-aligned dynamic shared memory of our kernels: 1 KB reserved by the system plus
+// < 1 KB of static barriers.  Every kernel that builds constant descriptors checks it at start.
+static constexpr uint32_t SMEM_RING = 2048;
 // Instruction descriptor for kind::f16, bf16 inputs, fp32 accumulate.
 __host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N, int a_mn_major,
                                                     int b_mn_major) {
