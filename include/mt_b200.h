@@ -94,9 +94,11 @@ int mt_add_interior(void* dpad, const void* dense, int N, int H, int W, int C, i
 
 /* ---- normalisation (InstanceNorm2d / AdaptiveInstanceNorm / LayerNorm) ---------------------
  * functions.py:17, norm.py:5-33.  stats/sums: [N][C][2] fp32; ss: (scale, shift) per (n,c);
- * mr: (mean, rstd); coef: [N][C][3]; gb: fc(s) output [N][2C] (weight | bias). */
+ * mr: (mean, rstd); coef: [N][C][3]; gb: fc(s) output [N][2C] (weight | bias).
+ * C is the STORED channel count; C_valid <= C the logical one (LayerNorm statistics run over
+ * C_valid*HW elements and ln_w / ln_b / dln_* hold C_valid entries; padded channels stay zero). */
 int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream);
-int mt_norm_finalize(const float* stats, int mode, int N, int C, int HW, float eps,
+int mt_norm_finalize(const float* stats, int mode, int N, int C, int C_valid, int HW, float eps,
                      const float* gb, const float* ln_w, const float* ln_b, float* ss, float* mr,
                      void* stream);
 /* out_pad[interior] = act(x*scale+shift) (+ residual) (+ noise, misc.py:25); ss may be NULL */
@@ -105,7 +107,7 @@ int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C
                       void* out_pad, int out_p, void* stream);
 int mt_norm_bwd_reduce(const void* g, const void* x, const float* ss, int N, int HW, int C,
                        int act, float slope, float* sums, void* stream);
-int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C, int HW,
+int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C, int C_valid, int HW,
                          const float* gb, const float* ln_w, float* coef, float* dgb,
                          float* dln_w, float* dln_b, void* stream);
 int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float* coef, int N,

@@ -75,7 +75,7 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 
 // ---------------------------------------------------------------- forward finalize
 // stats -> ss[n][c] = (scale, shift) with y = x*scale + shift, mr[n][c] = (mean, rstd)
-__global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, int N, int C,
+__global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, int N, int C, int Cv,
                                      int HW, float eps, const float* __restrict__ gb,
                                      const float* __restrict__ ln_w, const float* __restrict__ ln_b,
                                      float* __restrict__ ss, float* __restrict__ mr) {
@@ -83,7 +83,7 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, 
   __shared__ float tot[2];
   if (mode == MT_NORM_LAYER) {
     float s0 = 0.f, s1 = 0.f;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    for (int c = threadIdx.x; c < Cv; c += blockDim.x) {
       s0 += stats[((long long)n * C + c) * 2];
       s1 += stats[((long long)n * C + c) * 2 + 1];
     }
@@ -104,10 +104,11 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, 
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float mean, var, A = 1.f, B = 0.f;
     if (mode == MT_NORM_LAYER) {
-      const float cnt = (float)C * (float)HW;
+      const float cnt = (float)Cv * (float)HW;
       mean = tot[0] / cnt;
       var = tot[1] / cnt - mean * mean;
-      if (ln_w) { A = ln_w[c]; B = ln_b[c]; }
+      if (c >= Cv) { A = 0.f; B = 0.f; }           // padded storage channels stay zero
+      else if (ln_w) { A = ln_w[c]; B = ln_b[c]; }
     } else {
       mean = stats[((long long)n * C + c) * 2] / (float)HW;
       var = stats[((long long)n * C + c) * 2 + 1] / (float)HW - mean * mean;
@@ -175,7 +176,7 @@ affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
 // sums[n][c] = (sum g, sum g*x) with g already masked by act'.  Produces coef[n][c][3] such that
 //   dx = c0*g + c1*x + c2, and the parameter gradients.
 __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const float* __restrict__ mr,
-                                         int mode, int N, int C, int HW,
+                                         int mode, int N, int C, int Cv, int HW,
                                          const float* __restrict__ gb, const float* __restrict__ ln_w,
                                          float* __restrict__ coef, float* __restrict__ dgb,
                                          float* __restrict__ dln_w, float* __restrict__ dln_b) {
@@ -185,7 +186,7 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
   if (mode == MT_NORM_LAYER) {
     // mean_n(A g) and mean_n(A g xhat) over all (c, hw)
     float s0 = 0.f, s1 = 0.f;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    for (int c = threadIdx.x; c < Cv; c += blockDim.x) {
       const float mean = mr[((long long)n * C + c) * 2], rstd = mr[((long long)n * C + c) * 2 + 1];
       const float sg = sums[((long long)n * C + c) * 2], sgx = sums[((long long)n * C + c) * 2 + 1];
       const float sgxh = (sgx - mean * sg) * rstd;
@@ -202,7 +203,7 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
     if (threadIdx.x == 0) {
       float t0 = 0.f, t1 = 0.f;
       for (int i = 0; i < (blockDim.x + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
-      const float cnt = (float)C * (float)HW;
+      const float cnt = (float)Cv * (float)HW;
       tot[0] = t0 / cnt; tot[1] = t1 / cnt;
     }
     __syncthreads();
@@ -213,12 +214,13 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
     const float sgxh = (sgx - mean * sg) * rstd;   // sum g*xhat
     float A = 1.f, mg, mgx;
     if (mode == MT_NORM_LAYER) {
-      A = ln_w ? ln_w[c] : 1.f;
+      A = c >= Cv ? 0.f : (ln_w ? ln_w[c] : 1.f);
       mg = tot[0]; mgx = tot[1];                    // already include A
-      // dx = rstd*(A g - mg - xhat*mgx)
+      // dx = rstd*(A g - mg - xhat*mgx); padded storage channels get no gradient
+      const float live = c >= Cv ? 0.f : 1.f;
       coef[((long long)n * C + c) * 3 + 0] = rstd * A;
-      coef[((long long)n * C + c) * 3 + 1] = -rstd * rstd * mgx;
-      coef[((long long)n * C + c) * 3 + 2] = -rstd * (mg - mean * rstd * mgx);
+      coef[((long long)n * C + c) * 3 + 1] = -rstd * rstd * mgx * live;
+      coef[((long long)n * C + c) * 3 + 2] = -rstd * (mg - mean * rstd * mgx) * live;
     } else {
       if (mode == MT_NORM_ADAIN) {
         A = 1.f + gb[(long long)n * 2 * C + c];
@@ -335,11 +337,12 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
 extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream) {
   return reduce_launch(false, x, nullptr, nullptr, N, HW, C, 0, 0.f, stats, ST(stream));
 }
-extern "C" int mt_norm_finalize(const float* stats, int mode, int N, int C, int HW, float eps,
+extern "C" int mt_norm_finalize(const float* stats, int mode, int N, int C, int C_valid, int HW, float eps,
                                 const float* gb, const float* ln_w, const float* ln_b, float* ss,
                                 float* mr, void* stream) {
   if (mode == MT_NORM_ADAIN && !gb) return -1008;
-  norm_finalize_kernel<<<N, 256, 0, ST(stream)>>>(stats, mode, N, C, HW, eps, gb, ln_w, ln_b, ss, mr);
+  if (C_valid <= 0 || C_valid > C) return -1005;
+  norm_finalize_kernel<<<N, 256, 0, ST(stream)>>>(stats, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr);
   return cuda_rc();
 }
 extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,
@@ -356,10 +359,11 @@ extern "C" int mt_norm_bwd_reduce(const void* g, const void* x, const float* ss,
   return reduce_launch(true, x, g, ss, N, HW, C, act, slope, sums, ST(stream));
 }
 extern "C" int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C,
-                                    int HW, const float* gb, const float* ln_w, float* coef,
+                                    int C_valid, int HW, const float* gb, const float* ln_w, float* coef,
                                     float* dgb, float* dln_w, float* dln_b, void* stream) {
   if (mode == MT_NORM_ADAIN && (!gb || !dgb)) return -1008;
-  norm_bwd_finalize_kernel<<<N, 256, 0, ST(stream)>>>(sums, mr, mode, N, C, HW, gb, ln_w, coef,
+  if (C_valid <= 0 || C_valid > C) return -1005;
+  norm_bwd_finalize_kernel<<<N, 256, 0, ST(stream)>>>(sums, mr, mode, N, C, C_valid, HW, gb, ln_w, coef,
                                                       dgb, dln_w, dln_b);
   return cuda_rc();
 }

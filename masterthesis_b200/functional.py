@@ -76,7 +76,7 @@ class ConvNormAct(Function):
         stats = ops.plane_stats(raw)
         gb = p1 if mode == "adain" else None
         lw, lb = (p1, p2) if mode == "layer" else (None, None)
-        ss, mr = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb)
+        ss, mr = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb, C_valid=geom.Cout)
         out = ops.affine_act_fwd(raw, ss, act=act, noise=noise, out_p=out_pad)
         ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
@@ -91,7 +91,7 @@ class ConvNormAct(Function):
         G = ops.reflect_fold(_c(dout), op)
         dy, dgb, dlw, dlb = ops.norm_bwd(G, raw, ss, mr, mode, act=act,
                                          gb=_c(p1) if mode == "adain" else None,
-                                         ln_w=p1 if mode == "layer" else None)
+                                         ln_w=p1 if mode == "layer" else None, C_valid=g.Cout)
         dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
         dw = ops.conv_wgrad(x, dy, g) if ctx.needs_input_grad[1] else None
         db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
@@ -202,8 +202,11 @@ class RgbHead(Function):
 
     @staticmethod
     def forward(ctx, x, weight):
-        Co = weight.shape[1]
-        w2 = weight.detach().reshape(weight.shape[0], Co).contiguous().float()
+        Cin, Co = weight.shape[0], weight.shape[1]
+        w2 = weight.detach().reshape(Cin, Co).float()
+        if x.shape[3] != Cin:                       # stored channels are padded to a multiple of 8
+            w2 = torch.cat((w2, w2.new_zeros(x.shape[3] - Cin, Co)))
+        w2 = w2.contiguous()
         y = ops.rgb_head_fwd(x, w2, Co)
         ctx.save_for_backward(x, y, w2)
         ctx.wshape = weight.shape
@@ -213,7 +216,7 @@ class RgbHead(Function):
     def backward(ctx, dy):
         x, y, w2 = ctx.saved_tensors
         dx, dw = ops.rgb_head_bwd(dy.float(), y, x, w2, w2.shape[1])
-        return dx, dw.view(ctx.wshape)
+        return dx, dw[:ctx.wshape[0]].reshape(ctx.wshape)
 
 
 class SumSqInterior(Function):
@@ -230,3 +233,66 @@ class SumSqInterior(Function):
         (x,) = ctx.saved_tensors
         scale = (dout.float() * 2.0).reshape(())
         return ops.scale_interior(x, scale.contiguous(), ctx.pad), None
+
+
+class ConcatChannels(Function):
+    """torch.cat([x, v.expand(H, W)], dim=1) of the reference's decoders (blocks.py:198-205 DecResnetBlock,
+    networks.py:320-332 DecoderConcat) on NHWC bf16: x [N,H,W,Cs] holds Cx logical channels, v [N,Cv]
+    fp32 is broadcast over the plane into channels Cx..Cx+Cv-1; the result is padded by `out_pad`
+    (reflection border) for a following 3x3 convolution.  Layout glue: torch copies, no arithmetic."""
+
+    @staticmethod
+    def forward(ctx, x, v, Cx, out_pad):
+        N, H, W, Cs = x.shape
+        Cv = v.shape[1]
+        Ct = ops.cs(Cx + Cv)
+        out = ops.empty_act(N, H + 2 * out_pad, W + 2 * out_pad, Ct, x.device)
+        inner = out[:, out_pad:out_pad + H, out_pad:out_pad + W, :]
+        inner[..., :Cx] = x[..., :Cx]
+        inner[..., Cx:Cx + Cv] = v.to(torch.bfloat16)[:, None, None, :]
+        if Ct > Cx + Cv:
+            inner[..., Cx + Cv:] = 0
+        ops.reflect_border_(out, out_pad)
+        ctx.meta = (Cx, Cv, Cs, out_pad)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        Cx, Cv, Cs, op = ctx.meta
+        g = ops.reflect_fold(_c(dout), op)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if Cs == Cx:
+                dx = g[..., :Cx].contiguous()
+            else:
+                dx = torch.zeros(g.shape[:3] + (Cs,), dtype=g.dtype, device=g.device)
+                dx[..., :Cx] = g[..., :Cx]
+        dv = g[..., Cx:Cx + Cv].float().sum(dim=(1, 2)) if ctx.needs_input_grad[1] else None
+        return dx, dv, None, None
+
+
+class ResidualPad(Function):
+    """out = x + y written into a buffer padded by `out_pad`; x is padded by x_pad, y dense
+    (the `out += residual` of DecResnetBlock, blocks.py:206)."""
+
+    @staticmethod
+    def forward(ctx, x, y, x_pad, out_pad):
+        out = ops.affine_act_fwd(y, None, act=None, res_pad=x, res_p=x_pad, out_p=out_pad)
+        ops.reflect_border_(out, out_pad)
+        ctx.meta = (x_pad, out_pad, x.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x_pad, op, xshape = ctx.meta
+        G = ops.reflect_fold(_c(dout), op)
+        if G is dout:
+            G = G.clone()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if x_pad:
+                dx = torch.zeros(xshape, dtype=G.dtype, device=G.device)
+                ops.add_interior_(dx, G, x_pad)
+            else:
+                dx = G
+        return dx, G, None, None

@@ -26,30 +26,30 @@ def _bce(x, target):
 
 
 class AdaINModel(Model):
+    reparam = True      # ReparameterizedStyleEncoder: Es returns (z, mu, logvar)
+
     def __init__(self, args):
         super().__init__(args)
         self.latent_dim = args.latent_dim
-        for flag, why in (('ms_dis', 'MultiScaleDiscriminator'), ('use_ragan', 'relativistic GAN'),
-                          ('dis_sn', 'spectral norm'), ('use_dropout', 'dropout')):
+        for flag, why in (('use_ragan', 'relativistic GAN'), ('dis_sn', 'spectral norm'),
+                          ('use_dropout', 'dropout')):
             if getattr(args, flag, False):
                 raise NotImplementedError(f"--{flag} ({why}) is outside the accelerated path (SURVEY.md §8f)")
         if getattr(args, 'vgg_loss', None) is not None:
             raise NotImplementedError("VGG perceptual loss needs downloaded weights; not on the accelerated path")
         m = self.model
         m.content_encoder = networks.ContentEncoder(args.input_dim, dim=args.dim, norm_layer=args.enc_norm)
-        # --concat / --reparam are ignored exactly as in the reference (adain_model.py:17-22)
-        m.style_encoder = networks.ReparameterizedStyleEncoder(
-            args.input_dim, output_dim=self.latent_dim, dim=args.dim, num_domains=args.num_domains,
-            norm_layer=None, activation='lrelu')
-        m.decoder = networks.AdaINDecoder(args.input_dim, dim=m.content_encoder.output_dim,
-                                          num_domains=args.num_domains, latent_dim=self.latent_dim,
-                                          up_type=args.up_type, norm_layer=args.dec_norm,
-                                          dropout=args.use_dropout)
+        self._build_generator(args)
         if 'train' in args.mode:
             for name in ('discriminator1', 'discriminator2'):
-                m[name] = networks.Discriminator(args.input_dim, dim=args.dim, norm_layer=args.dis_norm,
-                                                 sn=args.dis_sn, num_domains=args.num_domains,
-                                                 image_size=args.crop_size)
+                if args.ms_dis:       # dim is NOT forwarded by the reference (adain_model.py:33-42)
+                    m[name] = networks.MultiScaleDiscriminator(args.input_dim, norm_layer=args.dis_norm,
+                                                               sn=args.dis_sn, num_domains=args.num_domains,
+                                                               num_scales=args.num_scales)
+                else:
+                    m[name] = networks.Discriminator(args.input_dim, dim=args.dim, norm_layer=args.dis_norm,
+                                                     sn=args.dis_sn, num_domains=args.num_domains,
+                                                     image_size=args.crop_size)
             for net in list(m):
                 self.optimizer[net] = FlatAdam(m[net].parameters(), lr=args.lr,
                                                betas=(args.beta1, float(args.beta2)), weight_decay=args.wd)
@@ -62,6 +62,17 @@ class AdaINModel(Model):
             if args.gan_mode not in ('vanilla', 'lsgan', 'wgangp', 'hinge'):
                 raise NotImplementedError(f'Loss {args.gan_mode} is not implemented')
             self.print_loss = ['g_adv', 'g_cls', 'l1_cc_rec']
+
+    def _build_generator(self, args):
+        m = self.model
+        # --concat / --reparam are ignored exactly as in the reference (adain_model.py:17-22)
+        m.style_encoder = networks.ReparameterizedStyleEncoder(
+            args.input_dim, output_dim=self.latent_dim, dim=args.dim, num_domains=args.num_domains,
+            norm_layer=None, activation='lrelu')
+        m.decoder = networks.AdaINDecoder(args.input_dim, dim=m.content_encoder.output_dim,
+                                          num_domains=args.num_domains, latent_dim=self.latent_dim,
+                                          up_type=args.up_type, norm_layer=args.dec_norm,
+                                          dropout=args.use_dropout)
 
     # ------------------------------------------------------------------ small pieces
     def gan_loss(self, pred, is_real):
@@ -85,7 +96,9 @@ class AdaINModel(Model):
         return self.model.content_encoder.run(img, self.rng)
 
     def Es(self, img, c):
-        return self.model.style_encoder.run(img, c, self.rng)
+        """-> (z_s, mu, logvar); mu / logvar are None for the plain StyleEncoder (BaseModel w/o --reparam)"""
+        out = self.model.style_encoder.run(img, c, self.rng)
+        return out if self.reparam else (out, None, None)
 
     def G(self, z_c, z_s, c):
         return self.model.decoder.run(z_c, z_s, c)
@@ -164,16 +177,40 @@ class AdaINModel(Model):
 
     def backward_discriminator(self, netD, real, fake, c_org):
         n = real.shape[0]
-        pred, pred_cls = netD.run(torch.cat((fake.detach(), real)))
-        pred_fake, pred_real = pred[:n], pred[n:]
-        if 'hinge' in self.args.gan_mode:
-            loss_d_adv = F.relu(1.0 - pred_real).mean() + F.relu(1.0 + pred_fake).mean()
+        both = torch.cat((fake.detach(), real))
+        if self.args.ms_dis:           # backward_multi_scale_discriminator (:182-199)
+            loss_d_adv, loss_d_cls = 0, 0
+            for pred, pred_cls in netD.run(both):
+                loss_d_adv = loss_d_adv + self.gan_loss(pred[:n], 0) + self.gan_loss(pred[n:], 1)
+                loss_d_cls = loss_d_cls + _bce(pred_cls[n:], c_org)
         else:
-            loss_d_adv = self.gan_loss(pred_fake, 0) + self.gan_loss(pred_real, 1)
-        loss_d_cls = _bce(pred_cls[n:], c_org)
+            pred, pred_cls = netD.run(both)
+            pred_fake, pred_real = pred[:n], pred[n:]
+            if 'hinge' in self.args.gan_mode:
+                loss_d_adv = F.relu(1.0 - pred_real).mean() + F.relu(1.0 + pred_fake).mean()
+            else:
+                loss_d_adv = self.gan_loss(pred_fake, 0) + self.gan_loss(pred_real, 1)
+            loss_d_cls = _bce(pred_cls[n:], c_org)
         loss_d = loss_d_adv + self.args.lambda_cls * loss_d_cls
         loss_d.backward()
         self._scalars.update(d_adv=loss_d_adv.detach(), d_cls=loss_d_cls.detach(), d_total=loss_d.detach())
+
+    # ------------------------------------------------------------------ content discriminator (:136-144)
+    def update_content_discriminator(self, img, c_org):
+        with torch.no_grad():
+            z_c = self.Ec(img)
+        opt = self.optimizer.content_discriminator
+        opt.zero_grad()
+        loss_d_content = _bce(self.model.content_discriminator.run(z_c), c_org)
+        loss_d_content.backward()
+        self._scalars.update(loss_dc=loss_d_content.detach())
+        if self.dp is not None:
+            self.dp.allreduce([opt])
+        # nn.utils.clip_grad_norm_(params, 5) on the flat bucket (after the all-reduce: a global norm)
+        bucket = opt.grad_bucket
+        total_norm = torch.linalg.vector_norm(bucket) * opt.grad_scale
+        bucket.mul_(torch.clamp(5.0 / (total_norm + 1e-6), max=1.0))
+        opt.step()
 
     # ------------------------------------------------------------------ phases G1 / G2 (:225-394)
     def update_generator(self, img, c_org):
@@ -187,6 +224,12 @@ class AdaINModel(Model):
         self._step('content_encoder', 'decoder')
 
     def _g_adv(self, netD, fake, c_org):
+        if self.args.ms_dis:
+            adv, cls = 0, 0
+            for pred_fake, pred_fake_cls in netD.run(fake):
+                adv = adv + self.gan_loss(pred_fake, 1)
+                cls = cls + _bce(pred_fake_cls, c_org)
+            return adv, cls * self.args.lambda_cls_G
         pred_fake, pred_fake_cls = netD.run(fake)
         adv = -pred_fake.mean() if 'hinge' in self.args.gan_mode else self.gan_loss(pred_fake, 1)
         return adv, _bce(pred_fake_cls, c_org) * self.args.lambda_cls_G
@@ -210,6 +253,10 @@ class AdaINModel(Model):
         z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B, dim=0)
         img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
                            torch.cat((cls_a, cls_b)))
+        loss_g_content = None
+        if self.args.use_dis_content:          # backward_content_discriminator (:334-337)
+            with self._frozen('content_discriminator'):
+                loss_g_content = _bce(self.model.content_discriminator.run(z_c), 1 - c_org)
         with self._frozen('discriminator1'):
             loss_g_adv, loss_g_cls = self._g_adv(self.model.discriminator1, img_fake, c_org)
         loss_g_self = F.l1_loss(img_self, img) * self.args.lambda_rec
@@ -219,9 +266,15 @@ class AdaINModel(Model):
         loss_kl_zc = Fn.SumSqInterior.apply(z_c, CONTENT_PAD) / n_zc * 0.01
         # SUM over the batch, not a mean (:313-314): under data parallelism it must add up over
         # ranks while the gradient all-reduce averages -> pre-scale by the world size.
-        loss_kl_zs = torch.sum(1 + logvar - mu.pow(2) - logvar.exp()) * (-0.5) * 0.01
+        if self.reparam:
+            loss_kl_zs = torch.sum(1 + logvar - mu.pow(2) - logvar.exp()) * (-0.5) * 0.01
+        else:                                  # base_model.py:346-347: a mean, no world scaling
+            loss_kl_zs = torch.mean(z_s.pow(2)) * 0.01
         loss_g = loss_g_adv + loss_g_cls + loss_g_self + loss_g_cc + loss_kl_zc + loss_kl_zs
-        (loss_g + (world - 1) * loss_kl_zs if world > 1 else loss_g).backward()
+        if loss_g_content is not None:
+            loss_g = loss_g + loss_g_content
+            self._scalars.update(g_content=loss_g_content.detach())
+        (loss_g + (world - 1) * loss_kl_zs if (world > 1 and self.reparam) else loss_g).backward()
         self._scalars.update(g_adv=loss_g_adv.detach(), g_cls=loss_g_cls.detach(),
                              kl_zc=loss_kl_zc.detach(), kl_zs=loss_kl_zs.detach(),
                              l1_self_rec=loss_g_self.detach(), l1_cc_rec=loss_g_cc.detach(),
@@ -233,24 +286,35 @@ class AdaINModel(Model):
         z_ca, z_cb = torch.split(self.Ec(img), B, dim=0)
         z_sr = self.get_z_random(B, self.args.latent_dim)
         img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
-        with self._frozen('discriminator2', 'style_encoder'):
-            loss_g_adv2, loss_g_cls2 = self._g_adv(self.model.discriminator2, img_random, c_org)
-            _, mu2, _ = self.Es(img_random, c_org)
-        mu2_a, mu2_b = torch.split(mu2, B, dim=0)
-        loss_z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
+        # the reference scores img_random with discriminator1 under --ms_dis (:361) and with
+        # discriminator2 otherwise (:378)
+        dname = 'discriminator1' if self.args.ms_dis else 'discriminator2'
+        with self._frozen(dname, 'style_encoder'):
+            loss_g_adv2, loss_g_cls2 = self._g_adv(self.model[dname], img_random, c_org)
+            z_sr_rec, mu2, _ = self.Es(img_random, c_org)
+        if self.reparam:
+            mu2_a, mu2_b = torch.split(mu2, B, dim=0)
+            loss_z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
+        else:                                  # base_model.py:417-420 uses z_sr_a twice
+            z_sr_a, _ = torch.split(z_sr_rec, B, dim=0)
+            loss_z_l1 = (F.l1_loss(z_sr_a, z_sr) + F.l1_loss(z_sr_a, z_sr)) * 10
         (loss_z_l1 + loss_g_adv2 + loss_g_cls2).backward()
         self._scalars.update(l1_recon_z=loss_z_l1.detach(), gan2=loss_g_adv2.detach(),
                              gan2_cls=loss_g_cls2.detach())
 
     # ------------------------------------------------------------------ the iteration (:421-430)
     def optimize_parameters(self, global_iter):
-        if self.args.use_dis_content:
-            raise NotImplementedError("--use_dis_content is the next row of the scope table (SURVEY.md §8f-1)")
-        self._run_iteration(self._iteration)
+        if self.args.use_dis_content and global_iter % self.args.d_iter != 0:
+            self._run_iteration(self._content_iteration, 'content')
+        else:
+            self._run_iteration(self._iteration, 'main')
 
     def _iteration(self):
         self.update_discriminator(self.img, self.c_org)
         self.update_generator(self.img, self.c_org)
+
+    def _content_iteration(self):
+        self.update_content_discriminator(self.img, self.c_org)
 
     def compute_visuals(self):
         B = self.args.batch_size

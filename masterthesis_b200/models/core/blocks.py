@@ -351,3 +351,45 @@ class AdaINResnetBlock(nn.Module):
 
     def forward(self, x, z):
         return from_padded(self.run(to_padded(x, 1), z, out_pad=0), self.conv2.conv.out_channels)
+
+
+class DecResnetBlock(nn.Module):
+    """conv3 -> IN -> cat(z) -> 1x1+ReLU -> 1x1+ReLU -> conv3 -> IN -> cat(z) -> 1x1+ReLU -> 1x1+ReLU
+    -> + x   (reference blocks.py:169-208, the residual block of BaseModel's default Decoder)."""
+
+    def __init__(self, n_channel: int, add_channel: int, norm_layer: str = 'instance',
+                 padding_type: str = 'reflect', stride: int = 1, dropout: bool = False):
+        super().__init__()
+        self.conv1 = ConvBlock(n_channel, n_channel, 3, stride=stride, padding=1, padding_type=padding_type)
+        self.conv2 = ConvBlock(n_channel, n_channel, 3, stride=stride, padding=1, padding_type=padding_type)
+        self.norm = get_norm_layer(norm_layer)(n_channel)
+        c = n_channel + add_channel
+        self.block1 = nn.Sequential(Conv2d(c, c, 1, stride, 0), nn.ReLU(), Conv2d(c, n_channel, 1, 1, 0), nn.ReLU())
+        self.block2 = nn.Sequential(Conv2d(c, c, 1, 1, 0), nn.ReLU(), Conv2d(c, n_channel, 1, 1, 0), nn.ReLU())
+        self.dropout = nn.Dropout(0.5) if dropout else nn.Identity()
+        self._dropout, self._stride = dropout, stride
+        self.n_channel = n_channel
+
+    def _half(self, x, z, conv, block, out_pad):
+        c = conv.conv
+        wf, wb = c.packed()
+        h = Fn.ConvNormAct.apply(x, c.weight, c.bias, wf, wb, c.geom(), 'instance', None, None, None, 0, None)
+        h = Fn.ConcatChannels.apply(h, z, self.n_channel, 0)
+        for i, pad in ((0, 0), (2, out_pad)):
+            m = block[i]
+            wf, wb = m.packed()
+            h = Fn.ConvAct.apply(h, m.weight, m.bias, wf, wb, m.geom(), 'relu', pad)
+        return h
+
+    def run(self, x, z, out_pad=1):
+        """x padded by 1; z [N, add_channel] fp32.  Returns x + block(x, z) padded by out_pad."""
+        if self._dropout:
+            raise NotImplementedError("--use_dropout is outside the accelerated path (SURVEY.md 8f-4)")
+        if self._stride != 1 or not isinstance(self.norm, nn.InstanceNorm2d) or self.conv1.rpad != 1:
+            raise NotImplementedError("DecResnetBlock is accelerated for stride 1, instance norm, reflect padding")
+        h = self._half(x, z, self.conv1, self.block1, 1)
+        h = self._half(h, z, self.conv2, self.block2, 0)
+        return Fn.ResidualPad.apply(x, h, 1, out_pad)
+
+    def forward(self, x, z):
+        return from_padded(self.run(to_padded(x, 1), z, out_pad=0), self.n_channel)

@@ -11,7 +11,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from ... import functional as Fn
-from .blocks import (AdaINResnetBlock, Conv2d, ConvBlock, DownResnetBlock, ResnetBlock,
+from .blocks import (AdaINResnetBlock, Conv2d, ConvBlock, DecResnetBlock, DownResnetBlock, ResnetBlock,
                      UpsampleBlock, from_padded, to_padded)
 from .functions import get_activation_layer, get_norm_layer
 from .misc import GaussianNoiseLayer
@@ -58,6 +58,43 @@ class ContentEncoder(nn.Module):
 
     def forward(self, x):
         return from_padded(self.run(x), self.output_dim, CONTENT_PAD)
+
+
+class StyleEncoder(nn.Module):
+    """cat(x, one-hot maps) -> 7x7 conv + act -> num_downs x (4x4 s2 conv + act) -> GAP -> 1x1 conv
+    (reference networks.py:45-85; BaseModel without --reparam).  All ConvBlocks are bias-free."""
+
+    def __init__(self, input_dim: int, output_dim: int = 8, dim: int = 64, num_downs: int = 4,
+                 num_domains: int = 2, padding_type: str = 'reflect', activation: str = 'relu'):
+        super().__init__()
+        layers = [ConvBlock(input_dim + num_domains, dim, 7, 1, padding=3, padding_type=padding_type,
+                            activation=activation)]
+        max_filter_size = 256
+        out_dim = dim
+        for _ in range(num_downs):
+            in_dim = min(max_filter_size, dim)
+            out_dim = min(max_filter_size, dim * 2)
+            layers.append(ConvBlock(in_dim, out_dim, 4, 2, padding=1, padding_type=padding_type,
+                                    activation=activation))
+            dim *= 2
+        layers.append(nn.AdaptiveAvgPool2d(1))
+        layers.append(Conv2d(out_dim, output_dim, 1, 1, 0))
+        layers[0].stem = True
+        self.model = nn.Sequential(*layers)
+        self.num_downs, self.out_nch = num_downs, out_dim
+
+    def run(self, img, c, rng=None):
+        if self.model[0].rpad != 3:
+            raise NotImplementedError("StyleEncoder is accelerated for reflect padding")
+        x = to_padded(img, 3, onehot=c)
+        for i in range(1 + self.num_downs):
+            x = self.model[i].run(x, out_pad=0 if i == self.num_downs else 1)
+        feat = Fn.GlobalAvgPool.apply(x)[:, :self.out_nch]
+        head = self.model[-1]
+        return F.linear(feat, head.weight.flatten(1), head.bias)
+
+    def forward(self, x, c):
+        return self.run(x, c)
 
 
 class ReparameterizedStyleEncoder(nn.Module):
@@ -164,6 +201,168 @@ class AdaINDecoder(nn.Module):
 
     def forward(self, x, z, c):
         return self.run(to_padded(x, CONTENT_PAD), z, c)
+
+
+def _run_ups(dec2, out):
+    for up in dec2:
+        out = up.run(out)
+    return out
+
+
+def _make_ups(dim, output_dim, num_ups, up_type, norm_layer, activation, bias):
+    ups = []
+    for _ in range(num_ups):
+        ups.append(UpsampleBlock(dim, dim // 2, 3, 2, 1, 1, norm_layer=norm_layer, activation=activation,
+                                 up_type=up_type, bias=bias))
+        dim = dim // 2
+    if 'transpose' in up_type:
+        ups.append(UpsampleBlock(dim, output_dim, 1, 1, 0, activation='tanh', up_type='transpose'))
+    else:
+        ups.append(ConvBlock(dim, output_dim, 7, 1, 3, activation='tanh'))
+    return nn.Sequential(*ups)
+
+
+class Decoder(nn.Module):
+    """style MLP -> n_blocks x DecResnetBlock (one 256-slice of the MLP output each) -> the same
+    up-sampling tail as AdaINDecoder   (reference networks.py:148-205; BaseModel's default decoder)."""
+
+    def __init__(self, output_dim: int, dim: int = 256, n_blocks: int = 4, num_domains: int = 2,
+                 num_ups: int = 2, latent_dim: int = 8, up_type: str = 'transpose', dropout: bool = False,
+                 norm_layer: str = 'layer', activation: str = 'relu', bias: bool = True):
+        super().__init__()
+        self.dim_add = dim
+        self.dec1 = nn.ModuleList([DecResnetBlock(dim, self.dim_add, dropout=dropout) for _ in range(n_blocks)])
+        self.dec2 = _make_ups(dim, output_dim, num_ups, up_type, norm_layer, activation, bias)
+        self.linear = nn.Sequential(nn.Linear(latent_dim + num_domains, 256), nn.ReLU(inplace=True),
+                                    nn.Linear(256, 256), nn.ReLU(inplace=True),
+                                    nn.Linear(256, self.dim_add * n_blocks))
+
+    def run(self, z_c, z, c):
+        s = self.linear(torch.cat([c, z], 1))
+        out = z_c
+        n = len(self.dec1)
+        for i, (dec, zi) in enumerate(zip(self.dec1, torch.split(s, self.dim_add, dim=1))):
+            out = dec.run(out, zi.contiguous(), out_pad=0 if i == n - 1 else 1)
+        if n == 0:
+            out = out[:, CONTENT_PAD:-CONTENT_PAD, CONTENT_PAD:-CONTENT_PAD, :].contiguous()
+        return _run_ups(self.dec2, out)
+
+    def forward(self, x, z, c):
+        return self.run(to_padded(x, CONTENT_PAD), z, c)
+
+
+class DecoderConcat(nn.Module):
+    """ResnetBlock -> cat(c, z maps) -> n_blocks x ResnetBlock -> cat z -> ConvT+LN+ReLU -> cat z ->
+    ConvT+LN+ReLU -> cat z -> ConvT 1x1 + tanh   (reference networks.py:272-333; BaseModel --concat).
+    The odd channel counts (268/276/138/146/73/81 at latent 8, 4 domains) are stored rounded up to 8."""
+
+    def __init__(self, output_dim: int, dim: int = 256, n_blocks: int = 3, num_domains: int = 2,
+                 latent_dim: int = 8, up_type: str = 'transpose', dropout: bool = False,
+                 norm_layer: str = 'layer', activation: str = 'relu', bias: bool = True):
+        super().__init__()
+        self.dec_share = ResnetBlock(dim, dim)
+        nch = dim + latent_dim + num_domains
+        self.dec1 = nn.Sequential(*[ResnetBlock(nch, nch, dropout=dropout) for _ in range(n_blocks)])
+        self._c0, self._c1 = dim, nch
+        nch = nch + latent_dim
+        self.dec2 = UpsampleBlock(nch, nch // 2, 3, 2, 1, 1, norm_layer=norm_layer, activation=activation,
+                                  up_type=up_type, bias=bias)
+        nch = nch // 2
+        self._c2 = nch
+        nch = nch + latent_dim
+        self.dec3 = UpsampleBlock(nch, nch // 2, 3, 2, 1, 1, norm_layer=norm_layer, activation=activation,
+                                  up_type=up_type, bias=bias)
+        nch = nch // 2
+        self._c3 = nch
+        nch = nch + latent_dim
+        if 'transpose' in up_type:
+            self.dec4 = UpsampleBlock(nch, output_dim, 1, 1, 0, activation='tanh', up_type='transpose')
+        else:
+            self.dec4 = ConvBlock(nch, output_dim, 7, 1, 3, activation='tanh')
+
+    def run(self, z_c, z, c):
+        n = len(self.dec1)
+        out = self.dec_share.run(z_c, out_pad=0)
+        out = Fn.ConcatChannels.apply(out, torch.cat([c, z], 1), self._c0, 1 if n else 0)
+        for i, blk in enumerate(self.dec1):
+            out = blk.run(out, out_pad=0 if i == n - 1 else 1)
+        out = self.dec2.run(Fn.ConcatChannels.apply(out, z, self._c1, 0))
+        out = self.dec3.run(Fn.ConcatChannels.apply(out, z, self._c2, 0))
+        return self.dec4.run(Fn.ConcatChannels.apply(out, z, self._c3, 0))
+
+    def forward(self, x, z, c):
+        return self.run(to_padded(x, CONTENT_PAD), z, c)
+
+
+class ContentDiscriminator(nn.Module):
+    """3 x (refl1 -> 7x7 s2 conv + IN + LReLU) -> 4x4 conv + LReLU -> 1x1 conv -> GAP: domain logits of a
+    content code   (reference networks.py:386-419, --use_dis_content)."""
+
+    def __init__(self, dim: int = 256, num_domains: int = 3, norm_layer: str = 'instance',
+                 activation: str = 'lrelu', padding_type: str = 'reflect', bias: bool = True):
+        super().__init__()
+        layers = [ConvBlock(dim, dim, kernel_size=7, stride=2, padding=1, padding_type=padding_type,
+                            norm_layer=norm_layer, activation=activation, bias=bias) for _ in range(3)]
+        layers.append(ConvBlock(dim, dim, kernel_size=4, stride=1, padding=0, padding_type=padding_type,
+                                activation=activation, bias=bias))
+        layers.append(Conv2d(dim, num_domains, 1, 1, 0))
+        self.model = nn.Sequential(*layers)
+        self.pool = nn.AdaptiveAvgPool2d(1)
+        self.dim = dim
+
+    def run(self, z_c):
+        """z_c: padded NHWC bf16 content code (CONTENT_PAD = the reflection pad of the first conv)."""
+        x = z_c
+        for i in range(4):
+            x = self.model[i].run(x, out_pad=1 if i < 2 else 0)
+        feat = Fn.GlobalAvgPool.apply(x)[:, :self.dim]     # GAP commutes with the 1x1 conv + bias
+        head = self.model[4]
+        return F.linear(feat, head.weight.flatten(1), head.bias)
+
+    def forward(self, x):
+        return self.run(to_padded(x, CONTENT_PAD))
+
+
+class MultiScaleDiscriminator(nn.Module):
+    """n_layers x (4x4 s2 zero-padded conv + LReLU) applied at num_scales image scales (AvgPool2d(3,2,1,
+    count_include_pad=False) between them), heads `dis` (1x1 -> 1) and `cls` (1x1 -> nd, GAP)
+    (reference networks.py:421-466, --ms_dis)."""
+
+    def __init__(self, input_dim: int, dim: int = 64, n_layers: int = 6, num_domains: int = 2,
+                 norm_layer: str = None, activation: str = 'lrelu', padding_type: str = None,
+                 num_scales: int = 3, sn: bool = False):
+        super().__init__()
+        self.num_scales = num_scales
+        self.downsample = nn.AvgPool2d(3, stride=2, padding=[1, 1], count_include_pad=False)
+        layers = [ConvBlock(input_dim, dim, 4, 2, 1, norm_layer=None, activation=activation,
+                            padding_type=padding_type, sn=sn)]
+        for _ in range(n_layers - 1):
+            layers.append(ConvBlock(dim, dim * 2, 4, 2, 1, norm_layer=norm_layer, activation=activation,
+                                    padding_type=padding_type, sn=sn))
+            dim *= 2
+        self.model = nn.Sequential(*layers)
+        self.dis = Conv2d(dim, 1, 1, 1, 0)
+        self.cls = Conv2d(dim, num_domains, 1, 1, 0)
+        self.pool = nn.AdaptiveAvgPool2d(1)
+        self.output_dim = dim
+
+    def run(self, img):
+        outputs = []
+        x = img
+        for _ in range(self.num_scales):
+            h = to_padded(x, self.model[0].rpad)
+            n = len(self.model)
+            for i, blk in enumerate(self.model):
+                h = blk.run(h, out_pad=0 if i == n - 1 else self.model[i + 1].rpad)
+            hf = h.float()[..., :self.output_dim]
+            dis = torch.einsum('nhwc,c->nhw', hf, self.dis.weight[0, :, 0, 0]).unsqueeze(1) + self.dis.bias.view(1, 1, 1, 1)
+            cls = F.linear(hf.mean(dim=(1, 2)), self.cls.weight.flatten(1), self.cls.bias)
+            outputs.append((dis, cls))
+            x = self.downsample(x)
+        return outputs
+
+    def forward(self, x):
+        return self.run(x)
 
 
 class Discriminator(nn.Module):

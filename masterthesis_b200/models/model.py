@@ -53,8 +53,8 @@ class Model(ABC, nn.Module):
         # draws (self.rng, parity tests) always run eagerly.
         self.use_graph = bool(getattr(args, 'cuda_graph', True)) and os.environ.get('MT_CUDA_GRAPH', '1') != '0'
         self.graph_warmup = 2    # eager iterations before capture (lazy init, allocator warm-up)
-        self._graph = None
-        self._eager_iters = 0
+        self._graphs = {}        # iteration kind ('main' / 'content') -> captured graph record
+        self._eager_iters = {}
         self._scalars = {}
 
     @abstractmethod
@@ -68,8 +68,13 @@ class Model(ABC, nn.Module):
     # ------------------------------------------------------------------ iteration driver
     def reset_graph(self):
         """forget the captured iteration (call after changing loss weights, batch shape, ...)"""
-        self._graph = None
-        self._eager_iters = 0
+        self._graphs = {}
+        self._eager_iters = {}
+
+    @property
+    def _graph(self):
+        """the captured main iteration (None while running eagerly)"""
+        return self._graphs.get('main')
 
     def _static_inputs(self, x1, y1, x2, y2):
         """Keep the stacked batch in persistent device buffers (a captured iteration reads them in
@@ -92,7 +97,7 @@ class Model(ABC, nn.Module):
         keys = list(self._scalars)
         return keys, torch.stack([self._scalars[k].float().reshape(()) for k in keys])
 
-    def _run_iteration(self, body):
+    def _run_iteration(self, body, kind='main'):
         """Run `body()` (enqueues one full training iteration and fills self._scalars with 0-dim
         device tensors) eagerly or as a CUDA-graph replay, then read all losses with ONE host sync."""
         from .. import ops
@@ -102,13 +107,13 @@ class Model(ABC, nn.Module):
             self._scalars = {}
             body()
             keys, vec = self._loss_vector()
-        elif self._graph is None and self._eager_iters < self.graph_warmup:
-            self._eager_iters += 1
+        elif kind not in self._graphs and self._eager_iters.get(kind, 0) < self.graph_warmup:
+            self._eager_iters[kind] = self._eager_iters.get(kind, 0) + 1
             self._scalars = {}
             body()
             keys, vec = self._loss_vector()
         else:
-            if self._graph is None:
+            if kind not in self._graphs:
                 blocks.invalidate_packs()
                 ctx = GraphHyper(self.device)
                 for opt in self.optimizer.values():
@@ -124,16 +129,19 @@ class Model(ABC, nn.Module):
                 finally:
                     for opt in self.optimizer.values():
                         opt.graph_ctx = None
-                self._graph = dict(graph=graph, ctx=ctx, keys=keys, vec=vec, launches=ops.launches() - l0)
+                self._graphs[kind] = dict(graph=graph, ctx=ctx, keys=keys, vec=vec, launches=ops.launches() - l0)
             else:
-                self._graph['ctx'].advance()
-                ops._count(self._graph['launches'])
-            g = self._graph
+                self._graphs[kind]['ctx'].advance()
+                ops._count(self._graphs[kind]['launches'])
+            g = self._graphs[kind]
             g['ctx'].upload()
             g['graph'].replay()
             keys, vec = g['keys'], g['vec']
         for k, v in zip(keys, vec.tolist()):     # the one host sync of the iteration
-            self.loss[k] = v
+            if k == 'loss_dc':                   # reference keeps it outside self.loss (adain_model.py:142)
+                self.loss_dc = v
+            else:
+                self.loss[k] = v
 
     # ------------------------------------------------------------------ lifecycle
     def initialize(self):

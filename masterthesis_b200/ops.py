@@ -319,11 +319,11 @@ def plane_stats(x):
 
 
 @_checked
-def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None):
+def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None, C_valid=None):
     N, C, _ = stats.shape
     ss = _T.empty_like(stats)
     mr = _T.empty_like(stats)
-    check(_lib.lib().mt_norm_finalize(_p(stats), NORM[mode], N, C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
+    check(_lib.lib().mt_norm_finalize(_p(stats), NORM[mode], N, C, C_valid or C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
                                       _p(ss), _p(mr), _stream()), "norm_finalize")
     _count()
     return ss, mr
@@ -341,7 +341,7 @@ def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, 
 
 
 @_checked
-def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None):
+def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None):
     """g, x dense [N,H,W,C].  Returns (dx, dgb | None, dln_w | None, dln_b | None)."""
     N, H, W, C = x.shape
     L = _lib.lib()
@@ -351,9 +351,9 @@ def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None):
                                _stream()), "norm_bwd_reduce")
     coef = _T.empty((N, C, 3), dtype=torch.float32, device=dev)
     dgb = _T.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
-    dlw = torch.zeros(C, dtype=torch.float32, device=dev) if (mode == "layer" and ln_w is not None) else None
-    dlb = torch.zeros(C, dtype=torch.float32, device=dev) if dlw is not None else None
-    check(L.mt_norm_bwd_finalize(_p(sums), _p(mr), NORM[mode], N, C, H * W, _p(gb), _p(ln_w), _p(coef),
+    dlw = torch.zeros(C_valid or C, dtype=torch.float32, device=dev) if (mode == "layer" and ln_w is not None) else None
+    dlb = torch.zeros(C_valid or C, dtype=torch.float32, device=dev) if dlw is not None else None
+    check(L.mt_norm_bwd_finalize(_p(sums), _p(mr), NORM[mode], N, C, C_valid or C, H * W, _p(gb), _p(ln_w), _p(coef),
                                  _p(dgb), _p(dlw), _p(dlb), _stream()), "norm_bwd_finalize")
     dx = _T.empty_like(x)
     check(L.mt_norm_bwd_apply(_p(g), _p(x), _p(ss), _p(coef), N, H * W, C, ACT[act], LRELU_SLOPE,

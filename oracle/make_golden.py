@@ -50,6 +50,8 @@ def patch_rng(models, draws):
     misc.GaussianNoiseLayer.forward = noise_forward
     networks.ReparameterizedStyleEncoder.reparameterize = reparameterize
     adain_model.AdaINModel.get_z_random = get_z_random
+    from models import base_model
+    base_model.BaseModel.get_z_random = get_z_random
 
 
 def nets_case(name, dim, size, N, nd=4, latent=8, seed=1, sub=1):
@@ -114,17 +116,91 @@ def nets_case(name, dim, size, N, nd=4, latent=8, seed=1, sub=1):
     print(name, 'draws', draws.log, {k: float(v.abs().max()) for k, v in out.items() if not k.startswith('grad')})
 
 
-def step_case(name, dim, size, B, iters=2, nd=4, seed=2):
-    """AdaINModel.optimize_parameters (default flags) — the 13 losses per iteration and a
-    checksum of every parameter tensor after `iters` iterations."""
+def nets_base_case(name, dim, size, N, nd=4, latent=8, seed=3, sub=1):
+    """The networks only BaseModel / the optional flags use, each on its own: StyleEncoder, Decoder,
+    DecoderConcat, ContentDiscriminator, MultiScaleDiscriminator (forward outputs, input gradients
+    and a few parameter gradients of a fixed linear functional)."""
+    from models.core import networks
+    torch.manual_seed(0)
+    C = dim * 4
+    Es = networks.StyleEncoder(3, latent, dim, num_domains=nd, activation='lrelu')
+    G1 = networks.Decoder(3, C, num_domains=nd, latent_dim=latent)
+    G2 = networks.DecoderConcat(3, C, num_domains=nd, latent_dim=latent)
+    Dc = networks.ContentDiscriminator(C, nd)
+    Dm = networks.MultiScaleDiscriminator(3, dim, num_domains=nd)
+    meta = {'dim': dim, 'size': size, 'N': N, 'nd': nd, 'latent': latent, 'seed': seed, 'sub': sub, 'shapes': {}}
+    named = (('style_encoder', Es), ('decoder', G1), ('decoder_concat', G2), ('content_discriminator', Dc),
+             ('ms_discriminator', Dm))
+    for n, net in named:
+        meta['shapes'][n] = load_synth(net, seed, n + '.')
+    s = sub
+    out = {}
+    c = synth.synth_onehot(N, nd, seed)
+    img = synth.synth_images(N, size, seed, 'img_se').requires_grad_(True)
+    z = Es(img, c)
+    (z * synth.synth_tensor('proj_se', z.shape, seed)).sum().backward()
+    out['se.z'], out['se.dimg'] = z.detach(), img.grad[:, :, ::s, ::s]
+    q = max(1, s // 4)
+    for tag, G in (('dec', G1), ('decc', G2)):
+        zc_in = synth.synth_tensor('zc_in', (N, C, size // 4, size // 4), seed) * (C * (size // 4) ** 2) ** 0.5
+        zc_in = zc_in.to(torch.bfloat16).float().requires_grad_(True)
+        zs_in = (synth.synth_tensor('zs_in', (N, latent), seed) * latent ** 0.5).requires_grad_(True)
+        if tag == 'dec':
+            # forward only: the reference's DecResnetBlock cannot be back-propagated (`out += residual`
+            # modifies the output of a ReLU in place, blocks.py:206; torch raises in backward)
+            with torch.no_grad():
+                out['dec.fake'] = G(zc_in, zs_in, c)[:, :, ::s, ::s]
+            continue
+        fake = G(zc_in, zs_in, c)
+        (fake * synth.synth_tensor('proj', fake.shape, seed)).sum().backward()
+        out[f'{tag}.fake'] = fake.detach()[:, :, ::s, ::s]
+        out[f'{tag}.dzc'], out[f'{tag}.dzs'] = zc_in.grad[:, :, ::q, ::q], zs_in.grad
+    zc2 = synth.synth_tensor('zc_dc', (N, C, 64, 64), seed) * (C * 64 * 64) ** 0.5
+    zc2 = zc2.to(torch.bfloat16).float().requires_grad_(True)
+    pred = Dc(zc2)
+    (pred * synth.synth_tensor('proj_dc', pred.shape, seed)).sum().backward()
+    out['dc.pred'], out['dc.dzc'] = pred.detach(), zc2.grad[:, :, ::4, ::4]
+    img4 = synth.synth_images(N, 256, seed, 'img_ms').requires_grad_(True)
+    tot = 0
+    for i, (dis, cls) in enumerate(Dm(img4)):
+        out[f'ms.dis{i}'], out[f'ms.cls{i}'] = dis.detach(), cls.detach()
+        tot = tot + (dis * synth.synth_tensor(f'proj_ms{i}', dis.shape, seed)).sum() + (cls * c).sum()
+    tot.backward()
+    out['ms.dimg'] = img4.grad[:, :, ::8, ::8]
+    keys = {'style_encoder': ['model.0.block.1.weight', 'model.3.block.1.weight', 'model.6.weight'],
+            'decoder': ['dec1.0.conv1.block.1.weight', 'dec1.1.block1.0.weight', 'dec1.3.block2.2.bias',
+                        'dec2.0.block.0.weight', 'linear.4.weight'],
+            'decoder_concat': ['dec_share.model.0.block.1.weight', 'dec1.1.model.1.block.1.weight',
+                               'dec2.block.0.weight', 'dec2.block.1.weight', 'dec3.block.1.bias', 'dec4.block.0.weight'],
+            'content_discriminator': ['model.0.block.1.weight', 'model.2.block.1.bias', 'model.3.block.1.weight',
+                                      'model.4.weight'],
+            'ms_discriminator': ['model.0.block.0.weight', 'model.4.block.0.weight', 'dis.weight', 'cls.bias']}
+    for n, net in named:
+        sd = dict(net.named_parameters())
+        for k in keys[n]:
+            g = sd[k].grad
+            if g is None:
+                continue
+            out[f'grad.{n}.{k}'] = g if g.numel() <= 20000 else g.flatten()[:: max(1, g.numel() // 20000)]
+    np.savez_compressed(os.path.join(OUT, name + '.npz'), meta=json.dumps(meta),
+                        **{k: v.numpy().astype(np.float32) for k, v in out.items()})
+    print(name, {k: float(v.abs().max()) for k, v in out.items() if not k.startswith('grad')})
+
+
+def step_case(name, dim, size, B, iters=2, nd=4, seed=2, model='AdaINModel', **flags):
+    """Model.optimize_parameters — the losses per iteration and a checksum of every parameter tensor
+    after `iters` iterations.  model / flags select BaseModel, --concat --reparam, --ms_dis,
+    --use_dis_content (losses of a content-discriminator iteration: `loss_dc` only)."""
     models = ref_import.import_reference()
     draws = synth.Draws(seed)
     patch_rng(models, draws)
-    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=B, num_domains=nd, init_type=None)
+    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=B, num_domains=nd, init_type=None,
+                                   **flags)
     torch.manual_seed(0)
-    m = models.AdaINModel(args)
+    m = getattr(models, model)(args)
     m.device = 'cpu'
-    meta = {'dim': dim, 'size': size, 'B': B, 'nd': nd, 'seed': seed, 'iters': iters, 'shapes': {}}
+    meta = {'dim': dim, 'size': size, 'B': B, 'nd': nd, 'seed': seed, 'iters': iters, 'shapes': {},
+            'model': model, 'flags': flags}
     for n in m.model:
         meta['shapes'][n] = load_synth(m.model[n], seed, n + '.')
     batch = {'x1': synth.synth_images(B, size, seed, 'x1'), 'x2': synth.synth_images(B, size, seed, 'x2'),
@@ -135,6 +211,8 @@ def step_case(name, dim, size, B, iters=2, nd=4, seed=2):
         m.optimize_parameters(it)
         for k, v in m.loss.items():
             out[f'loss.{it}.{k}'] = torch.tensor(v)
+        if getattr(m, 'loss_dc', None) is not None:
+            out[f'loss.{it}.loss_dc'] = torch.tensor(m.loss_dc)
     for n in m.model:
         for k, v in m.model[n].state_dict().items():
             v = v.detach().float()
@@ -150,6 +228,13 @@ if __name__ == '__main__':
     os.makedirs(OUT, exist_ok=True)
     ref_import.import_reference()
     torch.set_num_threads(os.cpu_count())
-    nets_case('nets_dim16_64', dim=16, size=64, N=2)
-    nets_case('nets_dim64_256', dim=64, size=256, N=1, sub=8)
-    step_case('step_dim8_64', dim=8, size=64, B=1)
+    which = sys.argv[1:] or ['adain', 'base']
+    if 'adain' in which:
+        nets_case('nets_dim16_64', dim=16, size=64, N=2)
+        nets_case('nets_dim64_256', dim=64, size=256, N=1, sub=8)
+        step_case('step_dim8_64', dim=8, size=64, B=1)
+    if 'base' in which:
+        nets_base_case('nets_base_dim16_64', dim=16, size=64, N=2)
+        step_case('step_basec_dim8_64', dim=8, size=64, B=1, model='BaseModel', concat=True)
+        step_case('step_basecr_dim8_64', dim=8, size=64, B=1, model='BaseModel', concat=True, reparam=True)
+        step_case('step_dcms_dim8_256', dim=8, size=256, B=1, iters=4, use_dis_content=True, ms_dis=True)

@@ -47,31 +47,52 @@ def bce_logits(x, target):
 
 
 class AdaINStep:
-    """State + one iteration of AdaINModel with default flags (no content-D, vanilla GAN, no VGG)."""
+    """State + one iteration of AdaINModel / BaseModel (vanilla GAN, no VGG).
+    model='adain': ReparameterizedStyleEncoder + AdaINDecoder (adain_model.py);
+    model='base' : StyleEncoder or (reparam) ReparameterizedStyleEncoder, Decoder or (concat)
+                   DecoderConcat (base_model.py).
+    ms_dis: MultiScaleDiscriminator; use_dis_content: ContentDiscriminator with the d_iter schedule."""
 
     def __init__(self, params, B, lr=1e-4, betas=(0.5, 0.999), wd=1e-4, lambda_rec=10.0,
-                 lambda_cls=1.0, lambda_cls_G=5.0, latent_dim=8):
+                 lambda_cls=1.0, lambda_cls_G=5.0, latent_dim=8, model='adain', reparam=True,
+                 concat=False, ms_dis=False, use_dis_content=False, d_iter=3):
         self.P = {n: {k: v.detach().clone().requires_grad_(True) for k, v in params[n].items()}
                   for n in params}
-        self.opt = {n: Adam(self.P[n], lr, betas, wd) for n in self.P}
+        self.opt = {n: Adam(self.P[n], lr / 2.5 if n == 'content_discriminator' else lr, betas, wd)
+                    for n in self.P}
+        self.model, self.concat, self.ms_dis = model, concat, ms_dis
+        self.reparam = True if model == 'adain' else reparam
+        self.use_dis_content, self.d_iter, self.it = use_dis_content, d_iter, 0
+        self.loss_dc = None
         self.B, self.latent = B, latent_dim
         self.lrec, self.lcls, self.lclsg = lambda_rec, lambda_cls, lambda_cls_G
         self.loss = {}
 
     # -- networks -------------------------------------------------------------------------
     def Ec(self, x, draw):
-        n = draw((x.size(0), 256, x.size(2) // 4, x.size(3) // 4)) if draw else None
+        C = self.P['content_encoder']['model.3.model.0.block.1.weight'].shape[0]
+        n = draw((x.size(0), C, x.size(2) // 4, x.size(3) // 4)) if draw else None
         return nets.content_encoder(self.P['content_encoder'], x, n)
 
     def Es(self, x, c, draw):
+        """-> (z, mu, logvar); mu = logvar = None for the plain StyleEncoder"""
+        if not self.reparam:
+            return nets.style_encoder_plain(self.P['style_encoder'], x, c), None, None
         eps = draw((x.size(0), self.latent))
         return nets.style_encoder_reparam(self.P['style_encoder'], x, c, eps)
 
     def G(self, zc, zs, c):
-        return nets.adain_decoder(self.P['decoder'], zc, zs, c)
+        if self.model == 'adain':
+            return nets.adain_decoder(self.P['decoder'], zc, zs, c)
+        if self.concat:
+            return nets.decoder_concat(self.P['decoder'], zc, zs, c)
+        return nets.decoder(self.P['decoder'], zc, zs, c)
 
     def D(self, which, x):
-        return nets.discriminator(self.P[which], x)
+        """-> list of (real/fake map, class logits), one entry per scale"""
+        if self.ms_dis:
+            return nets.ms_discriminator(self.P[which], x)
+        return [nets.discriminator(self.P[which], x)]
 
     # -- phases (adain_model.py:146-180, 225-239, 241-394) ----------------------------------
     def update_discriminator(self, img, c_org, draw):
@@ -90,10 +111,10 @@ class AdaINStep:
             img_random = torch.cat((img_br, img_ar))
         for which, fake in (('discriminator1', img_fake), ('discriminator2', img_random)):
             self.opt[which].zero_grad()
-            pred_fake, _ = self.D(which, fake)
-            pred_real, pred_real_cls = self.D(which, img)
-            d_adv = bce_logits(pred_fake, 0) + bce_logits(pred_real, 1)
-            d_cls = bce_logits(pred_real_cls, c_org)
+            d_adv, d_cls = 0, 0
+            for (pred_fake, _), (pred_real, pred_real_cls) in zip(self.D(which, fake), self.D(which, img)):
+                d_adv = d_adv + bce_logits(pred_fake, 0) + bce_logits(pred_real, 1)
+                d_cls = d_cls + bce_logits(pred_real_cls, c_org)
             d = d_adv + self.lcls * d_cls
             d.backward()
             self.loss.update(d_adv=d_adv.item(), d_cls=d_cls.item(), d_total=d.item())
@@ -117,14 +138,25 @@ class AdaINStep:
         z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B)
         img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
                            torch.cat((cls_a, cls_b)))
-        pred_fake, pred_fake_cls = self.D('discriminator1', img_fake)
-        g_adv = bce_logits(pred_fake, 1)
-        g_cls = bce_logits(pred_fake_cls, c_org) * self.lclsg
+        g_content = None
+        if self.use_dis_content:
+            g_content = bce_logits(nets.content_discriminator(self.P['content_discriminator'], z_c), 1 - c_org)
+        g_adv, g_cls = 0, 0
+        for pred_fake, pred_fake_cls in self.D('discriminator1', img_fake):
+            g_adv = g_adv + bce_logits(pred_fake, 1)
+            g_cls = g_cls + bce_logits(pred_fake_cls, c_org)
+        g_cls = g_cls * self.lclsg
         g_self = F.l1_loss(img_self, img) * self.lrec
         g_cc = F.l1_loss(img_recon, img) * self.lrec
         kl_zc = torch.mean(z_c ** 2) * 0.01
-        kl_zs = torch.sum(1 + logvar - mu ** 2 - logvar.exp()) * (-0.5) * 0.01
+        if self.reparam:
+            kl_zs = torch.sum(1 + logvar - mu ** 2 - logvar.exp()) * (-0.5) * 0.01
+        else:
+            kl_zs = torch.mean(z_s ** 2) * 0.01
         total = g_adv + g_cls + g_self + g_cc + kl_zc + kl_zs
+        if g_content is not None:
+            total = total + g_content
+            self.loss.update(g_content=g_content.item())
         total.backward()
         self.loss.update(g_adv=g_adv.item(), g_cls=g_cls.item(), kl_zc=kl_zc.item(), kl_zs=kl_zs.item(),
                          l1_self_rec=g_self.item(), l1_cc_rec=g_cc.item(), total_g=total.item())
@@ -135,17 +167,38 @@ class AdaINStep:
         z_ca, z_cb = torch.split(self.Ec(img, draw), B)
         z_sr = draw((B, self.latent))
         img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
-        pred_fake, pred_fake_cls = self.D('discriminator2', img_random)
-        g_adv2 = bce_logits(pred_fake, 1)
-        g_cls2 = bce_logits(pred_fake_cls, c_org) * self.lclsg
-        _, mu2, _ = self.Es(img_random, c_org, draw)
-        mu2_a, mu2_b = torch.split(mu2, B)
-        z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
+        g_adv2, g_cls2 = 0, 0      # discriminator1 under ms_dis (base_model.py:361), else discriminator2
+        for pred_fake, pred_fake_cls in self.D('discriminator1' if self.ms_dis else 'discriminator2', img_random):
+            g_adv2 = g_adv2 + bce_logits(pred_fake, 1)
+            g_cls2 = g_cls2 + bce_logits(pred_fake_cls, c_org)
+        g_cls2 = g_cls2 * self.lclsg
+        z_rec, mu2, _ = self.Es(img_random, c_org, draw)
+        if self.reparam:
+            mu2_a, mu2_b = torch.split(mu2, B)
+            z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
+        else:                      # base_model.py:417-420: z_sr_a is used twice
+            z_a, _ = torch.split(z_rec, B)
+            z_l1 = (F.l1_loss(z_a, z_sr) + F.l1_loss(z_a, z_sr)) * 10
         (z_l1 + g_adv2 + g_cls2).backward()
         self.loss.update(l1_recon_z=z_l1.item(), gan2=g_adv2.item(), gan2_cls=g_cls2.item())
 
+    def update_content_discriminator(self, img, c_org, draw):
+        """adain_model.py:136-144."""
+        z_c = self.Ec(img, draw)
+        opt = self.opt['content_discriminator']
+        opt.zero_grad()
+        loss = bce_logits(nets.content_discriminator(self.P['content_discriminator'], z_c.detach()), c_org)
+        loss.backward()
+        self.loss_dc = loss.item()
+        torch.nn.utils.clip_grad_norm_(list(self.P['content_discriminator'].values()), 5)
+        opt.step()
+
     def optimize_parameters(self, img, c_org, draw):
-        """adain_model.py:428-430 (no content discriminator)."""
+        """adain_model.py:421-430."""
+        it, self.it = self.it, self.it + 1
+        if self.use_dis_content and it % self.d_iter != 0:
+            self.update_content_discriminator(img, c_org, draw)
+            return dict(self.loss)
         self.update_discriminator(img, c_org, draw)
         for n in ('content_encoder', 'style_encoder', 'decoder'):
             self.opt[n].zero_grad()

@@ -93,10 +93,11 @@ def nets_vs_golden(name):
     return r
 
 
-def make_model(dim, size, B, nd=4, seed=2, shapes=None):
+def make_model(dim, size, B, nd=4, seed=2, shapes=None, model='AdaINModel', **flags):
     from masterthesis_b200 import models
-    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=B, num_domains=nd, init_type=None)
-    m = models.AdaINModel(args)
+    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=B, num_domains=nd, init_type=None,
+                                   **flags)
+    m = getattr(models, model)(args)
     if shapes is None:
         shapes = {n: {k: list(v.shape) for k, v in m.model[n].state_dict().items()} for n in m.model}
     params = {n: synth.synth_params(shapes[n], seed, n + '.') for n in m.model}
@@ -229,6 +230,110 @@ def sampling_vs_oracle(dim=64, size=256, N=2, nd=4, seed=5):
             'emu_forward_reference': rel(e1, r1), 'emu_forward_random': rel(e2, r2)}
 
 
+def base_nets_vs_golden(name='nets_base_dim16_64'):
+    """StyleEncoder / Decoder / DecoderConcat / ContentDiscriminator / MultiScaleDiscriminator on the
+    CUDA path vs the reference's recorded outputs and gradients (same computations as
+    oracle/make_golden.py:nets_base_case).  The reference cannot back-propagate its Decoder
+    (DecResnetBlock's in-place residual add), so Decoder gradients are checked against the oracle."""
+    from masterthesis_b200.models.core import networks
+    from masterthesis_b200.models.core.blocks import to_padded
+    meta, gold = load_gold(name)
+    seed, N, nd, size, s, dim, latent = (meta[k] for k in ('seed', 'N', 'nd', 'size', 'sub', 'dim', 'latent'))
+    C = dim * 4
+    ns = {'style_encoder': networks.StyleEncoder(3, latent, dim, num_domains=nd, activation='lrelu'),
+          'decoder': networks.Decoder(3, C, num_domains=nd, latent_dim=latent),
+          'decoder_concat': networks.DecoderConcat(3, C, num_domains=nd, latent_dim=latent),
+          'content_discriminator': networks.ContentDiscriminator(C, nd),
+          'ms_discriminator': networks.MultiScaleDiscriminator(3, dim, num_domains=nd)}
+    P = {}
+    for n, net in ns.items():
+        P[n] = synth.synth_params(meta['shapes'][n], seed, n + '.')
+        net.load_state_dict(P[n])
+        net.to(DEV)
+    c = synth.synth_onehot(N, nd, seed).to(DEV)
+    r = {}
+    img = synth.synth_images(N, size, seed, 'img_se').to(DEV).requires_grad_(True)
+    z = ns['style_encoder'].run(img, c)
+    (z * synth.synth_tensor('proj_se', z.shape, seed).to(DEV)).sum().backward()
+    r['se.z'], r['cos_se.dimg'] = rel(z.detach(), gold['se.z']), cos(img.grad[:, :, ::s, ::s], gold['se.dimg'])
+    q = max(1, s // 4)
+    for tag, name_ in (('dec', 'decoder'), ('decc', 'decoder_concat')):
+        zc_in = synth.synth_tensor('zc_in', (N, C, size // 4, size // 4), seed) * (C * (size // 4) ** 2) ** 0.5
+        zc_in = zc_in.to(torch.bfloat16).float().to(DEV).requires_grad_(True)
+        zs_in = (synth.synth_tensor('zs_in', (N, latent), seed) * latent ** 0.5).to(DEV).requires_grad_(True)
+        fake = ns[name_].run(to_padded(zc_in, 1), zs_in, c)
+        proj = synth.synth_tensor('proj', fake.shape, seed).to(DEV)
+        (fake * proj).sum().backward()
+        r[f'{tag}.fake'] = rel(fake.detach()[:, :, ::s, ::s], gold[f'{tag}.fake'])
+        if tag == 'dec':       # gradients vs the fp32 oracle (out-of-place residual add)
+            Po = {k: v.to(DEV).requires_grad_(True) for k, v in P['decoder'].items()}
+            zc_o, zs_o = zc_in.detach().clone().requires_grad_(True), zs_in.detach().clone().requires_grad_(True)
+            (onets.decoder(Po, zc_o, zs_o, c) * proj).sum().backward()
+            r['cos_dec.dzc'], r['cos_dec.dzs'] = cos(zc_in.grad, zc_o.grad), cos(zs_in.grad, zs_o.grad)
+            mine = dict(ns['decoder'].named_parameters())
+            for k in ('dec1.0.conv1.block.1.weight', 'dec1.1.block1.0.weight', 'dec1.3.block2.2.bias',
+                      'dec2.0.block.0.weight', 'linear.4.weight'):
+                r[f'cos_decoder.{k}'] = cos(mine[k].grad, Po[k].grad)
+        else:
+            r['cos_decc.dzc'] = cos(zc_in.grad[:, :, ::q, ::q], gold['decc.dzc'])
+            r['cos_decc.dzs'] = cos(zs_in.grad, gold['decc.dzs'])
+            # yardstick: the oracle with bf16 storage emulated vs the fp32 oracle on the same input
+            from tests import emu
+            Po = {k: v.to(DEV) for k, v in P['decoder_concat'].items()}
+            with torch.no_grad():
+                f32 = onets.decoder_concat(Po, zc_in.detach(), zs_in.detach(), c)
+                with emu.bf16_storage():
+                    e16 = onets.decoder_concat(Po, zc_in.detach(), zs_in.detach(), c)
+            r['emu_decc.fake'] = rel(e16, f32)
+    zc2 = synth.synth_tensor('zc_dc', (N, C, 64, 64), seed) * (C * 64 * 64) ** 0.5
+    zc2 = zc2.to(torch.bfloat16).float().to(DEV).requires_grad_(True)
+    pred = ns['content_discriminator'].run(to_padded(zc2, 1))
+    (pred * synth.synth_tensor('proj_dc', pred.shape, seed).to(DEV)).sum().backward()
+    r['dc.pred'], r['cos_dc.dzc'] = rel(pred.detach(), gold['dc.pred']), cos(zc2.grad[:, :, ::4, ::4], gold['dc.dzc'])
+    img4 = synth.synth_images(N, 256, seed, 'img_ms').to(DEV).requires_grad_(True)
+    tot = 0
+    for i, (dis, cls) in enumerate(ns['ms_discriminator'].run(img4)):
+        r[f'ms.dis{i}'], r[f'ms.cls{i}'] = rel(dis.detach(), gold[f'ms.dis{i}']), rel(cls.detach(), gold[f'ms.cls{i}'])
+        tot = tot + (dis * synth.synth_tensor(f'proj_ms{i}', dis.shape, seed).to(DEV)).sum() + (cls * c).sum()
+    tot.backward()
+    r['cos_ms.dimg'] = cos(img4.grad[:, :, ::8, ::8], gold['ms.dimg'])
+    for k, g in gold.items():
+        if not k.startswith('grad.'):
+            continue
+        _, n, key = k.split('.', 2)
+        if n == 'content_discriminator' and key == 'model.2.block.1.bias':
+            continue    # a bias in front of InstanceNorm: its exact gradient is 0, the recorded one is rounding noise
+        mine = dict(ns[n].named_parameters())[key].grad
+        if mine.numel() > 20000:
+            mine = mine.flatten()[:: max(1, mine.numel() // 20000)]
+        r['cos_' + k[5:]] = cos(mine, g.flatten())
+    return r
+
+
+def flag_step_vs_golden(name):
+    """BaseModel --concat [--reparam] / AdaINModel --use_dis_content --ms_dis on the CUDA path vs the
+    REFERENCE's recorded losses, iteration by iteration (replayed CPU draws, eager launches)."""
+    meta, gold = load_gold(name)
+    seed, B, nd, size, dim = meta['seed'], meta['B'], meta['nd'], meta['size'], meta['dim']
+    m, _ = make_model(dim, size, B, nd, seed, meta['shapes'], model=meta['model'], **meta['flags'])
+    m.rng = synth.Draws(seed)
+    b = batch(B, size, nd, seed)
+    r = {}
+    for it in range(meta['iters']):
+        m.set_inputs(b)
+        m.optimize_parameters(it)
+        mine = dict(m.loss)
+        if getattr(m, 'loss_dc', None) is not None:
+            mine['loss_dc'] = m.loss_dc
+        for k, v in mine.items():
+            ref = float(gold[f'loss.{it}.{k}'])
+            err = abs(v - ref) / max(1.0, abs(ref))
+            r[f'loss_it{it}.{k}'] = err if err == err else float('inf')
+        assert set(mine) == {k.split('.', 2)[2] for k in gold if k.startswith(f'loss.{it}.')}, (it, sorted(mine))
+    assert [list(s_) for s_ in m.rng.log] == meta['draws'], "RNG call order differs from the reference"
+    return r
+
+
 def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6):
     """The CUDA-graph replay of the iteration (Model._run_iteration) vs the eager launch sequence:
     same weights, same batch, same torch seed (device Philox draws), `iters` iterations including
@@ -262,6 +367,10 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6):
 
 CASES = {
     'graph_vs_eager': graph_vs_eager,
+    'nets_base_dim16_64': base_nets_vs_golden,
+    'step_basec': lambda: flag_step_vs_golden('step_basec_dim8_64'),
+    'step_basecr': lambda: flag_step_vs_golden('step_basecr_dim8_64'),
+    'step_dcms': lambda: flag_step_vs_golden('step_dcms_dim8_256'),
     'nets_dim16_64': lambda: nets_vs_golden('nets_dim16_64'),
     'nets_dim64_256': lambda: nets_vs_golden('nets_dim64_256'),
     'step_dim8_64': step_vs_golden,
