@@ -5,6 +5,7 @@ Metrics: outputs/losses max|a-b| / max|b|; gradients cosine similarity.  The tol
 in tests/test_model_gpu.py.  Keys starting with `emu` are the bf16-storage-emulated oracle vs the
 fp32 oracle (tests/emu.py): the precision any bf16-storage implementation can reach on that input.
 """
+import contextlib
 import json
 import os
 
@@ -334,23 +335,82 @@ def flag_step_vs_golden(name):
     return r
 
 
-def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6):
+def base_default_step_vs_oracle(dim=8, size=64, B=1, nd=4, seed=4, iters=2):
+    """BaseModel with default flags (StyleEncoder + Decoder/DecResnetBlock) trains on the CUDA path; the
+    reference itself cannot (DecResnetBlock's in-place add breaks autograd), so the oracle (out-of-place
+    add, otherwise base_model.py line for line) is the yardstick for the losses of `iters` iterations."""
+    m, params = make_model(dim, size, B, nd, seed, model='BaseModel')
+    m.rng = synth.Draws(seed)
+    st = ostep.AdaINStep({n: {k: v.to(DEV) for k, v in p.items()} for n, p in params.items()}, B,
+                         model='base', reparam=False, concat=False)
+    src = synth.Draws(seed)
+    odraw = lambda shape: src(shape).to(DEV)  # noqa: E731
+    b = batch(B, size, nd, seed)
+    r = {}
+    for it in range(iters):
+        m.set_inputs(b)
+        m.optimize_parameters(it)
+        ref = st.optimize_parameters(m.img.clone(), m.c_org.clone(), odraw)
+        assert set(ref) == set(m.loss)
+        for k in ref:
+            r[f'loss_it{it}.{k}'] = abs(m.loss[k] - ref[k]) / max(1.0, abs(ref[k]))
+    return r
+
+
+def base_sampling_vs_oracle(dim=64, size=256, N=1, nd=4, seed=6):
+    """BASELINE config 1 on the GPU: BaseModel (default flags) generator forward, batch 1, 256x256 —
+    forward_reference (Ec -> StyleEncoder -> Decoder) and forward_random vs the fp32 oracle."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    from masterthesis_b200 import models
+    from tests import emu
+    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=N, num_domains=nd, init_type=None,
+                                   mode='test')
+    m = models.BaseModel(args)
+    shapes = {n: {k: list(v.shape) for k, v in m.model[n].state_dict().items()} for n in m.model}
+    params = {n: synth.synth_params(shapes[n], seed, n + '.') for n in m.model}
+    for n in m.model:
+        m.model[n].load_state_dict(params[n])
+    m.initialize()
+    m.rng = synth.Draws(seed)
+    st = ostep.AdaINStep({n: {k: v.to(DEV) for k, v in p.items()} for n, p in params.items()}, N,
+                         model='base', reparam=False, concat=False)
+    a = synth.synth_images(N, size, seed, 'src').to(DEV)
+    b = synth.synth_images(N, size, seed, 'ref').to(DEV)
+    c = synth.synth_onehot(N, nd, seed).to(DEV)
+    z = synth.synth_tensor('zr', (N, 8), seed).to(DEV)
+    with torch.no_grad():
+        y1, _, _ = m.forward_reference(a, b, c)
+        y2, _, _ = m.forward_random(a, z, c)
+    out = {}
+    for tag, wrap in (('', contextlib.nullcontext), ('emu_', emu.bf16_storage)):
+        src = synth.Draws(seed)
+        draw = lambda shape: src(shape).to(DEV)  # noqa: E731
+        with wrap():
+            out[tag + 'ref'] = st.forward_reference(a, b, c, draw)
+            out[tag + 'rnd'] = st.forward_random(a, z, c, draw)
+    return {'forward_reference': rel(y1, out['ref']), 'forward_random': rel(y2, out['rnd']),
+            'emu_forward_reference': rel(out['emu_ref'], out['ref']),
+            'emu_forward_random': rel(out['emu_rnd'], out['rnd'])}
+
+
+def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
     """The CUDA-graph replay of the iteration (Model._run_iteration) vs the eager launch sequence:
     same weights, same batch, same torch seed (device Philox draws), `iters` iterations including
     the 2 eager warm-up iterations, the capture and several replays, with a changing learning rate."""
     out = {}
     for mode in ('eager', 'graph'):
-        m, _ = make_model(dim, size, B, nd, seed)
+        m, _ = make_model(dim, size, B, nd, seed, **flags)
         m.use_graph = mode == 'graph'
         b = {k: v.to(DEV) for k, v in batch(B, size, nd, seed).items()}
         torch.manual_seed(77)
         hist = []
         for it in range(iters):
             for opt in m.optimizer.values():          # what update_lr() does through the schedulers
-                opt.param_groups[0]['lr'] = 1e-4 * (1.0 - 0.1 * it)
+                opt.param_groups[0]['lr'] = 1e-4 * (1.0 - 0.05 * it)
             m.set_inputs(b)
             m.optimize_parameters(it)
-            hist.append(dict(m.loss))
+            hist.append(dict(m.loss, **({'loss_dc': m.loss_dc} if getattr(m, 'loss_dc', None) is not None else {})))
         torch.cuda.synchronize()
         out[mode] = (hist, {n: torch.cat([p.detach().flatten() for p in m.model[n].parameters()]).clone()
                             for n in m.model}, m._graph is not None)
@@ -371,6 +431,9 @@ CASES = {
     'step_basec': lambda: flag_step_vs_golden('step_basec_dim8_64'),
     'step_basecr': lambda: flag_step_vs_golden('step_basecr_dim8_64'),
     'step_dcms': lambda: flag_step_vs_golden('step_dcms_dim8_256'),
+    'step_base_default': base_default_step_vs_oracle,
+    'sampling_base_256': base_sampling_vs_oracle,
+    'graph_vs_eager_dc': lambda: graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True),
     'nets_dim16_64': lambda: nets_vs_golden('nets_dim16_64'),
     'nets_dim64_256': lambda: nets_vs_golden('nets_dim64_256'),
     'step_dim8_64': step_vs_golden,

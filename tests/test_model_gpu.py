@@ -93,3 +93,25 @@ def test_flagged_training_steps_vs_reference_golden(name):
     reference's recorded value."""
     from tests.model_cases import flag_step_vs_golden
     _check(flag_step_vs_golden(name), 1e-2, 0.0)
+
+
+def test_base_default_training_step_vs_oracle():
+    """BaseModel default flags (StyleEncoder + Decoder): losses of 2 iterations within 1e-2 of the oracle."""
+    from tests.model_cases import base_default_step_vs_oracle
+    _check(base_default_step_vs_oracle(), 1e-2, 0.0)
+
+
+def test_base_sampling_vs_oracle():
+    """BASELINE config 1 (BaseModel generator forward, batch 1, 256x256) on the GPU vs the fp32 oracle,
+    bounded like test_sampling_vs_oracle."""
+    from tests.model_cases import base_sampling_vs_oracle
+    res = base_sampling_vs_oracle()
+    for k in ('forward_reference', 'forward_random'):
+        assert res[k] <= 1e-1 and res[k] <= max(2e-2, 1.5 * res['emu_' + k]), res
+
+
+def test_cuda_graph_with_content_discriminator_schedule():
+    """--use_dis_content alternates two iteration kinds (d_iter = 3): each is captured in its own CUDA
+    graph; 10 iterations (warm-up, both captures, replays) match the eager launch sequence."""
+    from tests.model_cases import graph_vs_eager
+    _check(graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True), 5e-3, 0.9999)
