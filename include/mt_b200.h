@@ -105,13 +105,15 @@ int mt_norm_finalize(const float* stats, int mode, int N, int C, int C_valid, in
 int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C, int act,
                       float slope, const void* res_pad, int res_p, const float* noise,
                       void* out_pad, int out_p, void* stream);
-int mt_norm_bwd_reduce(const void* g, const void* x, const float* ss, int N, int HW, int C,
-                       int act, float slope, float* sums, void* stream);
+/* g: gradient of the block output, dense (g_pad = 0) or the consumer's PADDED gradient buffer
+ * [N, H+2g_pad, W+2g_pad, C], in which case the adjoint of ReflectionPad2d is applied on the fly */
+int mt_norm_bwd_reduce(const void* g, int g_pad, const void* x, const float* ss, int N, int H, int W,
+                       int C, int act, float slope, float* sums, void* stream);
 int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C, int C_valid, int HW,
                          const float* gb, const float* ln_w, float* coef, float* dgb,
                          float* dln_w, float* dln_b, void* stream);
-int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float* coef, int N,
-                      int HW, int C, int act, float slope, void* dx, void* stream);
+int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss, const float* coef,
+                      int N, int H, int W, int C, int act, float slope, void* dx, void* stream);
 /* backward of conv+bias+activation written into a padded buffer: fold + act' */
 int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C, int pad,
                     int act, float slope, void* dy, void* stream);

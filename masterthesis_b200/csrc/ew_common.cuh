@@ -23,6 +23,25 @@ __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
     f[2 * i + 1] = t.y;
   }
 }
+// raw 16-byte streaming load (read-only path, no L1 allocation) + conversion, kept apart so that a
+// thread can issue several loads before it touches the first result (memory-level parallelism:
+// ~35 KB must be in flight per SM to saturate HBM3e)
+__device__ __forceinline__ uint4 ldg16(const __nv_bfloat16* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void cvt8(const uint4& r, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
 __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
   uint4 r;
   __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
@@ -53,6 +72,35 @@ __device__ __forceinline__ int reflect_fold_sources(int i, int L, int p, int (&s
   const int k = L - 2 - i;                                     // bottom / right border offset
   if (k >= 0 && k < p) src[n++] = L + p + k;
   return n;
+}
+
+// compile-time variants for the hot loops (a run-time `act` costs a branch ladder per element)
+template <int ACT>
+__device__ __forceinline__ float act_fwd_t(float v, float slope) {
+  if (ACT == 1) return fmaxf(v, 0.f);
+  if (ACT == 2) return v > 0.f ? v : v * slope;
+  if (ACT == 3) return tanhf(v);
+  return v;
+}
+template <int ACT>
+__device__ __forceinline__ float act_grad_pre_t(float y, float slope) {
+  if (ACT == 1) return y > 0.f ? 1.f : 0.f;
+  if (ACT == 2) return y > 0.f ? 1.f : slope;
+  return 1.f;
+}
+// p / W for 0 <= p < 2^24 with a precomputed reciprocal (magic = ceil(2^40 / W))
+struct FastDiv {
+  unsigned long long magic;
+  int d;
+};
+static inline FastDiv make_fastdiv(int d) {
+  FastDiv f;
+  f.d = d;
+  f.magic = ((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d;
+  return f;
+}
+__device__ __forceinline__ int fast_div(int p, const FastDiv& f) {
+  return (int)(((unsigned long long)(unsigned)p * f.magic) >> 40);
 }
 
 __device__ __forceinline__ float act_fwd(float v, int act, float slope) {

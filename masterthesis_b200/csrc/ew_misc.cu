@@ -208,7 +208,52 @@ rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
   const long long total = (long long)N * HW;
-  if (pl < lanes)
+  if ((32 % V) == 0 && V >= Co) {
+    // fast path: the V threads of a pixel sit in one warp; thread v < Co fetches channel v of dy / y
+    // and the group shares the three products by shuffle (instead of 2*Co scalar loads per thread);
+    // two pixels per iteration keep two 16-byte loads in flight.
+    const int lane = threadIdx.x & 31, grp = (lane / V) * V;
+    const long long stride = (long long)gridDim.x * lanes;
+    // loop bound on the warp's FIRST pixel so that every lane takes part in the shuffles
+    for (long long i0 = (long long)blockIdx.x * lanes + pl; i0 - lane / V < total; i0 += 2 * stride) {
+      const long long i1 = i0 + stride;
+      const bool ok0 = i0 < total, ok1 = i1 < total;
+      uint4 x0 = make_uint4(0, 0, 0, 0), x1 = make_uint4(0, 0, 0, 0);
+      if (ok0) x0 = ldg16(x + i0 * C + v * 8);
+      if (ok1) x1 = ldg16(x + i1 * C + v * 8);
+      float own0 = 0.f, own1 = 0.f;
+      if (v < Co && ok0) {
+        const long long k0 = ((i0 / HW) * Co + v) * HW + (i0 % HW);
+        const float yy = __ldg(y + k0);
+        own0 = __ldg(dy + k0) * (1.f - yy * yy);
+        if (ok1) {
+          const long long k1 = ((i1 / HW) * Co + v) * HW + (i1 % HW);
+          const float y1 = __ldg(y + k1);
+          own1 = __ldg(dy + k1) * (1.f - y1 * y1);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const float own = u ? own1 : own0;
+        float g[4];
+#pragma unroll
+        for (int o = 0; o < 4; ++o) g[o] = __shfl_sync(0xffffffffu, own, grp + (o < V ? o : 0));
+#pragma unroll
+        for (int o = 0; o < 4; ++o) if (o >= Co) g[o] = 0.f;
+        if (u ? !ok1 : !ok0) continue;
+        float f[8], d[8];
+        cvt8(u ? x1 : x0, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 q = *reinterpret_cast<const float4*>(ws + (v * 8 + j) * 4);
+          d[j] = g[0] * q.x + g[1] * q.y + g[2] * q.z + g[3] * q.w;
+          acc[j][0] += f[j] * g[0]; acc[j][1] += f[j] * g[1];
+          acc[j][2] += f[j] * g[2]; acc[j][3] += f[j] * g[3];
+        }
+        store8(dx + (u ? i1 : i0) * C + v * 8, d);
+      }
+    }
+  } else if (pl < lanes)
     for (long long i = (long long)blockIdx.x * lanes + pl; i < total; i += (long long)gridDim.x * lanes) {
       const int n = (int)(i / HW);
       const int pix = (int)(i % HW);

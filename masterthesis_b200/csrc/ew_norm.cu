@@ -4,6 +4,7 @@
 // norm.py:23-33 ((1+w)*IN(x)+b with w,b = chunk(fc(s),2)), norm.py:5-21 (F.layer_norm over
 // (C,H,W), per-channel affine), misc.py:18-26 (x + noise), blocks.py:137,166 (residual add).
 #include "../../include/mt_b200.h"
+#include <stdlib.h>
 #include "ew_common.cuh"
 
 namespace mt {
@@ -11,46 +12,87 @@ namespace mt {
 // ---------------------------------------------------------------- statistics
 // x [N, HW, C] -> stats [N][C][2] += (sum, sumsq).  One CTA = (n, pixel chunk); thread = one
 // 8-channel vector x a pixel lane; warp reads are 512 contiguous bytes.
-template <bool kBackward>
-__global__ void __launch_bounds__(256)
+// The backward variant reads the gradient through the ADJOINT of the reflection padding when
+// gp > 0: g is then the padded buffer [N, H+2gp, W+2gp, C] written by the consumer's data-gradient
+// and fold(g) is formed on the fly (only pixels next to the border have extra terms).
+constexpr int EW_UNROLL = 4;
+
+__device__ __forceinline__ void add_fold_extras(const __nv_bfloat16* __restrict__ g, int n, int h, int w,
+                                                int H, int W, int C, int v, int gp, float (&gv)[8]) {
+  int hs[3], ws[3];
+  const int nh = reflect_fold_sources(h, H, gp, hs), nw = reflect_fold_sources(w, W, gp, ws);
+  if (nh * nw == 1) return;
+  const int Hp = H + 2 * gp, Wp = W + 2 * gp;
+  for (int a = 0; a < nh; ++a)
+    for (int b = 0; b < nw; ++b) {
+      if (a == 0 && b == 0) continue;                       // the main term is already loaded
+      float f[8];
+      load8(g + (((long long)n * Hp + hs[a]) * Wp + ws[b]) * C + v * 8, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gv[j] += f[j];
+    }
+}
+
+template <bool kBackward, int ACT>
+__global__ void __launch_bounds__(256, 2)
 plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ g,
-                    const float* __restrict__ ss, int HW, int C, int chunks, int act, float slope,
-                    float* __restrict__ out) {
+                    const float* __restrict__ ss, int H, int W, FastDiv divW, int C, int gp, int chunks,
+                    float slope, float* __restrict__ out) {
   extern __shared__ float red[];  // [lanes][V*16]
-  const int V = C / 8;
+  const int V = C / 8, HW = H * W;
   const int lanes = blockDim.x / V;
   const int n = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   const int per = (HW + chunks - 1) / chunks;
   const int p0 = chunk * per, p1 = min(HW, p0 + per);
+  const int Hp = H + 2 * gp, Wp = W + 2 * gp;
   float a0[8], a1[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) a0[j] = a1[j] = 0.f;
   float sc[8], sh[8];
   if (kBackward) {
+    const float4* s4 = reinterpret_cast<const float4*>(ss + ((long long)n * C + v * 8) * 2);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      sc[j] = ss[((long long)n * C + v * 8 + j) * 2];
-      sh[j] = ss[((long long)n * C + v * 8 + j) * 2 + 1];
+    for (int j = 0; j < 4; ++j) {
+      const float4 q = __ldg(s4 + j);
+      sc[2 * j] = q.x; sh[2 * j] = q.y; sc[2 * j + 1] = q.z; sh[2 * j + 1] = q.w;
     }
   }
   if (pl < lanes) {
-    for (int p = p0 + pl; p < p1; p += lanes) {
-      const long long off = ((long long)n * HW + p) * C + v * 8;
-      float xv[8];
-      load8(x + off, xv);
-      if (!kBackward) {
+    for (int pb = p0 + pl; pb < p1; pb += EW_UNROLL * lanes) {
+      uint4 xr[EW_UNROLL], gr[EW_UNROLL];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { a0[j] += xv[j]; a1[j] += xv[j] * xv[j]; }
-      } else {
-        float gv[8];
-        load8(g + off, gv);
+      for (int u = 0; u < EW_UNROLL; ++u) {
+        const int p = pb + u * lanes;
+        if (p < p1) {
+          xr[u] = ldg16(x + ((long long)n * HW + p) * C + v * 8);
+          if (kBackward) {   // (h+gp)*Wp + w+gp == p + 2*gp*h + gp*Wp + gp
+            const int h = gp ? fast_div(p, divW) : 0;
+            gr[u] = ldg16(g + ((long long)n * Hp * Wp + p + 2 * gp * h + gp * Wp + gp) * C + v * 8);
+          }
+        }
+      }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float y = xv[j] * sc[j] + sh[j];           // pre-activation (A*xhat + B)
-          const float gg = gv[j] * act_grad_pre(y, act, slope);
-          a0[j] += gg;                                      // sum g
-          a1[j] += gg * xv[j];                              // sum g*x  (xhat folded in finalize)
+      for (int u = 0; u < EW_UNROLL; ++u) {
+        const int p = pb + u * lanes;
+        if (p < p1) {
+          float xv[8];
+          cvt8(xr[u], xv);
+          if (!kBackward) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { a0[j] += xv[j]; a1[j] += xv[j] * xv[j]; }
+          } else {
+            float gv[8];
+            cvt8(gr[u], gv);
+            if (gp) { const int h = fast_div(p, divW); add_fold_extras(g, n, h, p - h * W, H, W, C, v, gp, gv); }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float y = xv[j] * sc[j] + sh[j];           // pre-activation (A*xhat + B)
+              const float gg = gv[j] * act_grad_pre_t<ACT>(y, slope);
+              a0[j] += gg;                                      // sum g
+              a1[j] += gg * xv[j];                              // sum g*x  (xhat folded in finalize)
+            }
+          }
         }
       }
     }
@@ -129,9 +171,10 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, 
 // out_pad[n, h+po, w+po, :] = act(x*scale + shift) (+ res_pad[n, h+pr, w+pr, :]) (+ noise)
 // grid = (pixel chunks, N); a thread owns ONE 8-channel vector (its scale/shift live in registers)
 // and walks pixels, so a warp reads/writes 512 contiguous bytes per pixel row.
-__global__ void __launch_bounds__(256)
+template <int ACT>
+__global__ void __launch_bounds__(256, 2)
 affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ss, int H, int W,
-                      int C, int act, float slope, const __nv_bfloat16* __restrict__ res, int pr,
+                      FastDiv divW, int C, float slope, const __nv_bfloat16* __restrict__ res, int pr,
                       const float* __restrict__ noise, __nv_bfloat16* __restrict__ out, int po) {
   const int V = C / 8, lanes = blockDim.x / V;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
@@ -149,26 +192,44 @@ affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
     }
   }
   const int Hr = H + 2 * pr, Wr = W + 2 * pr, Ho = H + 2 * po, Wo = W + 2 * po;
-  for (int p = blockIdx.x * lanes + pl; p < HW; p += gridDim.x * lanes) {
-    const int h = p / W, w = p - h * W;
-    const long long i = ((long long)n * HW + p) * C + v * 8;
-    float f[8];
-    load8(x + i, f);
+  const int stride = gridDim.x * lanes;
+  for (int pb = blockIdx.x * lanes + pl; pb < HW; pb += EW_UNROLL * stride) {
+    uint4 xr[EW_UNROLL], rr[EW_UNROLL];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = act_fwd(f[j] * sc[j] + sh[j], act, slope);
-    if (res) {
-      float r[8];
-      load8(res + (((long long)n * Hr + h + pr) * Wr + w + pr) * C + v * 8, r);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    for (int u = 0; u < EW_UNROLL; ++u) {
+      const int p = pb + u * stride;
+      if (p < HW) {
+        xr[u] = ldg16(x + ((long long)n * HW + p) * C + v * 8);
+        if (res) {
+          const int h = pr ? fast_div(p, divW) : 0;
+          rr[u] = ldg16(res + ((long long)n * Hr * Wr + p + 2 * pr * h + pr * Wr + pr) * C + v * 8);
+        }
+      }
     }
-    if (noise) {
-      float r[8];
-      load8f(noise + i, r);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    for (int u = 0; u < EW_UNROLL; ++u) {
+      const int p = pb + u * stride;
+      if (p < HW) {
+        const int h = po ? fast_div(p, divW) : 0;
+        float f[8];
+        cvt8(xr[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = act_fwd_t<ACT>(f[j] * sc[j] + sh[j], slope);
+        if (res) {
+          float r[8];
+          cvt8(rr[u], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] += r[j];
+        }
+        if (noise) {
+          float r[8];
+          load8f(noise + ((long long)n * HW + p) * C + v * 8, r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] += r[j];
+        }
+        store8(out + ((long long)n * Ho * Wo + p + 2 * po * h + po * Wo + po) * C + v * 8, f);
+      }
     }
-    store8(out + (((long long)n * Ho + h + po) * Wo + w + po) * C + v * 8, f);
   }
 }
 
@@ -236,34 +297,67 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
   }
 }
 
-// dx = c0*(g*act'(y)) + c1*x + c2      grid = (pixel chunks, N), coefficients in registers
-__global__ void __launch_bounds__(256)
+// dx = c0*(fold(g)*act'(y)) + c1*x + c2      grid = (pixel chunks, N), coefficients in registers;
+// g is padded by gp (0: dense) and folded on the fly like in plane_reduce_kernel<true>.
+template <int ACT>
+__global__ void __launch_bounds__(256, 2)
 norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
-                      const float* __restrict__ ss, const float* __restrict__ coef, int HW, int C,
-                      int act, float slope, __nv_bfloat16* __restrict__ dx) {
-  const int V = C / 8, lanes = blockDim.x / V;
+                      const float* __restrict__ ss, const float* __restrict__ coef, int H, int W,
+                      FastDiv divW, int C, int gp, float slope, __nv_bfloat16* __restrict__ dx) {
+  const int V = C / 8, lanes = blockDim.x / V, HW = H * W;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   if (pl >= lanes) return;
   const int n = blockIdx.y;
+  const int Hp = H + 2 * gp, Wp = W + 2 * gp;
   float sc[8], sh[8], c0[8], c1[8], c2[8];
   const float* s = ss + ((long long)n * C + v * 8) * 2;
   const float* cf = coef + ((long long)n * C + v * 8) * 3;
+  {
+    float t[16], u[24];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    sc[j] = __ldg(s + 2 * j); sh[j] = __ldg(s + 2 * j + 1);
-    c0[j] = __ldg(cf + 3 * j); c1[j] = __ldg(cf + 3 * j + 1); c2[j] = __ldg(cf + 3 * j + 2);
-  }
-  for (int p = blockIdx.x * lanes + pl; p < HW; p += gridDim.x * lanes) {
-    const long long i = ((long long)n * HW + p) * C + v * 8;
-    float xv[8], gv[8], o[8];
-    load8(x + i, xv);
-    load8(g + i, gv);
+    for (int j = 0; j < 4; ++j) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(s) + j);
+      t[4 * j] = q.x; t[4 * j + 1] = q.y; t[4 * j + 2] = q.z; t[4 * j + 3] = q.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(cf) + j);
+      u[4 * j] = q.x; u[4 * j + 1] = q.y; u[4 * j + 2] = q.z; u[4 * j + 3] = q.w;
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float y = xv[j] * sc[j] + sh[j];
-      o[j] = c0[j] * (gv[j] * act_grad_pre(y, act, slope)) + c1[j] * xv[j] + c2[j];
+      sc[j] = t[2 * j]; sh[j] = t[2 * j + 1];
+      c0[j] = u[3 * j]; c1[j] = u[3 * j + 1]; c2[j] = u[3 * j + 2];
     }
-    store8(dx + i, o);
+  }
+  const int stride = gridDim.x * lanes;
+  for (int pb = blockIdx.x * lanes + pl; pb < HW; pb += EW_UNROLL * stride) {
+    uint4 xr[EW_UNROLL], gr[EW_UNROLL];
+#pragma unroll
+    for (int u = 0; u < EW_UNROLL; ++u) {
+      const int p = pb + u * stride;
+      if (p < HW) {
+        const int h = gp ? fast_div(p, divW) : 0;
+        xr[u] = ldg16(x + ((long long)n * HW + p) * C + v * 8);
+        gr[u] = ldg16(g + ((long long)n * Hp * Wp + p + 2 * gp * h + gp * Wp + gp) * C + v * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < EW_UNROLL; ++u) {
+      const int p = pb + u * stride;
+      if (p < HW) {
+        float xv[8], gv[8], o[8];
+        cvt8(xr[u], xv);
+        cvt8(gr[u], gv);
+        if (gp) { const int h = fast_div(p, divW); add_fold_extras(g, n, h, p - h * W, H, W, C, v, gp, gv); }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float y = xv[j] * sc[j] + sh[j];
+          o[j] = c0[j] * (gv[j] * act_grad_pre_t<ACT>(y, slope)) + c1[j] * xv[j] + c2[j];
+        }
+        store8(dx + ((long long)n * HW + p) * C + v * 8, o);
+      }
+    }
   }
 }
 
@@ -303,39 +397,50 @@ act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16*
 using namespace mt;
 #define ST(s) ((cudaStream_t)(s))
 
-// grid (pixel chunks, N) for the per-plane kernels: ~8 CTAs per SM, >= 4 pixels per pixel lane
+// grid (pixel chunks, N) for the per-plane kernels: ~2 resident CTAs per SM (each thread keeps
+// EW_UNROLL loads per tensor in flight and amortises its per-channel coefficients over many
+// pixels), >= 4 pixels per pixel lane
+static int ew_ctas_per_sm() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MT_EW_CTAS"); v = e ? atoi(e) : 4; if (v < 1) v = 1; }
+  return v;
+}
 static dim3 plane_grid(int N, int HW, int C) {
   const int lanes = 256 / (C / 8);
-  int chunks = (8 * NUM_SMS + N - 1) / N;
+  int chunks = (ew_ctas_per_sm() * NUM_SMS + N - 1) / N;
   const int max_chunks = (HW + lanes * 4 - 1) / (lanes * 4);
   if (chunks > max_chunks) chunks = max_chunks;
   if (chunks < 1) chunks = 1;
   return dim3((unsigned)chunks, (unsigned)N);
 }
 
-static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int HW,
-                         int C, int act, float slope, float* out, cudaStream_t st) {
+static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int H, int W,
+                         int C, int gp, int act, float slope, float* out, cudaStream_t st) {
+  const int HW = H * W;
   if (C % 8 || C / 8 > 256) return -1003;
   cudaError_t e = cudaMemsetAsync(out, 0, (size_t)N * C * 2 * sizeof(float), st);
   if (e != cudaSuccess) return -(int)e;
   const int V = C / 8;
   const int lanes = 256 / V;
-  int chunks = (4 * NUM_SMS + N - 1) / N;
+  int chunks = (ew_ctas_per_sm() * NUM_SMS + N - 1) / N;
   const int max_chunks = (HW + lanes * 4 - 1) / (lanes * 4);
   if (chunks > max_chunks) chunks = max_chunks;
   if (chunks < 1) chunks = 1;
   const size_t smem = (size_t)lanes * V * 16 * sizeof(float);
-  if (bwd)
-    plane_reduce_kernel<true><<<N * chunks, 256, smem, st>>>(
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, HW, C, chunks, act, slope, out);
-  else
-    plane_reduce_kernel<false><<<N * chunks, 256, smem, st>>>(
-        (const __nv_bfloat16*)x, nullptr, nullptr, HW, C, chunks, 0, 0.f, out);
+  const FastDiv dw = make_fastdiv(W);
+  if ((long long)H * W >= (1 << 24)) return -1005;
+#define MT_RED(B, A) plane_reduce_kernel<B, A><<<N * chunks, 256, smem, st>>>(                  \
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out)
+  if (!bwd) MT_RED(false, 0);
+  else if (act == MT_ACT_RELU) MT_RED(true, 1);
+  else if (act == MT_ACT_LRELU) MT_RED(true, 2);
+  else MT_RED(true, 0);
+#undef MT_RED
   return cuda_rc();
 }
 
 extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream) {
-  return reduce_launch(false, x, nullptr, nullptr, N, HW, C, 0, 0.f, stats, ST(stream));
+  return reduce_launch(false, x, nullptr, nullptr, N, HW, 1, C, 0, 0, 0.f, stats, ST(stream));
 }
 extern "C" int mt_norm_finalize(const float* stats, int mode, int N, int C, int C_valid, int HW, float eps,
                                 const float* gb, const float* ln_w, const float* ln_b, float* ss,
@@ -349,14 +454,23 @@ extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, i
                                  int act, float slope, const void* res_pad, int res_p,
                                  const float* noise, void* out_pad, int out_p, void* stream) {
   if (C % 8 || C / 8 > 256) return -1003;
-  affine_act_fwd_kernel<<<plane_grid(N, H * W, C), 256, 0, ST(stream)>>>(
-      (const __nv_bfloat16*)x, ss, H, W, C, act, slope, (const __nv_bfloat16*)res_pad, res_p,
-      noise, (__nv_bfloat16*)out_pad, out_p);
+  if ((long long)H * W >= (1 << 24)) return -1005;
+  const FastDiv dw = make_fastdiv(W);
+#define MT_AFF(A) affine_act_fwd_kernel<A><<<plane_grid(N, H * W, C), 256, 0, ST(stream)>>>(     \
+      (const __nv_bfloat16*)x, ss, H, W, dw, C, slope, (const __nv_bfloat16*)res_pad, res_p, noise, \
+      (__nv_bfloat16*)out_pad, out_p)
+  switch (act) {
+    case MT_ACT_RELU: MT_AFF(1); break;
+    case MT_ACT_LRELU: MT_AFF(2); break;
+    case MT_ACT_TANH: MT_AFF(3); break;
+    default: MT_AFF(0); break;
+  }
+#undef MT_AFF
   return cuda_rc();
 }
-extern "C" int mt_norm_bwd_reduce(const void* g, const void* x, const float* ss, int N, int HW,
-                                  int C, int act, float slope, float* sums, void* stream) {
-  return reduce_launch(true, x, g, ss, N, HW, C, act, slope, sums, ST(stream));
+extern "C" int mt_norm_bwd_reduce(const void* g, int g_pad, const void* x, const float* ss, int N, int H,
+                                  int W, int C, int act, float slope, float* sums, void* stream) {
+  return reduce_launch(true, x, g, ss, N, H, W, C, g_pad, act, slope, sums, ST(stream));
 }
 extern "C" int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C,
                                     int C_valid, int HW, const float* gb, const float* ln_w, float* coef,
@@ -367,13 +481,19 @@ extern "C" int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode
                                                       dgb, dln_w, dln_b);
   return cuda_rc();
 }
-extern "C" int mt_norm_bwd_apply(const void* g, const void* x, const float* ss, const float* coef,
-                                 int N, int HW, int C, int act, float slope, void* dx,
-                                 void* stream) {
+extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss,
+                                 const float* coef, int N, int H, int W, int C, int act, float slope,
+                                 void* dx, void* stream) {
   if (C % 8 || C / 8 > 256) return -1003;
-  norm_bwd_apply_kernel<<<plane_grid(N, HW, C), 256, 0, ST(stream)>>>(
-      (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, HW, C, act, slope,
-      (__nv_bfloat16*)dx);
+  if ((long long)H * W >= (1 << 24)) return -1005;
+  const FastDiv dw = make_fastdiv(W);
+#define MT_APP(A) norm_bwd_apply_kernel<A><<<plane_grid(N, H * W, C), 256, 0, ST(stream)>>>(     \
+      (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, H, W, dw, C, g_pad, slope,       \
+      (__nv_bfloat16*)dx)
+  if (act == MT_ACT_RELU) MT_APP(1);
+  else if (act == MT_ACT_LRELU) MT_APP(2);
+  else MT_APP(0);
+#undef MT_APP
   return cuda_rc();
 }
 extern "C" int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C,

@@ -88,10 +88,9 @@ class ConvNormAct(Function):
     def backward(ctx, dout):
         x, raw, ss, mr, p1, wb = ctx.saved_tensors
         g, mode, act, op = ctx.geom, ctx.mode, ctx.act, ctx.out_pad
-        G = ops.reflect_fold(_c(dout), op)
-        dy, dgb, dlw, dlb = ops.norm_bwd(G, raw, ss, mr, mode, act=act,
+        dy, dgb, dlw, dlb = ops.norm_bwd(_c(dout), raw, ss, mr, mode, act=act,
                                          gb=_c(p1) if mode == "adain" else None,
-                                         ln_w=p1 if mode == "layer" else None, C_valid=g.Cout)
+                                         ln_w=p1 if mode == "layer" else None, C_valid=g.Cout, g_pad=op)
         dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
         dw = ops.conv_wgrad(x, dy, g) if ctx.needs_input_grad[1] else None
         db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
@@ -125,19 +124,22 @@ class ResBlock(Function):
     def backward(ctx, dout):
         x, raw1, h, raw2, ss1, mr1, ss2, mr2, gb, wb1, wb2 = ctx.saved_tensors
         g, mode, act, op = ctx.geom, ctx.mode, ctx.act, ctx.out_pad
-        G = ops.reflect_fold(_c(dout), op)
-        dy2, dgb2, _, _ = ops.norm_bwd(G, raw2, ss2, mr2, mode, act=None, gb=gb)
+        dout = _c(dout)
+        # the adjoint of the reflection borders is applied inside the norm-backward kernels (g_pad)
+        dy2, dgb2, _, _ = ops.norm_bwd(dout, raw2, ss2, mr2, mode, act=None, gb=gb, g_pad=op)
         dw2 = ops.conv_wgrad(h, dy2, g) if ctx.needs_input_grad[2] else None
         dh = ops.conv_dgrad(dy2, wb2, g, h.shape[1], h.shape[2])
-        G1 = ops.reflect_fold(dh, 1)
-        dy1, dgb1, _, _ = ops.norm_bwd(G1, raw1, ss1, mr1, mode, act=act, gb=gb)
+        dy1, dgb1, _, _ = ops.norm_bwd(dh, raw1, ss1, mr1, mode, act=act, gb=gb, g_pad=1)
         dw1 = ops.conv_wgrad(x, dy1, g) if ctx.needs_input_grad[1] else None
         dx = None
         if ctx.needs_input_grad[0]:
             dx = ops.conv_dgrad(dy1, wb1, g, x.shape[1], x.shape[2])
-            if G is dout:  # out_pad == 0: do not alias the incoming gradient
-                G = G.clone()
-            ops.add_interior_(dx, G, 1)
+            if op == 1:
+                # residual path: out_pad = pad(x_int + h) and x is padded like out, so adding the PADDED
+                # dout is the same as adding fold(dout) to the interior once x's producer folds dx
+                ops.add_interior_(dx, dout, 0)
+            else:
+                ops.add_interior_(dx, ops.reflect_fold(dout, op), 1)
         dgb = (dgb1 + dgb2) if mode == "adain" else None
         return dx, dw1, dw2, None, None, None, None, None, None, dgb, None, None, None
 

@@ -341,13 +341,16 @@ def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, 
 
 
 @_checked
-def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None):
-    """g, x dense [N,H,W,C].  Returns (dx, dgb | None, dln_w | None, dln_b | None)."""
+def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None, g_pad=0):
+    """x dense [N,H,W,C]; g dense, or (g_pad > 0) the consumer's padded gradient buffer
+    [N,H+2g_pad,W+2g_pad,C] that is folded (adjoint of the reflection border) on the fly.
+    Returns (dx, dgb | None, dln_w | None, dln_b | None)."""
     N, H, W, C = x.shape
+    assert tuple(g.shape) == (N, H + 2 * g_pad, W + 2 * g_pad, C) and g.is_contiguous()
     L = _lib.lib()
     dev = x.device
     sums = _T.empty((N, C, 2), dtype=torch.float32, device=dev)
-    check(L.mt_norm_bwd_reduce(_p(g), _p(x), _p(ss), N, H * W, C, ACT[act], LRELU_SLOPE, _p(sums),
+    check(L.mt_norm_bwd_reduce(_p(g), g_pad, _p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(sums),
                                _stream()), "norm_bwd_reduce")
     coef = _T.empty((N, C, 3), dtype=torch.float32, device=dev)
     dgb = _T.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
@@ -356,7 +359,7 @@ def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None):
     check(L.mt_norm_bwd_finalize(_p(sums), _p(mr), NORM[mode], N, C, C_valid or C, H * W, _p(gb), _p(ln_w), _p(coef),
                                  _p(dgb), _p(dlw), _p(dlb), _stream()), "norm_bwd_finalize")
     dx = _T.empty_like(x)
-    check(L.mt_norm_bwd_apply(_p(g), _p(x), _p(ss), _p(coef), N, H * W, C, ACT[act], LRELU_SLOPE,
+    check(L.mt_norm_bwd_apply(_p(g), g_pad, _p(x), _p(ss), _p(coef), N, H, W, C, ACT[act], LRELU_SLOPE,
                               _p(dx), _stream()), "norm_bwd_apply")
     _count(3)
     return dx, dgb, dlw, dlb
