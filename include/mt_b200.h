@@ -58,6 +58,14 @@ int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, int kw, int t
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
 int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,
                   void* y, void* stream);
+/* Same, with the statistics pass of the following InstanceNorm / LayerNorm (blocks.py:38-41,
+ * networks.py:470-489) fused into the conv epilogue: per-channel sum / sum of squares of the STORED
+ * bf16 output of every pixel tile go to stats[N][parts][Cout_s][2] (fp32, every slot written once,
+ * no zeroing needed); mt_norm_finalize adds the parts.  `parts` must be mt_conv_stats_parts(d, 0),
+ * which is 0 for shapes that cannot fuse (the caller then runs mt_plane_stats). */
+int mt_conv_stats_parts(const MtConv2d* d, int transposed);
+int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,
+                        void* y, float* stats, int parts, void* stream);
 /* d(loss)/d(input buffer), including the reflection border rows/cols (folded later) */
 int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx, void* stream);
 /* d(loss)/d(weight) accumulated (+=) into fp32 dw_packed[taps][Cout][Cin_s] (window mode:
@@ -70,6 +78,9 @@ int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int 
  * Descriptor: Hin/Win = input dims, Hout/Wout = 2*Hin, 2*Win; kh=kw=3, stride=2, zpad=1. */
 int mt_conv_transpose2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
                             const float* bias, void* y, void* stream);
+/* with fused output statistics, as mt_conv2d_fwd_stats; parts = mt_conv_stats_parts(d, 1) */
+int mt_conv_transpose2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd,
+                                  const float* bias, void* y, float* stats, int parts, void* stream);
 int mt_conv_transpose2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
                               void* stream);
 int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
@@ -98,7 +109,8 @@ int mt_add_interior(void* dpad, const void* dense, int N, int H, int W, int C, i
  * C is the STORED channel count; C_valid <= C the logical one (LayerNorm statistics run over
  * C_valid*HW elements and ln_w / ln_b / dln_* hold C_valid entries; padded channels stay zero). */
 int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream);
-int mt_norm_finalize(const float* stats, int mode, int N, int C, int C_valid, int HW, float eps,
+/* stats: [N][parts][C][2] (parts = 1 from mt_plane_stats, per-tile slots from mt_conv2d_fwd_stats) */
+int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,
                      const float* gb, const float* ln_w, const float* ln_b, float* ss, float* mr,
                      void* stream);
 /* out_pad[interior] = act(x*scale+shift) (+ residual) (+ noise, misc.py:25); ss may be NULL */

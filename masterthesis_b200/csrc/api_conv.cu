@@ -27,12 +27,14 @@ static void load_encode() {
 }
 
 int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
-              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr) {
+              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr,
+              bool swizzle128) {
   std::call_once(g_encode_once, load_encode);
   if (!g_encode) return -1001;
   CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
                         const_cast<void*>(base), dims, strides_bytes, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -(2000 + (int)r);
 }
@@ -52,6 +54,8 @@ struct ConvLike {
   int n_store, n_bias;
   long long out_n_stride, out_h_stride, out_w_stride, out_off;
   int act; float slope; const float* bias; void* out;
+  float* stats;             // optional fused plane statistics [Nt][stat_parts][n_store][2]
+  int stat_parts, stat_part0;
 };
 
 static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
@@ -115,7 +119,29 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     rc = make_tmap(&tmB, c.b, 3, dims, str, box, es);
   }
   if (rc) return rc;
-  return launch_igemm(tmA, tmB, p, stream);
+  CUtensorMap tmC;
+  {
+    // Output box of the epilogue's TMA store: the VALID pixel range of this launch as a strided
+    // view (interior of a padded buffer, one sub-pixel phase, ...), so that the store clips tile
+    // overhang by itself.  64-channel slabs use the 128B swizzle, narrower tiles dense rows.
+    const int sw = p.BN < 64 ? p.BN : 64;
+    uint64_t dims[4] = {(uint64_t)c.n_store, (uint64_t)c.Wt, (uint64_t)c.Ht, (uint64_t)c.Nt};
+    uint64_t str[3] = {(uint64_t)c.out_w_stride * 2, (uint64_t)c.out_h_stride * 2,
+                       (uint64_t)c.out_n_stride * 2};
+    uint32_t box[4] = {(uint32_t)sw, (uint32_t)p.TW, (uint32_t)p.TH, (uint32_t)p.TN};
+    uint32_t es[4] = {1, 1, 1, 1};
+    rc = make_tmap(&tmC, reinterpret_cast<const __nv_bfloat16*>(c.out) + c.out_off, 4, dims, str, box,
+                   es, sw == 64);
+  }
+  if (rc) return rc;
+  // fused statistics need one image per tile and the 64-column slab path
+  if (c.stats) {
+    // the caller sized the buffer with mt_conv_stats_parts(): same tile choice, one image per tile
+    if (p.TN != 1 || p.BN < 64 || c.stat_part0 + p.tiles_w * p.tiles_h > c.stat_parts) return -1012;
+    p.stats = c.stats; p.n_stat_c = c.n_store;
+    p.stat_parts = c.stat_parts; p.stat_part0 = c.stat_part0;
+  }
+  return launch_igemm(tmA, tmB, tmC, p, stream);
 }
 
 static int check_desc(const MtConv2d* d) {
@@ -139,6 +165,29 @@ extern "C" int mt_conv_window_mode(int Cin_s, int kw) {
 
 extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
                              const float* bias, void* y, void* stream) {
+  return mt_conv2d_fwd_stats(d, x, w_fwd, bias, y, nullptr, 0, stream);
+}
+
+// Number of per-tile partial-sum slots per image that the fused statistics of this conv produce
+// (0: the shape cannot fuse them — several images per tile, or a Cout tile narrower than a slab).
+extern "C" int mt_conv_stats_parts(const MtConv2d* d, int transposed) {
+  if (check_desc(d)) return 0;
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("MT_CONV_NO_STATS"); off = e ? atoi(e) : 0; }
+  if (off || pick_bn(d->Cout) < 64) return 0;
+  int tw, th, tn;
+  if (transposed) {
+    if ((d->Hout & 1) || (d->Wout & 1)) return 0;
+    pick_tile(128, d->Wout / 2, d->Hout / 2, d->N, 1, &tw, &th, &tn);
+    return tn == 1 ? 4 * cdiv(d->Wout / 2, tw) * cdiv(d->Hout / 2, th) : 0;
+  }
+  pick_tile(128, d->Wout, d->Hout, d->N, d->stride, &tw, &th, &tn);
+  return tn == 1 ? cdiv(d->Wout, tw) * cdiv(d->Hout, th) : 0;
+}
+
+extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd,
+                                   const float* bias, void* y, float* stats, int parts,
+                                   void* stream) {
   int rc = check_desc(d);
   if (rc) return rc;
   ConvLike c;
@@ -164,6 +213,7 @@ extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd
   c.out_n_stride = (long long)d->out_H * d->out_W * d->Cout_s;
   c.out_off = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
   c.act = d->act; c.slope = d->slope; c.bias = bias; c.out = y;
+  c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;
   return run_conv_like(c, (cudaStream_t)stream);
 }
 
@@ -186,6 +236,7 @@ static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, lo
       q.w_base = r0 * kw + s0; q.w_step_r = 2 * kw; q.w_step_s = 2;
       q.out_h_stride = 2 * row_pitch; q.out_w_stride = 2 * pix_pitch;
       q.out_off = base_off + ph * row_pitch + pw * pix_pitch;
+      q.stat_part0 = (ph * 2 + pw) * (c.stat_parts / 4);
       int rc = run_conv_like(q, stream);
       if (rc) return rc;
     }
@@ -218,6 +269,12 @@ extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_
 
 extern "C" int mt_conv_transpose2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
                                        const float* bias, void* y, void* stream) {
+  return mt_conv_transpose2d_fwd_stats(d, x, w_fwd, bias, y, nullptr, 0, stream);
+}
+
+extern "C" int mt_conv_transpose2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd,
+                                             const float* bias, void* y, float* stats, int parts,
+                                             void* stream) {
   int rc = check_desc(d);
   if (rc) return rc;
   if (d->stride != 2) return -1004;
@@ -232,8 +289,9 @@ extern "C" int mt_conv_transpose2d_fwd(const MtConv2d* d, const void* x, const v
   const long long pix = d->Cout_s, row = (long long)d->out_W * d->Cout_s;
   c.out_n_stride = (long long)d->out_H * row;
   const long long base = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
-  return run_phases(c, d->kh, d->kw, d->zpad, d->Hout, d->Wout, row, pix, base,
-                    (cudaStream_t)stream);
+  if (stats && (parts <= 0 || parts % 4)) return -1012;
+  c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;   // run_phases: phase i fills quarter i
+  return run_phases(c, d->kh, d->kw, d->zpad, d->Hout, d->Wout, row, pix, base, (cudaStream_t)stream);
 }
 
 extern "C" int mt_conv_transpose2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd,

@@ -117,7 +117,21 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 
 // ---------------------------------------------------------------- forward finalize
 // stats -> ss[n][c] = (scale, shift) with y = x*scale + shift, mr[n][c] = (mean, rstd)
-__global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, int N, int C, int Cv,
+// `stats` is [N][parts][C][2]: parts = 1 from mt_plane_stats, one slot per pixel tile from the
+// fused conv epilogue (mt_conv2d_fwd_stats); the parts are added here.
+__device__ __forceinline__ float2 sum_parts(const float* __restrict__ stats, int n, int parts, int C,
+                                            int c) {
+  const float2* s = reinterpret_cast<const float2*>(stats) + (long long)n * parts * C + c;
+  float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
+  int i = 0;
+  for (; i + 1 < parts; i += 2) {          // two independent chains
+    const float2 u = s[(long long)i * C], v = s[(long long)(i + 1) * C];
+    a.x += u.x; a.y += u.y; b.x += v.x; b.y += v.y;
+  }
+  if (i < parts) { const float2 u = s[(long long)i * C]; a.x += u.x; a.y += u.y; }
+  return make_float2(a.x + b.x, a.y + b.y);
+}
+__global__ void norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N, int C, int Cv,
                                      int HW, float eps, const float* __restrict__ gb,
                                      const float* __restrict__ ln_w, const float* __restrict__ ln_b,
                                      float* __restrict__ ss, float* __restrict__ mr) {
@@ -126,8 +140,9 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, 
   if (mode == MT_NORM_LAYER) {
     float s0 = 0.f, s1 = 0.f;
     for (int c = threadIdx.x; c < Cv; c += blockDim.x) {
-      s0 += stats[((long long)n * C + c) * 2];
-      s1 += stats[((long long)n * C + c) * 2 + 1];
+      const float2 t = sum_parts(stats, n, parts, C, c);
+      s0 += t.x;
+      s1 += t.y;
     }
     __shared__ float r0[32], r1[32];
     for (int o = 16; o; o >>= 1) {
@@ -152,8 +167,9 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int mode, 
       if (c >= Cv) { A = 0.f; B = 0.f; }           // padded storage channels stay zero
       else if (ln_w) { A = ln_w[c]; B = ln_b[c]; }
     } else {
-      mean = stats[((long long)n * C + c) * 2] / (float)HW;
-      var = stats[((long long)n * C + c) * 2 + 1] / (float)HW - mean * mean;
+      const float2 t = sum_parts(stats, n, parts, C, c);
+      mean = t.x / (float)HW;
+      var = t.y / (float)HW - mean * mean;
       if (mode == MT_NORM_ADAIN) {
         A = 1.f + gb[(long long)n * 2 * C + c];
         B = gb[(long long)n * 2 * C + C + c];
@@ -442,12 +458,12 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
 extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream) {
   return reduce_launch(false, x, nullptr, nullptr, N, HW, 1, C, 0, 0, 0.f, stats, ST(stream));
 }
-extern "C" int mt_norm_finalize(const float* stats, int mode, int N, int C, int C_valid, int HW, float eps,
+extern "C" int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,
                                 const float* gb, const float* ln_w, const float* ln_b, float* ss,
                                 float* mr, void* stream) {
   if (mode == MT_NORM_ADAIN && !gb) return -1008;
-  if (C_valid <= 0 || C_valid > C) return -1005;
-  norm_finalize_kernel<<<N, 256, 0, ST(stream)>>>(stats, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr);
+  if (C_valid <= 0 || C_valid > C || parts < 1) return -1005;
+  norm_finalize_kernel<<<N, 256, 0, ST(stream)>>>(stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr);
   return cuda_rc();
 }
 extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,

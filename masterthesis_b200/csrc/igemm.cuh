@@ -34,8 +34,9 @@ struct IgemmParams {
   float slope;
   const float* bias;
   __nv_bfloat16* out;
-  float* stats;        // optional [N][n_stat_c][2] fp32 (sum, sumsq) accumulated with atomics
-  int n_stat_c;
+  float* stats;        // optional fused plane statistics: [N][stat_parts][n_stat_c][2] fp32 partial
+  int n_stat_c;        // (sum, sumsq) per pixel tile; this launch fills slots stat_part0 + tile index
+  int stat_parts, stat_part0;
 };
 
 // dW_tap[Cout, Cin] = sum_pixels dY[pix, Cout]^T * X_tap[pix, Cin]   (both operands MN-major)
@@ -55,10 +56,11 @@ struct WgradParams {
 };
 
 int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
-              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr);
+              const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr,
+              bool swizzle128 = true);
 
-int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p,
-                 cudaStream_t stream);
+int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                 const IgemmParams& p, cudaStream_t stream);
 int launch_wgrad(const CUtensorMap& tmA, const CUtensorMap& tmB, const WgradParams& p,
                  cudaStream_t stream);
 

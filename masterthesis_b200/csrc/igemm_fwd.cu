@@ -37,69 +37,100 @@ static constexpr int NUM_EPI_WARPS = 8;
 static constexpr int NUM_THREADS = 64 + 32 * NUM_EPI_WARPS;
 __device__ long long g_ts[64];   // debug timestamps of CTA 0 (MT_IGEMM_DBG & 32)
 
-// Epilogue of one warp: TMEM lane quadrant q, columns [col_begin, col_end) of one 128-row
-// accumulator.  Activation / bias are compile-time so the per-element code is cvt + pack only.
-template <int ACT, bool BIAS>
-__device__ __forceinline__ void epilogue_warp(const IgemmParams& p, uint32_t tmem_acc, int q, int lane,
-                                              int col_begin, int col_end, int c_base, int w0, int h0,
-                                              int n0) {
-  const int m = q * 32 + lane;
-  const int w_i = m % p.TW;
-  const int h_i = (m / p.TW) % p.TH;
-  const int n_i = m / (p.TW * p.TH);
-  const int w = w0 + w_i, h = h0 + h_i, n = n0 + n_i;
-  const bool row_ok = (w < p.Wt) && (h < p.Ht) && (n < p.Nt);
-  __nv_bfloat16* orow = p.out + p.out_off + (long long)n * p.out_n_stride +
-                        (long long)h * p.out_h_stride + (long long)w * p.out_w_stride;
-  for (int c0 = col_begin; c0 < col_end; c0 += 32) {
-    if (c_base + c0 >= p.n_store) break;  // warp-uniform
-    uint32_t v[32];
-    tmem_ld32(tmem_acc + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
-    tmem_ld_wait();
-    if (!row_ok) continue;
+// Epilogue of one thread (= one accumulator row) for one slab of SW columns: TMEM -> registers ->
+// bias / activation -> bf16 -> this row of the staging box in shared memory.  The box is laid out as
+// the output tensor map expects it (128-byte rows with the 128B swizzle when SW == 64, dense rows
+// otherwise); a TMA store then writes whole 128-byte lines, where per-lane global stores touched 32
+// different lines per instruction.  Rows outside the valid pixel range are staged as zeros (the
+// store clips them; the fused plane statistics must not see them).
+template <int ACT, bool BIAS, int SW>
+__device__ __forceinline__ void epilogue_slab(const IgemmParams& p, uint32_t tmem_addr,
+                                              uint32_t stage_row, int r7, bool row_ok, int c_glob) {
+  constexpr int LD = SW < 32 ? 32 : SW;
+  uint32_t v[LD];
+  {
+    uint32_t(&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
+    tmem_ld32(tmem_addr, lo);
+    if (LD == 64) {
+      uint32_t(&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[LD - 32]);
+      tmem_ld32(tmem_addr + 32, hi);
+    }
+  }
+  tmem_ld_wait();
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      const int c = c_base + c0 + g * 8;
-      if (c < p.n_store) {
-        float f[8];
+  for (int g = 0; g < SW / 8; ++g) {
+    const int c = c_glob + g * 8;
+    float f[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
-        if (BIAS) {
-          if (c + 8 <= p.n_bias) {
-            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
-            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
-            f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-            f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
-          } else {
+    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
+    if (BIAS) {
+      if (c + 8 <= p.n_bias) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
+        f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+        f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+      } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (c + j < p.n_bias) f[j] += __ldg(p.bias + c + j);
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (ACT == ACT_RELU) f[j] = fmaxf(f[j], 0.f);
-          if (ACT == ACT_LRELU) f[j] = f[j] > 0.f ? f[j] : f[j] * p.slope;
-          if (ACT == ACT_TANH) f[j] = tanhf(f[j]);
-        }
-        uint4 pk;
-        __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
-        __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
-        __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
-        __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
-        pk.x = *reinterpret_cast<uint32_t*>(&t0);
-        pk.y = *reinterpret_cast<uint32_t*>(&t1);
-        pk.z = *reinterpret_cast<uint32_t*>(&t2);
-        pk.w = *reinterpret_cast<uint32_t*>(&t3);
-        *reinterpret_cast<uint4*>(orow + c) = pk;
+        for (int j = 0; j < 8; ++j)
+          if (c + j < p.n_bias) f[j] += __ldg(p.bias + c + j);
       }
     }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (ACT == ACT_RELU) f[j] = fmaxf(f[j], 0.f);
+      if (ACT == ACT_LRELU) f[j] = f[j] > 0.f ? f[j] : f[j] * p.slope;
+      if (ACT == ACT_TANH) f[j] = tanhf(f[j]);
+      if (!row_ok) f[j] = 0.f;
+    }
+    __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]);
+    __nv_bfloat162 t1 = __floats2bfloat162_rn(f[2], f[3]);
+    __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]);
+    __nv_bfloat162 t3 = __floats2bfloat162_rn(f[6], f[7]);
+    const int chunk = SW == 64 ? (g ^ r7) : g;
+    sts128(stage_row + chunk * 16, *reinterpret_cast<uint32_t*>(&t0), *reinterpret_cast<uint32_t*>(&t1),
+           *reinterpret_cast<uint32_t*>(&t2), *reinterpret_cast<uint32_t*>(&t3));
+  }
+}
+
+// Per-channel sum and sum of squares of one staged 128 x 64 slab (the bf16 values that go to
+// memory, i.e. exactly what a separate statistics pass over the stored tensor would read), written
+// to this tile's slot of the partial-sum buffer p.stats[n][part][c][2] with plain stores: every slot
+// is written exactly once, so the buffer needs no zeroing and there are no atomics to fight over a
+// few thousand addresses; the norm finalize kernel adds the parts.
+// Warp wq of the 128-thread team owns columns 16*wq .. +15: lane = (row selector 0..3) x (column
+// pair 0..7); the four rows of one step are 2 apart, which puts their 32-byte pieces in distinct
+// banks under the 128B swizzle.
+__device__ __forceinline__ void slab_stats(const IgemmParams& p, uint32_t stage_buf, int tt, int c_glob,
+                                           int n, int part) {
+  const int wq = tt >> 5, lane = tt & 31;
+  const int cpl = lane & 7, rsel = lane >> 3;
+  const int chunk = 2 * wq + (cpl >> 2);
+  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+  for (int i = 0; i < 32; ++i) {
+    const int r = 8 * (i >> 1) + 2 * rsel + (i & 1);
+    const uint32_t w = lds32(stage_buf + r * 128 + (((chunk ^ (r & 7)) << 4) | ((cpl & 3) << 2)));
+    const float x0 = __uint_as_float(w << 16), x1 = __uint_as_float(w & 0xffff0000u);
+    s0 += x0; q0 = fmaf(x0, x0, q0);
+    s1 += x1; q1 = fmaf(x1, x1, q1);
+  }
+#pragma unroll
+  for (int o = 8; o <= 16; o <<= 1) {
+    s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+    q0 += __shfl_xor_sync(0xffffffffu, q0, o);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+  }
+  const int c = c_glob + 16 * wq + 2 * cpl;
+  if (rsel == 0 && c < p.n_stat_c) {
+    float* d = p.stats + (((long long)n * p.stat_parts + part) * p.n_stat_c + c) * 2;
+    *reinterpret_cast<float4*>(d) = make_float4(s0, q0, s1, q1);
   }
 }
 
 // Work item -> (Cout tile, pixel-tile origin of THIS CTA).  Pixel tiles are numbered w-fastest; a
 // pair owns tiles 2j and 2j+1 (an out-of-range tile loads zeros and stores nothing).
-struct WorkCoord { int n_tile, w0, h0, n0; };
+struct WorkCoord { int n_tile, w0, h0, n0, part; };
 template <int CG>
 __device__ __forceinline__ WorkCoord decode_work(const IgemmParams& p, int item, int rank) {
   WorkCoord c;
@@ -110,6 +141,7 @@ __device__ __forceinline__ WorkCoord decode_work(const IgemmParams& p, int item,
   const int th = pt % p.tiles_h;
   const int tn = pt / p.tiles_h;
   c.w0 = tw * p.TW; c.h0 = th * p.TH; c.n0 = tn * p.TN;
+  c.part = p.stat_part0 + th * p.tiles_w + tw;   // slot of the fused statistics (TN == 1)
   return c;
 }
 
@@ -157,7 +189,7 @@ __device__ __forceinline__ void mma_round(MmaCtx& c, int kb) {
 template <int CG, int BN, int S>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const IgemmParams p) {
+                  const __grid_constant__ CUtensorMap tmC, const IgemmParams p) {
   constexpr int B_ROWS = BN / CG;                           // weight rows staged by this CTA
   constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_ROWS * BK * 2;
   constexpr int ACC_COLS = BN < 32 ? 32 : BN;               // TMEM columns per accumulator stage
@@ -186,6 +218,7 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmC);
     for (int i = 0; i < S; ++i) {
       mbar_init(smem_u32(&bar_full[i]), 1);
       mbar_init(smem_u32(&bar_empty[i]), 1);
@@ -280,24 +313,36 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     __syncwarp();
   } else {
-    // ================= epilogue: TMEM -> regs -> bias/act -> bf16 -> HBM =================
+    // ========== epilogue: TMEM -> regs -> bias/act -> bf16 -> smem box -> TMA store ==========
+    // Two teams of four warps (one warp per TMEM lane quadrant); team g takes the 64-column slabs
+    // g, g+2, ... of the tile and owns one 16 KiB staging box behind the operand ring.
+    constexpr int SW = BN < 64 ? BN : 64;
+    constexpr int NSLAB = BN / SW;
     const int q = warp & 3;            // TMEM lane quadrant this warp may access
-    const int grp = (warp - 2) >> 2;   // which half of the columns
-    constexpr int PER = BN / 2 < 32 ? 32 : BN / 2;
-    const int col_begin = grp * PER, col_end = min(BN, col_begin + PER);
+    const int grp = (warp - 2) >> 2;   // team
+    const int m = q * 32 + lane;       // accumulator row = pixel of the tile
+    const int tt = ((warp - 2) & 3) * 32 + lane;
+    const uint32_t stage_buf = smem_base + S * STAGE_BYTES + grp * (BM * 128);
+    const uint32_t stage_row = stage_buf + m * (SW * 2);
+    const int w_i = m % p.TW, h_i = (m / p.TW) % p.TH, n_i = m / (p.TW * p.TH);
     const bool hb = p.n_bias > 0;
     int tile_i = 0;
     for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
       const WorkCoord wc = decode_work<CG>(p, item, rank);
       const int acc = tile_i & 1;
       const uint32_t acc_ph = (tile_i >> 1) & 1;
+      const bool row_ok = (wc.w0 + w_i < p.Wt) && (wc.h0 + h_i < p.Ht) && (wc.n0 + n_i < p.Nt);
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_ph);
       tc_fence_after();
       if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
-      if (col_begin < col_end) {
-        const uint32_t tmem_acc = tmem_base + acc * ACC_COLS;
-        const int c_base = wc.n_tile * BN;
-#define MT_EPI(A, B) epilogue_warp<A, B>(p, tmem_acc, q, lane, col_begin, col_end, c_base, wc.w0, wc.h0, wc.n0)
+      const uint32_t tmem_row = tmem_base + acc * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
+      bool released = false;
+      for (int sl = grp; sl < NSLAB; sl += 2) {
+        const int c_glob = wc.n_tile * BN + sl * SW;
+        if (c_glob >= p.n_store) break;                       // team-uniform
+        if (tt == 0) bulk_wait_read0();                       // previous store has left the box
+        named_bar_sync(1 + grp, 128);
+#define MT_EPI(A, B) epilogue_slab<A, B, SW>(p, tmem_row + sl * SW, stage_row, m & 7, row_ok, c_glob)
         switch (p.act) {
           case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
           case ACT_LRELU: if (hb) MT_EPI(ACT_LRELU, true); else MT_EPI(ACT_LRELU, false); break;
@@ -305,15 +350,35 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           default:        if (hb) MT_EPI(ACT_NONE, true);  else MT_EPI(ACT_NONE, false);  break;
         }
 #undef MT_EPI
+        if (sl + 2 >= NSLAB || c_glob + 2 * SW >= p.n_store) {
+          // last TMEM read of this warp for the tile: hand the accumulator back right away
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
+            else mbar_arrive(smem_u32(&bar_tempty[acc]));
+          }
+          released = true;
+        }
+        fence_proxy_async();
+        named_bar_sync(1 + grp, 128);
+        if (tt == 0) {
+          tma_store_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
+          bulk_commit();
+        }
+        if (SW == 64 && p.stats != nullptr && wc.n0 < p.Nt) slab_stats(p, stage_buf, tt, c_glob, wc.n0, wc.part);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {                 // hand the accumulator back to the (leader's) MMA thread
-        if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
-        else mbar_arrive(smem_u32(&bar_tempty[acc]));
+      if (!released) {                 // a team without slabs in this tile
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
+          else mbar_arrive(smem_u32(&bar_tempty[acc]));
+        }
       }
       if (stamp && warp == 2 && tile_i < 8) g_ts[25 + 2 * tile_i] = clock64() - T0;
     }
+    if (tt == 0) bulk_wait0();         // the stores are complete before the CTA retires
   }
 
   // ---- teardown
@@ -334,12 +399,13 @@ struct StageCfg {
   static constexpr int kStageBytes = A_STAGE_BYTES + (BN / CG) * BK * 2;
   static constexpr int kFit = (208 * 1024) / kStageBytes;
   static constexpr int kStages = kFit > 8 ? 8 : kFit;
-  static constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024;
+  // operand ring + alignment slack + two 16 KiB staging boxes of the epilogue teams
+  static constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024 + 2 * BM * 128;
 };
 
 template <int CG, int BN>
-static cudaError_t launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p,
-                              cudaStream_t stream) {
+static cudaError_t launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                              const IgemmParams& p, cudaStream_t stream) {
   using Cfg = StageCfg<CG, BN>;
   auto* kern = igemm_conv_kernel<CG, BN, Cfg::kStages>;
   static bool attr_set = false;
@@ -361,11 +427,11 @@ static cudaError_t launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, co
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p);
+  return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
 }
 
-int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p_in,
-                 cudaStream_t stream) {
+int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                 const IgemmParams& p_in, cudaStream_t stream) {
   IgemmParams p = p_in;
   if (g_num_sms == 0) {
     int dev = 0;
@@ -380,13 +446,13 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmPara
   cudaError_t e = cudaErrorInvalidValue;
   const int key = p.cg * 1000 + p.BN;
   switch (key) {
-    case 2256: e = launch_cfg<2, 256>(tmA, tmB, p, stream); break;
-    case 2128: e = launch_cfg<2, 128>(tmA, tmB, p, stream); break;
-    case 1256: e = launch_cfg<1, 256>(tmA, tmB, p, stream); break;
-    case 1128: e = launch_cfg<1, 128>(tmA, tmB, p, stream); break;
-    case 1064: e = launch_cfg<1, 64>(tmA, tmB, p, stream); break;
-    case 1032: e = launch_cfg<1, 32>(tmA, tmB, p, stream); break;
-    case 1016: e = launch_cfg<1, 16>(tmA, tmB, p, stream); break;
+    case 2256: e = launch_cfg<2, 256>(tmA, tmB, tmC, p, stream); break;
+    case 2128: e = launch_cfg<2, 128>(tmA, tmB, tmC, p, stream); break;
+    case 1256: e = launch_cfg<1, 256>(tmA, tmB, tmC, p, stream); break;
+    case 1128: e = launch_cfg<1, 128>(tmA, tmB, tmC, p, stream); break;
+    case 1064: e = launch_cfg<1, 64>(tmA, tmB, tmC, p, stream); break;
+    case 1032: e = launch_cfg<1, 32>(tmA, tmB, tmC, p, stream); break;
+    case 1016: e = launch_cfg<1, 16>(tmA, tmB, tmC, p, stream); break;
     default: return -1010;
   }
   if (e == cudaSuccess) e = cudaGetLastError();

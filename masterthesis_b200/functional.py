@@ -71,9 +71,8 @@ class ConvNormAct(Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, wf, wb, geom, mode, p1, p2, act, out_pad, noise):
-        raw = ops.conv_fwd(x, wf, bias, geom)
+        raw, stats = ops.conv_fwd_stats(x, wf, bias, geom)
         N, H, W, C = raw.shape
-        stats = ops.plane_stats(raw)
         gb = p1 if mode == "adain" else None
         lw, lb = (p1, p2) if mode == "layer" else (None, None)
         ss, mr = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb, C_valid=geom.Cout)
@@ -107,13 +106,13 @@ class ResBlock(Function):
     @staticmethod
     def forward(ctx, x, w1, w2, wf1, wb1, wf2, wb2, geom, mode, gb, act, out_pad, noise):
         gbc = _c(gb) if mode == "adain" else None
-        raw1 = ops.conv_fwd(x, wf1, None, geom)
+        raw1, st1 = ops.conv_fwd_stats(x, wf1, None, geom)
         N, H, W, C = raw1.shape
-        ss1, mr1 = ops.norm_finalize(ops.plane_stats(raw1), mode, H * W, gbc)
+        ss1, mr1 = ops.norm_finalize(st1, mode, H * W, gbc)
         h = ops.affine_act_fwd(raw1, ss1, act=act, out_p=1)
         ops.reflect_border_(h, 1)
-        raw2 = ops.conv_fwd(h, wf2, None, geom)
-        ss2, mr2 = ops.norm_finalize(ops.plane_stats(raw2), mode, H * W, gbc)
+        raw2, st2 = ops.conv_fwd_stats(h, wf2, None, geom)
+        ss2, mr2 = ops.norm_finalize(st2, mode, H * W, gbc)
         out = ops.affine_act_fwd(raw2, ss2, act=None, res_pad=x, res_p=1, noise=noise, out_p=out_pad)
         ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad

@@ -212,6 +212,29 @@ def conv_fwd(x, wf, bias, g: ConvGeom, act=None, out_pad=0, out=None):
 
 
 @_checked
+def conv_fwd_stats(x, wf, bias, g: ConvGeom):
+    """conv_fwd (no activation, dense output) plus the plane statistics of its stored output,
+    [N, Cout_s, 2] fp32 (sum, sum of squares): fused into the conv epilogue where the tile shape
+    allows it, else by the separate mt_plane_stats pass."""
+    _require_cuda(x)
+    N, Hin, Win, C = x.shape
+    assert C == g.Cin_s and x.dtype == torch.bfloat16 and x.is_contiguous()
+    d = g.desc(N, Hin, Win, 0, None)
+    out = empty_act(N, d.out_H, d.out_W, g.Cout_s, x.device)
+    L = _lib.lib()
+    parts = L.mt_conv_stats_parts(ctypes.byref(d), int(g.transposed))
+    stats = _T.empty((N, parts, g.Cout_s, 2), dtype=torch.float32, device=x.device) if parts else None
+    fn = L.mt_conv_transpose2d_fwd_stats if g.transposed else L.mt_conv2d_fwd_stats
+    with _timed("fwd", g, N, Hin, Win):
+        check(fn(ctypes.byref(d), _p(x), _p(wf), _p(bias), _p(out), _p(stats), parts, _stream()),
+              "conv_fwd_stats")
+    _count(4 if g.transposed else 1)
+    if stats is None:
+        stats = plane_stats(out)
+    return out, stats
+
+
+@_checked
 def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
     """dy: dense [N,Ho,Wo,Cout_s] -> dx [N,Hin,Win,Cin_s] (gradient of the padded input buffer)."""
     _require_cuda(dy)
@@ -320,10 +343,11 @@ def plane_stats(x):
 
 @_checked
 def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None, C_valid=None):
-    N, C, _ = stats.shape
-    ss = _T.empty_like(stats)
-    mr = _T.empty_like(stats)
-    check(_lib.lib().mt_norm_finalize(_p(stats), NORM[mode], N, C, C_valid or C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
+    parts = stats.shape[1] if stats.dim() == 4 else 1      # per-tile partial sums of a fused conv
+    N, C = stats.shape[0], stats.shape[-2]
+    ss = _T.empty((N, C, 2), dtype=torch.float32, device=stats.device)
+    mr = _T.empty_like(ss)
+    check(_lib.lib().mt_norm_finalize(_p(stats), parts, NORM[mode], N, C, C_valid or C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
                                       _p(ss), _p(mr), _stream()), "norm_finalize")
     _count()
     return ss, mr

@@ -184,7 +184,37 @@ def pad_case(N, C, H, W, p, seed=0):
     return r
 
 
+def fused_stats_case(N, Cin, Cout, H, W, k=3, stride=1, transposed=False, bias=True, seed=0):
+    """Plane statistics fused into the conv epilogue (mt_conv2d_fwd_stats) vs the separate pass
+    over the stored output (mt_plane_stats) and vs torch on that output; the conv output itself must
+    be bit-identical to mt_conv2d_fwd.  Shapes with tile overhang exercise the zero-staged rows."""
+    torch.manual_seed(seed)
+    rp = 0 if transposed else k // 2
+    g = ConvGeom(Cin, Cout, k, k, 2 if transposed else stride, 1 if transposed else 0, transposed)
+    x = bf(torch.randn(N, Cin, H, W, device=DEV))
+    xn = to_nhwc(F.pad(x, (rp,) * 4, mode="reflect") if rp else x)
+    w = bf(torch.randn(*((Cin, Cout) if transposed else (Cout, Cin)), k, k, device=DEV) * 0.05)
+    b = torch.randn(Cout, device=DEV) if bias else None
+    wf, _ = ops.pack_weight(w, g)
+    y0 = ops.conv_fwd(xn, wf, b, g)
+    y, st = ops.conv_fwd_stats(xn, wf, b, g)
+    fused = st.dim() == 4
+    tot = st.sum(1) if fused else st
+    sep = ops.plane_stats(y)
+    yf = y.float()
+    ref = torch.stack((yf.sum((1, 2)), (yf * yf).sum((1, 2))), -1)
+    return {"same_output": 0.0 if torch.equal(y0, y) else 1.0,
+            "fused": 0.0 if fused else 1.0,
+            "vs_separate": rel(tot, sep) * 1e2,       # both fp32 sums of the same bf16 values: 1e-4
+            "vs_torch": rel(tot, ref) * 1e2}
+
+
 CASES = {
+    "fused_stats_hot": lambda: fused_stats_case(2, 256, 256, 64, 64, bias=False),
+    "fused_stats_overhang": lambda: fused_stats_case(3, 64, 136, 24, 40),
+    "fused_stats_s2": lambda: fused_stats_case(2, 64, 128, 64, 64, k=3, stride=2),
+    "fused_stats_convT": lambda: fused_stats_case(2, 128, 64, 32, 32, transposed=True),
+    "fused_stats_convT_overhang": lambda: fused_stats_case(1, 256, 128, 12, 20, transposed=True),
     # the hot shape: ResnetBlock / AdaINResnetBlock conv (blocks.py:131-134,150-151)
     "conv3x3_256": lambda: conv_case(2, 256, 256, 64, 64, 3, 1, 1, bias=False),
     "conv3x3_s2": lambda: conv_case(2, 64, 128, 64, 64, 3, 2, 1),

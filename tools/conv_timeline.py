@@ -9,10 +9,15 @@ g = ConvGeom(256, 256, 3, 3, 1, 0)
 x = torch.randn(N, 66, 66, 256, device='cuda').to(torch.bfloat16)
 w = torch.randn(256, 256, 3, 3, device='cuda') * 0.05
 wf, wb = ops.pack_weight(w, g)
-for _ in range(3): ops.conv_fwd(x, wf, None, g)
+fwd = (lambda: ops.conv_fwd_stats(x, wf, None, g)) if os.environ.get("MT_STATS") else (lambda: ops.conv_fwd(x, wf, None, g))
+for _ in range(3): fwd()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record(); ops.conv_fwd(x, wf, None, g); e1.record(); torch.cuda.synchronize()
+e0.record()
+for _ in range(10): fwd()
+e1.record(); torch.cuda.synchronize()
+print(f"avg of 10 back-to-back: {e0.elapsed_time(e1)*100:.1f} us")
+e0.record(); fwd(); e1.record(); torch.cuda.synchronize()
 buf = (ctypes.c_longlong * 64)()
 _lib.lib().mt_debug_timestamps.argtypes = [ctypes.c_void_p]
 _lib.check(_lib.lib().mt_debug_timestamps(ctypes.cast(buf, ctypes.c_void_p)), "ts")
