@@ -80,41 +80,46 @@ static int run_wgrad_like(const WgradLike& c, cudaStream_t stream) {
 // ------------------------------------------------------------------ pack / unpack
 // Source weight element for (n_idx -> out channel of the packed row, k_idx, r, s):
 //   Conv2d          W[co][ci][r][s]   ConvTranspose2d  W[ci][co][r][s]
-__device__ __forceinline__ long long w_index(int co, int ci, int r, int s, int Cout, int Cin,
-                                             int kh, int kw, int transposed) {
-  return transposed ? (((long long)ci * Cout + co) * kh + r) * kw + s
-                    : (((long long)co * Cin + ci) * kh + r) * kw + s;
+// 32-bit index arithmetic throughout: weight tensors have < 2^31 elements (checked by the
+// launchers) and a 64-bit division costs ~5x a 32-bit one — these kernels are nothing but divisions.
+__device__ __forceinline__ unsigned w_index(unsigned co, unsigned ci, unsigned r, unsigned s,
+                                            unsigned Cout, unsigned Cin, unsigned kh, unsigned kw,
+                                            int transposed) {
+  return transposed ? ((ci * Cout + co) * kh + r) * kw + s : ((co * Cin + ci) * kh + r) * kw + s;
 }
 
-__global__ void pack_weight_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw,
+__global__ void pack_weight_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh_, int kw_,
                                    int transposed, int window, __nv_bfloat16* __restrict__ wf,
                                    __nv_bfloat16* __restrict__ wb) {
-  const int Cin_s = (Cin + 7) & ~7, Cout_s = (Cout + 7) & ~7;
-  const long long nf = window ? (long long)kh * Cout * 64 : (long long)kh * kw * Cout * Cin_s;
-  const long long nb = (long long)kh * kw * Cin * Cout_s;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nf + nb; i += stride) {
+  const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned nf = window ? kh * Cout * 64 : kh * kw * Cout * Cin_s;
+  const unsigned nb = kh * kw * Cin * Cout_s;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nf + nb; i += stride) {
     if (i < nf) {
       if (!wf) continue;
       float v = 0.f;
       if (window) {
-        const int e = (int)(i % 64); long long t = i / 64;
-        const int co = (int)(t % Cout); const int r = (int)(t / Cout);
-        const int s = e / Cin_s, ci = e % Cin_s;
+        const unsigned e = i % 64, t = i / 64;
+        const unsigned r = t / Cout, co = t - r * Cout;
+        const unsigned s = e / Cin_s, ci = e - s * Cin_s;
         if (s < kw && ci < Cin) v = w[w_index(co, ci, r, s, Cout, Cin, kh, kw, transposed)];
       } else {
-        const int ci = (int)(i % Cin_s); long long t = i / Cin_s;
-        const int co = (int)(t % Cout); const int tap = (int)(t / Cout);
-        if (ci < Cin) v = w[w_index(co, ci, tap / kw, tap % kw, Cout, Cin, kh, kw, transposed)];
+        const unsigned t = i / Cin_s, ci = i - t * Cin_s;
+        const unsigned tap = t / Cout, co = t - tap * Cout;
+        const unsigned r = tap / kw;
+        if (ci < Cin) v = w[w_index(co, ci, r, tap - r * kw, Cout, Cin, kh, kw, transposed)];
       }
       wf[i] = __float2bfloat16(v);
     } else {
       if (!wb) continue;
-      const long long j = i - nf;
-      const int co = (int)(j % Cout_s); long long t = j / Cout_s;
-      const int ci = (int)(t % Cin); const int tap = (int)(t / Cin);
+      const unsigned j = i - nf;
+      const unsigned t = j / Cout_s, co = j - t * Cout_s;
+      const unsigned tap = t / Cin, ci = t - tap * Cin;
+      const unsigned r = tap / kw;
       float v = 0.f;
-      if (co < Cout) v = w[w_index(co, ci, tap / kw, tap % kw, Cout, Cin, kh, kw, transposed)];
+      if (co < Cout) v = w[w_index(co, ci, r, tap - r * kw, Cout, Cin, kh, kw, transposed)];
       wb[j] = __float2bfloat16(v);
     }
   }
@@ -122,21 +127,23 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Cout, int Ci
 
 // dw_packed -> dw (OIHW / IOHW fp32). Conv2d: [tap][Cout][Cin_s] (window: [kh][Cout][64]);
 // ConvTranspose2d: [tap][Cin][Cout_s].
-__global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout, int Cin, int kh, int kw,
+__global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_, int kw_,
                                     int transposed, int window, float* __restrict__ dw) {
-  const int Cin_s = (Cin + 7) & ~7, Cout_s = (Cout + 7) & ~7;
-  const long long n = (long long)Cout * Cin * kh * kw;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const int s = (int)(i % kw); long long t = i / kw;
-    const int r = (int)(t % kh); t /= kh;
-    int co, ci;
-    if (transposed) { co = (int)(t % Cout); ci = (int)(t / Cout); }
-    else            { ci = (int)(t % Cin);  co = (int)(t / Cin); }
-    long long src;
-    if (transposed) src = ((long long)(r * kw + s) * Cin + ci) * Cout_s + co;
-    else if (window) src = ((long long)r * Cout + co) * 64 + s * Cin_s + ci;
-    else src = ((long long)(r * kw + s) * Cout + co) * Cin_s + ci;
+  const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned n = Cout * Cin * kh * kw;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    unsigned t = i / kw;
+    const unsigned s = i - t * kw;
+    const unsigned t2 = t / kh, r = t - t2 * kh;
+    unsigned co, ci;
+    if (transposed) { ci = t2 / Cout; co = t2 - ci * Cout; }
+    else            { co = t2 / Cin;  ci = t2 - co * Cin; }
+    unsigned src;
+    if (transposed) src = ((r * kw + s) * Cin + ci) * Cout_s + co;
+    else if (window) src = (r * Cout + co) * 64 + s * Cin_s + ci;
+    else src = ((r * kw + s) * Cout + co) * Cin_s + ci;
     dw[i] = g[src];
   }
 }
@@ -157,6 +164,7 @@ extern "C" int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, in
                                    void* stream) {
   const long long n = mt_packed_weight_elems(Cout, Cin, kh, kw, window, 0) +
                       mt_packed_weight_elems(Cout, Cin, kh, kw, window, 1);
+  if (n >= (1ll << 31)) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   pack_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(

@@ -204,30 +204,39 @@ rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
   __syncthreads();
   const int V = C / 8, lanes = blockDim.x / V;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  // this thread's 8 channels x 4 outputs of the weight stay in registers: the same shared-memory
+  // words read by all 8 channel groups of a warp were an 8-way bank conflict per pixel
+  float4 wq[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) wq[j] = *reinterpret_cast<const float4*>(ws + (v * 8 + j) * 4);
   float acc[8][4];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
   const long long total = (long long)N * HW;
-  if ((32 % V) == 0 && V >= Co) {
+  if ((32 % V) == 0 && V >= Co && total * C < (1ll << 31)) {
     // fast path: the V threads of a pixel sit in one warp; thread v < Co fetches channel v of dy / y
     // and the group shares the three products by shuffle (instead of 2*Co scalar loads per thread);
     // two pixels per iteration keep two 16-byte loads in flight.
     const int lane = threadIdx.x & 31, grp = (lane / V) * V;
-    const long long stride = (long long)gridDim.x * lanes;
+    // 32-bit index arithmetic (a 64-bit division costs more than the payload of one pixel)
+    const int stride = (int)gridDim.x * lanes, tot = (int)total;
+    const unsigned uHW = (unsigned)HW;
     // loop bound on the warp's FIRST pixel so that every lane takes part in the shuffles
-    for (long long i0 = (long long)blockIdx.x * lanes + pl; i0 - lane / V < total; i0 += 2 * stride) {
-      const long long i1 = i0 + stride;
-      const bool ok0 = i0 < total, ok1 = i1 < total;
+    for (int i0 = (int)blockIdx.x * lanes + pl; i0 - lane / V < tot; i0 += 2 * stride) {
+      const int i1 = i0 + stride;
+      const bool ok0 = i0 < tot, ok1 = i1 < tot;
       uint4 x0 = make_uint4(0, 0, 0, 0), x1 = make_uint4(0, 0, 0, 0);
       if (ok0) x0 = ldg16(x + i0 * C + v * 8);
       if (ok1) x1 = ldg16(x + i1 * C + v * 8);
       float own0 = 0.f, own1 = 0.f;
       if (v < Co && ok0) {
-        const long long k0 = ((i0 / HW) * Co + v) * HW + (i0 % HW);
+        const unsigned n0 = (unsigned)i0 / uHW;
+        const unsigned k0 = (n0 * Co + v) * uHW + ((unsigned)i0 - n0 * uHW);
         const float yy = __ldg(y + k0);
         own0 = __ldg(dy + k0) * (1.f - yy * yy);
         if (ok1) {
-          const long long k1 = ((i1 / HW) * Co + v) * HW + (i1 % HW);
+          const unsigned n1 = (unsigned)i1 / uHW;
+          const unsigned k1 = (n1 * Co + v) * uHW + ((unsigned)i1 - n1 * uHW);
           const float y1 = __ldg(y + k1);
           own1 = __ldg(dy + k1) * (1.f - y1 * y1);
         }
@@ -245,12 +254,12 @@ rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
         cvt8(u ? x1 : x0, f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float4 q = *reinterpret_cast<const float4*>(ws + (v * 8 + j) * 4);
+          const float4 q = wq[j];
           d[j] = g[0] * q.x + g[1] * q.y + g[2] * q.z + g[3] * q.w;
           acc[j][0] += f[j] * g[0]; acc[j][1] += f[j] * g[1];
           acc[j][2] += f[j] * g[2]; acc[j][3] += f[j] * g[3];
         }
-        store8(dx + (u ? i1 : i0) * C + v * 8, d);
+        store8(dx + (long long)(u ? i1 : i0) * C + v * 8, d);
       }
     }
   } else if (pl < lanes)
@@ -267,7 +276,7 @@ rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
       load8(x + i * C + v * 8, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float4 q = *reinterpret_cast<const float4*>(ws + (v * 8 + j) * 4);
+        const float4 q = wq[j];
         d[j] = g[0] * q.x + g[1] * q.y + g[2] * q.z + g[3] * q.w;
         acc[j][0] += f[j] * g[0]; acc[j][1] += f[j] * g[1];
         acc[j][2] += f[j] * g[2]; acc[j][3] += f[j] * g[3];

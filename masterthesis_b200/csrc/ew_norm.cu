@@ -118,47 +118,89 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 // ---------------------------------------------------------------- forward finalize
 // stats -> ss[n][c] = (scale, shift) with y = x*scale + shift, mr[n][c] = (mean, rstd)
 // `stats` is [N][parts][C][2]: parts = 1 from mt_plane_stats, one slot per pixel tile from the
-// fused conv epilogue (mt_conv2d_fwd_stats); the parts are added here.
-__device__ __forceinline__ float2 sum_parts(const float* __restrict__ stats, int n, int parts, int C,
-                                            int c) {
-  const float2* s = reinterpret_cast<const float2*>(stats) + (long long)n * parts * C + c;
-  float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
-  int i = 0;
-  for (; i + 1 < parts; i += 2) {          // two independent chains
-    const float2 u = s[(long long)i * C], v = s[(long long)(i + 1) * C];
-    a.x += u.x; a.y += u.y; b.x += v.x; b.y += v.y;
+// fused conv epilogue (mt_conv2d_fwd_stats).  Phase A adds the parts in a fixed order (thread =
+// channel x part group, FIN_UNROLL loads in flight each: the sum is a chain of L2 round trips, so
+// the parallelism across threads and blocks is what bounds it); phase B is per channel.
+// grid = (N, channel splits): InstanceNorm / AdaIN blocks own FIN_CSPLIT channels each, LayerNorm
+// needs the whole sample in one block.
+static constexpr int FIN_UNROLL = 8;
+static constexpr int FIN_CSPLIT = 64;
+__global__ void __launch_bounds__(1024)
+norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N, int C, int Cv,
+                     int HW, float eps, const float* __restrict__ gb, const float* __restrict__ ln_w,
+                     const float* __restrict__ ln_b, float* __restrict__ ss, float* __restrict__ mr) {
+  extern __shared__ float tot_c[];   // [channels of this block][2]
+  __shared__ float2 part_sm[1024];
+  const int n = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
+  const int cb = gridDim.y > 1 ? blockIdx.y * FIN_CSPLIT : 0;           // first channel of the block
+  const int Cb = gridDim.y > 1 ? min(FIN_CSPLIT, C - cb) : C;           // channels of the block
+  const float2* sp = reinterpret_cast<const float2*>(stats) + (long long)n * parts * C + cb;
+  if (parts == 1) {
+    for (int c = tid; c < Cb; c += T) {
+      const float2 t = sp[c];
+      tot_c[2 * c] = t.x; tot_c[2 * c + 1] = t.y;
+    }
+  } else {
+    const int Cw = Cb < T ? Cb : T, G = T / Cw;
+    const int c0 = tid % Cw, pg = tid / Cw;
+    if (pg < G)
+      for (int c = c0; c < Cb; c += Cw) {
+        float2 a[FIN_UNROLL];
+#pragma unroll
+        for (int u = 0; u < FIN_UNROLL; ++u) a[u] = make_float2(0.f, 0.f);
+        int i = pg;
+        for (; i + (FIN_UNROLL - 1) * G < parts; i += FIN_UNROLL * G) {
+#pragma unroll
+          for (int u = 0; u < FIN_UNROLL; ++u) {
+            const float2 t = sp[(long long)(i + u * G) * C + c];
+            a[u].x += t.x; a[u].y += t.y;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < FIN_UNROLL - 1; ++u)
+          if (i + u * G < parts) {
+            const float2 t = sp[(long long)(i + u * G) * C + c];
+            a[u].x += t.x; a[u].y += t.y;
+          }
+        float2 r = a[0];
+#pragma unroll
+        for (int u = 1; u < FIN_UNROLL; ++u) { r.x += a[u].x; r.y += a[u].y; }
+        if (G == 1) { tot_c[2 * c] = r.x; tot_c[2 * c + 1] = r.y; }
+        else part_sm[tid] = r;                     // G > 1 implies Cw == Cb: one pass
+      }
+    if (G > 1) {
+      __syncthreads();
+      if (tid < Cb) {
+        float2 r = part_sm[tid];
+        for (int g = 1; g < G; ++g) { const float2 t = part_sm[g * Cw + tid]; r.x += t.x; r.y += t.y; }
+        tot_c[2 * tid] = r.x; tot_c[2 * tid + 1] = r.y;
+      }
+    }
   }
-  if (i < parts) { const float2 u = s[(long long)i * C]; a.x += u.x; a.y += u.y; }
-  return make_float2(a.x + b.x, a.y + b.y);
-}
-__global__ void norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N, int C, int Cv,
-                                     int HW, float eps, const float* __restrict__ gb,
-                                     const float* __restrict__ ln_w, const float* __restrict__ ln_b,
-                                     float* __restrict__ ss, float* __restrict__ mr) {
-  const int n = blockIdx.x;
+  __syncthreads();
   __shared__ float tot[2];
-  if (mode == MT_NORM_LAYER) {
+  if (mode == MT_NORM_LAYER) {                     // gridDim.y == 1
     float s0 = 0.f, s1 = 0.f;
-    for (int c = threadIdx.x; c < Cv; c += blockDim.x) {
-      const float2 t = sum_parts(stats, n, parts, C, c);
-      s0 += t.x;
-      s1 += t.y;
+    for (int c = tid; c < Cv; c += T) {
+      s0 += tot_c[2 * c];
+      s1 += tot_c[2 * c + 1];
     }
     __shared__ float r0[32], r1[32];
     for (int o = 16; o; o >>= 1) {
       s0 += __shfl_xor_sync(0xffffffffu, s0, o);
       s1 += __shfl_xor_sync(0xffffffffu, s1, o);
     }
-    if ((threadIdx.x & 31) == 0) { r0[threadIdx.x >> 5] = s0; r1[threadIdx.x >> 5] = s1; }
+    if ((tid & 31) == 0) { r0[tid >> 5] = s0; r1[tid >> 5] = s1; }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       float t0 = 0.f, t1 = 0.f;
-      for (int i = 0; i < (blockDim.x + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
+      for (int i = 0; i < (T + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
       tot[0] = t0; tot[1] = t1;
     }
     __syncthreads();
   }
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  for (int cl = tid; cl < Cb; cl += T) {
+    const int c = cb + cl;
     float mean, var, A = 1.f, B = 0.f;
     if (mode == MT_NORM_LAYER) {
       const float cnt = (float)Cv * (float)HW;
@@ -167,9 +209,8 @@ __global__ void norm_finalize_kernel(const float* __restrict__ stats, int parts,
       if (c >= Cv) { A = 0.f; B = 0.f; }           // padded storage channels stay zero
       else if (ln_w) { A = ln_w[c]; B = ln_b[c]; }
     } else {
-      const float2 t = sum_parts(stats, n, parts, C, c);
-      mean = t.x / (float)HW;
-      var = t.y / (float)HW - mean * mean;
+      mean = tot_c[2 * cl] / (float)HW;
+      var = tot_c[2 * cl + 1] / (float)HW - mean * mean;
       if (mode == MT_NORM_ADAIN) {
         A = 1.f + gb[(long long)n * 2 * C + c];
         B = gb[(long long)n * 2 * C + C + c];
@@ -463,7 +504,9 @@ extern "C" int mt_norm_finalize(const float* stats, int parts, int mode, int N, 
                                 float* mr, void* stream) {
   if (mode == MT_NORM_ADAIN && !gb) return -1008;
   if (C_valid <= 0 || C_valid > C || parts < 1) return -1005;
-  norm_finalize_kernel<<<N, 256, 0, ST(stream)>>>(stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr);
+  const int threads = parts > 1 ? 1024 : 256;
+  const int splits = (parts > 1 && mode != MT_NORM_LAYER && C > FIN_CSPLIT) ? (C + FIN_CSPLIT - 1) / FIN_CSPLIT : 1;
+  norm_finalize_kernel<<<dim3(N, splits), threads, (size_t)C * 2 * sizeof(float), ST(stream)>>>(stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr);
   return cuda_rc();
 }
 extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,

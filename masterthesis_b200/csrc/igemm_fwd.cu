@@ -225,7 +225,8 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&bar_tfull[i]), 1);
-      mbar_init(smem_u32(&bar_tempty[i]), CG * NUM_EPI_WARPS);
+      // one-slab tiles (BN <= 64) alternate between the two epilogue teams: 4 warps drain a stage
+      mbar_init(smem_u32(&bar_tempty[i]), BN <= 64 ? CG * (NUM_EPI_WARPS / 2) : CG * NUM_EPI_WARPS);
     }
     fence_barrier_init();
   }
@@ -315,7 +316,9 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   } else {
     // ========== epilogue: TMEM -> regs -> bias/act -> bf16 -> smem box -> TMA store ==========
     // Two teams of four warps (one warp per TMEM lane quadrant); team g takes the 64-column slabs
-    // g, g+2, ... of the tile and owns one 16 KiB staging box behind the operand ring.
+    // g, g+2, ... of the tile and owns one 16 KiB staging box behind the operand ring.  Tiles of a
+    // single slab (BN <= 64) alternate between the teams instead (team = accumulator stage), so
+    // that both stay busy where the epilogue, not the MMA, is the limiter.
     constexpr int SW = BN < 64 ? BN : 64;
     constexpr int NSLAB = BN / SW;
     const int q = warp & 3;            // TMEM lane quadrant this warp may access
@@ -328,8 +331,9 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const bool hb = p.n_bias > 0;
     int tile_i = 0;
     for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
-      const WorkCoord wc = decode_work<CG>(p, item, rank);
       const int acc = tile_i & 1;
+      if (NSLAB == 1 && acc != grp) continue;
+      const WorkCoord wc = decode_work<CG>(p, item, rank);
       const uint32_t acc_ph = (tile_i >> 1) & 1;
       const bool row_ok = (wc.w0 + w_i < p.Wt) && (wc.h0 + h_i < p.Ht) && (wc.n0 + n_i < p.Nt);
       mbar_wait(smem_u32(&bar_tfull[acc]), acc_ph);
@@ -337,7 +341,7 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
       const uint32_t tmem_row = tmem_base + acc * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
       bool released = false;
-      for (int sl = grp; sl < NSLAB; sl += 2) {
+      for (int sl = NSLAB == 1 ? 0 : grp; sl < NSLAB; sl += 2) {
         const int c_glob = wc.n_tile * BN + sl * SW;
         if (c_glob >= p.n_store) break;                       // team-uniform
         if (tt == 0) bulk_wait_read0();                       // previous store has left the box
