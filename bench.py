@@ -159,12 +159,27 @@ def conv_roofline(model, batch, pk):
         with open(os.environ['MT_BENCH_DUMP'], 'w') as f:
             for k, v in sorted(by_label.items(), key=lambda kv: -kv[1][1]):
                 f.write(f"{k[0]:6s} {k[1]:40s} launches {v[2]:3d}  ms {v[1]:8.3f}  TFLOP/s {v[0] / (v[1] * 1e-3) / 1e12:8.1f}\n")
-    roof = {"bound": "tensor", "kernel": "igemm_conv_kernel + igemm_wgrad_kernel (all conv launches of one iteration)",
-            "achieved": tot_f / (tot_ms * 1e-3) / 1e12 if tot_ms else None, "peak": peak, "unit": "TFLOP/s",
-            "frac": (tot_f / (tot_ms * 1e-3) / 1e12 / peak) if tot_ms else None, "traffic": None,
-            "peak_source": pk["source"], "launches": sum(v[2] for v in by_kind.values()),
-            "conv_ms_per_iter": tot_ms,
-            "by_kind": {k: {"tflops": v[0] / (v[1] * 1e-3) / 1e12, "ms": v[1], "launches": v[2]} for k, v in by_kind.items()},
+    # Dominant kernel: igemm_conv_kernel<2,256,6> on the 3x3 256->256 conv at 64x64 (forward and
+    # data-gradient launches of ResnetBlock / AdaINResnetBlock: ~25 % of the step).
+    HOT = "conv3x3s1_256->256@64x64"
+    hot = [v for k, v in by_label.items() if k[1] == HOT and k[0] in ("fwd", "dgrad")]
+    hot_f, hot_ms, hot_n = (sum(v[i] for v in hot) for i in range(3))
+    ach = hot_f / (hot_ms * 1e-3) / 1e12 if hot_ms else None
+    all_ach = tot_f / (tot_ms * 1e-3) / 1e12 if tot_ms else None
+    roof = {"bound": "tensor", "kernel": f"igemm_conv_kernel<2,256,6> on {HOT} (fwd + dgrad launches)",
+            "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak if ach else None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one N = 16 launch, ncu --set full capture in
+            # profiles/r1_ncu_conv_hot_full.txt (algorithmic: 35.7 MB in + 1.2 MB weights + 33.5 MB out,
+            # the output stays in L2)
+            "traffic": 38.43e6,
+            "peak_source": pk["source"], "launches": hot_n,
+            "flop_per_launch_n16": 2.0 * 16 * 64 * 64 * 256 * 256 * 9,
+            "ms_per_iter": hot_ms,
+            "all_convs": {"kernel": "igemm_conv_kernel + igemm_wgrad_kernel (every conv launch of one iteration)",
+                          "achieved": all_ach, "frac": all_ach / peak if all_ach else None,
+                          "launches": sum(v[2] for v in by_kind.values()), "conv_ms_per_iter": tot_ms,
+                          "by_kind": {k: {"tflops": v[0] / (v[1] * 1e-3) / 1e12, "ms": v[1], "launches": v[2]}
+                                      for k, v in by_kind.items()}},
             "top_classes": [{"kind": k[0], "shape": k[1], "tflops": v[0] / (v[1] * 1e-3) / 1e12, "ms": v[1], "launches": v[2]}
                             for k, v in top]}
     return roof

@@ -34,4 +34,4 @@ print("device ms:", [f"{d:.1f}" for d in dev])
 l0 = ops.launches(); m.optimize_parameters(0); print("mt launches / iteration:", ops.launches() - l0)
 os.environ.setdefault("MT_BENCH_DUMP", os.path.join(ROOT, "gpurun_out", f"conv_classes_b{B}.txt"))
 roof = bench.conv_roofline(m, b, bench.peaks())
-print("conv ms/iter", roof["conv_ms_per_iter"], "TFLOP/s", roof["achieved"])
+print("conv ms/iter", roof["all_convs"]["conv_ms_per_iter"], "TFLOP/s", roof["all_convs"]["achieved"])
