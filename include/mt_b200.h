@@ -69,11 +69,13 @@ int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd, con
 /* d(loss)/d(input buffer), including the reflection border rows/cols (folded later) */
 int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx, void* stream);
 /* d(loss)/d(weight) accumulated (+=) into fp32 dw_packed[taps][Cout][Cin_s] (window mode:
- * [kh][Cout][64]); mt_unpack_conv_wgrad scatters it back to OIHW. */
+ * [kh][Cout][64]); mt_unpack_conv_wgrad scatters (or adds) it back to OIHW. */
 int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
                     void* stream);
+/* accumulate != 0: dw += unpacked (straight into the parameter's .grad, what autograd's
+ * AccumulateGrad would do with a returned tensor) */
 int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
-                         int transposed, int window, float* dw, void* stream);
+                         int transposed, int window, int accumulate, float* dw, void* stream);
 /* nn.ConvTranspose2d(k=3, s=2, p=1, op=1) forward / dgrad / wgrad     blocks.py:69-73.
  * Descriptor: Hin/Win = input dims, Hout/Wout = 2*Hin, 2*Win; kh=kw=3, stride=2, zpad=1. */
 int mt_conv_transpose2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,

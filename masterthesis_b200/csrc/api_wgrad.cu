@@ -128,7 +128,8 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Cout_, int C
 // dw_packed -> dw (OIHW / IOHW fp32). Conv2d: [tap][Cout][Cin_s] (window: [kh][Cout][64]);
 // ConvTranspose2d: [tap][Cin][Cout_s].
 __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_, int kw_,
-                                    int transposed, int window, float* __restrict__ dw) {
+                                    int transposed, int window, int accumulate,
+                                    float* __restrict__ dw) {
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned n = Cout * Cin * kh * kw;
@@ -144,7 +145,7 @@ __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int 
     if (transposed) src = ((r * kw + s) * Cin + ci) * Cout_s + co;
     else if (window) src = (r * Cout + co) * 64 + s * Cin_s + ci;
     else src = ((r * kw + s) * Cout + co) * Cin_s + ci;
-    dw[i] = g[src];
+    dw[i] = accumulate ? dw[i] + g[src] : g[src];
   }
 }
 
@@ -174,12 +175,13 @@ extern "C" int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, in
 }
 
 extern "C" int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
-                                    int transposed, int window, float* dw, void* stream) {
+                                    int transposed, int window, int accumulate, float* dw,
+                                    void* stream) {
   const long long n = (long long)Cout * Cin * kh * kw;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   unpack_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, Cout, Cin, kh, kw,
-                                                                transposed, window, dw);
+                                                                transposed, window, accumulate, dw);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
 }

@@ -37,6 +37,18 @@ class ImageToNHWC(Function):
         return dimg, None, None
 
 
+def _wgrad(weight, x, dy, geom, needed):
+    """dL/dW of one conv site: added into weight.grad on the side stream when the parameter already
+    has a gradient buffer (FlatAdam's bucket view), else returned for autograd to accumulate."""
+    if not needed:
+        return None
+    gr = weight.grad
+    if gr is not None and gr.is_contiguous() and gr.dtype == torch.float32 and torch.is_grad_enabled() is False:
+        ops.conv_wgrad_into(x, dy, geom, gr)
+        return None
+    return ops.conv_wgrad(x, dy, geom)
+
+
 class ConvAct(Function):
     """[pre-padded input] -> Conv2d/ConvTranspose2d (+bias) (+activation) -> padded output
     (ConvBlock without norm: blocks.py:10-46; used by Discriminator, style encoder, shortcuts)."""
@@ -47,6 +59,7 @@ class ConvAct(Function):
         ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.act, ctx.out_pad = geom, act, out_pad
         ctx.has_bias = bias is not None
+        ctx.weight = weight
         ctx.save_for_backward(x, out if (act is not None) else None, wb)
         return out
 
@@ -60,7 +73,7 @@ class ConvAct(Function):
         else:
             dy = ops.act_bwd_fold(dout, out, op, act)
         dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
-        dw = ops.conv_wgrad(x, dy, g) if ctx.needs_input_grad[1] else None
+        dw = _wgrad(ctx.weight, x, dy, g, ctx.needs_input_grad[1])
         db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
         return dx, dw, db, None, None, None, None, None
 
@@ -80,6 +93,7 @@ class ConvNormAct(Function):
         ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
         ctx.has_bias = bias is not None
+        ctx.weight = weight
         ctx.save_for_backward(x, raw, ss, mr, p1, wb)
         return out
 
@@ -91,7 +105,7 @@ class ConvNormAct(Function):
                                          gb=_c(p1) if mode == "adain" else None,
                                          ln_w=p1 if mode == "layer" else None, C_valid=g.Cout, g_pad=op)
         dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
-        dw = ops.conv_wgrad(x, dy, g) if ctx.needs_input_grad[1] else None
+        dw = _wgrad(ctx.weight, x, dy, g, ctx.needs_input_grad[1])
         db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
         dp1 = dgb if mode == "adain" else (dlw.view_as(p1) if mode == "layer" and dlw is not None else None)
         dp2 = dlb.view_as(p1) if (mode == "layer" and dlb is not None) else None
@@ -116,6 +130,7 @@ class ResBlock(Function):
         out = ops.affine_act_fwd(raw2, ss2, act=None, res_pad=x, res_p=1, noise=noise, out_p=out_pad)
         ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
+        ctx.w1, ctx.w2 = w1, w2
         ctx.save_for_backward(x, raw1, h, raw2, ss1, mr1, ss2, mr2, gbc, wb1, wb2)
         return out
 
@@ -126,10 +141,10 @@ class ResBlock(Function):
         dout = _c(dout)
         # the adjoint of the reflection borders is applied inside the norm-backward kernels (g_pad)
         dy2, dgb2, _, _ = ops.norm_bwd(dout, raw2, ss2, mr2, mode, act=None, gb=gb, g_pad=op)
-        dw2 = ops.conv_wgrad(h, dy2, g) if ctx.needs_input_grad[2] else None
+        dw2 = _wgrad(ctx.w2, h, dy2, g, ctx.needs_input_grad[2])
         dh = ops.conv_dgrad(dy2, wb2, g, h.shape[1], h.shape[2])
         dy1, dgb1, _, _ = ops.norm_bwd(dh, raw1, ss1, mr1, mode, act=act, gb=gb, g_pad=1)
-        dw1 = ops.conv_wgrad(x, dy1, g) if ctx.needs_input_grad[1] else None
+        dw1 = _wgrad(ctx.w1, x, dy1, g, ctx.needs_input_grad[1])
         dx = None
         if ctx.needs_input_grad[0]:
             dx = ops.conv_dgrad(dy1, wb1, g, x.shape[1], x.shape[2])
@@ -160,6 +175,7 @@ class DownBlock(Function):
         out = ops.pool_add_act_fwd(c, d, "lrelu", out_pad)
         ops.reflect_border_(out, out_pad)
         ctx.geoms, ctx.out_pad = geoms, out_pad
+        ctx.ws = (wA, wB, wS)
         ctx.save_for_backward(a, b, pa, out, wbA, wbB, wbS)
         return out
 
@@ -169,13 +185,13 @@ class DownBlock(Function):
         gA, gB, gS = ctx.geoms
         need = ctx.needs_input_grad
         dd, dc = ops.pool_add_act_bwd(_c(dout), out, ctx.out_pad, "lrelu")
-        dwB = ops.conv_wgrad(b, dc, gB) if need[3] else None
+        dwB = _wgrad(ctx.ws[1], b, dc, gB, need[3])
         dbB = _bias_grad(dc, gB.Cout) if need[4] else None
         db_pad = ops.conv_dgrad(dc, wbB, gB, b.shape[1], b.shape[2])
         dyA = ops.act_bwd_fold(db_pad, b, 1, "lrelu")
-        dwA = ops.conv_wgrad(a, dyA, gA) if need[1] else None
+        dwA = _wgrad(ctx.ws[0], a, dyA, gA, need[1])
         dbA = _bias_grad(dyA, gA.Cout) if need[2] else None
-        dwS = ops.conv_wgrad(pa, dd, gS) if need[5] else None
+        dwS = _wgrad(ctx.ws[2], pa, dd, gS, need[5])
         dbS = _bias_grad(dd, gS.Cout) if need[6] else None
         da = None
         if need[0]:

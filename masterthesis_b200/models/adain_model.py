@@ -14,6 +14,7 @@ import torch
 import torch.nn.functional as F
 
 from .. import functional as Fn
+from .. import ops
 from ..optim import FlatAdam
 from .core import networks
 from .core.networks import CONTENT_PAD
@@ -193,6 +194,7 @@ class AdaINModel(Model):
             loss_d_cls = _bce(pred_cls[n:], c_org)
         loss_d = loss_d_adv + self.args.lambda_cls * loss_d_cls
         loss_d.backward()
+        ops.join_side()      # pending side-stream weight gradients land before the bucket is read
         self._scalars.update(d_adv=loss_d_adv.detach(), d_cls=loss_d_cls.detach(), d_total=loss_d.detach())
 
     # ------------------------------------------------------------------ content discriminator (:136-144)
@@ -203,6 +205,7 @@ class AdaINModel(Model):
         opt.zero_grad()
         loss_d_content = _bce(self.model.content_discriminator.run(z_c), c_org)
         loss_d_content.backward()
+        ops.join_side()      # pending side-stream weight gradients land before the bucket is read
         self._scalars.update(loss_dc=loss_d_content.detach())
         if self.dp is not None:
             self.dp.allreduce([opt])
@@ -275,6 +278,7 @@ class AdaINModel(Model):
             loss_g = loss_g + loss_g_content
             self._scalars.update(g_content=loss_g_content.detach())
         (loss_g + (world - 1) * loss_kl_zs if (world > 1 and self.reparam) else loss_g).backward()
+        ops.join_side()      # pending side-stream weight gradients land before the bucket is read
         self._scalars.update(g_adv=loss_g_adv.detach(), g_cls=loss_g_cls.detach(),
                              kl_zc=loss_kl_zc.detach(), kl_zs=loss_kl_zs.detach(),
                              l1_self_rec=loss_g_self.detach(), l1_cc_rec=loss_g_cc.detach(),
@@ -299,6 +303,7 @@ class AdaINModel(Model):
             z_sr_a, _ = torch.split(z_sr_rec, B, dim=0)
             loss_z_l1 = (F.l1_loss(z_sr_a, z_sr) + F.l1_loss(z_sr_a, z_sr)) * 10
         (loss_z_l1 + loss_g_adv2 + loss_g_cls2).backward()
+        ops.join_side()      # pending side-stream weight gradients land before the bucket is read
         self._scalars.update(l1_recon_z=loss_z_l1.detach(), gan2=loss_g_adv2.detach(),
                              gan2_cls=loss_g_cls2.detach())
 

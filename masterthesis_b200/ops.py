@@ -250,10 +250,7 @@ def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
     return dx
 
 
-@_checked
-def conv_wgrad(x, dy, g: ConvGeom):
-    """-> fp32 weight gradient in the master layout (OIHW, or IOHW for transposed)."""
-    _require_cuda(x)
+def _wgrad_launch(x, dy, g: ConvGeom, dw, accumulate, stream):
     N, Hin, Win, _ = x.shape
     L = _lib.lib()
     d = g.desc(N, Hin, Win)
@@ -266,13 +263,62 @@ def conv_wgrad(x, dy, g: ConvGeom):
     packed = torch.zeros(n, dtype=torch.float32, device=x.device)
     fn = L.mt_conv_transpose2d_wgrad if g.transposed else L.mt_conv2d_wgrad
     with _timed("wgrad", g, N, Hin, Win):
-        check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), _stream()), "conv_wgrad")
+        check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), stream), "conv_wgrad")
+    check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
+                                 int(g.window), int(accumulate), _p(dw), stream), "unpack_wgrad")
+    _count(2)
+    return packed
+
+
+@_checked
+def conv_wgrad(x, dy, g: ConvGeom):
+    """-> fp32 weight gradient in the master layout (OIHW, or IOHW for transposed)."""
+    _require_cuda(x)
     shape = (g.Cin, g.Cout, g.kh, g.kw) if g.transposed else (g.Cout, g.Cin, g.kh, g.kw)
     dw = _T.empty(shape, dtype=torch.float32, device=x.device)
-    check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
-                                 int(g.window), _p(dw), _stream()), "unpack_wgrad")
-    _count(2)
+    _wgrad_launch(x, dy, g, dw, False, _stream())
     return dw
+
+
+# Weight gradients off the critical path.  Nothing in a backward pass consumes a weight gradient
+# before the optimizer does, while the data gradient is what the next backward node waits for: the
+# wgrad kernel (tensor-bound) therefore runs on a side stream, next to the HBM-bound norm-backward
+# kernels of the main stream, and adds its result straight into the parameter's .grad (a view of the
+# optimizer's flat bucket).  The main stream joins before anything reads the bucket (join_side(),
+# called after every .backward()).  Operands are kept alive on the host side until the join: no
+# record_stream(), so the scheme is the same under CUDA-graph capture (fork / join become graph edges).
+SIDE_WGRAD = _os.environ.get("MT_WGRAD_SIDE", "1") == "1"
+_side_streams = {}
+_side_keep = []
+
+
+def _side_stream(device):
+    s = _side_streams.get(device)
+    if s is None:
+        s = _side_streams[device] = torch.cuda.Stream(device=device)
+    return s
+
+
+def conv_wgrad_into(x, dy, g: ConvGeom, grad):
+    """grad (fp32, master layout, contiguous) += dL/dW, asynchronously on the side stream."""
+    _require_cuda(x)
+    assert grad.is_contiguous() and grad.dtype == torch.float32
+    if PROFILE is not None or POISON or not SIDE_WGRAD:
+        _wgrad_launch(x, dy, g, grad, True, _stream())
+        return
+    side = _side_stream(x.device)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        packed = _wgrad_launch(x, dy, g, grad, True, side.cuda_stream)
+    _side_keep.append((x, dy, packed))
+
+
+def join_side():
+    """make the current stream wait for every pending side-stream weight gradient"""
+    if _side_keep:
+        dev = _side_keep[0][0].device
+        torch.cuda.current_stream().wait_stream(_side_streams[dev])
+        _side_keep.clear()
 
 
 # ----------------------------------------------------------------------------- layout

@@ -95,6 +95,7 @@ class FlatAdam(torch.optim.Optimizer):
 
     def zero_grad(self, set_to_none: bool = False):
         self._ensure_flat()
+        ops.join_side()               # no side-stream weight gradient may still be adding into the bucket
         self._flat['g'].zero_()
         off = 0
         for p in self._params():      # re-attach views that were replaced (p.grad = None, ...)
@@ -110,6 +111,7 @@ class FlatAdam(torch.optim.Optimizer):
     @torch.no_grad()
     def step(self, closure=None):
         self._ensure_flat()
+        ops.join_side()
         g0 = self.param_groups[0]
         ps = self._params()
         off = 0

@@ -29,6 +29,9 @@ class DataParallelGroup:
 
     def allreduce(self, optimizers):
         """sum the gradient buckets over ranks; Adam then scales by 1/world."""
+        if torch.cuda.is_available():
+            from . import ops
+            ops.join_side()
         for opt in optimizers:
             dist.all_reduce(opt.grad_bucket, op=dist.ReduceOp.SUM)
             opt.grad_scale = 1.0 / self.world
