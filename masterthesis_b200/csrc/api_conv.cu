@@ -219,8 +219,45 @@ extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void*
 
 // Sub-pixel phase launcher shared by stride-2 dgrad and ConvTranspose2d forward:
 //   out[2a+ph, 2b+pw] = sum_{r == (ph+zp) mod 2, s == (pw+zp) mod 2} A[a + (ph+zp-r)/2, ...] W[r,s]
+// The four phases are independent (disjoint output pixels).  Since one phase often cannot fill the GPU
+// (small maps: discriminator / style-encoder tails, a persistent launch of 4-64 CTAs on 148 SMs)
+// they run side by side on three auxiliary streams forked from and joined back into the caller's
+// stream with events — plain stream semantics for the caller, graph edges under capture.
+struct PhaseFork {
+  cudaStream_t aux[3];
+  cudaEvent_t fork, join[3];
+  bool ok = false, tried = false;
+  int max_ctas = 1 << 30;     // fork when no phase uses more CTAs than this (MT_PHASE_FORK, 0 = never);
+                              // measured: forking always wins (CTA-level interleaving hides the tails)
+};
+static PhaseFork g_fork;
+static bool phase_fork_ready() {
+  if (g_fork.tried) return g_fork.ok;
+  g_fork.tried = true;
+  const char* e = getenv("MT_PHASE_FORK");
+  if (e) g_fork.max_ctas = atoi(e);
+  if (g_fork.max_ctas <= 0) return false;
+  if (cudaEventCreateWithFlags(&g_fork.fork, cudaEventDisableTiming) != cudaSuccess) return false;
+  for (int i = 0; i < 3; ++i) {
+    if (cudaStreamCreateWithFlags(&g_fork.aux[i], cudaStreamNonBlocking) != cudaSuccess) return false;
+    if (cudaEventCreateWithFlags(&g_fork.join[i], cudaEventDisableTiming) != cudaSuccess) return false;
+  }
+  g_fork.ok = true;
+  return true;
+}
+static int phase_work_items(const ConvLike& q) {
+  int tw, th, tn;
+  pick_tile(128, q.Wt, q.Ht, q.Nt, q.a_mul, &tw, &th, &tn);
+  const int BN = pick_bn(q.Bn);
+  const int pix = cdiv(q.Wt, tw) * cdiv(q.Ht, th) * cdiv(q.Nt, tn);
+  const int cg = (BN >= 128 && pix >= 8) ? 2 : 1;
+  return cdiv(pix, cg) * cdiv(q.Bn, BN) * cg;          // CTAs the persistent launch would use
+}
+
 static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, long long row_pitch,
                       long long pix_pitch, long long base_off, cudaStream_t stream) {
+  ConvLike qs[4];
+  int n = 0, max_ctas = 0;
   for (int ph = 0; ph < 2; ++ph)
     for (int pw = 0; pw < 2; ++pw) {
       const int r0 = (ph + zp) & 1, s0 = (pw + zp) & 1;
@@ -237,10 +274,30 @@ static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, lo
       q.out_h_stride = 2 * row_pitch; q.out_w_stride = 2 * pix_pitch;
       q.out_off = base_off + ph * row_pitch + pw * pix_pitch;
       q.stat_part0 = (ph * 2 + pw) * (c.stat_parts / 4);
-      int rc = run_conv_like(q, stream);
+      const int ctas = phase_work_items(q);
+      if (ctas > max_ctas) max_ctas = ctas;
+      qs[n++] = q;
+    }
+  const bool fork = n > 1 && phase_fork_ready() && max_ctas <= g_fork.max_ctas;
+  if (!fork) {
+    for (int i = 0; i < n; ++i) {
+      int rc = run_conv_like(qs[i], stream);
       if (rc) return rc;
     }
-  return 0;
+    return 0;
+  }
+  if (cudaEventRecord(g_fork.fork, stream) != cudaSuccess) return -1013;
+  int rc = 0;
+  for (int i = 1; i < n && !rc; ++i) {
+    if (cudaStreamWaitEvent(g_fork.aux[i - 1], g_fork.fork, 0) != cudaSuccess) rc = -1013;
+    if (!rc) rc = run_conv_like(qs[i], g_fork.aux[i - 1]);
+    // the join is recorded even after a failed launch so that a capture is never left forked
+    if (cudaEventRecord(g_fork.join[i - 1], g_fork.aux[i - 1]) != cudaSuccess && !rc) rc = -1013;
+  }
+  const int rc0 = run_conv_like(qs[0], stream);
+  for (int i = 1; i < n; ++i)
+    if (cudaStreamWaitEvent(stream, g_fork.join[i - 1], 0) != cudaSuccess && !rc) rc = -1013;
+  return rc ? rc : rc0;
 }
 
 extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
