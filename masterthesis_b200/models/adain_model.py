@@ -7,6 +7,8 @@ discriminator phase run without an autograd graph (the reference builds one and 
 the real and fake discriminator passes are batched into one call; the 13 loss scalars are read
 back with ONE host sync per iteration instead of 13 `.item()` calls.
 """
+import contextlib
+import os
 import time
 from contextlib import contextmanager
 
@@ -169,12 +171,29 @@ class AdaINModel(Model):
                                                 torch.cat((cls_b, cls_b))), B, dim=0)
             img_fake = torch.cat((img_ba, img_ab))
             img_random = torch.cat((img_br, img_ar))
-        self.optimizer.discriminator1.zero_grad()
-        self.backward_discriminator(self.model.discriminator1, img, img_fake, c_org)
-        self._step('discriminator1')
+        # The two discriminator updates are independent (separate networks, optimizers and inputs) and
+        # their tail layers leave most SMs idle: D1 runs on an auxiliary stream next to D2.  Host
+        # order is the reference's (D1 then D2), so self.loss ends up with D2's values as there.
+        aux, cur = self._aux_stream(), torch.cuda.current_stream()
+        if aux is not None:
+            aux.wait_stream(cur)
+        with (torch.cuda.stream(aux) if aux is not None else contextlib.nullcontext()):
+            self.optimizer.discriminator1.zero_grad()
+            self.backward_discriminator(self.model.discriminator1, img, img_fake, c_org)
+            self._step('discriminator1')
         self.optimizer.discriminator2.zero_grad()
         self.backward_discriminator(self.model.discriminator2, img, img_random, c_org)
         self._step('discriminator2')
+        if aux is not None:
+            cur.wait_stream(aux)
+
+    def _aux_stream(self):
+        """second stream for the D1 || D2 overlap (MT_CONCURRENT_D=0 or the debug modes disable it)"""
+        if os.environ.get('MT_CONCURRENT_D', '1') != '1' or ops.POISON or ops.PROFILE is not None:
+            return None
+        if getattr(self, '_aux', None) is None:
+            self._aux = torch.cuda.Stream()
+        return self._aux
 
     def backward_discriminator(self, netD, real, fake, c_org):
         n = real.shape[0]

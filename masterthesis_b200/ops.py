@@ -288,15 +288,13 @@ def conv_wgrad(x, dy, g: ConvGeom):
 # called after every .backward()).  Operands are kept alive on the host side until the join: no
 # record_stream(), so the scheme is the same under CUDA-graph capture (fork / join become graph edges).
 SIDE_WGRAD = _os.environ.get("MT_WGRAD_SIDE", "1") == "1"
-_side_streams = {}
-_side_keep = []
+_side_streams = {}     # (device, main stream handle) -> side stream: one per stream that runs a backward
+_side_keep = {}        # same key -> [(x, dy, packed)] alive until that stream joined
 
 
-def _side_stream(device):
-    s = _side_streams.get(device)
-    if s is None:
-        s = _side_streams[device] = torch.cuda.Stream(device=device)
-    return s
+def _side_key(device):
+    cur = torch.cuda.current_stream(device)
+    return (device, cur.cuda_stream), cur
 
 
 def conv_wgrad_into(x, dy, g: ConvGeom, grad):
@@ -306,19 +304,25 @@ def conv_wgrad_into(x, dy, g: ConvGeom, grad):
     if PROFILE is not None or POISON or not SIDE_WGRAD:
         _wgrad_launch(x, dy, g, grad, True, _stream())
         return
-    side = _side_stream(x.device)
-    side.wait_stream(torch.cuda.current_stream())
+    key, cur = _side_key(x.device)
+    side = _side_streams.get(key)
+    if side is None:
+        side = _side_streams[key] = torch.cuda.Stream(device=x.device)
+    side.wait_stream(cur)
     with torch.cuda.stream(side):
         packed = _wgrad_launch(x, dy, g, grad, True, side.cuda_stream)
-    _side_keep.append((x, dy, packed))
+    _side_keep.setdefault(key, []).append((x, dy, packed))
 
 
 def join_side():
-    """make the current stream wait for every pending side-stream weight gradient"""
-    if _side_keep:
-        dev = _side_keep[0][0].device
-        torch.cuda.current_stream().wait_stream(_side_streams[dev])
-        _side_keep.clear()
+    """make the current stream wait for the side-stream weight gradients it forked"""
+    if not _side_keep:
+        return
+    key, cur = _side_key(torch.device("cuda", torch.cuda.current_device()))
+    pending = _side_keep.get(key)
+    if pending:
+        cur.wait_stream(_side_streams[key])
+        pending.clear()
 
 
 # ----------------------------------------------------------------------------- layout
