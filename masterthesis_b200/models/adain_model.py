@@ -161,8 +161,8 @@ class AdaINModel(Model):
         B = self.args.batch_size
         with torch.no_grad():
             cls_a, cls_b = torch.split(c_org, B, dim=0)
-            z_ca, z_cb = torch.split(self.Ec(img), B, dim=0)
-            z_s, _, _ = self.Es(img, c_org)
+            z_c, (z_s, _, _) = self._encode(img, c_org)
+            z_ca, z_cb = torch.split(z_c, B, dim=0)
             z_sa, z_sb = torch.split(z_s, B, dim=0)
             z_sr = self.get_z_random(B, self.args.latent_dim)
             img_ba, img_br = torch.split(self.G(torch.cat((z_cb, z_cb)), torch.cat((z_sa, z_sr)),
@@ -186,6 +186,26 @@ class AdaINModel(Model):
         self._step('discriminator2')
         if aux is not None:
             cur.wait_stream(aux)
+
+    def _fork(self, fn_main, fn_aux):
+        """(fn_main(), fn_aux()) with fn_aux on the auxiliary stream.  For INDEPENDENT networks only
+        (no shared parameters): autograd runs each one's backward on the stream of its forward, so
+        the overlap holds in the backward pass too.  Host order is fn_main then fn_aux."""
+        aux = self._aux_stream()
+        if aux is None:
+            return fn_main(), fn_aux()
+        cur = torch.cuda.current_stream()
+        aux.wait_stream(cur)          # fork point BEFORE fn_main is enqueued: aux does not wait for it
+        a = fn_main()
+        with torch.cuda.stream(aux):
+            b = fn_aux()
+        cur.wait_stream(aux)
+        return a, b
+
+    def _encode(self, img, c):
+        """(Ec(img), Es(img, c)): the style encoder (no norms, small maps) leaves SMs idle that the
+        content encoder's convs can use.  Ec first on the host, as in the reference (RNG draw order)."""
+        return self._fork(lambda: self.Ec(img), lambda: self.Es(img, c))
 
     def _aux_stream(self):
         """second stream for the D1 || D2 overlap (MT_CONCURRENT_D=0 or the debug modes disable it)"""
@@ -260,9 +280,8 @@ class AdaINModel(Model):
         B = self.args.batch_size
         world = 1 if self.dp is None else self.dp.world
         cls_a, cls_b = torch.split(c_org, B, dim=0)
-        z_c = self.Ec(img)
+        z_c, (z_s, mu, logvar) = self._encode(img, c_org)
         z_ca, z_cb = torch.split(z_c, B, dim=0)
-        z_s, mu, logvar = self.Es(img, c_org)
         z_sa, z_sb = torch.split(z_s, B, dim=0)
         img_ba, img_aa = torch.split(self.G(torch.cat((z_cb, z_ca)), torch.cat((z_sa, z_sa)),
                                             torch.cat((cls_a, cls_a))), B, dim=0)
@@ -270,8 +289,12 @@ class AdaINModel(Model):
                                             torch.cat((cls_b, cls_b))), B, dim=0)
         img_fake = torch.cat((img_ba, img_ab))
         img_self = torch.cat((img_aa, img_bb))
-        z_c_rec_b, z_c_rec_a = torch.split(self.Ec(img_fake), B, dim=0)
-        z_s_rec, _, _ = self.Es(img_fake, c_org)
+        # the adversarial branch (D1 on the fakes) is independent of the reconstruction branch
+        with self._frozen('discriminator1'):
+            z_c_rec, ((z_s_rec, _, _), (loss_g_adv, loss_g_cls)) = self._fork(
+                lambda: self.Ec(img_fake),
+                lambda: (self.Es(img_fake, c_org), self._g_adv(self.model.discriminator1, img_fake, c_org)))
+        z_c_rec_b, z_c_rec_a = torch.split(z_c_rec, B, dim=0)
         z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B, dim=0)
         img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
                            torch.cat((cls_a, cls_b)))
@@ -279,8 +302,6 @@ class AdaINModel(Model):
         if self.args.use_dis_content:          # backward_content_discriminator (:334-337)
             with self._frozen('content_discriminator'):
                 loss_g_content = _bce(self.model.content_discriminator.run(z_c), 1 - c_org)
-        with self._frozen('discriminator1'):
-            loss_g_adv, loss_g_cls = self._g_adv(self.model.discriminator1, img_fake, c_org)
         loss_g_self = F.l1_loss(img_self, img) * self.args.lambda_rec
         loss_g_cc = F.l1_loss(img_recon, img) * self.args.lambda_rec
         N, Hp, Wp, _ = z_c.shape
@@ -297,7 +318,7 @@ class AdaINModel(Model):
             loss_g = loss_g + loss_g_content
             self._scalars.update(g_content=loss_g_content.detach())
         (loss_g + (world - 1) * loss_kl_zs if (world > 1 and self.reparam) else loss_g).backward()
-        ops.join_side()      # pending side-stream weight gradients land before the bucket is read
+        ops.join_side(all_streams=True)      # incl. the style encoder's, whose backward ran on the aux stream
         self._scalars.update(g_adv=loss_g_adv.detach(), g_cls=loss_g_cls.detach(),
                              kl_zc=loss_kl_zc.detach(), kl_zs=loss_kl_zs.detach(),
                              l1_self_rec=loss_g_self.detach(), l1_cc_rec=loss_g_cc.detach(),
@@ -313,8 +334,9 @@ class AdaINModel(Model):
         # discriminator2 otherwise (:378)
         dname = 'discriminator1' if self.args.ms_dis else 'discriminator2'
         with self._frozen(dname, 'style_encoder'):
-            loss_g_adv2, loss_g_cls2 = self._g_adv(self.model[dname], img_random, c_org)
-            z_sr_rec, mu2, _ = self.Es(img_random, c_org)
+            (loss_g_adv2, loss_g_cls2), (z_sr_rec, mu2, _) = self._fork(
+                lambda: self._g_adv(self.model[dname], img_random, c_org),
+                lambda: self.Es(img_random, c_org))
         if self.reparam:
             mu2_a, mu2_b = torch.split(mu2, B, dim=0)
             loss_z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10
@@ -322,7 +344,7 @@ class AdaINModel(Model):
             z_sr_a, _ = torch.split(z_sr_rec, B, dim=0)
             loss_z_l1 = (F.l1_loss(z_sr_a, z_sr) + F.l1_loss(z_sr_a, z_sr)) * 10
         (loss_z_l1 + loss_g_adv2 + loss_g_cls2).backward()
-        ops.join_side()      # pending side-stream weight gradients land before the bucket is read
+        ops.join_side(all_streams=True)
         self._scalars.update(l1_recon_z=loss_z_l1.detach(), gan2=loss_g_adv2.detach(),
                              gan2_cls=loss_g_cls2.detach())
 

@@ -288,8 +288,9 @@ def conv_wgrad(x, dy, g: ConvGeom):
 # called after every .backward()).  Operands are kept alive on the host side until the join: no
 # record_stream(), so the scheme is the same under CUDA-graph capture (fork / join become graph edges).
 SIDE_WGRAD = _os.environ.get("MT_WGRAD_SIDE", "1") == "1"
-_side_streams = {}     # (device, main stream handle) -> side stream: one per stream that runs a backward
-_side_keep = {}        # same key -> [(x, dy, packed)] alive until that stream joined
+_side_streams = {}     # device -> THE side stream: every wgrad of the process runs on it, in order,
+                       # so that two backward streams adding into the same .grad cannot interleave
+_side_keep = {}        # (device, origin stream handle) -> [(x, dy, packed)] alive until that origin joined
 
 
 def _side_key(device):
@@ -305,24 +306,29 @@ def conv_wgrad_into(x, dy, g: ConvGeom, grad):
         _wgrad_launch(x, dy, g, grad, True, _stream())
         return
     key, cur = _side_key(x.device)
-    side = _side_streams.get(key)
+    side = _side_streams.get(x.device)
     if side is None:
-        side = _side_streams[key] = torch.cuda.Stream(device=x.device)
+        side = _side_streams[x.device] = torch.cuda.Stream(device=x.device)
     side.wait_stream(cur)
     with torch.cuda.stream(side):
         packed = _wgrad_launch(x, dy, g, grad, True, side.cuda_stream)
     _side_keep.setdefault(key, []).append((x, dy, packed))
 
 
-def join_side():
-    """make the current stream wait for the side-stream weight gradients it forked"""
+def join_side(all_streams=False):
+    """Make the current stream wait for the side-stream weight gradients forked from it; with
+    `all_streams` also for those forked by backward nodes that ran on other streams (a network whose
+    forward was issued on an auxiliary stream has its backward there)."""
     if not _side_keep:
         return
     key, cur = _side_key(torch.device("cuda", torch.cuda.current_device()))
-    pending = _side_keep.get(key)
-    if pending:
-        cur.wait_stream(_side_streams[key])
-        pending.clear()
+    waited = False
+    for k, pending in _side_keep.items():
+        if pending and (all_streams or k == key):
+            if not waited:
+                cur.wait_stream(_side_streams[k[0]])
+                waited = True
+            pending.clear()
 
 
 # ----------------------------------------------------------------------------- layout
