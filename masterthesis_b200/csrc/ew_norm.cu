@@ -454,21 +454,33 @@ act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16*
 using namespace mt;
 #define ST(s) ((cudaStream_t)(s))
 
-// grid (pixel chunks, N) for the per-plane kernels: ~2 resident CTAs per SM (each thread keeps
-// EW_UNROLL loads per tensor in flight and amortises its per-channel coefficients over many
-// pixels), >= 4 pixels per pixel lane
-static int ew_ctas_per_sm() {
+// Grid (pixel chunks, N) of the per-plane kernels: exactly ONE wave — SMs x the number of CTAs
+// of THIS kernel instantiation that fit on an SM (register-limited: 2-3 for the 66-100 register
+// kernels here).  A fixed "4 CTAs per SM" grid ran 1.33 waves on the 3-resident kernels, i.e. a
+// third of the time with a quarter of the machine (ncu: launch__waves_per_multiprocessor).
+// MT_EW_CTAS overrides the per-SM count.
+static int ew_ctas_override() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("MT_EW_CTAS"); v = e ? atoi(e) : 4; if (v < 1) v = 1; }
+  if (v < 0) { const char* e = getenv("MT_EW_CTAS"); v = e ? atoi(e) : 0; if (v < 0) v = 0; }
   return v;
 }
-static dim3 plane_grid(int N, int HW, int C) {
+template <typename K>
+static int resident_ctas(K kern, size_t smem) {
+  if (ew_ctas_override()) return ew_ctas_override();
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, 256, smem) != cudaSuccess || n < 1) n = 2;
+  return n;
+}
+static int plane_chunks(int N, int HW, int C, int ctas_per_sm) {
   const int lanes = 256 / (C / 8);
-  int chunks = (ew_ctas_per_sm() * NUM_SMS + N - 1) / N;
+  int chunks = (ctas_per_sm * NUM_SMS) / N;                 // floor: never spill into a second wave
   const int max_chunks = (HW + lanes * 4 - 1) / (lanes * 4);
   if (chunks > max_chunks) chunks = max_chunks;
   if (chunks < 1) chunks = 1;
-  return dim3((unsigned)chunks, (unsigned)N);
+  return chunks;
+}
+static dim3 plane_grid(int N, int HW, int C, int ctas_per_sm) {
+  return dim3((unsigned)plane_chunks(N, HW, C, ctas_per_sm), (unsigned)N);
 }
 
 static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int H, int W,
@@ -479,15 +491,15 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
   if (e != cudaSuccess) return -(int)e;
   const int V = C / 8;
   const int lanes = 256 / V;
-  int chunks = (ew_ctas_per_sm() * NUM_SMS + N - 1) / N;
-  const int max_chunks = (HW + lanes * 4 - 1) / (lanes * 4);
-  if (chunks > max_chunks) chunks = max_chunks;
-  if (chunks < 1) chunks = 1;
   const size_t smem = (size_t)lanes * V * 16 * sizeof(float);
   const FastDiv dw = make_fastdiv(W);
   if ((long long)H * W >= (1 << 24)) return -1005;
-#define MT_RED(B, A) plane_reduce_kernel<B, A><<<N * chunks, 256, smem, st>>>(                  \
-      (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out)
+#define MT_RED(B, A)                                                                              \
+  do {                                                                                            \
+    const int chunks = plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<B, A>, smem));    \
+    plane_reduce_kernel<B, A><<<N * chunks, 256, smem, st>>>(                                     \
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out); \
+  } while (0)
   if (!bwd) MT_RED(false, 0);
   else if (act == MT_ACT_RELU) MT_RED(true, 1);
   else if (act == MT_ACT_LRELU) MT_RED(true, 2);
@@ -515,7 +527,7 @@ extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, i
   if (C % 8 || C / 8 > 256) return -1003;
   if ((long long)H * W >= (1 << 24)) return -1005;
   const FastDiv dw = make_fastdiv(W);
-#define MT_AFF(A) affine_act_fwd_kernel<A><<<plane_grid(N, H * W, C), 256, 0, ST(stream)>>>(     \
+#define MT_AFF(A) affine_act_fwd_kernel<A><<<plane_grid(N, H * W, C, resident_ctas(affine_act_fwd_kernel<A>, 0)), 256, 0, ST(stream)>>>(     \
       (const __nv_bfloat16*)x, ss, H, W, dw, C, slope, (const __nv_bfloat16*)res_pad, res_p, noise, \
       (__nv_bfloat16*)out_pad, out_p)
   switch (act) {
@@ -546,7 +558,7 @@ extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const 
   if (C % 8 || C / 8 > 256) return -1003;
   if ((long long)H * W >= (1 << 24)) return -1005;
   const FastDiv dw = make_fastdiv(W);
-#define MT_APP(A) norm_bwd_apply_kernel<A><<<plane_grid(N, H * W, C), 256, 0, ST(stream)>>>(     \
+#define MT_APP(A) norm_bwd_apply_kernel<A><<<plane_grid(N, H * W, C, resident_ctas(norm_bwd_apply_kernel<A>, 0)), 256, 0, ST(stream)>>>(     \
       (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, H, W, dw, C, g_pad, slope,       \
       (__nv_bfloat16*)dx)
   if (act == MT_ACT_RELU) MT_APP(1);
