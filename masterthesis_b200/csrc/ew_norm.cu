@@ -17,23 +17,32 @@ namespace mt {
 // and fold(g) is formed on the fly (only pixels next to the border have extra terms).
 constexpr int EW_UNROLL = 4;
 
-__device__ __forceinline__ void add_fold_extras(const __nv_bfloat16* __restrict__ g, int n, int h, int w,
-                                                int H, int W, int C, int v, int gp, float (&gv)[8]) {
+// Index arithmetic of the per-plane kernels is 32-bit relative to a per-image base pointer (one
+// image has < 2^31 elements, checked by the launchers): with 64-bit multiplies per access the
+// kernels spent ~40 of their ~170 instructions per 16-byte vector on addresses and were issue-bound
+// at 2 TB/s (ncu: smsp__issue_active 51 %, 148 IMAD in the unrolled loop).
+__device__ __forceinline__ bool near_border(int h, int w, int H, int W, int gp) {
+  return (unsigned)(h - 1) < (unsigned)gp || (unsigned)(H - 2 - h) < (unsigned)gp ||
+         (unsigned)(w - 1) < (unsigned)gp || (unsigned)(W - 2 - w) < (unsigned)gp;
+}
+// gimg: the padded gradient image of this sample, already offset by the thread's channel vector
+__device__ __forceinline__ void add_fold_extras(const __nv_bfloat16* __restrict__ gimg, int h, int w,
+                                                int H, int W, int C, int gp, float (&gv)[8]) {
+  if (!near_border(h, w, H, W, gp)) return;
   int hs[3], ws[3];
   const int nh = reflect_fold_sources(h, H, gp, hs), nw = reflect_fold_sources(w, W, gp, ws);
-  if (nh * nw == 1) return;
-  const int Hp = H + 2 * gp, Wp = W + 2 * gp;
+  const int Wp = W + 2 * gp;
   for (int a = 0; a < nh; ++a)
     for (int b = 0; b < nw; ++b) {
       if (a == 0 && b == 0) continue;                       // the main term is already loaded
       float f[8];
-      load8(g + (((long long)n * Hp + hs[a]) * Wp + ws[b]) * C + v * 8, f);
+      load8(gimg + (hs[a] * Wp + ws[b]) * C, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) gv[j] += f[j];
     }
 }
 
-template <bool kBackward, int ACT>
+template <bool kBackward, int ACT, bool GP>
 __global__ void __launch_bounds__(256, 2)
 plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ g,
                     const float* __restrict__ ss, int H, int W, FastDiv divW, int C, int gp, int chunks,
@@ -45,7 +54,10 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   const int per = (HW + chunks - 1) / chunks;
   const int p0 = chunk * per, p1 = min(HW, p0 + per);
-  const int Hp = H + 2 * gp, Wp = W + 2 * gp;
+  const int Wp = W + 2 * gp;
+  const __nv_bfloat16* ximg = x + (size_t)n * HW * C + v * 8;
+  const __nv_bfloat16* gimg = kBackward ? g + (size_t)n * (H + 2 * gp) * Wp * C + v * 8 : nullptr;
+  const int goff = (gp * Wp + gp) * C;          // interior origin of the padded gradient
   float a0[8], a1[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) a0[j] = a1[j] = 0.f;
@@ -61,14 +73,15 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
   if (pl < lanes) {
     for (int pb = p0 + pl; pb < p1; pb += EW_UNROLL * lanes) {
       uint4 xr[EW_UNROLL], gr[EW_UNROLL];
+      int hh[EW_UNROLL];
 #pragma unroll
       for (int u = 0; u < EW_UNROLL; ++u) {
         const int p = pb + u * lanes;
         if (p < p1) {
-          xr[u] = ldg16(x + ((long long)n * HW + p) * C + v * 8);
+          xr[u] = ldg16(ximg + p * C);
           if (kBackward) {   // (h+gp)*Wp + w+gp == p + 2*gp*h + gp*Wp + gp
-            const int h = gp ? fast_div(p, divW) : 0;
-            gr[u] = ldg16(g + ((long long)n * Hp * Wp + p + 2 * gp * h + gp * Wp + gp) * C + v * 8);
+            hh[u] = GP ? fast_div(p, divW) : 0;
+            gr[u] = ldg16(gimg + goff + (p + 2 * gp * hh[u]) * C);
           }
         }
       }
@@ -84,7 +97,7 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
           } else {
             float gv[8];
             cvt8(gr[u], gv);
-            if (gp) { const int h = fast_div(p, divW); add_fold_extras(g, n, h, p - h * W, H, W, C, v, gp, gv); }
+            if (GP) add_fold_extras(gimg, hh[u], p - hh[u] * W, H, W, C, gp, gv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float y = xv[j] * sc[j] + sh[j];           // pre-activation (A*xhat + B)
@@ -228,7 +241,7 @@ norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N
 // out_pad[n, h+po, w+po, :] = act(x*scale + shift) (+ res_pad[n, h+pr, w+pr, :]) (+ noise)
 // grid = (pixel chunks, N); a thread owns ONE 8-channel vector (its scale/shift live in registers)
 // and walks pixels, so a warp reads/writes 512 contiguous bytes per pixel row.
-template <int ACT>
+template <int ACT, bool RES, bool NOISE>
 __global__ void __launch_bounds__(256, 2)
 affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ss, int H, int W,
                       FastDiv divW, int C, float slope, const __nv_bfloat16* __restrict__ res, int pr,
@@ -248,43 +261,47 @@ affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
       sc[2 * j] = q.x; sh[2 * j] = q.y; sc[2 * j + 1] = q.z; sh[2 * j + 1] = q.w;
     }
   }
-  const int Hr = H + 2 * pr, Wr = W + 2 * pr, Ho = H + 2 * po, Wo = W + 2 * po;
+  const int Wr = W + 2 * pr, Wo = W + 2 * po;
+  // per-image bases (already at the interior origin and at this thread's channel vector)
+  const __nv_bfloat16* ximg = x + (size_t)n * HW * C + v * 8;
+  const __nv_bfloat16* rimg = RES ? res + ((size_t)n * (H + 2 * pr) * Wr + pr * Wr + pr) * C + v * 8 : nullptr;
+  const float* nimg = NOISE ? noise + (size_t)n * HW * C + v * 8 : nullptr;
+  __nv_bfloat16* oimg = out + ((size_t)n * (H + 2 * po) * Wo + po * Wo + po) * C + v * 8;
+  const bool need_h = (RES && pr) || po;
   const int stride = gridDim.x * lanes;
   for (int pb = blockIdx.x * lanes + pl; pb < HW; pb += EW_UNROLL * stride) {
     uint4 xr[EW_UNROLL], rr[EW_UNROLL];
+    int hh[EW_UNROLL];
 #pragma unroll
     for (int u = 0; u < EW_UNROLL; ++u) {
       const int p = pb + u * stride;
       if (p < HW) {
-        xr[u] = ldg16(x + ((long long)n * HW + p) * C + v * 8);
-        if (res) {
-          const int h = pr ? fast_div(p, divW) : 0;
-          rr[u] = ldg16(res + ((long long)n * Hr * Wr + p + 2 * pr * h + pr * Wr + pr) * C + v * 8);
-        }
+        xr[u] = ldg16(ximg + p * C);
+        hh[u] = need_h ? fast_div(p, divW) : 0;
+        if (RES) rr[u] = ldg16(rimg + (p + 2 * pr * hh[u]) * C);
       }
     }
 #pragma unroll
     for (int u = 0; u < EW_UNROLL; ++u) {
       const int p = pb + u * stride;
       if (p < HW) {
-        const int h = po ? fast_div(p, divW) : 0;
         float f[8];
         cvt8(xr[u], f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) f[j] = act_fwd_t<ACT>(f[j] * sc[j] + sh[j], slope);
-        if (res) {
+        if (RES) {
           float r[8];
           cvt8(rr[u], r);
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] += r[j];
         }
-        if (noise) {
+        if (NOISE) {
           float r[8];
-          load8f(noise + ((long long)n * HW + p) * C + v * 8, r);
+          load8f(nimg + p * C, r);
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] += r[j];
         }
-        store8(out + ((long long)n * Ho * Wo + p + 2 * po * h + po * Wo + po) * C + v * 8, f);
+        store8(oimg + (p + 2 * po * hh[u]) * C, f);
       }
     }
   }
@@ -356,7 +373,7 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
 
 // dx = c0*(fold(g)*act'(y)) + c1*x + c2      grid = (pixel chunks, N), coefficients in registers;
 // g is padded by gp (0: dense) and folded on the fly like in plane_reduce_kernel<true>.
-template <int ACT>
+template <int ACT, bool GP>
 __global__ void __launch_bounds__(256, 2)
 norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
                       const float* __restrict__ ss, const float* __restrict__ coef, int H, int W,
@@ -365,7 +382,11 @@ norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* 
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   if (pl >= lanes) return;
   const int n = blockIdx.y;
-  const int Hp = H + 2 * gp, Wp = W + 2 * gp;
+  const int Wp = W + 2 * gp;
+  const __nv_bfloat16* ximg = x + (size_t)n * HW * C + v * 8;
+  const __nv_bfloat16* gimg = g + (size_t)n * (H + 2 * gp) * Wp * C + v * 8;
+  __nv_bfloat16* dimg = dx + (size_t)n * HW * C + v * 8;
+  const int goff = (gp * Wp + gp) * C;
   float sc[8], sh[8], c0[8], c1[8], c2[8];
   const float* s = ss + ((long long)n * C + v * 8) * 2;
   const float* cf = coef + ((long long)n * C + v * 8) * 3;
@@ -390,13 +411,14 @@ norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* 
   const int stride = gridDim.x * lanes;
   for (int pb = blockIdx.x * lanes + pl; pb < HW; pb += EW_UNROLL * stride) {
     uint4 xr[EW_UNROLL], gr[EW_UNROLL];
+    int hh[EW_UNROLL];
 #pragma unroll
     for (int u = 0; u < EW_UNROLL; ++u) {
       const int p = pb + u * stride;
       if (p < HW) {
-        const int h = gp ? fast_div(p, divW) : 0;
-        xr[u] = ldg16(x + ((long long)n * HW + p) * C + v * 8);
-        gr[u] = ldg16(g + ((long long)n * Hp * Wp + p + 2 * gp * h + gp * Wp + gp) * C + v * 8);
+        hh[u] = GP ? fast_div(p, divW) : 0;
+        xr[u] = ldg16(ximg + p * C);
+        gr[u] = ldg16(gimg + goff + (p + 2 * gp * hh[u]) * C);
       }
     }
 #pragma unroll
@@ -406,13 +428,13 @@ norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* 
         float xv[8], gv[8], o[8];
         cvt8(xr[u], xv);
         cvt8(gr[u], gv);
-        if (gp) { const int h = fast_div(p, divW); add_fold_extras(g, n, h, p - h * W, H, W, C, v, gp, gv); }
+        if (GP) add_fold_extras(gimg, hh[u], p - hh[u] * W, H, W, C, gp, gv);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float y = xv[j] * sc[j] + sh[j];
           o[j] = c0[j] * (gv[j] * act_grad_pre_t<ACT>(y, slope)) + c1[j] * xv[j] + c2[j];
         }
-        store8(dx + ((long long)n * HW + p) * C + v * 8, o);
+        store8(dimg + p * C, o);
       }
     }
   }
@@ -483,6 +505,11 @@ static dim3 plane_grid(int N, int HW, int C, int ctas_per_sm) {
   return dim3((unsigned)plane_chunks(N, HW, C, ctas_per_sm), (unsigned)N);
 }
 
+// per-image element counts must fit 32-bit offsets (padded extents included)
+static bool image_fits(int H, int W, int C, int pad) {
+  return (long long)(H + 2 * pad) * (W + 2 * pad) * C < (1ll << 31) && (long long)H * W < (1 << 24);
+}
+
 static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int H, int W,
                          int C, int gp, int act, float slope, float* out, cudaStream_t st) {
   const int HW = H * W;
@@ -493,17 +520,19 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
   const int lanes = 256 / V;
   const size_t smem = (size_t)lanes * V * 16 * sizeof(float);
   const FastDiv dw = make_fastdiv(W);
-  if ((long long)H * W >= (1 << 24)) return -1005;
-#define MT_RED(B, A)                                                                              \
+  if (!image_fits(H, W, C, gp)) return -1005;
+#define MT_RED(B, A, G)                                                                           \
   do {                                                                                            \
-    const int chunks = plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<B, A>, smem));    \
-    plane_reduce_kernel<B, A><<<N * chunks, 256, smem, st>>>(                                     \
+    const int chunks = plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<B, A, G>, smem)); \
+    plane_reduce_kernel<B, A, G><<<N * chunks, 256, smem, st>>>(                                  \
         (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out); \
   } while (0)
-  if (!bwd) MT_RED(false, 0);
-  else if (act == MT_ACT_RELU) MT_RED(true, 1);
-  else if (act == MT_ACT_LRELU) MT_RED(true, 2);
-  else MT_RED(true, 0);
+#define MT_RED_G(A) do { if (gp) MT_RED(true, A, true); else MT_RED(true, A, false); } while (0)
+  if (!bwd) MT_RED(false, 0, false);
+  else if (act == MT_ACT_RELU) MT_RED_G(1);
+  else if (act == MT_ACT_LRELU) MT_RED_G(2);
+  else MT_RED_G(0);
+#undef MT_RED_G
 #undef MT_RED
   return cuda_rc();
 }
@@ -525,11 +554,20 @@ extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, i
                                  int act, float slope, const void* res_pad, int res_p,
                                  const float* noise, void* out_pad, int out_p, void* stream) {
   if (C % 8 || C / 8 > 256) return -1003;
-  if ((long long)H * W >= (1 << 24)) return -1005;
+  if (!image_fits(H, W, C, res_p > out_p ? res_p : out_p)) return -1005;
   const FastDiv dw = make_fastdiv(W);
-#define MT_AFF(A) affine_act_fwd_kernel<A><<<plane_grid(N, H * W, C, resident_ctas(affine_act_fwd_kernel<A>, 0)), 256, 0, ST(stream)>>>(     \
+#define MT_AFF3(A, R, Z)                                                                          \
+  affine_act_fwd_kernel<A, R, Z><<<plane_grid(N, H * W, C, resident_ctas(affine_act_fwd_kernel<A, R, Z>, 0)), \
+                                   256, 0, ST(stream)>>>(                                         \
       (const __nv_bfloat16*)x, ss, H, W, dw, C, slope, (const __nv_bfloat16*)res_pad, res_p, noise, \
       (__nv_bfloat16*)out_pad, out_p)
+#define MT_AFF(A)                                                                                 \
+  do {                                                                                            \
+    if (res_pad && noise) MT_AFF3(A, true, true);                                                 \
+    else if (res_pad) MT_AFF3(A, true, false);                                                    \
+    else if (noise) MT_AFF3(A, false, true);                                                      \
+    else MT_AFF3(A, false, false);                                                                \
+  } while (0)
   switch (act) {
     case MT_ACT_RELU: MT_AFF(1); break;
     case MT_ACT_LRELU: MT_AFF(2); break;
@@ -537,6 +575,7 @@ extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, i
     default: MT_AFF(0); break;
   }
 #undef MT_AFF
+#undef MT_AFF3
   return cuda_rc();
 }
 extern "C" int mt_norm_bwd_reduce(const void* g, int g_pad, const void* x, const float* ss, int N, int H,
@@ -556,15 +595,18 @@ extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const 
                                  const float* coef, int N, int H, int W, int C, int act, float slope,
                                  void* dx, void* stream) {
   if (C % 8 || C / 8 > 256) return -1003;
-  if ((long long)H * W >= (1 << 24)) return -1005;
+  if (!image_fits(H, W, C, g_pad)) return -1005;
   const FastDiv dw = make_fastdiv(W);
-#define MT_APP(A) norm_bwd_apply_kernel<A><<<plane_grid(N, H * W, C, resident_ctas(norm_bwd_apply_kernel<A>, 0)), 256, 0, ST(stream)>>>(     \
-      (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, H, W, dw, C, g_pad, slope,       \
-      (__nv_bfloat16*)dx)
+#define MT_APP2(A, G)                                                                             \
+  norm_bwd_apply_kernel<A, G><<<plane_grid(N, H * W, C, resident_ctas(norm_bwd_apply_kernel<A, G>, 0)), 256, 0, \
+                                ST(stream)>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, H, \
+                                              W, dw, C, g_pad, slope, (__nv_bfloat16*)dx)
+#define MT_APP(A) do { if (g_pad) MT_APP2(A, true); else MT_APP2(A, false); } while (0)
   if (act == MT_ACT_RELU) MT_APP(1);
   else if (act == MT_ACT_LRELU) MT_APP(2);
   else MT_APP(0);
 #undef MT_APP
+#undef MT_APP2
   return cuda_rc();
 }
 extern "C" int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C,
