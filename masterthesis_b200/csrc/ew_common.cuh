@@ -116,7 +116,10 @@ __device__ __forceinline__ float act_grad_pre(float y, int act, float slope) {
   return 1.f;
 }
 
+// Flat-index kernels decompose a 32-bit index (a 64-bit division costs ~5x a 32-bit one and these
+// kernels do three per element): more than 2^31 work items yields grid 0, i.e. a launch error.
 static inline int grid_for(long long work_items, int block, int max_waves = 8) {
+  if (work_items >= (1ll << 31)) return 0;
   long long b = (work_items + block - 1) / block;
   const long long cap = (long long)NUM_SMS * max_waves;
   if (b > cap) b = cap;

@@ -12,9 +12,8 @@ __global__ void image_to_nhwc_kernel(const float* __restrict__ img, const float*
                                      __nv_bfloat16* __restrict__ out) {
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = Cs / 8;
   const long long total = (long long)N * Hp * Wp * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int wp = (int)(t % Wp); t /= Wp;
     const int hp = (int)(t % Hp); const int n = (int)(t / Hp);
     const int h = reflect_src(hp, H, p), w = reflect_src(wp, W, p);
@@ -27,7 +26,7 @@ __global__ void image_to_nhwc_kernel(const float* __restrict__ img, const float*
       else if (c < Ci + nd) x = __ldg(onehot + (long long)n * nd + (c - Ci));
       f[j] = x;
     }
-    store8(out + i * 8, f);
+    store8(out + (size_t)i * 8, f);
   }
 }
 
@@ -36,9 +35,8 @@ __global__ void image_grad_kernel(const __nv_bfloat16* __restrict__ dpad, int N,
                                   int W, int p, int Cs, float* __restrict__ dimg) {
   const int Wp = W + 2 * p, Hp = H + 2 * p;
   const long long total = (long long)N * H * W;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int w = (int)(i % W); long long t = i / W;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int w = (int)(i % W); unsigned t = i / W;
     const int h = (int)(t % H); const int n = (int)(t / H);
     int hs[3], ws[3];
     const int nh = reflect_fold_sources(h, H, p, hs), nw = reflect_fold_sources(w, W, p, ws);
@@ -60,9 +58,8 @@ __global__ void reflect_border_kernel(__nv_bfloat16* __restrict__ buf, int N, in
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const int border_px = Hp * Wp - H * W;
   const long long total = (long long)N * border_px * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     int b = (int)(t % border_px); const int n = (int)(t / border_px);
     int hp, wp;
     if (b < 2 * p * Wp) {            // full top and bottom rows
@@ -86,9 +83,8 @@ __global__ void reflect_fold_kernel(const __nv_bfloat16* __restrict__ dpad, int 
                                     int C, int p, __nv_bfloat16* __restrict__ dense) {
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const long long total = (long long)N * H * W * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % W); t /= W;
     const int h = (int)(t % H); const int n = (int)(t / H);
     int hs[3], ws[3];
@@ -102,7 +98,7 @@ __global__ void reflect_fold_kernel(const __nv_bfloat16* __restrict__ dpad, int 
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] += f[j];
       }
-    store8(dense + i * 8, acc);
+    store8(dense + (size_t)i * 8, acc);
   }
 }
 
@@ -111,15 +107,14 @@ __global__ void add_interior_kernel(__nv_bfloat16* __restrict__ dpad, const __nv
                                     int N, int H, int W, int C, int p) {
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const long long total = (long long)N * H * W * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % W); t /= W;
     const int h = (int)(t % H); const int n = (int)(t / H);
     __nv_bfloat16* d = dpad + (((long long)n * Hp + h + p) * Wp + w + p) * C + v * 8;
     float a[8], b[8];
     load8(d, a);
-    load8(dense + i * 8, b);
+    load8(dense + (size_t)i * 8, b);
 #pragma unroll
     for (int j = 0; j < 8; ++j) a[j] += b[j];
     store8(d, a);

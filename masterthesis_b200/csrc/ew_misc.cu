@@ -12,9 +12,8 @@ avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int p, int N, int H, in
                     __nv_bfloat16* __restrict__ out) {
   const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * Ho * Wo * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % Wo); t /= Wo;
     const int h = (int)(t % Ho); const int n = (int)(t / Ho);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -29,7 +28,7 @@ avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int p, int N, int H, in
       }
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] *= 0.25f;
-    store8(out + i * 8, acc);
+    store8(out + (size_t)i * 8, acc);
   }
 }
 
@@ -39,9 +38,8 @@ avgpool2_bwd_add_kernel(const __nv_bfloat16* __restrict__ dpo, __nv_bfloat16* __
                         int p, int N, int H, int W, int C) {
   const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * H * W * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % W); t /= W;
     const int h = (int)(t % H); const int n = (int)(t / H);
     if (h / 2 >= Ho || w / 2 >= Wo) continue;
@@ -62,9 +60,8 @@ pool_add_act_fwd_kernel(const __nv_bfloat16* __restrict__ c, const __nv_bfloat16
                         __nv_bfloat16* __restrict__ out, int po) {
   const int Ho = H / 2, Wo = W / 2, V = C / 8;
   const long long total = (long long)N * Ho * Wo * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % Wo); t /= Wo;
     const int h = (int)(t % Ho); const int n = (int)(t / Ho);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -78,7 +75,7 @@ pool_add_act_fwd_kernel(const __nv_bfloat16* __restrict__ c, const __nv_bfloat16
         for (int j = 0; j < 8; ++j) acc[j] += f[j];
       }
     float dv[8];
-    load8(d + i * 8, dv);
+    load8(d + (size_t)i * 8, dv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = act_fwd(acc[j] * 0.25f + dv[j], act, slope);
     store8(out + (((long long)n * (Ho + 2 * po) + h + po) * (Wo + 2 * po) + w + po) * C + v * 8, acc);
@@ -92,9 +89,8 @@ pool_add_act_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
                         __nv_bfloat16* __restrict__ dd, __nv_bfloat16* __restrict__ dc) {
   const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = Ho + 2 * po, Wp = Wo + 2 * po;
   const long long total = (long long)N * Ho * Wo * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % Wo); t /= Wo;
     const int h = (int)(t % Ho); const int n = (int)(t / Ho);
     int hs[3], ws[3];
@@ -111,7 +107,7 @@ pool_add_act_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
     load8(outp + (((long long)n * Hp + h + po) * Wp + w + po) * C + v * 8, o);
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] *= act_grad_pre(o[j], act, slope);
-    store8(dd + i * 8, g);
+    store8(dd + (size_t)i * 8, g);
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] *= 0.25f;
 #pragma unroll
@@ -151,15 +147,14 @@ gap_bwd_kernel(const float* __restrict__ dout, int N, int HW, int C, __nv_bfloat
   const int V = C / 8;
   const long long total = (long long)N * HW * V;
   const float inv = 1.f / (float)HW;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int v = (int)(i % V);
-    const int n = (int)(i / ((long long)HW * V));
+    const int n = (int)(i / (unsigned)(HW * V));
     float g[8];
     load8f(dout + (long long)n * C + v * 8, g);
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] *= inv;
-    store8(dx + i * 8, g);
+    store8(dx + (size_t)i * 8, g);
   }
 }
 
@@ -172,8 +167,7 @@ rgb_head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
     ws[i] = (i & 3) < Co ? wgt[(i >> 2) * Co + (i & 3)] : 0.f;
   __syncthreads();
   const long long total = (long long)N * HW;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int n = (int)(i / HW);
     const int pix = (int)(i % HW);
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
@@ -304,9 +298,8 @@ sumsq_interior_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, 
   const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * H * W * V;
   float s = 0.f;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % W); t /= W;
     const int h = (int)(t % H); const int n = (int)(t / H);
     float f[8];
@@ -331,18 +324,17 @@ scale_interior_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
   const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * Hp * Wp * V;
   const float sc = __ldg(scale);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    unsigned t = i / V;
     const int wp = (int)(t % Wp); t /= Wp;
     const int hp = (int)(t % Hp);
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (hp >= p && hp < H + p && wp >= p && wp < W + p) {
-      load8(x + i * 8, f);
+      load8(x + (size_t)i * 8, f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] *= sc;
     }
-    store8(dx + i * 8, f);
+    store8(dx + (size_t)i * 8, f);
   }
 }
 

@@ -448,9 +448,8 @@ act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16*
                     __nv_bfloat16* __restrict__ dy) {
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const long long total = (long long)N * H * W * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); long long t = i / V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
     const int w = (int)(t % W); t /= W;
     const int h = (int)(t % H); const int n = (int)(t / H);
     int hs[3], ws[3];
@@ -467,7 +466,7 @@ act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16*
     load8(outp + (((long long)n * Hp + h + p) * Wp + w + p) * C + v * 8, o);
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] *= act_grad_pre(o[j], act, slope);
-    store8(dy + i * 8, acc);
+    store8(dy + (size_t)i * 8, acc);
   }
 }
 
