@@ -442,31 +442,48 @@ norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* 
 
 // dy[n,h,w,:] = fold(dpad)[n,h,w,:] * act'(out_pad interior)  — for conv+bias+act layers whose
 // activated output was written straight into the consumer's padded buffer (D, style encoder).
-__global__ void __launch_bounds__(256)
+template <int ACT>
+__global__ void __launch_bounds__(256, 2)
 act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16* __restrict__ outp,
-                    int N, int H, int W, int C, int p, int act, float slope,
+                    int H, int W, FastDiv divW, int C, int p, float slope,
                     __nv_bfloat16* __restrict__ dy) {
-  const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
-  const long long total = (long long)N * H * W * V;
-  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int v = (int)(i % V); unsigned t = i / V;
-    const int w = (int)(t % W); t /= W;
-    const int h = (int)(t % H); const int n = (int)(t / H);
-    int hs[3], ws[3];
-    const int nh = reflect_fold_sources(h, H, p, hs), nw = reflect_fold_sources(w, W, p, ws);
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int a = 0; a < nh; ++a)
-      for (int b = 0; b < nw; ++b) {
-        float f[8];
-        load8(dpad + (((long long)n * Hp + hs[a]) * Wp + ws[b]) * C + v * 8, f);
+  // per-plane layout as norm_bwd_apply_kernel: grid (pixel chunks, N), thread = channel vector x lane
+  const int V = C / 8, lanes = blockDim.x / V, HW = H * W;
+  const int v = threadIdx.x % V, pl = threadIdx.x / V;
+  if (pl >= lanes) return;
+  const int n = blockIdx.y, Wp = W + 2 * p;
+  const size_t img = (size_t)n * (H + 2 * p) * Wp * C + v * 8;
+  const __nv_bfloat16* gimg = dpad + img;
+  const __nv_bfloat16* oimg = outp + img;
+  __nv_bfloat16* dimg = dy + (size_t)n * HW * C + v * 8;
+  const int off0 = (p * Wp + p) * C;
+  const int stride = gridDim.x * lanes;
+  for (int pb = blockIdx.x * lanes + pl; pb < HW; pb += EW_UNROLL * stride) {
+    uint4 gr[EW_UNROLL], orr[EW_UNROLL];
+    int hh[EW_UNROLL];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    for (int u = 0; u < EW_UNROLL; ++u) {
+      const int q = pb + u * stride;
+      if (q < HW) {
+        hh[u] = p ? fast_div(q, divW) : 0;
+        const int pos = off0 + (q + 2 * p * hh[u]) * C;
+        gr[u] = ldg16(gimg + pos);
+        orr[u] = ldg16(oimg + pos);
       }
-    float o[8];
-    load8(outp + (((long long)n * Hp + h + p) * Wp + w + p) * C + v * 8, o);
+    }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] *= act_grad_pre(o[j], act, slope);
-    store8(dy + (size_t)i * 8, acc);
+    for (int u = 0; u < EW_UNROLL; ++u) {
+      const int q = pb + u * stride;
+      if (q < HW) {
+        float gv[8], o[8];
+        cvt8(gr[u], gv);
+        cvt8(orr[u], o);
+        if (p) add_fold_extras(gimg, hh[u], q - hh[u] * W, H, W, C, p, gv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gv[j] *= act_grad_pre_t<ACT>(o[j], slope);
+        store8(dimg + q * C, gv);
+      }
+    }
   }
 }
 
@@ -610,10 +627,16 @@ extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const 
 }
 extern "C" int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C,
                                int pad, int act, float slope, void* dy, void* stream) {
-  if (C % 8) return -1003;
-  const long long total = (long long)N * H * W * (C / 8);
-  act_bwd_fold_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
-      (const __nv_bfloat16*)dpad, (const __nv_bfloat16*)out_pad, N, H, W, C, pad, act, slope,
-      (__nv_bfloat16*)dy);
+  if (C % 8 || C / 8 > 256) return -1003;
+  if (!image_fits(H, W, C, pad)) return -1005;
+  const FastDiv dw = make_fastdiv(W);
+#define MT_ABF(A)                                                                                 \
+  act_bwd_fold_kernel<A><<<plane_grid(N, H * W, C, resident_ctas(act_bwd_fold_kernel<A>, 0)), 256, 0, \
+                           ST(stream)>>>((const __nv_bfloat16*)dpad, (const __nv_bfloat16*)out_pad, H, W, \
+                                         dw, C, pad, slope, (__nv_bfloat16*)dy)
+  if (act == MT_ACT_RELU) MT_ABF(1);
+  else if (act == MT_ACT_LRELU) MT_ABF(2);
+  else MT_ABF(0);
+#undef MT_ABF
   return cuda_rc();
 }

@@ -399,7 +399,10 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
     same weights, same batch, same torch seed (device Philox draws), `iters` iterations including
     the 2 eager warm-up iterations, the capture and several replays, with a changing learning rate."""
     out = {}
-    for mode in ('eager', 'graph'):
+    # a second eager run measures the run-to-run noise floor (fp32 atomics in the split-K weight
+    # gradients and in the plane reductions make two identical runs differ, and GAN dynamics amplify
+    # it over the iterations): the graph must stay within that floor, not within a fixed epsilon
+    for mode in ('eager', 'eager2', 'graph'):
         m, _ = make_model(dim, size, B, nd, seed, **flags)
         m.use_graph = mode == 'graph'
         b = {k: v.to(DEV) for k, v in batch(B, size, nd, seed).items()}
@@ -416,12 +419,14 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
                             for n in m.model}, m._graph is not None)
     assert out['graph'][2] and not out['eager'][2]
     r = {}
-    for it, (he, hg) in enumerate(zip(out['eager'][0], out['graph'][0])):
+    for it, (he, h2, hg) in enumerate(zip(out['eager'][0], out['eager2'][0], out['graph'][0])):
         for k in he:
-            r[f'loss_it{it}.{k}'] = abs(he[k] - hg[k]) / max(1.0, abs(he[k]))
+            scale = max(1.0, abs(he[k]))
+            r[f'loss_it{it}.{k}'] = max(0.0, abs(he[k] - hg[k]) / scale - 3.0 * abs(he[k] - h2[k]) / scale)
     for n in out['eager'][1]:
         r[f'cos_params.{n}'] = cos(out['graph'][1][n] - 0, out['eager'][1][n])
-        r[f'params.{n}'] = rel(out['graph'][1][n], out['eager'][1][n])
+        r[f'params.{n}'] = max(0.0, rel(out['graph'][1][n], out['eager'][1][n])
+                               - 3.0 * rel(out['eager2'][1][n], out['eager'][1][n]))
     return r
 
 

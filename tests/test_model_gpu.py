@@ -67,7 +67,8 @@ def test_sampling_vs_oracle():
 def test_cuda_graph_iteration_matches_eager():
     """6 iterations (2 eager warm-up, capture, replays; learning rate changed every iteration):
     the graph-replayed losses and final weights match the eager launch sequence.  Not bit-exact
-    because the weight-gradient split-K uses fp32 atomics (order varies run to run)."""
+    because the weight-gradient split-K uses fp32 atomics (order varies run to run): the bound is
+    5e-3 beyond three times the difference between two eager runs of the same sequence."""
     from tests.model_cases import graph_vs_eager
     res = graph_vs_eager()
     _check(res, 5e-3, 0.9999)
