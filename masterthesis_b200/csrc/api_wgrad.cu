@@ -125,6 +125,38 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Cout_, int C
   }
 }
 
+// Pair-per-thread variants (non-window layouts): a thread owns one (row, column) pair of a packed
+// operand and walks the T filter taps, so the index decomposition (two divisions) is paid once per
+// T elements, the master weight is read in runs of T consecutive floats and every packed row is
+// written with consecutive lanes on consecutive elements.
+//   pass 0: wf[tap][co][ci_s]  thread = (co, ci), ci fastest
+//   pass 1: wb[tap][ci][co_s]  thread = (ci, co), co fastest
+__global__ void __launch_bounds__(256)
+pack_weight_pairs_kernel(const float* __restrict__ w, int Cout_, int Cin_, int T_, int transposed,
+                         __nv_bfloat16* __restrict__ wf, __nv_bfloat16* __restrict__ wb) {
+  const unsigned Cout = Cout_, Cin = Cin_, T = T_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned n0 = wf ? Cout * Cin_s : 0, n1 = wb ? Cin * Cout_s : 0;
+  const unsigned stride = gridDim.x * blockDim.x;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1; i += stride) {
+    unsigned co, ci;
+    __nv_bfloat16* dst;
+    unsigned dst_stride;                       // elements between consecutive taps
+    if (i < n0) {
+      co = i / Cin_s; ci = i - co * Cin_s;
+      dst = wf + i; dst_stride = Cout * Cin_s;
+    } else {
+      const unsigned j = i - n0;
+      ci = j / Cout_s; co = j - ci * Cout_s;
+      dst = wb + j; dst_stride = Cin * Cout_s;
+    }
+    const bool valid = co < Cout && ci < Cin;
+    const float* src = w + (size_t)(transposed ? ci * Cout + co : co * Cin + ci) * T;
+    for (unsigned t = 0; t < T; ++t)
+      dst[(size_t)t * dst_stride] = __float2bfloat16(valid ? __ldg(src + t) : 0.f);
+  }
+}
+
 // dw_packed -> dw (OIHW / IOHW fp32). Conv2d: [tap][Cout][Cin_s] (window: [kh][Cout][64]);
 // ConvTranspose2d: [tap][Cin][Cout_s].
 __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_, int kw_,
@@ -166,6 +198,17 @@ extern "C" int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, in
   const long long n = mt_packed_weight_elems(Cout, Cin, kh, kw, window, 0) +
                       mt_packed_weight_elems(Cout, Cin, kh, kw, window, 1);
   if (n >= (1ll << 31)) return -1005;
+  if (!window) {
+    const long long pairs = (long long)(w_fwd ? Cout * round_up(Cin, 8) : 0) +
+                            (long long)(w_bwd ? Cin * round_up(Cout, 8) : 0);
+    int pb = (int)((pairs + 255) / 256);
+    if (pb > 148 * 16) pb = 148 * 16;
+    if (pb < 1) pb = 1;
+    pack_weight_pairs_kernel<<<pb, 256, 0, (cudaStream_t)stream>>>(
+        w, Cout, Cin, kh * kw, transposed, (__nv_bfloat16*)w_fwd, (__nv_bfloat16*)w_bwd);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+  }
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   pack_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
@@ -178,6 +221,7 @@ extern "C" int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, i
                                     int transposed, int window, int accumulate, float* dw,
                                     void* stream) {
   const long long n = (long long)Cout * Cin * kh * kw;
+  if (n >= (1ll << 31)) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   unpack_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, Cout, Cin, kh, kw,
