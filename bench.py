@@ -139,7 +139,7 @@ def sampling_throughput(iters=20):
         torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
     return {"metric": "translated_images_per_sec", "value": N / (ms * 1e-3), "ms_per_call": ms,
-            "config": "AdaINModel.forward_reference, N = 8, 256x256 (SURVEY config 2), eager launches; the "
+            "config": "AdaINModel.forward_reference, N = 8, 256x256 (SURVEY config 2), launch sequence replayed as a CUDA graph (test mode); the "
                       "reference API returns (image, seconds, GiB) per call",
             "model_tflops": 98.3e-3 * N / (ms * 1e-3)}
 

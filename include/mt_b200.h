@@ -110,8 +110,11 @@ int mt_add_interior(void* dpad, const void* dense, int N, int H, int W, int C, i
  * mr: (mean, rstd); coef: [N][C][3]; gb: fc(s) output [N][2C] (weight | bias).
  * C is the STORED channel count; C_valid <= C the logical one (LayerNorm statistics run over
  * C_valid*HW elements and ln_w / ln_b / dln_* hold C_valid entries; padded channels stay zero). */
-int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream);
-/* stats: [N][parts][C][2] (parts = 1 from mt_plane_stats, per-tile slots from mt_conv2d_fwd_stats) */
+/* stats[N][parts][C][2] = per-chunk (sum, sum of squares), parts = mt_plane_stats_parts(N, HW, C);
+ * plain stores, every slot written once (no zeroing, no atomics: reproducible forward passes) */
+int mt_plane_stats_parts(int N, int HW, int C);
+int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, int parts, void* stream);
+/* stats: [N][parts][C][2] (from mt_plane_stats or from the conv epilogue, mt_conv2d_fwd_stats) */
 int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,
                      const float* gb, const float* ln_w, const float* ln_b, float* ss, float* mr,
                      void* stream);

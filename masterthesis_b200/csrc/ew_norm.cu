@@ -124,7 +124,10 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
     for (int l = 0; l < lanes; ++l) s += red[l * V * 16 + t];
     const int vv = t / 16, k = t % 16;
     const int c = vv * 8 + (k & 7);
-    atomicAdd(out + ((long long)n * C + c) * 2 + (k >> 3), s);
+    if (kBackward) atomicAdd(out + ((long long)n * C + c) * 2 + (k >> 3), s);
+    // forward statistics: this chunk's slot of [N][chunks][C][2], plain store — the finalize kernel
+    // adds the slots in a fixed order, so a forward pass is reproducible bit for bit
+    else out[(((long long)n * chunks + chunk) * C + c) * 2 + (k >> 3)] = s;
   }
 }
 
@@ -530,8 +533,10 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
                          int C, int gp, int act, float slope, float* out, cudaStream_t st) {
   const int HW = H * W;
   if (C % 8 || C / 8 > 256) return -1003;
-  cudaError_t e = cudaMemsetAsync(out, 0, (size_t)N * C * 2 * sizeof(float), st);
-  if (e != cudaSuccess) return -(int)e;
+  if (bwd) {
+    cudaError_t e = cudaMemsetAsync(out, 0, (size_t)N * C * 2 * sizeof(float), st);
+    if (e != cudaSuccess) return -(int)e;
+  }
   const int V = C / 8;
   const int lanes = 256 / V;
   const size_t smem = (size_t)lanes * V * 16 * sizeof(float);
@@ -553,7 +558,15 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
   return cuda_rc();
 }
 
-extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, void* stream) {
+// number of partial-sum slots per image that mt_plane_stats writes for this shape
+extern "C" int mt_plane_stats_parts(int N, int HW, int C) {
+  if (C % 8 || C / 8 > 256 || N < 1) return 0;
+  const size_t smem = (size_t)(256 / (C / 8)) * (C / 8) * 16 * sizeof(float);
+  return plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<false, 0, false>, smem));
+}
+extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, int parts,
+                              void* stream) {
+  if (parts != mt_plane_stats_parts(N, HW, C)) return -1012;
   return reduce_launch(false, x, nullptr, nullptr, N, HW, 1, C, 0, 0, 0.f, stats, ST(stream));
 }
 extern "C" int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,

@@ -130,15 +130,14 @@ class AdaINModel(Model):
 
     def forward_random(self, img, z_r, c_trg):
         start = time.time()
-        img_fake = self.G(self.Ec(img), z_r, c_trg)
+        img_fake = self._run_sampling('random', lambda a, z, c: self.G(self.Ec(a), z, c), img, z_r, c_trg)
         end = time.time()
         return img_fake, end - start, self._mem_gib()
 
     def forward_reference(self, img_src, img_ref, c_trg):
         start = time.time()
-        z_c = self.Ec(img_src)
-        z_s, _, _ = self.Es(img_ref, c_trg)
-        img_fake = self.G(z_c, z_s, c_trg)
+        img_fake = self._run_sampling(
+            'reference', lambda a, b, c: self.G(self.Ec(a), self.Es(b, c)[0], c), img_src, img_ref, c_trg)
         end = time.time()
         return img_fake, end - start, self._mem_gib()
 

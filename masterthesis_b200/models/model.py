@@ -143,6 +143,38 @@ class Model(ABC, nn.Module):
             else:
                 self.loss[k] = v
 
+    # ------------------------------------------------------------------ sampling as a graph
+    def _run_sampling(self, kind, fn, *inputs):
+        """fn(*inputs) -> image for the sampling entry points (forward_reference / forward_random).
+        In test mode (fixed weights) the launch sequence is captured per (kind, input shapes) after
+        two eager calls and replayed from static input buffers: the ~100 launches of a sampling call
+        are host-bound when enqueued one by one.  Training-mode models, CPU-replayed draws
+        (self.rng), grad-enabled calls and MT_CUDA_GRAPH=0 stay eager."""
+        if (not self.use_graph or self.rng is not None or torch.is_grad_enabled()
+                or 'train' in self.args.mode or not all(t.is_cuda for t in inputs)):
+            return fn(*inputs)
+        key = (kind,) + tuple((tuple(t.shape), t.dtype) for t in inputs)
+        rec = self.__dict__.setdefault('_sample_graphs', {}).get(key)
+        if rec is None:
+            n = self._eager_iters.get(key, 0)
+            if n < self.graph_warmup:
+                self._eager_iters[key] = n + 1
+                return fn(*inputs)
+            static = [torch.empty_like(t).copy_(t) for t in inputs]
+            graph = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(graph):
+                out = fn(*static)
+            rec = self._sample_graphs[key] = dict(graph=graph, static=static, out=out)
+        for d, t in zip(rec['static'], inputs):
+            d.copy_(t)
+        rec['graph'].replay()
+        return rec['out'].clone()
+
+    def reset_sampling_graphs(self):
+        """drop the captured sampling graphs (after load(): they hold the packed weights)"""
+        self.__dict__.pop('_sample_graphs', None)
+
     # ------------------------------------------------------------------ lifecycle
     def initialize(self):
         if self.device != 'cuda':
@@ -184,6 +216,7 @@ class Model(ABC, nn.Module):
         torch.save({opt: self.optimizer[opt].state_dict() for opt in self.optimizer}, path)
 
     def load(self, checkpoint, opt_ckpt=None):
+        self.reset_sampling_graphs()
         if checkpoint is not None:
             ckpt = torch.load(checkpoint, map_location='cpu')
             for net in ckpt:

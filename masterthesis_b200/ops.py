@@ -390,9 +390,12 @@ def add_interior_(dpad, dense, pad):
 # ----------------------------------------------------------------------------- norms
 @_checked
 def plane_stats(x):
+    """[N, parts, C, 2] per-chunk (sum, sum of squares) of x [N,H,W,C]; norm_finalize adds the parts."""
     N, H, W, C = x.shape
-    stats = _T.empty((N, C, 2), dtype=torch.float32, device=x.device)
-    check(_lib.lib().mt_plane_stats(_p(x), N, H * W, C, _p(stats), _stream()), "plane_stats")
+    L = _lib.lib()
+    parts = L.mt_plane_stats_parts(N, H * W, C)
+    stats = _T.empty((N, parts, C, 2), dtype=torch.float32, device=x.device)
+    check(L.mt_plane_stats(_p(x), N, H * W, C, _p(stats), parts, _stream()), "plane_stats")
     _count()
     return stats
 
@@ -559,4 +562,4 @@ def scale_interior(x_pad, scale, pad):
 
 def channel_sum(dy):
     """sum over (n, h, w) of a dense bf16 tensor -> fp32 [C] (bias gradients)."""
-    return plane_stats(dy)[:, :, 0].sum(0)
+    return plane_stats(dy)[..., 0].sum((0, 1))

@@ -200,7 +200,7 @@ def fused_stats_case(N, Cin, Cout, H, W, k=3, stride=1, transposed=False, bias=T
     y, st = ops.conv_fwd_stats(xn, wf, b, g)
     fused = st.dim() == 4
     tot = st.sum(1) if fused else st
-    sep = ops.plane_stats(y)
+    sep = ops.plane_stats(y).sum(1)
     yf = y.float()
     ref = torch.stack((yf.sum((1, 2)), (yf * yf).sum((1, 2))), -1)
     return {"same_output": 0.0 if torch.equal(y0, y) else 1.0,

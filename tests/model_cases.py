@@ -430,7 +430,34 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
     return r
 
 
+def sampling_graph_vs_eager(dim=16, size=64, N=2, nd=4, seed=9):
+    """forward_random in test mode: the captured sampling graph (third call on) vs eager launches of
+    the same model, on inputs that change from call to call (static input buffers must be refreshed)."""
+    from masterthesis_b200 import models
+    args = ref_import.default_args(dim=dim, crop_size=size, batch_size=N, num_domains=nd, init_type='normal',
+                                   mode='test')
+    torch.manual_seed(seed)
+    m = models.AdaINModel(args)
+    m.initialize()
+    for n in m.model:
+        m.model[n].eval()          # GaussianNoiseLayer is the identity outside training (misc.py:18-26)
+    r = {}
+    with torch.no_grad():
+        for call in range(5):
+            a = synth.synth_images(N, size, seed + call, 'src').to(DEV)
+            z = synth.synth_tensor('zr', (N, 8), seed + call).to(DEV)
+            c = synth.synth_onehot(N, nd, seed + call).to(DEV)
+            m.use_graph = True
+            y_g, _, _ = m.forward_random(a, z, c)
+            m.use_graph = False
+            y_e, _, _ = m.forward_random(a, z, c)
+            r[f'call{call}'] = rel(y_g, y_e)
+    r['captured'] = 0.0 if getattr(m, '_sample_graphs', None) else 1.0
+    return r
+
+
 CASES = {
+    'sampling_graph_vs_eager': sampling_graph_vs_eager,
     'graph_vs_eager': graph_vs_eager,
     'nets_base_dim16_64': base_nets_vs_golden,
     'step_basec': lambda: flag_step_vs_golden('step_basec_dim8_64'),

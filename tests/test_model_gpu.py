@@ -116,3 +116,11 @@ def test_cuda_graph_with_content_discriminator_schedule():
     graph; 10 iterations (warm-up, both captures, replays) match the eager launch sequence."""
     from tests.model_cases import graph_vs_eager
     _check(graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True), 5e-3, 0.9999)
+
+
+def test_sampling_graph_matches_eager():
+    """Test-mode sampling (forward_random) replayed as a CUDA graph vs eager launches, 5 calls with
+    changing inputs (2 eager warm-ups, capture, replays): identical up to the atomics of the unfused
+    plane statistics."""
+    from tests.model_cases import sampling_graph_vs_eager
+    _check(sampling_graph_vs_eager(), 1e-3, 0.0)
