@@ -118,7 +118,8 @@ int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, int parts,
 int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,
                      const float* gb, const float* ln_w, const float* ln_b, float* ss, float* mr,
                      void* stream);
-/* out_pad[interior] = act(x*scale+shift) (+ residual) (+ noise, misc.py:25); ss may be NULL */
+/* out_pad[interior] = act(x*scale+shift) (+ residual) (+ noise, misc.py:25); ss may be NULL.
+ * With out_p > 0 the reflection border of out_pad is written too (no mt_reflect_border needed). */
 int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C, int act,
                       float slope, const void* res_pad, int res_p, const float* noise,
                       void* out_pad, int out_p, void* stream);

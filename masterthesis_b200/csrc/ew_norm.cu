@@ -305,6 +305,17 @@ affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
           for (int j = 0; j < 8; ++j) f[j] += r[j];
         }
         store8(oimg + (p + 2 * po * hh[u]) * C, f);
+        // the reflection border of the padded output (nn.ReflectionPad2d of the consumer,
+        // blocks.py:29-31): every padded position that mirrors this pixel gets the same vector
+        if (po && near_border(hh[u], p - hh[u] * W, H, W, po)) {
+          int hs[3], ws[3];
+          const int w = p - hh[u] * W;
+          const int nh = reflect_fold_sources(hh[u], H, po, hs), nw = reflect_fold_sources(w, W, po, ws);
+          __nv_bfloat16* opad = oimg - (po * Wo + po) * C;     // origin of the padded image
+          for (int a = 0; a < nh; ++a)
+            for (int b = 0; b < nw; ++b)
+              if (a | b) store8(opad + (hs[a] * Wo + ws[b]) * C, f);
+        }
       }
     }
   }

@@ -89,8 +89,7 @@ class ConvNormAct(Function):
         gb = p1 if mode == "adain" else None
         lw, lb = (p1, p2) if mode == "layer" else (None, None)
         ss, mr = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb, C_valid=geom.Cout)
-        out = ops.affine_act_fwd(raw, ss, act=act, noise=noise, out_p=out_pad)
-        ops.reflect_border_(out, out_pad)
+        out = ops.affine_act_fwd(raw, ss, act=act, noise=noise, out_p=out_pad)   # incl. reflection border
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
         ctx.has_bias = bias is not None
         ctx.weight = weight
@@ -123,12 +122,10 @@ class ResBlock(Function):
         raw1, st1 = ops.conv_fwd_stats(x, wf1, None, geom)
         N, H, W, C = raw1.shape
         ss1, mr1 = ops.norm_finalize(st1, mode, H * W, gbc)
-        h = ops.affine_act_fwd(raw1, ss1, act=act, out_p=1)
-        ops.reflect_border_(h, 1)
+        h = ops.affine_act_fwd(raw1, ss1, act=act, out_p=1)                       # incl. reflection border
         raw2, st2 = ops.conv_fwd_stats(h, wf2, None, geom)
         ss2, mr2 = ops.norm_finalize(st2, mode, H * W, gbc)
         out = ops.affine_act_fwd(raw2, ss2, act=None, res_pad=x, res_p=1, noise=noise, out_p=out_pad)
-        ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
         ctx.w1, ctx.w2 = w1, w2
         ctx.save_for_backward(x, raw1, h, raw2, ss1, mr1, ss2, mr2, gbc, wb1, wb2)
@@ -295,7 +292,6 @@ class ResidualPad(Function):
     @staticmethod
     def forward(ctx, x, y, x_pad, out_pad):
         out = ops.affine_act_fwd(y, None, act=None, res_pad=x, res_p=x_pad, out_p=out_pad)
-        ops.reflect_border_(out, out_pad)
         ctx.meta = (x_pad, out_pad, x.shape)
         return out
 

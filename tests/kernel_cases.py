@@ -134,8 +134,7 @@ def norm_case(mode, N, C, H, W, act, residual=False, noise=False, seed=0):
         res_pad = to_nhwc(F.pad(res_t, (1, 1, 1, 1), mode="reflect"))
     out = ops.affine_act_fwd(xn, ss, act=act, res_pad=res_pad, res_p=1,
                              noise=None if nz is None else nz.permute(0, 2, 3, 1).contiguous(),
-                             out_p=1)
-    ops.reflect_border_(out, 1)
+                             out_p=1)          # writes the reflection border too
     out_ref = F.pad(y_ref.detach(), (1, 1, 1, 1), mode="reflect")
     r = {"fwd": rel(from_nhwc(out, C), out_ref)}
     dx, dgb, dlw, dlb = ops.norm_bwd(to_nhwc(g), xn, ss, mr, mode, act=act,
