@@ -40,9 +40,9 @@ def peaks():
 
 
 def make_args(B, mode="train"):
-    from oracle import ref_import      # default_args only: a plain Namespace, no reference import
-    return ref_import.default_args(dim=64, crop_size=SIZE, batch_size=B, num_domains=ND,
-                                   latent_dim=LATENT, mode=mode, init_type="normal")
+    from masterthesis_b200.arguments import default_args
+    return default_args(dim=64, crop_size=SIZE, batch_size=B, num_domains=ND, latent_dim=LATENT,
+                        mode=mode, init_type="normal")
 
 
 def synth_batch(B, seed, pinned):
