@@ -34,8 +34,7 @@ class AdaINModel(Model):
     def __init__(self, args):
         super().__init__(args)
         self.latent_dim = args.latent_dim
-        for flag, why in (('use_ragan', 'relativistic GAN'), ('dis_sn', 'spectral norm'),
-                          ('use_dropout', 'dropout')):
+        for flag, why in (('dis_sn', 'spectral norm'), ('use_dropout', 'dropout')):
             if getattr(args, flag, False):
                 raise NotImplementedError(f"--{flag} ({why}) is outside the accelerated path (SURVEY.md §8f)")
         if getattr(args, 'vgg_loss', None) is not None:
@@ -225,7 +224,10 @@ class AdaINModel(Model):
         else:
             pred, pred_cls = netD.run(both)
             pred_fake, pred_real = pred[:n], pred[n:]
-            if 'hinge' in self.args.gan_mode:
+            if self.args.use_ragan:        # relativistic average (:206-208)
+                loss_d_adv = (self.gan_loss(pred_real - torch.mean(pred_fake), 1) +
+                              self.gan_loss(pred_fake - torch.mean(pred_real), 0)) / 2
+            elif 'hinge' in self.args.gan_mode:
                 loss_d_adv = F.relu(1.0 - pred_real).mean() + F.relu(1.0 + pred_fake).mean()
             else:
                 loss_d_adv = self.gan_loss(pred_fake, 0) + self.gan_loss(pred_real, 1)
@@ -264,13 +266,27 @@ class AdaINModel(Model):
         self.backward_decoder_random(img, c_org)
         self._step('content_encoder', 'decoder')
 
-    def _g_adv(self, netD, fake, c_org):
+    def _g_adv(self, netD, fake, c_org, real=None, netD_real=None):
+        """generator-side adversarial + classification loss.  `real` / `netD_real`: the relativistic
+        branch (--use_ragan, :286-292 and :360-366) also scores the real images, in phase G2 with
+        the OTHER discriminator (discriminator2 for the reals, discriminator1 for the fakes)."""
         if self.args.ms_dis:
             adv, cls = 0, 0
             for pred_fake, pred_fake_cls in netD.run(fake):
                 adv = adv + self.gan_loss(pred_fake, 1)
                 cls = cls + _bce(pred_fake_cls, c_org)
             return adv, cls * self.args.lambda_cls_G
+        if self.args.use_ragan:
+            if netD_real is netD:          # one call over both halves (no batch statistics in D)
+                n = fake.shape[0]
+                pred, pred_cls = netD.run(torch.cat((fake, real)))
+                pred_fake, pred_fake_cls, pred_real = pred[:n], pred_cls[:n], pred[n:]
+            else:
+                pred_real, _ = netD_real.run(real)
+                pred_fake, pred_fake_cls = netD.run(fake)
+            adv = (self.gan_loss(pred_real - torch.mean(pred_fake), 0) +
+                   self.gan_loss(pred_fake - torch.mean(pred_real), 1)) / 2
+            return adv, _bce(pred_fake_cls, c_org) * self.args.lambda_cls_G
         pred_fake, pred_fake_cls = netD.run(fake)
         adv = -pred_fake.mean() if 'hinge' in self.args.gan_mode else self.gan_loss(pred_fake, 1)
         return adv, _bce(pred_fake_cls, c_org) * self.args.lambda_cls_G
@@ -292,7 +308,8 @@ class AdaINModel(Model):
         with self._frozen('discriminator1'):
             z_c_rec, ((z_s_rec, _, _), (loss_g_adv, loss_g_cls)) = self._fork(
                 lambda: self.Ec(img_fake),
-                lambda: (self.Es(img_fake, c_org), self._g_adv(self.model.discriminator1, img_fake, c_org)))
+                lambda: (self.Es(img_fake, c_org),
+                         self._g_adv(self.model.discriminator1, img_fake, c_org, img, self.model.discriminator1)))
         z_c_rec_b, z_c_rec_a = torch.split(z_c_rec, B, dim=0)
         z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B, dim=0)
         img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
@@ -330,11 +347,12 @@ class AdaINModel(Model):
         z_sr = self.get_z_random(B, self.args.latent_dim)
         img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
         # the reference scores img_random with discriminator1 under --ms_dis (:361) and with
-        # discriminator2 otherwise (:378)
-        dname = 'discriminator1' if self.args.ms_dis else 'discriminator2'
-        with self._frozen(dname, 'style_encoder'):
+        # discriminator2 otherwise (:378); the relativistic branch (:361-362) takes the reals from
+        # discriminator2 and the fakes from discriminator1
+        dname = 'discriminator1' if (self.args.ms_dis or self.args.use_ragan) else 'discriminator2'
+        with self._frozen('discriminator1', 'discriminator2', 'style_encoder'):
             (loss_g_adv2, loss_g_cls2), (z_sr_rec, mu2, _) = self._fork(
-                lambda: self._g_adv(self.model[dname], img_random, c_org),
+                lambda: self._g_adv(self.model[dname], img_random, c_org, img, self.model.discriminator2),
                 lambda: self.Es(img_random, c_org))
         if self.reparam:
             mu2_a, mu2_b = torch.split(mu2, B, dim=0)

@@ -228,11 +228,16 @@ if __name__ == '__main__':
     os.makedirs(OUT, exist_ok=True)
     ref_import.import_reference()
     torch.set_num_threads(os.cpu_count())
-    which = sys.argv[1:] or ['adain', 'base']
+    which = sys.argv[1:] or ['adain', 'base', 'gan']
     if 'adain' in which:
         nets_case('nets_dim16_64', dim=16, size=64, N=2)
         nets_case('nets_dim64_256', dim=64, size=256, N=1, sub=8)
         step_case('step_dim8_64', dim=8, size=64, B=1)
+    if 'gan' in which:      # adversarial-loss variants (loss.py:41-64, adain_model.py:206-215,277-302,359-376)
+        step_case('step_ragan_dim8_64', dim=8, size=64, B=1, use_ragan=True)
+        step_case('step_hinge_dim8_64', dim=8, size=64, B=1, gan_mode='hinge')
+        step_case('step_lsgan_dim8_64', dim=8, size=64, B=1, gan_mode='lsgan')
+        step_case('step_wgangp_dim8_64', dim=8, size=64, B=1, gan_mode='wgangp')
     if 'base' in which:
         nets_base_case('nets_base_dim16_64', dim=16, size=64, N=2)
         step_case('step_basec_dim8_64', dim=8, size=64, B=1, model='BaseModel', concat=True)

@@ -47,7 +47,7 @@ def bce_logits(x, target):
 
 
 class AdaINStep:
-    """State + one iteration of AdaINModel / BaseModel (vanilla GAN, no VGG).
+    """State + one iteration of AdaINModel / BaseModel (no VGG).
     model='adain': ReparameterizedStyleEncoder + AdaINDecoder (adain_model.py);
     model='base' : StyleEncoder or (reparam) ReparameterizedStyleEncoder, Decoder or (concat)
                    DecoderConcat (base_model.py).
@@ -55,7 +55,8 @@ class AdaINStep:
 
     def __init__(self, params, B, lr=1e-4, betas=(0.5, 0.999), wd=1e-4, lambda_rec=10.0,
                  lambda_cls=1.0, lambda_cls_G=5.0, latent_dim=8, model='adain', reparam=True,
-                 concat=False, ms_dis=False, use_dis_content=False, d_iter=3):
+                 concat=False, ms_dis=False, use_dis_content=False, d_iter=3, gan_mode='vanilla',
+                 use_ragan=False):
         self.P = {n: {k: v.detach().clone().requires_grad_(True) for k, v in params[n].items()}
                   for n in params}
         self.opt = {n: Adam(self.P[n], lr / 2.5 if n == 'content_discriminator' else lr, betas, wd)
@@ -64,9 +65,46 @@ class AdaINStep:
         self.reparam = True if model == 'adain' else reparam
         self.use_dis_content, self.d_iter, self.it = use_dis_content, d_iter, 0
         self.loss_dc = None
+        self.gan_mode, self.use_ragan = gan_mode, use_ragan
         self.B, self.latent = B, latent_dim
         self.lrec, self.lcls, self.lclsg = lambda_rec, lambda_cls, lambda_cls_G
         self.loss = {}
+
+    # -- adversarial terms ------------------------------------------------------------------
+    def gan(self, pred, is_real):
+        """GANLoss.forward (loss.py:52-64): BCE-with-logits, MSE (lsgan) or the signed mean (wgangp).
+        loss.py:48 (`elif loss == 'wgangp' or 'hinge'`) leaves self.loss = None for 'hinge'; the
+        hinge branches of the model never call it."""
+        if 'wgangp' in self.gan_mode:
+            return -pred.mean() if is_real else pred.mean()
+        if self.gan_mode == 'lsgan':
+            return F.mse_loss(pred, torch.full_like(pred, 1.0 if is_real else 0.0))
+        return bce_logits(pred, 1 if is_real else 0)
+
+    def d_adv(self, pred_fake, pred_real):
+        """adain_model.py:206-215 (single-scale discriminator)"""
+        if self.use_ragan:
+            return (self.gan(pred_real - pred_fake.mean(), 1) + self.gan(pred_fake - pred_real.mean(), 0)) / 2
+        if 'hinge' in self.gan_mode:
+            return F.relu(1.0 - pred_real).mean() + F.relu(1.0 + pred_fake).mean()
+        return self.gan(pred_fake, 0) + self.gan(pred_real, 1)
+
+    def g_adv(self, which_fake, fake, c_org, which_real, real):
+        """adain_model.py:277-302 / :359-376 -> (adversarial, classification * lambda_cls_G)"""
+        if self.ms_dis:
+            adv, cls = 0, 0
+            for pred_fake, pred_fake_cls in self.D(which_fake, fake):
+                adv = adv + self.gan(pred_fake, 1)
+                cls = cls + bce_logits(pred_fake_cls, c_org)
+            return adv, cls * self.lclsg
+        if self.use_ragan:
+            pred_real, _ = self.D(which_real, real)[0]
+            pred_fake, pred_fake_cls = self.D(which_fake, fake)[0]
+            adv = (self.gan(pred_real - pred_fake.mean(), 0) + self.gan(pred_fake - pred_real.mean(), 1)) / 2
+            return adv, bce_logits(pred_fake_cls, c_org) * self.lclsg
+        pred_fake, pred_fake_cls = self.D(which_fake, fake)[0]
+        adv = -pred_fake.mean() if 'hinge' in self.gan_mode else self.gan(pred_fake, 1)
+        return adv, bce_logits(pred_fake_cls, c_org) * self.lclsg
 
     # -- networks -------------------------------------------------------------------------
     def Ec(self, x, draw):
@@ -113,7 +151,10 @@ class AdaINStep:
             self.opt[which].zero_grad()
             d_adv, d_cls = 0, 0
             for (pred_fake, _), (pred_real, pred_real_cls) in zip(self.D(which, fake), self.D(which, img)):
-                d_adv = d_adv + bce_logits(pred_fake, 0) + bce_logits(pred_real, 1)
+                if self.ms_dis:        # backward_multi_scale_discriminator (:182-199): GANLoss only
+                    d_adv = d_adv + self.gan(pred_fake, 0) + self.gan(pred_real, 1)
+                else:
+                    d_adv = d_adv + self.d_adv(pred_fake, pred_real)
                 d_cls = d_cls + bce_logits(pred_real_cls, c_org)
             d = d_adv + self.lcls * d_cls
             d.backward()
@@ -141,11 +182,7 @@ class AdaINStep:
         g_content = None
         if self.use_dis_content:
             g_content = bce_logits(nets.content_discriminator(self.P['content_discriminator'], z_c), 1 - c_org)
-        g_adv, g_cls = 0, 0
-        for pred_fake, pred_fake_cls in self.D('discriminator1', img_fake):
-            g_adv = g_adv + bce_logits(pred_fake, 1)
-            g_cls = g_cls + bce_logits(pred_fake_cls, c_org)
-        g_cls = g_cls * self.lclsg
+        g_adv, g_cls = self.g_adv('discriminator1', img_fake, c_org, 'discriminator1', img)
         g_self = F.l1_loss(img_self, img) * self.lrec
         g_cc = F.l1_loss(img_recon, img) * self.lrec
         kl_zc = torch.mean(z_c ** 2) * 0.01
@@ -167,11 +204,10 @@ class AdaINStep:
         z_ca, z_cb = torch.split(self.Ec(img, draw), B)
         z_sr = draw((B, self.latent))
         img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
-        g_adv2, g_cls2 = 0, 0      # discriminator1 under ms_dis (base_model.py:361), else discriminator2
-        for pred_fake, pred_fake_cls in self.D('discriminator1' if self.ms_dis else 'discriminator2', img_random):
-            g_adv2 = g_adv2 + bce_logits(pred_fake, 1)
-            g_cls2 = g_cls2 + bce_logits(pred_fake_cls, c_org)
-        g_cls2 = g_cls2 * self.lclsg
+        # fakes: discriminator1 under ms_dis (:350) and under use_ragan (:362, reals from
+        # discriminator2), else discriminator2
+        which = 'discriminator1' if (self.ms_dis or self.use_ragan) else 'discriminator2'
+        g_adv2, g_cls2 = self.g_adv(which, img_random, c_org, 'discriminator2', img)
         z_rec, mu2, _ = self.Es(img_random, c_org, draw)
         if self.reparam:
             mu2_a, mu2_b = torch.split(mu2, B)

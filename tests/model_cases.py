@@ -463,6 +463,8 @@ CASES = {
     'step_basec': lambda: flag_step_vs_golden('step_basec_dim8_64'),
     'step_basecr': lambda: flag_step_vs_golden('step_basecr_dim8_64'),
     'step_dcms': lambda: flag_step_vs_golden('step_dcms_dim8_256'),
+    **{f'step_{g}': (lambda g=g: flag_step_vs_golden(f'step_{g}_dim8_64'))
+       for g in ('ragan', 'hinge', 'lsgan', 'wgangp', 'nearest', 'dropout', 'sn')},
     'step_base_default': base_default_step_vs_oracle,
     'sampling_base_256': base_sampling_vs_oracle,
     'graph_vs_eager_dc': lambda: graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True),

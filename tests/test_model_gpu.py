@@ -87,11 +87,13 @@ def test_base_nets_vs_reference_golden():
     _check(res, 2e-2, 0.985, {'dec.fake': 5e-2})
 
 
-@pytest.mark.parametrize('name', ['step_basec_dim8_64', 'step_basecr_dim8_64', 'step_dcms_dim8_256'])
+@pytest.mark.parametrize('name', ['step_basec_dim8_64', 'step_basecr_dim8_64', 'step_dcms_dim8_256',
+                                  'step_ragan_dim8_64', 'step_hinge_dim8_64', 'step_lsgan_dim8_64',
+                                  'step_wgangp_dim8_64'])
 def test_flagged_training_steps_vs_reference_golden(name):
     """BaseModel --concat, BaseModel --concat --reparam, AdaINModel --use_dis_content --ms_dis (4
-    iterations through the d_iter schedule): every loss of every iteration within 1e-2 of the
-    reference's recorded value."""
+    iterations through the d_iter schedule), --use_ragan, --gan_mode hinge / lsgan / wgangp: every
+    loss of every iteration within 1e-2 of the reference's recorded value."""
     from tests.model_cases import flag_step_vs_golden
     _check(flag_step_vs_golden(name), 1e-2, 0.0)
 
