@@ -136,6 +136,15 @@ int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss, 
 int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int H, int W, int C, int pad,
                     int act, float slope, void* dy, void* stream);
 
+/* ---- optional generator variants -------------------------------------------- */
+/* nn.Upsample(scale_factor=2, mode='nearest') of UpsampleBlock(up_type='nearest')  blocks.py:74-76:
+ * dense [N,H,W,C] -> dense [N,2H,2W,C]; bwd sums each 2x2 block of dy [N,2H,2W,C] into dx [N,H,W,C] */
+int mt_upsample2_fwd(const void* x, int N, int H, int W, int C, void* out, void* stream);
+int mt_upsample2_bwd(const void* dy, int N, int H, int W, int C, void* dx, void* stream);
+/* nn.Dropout(0.5) of the decoder blocks (--use_dropout)  blocks.py:133-134,152,190: out = x * m over
+ * n bf16 elements, m holding 0 or 1/(1-p); also its own adjoint (dx = dy * m) */
+int mt_mul(const void* x, const void* m, long long n, void* out, void* stream);
+
 /* ---- style-encoder pooling algebra, RGB head, content regulariser --------------------------- */
 /* nn.AvgPool2d(2,2) over the interior of a padded buffer -> dense [N,H/2,W/2,C]  blocks.py:113 */
 int mt_avgpool2_fwd(const void* x_pad, int pad, int N, int H, int W, int C, void* out,

@@ -338,6 +338,60 @@ scale_interior_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
   }
 }
 
+// ---- optional generator variants ------------------------------------------------
+// nn.Upsample(scale_factor=2, mode='nearest') (blocks.py:75): out[n, y, x, :] = in[n, y/2, x/2, :].
+// One 16-byte vector per thread, indexed by the OUTPUT (coalesced stores; each input vector is read
+// by four threads, three of them out of L1/L2).
+__global__ void __launch_bounds__(256)
+upsample2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, int C,
+                     __nv_bfloat16* __restrict__ out) {
+  const int V = C / 8, Ho = 2 * H, Wo = 2 * W;
+  const long long total = (long long)N * Ho * Wo * V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
+    const int w = (int)(t % Wo); t /= Wo;
+    const int h = (int)(t % Ho); const int n = (int)(t / Ho);
+    const uint4 r = *reinterpret_cast<const uint4*>(
+        x + (((long long)n * H + h / 2) * W + w / 2) * C + v * 8);
+    *reinterpret_cast<uint4*>(out + (size_t)i * 8) = r;
+  }
+}
+// adjoint: dx[n, h, w, :] = sum of the 2x2 block of dy (fp32 sum, one rounding)
+__global__ void __launch_bounds__(256)
+upsample2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int N, int H, int W, int C,
+                     __nv_bfloat16* __restrict__ dx) {
+  const int V = C / 8, Wo = 2 * W;
+  const long long total = (long long)N * H * W * V;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int v = (int)(i % V); unsigned t = i / V;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H); const int n = (int)(t / H);
+    const __nv_bfloat16* p = dy + (((long long)n * 2 * H + 2 * h) * Wo + 2 * w) * C + v * 8;
+    const uint4 r0 = ldg16(p), r1 = ldg16(p + C), r2 = ldg16(p + (size_t)Wo * C),
+                r3 = ldg16(p + (size_t)Wo * C + C);
+    float a[8], b[8], c[8], d[8];
+    cvt8(r0, a); cvt8(r1, b); cvt8(r2, c); cvt8(r3, d);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = (a[j] + b[j]) + (c[j] + d[j]);
+    store8(dx + (size_t)i * 8, a);
+  }
+}
+// nn.Dropout(0.5) (blocks.py:133-134,152,190) with the mask drawn by the host framework:
+// out = x * m, m in {0, 1/(1-p)} stored as bf16 (exact); the same kernel is its own adjoint (g * m).
+__global__ void __launch_bounds__(256)
+mul_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ m, long long nvec,
+           __nv_bfloat16* __restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    const uint4 rx = ldg16(x + i * 8), rm = ldg16(m + i * 8);
+    float a[8], b[8];
+    cvt8(rx, a); cvt8(rm, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] *= b[j];
+    store8(out + i * 8, a);
+  }
+}
+
 }  // namespace mt
 
 using namespace mt;
@@ -345,6 +399,23 @@ using namespace mt;
 #define BF(p) ((__nv_bfloat16*)(p))
 #define CBF(p) ((const __nv_bfloat16*)(p))
 
+extern "C" int mt_upsample2_fwd(const void* x, int N, int H, int W, int C, void* out, void* stream) {
+  if (C % 8) return -1003;
+  upsample2_fwd_kernel<<<grid_for((long long)N * H * W * 4 * (C / 8), 256), 256, 0, ST(stream)>>>(
+      CBF(x), N, H, W, C, BF(out));
+  return cuda_rc();
+}
+extern "C" int mt_upsample2_bwd(const void* dy, int N, int H, int W, int C, void* dx, void* stream) {
+  if (C % 8) return -1003;
+  upsample2_bwd_kernel<<<grid_for((long long)N * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
+      CBF(dy), N, H, W, C, BF(dx));
+  return cuda_rc();
+}
+extern "C" int mt_mul(const void* x, const void* m, long long n, void* out, void* stream) {
+  if (n % 8) return -1003;
+  mul_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(x), CBF(m), n / 8, BF(out));
+  return cuda_rc();
+}
 extern "C" int mt_avgpool2_fwd(const void* x_pad, int pad, int N, int H, int W, int C, void* out,
                                void* stream) {
   if (C % 8) return -1003;

@@ -42,7 +42,7 @@ def _wgrad(weight, x, dy, geom, needed):
     has a gradient buffer (FlatAdam's bucket view), else returned for autograd to accumulate."""
     if not needed:
         return None
-    gr = weight.grad
+    gr = weight.grad if weight.is_leaf else None     # spectral-normalised weights are graph nodes
     if gr is not None and gr.is_contiguous() and gr.dtype == torch.float32 and torch.is_grad_enabled() is False:
         ops.conv_wgrad_into(x, dy, geom, gr)
         return None
@@ -309,3 +309,31 @@ class ResidualPad(Function):
             else:
                 dx = G
         return dx, G, None, None
+
+
+class UpsampleNearest2(Function):
+    """nn.Upsample(scale_factor=2, mode='nearest') of UpsampleBlock(up_type='nearest') (blocks.py:74-76)
+    on a dense NHWC bf16 tensor."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return ops.upsample2_fwd(_c(x))
+
+    @staticmethod
+    def backward(ctx, dout):
+        return ops.upsample2_bwd(_c(dout))
+
+
+class MaskMul(Function):
+    """nn.Dropout(p) in training mode (blocks.py:133-134,152,190): x * m with m in {0, 1/(1-p)} drawn by
+    the caller (bf16, same shape as x)."""
+
+    @staticmethod
+    def forward(ctx, x, m):
+        ctx.save_for_backward(m)
+        return ops.mul(_c(x), m)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (m,) = ctx.saved_tensors
+        return ops.mul(_c(dout), m), None

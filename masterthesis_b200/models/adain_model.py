@@ -4,7 +4,8 @@ src/models/adain_model.py:9-430, driving the CUDA networks of models/core/networ
 Differences that do not change results: the generator forwards of the
 discriminator phase run without an autograd graph (the reference builds one and never uses it,
 :203); weight gradients nobody consumes are skipped (D1 in phase G1, Es in phase G2, item 11);
-the real and fake discriminator passes are batched into one call; the 13 loss scalars are read
+the real and fake discriminator passes are batched into one call (two calls under --dis_sn,
+where each reference forward advances the power iteration); the 13 loss scalars are read
 back with ONE host sync per iteration instead of 13 `.item()` calls.
 """
 import contextlib
@@ -18,7 +19,7 @@ import torch.nn.functional as F
 from .. import functional as Fn
 from .. import ops
 from ..optim import FlatAdam
-from .core import networks
+from .core import blocks, networks
 from .core.networks import CONTENT_PAD
 from .model import Model
 
@@ -34,9 +35,6 @@ class AdaINModel(Model):
     def __init__(self, args):
         super().__init__(args)
         self.latent_dim = args.latent_dim
-        for flag, why in (('dis_sn', 'spectral norm'), ('use_dropout', 'dropout')):
-            if getattr(args, flag, False):
-                raise NotImplementedError(f"--{flag} ({why}) is outside the accelerated path (SURVEY.md §8f)")
         if getattr(args, 'vgg_loss', None) is not None:
             raise NotImplementedError("VGG perceptual loss needs downloaded weights; not on the accelerated path")
         m = self.model
@@ -215,14 +213,24 @@ class AdaINModel(Model):
 
     def backward_discriminator(self, netD, real, fake, c_org):
         n = real.shape[0]
-        both = torch.cat((fake.detach(), real))
+        if self.args.dis_sn:
+            # spectral norm: every reference forward runs one power iteration, so the fake and the real
+            # call see different W / sigma (:207-209) -> two calls, in the reference's order
+            outs_f, outs_r = netD.run(fake.detach()), netD.run(real)
+            if not self.args.ms_dis:
+                outs_f, outs_r = [outs_f], [outs_r]
+            outs = [(torch.cat((pf, pr)), torch.cat((cf, cr))) for (pf, cf), (pr, cr) in zip(outs_f, outs_r)]
+        else:
+            outs = netD.run(torch.cat((fake.detach(), real)))
+            if not self.args.ms_dis:
+                outs = [outs]
         if self.args.ms_dis:           # backward_multi_scale_discriminator (:182-199)
             loss_d_adv, loss_d_cls = 0, 0
-            for pred, pred_cls in netD.run(both):
+            for pred, pred_cls in outs:
                 loss_d_adv = loss_d_adv + self.gan_loss(pred[:n], 0) + self.gan_loss(pred[n:], 1)
                 loss_d_cls = loss_d_cls + _bce(pred_cls[n:], c_org)
         else:
-            pred, pred_cls = netD.run(both)
+            pred, pred_cls = outs[0]
             pred_fake, pred_real = pred[:n], pred[n:]
             if self.args.use_ragan:        # relativistic average (:206-208)
                 loss_d_adv = (self.gan_loss(pred_real - torch.mean(pred_fake), 1) +
@@ -277,7 +285,7 @@ class AdaINModel(Model):
                 cls = cls + _bce(pred_fake_cls, c_org)
             return adv, cls * self.args.lambda_cls_G
         if self.args.use_ragan:
-            if netD_real is netD:          # one call over both halves (no batch statistics in D)
+            if netD_real is netD and not self.args.dis_sn:   # one call over both halves (no batch statistics in D)
                 n = fake.shape[0]
                 pred, pred_cls = netD.run(torch.cat((fake, real)))
                 pred_fake, pred_fake_cls, pred_real = pred[:n], pred_cls[:n], pred[n:]
@@ -367,6 +375,7 @@ class AdaINModel(Model):
 
     # ------------------------------------------------------------------ the iteration (:421-430)
     def optimize_parameters(self, global_iter):
+        blocks.set_dropout_rng(self.rng)       # --use_dropout masks: replayed draws (parity) or device Philox
         if self.args.use_dis_content and global_iter % self.args.d_iter != 0:
             self._run_iteration(self._content_iteration, 'content')
         else:

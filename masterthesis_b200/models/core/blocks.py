@@ -63,6 +63,48 @@ class _ConvParams(nn.Module):
             self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem)))
         return self._pack[1]
 
+    # spectral normalisation ------------------------------------------------
+    spectral = False
+
+    def enable_spectral_norm(self, eps=1e-12):
+        """torch.nn.utils.spectral_norm(module, 'weight', n_power_iterations=1, eps, dim) as the
+        reference wraps its convs (functions.py:113-121, blocks.py:34-35,71-72): the parameter becomes
+        `weight_orig`, the power-iteration vectors are the buffers `weight_u` / `weight_v` (same
+        state_dict keys and order: bias, weight_orig, weight_u, weight_v)."""
+        w = self._parameters.pop('weight')
+        self.register_parameter('weight_orig', w)
+        h, wd = self._sn_matrix(w).shape
+        self.register_buffer('weight_u', F.normalize(w.new_empty(h).normal_(0, 1), dim=0, eps=eps))
+        self.register_buffer('weight_v', F.normalize(w.new_empty(wd).normal_(0, 1), dim=0, eps=eps))
+        self.sn_eps = eps
+        self.spectral = True
+        return self
+
+    def _sn_matrix(self, w):
+        # dim = 1 for transposed convs (functions.py:115-119), 0 otherwise
+        return w.transpose(0, 1).flatten(1) if self.transposed else w.flatten(1)
+
+    def sn_weight(self):
+        """W / sigma(W).  Training mode runs ONE power iteration per call (in place on the buffers,
+        outside the graph), exactly once per reference forward; sigma = u . (W v) is differentiated
+        through W only.  The matrix-vector products are two tiny GEMVs per conv on the fp32 master
+        weight (host framework ops); the convolution itself consumes the re-packed bf16 operand."""
+        w, u, v = self.weight_orig, self.weight_u, self.weight_v
+        wm = self._sn_matrix(w)
+        if self.training:
+            with torch.no_grad():
+                v.copy_(F.normalize(torch.mv(wm.t(), u), dim=0, eps=self.sn_eps))
+                u.copy_(F.normalize(torch.mv(wm, v), dim=0, eps=self.sn_eps))
+        sigma = torch.dot(u.clone(), torch.mv(wm, v.clone()))
+        return w / sigma
+
+    def operands(self, zpad=0, stem=False):
+        """(weight as autograd sees it, bf16 forward operand, bf16 backward operand)"""
+        if not self.spectral:
+            return (self.weight,) + tuple(self.packed(zpad, stem))
+        w = self.sn_weight()
+        return (w,) + tuple(ops.pack_weight(w, self.geom(zpad, stem)))
+
     def extra_repr(self):
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
                 f"stride={self.stride}, padding={self.padding}, bias={self.bias is not None}")
@@ -81,6 +123,35 @@ class ConvTranspose2d(_ConvParams):
                  bias=True):
         self.output_padding = output_padding
         super().__init__(in_channels, out_channels, kernel_size, stride, padding, bias)
+
+
+# ------------------------------------------------------------------------- dropout masks
+_DROPOUT_RNG = [None]
+
+
+def set_dropout_rng(rng):
+    """rng(shape_nchw) -> N(0,1) CPU tensor: replayed draws of the parity harness (keep = draw > 0,
+    the rule oracle/make_golden.py installs in the reference); None: device Philox (torch.rand)."""
+    _DROPOUT_RNG[0] = rng
+
+
+def dropout_mask(x, C, p):
+    """bf16 mask of x's NHWC shape holding 0 or 1/(1-p)   (nn.Dropout(p), blocks.py:133-134,152,190)"""
+    N, H, W, Cs = x.shape
+    rng = _DROPOUT_RNG[0]
+    if rng is not None:
+        keep = torch.zeros((N, H, W, Cs), dtype=torch.bool, device=x.device)
+        keep[..., :C] = (rng((N, C, H, W)) > 0).to(x.device).permute(0, 2, 3, 1)
+    else:
+        keep = torch.rand((N, H, W, Cs), device=x.device) >= p
+    return keep.to(torch.bfloat16) * (1.0 / (1.0 - p))
+
+
+def apply_dropout(h, C, module):
+    """h: dense NHWC bf16; module: the block's nn.Dropout (identity in eval mode)"""
+    if not module.training or module.p == 0:
+        return h
+    return Fn.MaskMul.apply(h, dropout_mask(h, C, module.p))
 
 
 # ------------------------------------------------------------------------- layout edges
@@ -128,9 +199,8 @@ class ConvBlock(nn.Module):
         if pad_cls is not None:
             layers.append(pad_cls(padding))
             self.rpad, padding = padding, 0
-        if sn:
-            spectral_norm(None)
-        layers.append(Conv2d(input_dim, output_dim, kernel_size, stride, padding, bias=bias))
+        conv = Conv2d(input_dim, output_dim, kernel_size, stride, padding, bias=bias)
+        layers.append(spectral_norm(conv) if sn else conv)
         if norm_cls is not None:
             layers.append(norm_cls(output_dim))
         if act_cls is not None:
@@ -167,17 +237,26 @@ class ConvBlock(nn.Module):
         self._check()
         conv = self.conv
         g = conv.geom(self.zpad, self.stem)
-        wf, wb = conv.packed(self.zpad, self.stem)
+        w, wf, wb = conv.operands(self.zpad, self.stem)
         act = self.act if act_override == 'keep' else act_override
         norm = self.norm
         if norm is None:
             assert noise is None
-            return Fn.ConvAct.apply(x, conv.weight, conv.bias, wf, wb, g, act, out_pad)
+            return Fn.ConvAct.apply(x, w, conv.bias, wf, wb, g, act, out_pad)
         if isinstance(norm, LayerNorm):
             mode, p1, p2 = 'layer', (norm.weight if norm.affine else None), (norm.bias if norm.affine else None)
         else:
             mode, p1, p2 = 'instance', None, None
-        return Fn.ConvNormAct.apply(x, conv.weight, conv.bias, wf, wb, g, mode, p1, p2, act, out_pad, noise)
+        return Fn.ConvNormAct.apply(x, w, conv.bias, wf, wb, g, mode, p1, p2, act, out_pad, noise)
+
+    def run_image_head(self, x):
+        """The decoders' image head when up_type != 'transpose' (networks.py:187-188,252-253,314-315:
+        ConvBlock(dim, 3, 7, 1, 3, activation='tanh'), zero padding, no bias): dense NHWC bf16 in, NCHW
+        fp32 image out.  The conv stores its pre-activation; tanh is applied on the 3-channel fp32
+        image at the layout edge (host framework op, like the NHWC->NCHW conversion it is fused with)."""
+        assert self.act == 'tanh' and self.norm is None and self.rpad == 0
+        y = self.run(x, act_override=None)
+        return torch.tanh(from_padded(y, self.conv.out_channels))
 
     def forward(self, x):
         y = self.run(to_padded(x, self.rpad))
@@ -195,14 +274,25 @@ class UpsampleBlock(nn.Module):
         get_padding_layer(padding_type)
         act_cls = get_activation_layer(activation)
         norm_cls = get_norm_layer(norm_layer)
-        if sn:
-            spectral_norm(None)
         layers = []
+        self.up_type = up_type
         if 'transpose' in up_type:
-            layers.append(ConvTranspose2d(input_dim, output_dim, kernel_size, stride, padding,
-                                          output_padding, bias=bias))
-        elif 'nearest' in up_type or 'pixelshuffle' in up_type:
-            raise NotImplementedError(f"up_type {up_type} is outside the accelerated path (SURVEY.md 8f-4)")
+            convt = ConvTranspose2d(input_dim, output_dim, kernel_size, stride, padding,
+                                    output_padding, bias=bias)
+            layers.append(spectral_norm(convt) if sn else convt)
+        elif 'nearest' in up_type:
+            # blocks.py:74-76: note that the inner ConvBlock gets the padding CLASS (or None) as its
+            # padding_type string, so it never pads by reflection: zero padding `padding`
+            layers += [nn.Upsample(scale_factor=2, mode='nearest'),
+                       ConvBlock(input_dim, output_dim, kernel_size, 1, padding, padding_type=None,
+                                 bias=bias, sn=sn)]
+        elif 'pixelshuffle' in up_type:
+            # blocks.py:77-79 builds ConvBlock(input_dim, output_dim) + PixelShuffle(2) and then a norm
+            # layer for output_dim channels on a tensor that has output_dim / 4: the reference itself
+            # raises in its first forward (F.layer_norm shape mismatch; DecoderConcat: 138 % 4 != 0), so
+            # there is no behaviour to reproduce
+            raise NotImplementedError("up_type 'pixelshuffle' cannot run in the reference either "
+                                      "(norm layer built for 4x the channels PixelShuffle leaves)")
         else:
             raise NotImplementedError(f"Mode {up_type} is not supported at the moment")
         if norm_cls is not None:
@@ -213,21 +303,24 @@ class UpsampleBlock(nn.Module):
 
     @property
     def conv(self):
-        return self.block[0]
+        return self.block[1].conv if 'nearest' in self.up_type else self.block[0]
 
     @property
     def norm(self):
-        return _find(self.block, (nn.InstanceNorm2d, LayerNorm))
+        for m in self.block:
+            if isinstance(m, (nn.InstanceNorm2d, LayerNorm)):
+                return m
+        return None
 
     @property
     def act(self):
         last = self.block[-1]
-        return None if isinstance(last, (ConvTranspose2d, nn.InstanceNorm2d, LayerNorm)) else act_name(last)
+        return None if isinstance(last, (ConvTranspose2d, ConvBlock, nn.InstanceNorm2d, LayerNorm)) else act_name(last)
 
     @property
     def is_rgb_head(self):
         c = self.conv
-        return (c.kernel_size == 1 and c.stride == 1 and c.padding == 0 and c.bias is None
+        return ('transpose' in self.up_type and not c.spectral and c.kernel_size == 1 and c.stride == 1 and c.padding == 0 and c.bias is None
                 and self.norm is None and self.act == 'tanh' and c.out_channels <= 4)
 
     def run(self, x, out_pad=0):
@@ -235,18 +328,24 @@ class UpsampleBlock(nn.Module):
         c = self.conv
         if self.is_rgb_head:
             return Fn.RgbHead.apply(x, c.weight)
-        if not (c.kernel_size == 3 and c.stride == 2 and c.padding == 1 and c.output_padding == 1):
-            raise NotImplementedError("only ConvTranspose2d(k=3,s=2,p=1,op=1) and the 1x1 tanh head are accelerated")
-        g = c.geom(1)
-        wf, wb = c.packed(1)
+        if 'nearest' in self.up_type:
+            # Upsample(x2) -> zero-padded stride-1 conv (TMA out-of-bounds fill supplies the zeros)
+            x = Fn.UpsampleNearest2.apply(x)
+            g = c.geom(self.block[1].zpad)
+            w, wf, wb = c.operands(self.block[1].zpad)
+        else:
+            if not (c.kernel_size == 3 and c.stride == 2 and c.padding == 1 and c.output_padding == 1):
+                raise NotImplementedError("only ConvTranspose2d(k=3,s=2,p=1,op=1) and the 1x1 tanh head are accelerated")
+            g = c.geom(1)
+            w, wf, wb = c.operands(1)
         norm = self.norm
         if norm is None:
-            return Fn.ConvAct.apply(x, c.weight, c.bias, wf, wb, g, self.act, out_pad)
+            return Fn.ConvAct.apply(x, w, c.bias, wf, wb, g, self.act, out_pad)
         if isinstance(norm, LayerNorm):
             mode, p1, p2 = 'layer', (norm.weight if norm.affine else None), (norm.bias if norm.affine else None)
         else:
             mode, p1, p2 = 'instance', None, None
-        return Fn.ConvNormAct.apply(x, c.weight, c.bias, wf, wb, g, mode, p1, p2, self.act, out_pad, None)
+        return Fn.ConvNormAct.apply(x, w, c.bias, wf, wb, g, mode, p1, p2, self.act, out_pad, None)
 
     def forward(self, x):
         y = self.run(to_padded(x, 0))
@@ -312,11 +411,16 @@ class ResnetBlock(nn.Module):
         self.dropout = dropout
 
     def run(self, x, out_pad=1, noise=None):
-        if self.dropout:
-            raise NotImplementedError("--use_dropout is outside the accelerated path (SURVEY.md 8f-4)")
         b1, b2 = self.model[0], self.model[1]
         if not (isinstance(b1.norm, nn.InstanceNorm2d) and b1.rpad == 1):
             raise NotImplementedError("ResnetBlock is accelerated for instance norm + reflect padding")
+        if self.dropout and self.model[2].training:
+            # x + Dropout(block(x)): the mask sits between the second norm and the residual add, so the
+            # block runs un-fused: ConvBlock, ConvBlock, mask, residual add (+ reflection border)
+            assert noise is None
+            h = b2.run(b1.run(x, out_pad=1), out_pad=0)
+            h = apply_dropout(h, b2.conv.out_channels, self.model[2])
+            return Fn.ResidualPad.apply(x, h, 1, out_pad)
         c1, c2 = b1.conv, b2.conv
         (wf1, wb1), (wf2, wb2) = c1.packed(), c2.packed()
         return Fn.ResBlock.apply(x, c1.weight, c2.weight, wf1, wb1, wf2, wb2, c1.geom(), 'instance',
@@ -341,10 +445,16 @@ class AdaINResnetBlock(nn.Module):
         self._dropout = dropout
 
     def run(self, x, z, out_pad=1):
-        if self._dropout:
-            raise NotImplementedError("--use_dropout is outside the accelerated path (SURVEY.md 8f-4)")
         gb = self.norm.modulation(z)
         c1, c2 = self.conv1.conv, self.conv2.conv
+        if self._dropout and self.dropout.training:
+            # the mask sits between the second AdaIN and the residual add: un-fused plan
+            (wf1, wb1), (wf2, wb2) = c1.packed(), c2.packed()
+            h = Fn.ConvNormAct.apply(x, c1.weight, None, wf1, wb1, c1.geom(), 'adain', gb, None,
+                                     act_name(self.activation), 1, None)
+            h = Fn.ConvNormAct.apply(h, c2.weight, None, wf2, wb2, c2.geom(), 'adain', gb, None, None, 0, None)
+            h = apply_dropout(h, c2.out_channels, self.dropout)
+            return Fn.ResidualPad.apply(x, h, 1, out_pad)
         (wf1, wb1), (wf2, wb2) = c1.packed(), c2.packed()
         return Fn.ResBlock.apply(x, c1.weight, c2.weight, wf1, wb1, wf2, wb2, c1.geom(), 'adain',
                                  gb, act_name(self.activation), out_pad, None)
@@ -383,12 +493,12 @@ class DecResnetBlock(nn.Module):
 
     def run(self, x, z, out_pad=1):
         """x padded by 1; z [N, add_channel] fp32.  Returns x + block(x, z) padded by out_pad."""
-        if self._dropout:
-            raise NotImplementedError("--use_dropout is outside the accelerated path (SURVEY.md 8f-4)")
         if self._stride != 1 or not isinstance(self.norm, nn.InstanceNorm2d) or self.conv1.rpad != 1:
             raise NotImplementedError("DecResnetBlock is accelerated for stride 1, instance norm, reflect padding")
         h = self._half(x, z, self.conv1, self.block1, 1)
         h = self._half(h, z, self.conv2, self.block2, 0)
+        if self._dropout:
+            h = apply_dropout(h, self.n_channel, self.dropout)
         return Fn.ResidualPad.apply(x, h, 1, out_pad)
 
     def forward(self, x, z):

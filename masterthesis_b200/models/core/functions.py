@@ -105,10 +105,13 @@ def init_weights(net, init_type='normal', init_gain=0.02):
 
     def visit(m):
         name = type(m).__name__
-        if hasattr(m, 'weight') and name.startswith('Conv'):
+        if (hasattr(m, 'weight') or getattr(m, 'spectral', False)) and name.startswith('Conv'):
             if init_type not in makers:
                 raise NotImplementedError('initialization method [%s] is not implemented' % init_type)
-            makers[init_type](m.weight.data)
+            if hasattr(m, 'weight'):
+                makers[init_type](m.weight.data)
+            # under spectral norm the reference initialises `m.weight`, a plain tensor copy that the next
+            # forward overwrites: `weight_orig` keeps torch's default init, only the bias is reset
             if getattr(m, 'bias', None) is not None:
                 init.constant_(m.bias.data, 0.0)
         elif 'BatchNorm2d' in name:
@@ -133,4 +136,12 @@ def init_net(net, init_type='normal', init_gain=0.02, device='cpu', gpu_ids=[]):
 
 
 def spectral_norm(module, name='weight', n_power_iterations=1, eps=1e-12, dim=None):
-    raise NotImplementedError("spectral norm (--dis_sn) is outside the accelerated path (SURVEY.md 8f-4)")
+    """reference functions.py:113-121 -> torch.nn.utils.spectral_norm(module, name, 1, eps, dim) with
+    dim = 1 for transposed convs, 0 otherwise.  `module` is one of this package's conv parameter
+    holders (blocks.Conv2d / blocks.ConvTranspose2d); the power iteration and W / sigma run in
+    `module.sn_weight()` at every forward (blocks.py of this package)."""
+    if name != 'weight' or n_power_iterations != 1:
+        raise NotImplementedError("spectral norm is built as the reference uses it: name='weight', one power iteration")
+    if dim is not None and dim != (1 if module.transposed else 0):
+        raise NotImplementedError("spectral norm over a non-default dim")
+    return module.enable_spectral_norm(eps)

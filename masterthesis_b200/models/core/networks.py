@@ -195,17 +195,21 @@ class AdaINDecoder(nn.Module):
                 out = dec.run(out, out_pad=0 if i == n - 1 else 1)
         if n == 0:
             out = out[:, CONTENT_PAD:-CONTENT_PAD, CONTENT_PAD:-CONTENT_PAD, :].contiguous()
-        for up in self.dec2:
-            out = up.run(out)
-        return out
+        return _run_ups(self.dec2, out)
 
     def forward(self, x, z, c):
         return self.run(to_padded(x, CONTENT_PAD), z, c)
 
 
+def _run_head(head, out):
+    """image head: ConvTranspose2d 1x1 + tanh (up_type 'transpose') or the 7x7 ConvBlock + tanh"""
+    return head.run_image_head(out) if isinstance(head, ConvBlock) else head.run(out)
+
+
 def _run_ups(dec2, out):
-    for up in dec2:
-        out = up.run(out)
+    n = len(dec2)
+    for i, up in enumerate(dec2):
+        out = _run_head(up, out) if i == n - 1 else up.run(out)
     return out
 
 
@@ -288,7 +292,7 @@ class DecoderConcat(nn.Module):
             out = blk.run(out, out_pad=0 if i == n - 1 else 1)
         out = self.dec2.run(Fn.ConcatChannels.apply(out, z, self._c1, 0))
         out = self.dec3.run(Fn.ConcatChannels.apply(out, z, self._c2, 0))
-        return self.dec4.run(Fn.ConcatChannels.apply(out, z, self._c3, 0))
+        return _run_head(self.dec4, Fn.ConcatChannels.apply(out, z, self._c3, 0))
 
     def forward(self, x, z, c):
         return self.run(to_padded(x, CONTENT_PAD), z, c)

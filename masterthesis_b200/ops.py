@@ -459,6 +459,42 @@ def act_bwd_fold(dpad, out_pad, pad, act):
     return dy
 
 
+# ----------------------------------------------------------------------------- optional variants
+@_checked
+def upsample2_fwd(x):
+    """nn.Upsample(scale_factor=2, mode='nearest') on dense NHWC bf16 (blocks.py:75)."""
+    _require_cuda(x)
+    N, H, W, C = x.shape
+    assert x.is_contiguous() and x.dtype == torch.bfloat16
+    out = empty_act(N, 2 * H, 2 * W, C, x.device)
+    check(_lib.lib().mt_upsample2_fwd(_p(x), N, H, W, C, _p(out), _stream()), "upsample2_fwd")
+    _count()
+    return out
+
+
+@_checked
+def upsample2_bwd(dy):
+    _require_cuda(dy)
+    N, Ho, Wo, C = dy.shape
+    assert dy.is_contiguous() and Ho % 2 == 0 and Wo % 2 == 0
+    dx = empty_act(N, Ho // 2, Wo // 2, C, dy.device)
+    check(_lib.lib().mt_upsample2_bwd(_p(dy), N, Ho // 2, Wo // 2, C, _p(dx), _stream()), "upsample2_bwd")
+    _count()
+    return dx
+
+
+@_checked
+def mul(x, m):
+    """x * m on bf16 tensors of the same shape (dropout mask; its own adjoint)."""
+    _require_cuda(x)
+    assert x.shape == m.shape and x.is_contiguous() and m.is_contiguous()
+    assert x.dtype == torch.bfloat16 and m.dtype == torch.bfloat16
+    out = _T.empty_like(x)
+    check(_lib.lib().mt_mul(_p(x), _p(m), x.numel(), _p(out), _stream()), "mul")
+    _count()
+    return out
+
+
 # ----------------------------------------------------------------------------- pooling / heads
 @_checked
 def avgpool2_fwd(x_pad, pad):

@@ -3,7 +3,8 @@
 
     python -m oracle.make_golden            # only works where /root/reference exists
 
-The three RNG call sites of the reference (misc.py:25, networks.py:132, adain_model.py:84) are
+The RNG call sites of the reference (misc.py:25, networks.py:132, adain_model.py:84, and the
+nn.Dropout(0.5) of --use_dropout: blocks.py:133-134,152,190) are
 redirected to oracle.synth.Draws so that the noise is reproducible from a seed instead of being
 stored; the arithmetic is the reference's own.  Weights are synthesised per state_dict key
 (oracle/synth.py) and loaded with load_state_dict, so no weight file is committed either.
@@ -47,6 +48,13 @@ def patch_rng(models, draws):
     def get_z_random(self, bs, latent_dim):
         return draws((bs, latent_dim)).to(self.device)
 
+    def dropout_forward(self, x):
+        # nn.Dropout(0.5) (blocks.py:133-134,152,190) with a replayable mask: keep = draw > 0, scale 1/(1-p)
+        if not self.training:
+            return x
+        return x * (draws(tuple(x.size())) > 0).to(x.dtype) / (1.0 - self.p)
+
+    torch.nn.Dropout.forward = dropout_forward
     misc.GaussianNoiseLayer.forward = noise_forward
     networks.ReparameterizedStyleEncoder.reparameterize = reparameterize
     adain_model.AdaINModel.get_z_random = get_z_random
@@ -228,7 +236,7 @@ if __name__ == '__main__':
     os.makedirs(OUT, exist_ok=True)
     ref_import.import_reference()
     torch.set_num_threads(os.cpu_count())
-    which = sys.argv[1:] or ['adain', 'base', 'gan']
+    which = sys.argv[1:] or ['adain', 'base', 'gan', 'opt']
     if 'adain' in which:
         nets_case('nets_dim16_64', dim=16, size=64, N=2)
         nets_case('nets_dim64_256', dim=64, size=256, N=1, sub=8)
@@ -238,6 +246,12 @@ if __name__ == '__main__':
         step_case('step_hinge_dim8_64', dim=8, size=64, B=1, gan_mode='hinge')
         step_case('step_lsgan_dim8_64', dim=8, size=64, B=1, gan_mode='lsgan')
         step_case('step_wgangp_dim8_64', dim=8, size=64, B=1, gan_mode='wgangp')
+    if 'opt' in which:      # optional generator / discriminator variants
+        step_case('step_nearest_dim8_64', dim=8, size=64, B=1, up_type='nearest')
+        step_case('step_dropout_dim8_64', dim=8, size=64, B=1, use_dropout=True)
+        step_case('step_sn_dim8_64', dim=8, size=64, B=1, dis_sn=True)
+        step_case('step_basec_ndsn_dim8_64', dim=8, size=64, B=1, model='BaseModel', concat=True,
+                  up_type='nearest', use_dropout=True, dis_sn=True)
     if 'base' in which:
         nets_base_case('nets_base_dim16_64', dim=16, size=64, N=2)
         step_case('step_basec_dim8_64', dim=8, size=64, B=1, model='BaseModel', concat=True)

@@ -56,9 +56,11 @@ class AdaINStep:
     def __init__(self, params, B, lr=1e-4, betas=(0.5, 0.999), wd=1e-4, lambda_rec=10.0,
                  lambda_cls=1.0, lambda_cls_G=5.0, latent_dim=8, model='adain', reparam=True,
                  concat=False, ms_dis=False, use_dis_content=False, d_iter=3, gan_mode='vanilla',
-                 use_ragan=False):
-        self.P = {n: {k: v.detach().clone().requires_grad_(True) for k, v in params[n].items()}
-                  for n in params}
+                 use_ragan=False, up_type='transpose', use_dropout=False):
+        # spectral-norm buffers (`*_u`, `*_v`, --dis_sn) are state, not parameters
+        self.P = {n: {k: v.detach().clone().requires_grad_(not k.endswith(('_u', '_v')))
+                      for k, v in params[n].items()} for n in params}
+        self.up_type, self.use_dropout = up_type, use_dropout
         self.opt = {n: Adam(self.P[n], lr / 2.5 if n == 'content_discriminator' else lr, betas, wd)
                     for n in self.P}
         self.model, self.concat, self.ms_dis = model, concat, ms_dis
@@ -119,12 +121,14 @@ class AdaINStep:
         eps = draw((x.size(0), self.latent))
         return nets.style_encoder_reparam(self.P['style_encoder'], x, c, eps)
 
-    def G(self, zc, zs, c):
+    def G(self, zc, zs, c, draw=None):
+        """`draw` feeds the decoder's Dropout(0.5) masks (--use_dropout; training mode only)"""
+        kw = dict(up_type=self.up_type, drop=draw if self.use_dropout else None)
         if self.model == 'adain':
-            return nets.adain_decoder(self.P['decoder'], zc, zs, c)
+            return nets.adain_decoder(self.P['decoder'], zc, zs, c, **kw)
         if self.concat:
-            return nets.decoder_concat(self.P['decoder'], zc, zs, c)
-        return nets.decoder(self.P['decoder'], zc, zs, c)
+            return nets.decoder_concat(self.P['decoder'], zc, zs, c, **kw)
+        return nets.decoder(self.P['decoder'], zc, zs, c, **kw)
 
     def D(self, which, x):
         """-> list of (real/fake map, class logits), one entry per scale"""
@@ -142,9 +146,9 @@ class AdaINStep:
             z_sa, z_sb = torch.split(z_s, B)
             z_sr = draw((B, self.latent))
             img_ba, img_br = torch.split(self.G(torch.cat((z_cb, z_cb)), torch.cat((z_sa, z_sr)),
-                                                torch.cat((cls_a, cls_a))), B)
+                                                torch.cat((cls_a, cls_a)), draw), B)
             img_ab, img_ar = torch.split(self.G(torch.cat((z_ca, z_ca)), torch.cat((z_sb, z_sr)),
-                                                torch.cat((cls_b, cls_b))), B)
+                                                torch.cat((cls_b, cls_b)), draw), B)
             img_fake = torch.cat((img_ba, img_ab))
             img_random = torch.cat((img_br, img_ar))
         for which, fake in (('discriminator1', img_fake), ('discriminator2', img_random)):
@@ -169,16 +173,16 @@ class AdaINStep:
         z_s, mu, logvar = self.Es(img, c_org, draw)
         z_sa, z_sb = torch.split(z_s, B)
         img_ba, img_aa = torch.split(self.G(torch.cat((z_cb, z_ca)), torch.cat((z_sa, z_sa)),
-                                            torch.cat((cls_a, cls_a))), B)
+                                            torch.cat((cls_a, cls_a)), draw), B)
         img_ab, img_bb = torch.split(self.G(torch.cat((z_ca, z_cb)), torch.cat((z_sb, z_sb)),
-                                            torch.cat((cls_b, cls_b))), B)
+                                            torch.cat((cls_b, cls_b)), draw), B)
         img_fake = torch.cat((img_ba, img_ab))
         img_self = torch.cat((img_aa, img_bb))
         z_c_rec_b, z_c_rec_a = torch.split(self.Ec(img_fake, draw), B)
         z_s_rec, _, _ = self.Es(img_fake, c_org, draw)
         z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B)
         img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
-                           torch.cat((cls_a, cls_b)))
+                           torch.cat((cls_a, cls_b)), draw)
         g_content = None
         if self.use_dis_content:
             g_content = bce_logits(nets.content_discriminator(self.P['content_discriminator'], z_c), 1 - c_org)
@@ -203,7 +207,7 @@ class AdaINStep:
         cls_a, cls_b = torch.split(c_org, B)
         z_ca, z_cb = torch.split(self.Ec(img, draw), B)
         z_sr = draw((B, self.latent))
-        img_random = torch.cat((self.G(z_cb, z_sr, cls_a), self.G(z_ca, z_sr, cls_b)))
+        img_random = torch.cat((self.G(z_cb, z_sr, cls_a, draw), self.G(z_ca, z_sr, cls_b, draw)))
         # fakes: discriminator1 under ms_dis (:350) and under use_ragan (:362, reals from
         # discriminator2), else discriminator2
         which = 'discriminator1' if (self.ms_dis or self.use_ragan) else 'discriminator2'

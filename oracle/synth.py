@@ -16,7 +16,7 @@ def _gen(name, seed):
 def synth_tensor(name, shape, seed=0):
     g = _gen(name, seed)
     shape = tuple(shape)
-    if name.endswith('weight') and len(shape) >= 2:
+    if name.endswith(('weight', 'weight_orig')) and len(shape) >= 2:    # weight_orig: spectral norm (--dis_sn)
         fan_in = 1
         for s in shape[1:]:
             fan_in *= s

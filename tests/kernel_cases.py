@@ -208,7 +208,34 @@ def fused_stats_case(N, Cin, Cout, H, W, k=3, stride=1, transposed=False, bias=T
             "vs_torch": rel(tot, ref) * 1e2}
 
 
+def upsample_case(N, C, H, W, seed=0):
+    """nn.Upsample(x2, nearest) forward and its adjoint (UpsampleBlock 'nearest', blocks.py:74-76)."""
+    torch.manual_seed(seed)
+    x = bf(torch.randn(N, C, H, W, device=DEV)).requires_grad_(True)
+    y_ref = F.interpolate(x, scale_factor=2, mode="nearest")
+    dy = bf(torch.randn_like(y_ref))
+    y_ref.backward(dy)
+    y = ops.upsample2_fwd(to_nhwc(x.detach()))
+    dx = ops.upsample2_bwd(to_nhwc(dy))
+    return {"fwd_exact": 0.0 if torch.equal(from_nhwc(y, C), y_ref.detach()) else 1.0,
+            "bwd": rel(from_nhwc(dx, C), x.grad)}
+
+
+def mask_mul_case(N, C, H, W, seed=0):
+    """Dropout(0.5) as a mask multiply (blocks.py:133-134,152,190): exact in bf16 (x * 0 or x * 2)."""
+    torch.manual_seed(seed)
+    x = to_nhwc(bf(torch.randn(N, C, H, W, device=DEV)))
+    m = (torch.rand(x.shape, device=DEV) >= 0.5).to(torch.bfloat16) * 2.0
+    y = ops.mul(x, m)
+    return {"exact": 0.0 if torch.equal(y, x * m) else 1.0}
+
+
 CASES = {
+    # optional variants (SURVEY.md 8f-4): nearest up-sampling tail, 7x7 zero-padded image head, dropout
+    "upsample2": lambda: upsample_case(2, 40, 12, 20),
+    "mask_mul": lambda: mask_mul_case(2, 24, 16, 16),
+    "conv3x3_zpad1": lambda: conv_case(2, 128, 64, 32, 32, 3, 1, 0, zpad=1),
+    "conv7x7_zpad3_rgb": lambda: conv_case(2, 64, 3, 32, 32, 7, 1, 0, zpad=3, bias=False),
     "fused_stats_hot": lambda: fused_stats_case(2, 256, 256, 64, 64, bias=False),
     "fused_stats_overhang": lambda: fused_stats_case(3, 64, 136, 24, 40),
     "fused_stats_s2": lambda: fused_stats_case(2, 64, 128, 64, 64, k=3, stride=2),

@@ -89,11 +89,13 @@ def test_base_nets_vs_reference_golden():
 
 @pytest.mark.parametrize('name', ['step_basec_dim8_64', 'step_basecr_dim8_64', 'step_dcms_dim8_256',
                                   'step_ragan_dim8_64', 'step_hinge_dim8_64', 'step_lsgan_dim8_64',
-                                  'step_wgangp_dim8_64'])
+                                  'step_wgangp_dim8_64', 'step_nearest_dim8_64', 'step_dropout_dim8_64',
+                                  'step_sn_dim8_64', 'step_basec_ndsn_dim8_64'])
 def test_flagged_training_steps_vs_reference_golden(name):
     """BaseModel --concat, BaseModel --concat --reparam, AdaINModel --use_dis_content --ms_dis (4
-    iterations through the d_iter schedule), --use_ragan, --gan_mode hinge / lsgan / wgangp: every
-    loss of every iteration within 1e-2 of the reference's recorded value."""
+    iterations through the d_iter schedule), --use_ragan, --gan_mode hinge / lsgan / wgangp,
+    --up_type nearest, --use_dropout, --dis_sn, and BaseModel --concat with the last three together:
+    every loss of every iteration within 1e-2 of the reference's recorded value."""
     from tests.model_cases import flag_step_vs_golden
     _check(flag_step_vs_golden(name), 1e-2, 0.0)
 
@@ -118,6 +120,13 @@ def test_cuda_graph_with_content_discriminator_schedule():
     graph; 10 iterations (warm-up, both captures, replays) match the eager launch sequence."""
     from tests.model_cases import graph_vs_eager
     _check(graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True), 5e-3, 0.9999)
+
+
+def test_cuda_graph_with_spectral_norm_and_nearest_upsampling():
+    """--dis_sn (power iteration + W / sigma inside the captured iteration, u / v buffers advancing on
+    every replay) and --up_type nearest: graph replays match the eager launch sequence."""
+    from tests.model_cases import graph_vs_eager
+    _check(graph_vs_eager(dis_sn=True, up_type='nearest'), 5e-3, 0.9999)
 
 
 def test_sampling_graph_matches_eager():
