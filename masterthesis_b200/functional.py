@@ -290,8 +290,9 @@ class ResidualPad(Function):
     (the `out += residual` of DecResnetBlock, blocks.py:206)."""
 
     @staticmethod
-    def forward(ctx, x, y, x_pad, out_pad):
-        out = ops.affine_act_fwd(y, None, act=None, res_pad=x, res_p=x_pad, out_p=out_pad)
+    def forward(ctx, x, y, x_pad, out_pad, noise=None):
+        # `noise`: optional fp32 NHWC tensor added on top (GaussianNoiseLayer behind the block, misc.py:25)
+        out = ops.affine_act_fwd(y, None, act=None, res_pad=x, res_p=x_pad, noise=noise, out_p=out_pad)
         ctx.meta = (x_pad, out_pad, x.shape)
         return out
 
@@ -308,7 +309,7 @@ class ResidualPad(Function):
                 ops.add_interior_(dx, G, x_pad)
             else:
                 dx = G
-        return dx, G, None, None
+        return dx, G, None, None, None
 
 
 class UpsampleNearest2(Function):

@@ -412,15 +412,18 @@ class ResnetBlock(nn.Module):
 
     def run(self, x, out_pad=1, noise=None):
         b1, b2 = self.model[0], self.model[1]
-        if not (isinstance(b1.norm, nn.InstanceNorm2d) and b1.rpad == 1):
-            raise NotImplementedError("ResnetBlock is accelerated for instance norm + reflect padding")
-        if self.dropout and self.model[2].training:
-            # x + Dropout(block(x)): the mask sits between the second norm and the residual add, so the
-            # block runs un-fused: ConvBlock, ConvBlock, mask, residual add (+ reflection border)
-            assert noise is None
+        if b1.rpad != 1:
+            raise NotImplementedError("ResnetBlock is accelerated for reflect padding")
+        drop = self.dropout and self.model[2].training
+        if drop or not isinstance(b1.norm, nn.InstanceNorm2d):
+            # x + Dropout(block(x)) (the mask sits between the second norm and the residual add), or a
+            # norm other than InstanceNorm (--enc_norm layer: each ConvBlock has its own affine
+            # LayerNorm): the block runs un-fused: ConvBlock, ConvBlock, [mask], residual add (+ noise,
+            # + reflection border)
             h = b2.run(b1.run(x, out_pad=1), out_pad=0)
-            h = apply_dropout(h, b2.conv.out_channels, self.model[2])
-            return Fn.ResidualPad.apply(x, h, 1, out_pad)
+            if drop:
+                h = apply_dropout(h, b2.conv.out_channels, self.model[2])
+            return Fn.ResidualPad.apply(x, h, 1, out_pad, noise)
         c1, c2 = b1.conv, b2.conv
         (wf1, wb1), (wf2, wb2) = c1.packed(), c2.packed()
         return Fn.ResBlock.apply(x, c1.weight, c2.weight, wf1, wb1, wf2, wb2, c1.geom(), 'instance',

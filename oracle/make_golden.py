@@ -246,6 +246,9 @@ if __name__ == '__main__':
         step_case('step_hinge_dim8_64', dim=8, size=64, B=1, gan_mode='hinge')
         step_case('step_lsgan_dim8_64', dim=8, size=64, B=1, gan_mode='lsgan')
         step_case('step_wgangp_dim8_64', dim=8, size=64, B=1, gan_mode='wgangp')
+    if 'norms' in which or 'opt' in which:      # non-default --enc_norm / --dec_norm / --dis_norm
+        step_case('step_norms_dim8_128', dim=8, size=128, B=1, enc_norm='layer', dec_norm='instance',
+                  dis_norm='instance')
     if 'opt' in which:      # optional generator / discriminator variants
         step_case('step_nearest_dim8_64', dim=8, size=64, B=1, up_type='nearest')
         step_case('step_dropout_dim8_64', dim=8, size=64, B=1, use_dropout=True)

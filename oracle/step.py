@@ -56,11 +56,13 @@ class AdaINStep:
     def __init__(self, params, B, lr=1e-4, betas=(0.5, 0.999), wd=1e-4, lambda_rec=10.0,
                  lambda_cls=1.0, lambda_cls_G=5.0, latent_dim=8, model='adain', reparam=True,
                  concat=False, ms_dis=False, use_dis_content=False, d_iter=3, gan_mode='vanilla',
-                 use_ragan=False, up_type='transpose', use_dropout=False):
+                 use_ragan=False, up_type='transpose', use_dropout=False, enc_norm='instance',
+                 dec_norm='layer', dis_norm=None):
         # spectral-norm buffers (`*_u`, `*_v`, --dis_sn) are state, not parameters
         self.P = {n: {k: v.detach().clone().requires_grad_(not k.endswith(('_u', '_v')))
                       for k, v in params[n].items()} for n in params}
         self.up_type, self.use_dropout = up_type, use_dropout
+        self.enc_norm, self.dec_norm, self.dis_norm = enc_norm, dec_norm, dis_norm
         self.opt = {n: Adam(self.P[n], lr / 2.5 if n == 'content_discriminator' else lr, betas, wd)
                     for n in self.P}
         self.model, self.concat, self.ms_dis = model, concat, ms_dis
@@ -112,7 +114,7 @@ class AdaINStep:
     def Ec(self, x, draw):
         C = self.P['content_encoder']['model.3.model.0.block.1.weight'].shape[0]
         n = draw((x.size(0), C, x.size(2) // 4, x.size(3) // 4)) if draw else None
-        return nets.content_encoder(self.P['content_encoder'], x, n)
+        return nets.content_encoder(self.P['content_encoder'], x, n, norm=self.enc_norm)
 
     def Es(self, x, c, draw):
         """-> (z, mu, logvar); mu = logvar = None for the plain StyleEncoder"""
@@ -123,7 +125,7 @@ class AdaINStep:
 
     def G(self, zc, zs, c, draw=None):
         """`draw` feeds the decoder's Dropout(0.5) masks (--use_dropout; training mode only)"""
-        kw = dict(up_type=self.up_type, drop=draw if self.use_dropout else None)
+        kw = dict(up_type=self.up_type, drop=draw if self.use_dropout else None, norm=self.dec_norm)
         if self.model == 'adain':
             return nets.adain_decoder(self.P['decoder'], zc, zs, c, **kw)
         if self.concat:
@@ -134,7 +136,7 @@ class AdaINStep:
         """-> list of (real/fake map, class logits), one entry per scale"""
         if self.ms_dis:
             return nets.ms_discriminator(self.P[which], x)
-        return [nets.discriminator(self.P[which], x)]
+        return [nets.discriminator(self.P[which], x, norm=self.dis_norm)]
 
     # -- phases (adain_model.py:146-180, 225-239, 241-394) ----------------------------------
     def update_discriminator(self, img, c_org, draw):
