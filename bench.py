@@ -27,6 +27,7 @@ METRIC = "train_images_per_sec"
 UNIT = "images/s"
 SIZE, ND, LATENT = 256, 4, 8
 B_PER_GPU = 8                      # BASELINE.json configs[2]: batch 8 -> 16 images per iteration
+JSON_OUT = sys.stdout               # re-pointed in __main__ so that stdout carries only the JSON line
 GFLOP_PER_B = 2414.0               # algorithmic GFLOP per unit batch at 256^2
 
 
@@ -158,7 +159,7 @@ def run_reference(a):
             "cpu_baseline": {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{steps} iteration(s) at batch 1 (2 images), 256x256, fp32 torch CPU"},
             "e2e": {"value": ips, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 def conv_roofline(model, batch, pk):
@@ -312,7 +313,7 @@ def run_ours(a):
             "clocks": clk, "gpu_launches": launches,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "roofline": roof, "cpu_baseline": cpu, "sampling": sampling}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 if __name__ == "__main__":
@@ -322,6 +323,9 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     a = ap.parse_args()
+    # stdout carries exactly ONE line (the JSON record); everything else the libraries print (the model
+    # mirrors the reference's "initialize network with ..." messages) goes to stderr
+    JSON_OUT, sys.stdout = sys.stdout, sys.stderr
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
     if a.impl == "reference":
         run_reference(a)
