@@ -16,6 +16,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
+from masterthesis_b200 import _lib  # noqa: E402
+if os.environ.get("MT_LIB"):            # a kernel variant built to another file (tuning experiments)
+    from pathlib import Path
+    _lib.LIB_PATH = Path(os.environ["MT_LIB"]).resolve()
 from masterthesis_b200 import ops  # noqa: E402
 
 REPS = int(os.environ.get("MT_REPS", "5"))

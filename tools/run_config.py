@@ -1,5 +1,5 @@
 """Other configurations of SURVEY 8d on one GPU: MT_B pairs per iteration, MT_SIZE crop, MT_MODEL
-(AdaINModel | BaseModel), MT_FLAGS (comma list: concat,reparam,use_dis_content,ms_dis).
+(AdaINModel | BaseModel), MT_FLAGS (comma list: concat,reparam,use_dis_content,ms_dis,dis_sn,use_dropout,up_type=nearest,...).
 Prints ms / iteration and images/s (5 timed iterations after 4 warm-up ones) and peak memory."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
@@ -11,8 +11,12 @@ flags = [f for f in os.environ.get("MT_FLAGS", "").split(",") if f]
 bench.SIZE = size
 args = bench.make_args(B)
 args.crop_size = size
-for f in flags:
-    setattr(args, f, True)
+for f in flags:          # `flag` sets a boolean, `key=value` a string option (up_type=nearest, dis_norm=instance, ...)
+    if '=' in f:
+        k, v = f.split('=', 1)
+        setattr(args, k, v)
+    else:
+        setattr(args, f, True)
 torch.manual_seed(1234)
 m = getattr(models, os.environ.get("MT_MODEL", "AdaINModel"))(args); m.initialize()
 b = {k: v.cuda() for k, v in bench.synth_batch(B, 100, False).items()}
