@@ -132,12 +132,16 @@ class AdaINModel(Model):
             for p in ps:
                 p.requires_grad_(True)
 
-    def _step(self, *nets):
-        """all-reduce (data parallel) + Adam for the given networks."""
+    def _step(self, *nets, prepack=True):
+        """all-reduce (data parallel) + Adam for the given networks (+ their bf16 weight packs, ahead of
+        the next use, on the pack stream)."""
         if self.dp is not None:
             self.dp.allreduce([self.optimizer[n] for n in nets])
+        blocks.join_prepack()              # no pack may still be reading the weights this step overwrites
         for n in nets:
             self.optimizer[n].step()
+        if prepack:                        # the stepped weights have another consumer in this iteration
+            blocks.prepack(*[self.model[n] for n in nets])
 
     # ------------------------------------------------------------------ sampling (:96-109)
     def _mem_gib(self):
@@ -277,6 +281,7 @@ class AdaINModel(Model):
         bucket = opt.grad_bucket
         total_norm = torch.linalg.vector_norm(bucket) * opt.grad_scale
         bucket.mul_(torch.clamp(5.0 / (total_norm + 1e-6), max=1.0))
+        blocks.join_prepack()
         opt.step()
 
     # ------------------------------------------------------------------ phases G1 / G2 (:225-394)
@@ -288,7 +293,7 @@ class AdaINModel(Model):
         for n in ('content_encoder', 'decoder'):
             self.optimizer[n].zero_grad()
         self.backward_decoder_random(img, c_org)
-        self._step('content_encoder', 'decoder')
+        self._step('content_encoder', 'decoder', prepack=False)      # next use: the next iteration
 
     def _g_adv(self, netD, fake, c_org, real=None, netD_real=None):
         """generator-side adversarial + classification loss.  `real` / `netD_real`: the relativistic
@@ -397,11 +402,17 @@ class AdaINModel(Model):
             self._run_iteration(self._iteration, 'main')
 
     def _iteration(self):
+        # weights stepped at the end of the previous iteration (all of them when an iteration is being
+        # captured): packed layer by layer on the pack stream, under the first convolutions
+        blocks.prepack(*self.model.values())
         self.update_discriminator(self.img, self.c_org)
         self.update_generator(self.img, self.c_org)
+        blocks.join_prepack()
 
     def _content_iteration(self):
+        blocks.prepack(self.model.content_encoder, self.model.content_discriminator)
         self.update_content_discriminator(self.img, self.c_org)
+        blocks.join_prepack()
 
     def compute_visuals(self):
         B = self.args.batch_size

@@ -6,6 +6,7 @@ Every block has two entry points:
   forward(x)    reference-compatible: NCHW fp32 in/out (layout conversion at the edge).
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -30,6 +31,56 @@ def invalidate_packs():
     _PACK_EPOCH[0] += 1
 
 
+# Weight packs ahead of their first use.  A pack is a ~8 us, 64-block kernel: at its point of use it sits
+# alone on the GPU in front of the convolution that needs it (78 of them per iteration).  Right after
+# an optimizer step (and at the start of an iteration) the networks' weights are re-packed on ONE
+# separate stream instead, layer by layer in module order, each pack followed by an event that the
+# consuming convolution waits for: the packs of the later layers run under the earlier layers' work.
+PREPACK = os.environ.get('MT_PREPACK', '1') == '1'
+_pack_streams = {}
+
+
+def _pack_stream(device):
+    s = _pack_streams.get(device)
+    if s is None:
+        s = _pack_streams[device] = torch.cuda.Stream(device=device)
+    return s
+
+
+def prepack(*nets):
+    """Re-pack, on the pack stream, every conv weight of `nets` whose cached pack is stale (same
+    geometry as its last use).  Call on the stream that just wrote the weights."""
+    if not PREPACK or ops.POISON or ops.PROFILE is not None:
+        return
+    todo = []
+    for net in nets:
+        for m in net.modules():
+            if isinstance(m, _ConvParams) and not m.spectral and m._pack is not None:
+                w = m.weight
+                (_, _, zpad, stem, _), _ = m._pack
+                key = (w._version, w.data_ptr(), zpad, stem, _PACK_EPOCH[0])
+                if m._pack[0] != key:
+                    todo.append((m, key, zpad, stem))
+    if not todo:
+        return
+    cur = torch.cuda.current_stream()
+    side = _pack_stream(todo[0][0].weight.device)
+    side.wait_stream(cur)
+    with torch.cuda.stream(side):
+        for m, key, zpad, stem in todo:
+            m._pack = (key, ops.pack_weight(m.weight, m.geom(zpad, stem)))
+            ev = torch.cuda.Event()
+            ev.record(side)
+            m._pack_event = ev
+
+
+def join_prepack():
+    """current stream waits for every pack issued so far (before the packed weights are overwritten by
+    the next optimizer step, and at the end of an iteration so that a captured graph has no open branch)"""
+    for dev, s in _pack_streams.items():
+        torch.cuda.current_stream(dev).wait_stream(s)
+
+
 class _ConvParams(nn.Module):
     transposed = False
 
@@ -42,6 +93,7 @@ class _ConvParams(nn.Module):
         self.bias = nn.Parameter(torch.empty(out_channels)) if bias else None
         self.reset_parameters()
         self._pack = None
+        self._pack_event = None
 
     def reset_parameters(self):
         # torch's nn.Conv2d / nn.ConvTranspose2d default init
@@ -61,6 +113,11 @@ class _ConvParams(nn.Module):
         key = (w._version, w.data_ptr(), zpad, stem, _PACK_EPOCH[0])
         if self._pack is None or self._pack[0] != key:
             self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem)))
+            self._pack_event = None
+        elif self._pack_event is not None:
+            # packed ahead of time on the pack stream (prepack below): every consuming stream orders
+            # itself behind that launch; waiting on the same event again is free
+            torch.cuda.current_stream().wait_event(self._pack_event)
         return self._pack[1]
 
     # spectral normalisation ------------------------------------------------
