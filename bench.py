@@ -325,7 +325,11 @@ if __name__ == "__main__":
     a = ap.parse_args()
     # stdout carries exactly ONE line (the JSON record); everything else the libraries print (the model
     # mirrors the reference's "initialize network with ..." messages) goes to stderr
-    JSON_OUT, sys.stdout = sys.stdout, sys.stderr
+    # (fd 1 itself is re-pointed: NCCL prints its version banner from C)
+    sys.stdout.flush()
+    JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = sys.stderr
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
     if a.impl == "reference":
         run_reference(a)
