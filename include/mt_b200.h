@@ -54,6 +54,15 @@ long long mt_packed_weight_elems(int Cout, int Cin, int kh, int kw, int window, 
 int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, int kw, int transposed,
                         int window, void* w_fwd, void* w_bwd, void* stream);
 
+/* ConvTranspose2d(k=3, s=2, p=1, op=1) — blocks.py:69-73 — runs its FORWARD in a merged-parity mode
+ * when mt_convT_merged_mode(kh, kw, zpad) is 1: two launches over the input pixel grid, GEMM columns
+ * (output column parity, Cout).  Its w_fwd operand is then [6 taps][2*Cout_s][Cin_s] bf16, packed by
+ * mt_pack_convT3x3s2_weight (mt_packed_convT3x3s2_elems elements); w_bwd and the weight-gradient
+ * layout are unchanged (mt_pack_conv_weight with w_fwd = NULL). */
+int mt_convT_merged_mode(int kh, int kw, int zpad);
+long long mt_packed_convT3x3s2_elems(int Cout, int Cin);
+int mt_pack_convT3x3s2_weight(const float* w, int Cout, int Cin, void* w_fwd, void* stream);
+
 /* ---- convolutions (implicit GEMM, tcgen05/TMEM, TMA) -------------------------------- */
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
 int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,

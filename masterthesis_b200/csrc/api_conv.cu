@@ -51,7 +51,7 @@ struct ConvLike {
   int taps_total, Bn, Bk, Bk_s;
   int Wt, Ht, Nt;           // pixel space
   int kh, kw, off_h, off_w, step_h, step_w, w_base, w_step_r, w_step_s;
-  int n_store, n_bias;
+  int n_store, n_bias, bias_wrap;
   long long out_n_stride, out_h_stride, out_w_stride, out_off;
   int act; float slope; const float* bias; void* out;
   float* stats;             // optional fused plane statistics [Nt][stat_parts][n_store][2]
@@ -75,7 +75,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   p.off_h = c.off_h; p.off_w = c.off_w; p.step_h = c.step_h; p.step_w = c.step_w;
   p.w_base = c.w_base; p.w_step_r = c.w_step_r; p.w_step_s = c.w_step_s;
   p.k_chunks = c.window ? 1 : cdiv(c.Ac, 64);
-  p.n_store = c.n_store; p.n_bias = c.bias ? c.n_bias : 0;
+  p.n_store = c.n_store; p.n_bias = c.bias ? c.n_bias : 0; p.bias_wrap = c.bias_wrap;
   // CTA pairs (one M = 256 MMA per two pixel tiles, half of the weight tile staged per CTA) whenever
   // the Cout tile is wide enough for the operand fetch to be the limiter and there is work for them.
   const int pix_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -161,6 +161,14 @@ extern "C" int mt_stored_channels(int c) { return round_up(c, 8); }
 // callers that append zeroed slack, because a 64-element window over-reads the last pixels.
 extern "C" int mt_conv_window_mode(int Cin_s, int kw) {
   return (Cin_s <= 16 && Cin_s * kw <= 64) ? 1 : 0;
+}
+
+// ConvTranspose2d(k=3, s=2, p=1[, op=1]) forward runs in the merged-parity mode (see
+// mt_conv_transpose2d_fwd_stats): its forward operand is packed by mt_pack_convT3x3s2_weight.
+extern "C" int mt_convT_merged_mode(int kh, int kw, int zpad) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("MT_CONVT_MERGED"); off = (e && atoi(e) == 0) ? 1 : 0; }
+  return (!off && kh == 3 && kw == 3 && zpad == 1) ? 1 : 0;
 }
 
 extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd,
@@ -347,6 +355,43 @@ extern "C" int mt_conv_transpose2d_fwd_stats(const MtConv2d* d, const void* x, c
   c.out_n_stride = (long long)d->out_H * row;
   const long long base = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
   if (stats && (parts <= 0 || parts % 4)) return -1012;
+  if (mt_convT_merged_mode(d->kh, d->kw, d->zpad) && d->Hout == 2 * d->Hin && d->Wout == 2 * d->Win) {
+    // ConvTranspose2d(k3, s2, p1, op1) as TWO stride-1 launches over the INPUT pixel grid, one per
+    // output row parity ph, each producing both column parities at once: GEMM columns = (pw, co),
+    // 2*Cout_s wide, which are contiguous in memory (pixels 2w and 2w+1 of output row 2h+ph).
+    //   out[2h+ph, 2w+pw, co] = sum_{dh,dw in {0,1}} x[h+dh, w+dw, :] . Wm[ph][dh][dw][(pw,co), :]
+    // with zero blocks where a (parity, offset) pair has no filter tap (mt_pack_convT3x3s2_weight) and
+    // x read as zero beyond the bottom / right edge (TMA out-of-bounds fill).  Against the four
+    // single-parity launches: each A tile is fetched 6 times instead of 9 and the Cout tile is twice
+    // as wide (these layers are bound by the L2 -> SM operand stream, not by the tensor pipe), for
+    // 12/9 of the MMA work.
+    ConvLike qs[2];
+    for (int ph = 0; ph < 2; ++ph) {
+      ConvLike q = c;
+      q.taps_total = 6; q.Bn = 2 * d->Cout_s;
+      q.Wt = d->Win; q.Ht = d->Hin;
+      q.kh = ph ? 2 : 1; q.kw = 2; q.off_h = 0; q.off_w = 0; q.step_h = 1; q.step_w = 1;
+      q.w_base = ph ? 2 : 0; q.w_step_r = 2; q.w_step_s = 1;
+      q.n_store = 2 * d->Cout_s; q.bias_wrap = d->Cout_s;
+      q.out_w_stride = 2 * pix; q.out_h_stride = 2 * row; q.out_off = base + ph * row;
+      // statistics slots are 2*Cout_s wide here: slot s covers the caller's parts 2s and 2s+1
+      q.stats = stats; q.stat_parts = parts / 2; q.stat_part0 = ph * (parts / 4);
+      qs[ph] = q;
+    }
+    if (!phase_fork_ready()) {
+      rc = run_conv_like(qs[0], (cudaStream_t)stream);
+      return rc ? rc : run_conv_like(qs[1], (cudaStream_t)stream);
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaEventRecord(g_fork.fork, st) != cudaSuccess) return -1013;
+    rc = 0;
+    if (cudaStreamWaitEvent(g_fork.aux[0], g_fork.fork, 0) != cudaSuccess) rc = -1013;
+    if (!rc) rc = run_conv_like(qs[0], g_fork.aux[0]);
+    if (cudaEventRecord(g_fork.join[0], g_fork.aux[0]) != cudaSuccess && !rc) rc = -1013;
+    const int rc1 = run_conv_like(qs[1], st);
+    if (cudaStreamWaitEvent(st, g_fork.join[0], 0) != cudaSuccess && !rc) rc = -1013;
+    return rc ? rc : rc1;
+  }
   c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;   // run_phases: phase i fills quarter i
   return run_phases(c, d->kh, d->kw, d->zpad, d->Hout, d->Wout, row, pix, base, (cudaStream_t)stream);
 }

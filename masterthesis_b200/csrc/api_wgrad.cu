@@ -181,9 +181,45 @@ __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int 
   }
 }
 
+// Forward operand of the merged-parity ConvTranspose2d(k3, s2, p1): wf[tap 0..5][(pw, co)][ci]
+// (rows: 2*Cout_s, columns: Cin_s).  Taps 0,1: output row parity 0 with input offsets (0, dw);
+// taps 2 + 2*dh + dw: row parity 1 with offsets (dh, dw).  Filter index per (parity, offset):
+// (0,0) -> 1, (1,0) -> 2, (1,1) -> 0, (0,1) -> none (zero block).  Source W[ci][co][r][s].
+__global__ void __launch_bounds__(256)
+pack_convT3x3s2_kernel(const float* __restrict__ w, int Cout_, int Cin_, __nv_bfloat16* __restrict__ wf) {
+  const unsigned Cout = Cout_, Cin = Cin_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned rows = 2 * Cout_s, per_tap = rows * Cin_s, n = 6 * per_tap;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned tap = i / per_tap, e = i - tap * per_tap;
+    const unsigned row = e / Cin_s, ci = e - row * Cin_s;
+    const unsigned pw = row / Cout_s, co = row - pw * Cout_s;
+    const unsigned ph = tap >= 2, t = ph ? tap - 2 : tap;
+    const unsigned dh = ph ? t >> 1 : 0, dw = t & 1;
+    const int r = ph == 0 ? 1 : (dh == 0 ? 2 : 0);
+    const int sx = pw == 0 ? (dw == 0 ? 1 : -1) : (dw == 0 ? 2 : 0);
+    float v = 0.f;
+    if (sx >= 0 && co < Cout && ci < Cin) v = __ldg(w + ((size_t)(ci * Cout + co) * 3 + r) * 3 + sx);
+    wf[i] = __float2bfloat16(v);
+  }
+}
+
 }  // namespace mt
 
 using namespace mt;
+
+extern "C" long long mt_packed_convT3x3s2_elems(int Cout, int Cin) {
+  return 6ll * 2 * round_up(Cout, 8) * round_up(Cin, 8);
+}
+extern "C" int mt_pack_convT3x3s2_weight(const float* w, int Cout, int Cin, void* w_fwd, void* stream) {
+  const long long n = mt_packed_convT3x3s2_elems(Cout, Cin);
+  if (n >= (1ll << 31)) return -1005;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_convT3x3s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, (__nv_bfloat16*)w_fwd);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
 
 extern "C" long long mt_packed_weight_elems(int Cout, int Cin, int kh, int kw, int window,
                                             int bwd) {

@@ -27,6 +27,8 @@ struct IgemmParams {
   int BN;                                  // Cout tile (16..256, multiple of 16)
   int n_store;                             // channels to store per pixel (multiple of 8)
   int n_bias;                              // number of valid bias entries (0: no bias)
+  int bias_wrap;                           // > 0: column c >= bias_wrap reads bias[c - bias_wrap] (two column
+                                           // groups sharing one bias: merged ConvTranspose2d phases)
   int stages;
   int tmem_cols;
   long long out_n_stride, out_h_stride, out_w_stride, out_off;  // elements

@@ -64,15 +64,16 @@ __device__ __forceinline__ void epilogue_slab(const IgemmParams& p, uint32_t tme
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
     if (BIAS) {
-      if (c + 8 <= p.n_bias) {
-        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
-        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
+      const int cb = (p.bias_wrap > 0 && c >= p.bias_wrap) ? c - p.bias_wrap : c;   // wrap is a multiple of 8
+      if (cb + 8 <= p.n_bias) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + cb));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + cb + 4));
         f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
         f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
       } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (c + j < p.n_bias) f[j] += __ldg(p.bias + c + j);
+          if (cb + j < p.n_bias) f[j] += __ldg(p.bias + cb + j);
       }
     }
 #pragma unroll

@@ -160,6 +160,11 @@ class ConvGeom:
         return cs(self.Cout)
 
     @property
+    def merged_convT(self) -> bool:
+        """ConvTranspose2d(k3, s2, p1) forward in the merged-parity mode (include/mt_b200.h)"""
+        return bool(self.transposed and _lib.lib().mt_convT_merged_mode(self.kh, self.kw, self.zpad))
+
+    @property
     def window(self) -> bool:
         return (self.stem and not self.transposed and self.zpad == 0 and self.Cin_s <= 16
                 and self.Cin_s * self.kw <= 64)
@@ -184,10 +189,18 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
     _require_cuda(w)
     L = _lib.lib()
     w = w.detach().contiguous().float()
-    nf = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0)
     nb = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 1)
-    wf = _T.empty(nf, dtype=torch.bfloat16, device=w.device)
     wb = _T.empty(nb, dtype=torch.bfloat16, device=w.device)
+    if g.merged_convT:
+        # ConvTranspose2d(k3, s2, p1): forward operand of the merged-parity mode, [6][2*Cout_s][Cin_s]
+        wf = _T.empty(L.mt_packed_convT3x3s2_elems(g.Cout, g.Cin), dtype=torch.bfloat16, device=w.device)
+        check(L.mt_pack_convT3x3s2_weight(_p(w), g.Cout, g.Cin, _p(wf), _stream()), "mt_pack_convT3x3s2_weight")
+        check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, 1, 0, None, _p(wb), _stream()),
+              "mt_pack_conv_weight")
+        _count(2)
+        return wf, wb
+    nf = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0)
+    wf = _T.empty(nf, dtype=torch.bfloat16, device=w.device)
     check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed), int(g.window),
                                 _p(wf), _p(wb), _stream()), "mt_pack_conv_weight")
     _count()
@@ -207,7 +220,7 @@ def conv_fwd(x, wf, bias, g: ConvGeom, act=None, out_pad=0, out=None):
     fn = _lib.lib().mt_conv_transpose2d_fwd if g.transposed else _lib.lib().mt_conv2d_fwd
     with _timed("fwd", g, N, Hin, Win):
         check(fn(ctypes.byref(d), _p(x), _p(wf), _p(bias), _p(out), _stream()), "conv_fwd")
-    _count(4 if g.transposed else 1)
+    _count((2 if g.merged_convT else 4) if g.transposed else 1)
     return out
 
 
@@ -228,7 +241,7 @@ def conv_fwd_stats(x, wf, bias, g: ConvGeom):
     with _timed("fwd", g, N, Hin, Win):
         check(fn(ctypes.byref(d), _p(x), _p(wf), _p(bias), _p(out), _p(stats), parts, _stream()),
               "conv_fwd_stats")
-    _count(4 if g.transposed else 1)
+    _count((2 if g.merged_convT else 4) if g.transposed else 1)
     if stats is None:
         stats = plane_stats(out)
     return out, stats

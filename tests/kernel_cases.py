@@ -256,6 +256,9 @@ CASES = {
     "conv7x7_s2_256": lambda: conv_case(1, 256, 256, 32, 32, 7, 2, 1),
     "convT_256_128": lambda: convT_case(2, 256, 128, 16, 16),
     "convT_128_64": lambda: convT_case(1, 128, 64, 24, 40, bias=False),
+    # odd channel counts of DecoderConcat (stored 56 -> 32): merged-parity columns straddle 64-wide slabs
+    "convT_odd": lambda: convT_case(2, 52, 26, 12, 20),
+    "convT_odd_wide": lambda: convT_case(1, 276, 138, 16, 16),
     "in_relu": lambda: norm_case("instance", 2, 256, 32, 32, "relu"),
     "in_res_noise": lambda: norm_case("instance", 2, 128, 16, 24, None, residual=True, noise=True),
     "adain_relu": lambda: norm_case("adain", 3, 256, 16, 16, "relu"),
