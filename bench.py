@@ -152,7 +152,7 @@ def run_reference(a):
     threads = os.cpu_count()
     steps, warmup = max(1, min(a.steps, 3)), max(0, min(a.warmup, 1))
     ips, sec = cpu_iteration_port(steps, warmup, threads)
-    line = {"impl": "reference", "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": 0,
+    line = {"impl": "reference", "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": a.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "AdaINModel.optimize_parameters, 256x256, 4 domains (CPU sample: batch 1 = 2 images/iteration)"},

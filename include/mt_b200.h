@@ -63,6 +63,15 @@ int mt_convT_merged_mode(int kh, int kw, int zpad);
 long long mt_packed_convT3x3s2_elems(int Cout, int Cin);
 int mt_pack_convT3x3s2_weight(const float* w, int Cout, int Cin, void* w_fwd, void* stream);
 
+/* The data gradient of a stride-2 convolution without zero padding (reflection-padded input:
+ * blocks.py:29-36 with stride 2, k = 3 or 4) runs in the same merged-parity mode when
+ * mt_conv_s2_dgrad_merged_mode(kh, kw, stride, zpad, Cin) is 1 (k = 4, or k = 3 with Cin <= 128): mt_conv2d_dgrad then expects w_bwd =
+ * [2*((k+1)/2 + k/2) taps][2*Cin_s][Cout_s] bf16 from mt_pack_conv_s2_dgrad_weight, and even Hin / Win
+ * (error -1014 otherwise).  w_fwd is unchanged (mt_pack_conv_weight with w_bwd = NULL). */
+int mt_conv_s2_dgrad_merged_mode(int kh, int kw, int stride, int zpad, int Cin);
+long long mt_packed_conv_s2_dgrad_elems(int Cout, int Cin, int k);
+int mt_pack_conv_s2_dgrad_weight(const float* w, int Cout, int Cin, int k, void* w_bwd, void* stream);
+
 /* ---- convolutions (implicit GEMM, tcgen05/TMEM, TMA) -------------------------------- */
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
 int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,

@@ -308,6 +308,33 @@ static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, lo
   return rc ? rc : rc0;
 }
 
+// the two row-parity launches of a merged-parity operation, side by side (qs[0] on an auxiliary stream)
+static int run_pair(const ConvLike* qs, cudaStream_t st) {
+  if (!phase_fork_ready()) {
+    const int rc = run_conv_like(qs[0], st);
+    return rc ? rc : run_conv_like(qs[1], st);
+  }
+  if (cudaEventRecord(g_fork.fork, st) != cudaSuccess) return -1013;
+  int rc = 0;
+  if (cudaStreamWaitEvent(g_fork.aux[0], g_fork.fork, 0) != cudaSuccess) rc = -1013;
+  if (!rc) rc = run_conv_like(qs[0], g_fork.aux[0]);
+  // the join is recorded even after a failed launch so that a capture is never left forked
+  if (cudaEventRecord(g_fork.join[0], g_fork.aux[0]) != cudaSuccess && !rc) rc = -1013;
+  const int rc1 = run_conv_like(qs[1], st);
+  if (cudaStreamWaitEvent(st, g_fork.join[0], 0) != cudaSuccess && !rc) rc = -1013;
+  return rc ? rc : rc1;
+}
+
+// Data gradient of a stride-2, un-padded (reflection-padded input) 3x3 / 4x4 convolution in the
+// merged-parity mode: see mt_conv2d_dgrad.  Its w_bwd operand is packed by mt_pack_conv_s2_dgrad_weight.
+extern "C" int mt_conv_s2_dgrad_merged_mode(int kh, int kw, int stride, int zpad, int Cin) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("MT_DGRAD_MERGED"); off = (e && atoi(e) == 0) ? 1 : 0; }
+  // k = 3 pays 12/9 of the MMA work for the wider tile: only where the layer is operand-bound (<= 128
+  // input channels, i.e. a Cout tile below 256 in the single-parity form); k = 4 has no zero blocks
+  return (!off && stride == 2 && zpad == 0 && kh == kw && (kh == 4 || (kh == 3 && Cin <= 128))) ? 1 : 0;
+}
+
 extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
                                void* stream) {
   int rc = check_desc(d);
@@ -328,6 +355,26 @@ extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_
     c.w_base = 0; c.w_step_r = d->kw; c.w_step_s = 1;
     c.out_h_stride = row; c.out_w_stride = pix; c.out_off = 0;
     return run_conv_like(c, (cudaStream_t)stream);
+  }
+  if (mt_conv_s2_dgrad_merged_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin)) {
+    // dx[2a+ph, 2b+pw, ci] = sum_{dh,dw} dy[a-dh, b-dw, :] . W[:, ci, ph+2dh, pw+2dw]   (taps beyond the
+    // filter are zero blocks, dy rows / columns outside the map read as zero).  As for the transposed
+    // convolution forward, the two column parities are GEMM columns (pw, ci): 2*Cin_s contiguous
+    // channels of the pixel pair (2b, 2b+1); one launch per row parity.  Needs even extents.
+    if ((d->Hin & 1) || (d->Win & 1)) return -1014;
+    const int k = d->kh, nr0 = (k + 1) / 2, nr1 = k / 2;
+    ConvLike qs[2];
+    for (int ph = 0; ph < 2; ++ph) {
+      ConvLike q = c;
+      q.taps_total = 2 * (nr0 + nr1); q.Bn = 2 * d->Cin_s;
+      q.Wt = d->Win / 2; q.Ht = d->Hin / 2;
+      q.kh = ph ? nr1 : nr0; q.kw = 2; q.off_h = 0; q.off_w = 0; q.step_h = -1; q.step_w = -1;
+      q.w_base = ph ? 2 * nr0 : 0; q.w_step_r = 2; q.w_step_s = 1;
+      q.n_store = 2 * d->Cin_s;
+      q.out_w_stride = 2 * pix; q.out_h_stride = 2 * row; q.out_off = ph * row;
+      qs[ph] = q;
+    }
+    return run_pair(qs, (cudaStream_t)stream);
   }
   return run_phases(c, d->kh, d->kw, d->zpad, d->Hin, d->Win, row, pix, 0, (cudaStream_t)stream);
 }
@@ -378,19 +425,7 @@ extern "C" int mt_conv_transpose2d_fwd_stats(const MtConv2d* d, const void* x, c
       q.stats = stats; q.stat_parts = parts / 2; q.stat_part0 = ph * (parts / 4);
       qs[ph] = q;
     }
-    if (!phase_fork_ready()) {
-      rc = run_conv_like(qs[0], (cudaStream_t)stream);
-      return rc ? rc : run_conv_like(qs[1], (cudaStream_t)stream);
-    }
-    cudaStream_t st = (cudaStream_t)stream;
-    if (cudaEventRecord(g_fork.fork, st) != cudaSuccess) return -1013;
-    rc = 0;
-    if (cudaStreamWaitEvent(g_fork.aux[0], g_fork.fork, 0) != cudaSuccess) rc = -1013;
-    if (!rc) rc = run_conv_like(qs[0], g_fork.aux[0]);
-    if (cudaEventRecord(g_fork.join[0], g_fork.aux[0]) != cudaSuccess && !rc) rc = -1013;
-    const int rc1 = run_conv_like(qs[1], st);
-    if (cudaStreamWaitEvent(st, g_fork.join[0], 0) != cudaSuccess && !rc) rc = -1013;
-    return rc ? rc : rc1;
+    return run_pair(qs, (cudaStream_t)stream);
   }
   c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;   // run_phases: phase i fills quarter i
   return run_phases(c, d->kh, d->kw, d->zpad, d->Hout, d->Wout, row, pix, base, (cudaStream_t)stream);

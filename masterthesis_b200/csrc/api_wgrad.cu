@@ -204,9 +204,46 @@ pack_convT3x3s2_kernel(const float* __restrict__ w, int Cout_, int Cin_, __nv_bf
   }
 }
 
+// Data-gradient operand of the merged-parity stride-2 convolution (k = 3 or 4, no zero padding):
+// wb[tap][(pw, ci)][co]  (rows: 2*Cin_s, columns: Cout_s).  Taps of row parity 0 first
+// (dh < (k+1)/2, dw < 2: index 2*dh + dw), then those of row parity 1 (dh < k/2).  Filter element
+// (r, s) = (ph + 2*dh, pw + 2*dw), a zero block when s >= k.  Source W[co][ci][r][s].
+__global__ void __launch_bounds__(256)
+pack_conv_s2_dgrad_kernel(const float* __restrict__ w, int Cout_, int Cin_, int k_,
+                          __nv_bfloat16* __restrict__ wb) {
+  const unsigned Cout = Cout_, Cin = Cin_, k = k_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned nr0 = (k + 1) / 2, nr1 = k / 2;
+  const unsigned rows = 2 * Cin_s, per_tap = rows * Cout_s, n = 2 * (nr0 + nr1) * per_tap;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned tap = i / per_tap, e = i - tap * per_tap;
+    const unsigned row = e / Cout_s, co = e - row * Cout_s;
+    const unsigned pw = row / Cin_s, ci = row - pw * Cin_s;
+    const unsigned ph = tap >= 2 * nr0, t = ph ? tap - 2 * nr0 : tap;
+    const unsigned r = ph + 2 * (t >> 1), sx = pw + 2 * (t & 1);
+    float v = 0.f;
+    if (sx < k && co < Cout && ci < Cin) v = __ldg(w + ((size_t)(co * Cin + ci) * k + r) * k + sx);
+    wb[i] = __float2bfloat16(v);
+  }
+}
+
 }  // namespace mt
 
 using namespace mt;
+
+extern "C" long long mt_packed_conv_s2_dgrad_elems(int Cout, int Cin, int k) {
+  return 2ll * ((k + 1) / 2 + k / 2) * 2 * round_up(Cin, 8) * round_up(Cout, 8);
+}
+extern "C" int mt_pack_conv_s2_dgrad_weight(const float* w, int Cout, int Cin, int k, void* w_bwd,
+                                            void* stream) {
+  const long long n = mt_packed_conv_s2_dgrad_elems(Cout, Cin, k);
+  if (n >= (1ll << 31) || (k != 3 && k != 4)) return -1005;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_conv_s2_dgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, k, (__nv_bfloat16*)w_bwd);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
 
 extern "C" long long mt_packed_convT3x3s2_elems(int Cout, int Cin) {
   return 6ll * 2 * round_up(Cout, 8) * round_up(Cin, 8);

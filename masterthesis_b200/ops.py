@@ -165,6 +165,12 @@ class ConvGeom:
         return bool(self.transposed and _lib.lib().mt_convT_merged_mode(self.kh, self.kw, self.zpad))
 
     @property
+    def merged_s2_dgrad(self) -> bool:
+        """stride-2 conv whose data gradient runs in the merged-parity mode (include/mt_b200.h)"""
+        return bool(not self.transposed and
+                    _lib.lib().mt_conv_s2_dgrad_merged_mode(self.kh, self.kw, self.stride, self.zpad, self.Cin))
+
+    @property
     def window(self) -> bool:
         return (self.stem and not self.transposed and self.zpad == 0 and self.Cin_s <= 16
                 and self.Cin_s * self.kw <= 64)
@@ -189,6 +195,18 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
     _require_cuda(w)
     L = _lib.lib()
     w = w.detach().contiguous().float()
+    if g.merged_s2_dgrad:
+        # stride-2 conv without zero padding: forward operand as usual, data-gradient operand of the
+        # merged-parity mode
+        nf = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0)
+        wf = _T.empty(nf, dtype=torch.bfloat16, device=w.device)
+        wb = _T.empty(L.mt_packed_conv_s2_dgrad_elems(g.Cout, g.Cin, g.kh), dtype=torch.bfloat16, device=w.device)
+        check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, 0, int(g.window), _p(wf), None,
+                                    _stream()), "mt_pack_conv_weight")
+        check(L.mt_pack_conv_s2_dgrad_weight(_p(w), g.Cout, g.Cin, g.kh, _p(wb), _stream()),
+              "mt_pack_conv_s2_dgrad_weight")
+        _count(2)
+        return wf, wb
     nb = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 1)
     wb = _T.empty(nb, dtype=torch.bfloat16, device=w.device)
     if g.merged_convT:
@@ -259,7 +277,7 @@ def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
     fn = _lib.lib().mt_conv_transpose2d_dgrad if g.transposed else _lib.lib().mt_conv2d_dgrad
     with _timed("dgrad", g, N, Hin, Win):
         check(fn(ctypes.byref(d), _p(dy), _p(wb), _p(dx), _stream()), "conv_dgrad")
-    _count(4 if (g.stride == 2 and not g.transposed) else 1)
+    _count((2 if g.merged_s2_dgrad else 4) if (g.stride == 2 and not g.transposed) else 1)
     return dx
 
 

@@ -257,6 +257,9 @@ CASES = {
     "convT_256_128": lambda: convT_case(2, 256, 128, 16, 16),
     "convT_128_64": lambda: convT_case(1, 128, 64, 24, 40, bias=False),
     # odd channel counts of DecoderConcat (stored 56 -> 32): merged-parity columns straddle 64-wide slabs
+    # merged-parity stride-2 data gradients: 4x4 (no zero blocks), 3x3 into few channels, odd channels
+    "conv4x4_s2_refl": lambda: conv_case(2, 64, 128, 32, 32, 4, 2, 1),
+    "conv3x3_s2_odd": lambda: conv_case(2, 44, 52, 20, 12, 3, 2, 1),
     "convT_odd": lambda: convT_case(2, 52, 26, 12, 20),
     "convT_odd_wide": lambda: convT_case(1, 276, 138, 16, 16),
     "in_relu": lambda: norm_case("instance", 2, 256, 32, 32, "relu"),
