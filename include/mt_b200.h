@@ -72,6 +72,16 @@ int mt_conv_s2_dgrad_merged_mode(int kh, int kw, int stride, int zpad, int Cin);
 long long mt_packed_conv_s2_dgrad_elems(int Cout, int Cin, int k);
 int mt_pack_conv_s2_dgrad_weight(const float* w, int Cout, int Cin, int k, void* w_bwd, void* stream);
 
+/* Row-window stems (mt_conv_window_mode) whose 64-element window also covers the next output pixel
+ * ((kw + stride) * Cin_s <= 64: the 7x7 image stems networks.py:30,76 and the stride-2 stems
+ * networks.py:117,361) compute two adjacent output pixels per GEMM row when
+ * mt_conv_window_pair_mode(Cin_s, kw, stride) is 1: mt_conv2d_fwd[_stats] then expects w_fwd =
+ * [kh][2*Cout_s][64] from mt_pack_conv_window_pair_weight and an even Wout (error -1014 otherwise). */
+int mt_conv_window_pair_mode(int Cin_s, int kw, int stride);
+long long mt_packed_conv_window_pair_elems(int Cout, int kh);
+int mt_pack_conv_window_pair_weight(const float* w, int Cout, int Cin, int kh, int kw, int stride,
+                                    void* w_fwd, void* stream);
+
 /* ---- convolutions (implicit GEMM, tcgen05/TMEM, TMA) -------------------------------- */
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
 int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,

@@ -178,6 +178,16 @@ extern "C" int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd
 
 // Number of per-tile partial-sum slots per image that the fused statistics of this conv produce
 // (0: the shape cannot fuse them — several images per tile, or a Cout tile narrower than a slab).
+// Row-window stems whose window also covers the NEXT output pixel ((kw + stride) * Cin_s <= 64) compute
+// two adjacent output pixels per GEMM row: columns (pixel parity, Cout), window stride 2 * stride.  The
+// 64-element windows are the operand stream that bounds these layers (7 x 128 B per output pixel for
+// the 7x7 stem): pairing halves it.  w_fwd is then packed by mt_pack_conv_window_pair_weight.
+extern "C" int mt_conv_window_pair_mode(int Cin_s, int kw, int stride) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("MT_STEM_PAIR"); off = (e && atoi(e) == 0) ? 1 : 0; }
+  return (!off && mt_conv_window_mode(Cin_s, kw) && (kw + stride) * Cin_s <= 64) ? 1 : 0;
+}
+
 extern "C" int mt_conv_stats_parts(const MtConv2d* d, int transposed) {
   if (check_desc(d)) return 0;
   static int off = -1;
@@ -188,6 +198,11 @@ extern "C" int mt_conv_stats_parts(const MtConv2d* d, int transposed) {
     if ((d->Hout & 1) || (d->Wout & 1)) return 0;
     pick_tile(128, d->Wout / 2, d->Hout / 2, d->N, 1, &tw, &th, &tn);
     return tn == 1 ? 4 * cdiv(d->Wout / 2, tw) * cdiv(d->Hout / 2, th) : 0;
+  }
+  if (d->window && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride) && !(d->Wout & 1)) {
+    // paired stem: tiles over Wout / 2 pixel pairs, each slot 2 * Cout_s wide = two of the caller's parts
+    pick_tile(128, d->Wout / 2, d->Hout, d->N, d->stride, &tw, &th, &tn);
+    return tn == 1 ? 2 * cdiv(d->Wout / 2, tw) * cdiv(d->Hout, th) : 0;
   }
   pick_tile(128, d->Wout, d->Hout, d->N, d->stride, &tw, &th, &tn);
   return tn == 1 ? cdiv(d->Wout, tw) * cdiv(d->Hout, th) : 0;
@@ -222,6 +237,14 @@ extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void*
   c.out_off = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
   c.act = d->act; c.slope = d->slope; c.bias = bias; c.out = y;
   c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;
+  if (win && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
+    if (d->Wout & 1) return -1014;
+    if (stats && (parts & 1)) return -1012;
+    c.Bn = 2 * d->Cout_s; c.n_store = 2 * d->Cout_s; c.bias_wrap = d->Cout_s;
+    c.Wt = d->Wout / 2; c.win_cols = d->Wout / 2; c.win_stride = 2 * d->stride;
+    c.out_w_stride = 2 * d->Cout_s;
+    c.stat_parts = parts / 2;
+  }
   return run_conv_like(c, (cudaStream_t)stream);
 }
 

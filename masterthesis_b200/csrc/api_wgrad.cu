@@ -227,9 +227,46 @@ pack_conv_s2_dgrad_kernel(const float* __restrict__ w, int Cout_, int Cin_, int 
   }
 }
 
+// Forward operand of a paired row-window stem: wf[r][(j, co)][e], rows 2*Cout_s, 64 window elements
+// e = (px, ci) with Cin_s channels per pixel; output pixel j of the pair sees filter column
+// s = px - j*stride (zero outside 0..kw-1).  Source W[co][ci][r][s].
+__global__ void __launch_bounds__(256)
+pack_window_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh_, int kw_, int stride_,
+                        __nv_bfloat16* __restrict__ wf) {
+  const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_, stride = stride_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned n = kh * 2 * Cout_s * 64;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned e = i & 63, t = i >> 6;
+    const unsigned r = t / (2 * Cout_s), row = t - r * 2 * Cout_s;
+    const unsigned j = row / Cout_s, co = row - j * Cout_s;
+    const unsigned px = e / Cin_s, ci = e - px * Cin_s;
+    const int sx = (int)px - (int)(j * stride);
+    float v = 0.f;
+    if (sx >= 0 && sx < (int)kw && ci < Cin && co < Cout)
+      v = __ldg(w + ((size_t)(co * Cin + ci) * kh + r) * kw + sx);
+    wf[i] = __float2bfloat16(v);
+  }
+}
+
 }  // namespace mt
 
 using namespace mt;
+
+extern "C" long long mt_packed_conv_window_pair_elems(int Cout, int kh) {
+  return (long long)kh * 2 * round_up(Cout, 8) * 64;
+}
+extern "C" int mt_pack_conv_window_pair_weight(const float* w, int Cout, int Cin, int kh, int kw,
+                                               int stride, void* w_fwd, void* stream) {
+  const long long n = mt_packed_conv_window_pair_elems(Cout, kh);
+  if (n >= (1ll << 31)) return -1005;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_window_pair_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, kh, kw, stride,
+                                                                    (__nv_bfloat16*)w_fwd);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
 
 extern "C" long long mt_packed_conv_s2_dgrad_elems(int Cout, int Cin, int k) {
   return 2ll * ((k + 1) / 2 + k / 2) * 2 * round_up(Cin, 8) * round_up(Cout, 8);

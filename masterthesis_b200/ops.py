@@ -165,6 +165,11 @@ class ConvGeom:
         return bool(self.transposed and _lib.lib().mt_convT_merged_mode(self.kh, self.kw, self.zpad))
 
     @property
+    def window_pair(self) -> bool:
+        """row-window stem computing two adjacent output pixels per GEMM row (include/mt_b200.h)"""
+        return bool(self.window and _lib.lib().mt_conv_window_pair_mode(self.Cin_s, self.kw, self.stride))
+
+    @property
     def merged_s2_dgrad(self) -> bool:
         """stride-2 conv whose data gradient runs in the merged-parity mode (include/mt_b200.h)"""
         return bool(not self.transposed and
@@ -195,6 +200,22 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
     _require_cuda(w)
     L = _lib.lib()
     w = w.detach().contiguous().float()
+    if g.window_pair:
+        # paired row-window stem: its own forward operand; the data-gradient operand by the usual rules
+        wf = _T.empty(L.mt_packed_conv_window_pair_elems(g.Cout, g.kh), dtype=torch.bfloat16, device=w.device)
+        check(L.mt_pack_conv_window_pair_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, g.stride, _p(wf), _stream()),
+              "mt_pack_conv_window_pair_weight")
+        if g.merged_s2_dgrad:
+            wb = _T.empty(L.mt_packed_conv_s2_dgrad_elems(g.Cout, g.Cin, g.kh), dtype=torch.bfloat16, device=w.device)
+            check(L.mt_pack_conv_s2_dgrad_weight(_p(w), g.Cout, g.Cin, g.kh, _p(wb), _stream()),
+                  "mt_pack_conv_s2_dgrad_weight")
+        else:
+            wb = _T.empty(L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, 1, 1), dtype=torch.bfloat16,
+                          device=w.device)
+            check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, 0, 1, None, _p(wb), _stream()),
+                  "mt_pack_conv_weight")
+        _count(2)
+        return wf, wb
     if g.merged_s2_dgrad:
         # stride-2 conv without zero padding: forward operand as usual, data-gradient operand of the
         # merged-parity mode
