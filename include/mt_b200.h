@@ -81,6 +81,10 @@ int mt_conv_window_pair_mode(int Cin_s, int kw, int stride);
 long long mt_packed_conv_window_pair_elems(int Cout, int kh);
 int mt_pack_conv_window_pair_weight(const float* w, int Cout, int Cin, int kh, int kw, int stride,
                                     void* w_fwd, void* stream);
+/* In the same mode mt_conv2d_wgrad writes dw_packed = [kh][2*Cout_s][64] fp32 (zeroed by the caller,
+ * mt_packed_conv_window_pair_elems elements); this unpack folds the two pixel parities into dW (OIHW). */
+int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw, int stride,
+                                     int accumulate, float* dw, void* stream);
 
 /* ---- convolutions (implicit GEMM, tcgen05/TMEM, TMA) -------------------------------- */
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */

@@ -249,9 +249,39 @@ pack_window_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh
   }
 }
 
+// dW[co][ci][r][s] (+)= g[r][co][s*Cin_s + ci] + g[r][Cout_s + co][(s + stride)*Cin_s + ci]
+__global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_,
+                                                int kw_, int stride_, int accumulate,
+                                                float* __restrict__ dw) {
+  const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_, stride = stride_;
+  const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
+  const unsigned n = Cout * Cin * kh * kw;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    unsigned t = i / kw;
+    const unsigned s = i - t * kw;
+    const unsigned t2 = t / kh, r = t - t2 * kh;
+    const unsigned co = t2 / Cin, ci = t2 - co * Cin;
+    const float v = g[((size_t)r * 2 * Cout_s + co) * 64 + s * Cin_s + ci] +
+                    g[((size_t)r * 2 * Cout_s + Cout_s + co) * 64 + (s + stride) * Cin_s + ci];
+    dw[i] = accumulate ? dw[i] + v : v;
+  }
+}
+
 }  // namespace mt
 
 using namespace mt;
+
+extern "C" int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
+                                                int stride, int accumulate, float* dw, void* stream) {
+  const long long n = (long long)Cout * Cin * kh * kw;
+  if (n >= (1ll << 31)) return -1005;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  unpack_window_pair_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, Cout, Cin, kh, kw,
+                                                                            stride, accumulate, dw);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
 
 extern "C" long long mt_packed_conv_window_pair_elems(int Cout, int kh) {
   return (long long)kh * 2 * round_up(Cout, 8) * 64;
@@ -353,6 +383,15 @@ extern "C" int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy,
   if (win) {
     c.kh = d->kh; c.kw = 1; c.off_h = 0; c.off_w = 0; c.step_h = 1; c.step_w = 0;
     c.N_store = 64;
+    if (mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
+      // paired stem (see mt_conv_window_pair_mode): dy read as [N, Hout, Wout/2, 2*Cout_s] — the same
+      // memory — against windows of stride 2*stride: M = (pixel parity, Cout) fills the 128-row MMA
+      // that a 64-channel stem left half empty, and half as many window rows are fetched.
+      // dw_packed is then [kh][2*Cout_s][64]; mt_unpack_conv_window_pair_wgrad folds the parities.
+      if (d->Wout & 1) return -1014;
+      c.Pw = d->Wout / 2; c.Pc = 2 * d->Cout_s; c.Pc_s = 2 * d->Cout_s;
+      c.win_stride = 2 * d->stride; c.win_cols = d->Wout / 2;
+    }
   } else {
     c.kh = d->kh; c.kw = d->kw; c.off_h = -d->zpad; c.off_w = -d->zpad; c.step_h = 1; c.step_w = 1;
     c.N_store = d->Cin_s;

@@ -308,6 +308,8 @@ def _wgrad_launch(x, dy, g: ConvGeom, dw, accumulate, stream):
     d = g.desc(N, Hin, Win)
     if g.transposed:
         n = g.kh * g.kw * g.Cin * g.Cout_s
+    elif g.window_pair:
+        n = L.mt_packed_conv_window_pair_elems(g.Cout, g.kh)
     elif g.window:
         n = g.kh * g.Cout * 64
     else:
@@ -316,8 +318,12 @@ def _wgrad_launch(x, dy, g: ConvGeom, dw, accumulate, stream):
     fn = L.mt_conv_transpose2d_wgrad if g.transposed else L.mt_conv2d_wgrad
     with _timed("wgrad", g, N, Hin, Win):
         check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), stream), "conv_wgrad")
-    check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
-                                 int(g.window), int(accumulate), _p(dw), stream), "unpack_wgrad")
+    if g.window_pair:
+        check(L.mt_unpack_conv_window_pair_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, g.stride,
+                                                 int(accumulate), _p(dw), stream), "unpack_wgrad")
+    else:
+        check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
+                                     int(g.window), int(accumulate), _p(dw), stream), "unpack_wgrad")
     _count(2)
     return packed
 
