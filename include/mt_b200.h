@@ -72,6 +72,14 @@ int mt_conv_s2_dgrad_merged_mode(int kh, int kw, int stride, int zpad, int Cin);
 long long mt_packed_conv_s2_dgrad_elems(int Cout, int Cin, int k);
 int mt_pack_conv_s2_dgrad_weight(const float* w, int Cout, int Cin, int k, void* w_bwd, void* stream);
 
+/* The data gradient of a stride-1 un-padded conv into <= 8 stored channels (the image gradient of the
+ * 7x7 stems, networks.py:30,76) computes a pixel pair per GEMM row when
+ * mt_conv_s1_dgrad_pair_mode(kh, kw, stride, zpad, Cin_s) is 1: w_bwd = [kh*(kw+1)][16][Cout_s] bf16 from
+ * mt_pack_conv_s1_dgrad_pair_weight, even Win (error -1014 otherwise). */
+int mt_conv_s1_dgrad_pair_mode(int kh, int kw, int stride, int zpad, int Cin_s);
+long long mt_packed_conv_s1_dgrad_pair_elems(int Cout, int k);
+int mt_pack_conv_s1_dgrad_pair_weight(const float* w, int Cout, int Cin, int k, void* w_bwd, void* stream);
+
 /* Row-window stems (mt_conv_window_mode) whose 64-element window also covers the next output pixel
  * ((kw + stride) * Cin_s <= 64: the 7x7 image stems networks.py:30,76 and the stride-2 stems
  * networks.py:117,361) compute two adjacent output pixels per GEMM row when

@@ -44,6 +44,7 @@ struct ConvLike {
   const void* a;            // activation operand, [An][Ah][Aw][Ac_s]
   int An, Ah, Aw, Ac, Ac_s; // logical/stored channels of A (K extent = Ac)
   int a_mul;                // TMA traversal stride on h, w (1 or 2)
+  int a_mul_w;              // > 0: traversal stride on w only (paired-pixel data gradient), else a_mul
   bool window;              // row-window stem mode
   int win_stride;           // pixel stride baked into the window map
   int win_cols;             // number of valid output columns in window mode
@@ -61,13 +62,13 @@ struct ConvLike {
 static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   IgemmParams p;
   memset(&p, 0, sizeof(p));
-  const int mul = c.window ? 1 : c.a_mul;
+  const int mul = c.window ? 1 : (c.a_mul_w > 0 ? c.a_mul_w : c.a_mul);
   p.BN = pick_bn(c.Bn);
   static int force_bn = -1;
   if (force_bn < 0) { const char* e = getenv("MT_IGEMM_BN"); force_bn = e ? atoi(e) : 0; }
   if (force_bn > 0 && force_bn < p.BN) p.BN = force_bn;
   p.n_tiles = cdiv(c.Bn, p.BN);
-  pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul, &p.TW, &p.TH, &p.TN);
+  pick_tile(128, c.Wt, c.Ht, c.Nt, c.a_mul_w > c.a_mul ? c.a_mul_w : c.a_mul, &p.TW, &p.TH, &p.TN);
   p.tiles_w = cdiv(c.Wt, p.TW); p.tiles_h = cdiv(c.Ht, p.TH); p.tiles_n = cdiv(c.Nt, p.TN);
   p.Wt = c.Wt; p.Ht = c.Ht; p.Nt = c.Nt;
   p.kh = c.kh; p.kw = c.kw;
@@ -98,8 +99,8 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
     uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
                        (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
-    uint32_t box[4] = {64, (uint32_t)(p.TW * c.a_mul), (uint32_t)(p.TH * c.a_mul), (uint32_t)p.TN};
-    uint32_t es[4] = {1, (uint32_t)c.a_mul, (uint32_t)c.a_mul, 1};
+    uint32_t box[4] = {64, (uint32_t)(p.TW * mul), (uint32_t)(p.TH * c.a_mul), (uint32_t)p.TN};
+    uint32_t es[4] = {1, (uint32_t)mul, (uint32_t)c.a_mul, 1};
     rc = make_tmap(&tmA, c.a, 4, dims, str, box, es);
   } else {
     // dim0: 64-element window starting at pixel (w*win_stride); dim1: output column.
@@ -358,6 +359,16 @@ extern "C" int mt_conv_s2_dgrad_merged_mode(int kh, int kw, int stride, int zpad
   return (!off && stride == 2 && zpad == 0 && kh == kw && (kh == 4 || (kh == 3 && Cin <= 128))) ? 1 : 0;
 }
 
+// Data gradient into <= 8 channels (the image: stems with reflection-padded input, stride 1): the
+// single-pixel form uses 8 of the 16 columns of the narrowest MMA and fetches one A tile per filter
+// tap.  Paired: columns (pixel parity, ci) = 16, kw + 1 column offsets per filter row, dy traversed
+// with stride 2 on w: kh*(kw+1) A tiles per pixel PAIR instead of 2*kh*kw.
+extern "C" int mt_conv_s1_dgrad_pair_mode(int kh, int kw, int stride, int zpad, int Cin_s) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("MT_DGRAD_PAIR"); off = (e && atoi(e) == 0) ? 1 : 0; }
+  return (!off && stride == 1 && zpad == 0 && kh == kw && Cin_s == 8) ? 1 : 0;
+}
+
 extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
                                void* stream) {
   int rc = check_desc(d);
@@ -372,6 +383,19 @@ extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_
   c.n_store = d->Cin_s; c.n_bias = 0; c.bias = nullptr; c.act = MT_ACT_NONE; c.out = dx;
   const long long pix = d->Cin_s, row = (long long)d->Win * d->Cin_s;
   c.out_n_stride = (long long)d->Hin * row;
+  if (mt_conv_s1_dgrad_pair_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin_s)) {
+    // dx[h, 2b+j, ci] = sum_r sum_t dy[h - r, 2b + 1 - t, :] . Wm[r][t][(j, ci), :],  t = 0..kw,
+    // filter column s = j - 1 + t (zero block outside 0..kw-1): mt_pack_conv_s1_dgrad_pair_weight
+    if (d->Win & 1) return -1014;
+    c.taps_total = d->kh * (d->kw + 1); c.Bn = 2 * d->Cin_s;
+    c.a_mul_w = 2;
+    c.Wt = d->Win / 2; c.Ht = d->Hin;
+    c.kh = d->kh; c.kw = d->kw + 1; c.off_h = 0; c.off_w = 1; c.step_h = -1; c.step_w = -1;
+    c.w_base = 0; c.w_step_r = d->kw + 1; c.w_step_s = 1;
+    c.n_store = 2 * d->Cin_s;
+    c.out_h_stride = row; c.out_w_stride = 2 * pix; c.out_off = 0;
+    return run_conv_like(c, (cudaStream_t)stream);
+  }
   if (d->stride == 1) {
     c.Wt = d->Win; c.Ht = d->Hin;
     c.kh = d->kh; c.kw = d->kw; c.off_h = d->zpad; c.off_w = d->zpad; c.step_h = -1; c.step_w = -1;

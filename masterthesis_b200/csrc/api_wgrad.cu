@@ -249,6 +249,27 @@ pack_window_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh
   }
 }
 
+// Data-gradient operand of the paired-pixel stride-1 mode (Cin_s == 8): wb[r*(kw+1) + t][(j, ci)][co],
+// 16 rows x Cout_s columns per tap; filter column s = j - 1 + t, zero block outside 0..kw-1.
+__global__ void __launch_bounds__(256)
+pack_conv_s1_dgrad_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int k_,
+                               __nv_bfloat16* __restrict__ wb) {
+  const unsigned Cout = Cout_, Cin = Cin_, k = k_;
+  const unsigned Cout_s = (Cout + 7) & ~7u;
+  const unsigned per_tap = 16 * Cout_s, n = k * (k + 1) * per_tap;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned tap = i / per_tap, e = i - tap * per_tap;
+    const unsigned row = e / Cout_s, co = e - row * Cout_s;
+    const unsigned j = row >> 3, ci = row & 7;
+    const unsigned r = tap / (k + 1), t = tap - r * (k + 1);
+    const int sx = (int)j - 1 + (int)t;
+    float v = 0.f;
+    if (sx >= 0 && sx < (int)k && ci < Cin && co < Cout)
+      v = __ldg(w + ((size_t)(co * Cin + ci) * k + r) * k + sx);
+    wb[i] = __float2bfloat16(v);
+  }
+}
+
 // dW[co][ci][r][s] (+)= g[r][co][s*Cin_s + ci] + g[r][Cout_s + co][(s + stride)*Cin_s + ci]
 __global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_,
                                                 int kw_, int stride_, int accumulate,
@@ -270,6 +291,21 @@ __global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int
 }  // namespace mt
 
 using namespace mt;
+
+extern "C" long long mt_packed_conv_s1_dgrad_pair_elems(int Cout, int k) {
+  return (long long)k * (k + 1) * 16 * round_up(Cout, 8);
+}
+extern "C" int mt_pack_conv_s1_dgrad_pair_weight(const float* w, int Cout, int Cin, int k, void* w_bwd,
+                                                 void* stream) {
+  const long long n = mt_packed_conv_s1_dgrad_pair_elems(Cout, k);
+  if (n >= (1ll << 31) || Cin > 8) return -1005;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_conv_s1_dgrad_pair_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, k,
+                                                                           (__nv_bfloat16*)w_bwd);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
+}
 
 extern "C" int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
                                                 int stride, int accumulate, float* dw, void* stream) {

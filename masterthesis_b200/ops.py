@@ -170,6 +170,12 @@ class ConvGeom:
         return bool(self.window and _lib.lib().mt_conv_window_pair_mode(self.Cin_s, self.kw, self.stride))
 
     @property
+    def pair_s1_dgrad(self) -> bool:
+        """stride-1 conv into <= 8 channels whose data gradient computes pixel pairs (include/mt_b200.h)"""
+        return bool(not self.transposed and _lib.lib().mt_conv_s1_dgrad_pair_mode(
+            self.kh, self.kw, self.stride, self.zpad, self.Cin_s))
+
+    @property
     def merged_s2_dgrad(self) -> bool:
         """stride-2 conv whose data gradient runs in the merged-parity mode (include/mt_b200.h)"""
         return bool(not self.transposed and
@@ -209,11 +215,26 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
             wb = _T.empty(L.mt_packed_conv_s2_dgrad_elems(g.Cout, g.Cin, g.kh), dtype=torch.bfloat16, device=w.device)
             check(L.mt_pack_conv_s2_dgrad_weight(_p(w), g.Cout, g.Cin, g.kh, _p(wb), _stream()),
                   "mt_pack_conv_s2_dgrad_weight")
+        elif g.pair_s1_dgrad:
+            wb = _T.empty(L.mt_packed_conv_s1_dgrad_pair_elems(g.Cout, g.kh), dtype=torch.bfloat16, device=w.device)
+            check(L.mt_pack_conv_s1_dgrad_pair_weight(_p(w), g.Cout, g.Cin, g.kh, _p(wb), _stream()),
+                  "mt_pack_conv_s1_dgrad_pair_weight")
         else:
             wb = _T.empty(L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, 1, 1), dtype=torch.bfloat16,
                           device=w.device)
             check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, 0, 1, None, _p(wb), _stream()),
                   "mt_pack_conv_weight")
+        _count(2)
+        return wf, wb
+    if g.pair_s1_dgrad:
+        # stride-1 conv into <= 8 channels: forward operand as usual, paired-pixel data-gradient operand
+        nf = L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0)
+        wf = _T.empty(nf, dtype=torch.bfloat16, device=w.device)
+        wb = _T.empty(L.mt_packed_conv_s1_dgrad_pair_elems(g.Cout, g.kh), dtype=torch.bfloat16, device=w.device)
+        check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, 0, int(g.window), _p(wf), None,
+                                    _stream()), "mt_pack_conv_weight")
+        check(L.mt_pack_conv_s1_dgrad_pair_weight(_p(w), g.Cout, g.Cin, g.kh, _p(wb), _stream()),
+              "mt_pack_conv_s1_dgrad_pair_weight")
         _count(2)
         return wf, wb
     if g.merged_s2_dgrad:

@@ -258,6 +258,9 @@ CASES = {
     "convT_128_64": lambda: convT_case(1, 128, 64, 24, 40, bias=False),
     # odd channel counts of DecoderConcat (stored 56 -> 32): merged-parity columns straddle 64-wide slabs
     # merged-parity stride-2 data gradients: 4x4 (no zero blocks), 3x3 into few channels, odd channels
+    # paired-pixel data gradient into <= 8 channels (stride 1): 3x3 with 8 channels, 1x1 with 5
+    "conv3x3_c8_pair": lambda: conv_case(2, 8, 16, 16, 12, 3, 1, 1),
+    "conv1x1_c5_pair": lambda: conv_case(2, 5, 24, 8, 10, 1, 1, 0),
     "conv4x4_s2_refl": lambda: conv_case(2, 64, 128, 32, 32, 4, 2, 1),
     "conv3x3_s2_odd": lambda: conv_case(2, 44, 52, 20, 12, 3, 2, 1),
     "convT_odd": lambda: convT_case(2, 52, 26, 12, 20),

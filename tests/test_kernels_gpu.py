@@ -15,7 +15,7 @@ def _cases():
     "convT_128_64", "in_relu", "in_res_noise", "adain_relu", "adain_res", "ln_relu",
     "in_lrelu_c1024", "pad1", "pad3", "c3_generic", "small_1x1_c32", "small_3x3_c32", "fused_stats_hot",
     "fused_stats_overhang", "fused_stats_s2", "fused_stats_convT", "fused_stats_convT_overhang",
-    "conv4x4_s2_refl", "conv3x3_s2_odd", "convT_odd", "convT_odd_wide", "upsample2", "mask_mul", "conv3x3_zpad1", "conv7x7_zpad3_rgb"])
+    "conv3x3_c8_pair", "conv1x1_c5_pair", "conv4x4_s2_refl", "conv3x3_s2_odd", "convT_odd", "convT_odd_wide", "upsample2", "mask_mul", "conv3x3_zpad1", "conv7x7_zpad3_rgb"])
 def test_kernel_case(name):
     from tests.kernel_cases import CASES, TOL
     res = CASES[name]()
