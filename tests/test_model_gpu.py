@@ -106,6 +106,11 @@ def test_flagged_training_steps_vs_reference_golden(name):
         # bf16-storage-emulated ORACLE (tests/emu.py) is itself 0.74e-2 / 0.98e-2 away from the fp32
         # reference on gan2_cls here, so these keys are bounded by 2e-2
         over = {k: 2e-2 for k in res if k.endswith('_cls')}
+        # ... and 5e-2 in the SECOND iteration, which runs on weights after one Adam step (a sign-like
+        # step of size lr whatever |grad|, so rounding noise in tiny gradients moves weights as far as
+        # signal does): measured 1.7e-2 .. 2.2e-2 over repeated runs (the weight-gradient split-K uses
+        # fp32 atomics, so the second iteration is not bit-reproducible run to run)
+        over.update({k: 5e-2 for k in res if k.startswith('loss_it1.') and k.endswith('_cls')})
     _check(res, 1e-2, 0.0, over)
 
 
