@@ -1,6 +1,6 @@
 """Run-to-run determinism of the eager sampling path on small shapes: MT_NET selects the part."""
 import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import torch
 from oracle import ref_import, synth
 from masterthesis_b200 import models

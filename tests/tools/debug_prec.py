@@ -1,7 +1,7 @@
 """Is the CUDA-vs-fp32 error intrinsic to bf16 storage?  Compare (a) CUDA path, (b) the oracle with
 bf16 rounding emulated at the same storage points, against the fp32 oracle."""
 import sys, os, types
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import torch
 import torch.nn.functional as F
 from oracle import synth, nets as onets

@@ -1,6 +1,6 @@
 """Find the first op whose output differs between two identical eager Ec forwards."""
 import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import torch
 from oracle import ref_import, synth
 from masterthesis_b200 import models, ops

@@ -4,7 +4,7 @@ reference, tests/test_oracle_golden.py) with its tensors moved to CUDA; noise / 
 CPU and copied, as the reference does (misc.py:25, networks.py:137, adain_model.py:84).
 /root/reference itself does not exist on the GPU box.  Prints images/s for true fp32 and TF32."""
 import json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 import bench
