@@ -201,6 +201,8 @@ def conv_roofline(model, batch, pk):
             # profiles/r1_ncu_conv_hot_full.txt (algorithmic: 35.7 MB in + 1.2 MB weights + 33.5 MB out,
             # the output stays in L2)
             "traffic": 38.43e6,
+            "traffic_note": "per 16-image launch (ncu capture); the stacked decoder calls launch it on 32 images: "
+                            "twice the algorithmic bytes and FLOPs per launch, same bytes per image",
             "peak_source": pk["source"], "launches": hot_n,
             "flop_per_launch_n16": 2.0 * 16 * 64 * 64 * 256 * 256 * 9,
             "ms_per_iter": hot_ms,
