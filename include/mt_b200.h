@@ -89,10 +89,11 @@ int mt_conv_window_pair_mode(int Cin_s, int kw, int stride);
 long long mt_packed_conv_window_pair_elems(int Cout, int kh);
 int mt_pack_conv_window_pair_weight(const float* w, int Cout, int Cin, int kh, int kw, int stride,
                                     void* w_fwd, void* stream);
-/* In the same mode mt_conv2d_wgrad writes dw_packed = [kh][2*Cout_s][64] fp32 (zeroed by the caller,
- * mt_packed_conv_window_pair_elems elements); this unpack folds the two pixel parities into dW (OIHW). */
-int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw, int stride,
-                                     int accumulate, float* dw, void* stream);
+/* In the same mode mt_conv2d_wgrad writes dw_packed = [splits][kh][2*Cout_s][64] fp32
+ * (mt_packed_conv_window_pair_elems elements per split); this unpack adds the splits and folds the two
+ * pixel parities into dW (OIHW). */
+int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int splits, int Cout, int Cin, int kh, int kw,
+                                     int stride, int accumulate, float* dw, void* stream);
 
 /* ---- convolutions (implicit GEMM, tcgen05/TMEM, TMA) -------------------------------- */
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
@@ -108,13 +109,18 @@ int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd, con
                         void* y, float* stats, int parts, void* stream);
 /* d(loss)/d(input buffer), including the reflection border rows/cols (folded later) */
 int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx, void* stream);
-/* d(loss)/d(weight) accumulated (+=) into fp32 dw_packed[taps][Cout][Cin_s] (window mode:
- * [kh][Cout][64]); mt_unpack_conv_wgrad scatters (or adds) it back to OIHW. */
-int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+/* d(loss)/d(weight) as split-K partial results: fp32 dw_packed[splits][taps][Cout][Cin_s] (window mode:
+ * [splits][kh][Cout][64]), splits = mt_conv2d_wgrad_splits(d), mt_packed_wgrad_elems() elements per split.
+ * Every split stores its own slab (no zeroing by the caller, no atomics); mt_unpack_conv_wgrad adds the
+ * slabs in split order and scatters (or adds) the result back to OIHW: weight gradients are
+ * reproducible bit for bit.  Error -1015 when `splits` does not match the query. */
+long long mt_packed_wgrad_elems(int Cout, int Cin, int kh, int kw, int transposed, int window);
+int mt_conv2d_wgrad_splits(const MtConv2d* d);
+int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed, int splits,
                     void* stream);
 /* accumulate != 0: dw += unpacked (straight into the parameter's .grad, what autograd's
  * AccumulateGrad would do with a returned tensor) */
-int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
+int mt_unpack_conv_wgrad(const float* dw_packed, int splits, int Cout, int Cin, int kh, int kw,
                          int transposed, int window, int accumulate, float* dw, void* stream);
 /* nn.ConvTranspose2d(k=3, s=2, p=1, op=1) forward / dgrad / wgrad     blocks.py:69-73.
  * Descriptor: Hin/Win = input dims, Hout/Wout = 2*Hin, 2*Win; kh=kw=3, stride=2, zpad=1. */
@@ -125,8 +131,9 @@ int mt_conv_transpose2d_fwd_stats(const MtConv2d* d, const void* x, const void* 
                                   const float* bias, void* y, float* stats, int parts, void* stream);
 int mt_conv_transpose2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
                               void* stream);
+int mt_conv_transpose2d_wgrad_splits(const MtConv2d* d);
 int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
-                              void* stream);
+                              int splits, void* stream);
 
 /* ---- layout / padding ------------------------------------------------------------------ */
 /* NCHW fp32 image (+ one-hot domain code tiled over H,W: networks.py:136-140) -> NHWC bf16 with
@@ -155,9 +162,11 @@ int mt_add_interior(void* dpad, const void* dense, int N, int H, int W, int C, i
 int mt_plane_stats_parts(int N, int HW, int C);
 int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, int parts, void* stream);
 /* stats: [N][parts][C][2] (from mt_plane_stats or from the conv epilogue, mt_conv2d_fwd_stats) */
+/* csum (optional, [N][C]): the per-channel plane sums, needed by mt_norm_bwd_params for the bias gradient of
+ * a biased convolution in front of a LayerNorm */
 int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,
                      const float* gb, const float* ln_w, const float* ln_b, float* ss, float* mr,
-                     void* stream);
+                     float* csum, void* stream);
 /* out_pad[interior] = act(x*scale+shift) (+ residual) (+ noise, misc.py:25); ss may be NULL.
  * With out_p > 0 the reflection border of out_pad is written too (no mt_reflect_border needed). */
 int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C, int act,
@@ -165,11 +174,24 @@ int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C
                       void* out_pad, int out_p, void* stream);
 /* g: gradient of the block output, dense (g_pad = 0) or the consumer's PADDED gradient buffer
  * [N, H+2g_pad, W+2g_pad, C], in which case the adjoint of ReflectionPad2d is applied on the fly */
+/* sums: [N][parts][C][2] per-chunk (sum g', sum g'*x), parts = mt_norm_bwd_parts(...); plain stores, every
+ * slot written once, added in a fixed order by mt_norm_bwd_finalize (reproducible backward passes) */
+int mt_norm_bwd_parts(int N, int H, int W, int C, int act, int g_pad);
 int mt_norm_bwd_reduce(const void* g, int g_pad, const void* x, const float* ss, int N, int H, int W,
-                       int C, int act, float slope, float* sums, void* stream);
-int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C, int C_valid, int HW,
-                         const float* gb, const float* ln_w, float* coef, float* dgb,
-                         float* dln_w, float* dln_b, void* stream);
+                       int C, int act, float slope, float* sums, int parts, void* stream);
+/* red (optional, [N][C][2]): per-sample (sum g'*xhat, sum g') for mt_norm_bwd_params */
+int mt_norm_bwd_finalize(const float* sums, int parts, const float* mr, int mode, int N, int C, int C_valid,
+                         int HW, const float* gb, const float* ln_w, float* coef, float* dgb, float* red,
+                         void* stream);
+/* Gradients that sum over the samples (in sample order): the LayerNorm affine parameters dln_w / dln_b
+ * [C_valid] (norm.py:19-21; both or neither) and dbias [C_valid] = sum_n sum_hw dx, the gradient of the bias
+ * of the convolution in front of the norm (needs coef and the forward csum; exactly zero for InstanceNorm /
+ * AdaIN, where the caller skips it).  accumulate != 0: += into the outputs (parameter .grad buffers). */
+int mt_norm_bwd_params(const float* red, const float* coef, const float* csum, int N, int C, int C_valid,
+                       int HW, float* dln_w, float* dln_b, float* dbias, int accumulate, void* stream);
+/* db[c] (+)= sum over `rows` of stats[row][c][0], c < C_valid: column sums of a dense tensor (bias gradients,
+ * blocks.py:36) from the partial sums of mt_plane_stats (rows = N * parts), added in row order */
+int mt_colsum_into(const float* stats, int rows, int C, int C_valid, float* db, int accumulate, void* stream);
 int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss, const float* coef,
                       int N, int H, int W, int C, int act, float slope, void* dx, void* stream);
 /* backward of conv+bias+activation written into a padded buffer: fold + act' */
@@ -204,11 +226,16 @@ int mt_gap_bwd(const float* dout, int N, int HW, int C, void* dx, void* stream);
 /* ConvTranspose2d(C -> Co<=4, k=1, no bias) + tanh, NHWC bf16 -> NCHW fp32  networks.py:248-251 */
 int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int C, int Co, float* y,
                     void* stream);
+/* dw_parts: scratch [parts][C][4] fp32, parts = mt_rgb_head_bwd_parts(N, HW, C) (per-block partial sums of
+ * dw, added in block order: reproducible) */
+int mt_rgb_head_bwd_parts(int N, int HW, int C);
 int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, const float* w, int N, int HW,
-                    int C, int Co, void* dx, float* dw, void* stream);
-/* sum(x^2) over the interior (adain_model.py:396-399) and dx = scale * x on the interior */
+                    int C, int Co, void* dx, float* dw, float* dw_parts, int parts, void* stream);
+/* sum(x^2) over the interior (adain_model.py:396-399) and dx = scale * x on the interior;
+ * partials: scratch [parts] fp32, parts = mt_sumsq_interior_parts(N, H, W, C) */
+int mt_sumsq_interior_parts(int N, int H, int W, int C);
 int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, int pad, float* out,
-                      void* stream);
+                      float* partials, int parts, void* stream);
 int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C, int pad,
                       void* dx_pad, void* stream);
 

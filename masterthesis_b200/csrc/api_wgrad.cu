@@ -16,8 +16,9 @@ struct WgradLike {
   float* out; int N_store;                   // row pitch of out (fp32 elements)
 };
 
-static int run_wgrad_like(const WgradLike& c, cudaStream_t stream) {
-  WgradParams p;
+// Tile / split-K plan of one weight gradient (shared by the launcher and by the *_wgrad_splits queries
+// with which the caller sizes dw_packed).
+static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   memset(&p, 0, sizeof(p));
   pick_tile(64, c.Pw, c.Ph, c.Pn, c.q_mul, &p.TW, &p.TH, &p.TN);
   p.tiles_w = cdiv(c.Pw, p.TW); p.tiles_h = cdiv(c.Ph, p.TH); p.tiles_n = cdiv(c.Pn, p.TN);
@@ -45,7 +46,14 @@ static int run_wgrad_like(const WgradLike& c, cudaStream_t stream) {
   p.N_valid = c.N_store;
   p.out_m_stride = c.N_store;
   p.out_tap_stride = (long long)c.Pc * c.N_store;
+  p.out_split_stride = (long long)p.kh * p.kw * p.out_tap_stride;
   p.out = c.out;
+}
+
+static int run_wgrad_like(const WgradLike& c, int splits, cudaStream_t stream) {
+  WgradParams p;
+  plan_wgrad(c, p);
+  if (splits != p.splits) return -1015;
 
   CUtensorMap tmP, tmQ;
   {
@@ -159,7 +167,10 @@ pack_weight_pairs_kernel(const float* __restrict__ w, int Cout_, int Cin_, int T
 
 // dw_packed -> dw (OIHW / IOHW fp32). Conv2d: [tap][Cout][Cin_s] (window: [kh][Cout][64]);
 // ConvTranspose2d: [tap][Cin][Cout_s].
-__global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_, int kw_,
+// `g` holds `splits` partial results `split_stride` elements apart (split-K slices of the weight-gradient
+// kernel), added here in split order.
+__global__ void unpack_wgrad_kernel(const float* __restrict__ g, int splits, unsigned split_stride,
+                                    int Cout_, int Cin_, int kh_, int kw_,
                                     int transposed, int window, int accumulate,
                                     float* __restrict__ dw) {
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_;
@@ -177,7 +188,9 @@ __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int Cout_, int 
     if (transposed) src = ((r * kw + s) * Cin + ci) * Cout_s + co;
     else if (window) src = (r * Cout + co) * 64 + s * Cin_s + ci;
     else src = ((r * kw + s) * Cout + co) * Cin_s + ci;
-    dw[i] = accumulate ? dw[i] + g[src] : g[src];
+    float v = g[src];
+    for (int sp = 1; sp < splits; ++sp) v += g[(size_t)sp * split_stride + src];
+    dw[i] = accumulate ? dw[i] + v : v;
   }
 }
 
@@ -271,7 +284,8 @@ pack_conv_s1_dgrad_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_,
 }
 
 // dW[co][ci][r][s] (+)= g[r][co][s*Cin_s + ci] + g[r][Cout_s + co][(s + stride)*Cin_s + ci]
-__global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int Cout_, int Cin_, int kh_,
+__global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int splits, unsigned split_stride,
+                                                int Cout_, int Cin_, int kh_,
                                                 int kw_, int stride_, int accumulate,
                                                 float* __restrict__ dw) {
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_, stride = stride_;
@@ -282,8 +296,10 @@ __global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int
     const unsigned s = i - t * kw;
     const unsigned t2 = t / kh, r = t - t2 * kh;
     const unsigned co = t2 / Cin, ci = t2 - co * Cin;
-    const float v = g[((size_t)r * 2 * Cout_s + co) * 64 + s * Cin_s + ci] +
-                    g[((size_t)r * 2 * Cout_s + Cout_s + co) * 64 + (s + stride) * Cin_s + ci];
+    const size_t s0 = ((size_t)r * 2 * Cout_s + co) * 64 + s * Cin_s + ci;
+    const size_t s1 = ((size_t)r * 2 * Cout_s + Cout_s + co) * 64 + (s + stride) * Cin_s + ci;
+    float v = 0.f;
+    for (int sp = 0; sp < splits; ++sp) v += g[(size_t)sp * split_stride + s0] + g[(size_t)sp * split_stride + s1];
     dw[i] = accumulate ? dw[i] + v : v;
   }
 }
@@ -307,14 +323,16 @@ extern "C" int mt_pack_conv_s1_dgrad_pair_weight(const float* w, int Cout, int C
   return e == cudaSuccess ? 0 : -(int)e;
 }
 
-extern "C" int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
-                                                int stride, int accumulate, float* dw, void* stream) {
+extern "C" int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int splits, int Cout, int Cin, int kh,
+                                                int kw, int stride, int accumulate, float* dw, void* stream) {
   const long long n = (long long)Cout * Cin * kh * kw;
-  if (n >= (1ll << 31)) return -1005;
+  const long long per = mt_packed_conv_window_pair_elems(Cout, kh);
+  if (n >= (1ll << 31) || per >= (1ll << 31) || splits < 1) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  unpack_window_pair_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, Cout, Cin, kh, kw,
-                                                                            stride, accumulate, dw);
+  unpack_window_pair_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, splits, (unsigned)per,
+                                                                            Cout, Cin, kh, kw, stride,
+                                                                            accumulate, dw);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
 }
@@ -393,23 +411,29 @@ extern "C" int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, in
   return e == cudaSuccess ? 0 : -(int)e;
 }
 
-extern "C" int mt_unpack_conv_wgrad(const float* dw_packed, int Cout, int Cin, int kh, int kw,
+extern "C" long long mt_packed_wgrad_elems(int Cout, int Cin, int kh, int kw, int transposed, int window) {
+  const int Cin_s = round_up(Cin, 8), Cout_s = round_up(Cout, 8);
+  if (transposed) return (long long)kh * kw * Cin * Cout_s;
+  return window ? (long long)kh * Cout * 64 : (long long)kh * kw * Cout * Cin_s;
+}
+
+extern "C" int mt_unpack_conv_wgrad(const float* dw_packed, int splits, int Cout, int Cin, int kh, int kw,
                                     int transposed, int window, int accumulate, float* dw,
                                     void* stream) {
   const long long n = (long long)Cout * Cin * kh * kw;
-  if (n >= (1ll << 31)) return -1005;
+  const long long per = mt_packed_wgrad_elems(Cout, Cin, kh, kw, transposed, window);
+  if (n >= (1ll << 31) || per >= (1ll << 31) || splits < 1) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  unpack_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, Cout, Cin, kh, kw,
-                                                                transposed, window, accumulate, dw);
+  unpack_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, splits, (unsigned)per, Cout, Cin,
+                                                                kh, kw, transposed, window, accumulate, dw);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
 }
 
-extern "C" int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
-                               void* stream) {
+static int describe_conv_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+                               WgradLike& c) {
   if (!d || d->Cin_s % 8 || d->Cout_s % 8) return -1003;
-  WgradLike c;
   memset(&c, 0, sizeof(c));
   if (d->window && !(mt_conv_window_mode(d->Cin_s, d->kw) && d->zpad == 0)) return -1009;
   const bool win = d->window != 0;
@@ -433,13 +457,27 @@ extern "C" int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy,
     c.N_store = d->Cin_s;
   }
   c.out = dw_packed;
-  return run_wgrad_like(c, (cudaStream_t)stream);
+  return 0;
 }
 
-extern "C" int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const void* dy,
-                                         float* dw_packed, void* stream) {
-  if (!d || d->Cin_s % 8 || d->Cout_s % 8) return -1003;
+extern "C" int mt_conv2d_wgrad_splits(const MtConv2d* d) {
   WgradLike c;
+  if (describe_conv_wgrad(d, nullptr, nullptr, nullptr, c)) return 0;
+  WgradParams p;
+  plan_wgrad(c, p);
+  return p.splits;
+}
+
+extern "C" int mt_conv2d_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+                               int splits, void* stream) {
+  WgradLike c;
+  const int rc = describe_conv_wgrad(d, x, dy, dw_packed, c);
+  return rc ? rc : run_wgrad_like(c, splits, (cudaStream_t)stream);
+}
+
+static int describe_convT_wgrad(const MtConv2d* d, const void* x, const void* dy, float* dw_packed,
+                                WgradLike& c) {
+  if (!d || d->Cin_s % 8 || d->Cout_s % 8) return -1003;
   memset(&c, 0, sizeof(c));
   // dW[ci][co][r][s] = sum x[hi, wi, ci] * dy[2hi - zpad + r, 2wi - zpad + s, co]
   c.p = x; c.Pn = d->N; c.Ph = d->Hin; c.Pw = d->Win; c.Pc = d->Cin; c.Pc_s = d->Cin_s;
@@ -448,5 +486,20 @@ extern "C" int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const
   c.kh = d->kh; c.kw = d->kw; c.off_h = -d->zpad; c.off_w = -d->zpad; c.step_h = 1; c.step_w = 1;
   c.N_store = d->Cout_s;
   c.out = dw_packed;
-  return run_wgrad_like(c, (cudaStream_t)stream);
+  return 0;
+}
+
+extern "C" int mt_conv_transpose2d_wgrad_splits(const MtConv2d* d) {
+  WgradLike c;
+  if (describe_convT_wgrad(d, nullptr, nullptr, nullptr, c)) return 0;
+  WgradParams p;
+  plan_wgrad(c, p);
+  return p.splits;
+}
+
+extern "C" int mt_conv_transpose2d_wgrad(const MtConv2d* d, const void* x, const void* dy,
+                                         float* dw_packed, int splits, void* stream) {
+  WgradLike c;
+  const int rc = describe_convT_wgrad(d, x, dy, dw_packed, c);
+  return rc ? rc : run_wgrad_like(c, splits, (cudaStream_t)stream);
 }

@@ -185,11 +185,12 @@ rgb_head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
   }
 }
 
-// g_o = dy_o*(1-y_o^2); dx[c] = sum_o g_o w[c][o]; dw[c][o] += sum_pix x[c] g_o
+// g_o = dy_o*(1-y_o^2); dx[c] = sum_o g_o w[c][o]; dwp[block][c][o] = this block's sum_pix x[c] g_o
+// (plain stores; rgb_head_dw_reduce_kernel adds the blocks in index order: reproducible)
 __global__ void __launch_bounds__(256)
 rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, int N,
-                    int HW, int C, int Co, __nv_bfloat16* __restrict__ dx, float* __restrict__ dw) {
+                    int HW, int C, int Co, __nv_bfloat16* __restrict__ dx, float* __restrict__ dwp) {
   extern __shared__ float sm[];  // ws[C*4] | red[lanes*V*32]
   float* ws = sm;
   float* red = sm + C * 4;
@@ -287,14 +288,29 @@ rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
     float s = 0.f;
     for (int l = 0; l < lanes; ++l) s += red[l * V * 32 + t];
     const int c = (t / 32) * 8 + (t % 32) / 4, o = t & 3;
-    if (o < Co) atomicAdd(dw + c * Co + o, s);
+    dwp[((size_t)blockIdx.x * C + c) * 4 + o] = s;
   }
 }
+__global__ void __launch_bounds__(256)
+rgb_head_dw_reduce_kernel(const float* __restrict__ dwp, int parts, int C, int Co, float* __restrict__ dw) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;     // (c, o) with o < 4
+  if (t >= C * 4) return;
+  float a[4] = {0.f, 0.f, 0.f, 0.f};
+  int i = 0;
+  for (; i + 3 < parts; i += 4) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) a[u] += dwp[(size_t)(i + u) * C * 4 + t];
+  }
+  for (; i < parts; ++i) a[0] += dwp[(size_t)i * C * 4 + t];
+  const int c = t >> 2, o = t & 3;
+  if (o < Co) dw[c * Co + o] = (a[0] + a[1]) + (a[2] + a[3]);
+}
 
-// sum of squares over the interior of a padded buffer (fp32 scalar, atomics) and its gradient
+// sum of squares over the interior of a padded buffer (per-block partial sums, added in block order by
+// sum_partials_kernel: reproducible) and its gradient
 __global__ void __launch_bounds__(256)
 sumsq_interior_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, int C, int p,
-                      float* __restrict__ out) {
+                      float* __restrict__ part) {
   const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * H * W * V;
   float s = 0.f;
@@ -314,8 +330,40 @@ sumsq_interior_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, 
   if (threadIdx.x == 0) {
     float t = 0.f;
     for (int i = 0; i < 8; ++i) t += r[i];
-    atomicAdd(out, t);
+    part[blockIdx.x] = t;
   }
+}
+// out[0] = sum of part[0..n) in a fixed order (one block of 256 threads, strided partial sums, then a
+// fixed shuffle / shared-memory tree)
+__global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restrict__ part, int n,
+                                                           float* __restrict__ out) {
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n; i += 256) s += part[i];
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ float r[8];
+  if ((threadIdx.x & 31) == 0) r[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += r[i];
+    out[0] = t;
+  }
+}
+// db[c] (+)= sum over the rows of stats[row][c][0]  (column sums of a dense tensor from the per-chunk
+// partial sums of mt_plane_stats; rows added in index order)
+__global__ void __launch_bounds__(128) colsum_finalize_kernel(const float* __restrict__ stats, int rows, int C,
+                                                              int Cv, float* __restrict__ db, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= Cv) return;
+  float a[4] = {0.f, 0.f, 0.f, 0.f};
+  int i = 0;
+  for (; i + 3 < rows; i += 4) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) a[u] += stats[((size_t)(i + u) * C + c) * 2];
+  }
+  for (; i < rows; ++i) a[0] += stats[((size_t)i * C + c) * 2];
+  const float v = (a[0] + a[1]) + (a[2] + a[3]);
+  db[c] = accumulate ? db[c] + v : v;
 }
 // dx_pad = scale[0] * x_pad on the interior, 0 on the border
 __global__ void __launch_bounds__(256)
@@ -465,24 +513,38 @@ extern "C" int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int
                         ST(stream)>>>(CBF(x), w, N, HW, C, Co, y);
   return cuda_rc();
 }
+extern "C" int mt_rgb_head_bwd_parts(int N, int HW, int C) {
+  if (C % 8 || C / 8 > 256) return 0;
+  const int lanes = 256 / (C / 8);
+  return grid_for(((long long)N * HW + lanes - 1) / lanes, 1, 4);
+}
 extern "C" int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, const float* w, int N,
-                               int HW, int C, int Co, void* dx, float* dw, void* stream) {
+                               int HW, int C, int Co, void* dx, float* dw, float* dw_parts, int parts,
+                               void* stream) {
   if (C % 8 || Co > 4 || Co < 1 || C / 8 > 256) return -1003;
-  cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)C * Co * sizeof(float), ST(stream));
-  if (e != cudaSuccess) return -(int)e;
   const int V = C / 8, lanes = 256 / V;
   const size_t smem = ((size_t)C * 4 + (size_t)lanes * V * 32) * sizeof(float);
-  int grid = grid_for(((long long)N * HW + lanes - 1) / lanes, 1, 4);
-  rgb_head_bwd_kernel<<<grid, 256, smem, ST(stream)>>>(dy, y, CBF(x), w, N, HW, C, Co, BF(dx), dw);
+  const int grid = mt_rgb_head_bwd_parts(N, HW, C);
+  if (parts != grid || !dw_parts) return -1012;
+  rgb_head_bwd_kernel<<<grid, 256, smem, ST(stream)>>>(dy, y, CBF(x), w, N, HW, C, Co, BF(dx), dw_parts);
+  rgb_head_dw_reduce_kernel<<<(C * 4 + 255) / 256, 256, 0, ST(stream)>>>(dw_parts, parts, C, Co, dw);
   return cuda_rc();
 }
+extern "C" int mt_sumsq_interior_parts(int N, int H, int W, int C) {
+  return C % 8 ? 0 : grid_for((long long)N * H * W * (C / 8), 256, 4);
+}
 extern "C" int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, int pad, float* out,
-                                 void* stream) {
+                                 float* partials, int parts, void* stream) {
   if (C % 8) return -1003;
-  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(float), ST(stream));
-  if (e != cudaSuccess) return -(int)e;
-  sumsq_interior_kernel<<<grid_for((long long)N * H * W * (C / 8), 256, 4), 256, 0, ST(stream)>>>(
-      CBF(x_pad), N, H, W, C, pad, out);
+  if (parts != mt_sumsq_interior_parts(N, H, W, C) || !partials) return -1012;
+  sumsq_interior_kernel<<<parts, 256, 0, ST(stream)>>>(CBF(x_pad), N, H, W, C, pad, partials);
+  sum_partials_kernel<<<1, 256, 0, ST(stream)>>>(partials, parts, out);
+  return cuda_rc();
+}
+extern "C" int mt_colsum_into(const float* stats, int rows, int C, int C_valid, float* db, int accumulate,
+                              void* stream) {
+  if (rows < 1 || C_valid < 1 || C_valid > C) return -1005;
+  colsum_finalize_kernel<<<(C_valid + 127) / 128, 128, 0, ST(stream)>>>(stats, rows, C, C_valid, db, accumulate);
   return cuda_rc();
 }
 extern "C" int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C,

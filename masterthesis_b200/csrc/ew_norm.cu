@@ -10,8 +10,10 @@
 namespace mt {
 
 // ---------------------------------------------------------------- statistics
-// x [N, HW, C] -> stats [N][C][2] += (sum, sumsq).  One CTA = (n, pixel chunk); thread = one
-// 8-channel vector x a pixel lane; warp reads are 512 contiguous bytes.
+// x [N, HW, C] -> per-chunk partial sums out[N][chunks][C][2].  One CTA = (n, pixel chunk); thread =
+// one 8-channel vector x a pixel lane; warp reads are 512 contiguous bytes.  Every slot is written
+// exactly once with a plain store (no zeroing, no atomics): the finalize kernels add the slots in a
+// fixed order, so forward AND backward passes are reproducible bit for bit.
 // The backward variant reads the gradient through the ADJOINT of the reflection padding when
 // gp > 0: g is then the padded buffer [N, H+2gp, W+2gp, C] written by the consumer's data-gradient
 // and fold(g) is formed on the fly (only pixels next to the border have extra terms).
@@ -124,10 +126,7 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
     for (int l = 0; l < lanes; ++l) s += red[l * V * 16 + t];
     const int vv = t / 16, k = t % 16;
     const int c = vv * 8 + (k & 7);
-    if (kBackward) atomicAdd(out + ((long long)n * C + c) * 2 + (k >> 3), s);
-    // forward statistics: this chunk's slot of [N][chunks][C][2], plain store — the finalize kernel
-    // adds the slots in a fixed order, so a forward pass is reproducible bit for bit
-    else out[(((long long)n * chunks + chunk) * C + c) * 2 + (k >> 3)] = s;
+    out[(((long long)n * chunks + chunk) * C + c) * 2 + (k >> 3)] = s;
   }
 }
 
@@ -141,16 +140,11 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 // needs the whole sample in one block.
 static constexpr int FIN_UNROLL = 8;
 static constexpr int FIN_CSPLIT = 64;
-__global__ void __launch_bounds__(1024)
-norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N, int C, int Cv,
-                     int HW, float eps, const float* __restrict__ gb, const float* __restrict__ ln_w,
-                     const float* __restrict__ ln_b, float* __restrict__ ss, float* __restrict__ mr) {
-  extern __shared__ float tot_c[];   // [channels of this block][2]
-  __shared__ float2 part_sm[1024];
-  const int n = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
-  const int cb = gridDim.y > 1 ? blockIdx.y * FIN_CSPLIT : 0;           // first channel of the block
-  const int Cb = gridDim.y > 1 ? min(FIN_CSPLIT, C - cb) : C;           // channels of the block
-  const float2* sp = reinterpret_cast<const float2*>(stats) + (long long)n * parts * C + cb;
+// tot_c[2*c], tot_c[2*c+1] (c < Cb) = sum over the `parts` slots of sp[part*C + c], in a fixed order
+// (part groups of FIN_UNROLL loads in flight per thread, then the groups in index order).
+__device__ __forceinline__ void sum_parts(const float2* __restrict__ sp, int parts, int C, int Cb,
+                                          float* tot_c, float2* part_sm) {
+  const int T = blockDim.x, tid = threadIdx.x;
   if (parts == 1) {
     for (int c = tid; c < Cb; c += T) {
       const float2 t = sp[c];
@@ -194,6 +188,24 @@ norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N
     }
   }
   __syncthreads();
+}
+
+// `csum` (optional, [N][C]): the per-channel plane sums, kept for the backward pass of a LayerNorm that
+// follows a biased convolution (the bias gradient sum_hw dx needs sum_hw x per channel).
+__global__ void __launch_bounds__(1024)
+norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N, int C, int Cv,
+                     int HW, float eps, const float* __restrict__ gb, const float* __restrict__ ln_w,
+                     const float* __restrict__ ln_b, float* __restrict__ ss, float* __restrict__ mr,
+                     float* __restrict__ csum) {
+  extern __shared__ float tot_c[];   // [channels of this block][2]
+  __shared__ float2 part_sm[1024];
+  const int n = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
+  const int cb = gridDim.y > 1 ? blockIdx.y * FIN_CSPLIT : 0;           // first channel of the block
+  const int Cb = gridDim.y > 1 ? min(FIN_CSPLIT, C - cb) : C;           // channels of the block
+  sum_parts(reinterpret_cast<const float2*>(stats) + (long long)n * parts * C + cb, parts, C, Cb, tot_c,
+            part_sm);
+  if (csum)
+    for (int cl = tid; cl < Cb; cl += T) csum[(long long)n * C + cb + cl] = tot_c[2 * cl];
   __shared__ float tot[2];
   if (mode == MT_NORM_LAYER) {                     // gridDim.y == 1
     float s0 = 0.f, s1 = 0.f;
@@ -322,45 +334,54 @@ affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
 }
 
 // ---------------------------------------------------------------- backward finalize
-// sums[n][c] = (sum g, sum g*x) with g already masked by act'.  Produces coef[n][c][3] such that
-//   dx = c0*g + c1*x + c2, and the parameter gradients.
-__global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const float* __restrict__ mr,
-                                         int mode, int N, int C, int Cv, int HW,
-                                         const float* __restrict__ gb, const float* __restrict__ ln_w,
-                                         float* __restrict__ coef, float* __restrict__ dgb,
-                                         float* __restrict__ dln_w, float* __restrict__ dln_b) {
-  const int n = blockIdx.x;
+// sums[n][part][c] = per-chunk (sum g, sum g*x) with g already masked by act'.  Adds the chunks in a
+// fixed order (sum_parts), then produces coef[n][c][3] such that dx = c0*g + c1*x + c2, the AdaIN
+// modulation gradients, and (optional) red[n][c] = (sum g*xhat, sum g) for norm_bwd_params_kernel.
+// grid = (N, channel splits) as in the forward finalize (LayerNorm: the whole sample in one block).
+__global__ void __launch_bounds__(1024)
+norm_bwd_finalize_kernel(const float* __restrict__ sums, int parts, const float* __restrict__ mr,
+                         int mode, int N, int C, int Cv, int HW, const float* __restrict__ gb,
+                         const float* __restrict__ ln_w, float* __restrict__ coef,
+                         float* __restrict__ dgb, float* __restrict__ red) {
+  extern __shared__ float tot_c[];   // [channels of this block][2]
+  __shared__ float2 part_sm[1024];
   __shared__ float tot[2];
   __shared__ float r0[32], r1[32];
-  if (mode == MT_NORM_LAYER) {
+  const int n = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
+  const int cb = gridDim.y > 1 ? blockIdx.y * FIN_CSPLIT : 0;
+  const int Cb = gridDim.y > 1 ? min(FIN_CSPLIT, C - cb) : C;
+  sum_parts(reinterpret_cast<const float2*>(sums) + (long long)n * parts * C + cb, parts, C, Cb, tot_c,
+            part_sm);
+  if (mode == MT_NORM_LAYER) {                     // gridDim.y == 1
     // mean_n(A g) and mean_n(A g xhat) over all (c, hw)
     float s0 = 0.f, s1 = 0.f;
-    for (int c = threadIdx.x; c < Cv; c += blockDim.x) {
+    for (int c = tid; c < Cv; c += T) {
       const float mean = mr[((long long)n * C + c) * 2], rstd = mr[((long long)n * C + c) * 2 + 1];
-      const float sg = sums[((long long)n * C + c) * 2], sgx = sums[((long long)n * C + c) * 2 + 1];
+      const float sg = tot_c[2 * c], sgx = tot_c[2 * c + 1];
       const float sgxh = (sgx - mean * sg) * rstd;
       const float A = ln_w ? ln_w[c] : 1.f;
       s0 += A * sg; s1 += A * sgxh;
-      if (dln_w) { atomicAdd(dln_w + c, sgxh); atomicAdd(dln_b + c, sg); }
     }
     for (int o = 16; o; o >>= 1) {
       s0 += __shfl_xor_sync(0xffffffffu, s0, o);
       s1 += __shfl_xor_sync(0xffffffffu, s1, o);
     }
-    if ((threadIdx.x & 31) == 0) { r0[threadIdx.x >> 5] = s0; r1[threadIdx.x >> 5] = s1; }
+    if ((tid & 31) == 0) { r0[tid >> 5] = s0; r1[tid >> 5] = s1; }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       float t0 = 0.f, t1 = 0.f;
-      for (int i = 0; i < (blockDim.x + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
+      for (int i = 0; i < (T + 31) / 32; ++i) { t0 += r0[i]; t1 += r1[i]; }
       const float cnt = (float)Cv * (float)HW;
       tot[0] = t0 / cnt; tot[1] = t1 / cnt;
     }
     __syncthreads();
   }
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  for (int cl = tid; cl < Cb; cl += T) {
+    const int c = cb + cl;
     const float mean = mr[((long long)n * C + c) * 2], rstd = mr[((long long)n * C + c) * 2 + 1];
-    const float sg = sums[((long long)n * C + c) * 2], sgx = sums[((long long)n * C + c) * 2 + 1];
+    const float sg = tot_c[2 * cl], sgx = tot_c[2 * cl + 1];
     const float sgxh = (sgx - mean * sg) * rstd;   // sum g*xhat
+    if (red) { red[((long long)n * C + c) * 2] = sgxh; red[((long long)n * C + c) * 2 + 1] = sg; }
     float A = 1.f, mg, mgx;
     if (mode == MT_NORM_LAYER) {
       A = c >= Cv ? 0.f : (ln_w ? ln_w[c] : 1.f);
@@ -383,6 +404,28 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ sums, const f
       coef[((long long)n * C + c) * 3 + 2] = -A * rstd * (mg - mean * rstd * mgx);
     }
   }
+}
+
+// Parameter gradients that sum over the samples, in sample order (reproducible): thread = channel.
+//   dln_w[c] (+)= sum_n sum(g*xhat),  dln_b[c] (+)= sum_n sum(g)          (LayerNorm affine, norm.py:19-21)
+//   dbias[c] (+)= sum_n sum_hw dx = sum_n (c0*sum(g) + c1*sum(x) + c2*HW)  (bias of the conv in front of
+//   the norm; csum = per-channel plane sums kept by the forward finalize.  For InstanceNorm / AdaIN this
+//   is exactly zero and the caller does not ask for it.)
+__global__ void norm_bwd_params_kernel(const float* __restrict__ red, const float* __restrict__ coef,
+                                       const float* __restrict__ csum, int N, int C, int Cv, int HW,
+                                       float* __restrict__ dln_w, float* __restrict__ dln_b,
+                                       float* __restrict__ dbias, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= Cv) return;
+  float sw = 0.f, sb = 0.f, sd = 0.f;
+  for (int n = 0; n < N; ++n) {
+    const long long i = (long long)n * C + c;
+    const float sgxh = red[i * 2], sg = red[i * 2 + 1];
+    sw += sgxh; sb += sg;
+    if (dbias) sd += coef[i * 3] * sg + coef[i * 3 + 1] * csum[i] + coef[i * 3 + 2] * (float)HW;
+  }
+  if (dln_w) { dln_w[c] = accumulate ? dln_w[c] + sw : sw; dln_b[c] = accumulate ? dln_b[c] + sb : sb; }
+  if (dbias) dbias[c] = accumulate ? dbias[c] + sd : sd;
 }
 
 // dx = c0*(fold(g)*act'(y)) + c1*x + c2      grid = (pixel chunks, N), coefficients in registers;
@@ -540,14 +583,12 @@ static bool image_fits(int H, int W, int C, int pad) {
   return (long long)(H + 2 * pad) * (W + 2 * pad) * C < (1ll << 31) && (long long)H * W < (1 << 24);
 }
 
+// `parts` != 0: launch (the caller's buffer has that many slots per image; -1012 on a mismatch);
+// `parts` == 0: only report the number of slots this instantiation produces.
 static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss, int N, int H, int W,
-                         int C, int gp, int act, float slope, float* out, cudaStream_t st) {
+                         int C, int gp, int act, float slope, float* out, int parts, cudaStream_t st) {
   const int HW = H * W;
-  if (C % 8 || C / 8 > 256) return -1003;
-  if (bwd) {
-    cudaError_t e = cudaMemsetAsync(out, 0, (size_t)N * C * 2 * sizeof(float), st);
-    if (e != cudaSuccess) return -(int)e;
-  }
+  if (C % 8 || C / 8 > 256 || N < 1) return -1003;
   const int V = C / 8;
   const int lanes = 256 / V;
   const size_t smem = (size_t)lanes * V * 16 * sizeof(float);
@@ -556,6 +597,8 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
 #define MT_RED(B, A, G)                                                                           \
   do {                                                                                            \
     const int chunks = plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<B, A, G>, smem)); \
+    if (parts == 0) return chunks;                                                                \
+    if (parts != chunks) return -1012;                                                            \
     plane_reduce_kernel<B, A, G><<<N * chunks, 256, smem, st>>>(                                  \
         (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out); \
   } while (0)
@@ -571,23 +614,22 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
 
 // number of partial-sum slots per image that mt_plane_stats writes for this shape
 extern "C" int mt_plane_stats_parts(int N, int HW, int C) {
-  if (C % 8 || C / 8 > 256 || N < 1) return 0;
-  const size_t smem = (size_t)(256 / (C / 8)) * (C / 8) * 16 * sizeof(float);
-  return plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<false, 0, false>, smem));
+  const int r = reduce_launch(false, nullptr, nullptr, nullptr, N, HW, 1, C, 0, 0, 0.f, nullptr, 0, nullptr);
+  return r < 0 ? 0 : r;
 }
 extern "C" int mt_plane_stats(const void* x, int N, int HW, int C, float* stats, int parts,
                               void* stream) {
-  if (parts != mt_plane_stats_parts(N, HW, C)) return -1012;
-  return reduce_launch(false, x, nullptr, nullptr, N, HW, 1, C, 0, 0, 0.f, stats, ST(stream));
+  if (parts < 1) return -1012;
+  return reduce_launch(false, x, nullptr, nullptr, N, HW, 1, C, 0, 0, 0.f, stats, parts, ST(stream));
 }
 extern "C" int mt_norm_finalize(const float* stats, int parts, int mode, int N, int C, int C_valid, int HW, float eps,
                                 const float* gb, const float* ln_w, const float* ln_b, float* ss,
-                                float* mr, void* stream) {
+                                float* mr, float* csum, void* stream) {
   if (mode == MT_NORM_ADAIN && !gb) return -1008;
   if (C_valid <= 0 || C_valid > C || parts < 1) return -1005;
   const int threads = parts > 1 ? 1024 : 256;
   const int splits = (parts > 1 && mode != MT_NORM_LAYER && C > FIN_CSPLIT) ? (C + FIN_CSPLIT - 1) / FIN_CSPLIT : 1;
-  norm_finalize_kernel<<<dim3(N, splits), threads, (size_t)C * 2 * sizeof(float), ST(stream)>>>(stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr);
+  norm_finalize_kernel<<<dim3(N, splits), threads, (size_t)C * 2 * sizeof(float), ST(stream)>>>(stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr, csum);
   return cuda_rc();
 }
 extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,
@@ -618,17 +660,35 @@ extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, i
 #undef MT_AFF3
   return cuda_rc();
 }
-extern "C" int mt_norm_bwd_reduce(const void* g, int g_pad, const void* x, const float* ss, int N, int H,
-                                  int W, int C, int act, float slope, float* sums, void* stream) {
-  return reduce_launch(true, x, g, ss, N, H, W, C, g_pad, act, slope, sums, ST(stream));
+extern "C" int mt_norm_bwd_parts(int N, int H, int W, int C, int act, int g_pad) {
+  const int r = reduce_launch(true, nullptr, nullptr, nullptr, N, H, W, C, g_pad, act, 0.f, nullptr, 0, nullptr);
+  return r < 0 ? 0 : r;
 }
-extern "C" int mt_norm_bwd_finalize(const float* sums, const float* mr, int mode, int N, int C,
+extern "C" int mt_norm_bwd_reduce(const void* g, int g_pad, const void* x, const float* ss, int N, int H,
+                                  int W, int C, int act, float slope, float* sums, int parts, void* stream) {
+  if (parts < 1) return -1012;
+  return reduce_launch(true, x, g, ss, N, H, W, C, g_pad, act, slope, sums, parts, ST(stream));
+}
+extern "C" int mt_norm_bwd_finalize(const float* sums, int parts, const float* mr, int mode, int N, int C,
                                     int C_valid, int HW, const float* gb, const float* ln_w, float* coef,
-                                    float* dgb, float* dln_w, float* dln_b, void* stream) {
+                                    float* dgb, float* red, void* stream) {
   if (mode == MT_NORM_ADAIN && (!gb || !dgb)) return -1008;
-  if (C_valid <= 0 || C_valid > C) return -1005;
-  norm_bwd_finalize_kernel<<<N, 256, 0, ST(stream)>>>(sums, mr, mode, N, C, C_valid, HW, gb, ln_w, coef,
-                                                      dgb, dln_w, dln_b);
+  if (C_valid <= 0 || C_valid > C || parts < 1) return -1005;
+  const int threads = parts > 1 ? 1024 : 256;
+  const int splits = (parts > 1 && mode != MT_NORM_LAYER && C > FIN_CSPLIT) ? (C + FIN_CSPLIT - 1) / FIN_CSPLIT : 1;
+  norm_bwd_finalize_kernel<<<dim3(N, splits), threads, (size_t)C * 2 * sizeof(float), ST(stream)>>>(
+      sums, parts, mr, mode, N, C, C_valid, HW, gb, ln_w, coef, dgb, red);
+  return cuda_rc();
+}
+extern "C" int mt_norm_bwd_params(const float* red, const float* coef, const float* csum, int N, int C,
+                                  int C_valid, int HW, float* dln_w, float* dln_b, float* dbias,
+                                  int accumulate, void* stream) {
+  if (C_valid <= 0 || C_valid > C || !red) return -1005;
+  if ((dln_w == nullptr) != (dln_b == nullptr)) return -1008;
+  if (dbias && (!coef || !csum)) return -1008;
+  if (!dln_w && !dbias) return 0;
+  norm_bwd_params_kernel<<<(C_valid + 127) / 128, 128, 0, ST(stream)>>>(red, coef, csum, N, C, C_valid, HW,
+                                                                        dln_w, dln_b, dbias, accumulate);
   return cuda_rc();
 }
 extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss,

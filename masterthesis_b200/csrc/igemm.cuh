@@ -54,7 +54,9 @@ struct WgradParams {
   int tmem_cols;
   int M_valid, N_valid;           // Cout, Cin(stored) extents to write
   long long out_tap_stride, out_m_stride;  // fp32 element strides of dW[tap][m][n]
-  float* out;                     // accumulated with atomics (must be zeroed by caller)
+  long long out_split_stride;     // ... and between the partial results of the split-K slices
+  float* out;                     // [splits][taps][M][N]: every split stores its own slab (plain stores, no
+                                  // zeroing, no atomics); the unpack kernels add the slabs in split order
 };
 
 int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,

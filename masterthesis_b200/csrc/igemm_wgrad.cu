@@ -4,7 +4,9 @@
 // Q the one sampled through the tap map (x for Conv2d, dy for ConvTranspose2d).  The reduction
 // dimension is the pixel index, so both operands are MN-major in shared memory: one 4-D TMA
 // box of (64 channels x 64 pixels) is a [K=64][MN=64] SWIZZLE_128B slab.  Split-K over pixel
-// tiles; fp32 partial tiles are combined with vector red.global.add.
+// tiles; every split stores its fp32 partial tile into its own slab of the output ([splits][taps][M][N],
+// plain 16-byte stores: no zeroing, no atomics) and the unpack kernel adds the slabs in split order, so
+// weight gradients are reproducible bit for bit.
 // Replaces autograd's Conv2d/ConvTranspose2d weight gradients (reference: the .backward() calls
 // of src/models/adain_model.py:219,316,391).
 #include "igemm.cuh"
@@ -16,9 +18,8 @@ static constexpr int WG_BM = 128;
 static constexpr int WG_BK = 64;           // pixels per stage
 static constexpr int WG_CHUNK = 64 * 128;  // one (64 ch x 64 pix) slab in bytes
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b),
-               "f"(c), "f"(d)
+__device__ __forceinline__ void st_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
                : "memory");
 }
 
@@ -153,7 +154,8 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
     const int q = warp & 3;
     const int m = m_tile * WG_BM + q * 32 + lane;
     const bool row_ok = m < p.M_valid;
-    float* orow = p.out + (long long)tap * p.out_tap_stride + (long long)m * p.out_m_stride;
+    float* orow = p.out + (long long)split * p.out_split_stride + (long long)tap * p.out_tap_stride +
+                  (long long)m * p.out_m_stride;
     const int n_base = n_tile * BN;
     mbar_wait(smem_u32(&bar_tmem_full), 0);
     tc_fence_after();
@@ -167,8 +169,8 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
         for (int g = 0; g < 4; ++g) {
           const int n = n_base + c0 + g * 4;
           if (n < p.N_valid)
-            red_add_v4(orow + n, __uint_as_float(v[g * 4 + 0]), __uint_as_float(v[g * 4 + 1]),
-                       __uint_as_float(v[g * 4 + 2]), __uint_as_float(v[g * 4 + 3]));
+            st_v4(orow + n, __uint_as_float(v[g * 4 + 0]), __uint_as_float(v[g * 4 + 1]),
+                  __uint_as_float(v[g * 4 + 2]), __uint_as_float(v[g * 4 + 3]));
         }
       }
     }

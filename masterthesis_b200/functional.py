@@ -18,8 +18,21 @@ def _c(t):
     return t if t is None or t.is_contiguous() else t.contiguous()
 
 
-def _bias_grad(dy, Cout):
-    return ops.channel_sum(dy)[:Cout]
+def _grad_buf(p):
+    """the parameter's gradient buffer if our kernels may add into it directly (a leaf with an fp32
+    contiguous .grad — FlatAdam's bucket view — and no higher-order graph being recorded), else None"""
+    if p is None or not p.is_leaf:
+        return None
+    gr = p.grad
+    if gr is not None and gr.is_contiguous() and gr.dtype == torch.float32 and not torch.is_grad_enabled():
+        return gr
+    return None
+
+
+def _bias_grad(dy, bias):
+    """dL/d(bias) = column sums of dy: added into bias.grad in place when possible (returns None, so
+    autograd launches no accumulation kernel), else returned"""
+    return ops.bias_grad(dy, bias.shape[0], into=_grad_buf(bias))
 
 
 class ImageToNHWC(Function):
@@ -42,8 +55,8 @@ def _wgrad(weight, x, dy, geom, needed):
     has a gradient buffer (FlatAdam's bucket view), else returned for autograd to accumulate."""
     if not needed:
         return None
-    gr = weight.grad if weight.is_leaf else None     # spectral-normalised weights are graph nodes
-    if gr is not None and gr.is_contiguous() and gr.dtype == torch.float32 and torch.is_grad_enabled() is False:
+    gr = _grad_buf(weight)                           # spectral-normalised weights are graph nodes
+    if gr is not None:
         ops.conv_wgrad_into(x, dy, geom, gr)
         return None
     return ops.conv_wgrad(x, dy, geom)
@@ -58,7 +71,7 @@ class ConvAct(Function):
         out = ops.conv_fwd(x, wf, bias, geom, act=act, out_pad=out_pad)
         ops.reflect_border_(out, out_pad)
         ctx.geom, ctx.act, ctx.out_pad = geom, act, out_pad
-        ctx.has_bias = bias is not None
+        ctx.bias = bias
         ctx.weight = weight
         ctx.save_for_backward(x, out if (act is not None) else None, wb)
         return out
@@ -74,7 +87,7 @@ class ConvAct(Function):
             dy = ops.act_bwd_fold(dout, out, op, act)
         dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
         dw = _wgrad(ctx.weight, x, dy, g, ctx.needs_input_grad[1])
-        db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        db = _bias_grad(dy, ctx.bias) if (ctx.bias is not None and ctx.needs_input_grad[2]) else None
         return dx, dw, db, None, None, None, None, None
 
 
@@ -88,26 +101,39 @@ class ConvNormAct(Function):
         N, H, W, C = raw.shape
         gb = p1 if mode == "adain" else None
         lw, lb = (p1, p2) if mode == "layer" else (None, None)
-        ss, mr = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb, C_valid=geom.Cout)
+        # a biased conv in front of a LayerNorm: keep the per-channel plane sums for the bias gradient
+        want_cs = mode == "layer" and bias is not None and bias.requires_grad
+        fin = ops.norm_finalize(stats, mode, H * W, _c(gb), lw, lb, C_valid=geom.Cout, csum=want_cs)
+        ss, mr, csum = fin if want_cs else (fin[0], fin[1], None)
         out = ops.affine_act_fwd(raw, ss, act=act, noise=noise, out_p=out_pad)   # incl. reflection border
         ctx.geom, ctx.mode, ctx.act, ctx.out_pad = geom, mode, act, out_pad
-        ctx.has_bias = bias is not None
+        ctx.bias, ctx.p2 = bias, p2
         ctx.weight = weight
-        ctx.save_for_backward(x, raw, ss, mr, p1, wb)
+        ctx.save_for_backward(x, raw, ss, mr, p1, wb, csum)
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        x, raw, ss, mr, p1, wb = ctx.saved_tensors
+        x, raw, ss, mr, p1, wb, csum = ctx.saved_tensors
         g, mode, act, op = ctx.geom, ctx.mode, ctx.act, ctx.out_pad
-        dy, dgb, dlw, dlb = ops.norm_bwd(_c(dout), raw, ss, mr, mode, act=act,
-                                         gb=_c(p1) if mode == "adain" else None,
-                                         ln_w=p1 if mode == "layer" else None, C_valid=g.Cout, g_pad=op)
+        bias, p2 = ctx.bias, ctx.p2
+        need_db = bias is not None and ctx.needs_input_grad[2]
+        ln = mode == "layer" and p1 is not None
+        dln_into = None
+        if ln and _grad_buf(p1) is not None and _grad_buf(p2) is not None:
+            dln_into = (_grad_buf(p1), _grad_buf(p2))
+        dy, dgb, dlw, dlb, db = ops.norm_bwd(
+            _c(dout), raw, ss, mr, mode, act=act, gb=_c(p1) if mode == "adain" else None,
+            ln_w=p1 if ln else None, C_valid=g.Cout, g_pad=op, csum=csum,
+            dln_into=dln_into, dbias_into=_grad_buf(bias) if need_db else None,
+            want_dbias=need_db and csum is not None)
+        if need_db and db is None and csum is None and _grad_buf(bias) is None:
+            # bias in front of InstanceNorm / AdaIN: sum_hw dx is exactly zero for every plane
+            db = torch.zeros_like(bias)
         dx = ops.conv_dgrad(dy, wb, g, x.shape[1], x.shape[2]) if ctx.needs_input_grad[0] else None
         dw = _wgrad(ctx.weight, x, dy, g, ctx.needs_input_grad[1])
-        db = _bias_grad(dy, g.Cout) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
-        dp1 = dgb if mode == "adain" else (dlw.view_as(p1) if mode == "layer" and dlw is not None else None)
-        dp2 = dlb.view_as(p1) if (mode == "layer" and dlb is not None) else None
+        dp1 = dgb if mode == "adain" else (dlw.view_as(p1) if ln and dlw is not None else None)
+        dp2 = dlb.view_as(p2) if (ln and dlb is not None) else None
         return dx, dw, db, None, None, None, None, dp1, dp2, None, None, None
 
 
@@ -137,10 +163,10 @@ class ResBlock(Function):
         g, mode, act, op = ctx.geom, ctx.mode, ctx.act, ctx.out_pad
         dout = _c(dout)
         # the adjoint of the reflection borders is applied inside the norm-backward kernels (g_pad)
-        dy2, dgb2, _, _ = ops.norm_bwd(dout, raw2, ss2, mr2, mode, act=None, gb=gb, g_pad=op)
+        dy2, dgb2 = ops.norm_bwd(dout, raw2, ss2, mr2, mode, act=None, gb=gb, g_pad=op)[:2]
         dw2 = _wgrad(ctx.w2, h, dy2, g, ctx.needs_input_grad[2])
         dh = ops.conv_dgrad(dy2, wb2, g, h.shape[1], h.shape[2])
-        dy1, dgb1, _, _ = ops.norm_bwd(dh, raw1, ss1, mr1, mode, act=act, gb=gb, g_pad=1)
+        dy1, dgb1 = ops.norm_bwd(dh, raw1, ss1, mr1, mode, act=act, gb=gb, g_pad=1)[:2]
         dw1 = _wgrad(ctx.w1, x, dy1, g, ctx.needs_input_grad[1])
         dx = None
         if ctx.needs_input_grad[0]:
@@ -173,6 +199,7 @@ class DownBlock(Function):
         ops.reflect_border_(out, out_pad)
         ctx.geoms, ctx.out_pad = geoms, out_pad
         ctx.ws = (wA, wB, wS)
+        ctx.bs = (bA, bB, bS)
         ctx.save_for_backward(a, b, pa, out, wbA, wbB, wbS)
         return out
 
@@ -182,14 +209,17 @@ class DownBlock(Function):
         gA, gB, gS = ctx.geoms
         need = ctx.needs_input_grad
         dd, dc = ops.pool_add_act_bwd(_c(dout), out, ctx.out_pad, "lrelu")
+        bA, bB, bS = ctx.bs
         dwB = _wgrad(ctx.ws[1], b, dc, gB, need[3])
-        dbB = _bias_grad(dc, gB.Cout) if need[4] else None
+        # dc is dd spread over the 2x2 windows with weight 1/4 (exact in bf16): its column sums equal dd's,
+        # so ONE pass over the quarter-size dd yields both bias gradients
+        dbB = _bias_grad(dd, bB) if (bB is not None and need[4]) else None
         db_pad = ops.conv_dgrad(dc, wbB, gB, b.shape[1], b.shape[2])
         dyA = ops.act_bwd_fold(db_pad, b, 1, "lrelu")
         dwA = _wgrad(ctx.ws[0], a, dyA, gA, need[1])
-        dbA = _bias_grad(dyA, gA.Cout) if need[2] else None
+        dbA = _bias_grad(dyA, bA) if (bA is not None and need[2]) else None
         dwS = _wgrad(ctx.ws[2], pa, dd, gS, need[5])
-        dbS = _bias_grad(dd, gS.Cout) if need[6] else None
+        dbS = _bias_grad(dd, bS) if (bS is not None and need[6]) else None
         da = None
         if need[0]:
             da = ops.conv_dgrad(dyA, wbA, gA, a.shape[1], a.shape[2])

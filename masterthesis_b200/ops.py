@@ -327,23 +327,22 @@ def _wgrad_launch(x, dy, g: ConvGeom, dw, accumulate, stream):
     N, Hin, Win, _ = x.shape
     L = _lib.lib()
     d = g.desc(N, Hin, Win)
-    if g.transposed:
-        n = g.kh * g.kw * g.Cin * g.Cout_s
-    elif g.window_pair:
+    if g.window_pair:
         n = L.mt_packed_conv_window_pair_elems(g.Cout, g.kh)
-    elif g.window:
-        n = g.kh * g.Cout * 64
     else:
-        n = g.kh * g.kw * g.Cout * g.Cin_s
-    packed = torch.zeros(n, dtype=torch.float32, device=x.device)
+        n = L.mt_packed_wgrad_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.transposed), int(g.window))
+    # split-K partial results, one slab per split (plain stores: no zero fill, no atomics), added in split
+    # order by the unpack kernel
+    splits = (L.mt_conv_transpose2d_wgrad_splits if g.transposed else L.mt_conv2d_wgrad_splits)(ctypes.byref(d))
+    packed = _T.empty(splits * n, dtype=torch.float32, device=x.device)
     fn = L.mt_conv_transpose2d_wgrad if g.transposed else L.mt_conv2d_wgrad
     with _timed("wgrad", g, N, Hin, Win):
-        check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), stream), "conv_wgrad")
+        check(fn(ctypes.byref(d), _p(x), _p(dy), _p(packed), splits, stream), "conv_wgrad")
     if g.window_pair:
-        check(L.mt_unpack_conv_window_pair_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, g.stride,
+        check(L.mt_unpack_conv_window_pair_wgrad(_p(packed), splits, g.Cout, g.Cin, g.kh, g.kw, g.stride,
                                                  int(accumulate), _p(dw), stream), "unpack_wgrad")
     else:
-        check(L.mt_unpack_conv_wgrad(_p(packed), g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
+        check(L.mt_unpack_conv_wgrad(_p(packed), splits, g.Cout, g.Cin, g.kh, g.kw, int(g.transposed),
                                      int(g.window), int(accumulate), _p(dw), stream), "unpack_wgrad")
     _count(2)
     return packed
@@ -480,15 +479,18 @@ def plane_stats(x):
 
 
 @_checked
-def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None, C_valid=None):
+def norm_finalize(stats, mode, HW, gb=None, ln_w=None, ln_b=None, C_valid=None, csum=False):
+    """-> (ss, mr) [, csum [N, C] fp32: the per-channel plane sums (kept for the bias gradient of a biased
+    convolution in front of a LayerNorm)]"""
     parts = stats.shape[1] if stats.dim() == 4 else 1      # per-tile partial sums of a fused conv
     N, C = stats.shape[0], stats.shape[-2]
     ss = _T.empty((N, C, 2), dtype=torch.float32, device=stats.device)
     mr = _T.empty_like(ss)
+    cs_ = _T.empty((N, C), dtype=torch.float32, device=stats.device) if csum else None
     check(_lib.lib().mt_norm_finalize(_p(stats), parts, NORM[mode], N, C, C_valid or C, HW, EPS, _p(gb), _p(ln_w), _p(ln_b),
-                                      _p(ss), _p(mr), _stream()), "norm_finalize")
+                                      _p(ss), _p(mr), _p(cs_), _stream()), "norm_finalize")
     _count()
-    return ss, mr
+    return (ss, mr, cs_) if csum else (ss, mr)
 
 
 @_checked
@@ -503,28 +505,49 @@ def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, 
 
 
 @_checked
-def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None, g_pad=0):
+def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None, g_pad=0, csum=None,
+             dln_into=None, dbias_into=None, want_dbias=False):
     """x dense [N,H,W,C]; g dense, or (g_pad > 0) the consumer's padded gradient buffer
     [N,H+2g_pad,W+2g_pad,C] that is folded (adjoint of the reflection border) on the fly.
-    Returns (dx, dgb | None, dln_w | None, dln_b | None)."""
+    LayerNorm affine gradients are added into `dln_into` = (weight.grad, bias.grad) when given, else
+    returned; the gradient of the bias of the convolution in front of a LayerNorm (`csum` from the forward
+    finalize) is added into `dbias_into` when given, returned when `want_dbias`.
+    Returns (dx, dgb | None, dln_w | None, dln_b | None, dbias | None)."""
     N, H, W, C = x.shape
     assert tuple(g.shape) == (N, H + 2 * g_pad, W + 2 * g_pad, C) and g.is_contiguous()
     L = _lib.lib()
     dev = x.device
-    sums = _T.empty((N, C, 2), dtype=torch.float32, device=dev)
-    check(L.mt_norm_bwd_reduce(_p(g), g_pad, _p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(sums),
+    Cv = C_valid or C
+    parts = L.mt_norm_bwd_parts(N, H, W, C, ACT[act], g_pad)
+    sums = _T.empty((N, parts, C, 2), dtype=torch.float32, device=dev)
+    check(L.mt_norm_bwd_reduce(_p(g), g_pad, _p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(sums), parts,
                                _stream()), "norm_bwd_reduce")
     coef = _T.empty((N, C, 3), dtype=torch.float32, device=dev)
     dgb = _T.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
-    dlw = torch.zeros(C_valid or C, dtype=torch.float32, device=dev) if (mode == "layer" and ln_w is not None) else None
-    dlb = torch.zeros(C_valid or C, dtype=torch.float32, device=dev) if dlw is not None else None
-    check(L.mt_norm_bwd_finalize(_p(sums), _p(mr), NORM[mode], N, C, C_valid or C, H * W, _p(gb), _p(ln_w), _p(coef),
-                                 _p(dgb), _p(dlw), _p(dlb), _stream()), "norm_bwd_finalize")
+    need_ln = mode == "layer" and ln_w is not None
+    need_db = mode == "layer" and csum is not None and (dbias_into is not None or want_dbias)
+    red = _T.empty((N, C, 2), dtype=torch.float32, device=dev) if (need_ln or need_db) else None
+    check(L.mt_norm_bwd_finalize(_p(sums), parts, _p(mr), NORM[mode], N, C, Cv, H * W, _p(gb), _p(ln_w), _p(coef),
+                                 _p(dgb), _p(red), _stream()), "norm_bwd_finalize")
+    dlw = dlb = dbias = None
+    if red is not None:
+        # the accumulating form needs every requested output to be a .grad buffer; otherwise fresh tensors
+        acc = (not need_ln or dln_into is not None) and (not need_db or dbias_into is not None)
+        if need_ln:
+            dlw, dlb = dln_into if acc else (_T.empty(Cv, dtype=torch.float32, device=dev),
+                                             _T.empty(Cv, dtype=torch.float32, device=dev))
+        if need_db:
+            dbias = dbias_into if acc else _T.empty(Cv, dtype=torch.float32, device=dev)
+        check(L.mt_norm_bwd_params(_p(red), _p(coef), _p(csum), N, C, Cv, H * W, _p(dlw), _p(dlb), _p(dbias),
+                                   int(acc), _stream()), "norm_bwd_params")
+        _count()
+        if acc:
+            dlw = dlb = dbias = None
     dx = _T.empty_like(x)
     check(L.mt_norm_bwd_apply(_p(g), g_pad, _p(x), _p(ss), _p(coef), N, H, W, C, ACT[act], LRELU_SLOPE,
                               _p(dx), _stream()), "norm_bwd_apply")
     _count(3)
-    return dx, dgb, dlw, dlb
+    return dx, dgb, dlw, dlb, dbias
 
 
 @_checked
@@ -648,9 +671,12 @@ def rgb_head_bwd(dy, y, x, w, Co):
     N, H, W, C = x.shape
     dx = _T.empty_like(x)
     dw = _T.empty((C, Co), dtype=torch.float32, device=x.device)
-    check(_lib.lib().mt_rgb_head_bwd(_p(dy.contiguous()), _p(y), _p(x), _p(w), N, H * W, C, Co, _p(dx),
-                                     _p(dw), _stream()), "rgb_head_bwd")
-    _count()
+    L = _lib.lib()
+    parts = L.mt_rgb_head_bwd_parts(N, H * W, C)
+    scratch = _T.empty((parts, C, 4), dtype=torch.float32, device=x.device)
+    check(L.mt_rgb_head_bwd(_p(dy.contiguous()), _p(y), _p(x), _p(w), N, H * W, C, Co, _p(dx),
+                            _p(dw), _p(scratch), parts, _stream()), "rgb_head_bwd")
+    _count(2)
     return dx, dw
 
 
@@ -658,9 +684,12 @@ def rgb_head_bwd(dy, y, x, w, Co):
 def sumsq_interior(x_pad, pad):
     N, Hp, Wp, C = x_pad.shape
     out = _T.empty((), dtype=torch.float32, device=x_pad.device)
-    check(_lib.lib().mt_sumsq_interior(_p(x_pad), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _p(out),
-                                       _stream()), "sumsq_interior")
-    _count()
+    L = _lib.lib()
+    parts = L.mt_sumsq_interior_parts(N, Hp - 2 * pad, Wp - 2 * pad, C)
+    scratch = _T.empty(parts, dtype=torch.float32, device=x_pad.device)
+    check(L.mt_sumsq_interior(_p(x_pad), N, Hp - 2 * pad, Wp - 2 * pad, C, pad, _p(out), _p(scratch), parts,
+                              _stream()), "sumsq_interior")
+    _count(2)
     return out
 
 
@@ -675,6 +704,15 @@ def scale_interior(x_pad, scale, pad):
     return dx
 
 
-def channel_sum(dy):
-    """sum over (n, h, w) of a dense bf16 tensor -> fp32 [C] (bias gradients)."""
-    return plane_stats(dy)[..., 0].sum((0, 1))
+def bias_grad(dy, C, into=None):
+    """sum over (n, h, w) of a dense bf16 tensor [N,H,W,C_s] -> its first C channels (the bias gradient of
+    the convolution that produced the tensor dy is the gradient of, blocks.py:36): per-chunk column sums
+    (mt_plane_stats) added in a fixed order.  `into` (the bias's .grad, fp32 [C]): += in place, returns
+    None; else a fresh fp32 [C] tensor."""
+    st = plane_stats(dy)
+    N, parts, Cs, _ = st.shape
+    out = into if into is not None else _T.empty(C, dtype=torch.float32, device=dy.device)
+    check(_lib.lib().mt_colsum_into(_p(st), N * parts, Cs, C, _p(out), int(into is not None), _stream()),
+          "colsum_into")
+    _count()
+    return None if into is not None else out

@@ -130,11 +130,14 @@ class FlatAdam(torch.optim.Optimizer):
             _lib.check(L.mt_adam_flat_dev(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
                                           f['v'].data_ptr(), f['n'], slot, ops._stream()), "mt_adam_flat_dev")
         else:
-            g0 = self.param_groups[0]
-            _lib.check(L.mt_adam_flat(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
-                                      f['v'].data_ptr(), f['n'], float(g0['lr']), g0['betas'][0],
-                                      g0['betas'][1], g0['eps'], g0['weight_decay'], self._step_count(),
-                                      float(self.grad_scale), ops._stream()), "mt_adam_flat")
+            # same kernel and the same host-computed scalars as the captured form, so that an eager
+            # iteration and a graph replay are bit-identical (a pageable H2D copy: ordered on the stream
+            # and staged before it returns)
+            hyper_dev = torch.tensor(hyper + (0.0,), dtype=torch.float32).to(f['p'].device)
+            _lib.check(L.mt_adam_flat_dev(f['p'].data_ptr(), f['g'].data_ptr(), f['m'].data_ptr(),
+                                          f['v'].data_ptr(), f['n'], hyper_dev.data_ptr(), ops._stream()),
+                       "mt_adam_flat_dev")
+            self._hyper_keep = hyper_dev
         ops._count()
         return None
 

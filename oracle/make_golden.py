@@ -195,10 +195,13 @@ def nets_base_case(name, dim, size, N, nd=4, latent=8, seed=3, sub=1):
     print(name, {k: float(v.abs().max()) for k, v in out.items() if not k.startswith('grad')})
 
 
-def step_case(name, dim, size, B, iters=2, nd=4, seed=2, model='AdaINModel', **flags):
-    """Model.optimize_parameters — the losses per iteration and a checksum of every parameter tensor
-    after `iters` iterations.  model / flags select BaseModel, --concat --reparam, --ms_dis,
-    --use_dis_content (losses of a content-discriminator iteration: `loss_dc` only)."""
+def step_case(name, dim, size, B, iters=2, nd=4, seed=2, model='AdaINModel', gsamp=128, **flags):
+    """Model.optimize_parameters — the losses per iteration, a checksum of every parameter tensor
+    after `iters` iterations, and a strided sample (`gsamp` elements per parameter tensor,
+    oracle.synth.grad_sample) of the gradients the reference hands to every optimizer.step() of the
+    FIRST iteration (`gsample.<i>.<net>` in call order; index in meta['gsample']).  model / flags
+    select BaseModel, --concat --reparam, --ms_dis, --use_dis_content (losses of a
+    content-discriminator iteration: `loss_dc` only)."""
     models = ref_import.import_reference()
     draws = synth.Draws(seed)
     patch_rng(models, draws)
@@ -214,9 +217,19 @@ def step_case(name, dim, size, B, iters=2, nd=4, seed=2, model='AdaINModel', **f
     batch = {'x1': synth.synth_images(B, size, seed, 'x1'), 'x2': synth.synth_images(B, size, seed, 'x2'),
              'y1': synth.synth_onehot(B, nd, seed, 'y'), 'y2': synth.synth_onehot(B, nd, seed, 'y', offset=1)}
     out = {}
+    gs_index, recording = [], [True]
+    for n in m.optimizer:
+        def rec(orig=m.optimizer[n].step, n=n):
+            if recording[0]:
+                idx, flat = synth.grad_sample(m.model[n].named_parameters(), gsamp)
+                out[f'gsample.{len(gs_index)}.{n}'] = flat
+                gs_index.append([n, {k: list(v) for k, v in idx.items()}])
+            return orig()
+        m.optimizer[n].step = rec
     for it in range(iters):
         m.set_inputs(batch)
         m.optimize_parameters(it)
+        recording[0] = False
         for k, v in m.loss.items():
             out[f'loss.{it}.{k}'] = torch.tensor(v)
         if getattr(m, 'loss_dc', None) is not None:
@@ -226,6 +239,7 @@ def step_case(name, dim, size, B, iters=2, nd=4, seed=2, model='AdaINModel', **f
             v = v.detach().float()
             out[f'param.{n}.{k}'] = torch.stack([v.sum(), v.abs().sum(), (v * v).sum()])
     meta['draws'] = [list(s) for s in draws.log]
+    meta['gsample'], meta['gsamp'] = gs_index, gsamp
     np.savez_compressed(os.path.join(OUT, name + '.npz'), meta=json.dumps(meta),
                         **{k: v.numpy().astype(np.float64 if k.startswith('param') else np.float32)
                            for k, v in out.items()})
@@ -241,6 +255,8 @@ if __name__ == '__main__':
         nets_case('nets_dim16_64', dim=16, size=64, N=2)
         nets_case('nets_dim64_256', dim=64, size=256, N=1, sub=8)
         step_case('step_dim8_64', dim=8, size=64, B=1)
+    if 'bench' in which:    # the benchmarked geometry (BASELINE config 3): dim 64, 256x256, batch 8
+        step_case('step_dim64_256_B8', dim=64, size=256, B=8, gsamp=512)
     if 'gan' in which:      # adversarial-loss variants (loss.py:41-64, adain_model.py:206-215,277-302,359-376)
         step_case('step_ragan_dim8_64', dim=8, size=64, B=1, use_ragan=True)
         step_case('step_hinge_dim8_64', dim=8, size=64, B=1, gan_mode='hinge')

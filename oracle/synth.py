@@ -58,3 +58,21 @@ class Draws:
         self.i += 1
         self.log.append(tuple(shape))
         return t
+
+
+def grad_sample(named_params, per_tensor=128):
+    """Strided sample of the gradients of `named_params` ((key, parameter) pairs in state_dict order):
+    up to `per_tensor` elements of every parameter tensor that has a gradient -> ({key: (offset, count)},
+    flat fp32 tensor).  The reference-side recorder (oracle/make_golden.py) and the CUDA-side checks
+    (tests/model_cases.py) use the same rule, so the committed samples compare element for element."""
+    index, parts, off = {}, [], 0
+    for k, p in named_params:
+        g = getattr(p, 'grad', None)
+        if g is None:
+            continue
+        g = g.detach().float().flatten().cpu()
+        g = g[:: max(1, g.numel() // per_tensor)][:per_tensor]
+        index[k] = (off, g.numel())
+        parts.append(g)
+        off += g.numel()
+    return index, (torch.cat(parts) if parts else torch.zeros(0))

@@ -127,8 +127,9 @@ def norm_case(mode, N, C, H, W, act, residual=False, noise=False, seed=0):
 
     xn = to_nhwc(x)
     stats = ops.plane_stats(xn)
-    ss, mr = ops.norm_finalize(stats, mode, H * W, None if gb is None else gb.detach(),
-                               None if lw is None else lw.detach(), None if lb is None else lb.detach())
+    ss, mr, csum = ops.norm_finalize(stats, mode, H * W, None if gb is None else gb.detach(),
+                                     None if lw is None else lw.detach(), None if lb is None else lb.detach(),
+                                     csum=True)
     res_pad = None
     if residual:
         res_pad = to_nhwc(F.pad(res_t, (1, 1, 1, 1), mode="reflect"))
@@ -137,10 +138,19 @@ def norm_case(mode, N, C, H, W, act, residual=False, noise=False, seed=0):
                              out_p=1)          # writes the reflection border too
     out_ref = F.pad(y_ref.detach(), (1, 1, 1, 1), mode="reflect")
     r = {"fwd": rel(from_nhwc(out, C), out_ref)}
-    dx, dgb, dlw, dlb = ops.norm_bwd(to_nhwc(g), xn, ss, mr, mode, act=act,
-                                     gb=None if gb is None else gb.detach(),
-                                     ln_w=None if lw is None else lw.detach())
+    dx, dgb, dlw, dlb, dbias = ops.norm_bwd(to_nhwc(g), xn, ss, mr, mode, act=act,
+                                            gb=None if gb is None else gb.detach(),
+                                            ln_w=None if lw is None else lw.detach(),
+                                            csum=csum if mode == "layer" else None, want_dbias=mode == "layer")
     r["dx"] = rel(from_nhwc(dx, C), x_ref.grad)
+    if mode == "layer":
+        # gradient of a bias added in front of the norm = sum_{n,h,w} dx, from the saved plane sums
+        r["dbias"] = rel(dbias, x_ref.grad.sum((0, 2, 3)))
+        # accumulate-into form: += into existing buffers
+        acc_w, acc_b, acc_d = torch.ones_like(dlw), torch.ones_like(dlb), torch.ones_like(dbias)
+        ops.norm_bwd(to_nhwc(g), xn, ss, mr, mode, act=act, ln_w=lw.detach(), csum=csum,
+                     dln_into=(acc_w, acc_b), dbias_into=acc_d)
+        r["acc_into"] = max(rel(acc_w - 1, dlw), rel(acc_b - 1, dlb), rel(acc_d - 1, dbias))
     if mode == "adain":
         r["dgb"] = rel(dgb, gb.grad)
     if mode == "layer":
@@ -230,7 +240,130 @@ def mask_mul_case(N, C, H, W, seed=0):
     return {"exact": 0.0 if torch.equal(y, x * m) else 1.0}
 
 
+def misc_case(N=3, C=72, H=12, W=20, p=1, seed=0):
+    """AvgPool2d(2), the DownResnetBlock sum + LeakyReLU, AdaptiveAvgPool2d(1), the RGB head, the
+    content regulariser and the fused Adam step, each against plain PyTorch fp32 (blocks.py:113,118-119,
+    networks.py:124,248-251, adain_model.py:396-399,58-61)."""
+    torch.manual_seed(seed)
+    r = {}
+    x = bf(torch.randn(N, C, H, W, device=DEV))
+    xp = to_nhwc(F.pad(x, (p,) * 4, mode="reflect"))
+    # avgpool2 forward / backward-add
+    r["avgpool2"] = rel(from_nhwc(ops.avgpool2_fwd(xp, p), C), F.avg_pool2d(x, 2))
+    dpo = bf(torch.randn(N, C, H // 2, W // 2, device=DEV))
+    base = bf(torch.randn(N, C, H + 2 * p, W + 2 * p, device=DEV))
+    acc = to_nhwc(base).clone()
+    ops.avgpool2_bwd_add_(to_nhwc(dpo), acc, p)
+    ref = base.clone()
+    ref[:, :, p:H + p, p:W + p] += 0.25 * F.interpolate(dpo, scale_factor=2, mode="nearest")
+    r["avgpool2_bwd_add"] = rel(from_nhwc(acc, C), bf(ref))
+    # pool_add_act forward / backward
+    c_ = bf(torch.randn(N, C, H, W, device=DEV)).requires_grad_(True)
+    d_ = bf(torch.randn(N, C, H // 2, W // 2, device=DEV)).requires_grad_(True)
+    y_ref = F.leaky_relu(F.avg_pool2d(c_, 2) + d_, 0.01)
+    yp_ref = F.pad(y_ref, (p,) * 4, mode="reflect")
+    g = bf(torch.randn_like(yp_ref))
+    yp_ref.backward(g)
+    out = ops.pool_add_act_fwd(to_nhwc(c_.detach()), to_nhwc(d_.detach()), "lrelu", p)
+    ops.reflect_border_(out, p)
+    r["pool_add_act_fwd"] = rel(from_nhwc(out, C), yp_ref.detach())
+    dd, dc = ops.pool_add_act_bwd(to_nhwc(g), out, p, "lrelu")
+    r["pool_add_act_dd"] = rel(from_nhwc(dd, C), d_.grad)
+    r["pool_add_act_dc"] = rel(from_nhwc(dc, C), c_.grad)
+    # global average pooling
+    r["gap_fwd"] = rel(ops.gap_fwd(to_nhwc(x))[:, :C], x.mean((2, 3)))
+    dg = torch.randn(N, ops.cs(C), device=DEV)
+    r["gap_bwd"] = rel(from_nhwc(ops.gap_bwd(dg, H, W), C), bf(dg[:, :C, None, None].expand(N, C, H, W) / (H * W)))
+    # RGB head
+    xr = bf(torch.randn(N, C, H, W, device=DEV)).requires_grad_(True)
+    w = (torch.randn(C, 3, device=DEV) * 0.2).requires_grad_(True)
+    y_ref = torch.tanh(torch.einsum("nchw,co->nohw", xr, w))
+    dy = torch.randn_like(y_ref)
+    y_ref.backward(dy)
+    w2 = torch.cat((w.detach(), w.new_zeros(ops.cs(C) - C, 3))).contiguous()
+    y = ops.rgb_head_fwd(to_nhwc(xr.detach()), w2, 3)
+    r["rgb_head_fwd"] = rel(y, y_ref.detach())
+    dx, dw = ops.rgb_head_bwd(dy, y, to_nhwc(xr.detach()), w2, 3)
+    r["rgb_head_dx"] = rel(from_nhwc(dx, C), xr.grad)
+    r["rgb_head_dw"] = rel(dw[:C], w.grad)
+    # bias gradient = column sums of a dense gradient tensor
+    db = ops.bias_grad(to_nhwc(x), C)
+    r["bias_grad"] = rel(db, x.sum((0, 2, 3)))
+    acc = torch.full((C,), 2.0, device=DEV)
+    ops.bias_grad(to_nhwc(x), C, into=acc)
+    r["bias_grad_into"] = rel(acc - 2.0, x.sum((0, 2, 3)))
+    # content regulariser
+    r["sumsq_interior"] = rel(ops.sumsq_interior(xp, p), (x * x).sum())
+    sc = torch.tensor(0.37, device=DEV)
+    dxp = ops.scale_interior(xp, sc, p)
+    ref = torch.zeros_like(F.pad(x, (p,) * 4))
+    ref[:, :, p:H + p, p:W + p] = 0.37 * x
+    r["scale_interior"] = rel(from_nhwc(dxp, C), ref)
+    return r
+
+
+def adam_case(n=10007, steps=3, seed=0):
+    """FlatAdam (mt_adam_flat) vs torch.optim.Adam with coupled weight decay (adain_model.py:58-61)."""
+    from masterthesis_b200.optim import FlatAdam
+    torch.manual_seed(seed)
+    p0 = torch.randn(n, device=DEV)
+    a = [torch.nn.Parameter(p0[:5000].clone().view(50, 100)), torch.nn.Parameter(p0[5000:].clone())]
+    b = [torch.nn.Parameter(p0[:5000].clone().view(50, 100)), torch.nn.Parameter(p0[5000:].clone())]
+    oa = FlatAdam(a, lr=1e-3, betas=(0.5, 0.999), weight_decay=1e-4)
+    ob = torch.optim.Adam(b, lr=1e-3, betas=(0.5, 0.999), weight_decay=1e-4)
+    for s in range(steps):
+        oa.zero_grad(); ob.zero_grad()
+        for pa, pb in zip(a, b):
+            g = torch.randn_like(pb) * (0.1 + s)
+            pa.grad.copy_(g); pb.grad = g.clone()
+        oa.step(); ob.step()
+    torch.cuda.synchronize()
+    # max |delta| relative to the total update (the weights themselves barely move in 3 steps)
+    num = max((pa.detach() - pb.detach()).abs().max().item() for pa, pb in zip(a, b))
+    den = max((pb.detach().flatten() - q).abs().max().item() for pb, q in zip(b, (p0[:5000], p0[5000:])))
+    return {"adam_update": num / den}
+
+
+def big_mean_norm_case(seed=0):
+    """InstanceNorm on planes whose mean is ~1e2 standard deviations away from zero (a conv bias in front
+    of InstanceNorm, networks.py:29-33): bounds the E[x^2] - E[x]^2 formulation against torch's two-pass
+    variance.  Inputs are bf16, so |mean| / std is limited to what bf16 can resolve (~2^7)."""
+    torch.manual_seed(seed)
+    N, C, H, W = 2, 64, 32, 32
+    x = bf(torch.randn(N, C, H, W, device=DEV) + 100.0 * torch.randn(N, C, 1, 1, device=DEV).sign())
+    xn = to_nhwc(x)
+    ss, mr = ops.norm_finalize(ops.plane_stats(xn), "instance", H * W)
+    out = ops.affine_act_fwd(xn, ss)
+    return {"fwd": rel(from_nhwc(out, C), F.instance_norm(x))}
+
+
 CASES = {
+    "misc_ops": misc_case,
+    "misc_ops_c256": lambda: misc_case(2, 256, 16, 16),
+    "adam_flat": adam_case,
+    "in_big_mean": big_mean_norm_case,
+    # ---- the launches of the benchmarked configuration (BASELINE config 3: dim 64, 256x256, batch 8):
+    # 16 / 32 images per call, i.e. 3.5 - 7 work items per CTA pair of the persistent conv kernel (TMEM
+    # double buffer and ring phases wrap across items) and split-K weight gradients over 16 / 32 images
+    "hot_n16": lambda: conv_case(16, 256, 256, 64, 64, 3, 1, 1, bias=False),
+    "hot_n32": lambda: conv_case(32, 256, 256, 64, 64, 3, 1, 1, bias=False),
+    "hot_stats_n16": lambda: fused_stats_case(16, 256, 256, 64, 64, bias=False),
+    "hot_stats_n32": lambda: fused_stats_case(32, 256, 256, 64, 64, bias=False),
+    "convT_256_128_n16": lambda: convT_case(16, 256, 128, 64, 64),
+    "convT_128_64_n16": lambda: convT_case(16, 128, 64, 128, 128),
+    "convT_128_64_n32": lambda: convT_case(32, 128, 64, 128, 128),
+    "stem7x7_n16": lambda: conv_case(16, 3, 64, 256, 256, 7, 1, 3, stem=True),
+    "stem4x4_s2_n16": lambda: conv_case(16, 7, 64, 256, 256, 4, 2, 1, stem=True),
+    "stem3x3_s2_n32": lambda: conv_case(32, 3, 64, 256, 256, 3, 2, 1, stem=True),
+    "down1_n16": lambda: conv_case(16, 64, 128, 256, 256, 3, 2, 1),
+    "down2_n16": lambda: conv_case(16, 128, 256, 128, 128, 3, 2, 1),
+    "dis_l2_n32": lambda: conv_case(32, 64, 128, 128, 128, 3, 2, 1, act="lrelu", out_pad=1),
+    "dis_l5_n32": lambda: conv_case(32, 512, 1024, 16, 16, 3, 2, 1),
+    "dis_l6_n32": lambda: conv_case(32, 1024, 1024, 8, 8, 3, 2, 1),
+    "es_conv_n16": lambda: conv_case(16, 64, 128, 128, 128, 3, 1, 1),
+    "adain_res_n32": lambda: norm_case("adain", 32, 256, 64, 64, None, residual=True),
+    "in_relu_n16": lambda: norm_case("instance", 16, 256, 64, 64, "relu"),
+    "ln_relu_n32": lambda: norm_case("layer", 32, 64, 256, 256, "relu"),
     # optional variants (SURVEY.md 8f-4): nearest up-sampling tail, 7x7 zero-padded image head, dropout
     "upsample2": lambda: upsample_case(2, 40, 12, 20),
     "mask_mul": lambda: mask_mul_case(2, 24, 16, 16),

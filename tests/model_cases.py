@@ -29,6 +29,39 @@ def cos(a, b):
     return (torch.dot(a, b) / (a.norm() * b.norm()).clamp_min(1e-30)).item()
 
 
+def loss_err(mine, ref):
+    """relative error of one loss scalar: |a - b| / |b| (max relative error <= 1e-2 on each
+    of the loss scalars); the floor only guards a reference value that is exactly zero"""
+    err = abs(mine - ref) / max(abs(ref), 1e-6)
+    return err if err == err else float('inf')
+
+
+def grad_sample_vs_golden(meta, gold, i, net, named_params):
+    """Our gradients at optimizer step `i` of the first iteration against the strided sample the
+    REFERENCE recorded at the same step (oracle/make_golden.py: gsample.<i>.<net>): cosine over the whole
+    sample, and the worst per-tensor cosine over the tensors that carry signal (rms >= 1e-3 of the
+    largest tensor's: a conv bias in front of InstanceNorm has an exactly-zero gradient, the reference
+    records rounding noise for it)."""
+    n_ref, index = meta['gsample'][i]
+    assert n_ref == net, (i, n_ref, net)
+    ref = gold[f'gsample.{i}.{net}'].double()
+    idx, mine = synth.grad_sample(named_params, meta['gsamp'])
+    mine = mine.double()
+    a, b, per = [], [], {}
+    for k, (off, cnt) in index.items():
+        if k not in idx:
+            continue
+        o2, c2 = idx[k]
+        assert c2 == cnt, (k, c2, cnt)
+        a.append(mine[o2:o2 + c2]); b.append(ref[off:off + cnt])
+        per[k] = (a[-1], b[-1])
+    rms = {k: float(v[1].pow(2).mean().sqrt()) for k, v in per.items()}
+    top = max(rms.values())
+    sig = [k for k in per if rms[k] >= 1e-3 * top]
+    worst = min(sig, key=lambda k: cos(*per[k]))
+    return cos(torch.cat(a), torch.cat(b)), cos(*per[worst]), worst
+
+
 def load_gold(name):
     z = np.load(os.path.join(GOLD, name + '.npz'))
     return json.loads(str(z['meta'])), {k: torch.from_numpy(z[k]) for k in z.files if k != 'meta'}
@@ -129,14 +162,19 @@ def step_vs_golden(name='step_dim8_64'):
     odraw_src = synth.Draws(seed)
     odraw = lambda shape: odraw_src(shape).to(DEV)  # noqa: E731
 
-    mine_g, ref_g = [], []
+    mine_g, ref_g, vs_ref = [], [], []
     for n in m.optimizer:
         opt = m.optimizer[n]
         orig = opt.step
 
         def rec(orig=orig, n=n, opt=opt):
+            from masterthesis_b200 import ops
+            ops.join_side(all_streams=True)
+            i = len(mine_g)
             mine_g.append((n, {k: p.grad.detach().clone() for k, p in m.model[n].named_parameters()
                                if p.grad is not None}))
+            if 'gsample' in meta and i < len(meta['gsample']):
+                vs_ref.append((i, n) + grad_sample_vs_golden(meta, gold, i, n, m.model[n].named_parameters()))
             return orig()
         opt.step = rec
     for n in st.opt:
@@ -175,12 +213,15 @@ def step_vs_golden(name='step_dim8_64'):
             with emu.bf16_storage():
                 st_e.optimize_parameters(m.img.clone(), m.c_org.clone(), edraw)
         for k in m.loss:
-            ref = float(gold[f'loss.{it}.{k}'])
-            err = abs(m.loss[k] - ref) / max(1.0, abs(ref))
-            r[f'loss_it{it}.{k}'] = err if err == err else float('inf')
+            r[f'loss_it{it}.{k}'] = loss_err(m.loss[k], float(gold[f'loss.{it}.{k}']))
     assert [list(s) for s in m.rng.log] == meta['draws'], "RNG call order differs from the reference"
+    # gradients handed to the optimizers in the first iteration vs the REFERENCE's recorded sample
+    for i, n, c_all, c_worst, worst in vs_ref:
+        r[f'cosref_step{i}_{n}'] = c_all
+        r[f'cosrefmin_step{i}_{n}'] = c_worst
+    r['_worst_tensors'] = {f'step{i}_{n}': w for i, n, _, _, w in vs_ref}
     # gradient cosine per (step point, net): first iteration only (identical weights there)
-    for i, ((n1, g1), (n2, g2)) in enumerate(zip(mine_g[:5], ref_g[:5])):
+    for i, ((n1, g1), (n2, g2)) in enumerate(zip(mine_g[:7], ref_g[:7])):
         assert n1 == n2
         a = torch.cat([g1[k].flatten() for k in g2 if k in g1])
         bb = torch.cat([g2[k].flatten() for k in g2 if k in g1])
@@ -190,6 +231,38 @@ def step_vs_golden(name='step_dim8_64'):
         if not (torch.isfinite(a).all() and torch.isfinite(bb).all()):
             r[f'nonfinite_step{i}_{n1}'] = float((~torch.isfinite(a)).sum() * 1000 + (~torch.isfinite(bb)).sum())
         # discriminator phases in the G steps skip D/Es grads by design; every key of ours must exist in ref
+    return r
+
+
+def step_losses_vs_golden(name='step_dim64_256_B8', iters=1):
+    """Light version of step_vs_golden (no oracle twins): `iters` iterations of optimize_parameters on the
+    CUDA path with the replayed draws vs the REFERENCE's recorded losses, plus the gradients of the first
+    iteration's optimizer steps vs the reference's recorded samples.  Used by __graft_entry__.smoke()."""
+    meta, gold = load_gold(name)
+    seed, B, nd, size, dim = meta['seed'], meta['B'], meta['nd'], meta['size'], meta['dim']
+    m, _ = make_model(dim, size, B, nd, seed, meta['shapes'], model=meta['model'], **meta['flags'])
+    m.rng = synth.Draws(seed)
+    vs_ref = []
+    for n in m.optimizer:
+        opt = m.optimizer[n]
+
+        def rec(orig=opt.step, n=n):
+            from masterthesis_b200 import ops
+            ops.join_side(all_streams=True)
+            i = len(vs_ref)
+            if i < len(meta.get('gsample', [])):
+                vs_ref.append((i, n) + grad_sample_vs_golden(meta, gold, i, n, m.model[n].named_parameters()))
+            return orig()
+        opt.step = rec
+    b = batch(B, size, nd, seed)
+    r = {}
+    for it in range(iters):
+        m.set_inputs(b)
+        m.optimize_parameters(it)
+        for k in m.loss:
+            r[f'loss_it{it}.{k}'] = loss_err(m.loss[k], float(gold[f'loss.{it}.{k}']))
+    for i, n, c_all, c_worst, worst in vs_ref:
+        r[f'cosref_step{i}_{n}'] = c_all
     return r
 
 
@@ -320,6 +393,18 @@ def flag_step_vs_golden(name):
     m.rng = synth.Draws(seed)
     b = batch(B, size, nd, seed)
     r = {}
+    vs_ref = []
+    for n in m.optimizer:
+        opt = m.optimizer[n]
+
+        def rec(orig=opt.step, n=n):
+            from masterthesis_b200 import ops
+            ops.join_side(all_streams=True)
+            i = len(vs_ref)
+            if i < len(meta.get('gsample', [])):
+                vs_ref.append((i, n) + grad_sample_vs_golden(meta, gold, i, n, m.model[n].named_parameters()))
+            return orig()
+        opt.step = rec
     for it in range(meta['iters']):
         m.set_inputs(b)
         m.optimize_parameters(it)
@@ -327,11 +412,11 @@ def flag_step_vs_golden(name):
         if getattr(m, 'loss_dc', None) is not None:
             mine['loss_dc'] = m.loss_dc
         for k, v in mine.items():
-            ref = float(gold[f'loss.{it}.{k}'])
-            err = abs(v - ref) / max(1.0, abs(ref))
-            r[f'loss_it{it}.{k}'] = err if err == err else float('inf')
+            r[f'loss_it{it}.{k}'] = loss_err(v, float(gold[f'loss.{it}.{k}']))
         assert set(mine) == {k.split('.', 2)[2] for k in gold if k.startswith(f'loss.{it}.')}, (it, sorted(mine))
     assert [list(s_) for s_ in m.rng.log] == meta['draws'], "RNG call order differs from the reference"
+    for i, n, c_all, c_worst, worst in vs_ref:
+        r[f'cosref_step{i}_{n}'] = c_all
     return r
 
 
@@ -353,7 +438,7 @@ def base_default_step_vs_oracle(dim=8, size=64, B=1, nd=4, seed=4, iters=2):
         ref = st.optimize_parameters(m.img.clone(), m.c_org.clone(), odraw)
         assert set(ref) == set(m.loss)
         for k in ref:
-            r[f'loss_it{it}.{k}'] = abs(m.loss[k] - ref[k]) / max(1.0, abs(ref[k]))
+            r[f'loss_it{it}.{k}'] = loss_err(m.loss[k], ref[k])
     return r
 
 
@@ -430,6 +515,40 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
     return r
 
 
+def determinism(dim=64, size=256, B=8, nd=4, seed=3, iters=3):
+    """Reproducibility of the whole training iteration: two eager runs and one CUDA-graph run of the same
+    `iters` iterations (same weights, batch and torch seed) must agree BIT FOR BIT in every loss and every
+    parameter — the statistics, the norm-backward sums and the split-K weight gradients are fixed-order
+    sums (no atomics), and the captured iteration launches the same kernels as the eager one.
+    Returns the number of differing values."""
+    out = {}
+    for mode in ('eager', 'eager2', 'graph'):
+        m, _ = make_model(dim, size, B, nd, seed)
+        m.use_graph = mode == 'graph'
+        m.graph_warmup = 1
+        b = {k: v.to(DEV) for k, v in batch(B, size, nd, seed).items()}
+        torch.manual_seed(77)
+        hist = []
+        for it in range(iters):
+            for opt in m.optimizer.values():
+                opt.param_groups[0]['lr'] = 1e-4 * (1.0 - 0.05 * it)
+            m.set_inputs(b)
+            m.optimize_parameters(it)
+            hist.append(dict(m.loss))
+        torch.cuda.synchronize()
+        out[mode] = (hist, {n: torch.cat([p.detach().flatten() for p in m.model[n].parameters()]).clone()
+                            for n in m.model}, m._graph is not None)
+        del m
+    assert out['graph'][2] and not out['eager'][2]
+    r = {}
+    for other in ('eager2', 'graph'):
+        r[f'{other}.loss_mismatches'] = float(sum(
+            a[k] != b_[k] for a, b_ in zip(out['eager'][0], out[other][0]) for k in a))
+        r[f'{other}.param_mismatches'] = float(sum(
+            int((out['eager'][1][n] != out[other][1][n]).sum()) for n in out['eager'][1]))
+    return r
+
+
 def sampling_graph_vs_eager(dim=16, size=64, N=2, nd=4, seed=9):
     """forward_random in test mode: the captured sampling graph (third call on) vs eager launches of
     the same model, on inputs that change from call to call (static input buffers must be refreshed)."""
@@ -472,4 +591,11 @@ CASES = {
     'nets_dim64_256': lambda: nets_vs_golden('nets_dim64_256'),
     'step_dim8_64': step_vs_golden,
     'sampling_256': sampling_vs_oracle,
+    # the benchmarked geometry (BASELINE config 3: dim 64, 256x256, batch 8 -> 16 / 32 images per call)
+    'step_dim64_256_B8': lambda: step_vs_golden('step_dim64_256_B8'),
+    'step_dim64_256_B8_light': step_losses_vs_golden,
+    'graph_vs_eager_bench': lambda: graph_vs_eager(dim=64, size=256, B=8, iters=5),
+    'sampling_256_n8': lambda: sampling_vs_oracle(N=8),
+    'determinism_bench': determinism,
+    'determinism_small': lambda: determinism(dim=8, size=64, B=2, iters=4),
 }

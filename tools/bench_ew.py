@@ -22,12 +22,13 @@ def timeit(name, fn, mbytes, reps=20, cold=True):
 stats = ops.plane_stats(x)
 ss, mr = ops.norm_finalize(stats, 'instance', H * W)
 L = ops._lib.lib()
-sums = torch.empty(N, C, 2, device='cuda'); coef = torch.randn(N, C, 3, device='cuda'); dx = torch.empty_like(x)
+bparts = L.mt_norm_bwd_parts(N, H, W, C, 1, 1)
+sums = torch.empty(N, bparts, C, 2, device='cuda'); coef = torch.randn(N, C, 3, device='cuda'); dx = torch.empty_like(x)
 for cold in (True, False):
     timeit("plane_stats", lambda: ops.plane_stats(x), MB, cold=cold)
     timeit("affine_act_fwd(+res,pad)", lambda: ops.affine_act_fwd(x, ss, act='relu', res_pad=xp, res_p=1, out_p=1), 3 * MB, cold=cold)
     timeit("affine_act_fwd", lambda: ops.affine_act_fwd(x, ss, act='relu', out_p=1), 2 * MB, cold=cold)
-    timeit("norm_bwd_reduce(fold)", lambda: ops.check(L.mt_norm_bwd_reduce(gp.data_ptr(), 1, x.data_ptr(), ss.data_ptr(), N, H, W, C, 1, 0.01, sums.data_ptr(), ops._stream()), "r"), 2 * MB, cold=cold)
+    timeit("norm_bwd_reduce(fold)", lambda: ops.check(L.mt_norm_bwd_reduce(gp.data_ptr(), 1, x.data_ptr(), ss.data_ptr(), N, H, W, C, 1, 0.01, sums.data_ptr(), bparts, ops._stream()), "r"), 2 * MB, cold=cold)
     timeit("norm_bwd_apply(fold)", lambda: ops.check(L.mt_norm_bwd_apply(gp.data_ptr(), 1, x.data_ptr(), ss.data_ptr(), coef.data_ptr(), N, H, W, C, 1, 0.01, dx.data_ptr(), ops._stream()), "a"), 3 * MB, cold=cold)
     timeit("reflect_fold", lambda: ops.reflect_fold(gp, 1), 2 * MB, cold=cold)
     timeit("torch copy (ref)", lambda: dx.copy_(x), 2 * MB, cold=cold)

@@ -15,7 +15,7 @@ if len(sys.argv) >= 3 and sys.argv[1] == "--one":
     CASES = dict(CASES); CASES.update(MCASES)
     res = CASES[sys.argv[2]]()
     torch.cuda.synchronize()
-    print("RESULT " + json.dumps(res))
+    print("RESULT " + json.dumps(res, default=str))
     sys.exit(0)
 
 from tests.kernel_cases import CASES  # noqa: E402
@@ -26,7 +26,7 @@ names = sys.argv[1:] or list(CASES)
 for n in names:
     try:
         p = subprocess.run([sys.executable, __file__, "--one", n], capture_output=True, text=True,
-                           timeout=180, cwd=ROOT)
+                           timeout=1200, cwd=ROOT)
         line = [l for l in p.stdout.splitlines() if l.startswith("RESULT ")]
         if line:
             print(f"{n:24s} {line[0][7:]}", flush=True)

@@ -48,13 +48,14 @@ def run(tag, N, H, W, C, mode):
     lb = torch.randn(C, device='cuda') if mode == 'layer' else None
     ss, mr = ops.norm_finalize(stats, mode, H * W, gb, lw, lb)
     L = ops._lib.lib()
-    sums = torch.empty(N, C, 2, device='cuda')
+    bparts = L.mt_norm_bwd_parts(N, H, W, C, 1, 0)
+    sums = torch.empty(N, bparts, C, 2, device='cuda')
     coef = torch.randn(N, C, 3, device='cuda') * 0.1
     dx = torch.empty_like(x)
     out = torch.empty_like(x)
     timed(f"{tag} affine+relu fwd", lambda: ops.affine_act_fwd(x, ss, act='relu', out=out), 2 * MB)
     timed(f"{tag} bwd reduce", lambda: ops.check(L.mt_norm_bwd_reduce(
-        g.data_ptr(), 0, x.data_ptr(), ss.data_ptr(), N, H, W, C, 1, 0.01, sums.data_ptr(), ops._stream()), "r"), 2 * MB)
+        g.data_ptr(), 0, x.data_ptr(), ss.data_ptr(), N, H, W, C, 1, 0.01, sums.data_ptr(), bparts, ops._stream()), "r"), 2 * MB)
     timed(f"{tag} bwd apply", lambda: ops.check(L.mt_norm_bwd_apply(
         g.data_ptr(), 0, x.data_ptr(), ss.data_ptr(), coef.data_ptr(), N, H, W, C, 1, 0.01, dx.data_ptr(),
         ops._stream()), "a"), 3 * MB)
