@@ -115,6 +115,29 @@ class _timed:
         return False
 
 
+class _timed_bytes:
+    """the same for an HBM-bound kernel: (kind, label, algorithmic_bytes, start_event, end_event)"""
+
+    def __init__(self, kind, shape, nbytes):
+        self.on = PROFILE is not None
+        if self.on:
+            self.kind, self.nbytes = kind, float(nbytes)
+            self.label = "x".join(str(int(v)) for v in shape)
+
+    def __enter__(self):
+        if self.on:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *a):
+        if self.on:
+            self.e1.record()
+            PROFILE.append((self.kind, self.label, self.nbytes, self.e0, self.e1))
+        return False
+
+
 def _p(t):
     return None if t is None else t.data_ptr()
 
@@ -498,8 +521,12 @@ def affine_act_fwd(x, ss, act=None, res_pad=None, res_p=0, noise=None, out_p=0, 
     N, H, W, C = x.shape
     if out is None:
         out = empty_act(N, H + 2 * out_p, W + 2 * out_p, C, x.device)
-    check(_lib.lib().mt_affine_act_fwd(_p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(res_pad),
-                                       res_p, _p(noise), _p(out), out_p, _stream()), "affine_act_fwd")
+    # algorithmic bytes: one bf16 read + one bf16 write per element (+ a bf16 residual read,
+    # + an fp32 noise read)
+    nb = x.numel() * (4 + (2 if res_pad is not None else 0) + (4 if noise is not None else 0))
+    with _timed_bytes("hbm.norm_apply_fwd", x.shape, nb):
+        check(_lib.lib().mt_affine_act_fwd(_p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(res_pad),
+                                           res_p, _p(noise), _p(out), out_p, _stream()), "affine_act_fwd")
     _count()
     return out
 
@@ -520,8 +547,9 @@ def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None, g_p
     Cv = C_valid or C
     parts = L.mt_norm_bwd_parts(N, H, W, C, ACT[act], g_pad)
     sums = _T.empty((N, parts, C, 2), dtype=torch.float32, device=dev)
-    check(L.mt_norm_bwd_reduce(_p(g), g_pad, _p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(sums), parts,
-                               _stream()), "norm_bwd_reduce")
+    with _timed_bytes("hbm.norm_bwd_reduce", x.shape, x.numel() * 4):        # dy + x
+        check(L.mt_norm_bwd_reduce(_p(g), g_pad, _p(x), _p(ss), N, H, W, C, ACT[act], LRELU_SLOPE, _p(sums),
+                                   parts, _stream()), "norm_bwd_reduce")
     coef = _T.empty((N, C, 3), dtype=torch.float32, device=dev)
     dgb = _T.empty((N, 2 * C), dtype=torch.float32, device=dev) if mode == "adain" else None
     need_ln = mode == "layer" and ln_w is not None
@@ -544,8 +572,9 @@ def norm_bwd(g, x, ss, mr, mode, act=None, gb=None, ln_w=None, C_valid=None, g_p
         if acc:
             dlw = dlb = dbias = None
     dx = _T.empty_like(x)
-    check(L.mt_norm_bwd_apply(_p(g), g_pad, _p(x), _p(ss), _p(coef), N, H, W, C, ACT[act], LRELU_SLOPE,
-                              _p(dx), _stream()), "norm_bwd_apply")
+    with _timed_bytes("hbm.norm_bwd_apply", x.shape, x.numel() * 6):         # dy + x + dx
+        check(L.mt_norm_bwd_apply(_p(g), g_pad, _p(x), _p(ss), _p(coef), N, H, W, C, ACT[act], LRELU_SLOPE,
+                                  _p(dx), _stream()), "norm_bwd_apply")
     _count(3)
     return dx, dgb, dlw, dlb, dbias
 

@@ -43,6 +43,19 @@ class DataParallelGroup:
                 for t in list(net.parameters()) + list(net.buffers()):
                     dist.broadcast(t.data, src=0)
 
+    def parameter_spread(self, nets):
+        """Data-parallel self check: every rank applies the same all-reduced gradients to the same weights,
+        so the parameters must stay identical.  -> {'max_rel_spread': max over networks of
+        (max - min over ranks of sum|p|) / mean, 'identical': spread == 0}."""
+        dev = 'cuda' if dist.get_backend() == 'nccl' else 'cpu'
+        sums = torch.stack([torch.cat([p.detach().double().abs().sum().reshape(1) for p in net.parameters()]).sum()
+                            for net in nets]).to(dev)
+        hi, lo = sums.clone(), sums.clone()
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        spread = float(((hi - lo) / hi.clamp_min(1e-30)).max().item())
+        return {'max_rel_spread_of_param_checksums': spread, 'identical': spread == 0.0, 'ranks': self.world}
+
     def max_over_ranks(self, value: float) -> float:
         t = torch.tensor([value], dtype=torch.float64,
                          device='cuda' if dist.get_backend() == 'nccl' else 'cpu')

@@ -1,8 +1,8 @@
-"""TEST INFRASTRUCTURE — import the UNMODIFIED reference (/root/reference/src) as a library.
-
-Only usable where /root/reference exists (the build container), i.e. by
-oracle/make_golden.py and by CPU tests that pin the oracle against the reference directly.
-Nothing on the GPU box imports this.  Two modules the reference imports but that are absent
+"""TEST INFRASTRUCTURE — import the UNMODIFIED reference as a library: from /root/reference/src where
+that exists (the build container: oracle/make_golden.py, CPU tests that pin the oracle against the
+reference directly), else from the byte-identical copy oracle/_ref/src that oracle/make_ref.py makes
+(git-ignored; it travels to the GPU box, where bench.py's reference legs and the -m gpu drop-in tests
+use it).  The product never imports this.  Two modules the reference imports but that are absent
 here and never touch arithmetic are stubbed (tensorboardX: model.py:13, matplotlib.cm:
 utils.py:7), and the two CPU-incompatible `.get_device()` lines (misc.py:25, loss.py:60-62)
 are patched harness-side to `.device` so the training step can run on CPU.
@@ -11,11 +11,12 @@ import os
 import sys
 import types
 
-REF_SRC = "/root/reference/src"
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SRC = "/root/reference/src" if os.path.isdir("/root/reference/src") else os.path.join(_HERE, "_ref", "src")
 
 
 def available() -> bool:
-    return os.path.isdir(REF_SRC)
+    return os.path.isdir(os.path.join(REF_SRC, "models"))
 
 
 def import_reference():
@@ -41,7 +42,7 @@ def import_reference():
     # the reference's top-level module names (models, utils, dataset) must win the import
     for name in ("models", "utils", "dataset"):
         mod = sys.modules.get(name)
-        if mod is not None and not getattr(mod, "__file__", "").startswith(REF_SRC):
+        if mod is not None and not (getattr(mod, "__file__", None) or "").startswith(REF_SRC):
             raise RuntimeError(f"module name clash: {name} already imported from {mod.__file__}")
     if REF_SRC not in sys.path:
         sys.path.insert(0, REF_SRC)
