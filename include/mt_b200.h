@@ -33,6 +33,10 @@ typedef struct MtConv2d {
   float slope;  /* LeakyReLU slope (functions.py:34 -> 0.01) */
   int window;   /* 1: image-stem row-window mode (requires mt_conv_window_mode(Cin_s,kw) and an
                    input buffer followed by >= 128 B of finite slack, e.g. from the image packer) */
+  int single;   /* 1: never use the merged-parity / paired-pixel column modes for this call (they need
+                   even extents: the caller sets it for odd image sizes, e.g. the reference's 540x960
+                   sampling size whose feature maps are 135 and 67 wide, sample.py:50) and packs the
+                   operands in the plain layouts of mt_pack_conv_weight */
 } MtConv2d;
 
 /* ---- library --------------------------------------------------------------------- */

@@ -19,16 +19,12 @@ CSRC = PKG_DIR / "csrc"
 HEADER = REPO_DIR / "include" / "mt_b200.h"
 LIB_PATH = PKG_DIR / "libmt_b200.so"
 
-NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-shared", "-Xcompiler", "-fPIC", "--use_fast_math",
-]
-
 
 class MtConv2d(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "N", "Hin", "Win", "Cin", "Cin_s", "Hout", "Wout", "Cout", "Cout_s",
-        "kh", "kw", "stride", "zpad", "out_H", "out_W", "out_pad", "act")] + [("slope", ctypes.c_float), ("window", ctypes.c_int)]
+        "kh", "kw", "stride", "zpad", "out_H", "out_W", "out_pad", "act")] + [("slope", ctypes.c_float), ("window", ctypes.c_int),
+                                                                               ("single", ctypes.c_int)]
 
 
 def sources():

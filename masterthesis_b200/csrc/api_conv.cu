@@ -200,7 +200,7 @@ extern "C" int mt_conv_stats_parts(const MtConv2d* d, int transposed) {
     pick_tile(128, d->Wout / 2, d->Hout / 2, d->N, 1, &tw, &th, &tn);
     return tn == 1 ? 4 * cdiv(d->Wout / 2, tw) * cdiv(d->Hout / 2, th) : 0;
   }
-  if (d->window && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride) && !(d->Wout & 1)) {
+  if (d->window && !d->single && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride) && !(d->Wout & 1)) {
     // paired stem: tiles over Wout / 2 pixel pairs, each slot 2 * Cout_s wide = two of the caller's parts
     pick_tile(128, d->Wout / 2, d->Hout, d->N, d->stride, &tw, &th, &tn);
     return tn == 1 ? 2 * cdiv(d->Wout / 2, tw) * cdiv(d->Hout, th) : 0;
@@ -238,7 +238,7 @@ extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void*
   c.out_off = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
   c.act = d->act; c.slope = d->slope; c.bias = bias; c.out = y;
   c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;
-  if (win && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
+  if (win && !d->single && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
     if (d->Wout & 1) return -1014;
     if (stats && (parts & 1)) return -1012;
     c.Bn = 2 * d->Cout_s; c.n_store = 2 * d->Cout_s; c.bias_wrap = d->Cout_s;
@@ -383,7 +383,7 @@ extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_
   c.n_store = d->Cin_s; c.n_bias = 0; c.bias = nullptr; c.act = MT_ACT_NONE; c.out = dx;
   const long long pix = d->Cin_s, row = (long long)d->Win * d->Cin_s;
   c.out_n_stride = (long long)d->Hin * row;
-  if (mt_conv_s1_dgrad_pair_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin_s)) {
+  if (!d->single && mt_conv_s1_dgrad_pair_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin_s)) {
     // dx[h, 2b+j, ci] = sum_r sum_t dy[h - r, 2b + 1 - t, :] . Wm[r][t][(j, ci), :],  t = 0..kw,
     // filter column s = j - 1 + t (zero block outside 0..kw-1): mt_pack_conv_s1_dgrad_pair_weight
     if (d->Win & 1) return -1014;
@@ -403,7 +403,7 @@ extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_
     c.out_h_stride = row; c.out_w_stride = pix; c.out_off = 0;
     return run_conv_like(c, (cudaStream_t)stream);
   }
-  if (mt_conv_s2_dgrad_merged_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin)) {
+  if (!d->single && mt_conv_s2_dgrad_merged_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin)) {
     // dx[2a+ph, 2b+pw, ci] = sum_{dh,dw} dy[a-dh, b-dw, :] . W[:, ci, ph+2dh, pw+2dw]   (taps beyond the
     // filter are zero blocks, dy rows / columns outside the map read as zero).  As for the transposed
     // convolution forward, the two column parities are GEMM columns (pw, ci): 2*Cin_s contiguous

@@ -443,7 +443,7 @@ static int describe_conv_wgrad(const MtConv2d* d, const void* x, const void* dy,
   if (win) {
     c.kh = d->kh; c.kw = 1; c.off_h = 0; c.off_w = 0; c.step_h = 1; c.step_w = 0;
     c.N_store = 64;
-    if (mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
+    if (!d->single && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
       // paired stem (see mt_conv_window_pair_mode): dy read as [N, Hout, Wout/2, 2*Cout_s] — the same
       // memory — against windows of stride 2*stride: M = (pixel parity, Cout) fills the 128-row MMA
       // that a 64-channel stem left half empty, and half as many window rows are fetched.

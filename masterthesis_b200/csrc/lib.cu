@@ -19,7 +19,7 @@ extern "C" const char* mt_error_string(int code) {
     case -1007: return "reflection pad must be smaller than the spatial size";
     case -1010: return "unsupported (cg, BN) implicit-GEMM tile";
     case -1013: return "stream fork/join of the sub-pixel phases failed";
-    case -1014: return "merged-parity / paired-pixel conv modes need even extents: for odd sizes run with MT_CONVT_MERGED=0 MT_DGRAD_MERGED=0 MT_STEM_PAIR=0 MT_DGRAD_PAIR=0";
+    case -1014: return "merged-parity / paired-pixel conv modes need even extents: set MtConv2d.single = 1 for odd sizes (and pack the plain operand layouts)";
     case -1015: return "weight gradient: `splits` does not match mt_conv2d_wgrad_splits() / mt_conv_transpose2d_wgrad_splits()";
     case -1012: return "`parts` does not match the *_parts() query of this entry point for this shape";
     case -1011: return "implicit-GEMM shared-memory ring is not at the expected offset";

@@ -57,18 +57,18 @@ def prepack(*nets):
         for m in net.modules():
             if isinstance(m, _ConvParams) and not m.spectral and m._pack is not None:
                 w = m.weight
-                (_, _, zpad, stem, _), _ = m._pack
-                key = (w._version, w.data_ptr(), zpad, stem, _PACK_EPOCH[0])
+                (_, _, zpad, stem, single, _), _ = m._pack
+                key = (w._version, w.data_ptr(), zpad, stem, single, _PACK_EPOCH[0])
                 if m._pack[0] != key:
-                    todo.append((m, key, zpad, stem))
+                    todo.append((m, key, zpad, stem, single))
     if not todo:
         return
     cur = torch.cuda.current_stream()
     side = _pack_stream(todo[0][0].weight.device)
     side.wait_stream(cur)
     with torch.cuda.stream(side):
-        for m, key, zpad, stem in todo:
-            m._pack = (key, ops.pack_weight(m.weight, m.geom(zpad, stem)))
+        for m, key, zpad, stem, single in todo:
+            m._pack = (key, ops.pack_weight(m.weight, m.geom(zpad, stem, single)))
             ev = torch.cuda.Event()
             ev.record(side)
             m._pack_event = ev
@@ -103,16 +103,18 @@ class _ConvParams(nn.Module):
             bound = 1 / math.sqrt(fan_in) if fan_in > 0 else 0
             nn.init.uniform_(self.bias, -bound, bound)
 
-    def geom(self, zpad=0, stem=False) -> ConvGeom:
+    def geom(self, zpad=0, stem=False, single=False) -> ConvGeom:
+        """`single`: the call has odd spatial extents, for which the merged-parity / paired-pixel launch
+        modes do not exist (plain operand layouts, MtConv2d.single)"""
         return ConvGeom(self.in_channels, self.out_channels, self.kernel_size, self.kernel_size,
-                        self.stride, zpad, self.transposed, stem)
+                        self.stride, zpad, self.transposed, stem, single)
 
-    def packed(self, zpad=0, stem=False):
+    def packed(self, zpad=0, stem=False, single=False):
         """bf16 GEMM operands of the fp32 master weight, refreshed when the weight changes."""
         w = self.weight
-        key = (w._version, w.data_ptr(), zpad, stem, _PACK_EPOCH[0])
+        key = (w._version, w.data_ptr(), zpad, stem, single, _PACK_EPOCH[0])
         if self._pack is None or self._pack[0] != key:
-            self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem)))
+            self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem, single)))
             self._pack_event = None
         elif self._pack_event is not None:
             # packed ahead of time on the pack stream (prepack below): every consuming stream orders
@@ -155,12 +157,12 @@ class _ConvParams(nn.Module):
         sigma = torch.dot(u.clone(), torch.mv(wm, v.clone()))
         return w / sigma
 
-    def operands(self, zpad=0, stem=False):
+    def operands(self, zpad=0, stem=False, single=False):
         """(weight as autograd sees it, bf16 forward operand, bf16 backward operand)"""
         if not self.spectral:
-            return (self.weight,) + tuple(self.packed(zpad, stem))
+            return (self.weight,) + tuple(self.packed(zpad, stem, single))
         w = self.sn_weight()
-        return (w,) + tuple(ops.pack_weight(w, self.geom(zpad, stem)))
+        return (w,) + tuple(ops.pack_weight(w, self.geom(zpad, stem, single)))
 
     def extra_repr(self):
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, "
@@ -293,8 +295,14 @@ class ConvBlock(nn.Module):
         """x: NHWC bf16 with `self.rpad` reflection border.  Returns a buffer padded by out_pad."""
         self._check()
         conv = self.conv
-        g = conv.geom(self.zpad, self.stem)
-        w, wf, wb = conv.operands(self.zpad, self.stem)
+        # odd extents (e.g. the reference's 540x960 sampling size: 135- and 67-wide feature maps): the
+        # pixel-pair launch modes need an even output width / even padded input, so such calls use the plain
+        # single-pixel launches with their own operand packs
+        _, Hp, Wp, _ = x.shape
+        Wo = (Wp + 2 * self.zpad - conv.kernel_size) // conv.stride + 1
+        single = bool((Hp | Wp | Wo) & 1)
+        g = conv.geom(self.zpad, self.stem, single)
+        w, wf, wb = conv.operands(self.zpad, self.stem, single)
         act = self.act if act_override == 'keep' else act_override
         norm = self.norm
         if norm is None:

@@ -173,6 +173,7 @@ class ConvGeom:
     zpad: int = 0          # logical zero padding (reflection padding lives in the input buffer)
     transposed: bool = False
     stem: bool = False     # input is an image buffer with slack -> row-window mode if eligible
+    single: bool = False   # odd spatial extents: no merged-parity / paired-pixel column modes (MtConv2d.single)
 
     @property
     def Cin_s(self):
@@ -190,18 +191,19 @@ class ConvGeom:
     @property
     def window_pair(self) -> bool:
         """row-window stem computing two adjacent output pixels per GEMM row (include/mt_b200.h)"""
-        return bool(self.window and _lib.lib().mt_conv_window_pair_mode(self.Cin_s, self.kw, self.stride))
+        return bool(self.window and not self.single and
+                    _lib.lib().mt_conv_window_pair_mode(self.Cin_s, self.kw, self.stride))
 
     @property
     def pair_s1_dgrad(self) -> bool:
         """stride-1 conv into <= 8 channels whose data gradient computes pixel pairs (include/mt_b200.h)"""
-        return bool(not self.transposed and _lib.lib().mt_conv_s1_dgrad_pair_mode(
+        return bool(not self.transposed and not self.single and _lib.lib().mt_conv_s1_dgrad_pair_mode(
             self.kh, self.kw, self.stride, self.zpad, self.Cin_s))
 
     @property
     def merged_s2_dgrad(self) -> bool:
         """stride-2 conv whose data gradient runs in the merged-parity mode (include/mt_b200.h)"""
-        return bool(not self.transposed and
+        return bool(not self.transposed and not self.single and
                     _lib.lib().mt_conv_s2_dgrad_merged_mode(self.kh, self.kw, self.stride, self.zpad, self.Cin))
 
     @property
@@ -219,7 +221,7 @@ class ConvGeom:
         Ho, Wo = self.out_hw(Hin, Win)
         return MtConv2d(N, Hin, Win, self.Cin, self.Cin_s, Ho, Wo, self.Cout, self.Cout_s,
                         self.kh, self.kw, self.stride, self.zpad, Ho + 2 * out_pad, Wo + 2 * out_pad,
-                        out_pad, ACT[act], LRELU_SLOPE, int(self.window))
+                        out_pad, ACT[act], LRELU_SLOPE, int(self.window), int(self.single))
 
 
 # ----------------------------------------------------------------------------- weights
