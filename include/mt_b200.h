@@ -243,6 +243,57 @@ int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, int pad, fl
 int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C, int pad,
                       void* dx_pad, void* stream);
 
+/* ---- small fp32 layers between the conv stacks and the losses (no library GEMMs in the iteration) ------- */
+/* nn.Linear: y[N][Out] = act(x[N][In] w[Out][In]^T + b)  (act: MT_ACT_NONE | MT_ACT_RELU)
+ * networks.py:127-128 (fc, fcVar), :256-261 (style MLP), norm.py:27 (AdaIN fc), :77,402-403 (1x1 heads) */
+int mt_linear_fwd(const float* x, const float* w, const float* b, int N, int In, int Out, int act,
+                  float* y, void* stream);
+/* g = dy * act'(y);  dw (+)= g^T x, db (+)= sum_n g (accumulate_params: += into .grad buffers),
+ * dx (+)= g w (accumulate_dx); dx / dw / db may be NULL; y only for MT_ACT_RELU.  Fixed-order sums. */
+int mt_linear_bwd(const float* dy, const float* y, const float* x, const float* w, int N, int In, int Out,
+                  int act, float* dx, float* dw, float* db, int accumulate_params, int accumulate_dx,
+                  void* stream);
+/* The decoder's style network in one call (networks.py:256-261 + norm.py:27 of every AdaINResnetBlock):
+ * h1 = relu(L0(cz)), h2 = relu(L1(h1)), s = L2(h2), gb[k] = fc_k(s) for k < n_heads ([N][head_out] each).
+ * mlp_w / mlp_b / head_w / head_b / gb are HOST arrays of device pointers (3 and n_heads entries). */
+int mt_style_mlp_fwd(const float* cz, int N, int in_dim, int hid, int style_dim,
+                     const float* const* mlp_w, const float* const* mlp_b, int n_heads, int head_out,
+                     const float* const* head_w, const float* const* head_b, float* h1, float* h2,
+                     float* s, float* const* gb, void* stream);
+/* dgb[k] [N][head_out] (host array of device pointers; NULL entries = no gradient) and / or ds_in
+ * [N][style_dim] -> every layer's gradients (written, or added when accumulate != 0) and dcz (optional).
+ * ds / dh2 / dh1: scratch of N*style_dim / N*hid / N*hid floats. */
+int mt_style_mlp_bwd(const float* cz, const float* h1, const float* h2, const float* s, int N,
+                     int in_dim, int hid, int style_dim, const float* const* mlp_w, int n_heads,
+                     int head_out, const float* const* head_w, const float* const* dgb, const float* ds_in,
+                     float* const* d_mlp_w, float* const* d_mlp_b, float* const* d_head_w,
+                     float* const* d_head_b, float* ds, float* dh2, float* dh1, float* dcz,
+                     int accumulate, void* stream);
+/* Discriminator heads (networks.py:373-376,380-383): h [N][S][S][Cs] bf16 (C valid channels) ->
+ * out [N][S+2][S+2] fp32 = Conv2d(C,1,1,padding=1,bias=False) (exact-zero border) and
+ * cls [N][nd] = Conv2d(C,nd,k=S,bias=False) + AdaptiveAvgPool2d(1); w1 [C], w2 [nd][C][S][S]; nd <= 8 */
+int mt_dis_head_fwd(const void* h, const float* w1, const float* w2, int N, int S, int Cs, int C, int nd,
+                    float* out, float* cls, void* stream);
+/* images n < cls_first carry no class gradient (the fake half of a discriminator batch); dh / (dw1, dw2)
+ * optional; accumulate != 0: dw1 / dw2 += (parameter .grad buffers) */
+int mt_dis_head_bwd(const float* dout, const float* dcls, const void* h, const float* w1, const float* w2,
+                    int N, int S, int Cs, int C, int nd, int cls_first, void* dh, float* dw1, float* dw2,
+                    int accumulate, void* stream);
+/* ---- loss layer: value and gradient in one pass (loss.py:52-64, adain_model.py:213-216,303-314) ---------- */
+/* nn.BCEWithLogitsLoss (mean over n) against target[n] or, when target == NULL, the constant target_const:
+ * loss[0] = the mean; dx (optional) = gscale / n * (sigmoid(x) - t) */
+int mt_loss_bce_logits(const float* x, const float* target, float target_const, int n, float gscale,
+                       float* loss, float* dx, void* stream);
+/* nn.L1Loss: loss[0] = weight * mean|a - b|, da (optional) = gscale / n * sign(a - b);
+ * partials: scratch [parts], parts = mt_loss_l1_parts(n); a, b, da 16-byte aligned */
+int mt_loss_l1_parts(long long n);
+int mt_loss_l1(const float* a, const float* b, long long n, float weight, float gscale, float* loss,
+               float* da, float* partials, int parts, void* stream);
+/* -0.5 * sum(1 + logvar - mu^2 - exp(logvar)) over n elements (adain_model.py:313-314);
+ * dmu = gscale * mu, dlogvar = gscale * 0.5 * (exp(logvar) - 1) (both or neither) */
+int mt_loss_kl_normal(const float* mu, const float* logvar, int n, float gscale, float* loss,
+                      float* dmu, float* dlogvar, void* stream);
+
 /* ---- optimizer ------------------------------------------------------------------------------ */
 /* torch.optim.Adam step (coupled L2 weight decay, adain_model.py:58-61) over a flat fp32 bucket;
  * g is multiplied by gscale first (data-parallel averaging). `step` is the 1-based step count. */

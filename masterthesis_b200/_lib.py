@@ -77,6 +77,7 @@ _CTYPE = {
     "float*": ctypes.c_void_p, "const float*": ctypes.c_void_p,
     "const char*": ctypes.c_char_p, "const MtConv2d*": ctypes.POINTER(MtConv2d),
     "const int*": ctypes.c_void_p, "int*": ctypes.c_void_p,
+    "const float* const*": ctypes.c_void_p, "float* const*": ctypes.c_void_p,     # host arrays of device pointers
 }
 
 

@@ -137,6 +137,47 @@ class ConvNormAct(Function):
         return dx, dw, db, None, None, None, None, dp1, dp2, None, None, None
 
 
+class NormAct(Function):
+    """{InstanceNorm2d | AdaptiveInstanceNorm | LayerNorm} (+ activation) on a dense NHWC bf16 tensor: the
+    stand-alone form behind the reference-compatible `forward` of the norm modules (norm.py:16-21,29-33,
+    functions.py:17); the networks use the fused ConvNormAct / ResBlock plans instead."""
+
+    @staticmethod
+    def forward(ctx, x, mode, p1, p2, act, C_valid):
+        N, H, W, C = x.shape
+        gb = _c(p1) if mode == "adain" else None
+        lw, lb = (p1, p2) if mode == "layer" else (None, None)
+        ss, mr = ops.norm_finalize(ops.plane_stats(x), mode, H * W, gb, lw, lb, C_valid=C_valid)
+        out = ops.affine_act_fwd(x, ss, act=act)
+        ctx.mode, ctx.act, ctx.C_valid = mode, act, C_valid
+        ctx.save_for_backward(x, ss, mr, p1)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, ss, mr, p1 = ctx.saved_tensors
+        mode = ctx.mode
+        ln = mode == "layer" and p1 is not None
+        dx, dgb, dlw, dlb, _ = ops.norm_bwd(_c(dout), x, ss, mr, mode, act=ctx.act,
+                                            gb=_c(p1) if mode == "adain" else None,
+                                            ln_w=p1 if ln else None, C_valid=ctx.C_valid)
+        dp1 = dgb if mode == "adain" else (dlw.view_as(p1) if ln else None)
+        dp2 = dlb.view_as(p1) if ln else None
+        return dx, None, dp1, dp2, None, None
+
+
+class AddNoise(Function):
+    """x + noise (GaussianNoiseLayer, misc.py:22-26) on a dense NHWC bf16 tensor; noise fp32 NHWC."""
+
+    @staticmethod
+    def forward(ctx, x, noise):
+        return ops.affine_act_fwd(x, None, noise=noise)
+
+    @staticmethod
+    def backward(ctx, dout):
+        return dout, None
+
+
 class ResBlock(Function):
     """x + norm(conv3x3(relu(norm(conv3x3(x)))))  with norm = InstanceNorm2d (ResnetBlock,
     blocks.py:121-138) or one shared AdaptiveInstanceNorm (AdaINResnetBlock, blocks.py:140-167).
@@ -368,3 +409,102 @@ class MaskMul(Function):
     def backward(ctx, dout):
         (m,) = ctx.saved_tensors
         return ops.mul(_c(dout), m), None
+
+
+class Linear(Function):
+    """nn.Linear (+ReLU) on fp32 [N, In] rows by our own kernels (fc / fcVar of the style encoder
+    networks.py:127-128, the 1x1 conv heads behind a global average pool networks.py:77,402-403: a weight
+    [Out, In, 1, 1] is the same memory as [Out, In])."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act=None):
+        x = _c(x.float())
+        w2 = _c(weight.detach()).view(weight.shape[0], -1)
+        y = ops.linear_fwd(x, w2, bias, act)
+        ctx.act, ctx.weight, ctx.bias = act, weight, bias
+        ctx.save_for_backward(x, y if act is not None else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y = ctx.saved_tensors
+        w, b = ctx.weight, ctx.bias
+        need_w = ctx.needs_input_grad[1]
+        dx, dw, db = ops.linear_bwd(_c(dy.float()), y, x, _c(w.detach()).view(w.shape[0], -1), ctx.act,
+                                    ctx.needs_input_grad[0], _grad_buf(w) if need_w else None,
+                                    _grad_buf(b) if (need_w and b is not None) else None,
+                                    has_bias=b is not None, need_params=need_w)
+        return dx, (None if dw is None else dw.view(w.shape)), db, None
+
+
+class DisHead(Function):
+    """The two heads of Discriminator (networks.py:373-376,380-383) on the last feature map h [N,S,S,Cs] bf16:
+    out = Conv2d(C, 1, 1, padding=1, bias=False)(h) -> [N,1,S+2,S+2] (exact-zero border) and
+    cls = AdaptiveAvgPool2d(1)(Conv2d(C, nd, k=S, bias=False)(h)) -> [N, nd]; one kernel each way."""
+
+    @staticmethod
+    def forward(ctx, h, w1, w2):
+        ctx.set_materialize_grads(False)
+        C, nd = w1.shape[1], w2.shape[0]
+        out, cls = ops.dis_head_fwd(_c(h), _c(w1.detach()).view(-1), _c(w2.detach()), C, nd)
+        ctx.w1, ctx.w2 = w1, w2
+        ctx.save_for_backward(h)
+        return out, cls
+
+    @staticmethod
+    def backward(ctx, dout, dcls):
+        (h,) = ctx.saved_tensors
+        w1, w2 = ctx.w1, ctx.w2
+        C, nd = w1.shape[1], w2.shape[0]
+        N, S = h.shape[0], h.shape[1]
+        if dout is None:
+            dout = torch.zeros((N, 1, S + 2, S + 2), dtype=torch.float32, device=h.device)
+        if dcls is None:
+            dcls = torch.zeros((N, nd), dtype=torch.float32, device=h.device)
+        need_w = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        into = None
+        if need_w and _grad_buf(w1) is not None and _grad_buf(w2) is not None:
+            into = (_grad_buf(w1), _grad_buf(w2))
+        dh, dw1, dw2 = ops.dis_head_bwd(_c(dout.float()), _c(dcls.float()), h, _c(w1.detach()).view(-1), _c(w2.detach()),
+                                        C, nd, 0, ctx.needs_input_grad[0], into, need_w)
+        return dh, (None if dw1 is None else dw1.view(w1.shape)), dw2
+
+
+class StyleMLP(Function):
+    """The decoder's style network as one plan (networks.py:256-261, norm.py:27 of every AdaINResnetBlock):
+    s = L2(relu(L1(relu(L0(cz))))) and gb_k = fc_k(s) for each of the K AdaIN blocks.
+    apply(cz, K, w0, b0, w1, b1, w2, b2, hw_0, hb_0, ..., hw_{K-1}, hb_{K-1}) -> (s, gb_0, ..., gb_{K-1})"""
+
+    @staticmethod
+    def forward(ctx, cz, K, *params):
+        ctx.set_materialize_grads(False)
+        cz = _c(cz.float())
+        mlp = [(_c(params[2 * i]), params[2 * i + 1]) for i in range(3)]
+        heads = [(_c(params[6 + 2 * k]), params[7 + 2 * k]) for k in range(K)]
+        h1, h2, s, gb = ops.style_mlp_fwd(cz, mlp, heads)
+        ctx.K, ctx.params = K, params
+        ctx.save_for_backward(cz, h1, h2, s)
+        return (s,) + tuple(gb)
+
+    @staticmethod
+    def backward(ctx, ds, *dgb):
+        cz, h1, h2, s = ctx.saved_tensors
+        K, params = ctx.K, ctx.params
+        mlp_w = [params[2 * i].detach() for i in range(3)]
+        head_w = [params[6 + 2 * k].detach() for k in range(K)]
+        bufs = [_grad_buf(p) for p in params]
+        need_params = any(ctx.needs_input_grad[2:])
+        into = None
+        if need_params and all(b is not None for b in bufs):
+            into = ([bufs[0], bufs[2], bufs[4]], [bufs[1], bufs[3], bufs[5]],
+                    [bufs[6 + 2 * k] for k in range(K)], [bufs[7 + 2 * k] for k in range(K)])
+        dcz, d_mw, d_mb, d_hw, d_hb = ops.style_mlp_bwd(cz, h1, h2, s, mlp_w, head_w, list(dgb), ds, into,
+                                                        ctx.needs_input_grad[0])
+        if into is not None or not need_params:
+            return (dcz, None) + (None,) * len(params)
+        out = []
+        for i in range(3):
+            out += [d_mw[i], d_mb[i]]
+        for k in range(K):
+            out += [d_hw[k], d_hb[k]]
+        return (dcz, None) + tuple(out)

@@ -74,6 +74,73 @@ class AdaINModel(Model):
                                           up_type=args.up_type, norm_layer=args.dec_norm,
                                           dropout=args.use_dropout)
 
+    # ------------------------------------------------------------------ the loss layer as kernels
+    # Default flags (vanilla GAN loss, single-scale discriminator, no relativistic term): every loss term is
+    # ONE launch that writes the scalar into a slot of a device vector and the gradient with respect to its
+    # input in the same pass (mt_loss_bce_logits / mt_loss_l1 / mt_loss_kl_normal); the phase then
+    # back-propagates from explicit gradients (torch.autograd.backward(roots, grads)), so no loss graph of
+    # tiny library kernels exists.  The named losses of the reference (loss sums, weights) are formed on the
+    # host from the raw terms after the one read-back of the iteration.  Other --gan_mode values, --use_ragan
+    # and --ms_dis keep the general torch formulation below.
+    SLOTS = ('d1_fake', 'd1_real', 'd1_cls', 'd2_fake', 'd2_real', 'd2_cls', 'g_adv', 'g_cls', 'l1_self', 'l1_cc',
+             'zc_sumsq', 'kl_zs', 'g_content', 'z_l1', 'gan2', 'gan2_cls', 'loss_dc')
+
+    @property
+    def fast_losses(self):
+        a = self.args
+        return (a.gan_mode == 'vanilla' and not a.use_ragan and not a.ms_dis
+                and os.environ.get('MT_FAST_LOSS', '1') == '1')
+
+    def _slot(self, name):
+        """1-element view of the loss vector for one raw term"""
+        if getattr(self, '_lbuf', None) is None:
+            self._lbuf = torch.zeros(len(self.SLOTS), dtype=torch.float32, device=self.device)
+        i = self.SLOTS.index(name)
+        self._raw_used.add(name)
+        return self._lbuf[i:i + 1]
+
+    def _loss_vector(self):
+        if not self.fast_losses:
+            return super()._loss_vector()
+        extra = list(self._scalars)        # terms that still came from torch (BaseModel without --reparam)
+        if extra:
+            vec = torch.cat([self._lbuf] + [self._scalars[k].float().reshape(1) for k in extra])
+        else:
+            vec = self._lbuf
+        return [('raw', self.SLOTS, tuple(self._raw_used), tuple(extra))], vec
+
+    def _named_losses(self, keys, values):
+        if not keys or not isinstance(keys[0], tuple):
+            return super()._named_losses(keys, values)
+        _, slots, used, extra = keys[0]
+        r = dict(zip(slots, values))
+        r.update(zip(extra, values[len(slots):]))
+        a = self.args
+        out = {}
+        if 'loss_dc' in used:
+            out['loss_dc'] = r['loss_dc']
+        if 'd2_fake' in used:
+            # the reference logs the values of the LAST discriminator update (discriminator2), :216-223
+            out['d_adv'] = r['d2_fake'] + r['d2_real']
+            out['d_cls'] = r['d2_cls']
+            out['d_total'] = out['d_adv'] + a.lambda_cls * out['d_cls']
+        if 'g_adv' in used:
+            if 'g_content' in used:
+                out['g_content'] = r['g_content']
+            out['g_adv'] = r['g_adv']
+            out['g_cls'] = r['g_cls'] * a.lambda_cls_G
+            out['kl_zc'] = r['zc_sumsq'] / self._n_zc * 0.01
+            out['kl_zs'] = r['kl_zs'] * 0.01 if 'kl_zs' in used else r['kl_zs_t']
+            out['l1_self_rec'] = r['l1_self']
+            out['l1_cc_rec'] = r['l1_cc']
+            out['total_g'] = (out['g_adv'] + out['g_cls'] + out['l1_self_rec'] + out['l1_cc_rec'] + out['kl_zc']
+                              + out['kl_zs'] + out.get('g_content', 0.0))
+        if 'gan2' in used:
+            out['l1_recon_z'] = r['z_l1']
+            out['gan2'] = r['gan2']
+            out['gan2_cls'] = r['gan2_cls'] * a.lambda_cls_G
+        return out.items()
+
     # ------------------------------------------------------------------ small pieces
     def gan_loss(self, pred, is_real):
         """GANLoss.forward (reference loss.py:52-64)."""
@@ -131,6 +198,13 @@ class AdaINModel(Model):
         finally:
             for p in ps:
                 p.requires_grad_(True)
+
+    def _const(self, value):
+        """cached 0-dim fp32 device constant (kernel arguments that are read from device memory)"""
+        c = self.__dict__.setdefault('_consts', {})
+        if value not in c:
+            c[value] = torch.tensor(float(value), dtype=torch.float32, device=self.device)
+        return c[value]
 
     def _step(self, *nets, prepack=True):
         """all-reduce (data parallel) + Adam for the given networks (+ their bf16 weight packs, ahead of
@@ -233,6 +307,24 @@ class AdaINModel(Model):
 
     def backward_discriminator(self, netD, real, fake, c_org):
         n = real.shape[0]
+        if self.fast_losses:
+            tag = 'd1' if netD is self.model.discriminator1 else 'd2'
+            if self.args.dis_sn:       # two calls (each advances the power iteration), reference order :207-209
+                (pf, cf), (pr, cr) = netD.run(fake.detach()), netD.run(real)
+                roots, halves = [pf, pr, cr], None
+            else:
+                pred, pred_cls = netD.run(torch.cat((fake.detach(), real)))
+                pf, pr, cr = pred[:n], pred[n:], pred_cls[n:]
+                roots, halves = [pred, pred_cls], (torch.empty_like(pred), torch.zeros_like(pred_cls))
+            g_f = ops.loss_bce_logits(pf.detach(), 0.0, 1.0, self._slot(tag + '_fake'),
+                                      dx_out=None if halves is None else halves[0][:n])
+            g_r = ops.loss_bce_logits(pr.detach(), 1.0, 1.0, self._slot(tag + '_real'),
+                                      dx_out=None if halves is None else halves[0][n:])
+            g_c = ops.loss_bce_logits(cr.detach(), c_org, self.args.lambda_cls, self._slot(tag + '_cls'),
+                                      dx_out=None if halves is None else halves[1][n:])
+            torch.autograd.backward(roots, [g_f, g_r, g_c] if halves is None else list(halves))
+            ops.join_side()
+            return
         if self.args.dis_sn:
             # spectral norm: every reference forward runs one power iteration, so the fake and the real
             # call see different W / sigma (:207-209) -> two calls, in the reference's order
@@ -271,10 +363,14 @@ class AdaINModel(Model):
             z_c = self.Ec(img)
         opt = self.optimizer.content_discriminator
         opt.zero_grad()
-        loss_d_content = _bce(self.model.content_discriminator.run(z_c), c_org)
-        loss_d_content.backward()
+        if self.fast_losses:
+            pred = self.model.content_discriminator.run(z_c)
+            torch.autograd.backward([pred], [ops.loss_bce_logits(pred.detach(), c_org, 1.0, self._slot('loss_dc'))])
+        else:
+            loss_d_content = _bce(self.model.content_discriminator.run(z_c), c_org)
+            loss_d_content.backward()
+            self._scalars.update(loss_dc=loss_d_content.detach())
         ops.join_side()      # pending side-stream weight gradients land before the bucket is read
-        self._scalars.update(loss_dc=loss_d_content.detach())
         if self.dp is not None:
             self.dp.allreduce([opt])
         # nn.utils.clip_grad_norm_(params, 5) on the flat bucket (after the all-reduce: a global norm)
@@ -294,6 +390,14 @@ class AdaINModel(Model):
             self.optimizer[n].zero_grad()
         self.backward_decoder_random(img, c_org)
         self._step('content_encoder', 'decoder', prepack=False)      # next use: the next iteration
+
+    def _g_adv_fast(self, netD, fake, c_org, adv_slot, cls_slot):
+        """generator-side adversarial + classification terms as (roots, gradients): BCE(D(fake), 1) and
+        lambda_cls_G * BCE(cls(fake), c_org), losses written to their slots"""
+        pred, pred_cls = netD.run(fake)
+        g_a = ops.loss_bce_logits(pred.detach(), 1.0, 1.0, self._slot(adv_slot))
+        g_c = ops.loss_bce_logits(pred_cls.detach(), c_org, self.args.lambda_cls_G, self._slot(cls_slot))
+        return [pred, pred_cls], [g_a, g_c]
 
     def _g_adv(self, netD, fake, c_org, real=None, netD_real=None):
         """generator-side adversarial + classification loss.  `real` / `netD_real`: the relativistic
@@ -331,24 +435,58 @@ class AdaINModel(Model):
             ((z_cb, z_ca), (z_sa, z_sa), (cls_a, cls_a)), ((z_ca, z_cb), (z_sb, z_sb), (cls_b, cls_b)))
         img_fake = torch.cat((img_ba, img_ab))
         img_self = torch.cat((img_aa, img_bb))
+        fast = self.fast_losses
         # the adversarial branch (D1 on the fakes) is independent of the reconstruction branch
         with self._frozen('discriminator1'):
-            z_c_rec, ((z_s_rec, _, _), (loss_g_adv, loss_g_cls)) = self._fork(
+            z_c_rec, ((z_s_rec, _, _), adv) = self._fork(
                 lambda: self.Ec(img_fake),
                 lambda: (self.Es(img_fake, c_org),
+                         self._g_adv_fast(self.model.discriminator1, img_fake, c_org, 'g_adv', 'g_cls') if fast else
                          self._g_adv(self.model.discriminator1, img_fake, c_org, img, self.model.discriminator1)))
         z_c_rec_b, z_c_rec_a = torch.split(z_c_rec, B, dim=0)
         z_s_rec_a, z_s_rec_b = torch.split(z_s_rec, B, dim=0)
         img_recon = self.G(torch.cat((z_c_rec_a, z_c_rec_b)), torch.cat((z_s_rec_a, z_s_rec_b)),
                            torch.cat((cls_a, cls_b)))
+        N, Hp, Wp, _ = z_c.shape
+        n_zc = N * (Hp - 2 * CONTENT_PAD) * (Wp - 2 * CONTENT_PAD) * self.model.content_encoder.output_dim
+        if fast:
+            # every term: value into its slot + gradient with respect to the network output it reads
+            roots, grads = adv
+            if self.args.use_dis_content:      # backward_content_discriminator (:334-337)
+                with self._frozen('content_discriminator'):
+                    pred_c = self.model.content_discriminator.run(z_c)
+                roots.append(pred_c)
+                grads.append(ops.loss_bce_logits(pred_c.detach(), 1 - c_org, 1.0, self._slot('g_content')))
+            roots += [img_self, img_recon]
+            grads += [ops.loss_l1(img_self.detach(), img, self.args.lambda_rec, self._slot('l1_self')),
+                      ops.loss_l1(img_recon.detach(), img, self.args.lambda_rec, self._slot('l1_cc'))]
+            # 0.01 * mean(z_c^2) (:396-399): sum of squares into its slot, gradient 0.02 / n * z_c
+            self._n_zc = n_zc
+            ops.sumsq_interior(z_c.detach(), CONTENT_PAD, out=self._slot('zc_sumsq'))
+            roots.append(z_c)
+            grads.append(ops.scale_interior(z_c.detach(), self._const(0.02 / n_zc), CONTENT_PAD))
+            extra = None
+            if self.reparam:
+                # a SUM over the batch (:313-314): under data parallelism it adds up over ranks while the
+                # gradient all-reduce averages -> the gradient is pre-scaled by the world size
+                dmu, dlv = ops.loss_kl_normal(mu.detach(), logvar.detach(), 0.01 * world, self._slot('kl_zs'))
+                roots += [mu, logvar]
+                grads += [dmu, dlv]
+            else:                              # base_model.py:346-347: a mean, no world scaling
+                extra = torch.mean(z_s.pow(2)) * 0.01
+                self._scalars.update(kl_zs_t=extra.detach())
+                roots.append(extra)
+                grads.append(None)
+            torch.autograd.backward(roots, grads)
+            ops.join_side(all_streams=True)
+            return
+        loss_g_adv, loss_g_cls = adv
         loss_g_content = None
         if self.args.use_dis_content:          # backward_content_discriminator (:334-337)
             with self._frozen('content_discriminator'):
                 loss_g_content = _bce(self.model.content_discriminator.run(z_c), 1 - c_org)
         loss_g_self = F.l1_loss(img_self, img) * self.args.lambda_rec
         loss_g_cc = F.l1_loss(img_recon, img) * self.args.lambda_rec
-        N, Hp, Wp, _ = z_c.shape
-        n_zc = N * (Hp - 2 * CONTENT_PAD) * (Wp - 2 * CONTENT_PAD) * self.model.content_encoder.output_dim
         loss_kl_zc = Fn.SumSqInterior.apply(z_c, CONTENT_PAD) / n_zc * 0.01
         # SUM over the batch, not a mean (:313-314): under data parallelism it must add up over
         # ranks while the gradient all-reduce averages -> pre-scale by the world size.
@@ -378,10 +516,23 @@ class AdaINModel(Model):
         # discriminator2 otherwise (:378); the relativistic branch (:361-362) takes the reals from
         # discriminator2 and the fakes from discriminator1
         dname = 'discriminator1' if (self.args.ms_dis or self.args.use_ragan) else 'discriminator2'
+        fast = self.fast_losses
         with self._frozen('discriminator1', 'discriminator2', 'style_encoder'):
-            (loss_g_adv2, loss_g_cls2), (z_sr_rec, mu2, _) = self._fork(
-                lambda: self._g_adv(self.model[dname], img_random, c_org, img, self.model.discriminator2),
+            adv, (z_sr_rec, mu2, _) = self._fork(
+                lambda: (self._g_adv_fast(self.model[dname], img_random, c_org, 'gan2', 'gan2_cls') if fast else
+                         self._g_adv(self.model[dname], img_random, c_org, img, self.model.discriminator2)),
                 lambda: self.Es(img_random, c_org))
+        if fast:
+            roots, grads = adv
+            # (L1(mu_a, z) + L1(mu_b, z)) * 10 (:380-383) = 20 * mean over both halves at once
+            # (base_model.py:417-420 without --reparam: the FIRST half of the re-encoded style, twice)
+            rec = mu2 if self.reparam else torch.cat((z_sr_rec[:B], z_sr_rec[:B]))
+            roots.append(rec)
+            grads.append(ops.loss_l1(rec.detach(), torch.cat((z_sr, z_sr)), 20.0, self._slot('z_l1')))
+            torch.autograd.backward(roots, grads)
+            ops.join_side(all_streams=True)
+            return
+        loss_g_adv2, loss_g_cls2 = adv
         if self.reparam:
             mu2_a, mu2_b = torch.split(mu2, B, dim=0)
             loss_z_l1 = (F.l1_loss(mu2_a, z_sr) + F.l1_loss(mu2_b, z_sr)) * 10

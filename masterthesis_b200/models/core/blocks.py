@@ -512,8 +512,11 @@ class AdaINResnetBlock(nn.Module):
         self.dropout = nn.Dropout(0.5) if dropout else nn.Identity()
         self._dropout = dropout
 
-    def run(self, x, z, out_pad=1):
-        gb = self.norm.modulation(z)
+    def run(self, x, z, out_pad=1, gb=None):
+        """gb: the block's AdaIN modulation fc(z) [N, 2C] when the decoder computed it with the style MLP
+        (functional.StyleMLP); else it is formed here from the style code z"""
+        if gb is None:
+            gb = self.norm.modulation(z)
         c1, c2 = self.conv1.conv, self.conv2.conv
         if self._dropout and self.dropout.training:
             # the mask sits between the second AdaIN and the residual add: un-fused plan

@@ -91,7 +91,7 @@ class StyleEncoder(nn.Module):
             x = self.model[i].run(x, out_pad=0 if i == self.num_downs else 1)
         feat = Fn.GlobalAvgPool.apply(x)[:, :self.out_nch]
         head = self.model[-1]
-        return F.linear(feat, head.weight.flatten(1), head.bias)
+        return Fn.Linear.apply(feat, head.weight, head.bias)
 
     def forward(self, x, c):
         return self.run(x, c)
@@ -142,8 +142,8 @@ class ReparameterizedStyleEncoder(nn.Module):
         for i in range(1, self.n_blocks):
             a = self.model[i].run(a, out_pad=0 if i == self.n_blocks - 1 else 1)
         feat = Fn.GlobalAvgPool.apply(a)[:, :self.out_nch]
-        mu = self.fc(feat)
-        logvar = self.fcVar(feat)
+        mu = Fn.Linear.apply(feat, self.fc.weight, self.fc.bias)
+        logvar = Fn.Linear.apply(feat, self.fcVar.weight, self.fcVar.bias)
         return self.reparameterize(mu, logvar, rng), mu, logvar
 
     def forward(self, x, c):
@@ -187,9 +187,12 @@ class AdaINDecoder(nn.Module):
         out = z_c
         n = len(self.dec1)
         if self.adain:
-            s = self.linear(torch.cat([c, z], 1))
+            # style MLP + the fc of every block's AdaIN as one plan of our own kernels
+            params = [p for i in (0, 2, 4) for p in (self.linear[i].weight, self.linear[i].bias)]
+            params += [p for dec in self.dec1 for p in (dec.norm.fc.weight, dec.norm.fc.bias)]
+            outs = Fn.StyleMLP.apply(torch.cat([c, z], 1), n, *params)
             for i, dec in enumerate(self.dec1):
-                out = dec.run(out, s, out_pad=0 if i == n - 1 else 1)
+                out = dec.run(out, None, out_pad=0 if i == n - 1 else 1, gb=outs[1 + i])
         else:
             for i, dec in enumerate(self.dec1):
                 out = dec.run(out, out_pad=0 if i == n - 1 else 1)
@@ -242,7 +245,8 @@ class Decoder(nn.Module):
                                     nn.Linear(256, self.dim_add * n_blocks))
 
     def run(self, z_c, z, c):
-        s = self.linear(torch.cat([c, z], 1))
+        params = [p for i in (0, 2, 4) for p in (self.linear[i].weight, self.linear[i].bias)]
+        s = Fn.StyleMLP.apply(torch.cat([c, z], 1), 0, *params)[0]
         out = z_c
         n = len(self.dec1)
         for i, (dec, zi) in enumerate(zip(self.dec1, torch.split(s, self.dim_add, dim=1))):
@@ -321,7 +325,7 @@ class ContentDiscriminator(nn.Module):
             x = self.model[i].run(x, out_pad=1 if i < 2 else 0)
         feat = Fn.GlobalAvgPool.apply(x)[:, :self.dim]     # GAP commutes with the 1x1 conv + bias
         head = self.model[4]
-        return F.linear(feat, head.weight.flatten(1), head.bias)
+        return Fn.Linear.apply(feat, head.weight, head.bias)
 
     def forward(self, x):
         return self.run(to_padded(x, CONTENT_PAD))
@@ -400,11 +404,14 @@ class Discriminator(nn.Module):
         n = len(self.model)
         for i, blk in enumerate(self.model):
             x = blk.run(x, out_pad=0 if i == n - 1 else 1)
-        # heads: 2 x (S*S*C) MACs per logit — host-side glue on the tiny [N,S,S,C] feature map
+        w2 = self.conv2.weight
+        if x.shape[1] == w2.shape[2] and x.shape[2] == w2.shape[3] and w2.shape[0] <= 8 and x.shape[1] <= 12:
+            # both heads in one kernel each way (mt_dis_head_fwd / _bwd): the k x k conv covers the whole map
+            return Fn.DisHead.apply(x, self.conv1.weight, w2)
+        # other image sizes than crop_size: the general form on the tiny [N,S,S,C] feature map
         h = x.float()[..., :self.output_dim]
         out = torch.einsum('nhwc,c->nhw', h, self.conv1.weight[0, :, 0, 0])
         out = F.pad(out, (1, 1, 1, 1)).unsqueeze(1)           # conv1 has padding=1: exact-zero border
-        w2 = self.conv2.weight
         if h.shape[1] == w2.shape[2] and h.shape[2] == w2.shape[3]:
             cls = torch.einsum('nhwc,dchw->nd', h, w2)
         else:

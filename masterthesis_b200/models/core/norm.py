@@ -1,7 +1,21 @@
-"""Parameter holders for the decoder norms (reference src/models/core/norm.py:5-33).  The
-arithmetic runs in csrc/ew_norm.cu through the enclosing block's fused plan."""
+"""The decoder norms (reference src/models/core/norm.py:5-33).  Inside the networks their arithmetic runs
+through the enclosing block's fused plan (csrc/ew_norm.cu via functional.ConvNormAct / ResBlock); called
+on their own, as the reference's modules can be, `forward` runs the same kernels un-fused on NCHW fp32
+tensors (layout conversion at the edge)."""
 import torch
 import torch.nn as nn
+
+from ... import functional as Fn
+
+
+def _nhwc(x):
+    from .blocks import to_padded
+    return to_padded(x, 0)
+
+
+def _nchw(y, C):
+    from .blocks import from_padded
+    return from_padded(y, C)
 
 
 class LayerNorm(nn.Module):
@@ -16,6 +30,12 @@ class LayerNorm(nn.Module):
             self.weight = nn.Parameter(torch.ones(n_out, 1, 1))
             self.bias = nn.Parameter(torch.zeros(n_out, 1, 1))
 
+    def forward(self, x):
+        """F.layer_norm(x, x.shape[1:], weight.expand, bias.expand) (norm.py:16-21); x NCHW fp32"""
+        C = x.shape[1]
+        w, b = (self.weight, self.bias) if self.affine else (None, None)
+        return _nchw(Fn.NormAct.apply(_nhwc(x), 'layer', w, b, None, C), C)
+
 
 class AdaptiveInstanceNorm(nn.Module):
     """(1 + w) * InstanceNorm(x) + b with (w, b) = chunk(fc(s), 2)   (norm.py:23-33)."""
@@ -28,3 +48,13 @@ class AdaptiveInstanceNorm(nn.Module):
     def modulation(self, s):
         """fc(s): [N, 2C] fp32 = (weight | bias); consumed by the AdaIN kernels."""
         return self.fc(s)
+
+    def forward(self, x, s):
+        """x NCHW fp32, s [N, style_dim] -> (1 + w) * IN(x) + b   (norm.py:29-33)"""
+        C = x.shape[1]
+        gb = self.modulation(s)
+        if C % 8:      # the kernels address (weight | bias) at the stored channel count
+            Cs = (C + 7) // 8 * 8
+            z = gb.new_zeros(gb.shape[0], Cs - C)
+            gb = torch.cat((gb[:, :C], z, gb[:, C:], z), 1)
+        return _nchw(Fn.NormAct.apply(_nhwc(x), 'adain', gb, None, None, C), C)

@@ -93,9 +93,17 @@ class Model(ABC, nn.Module):
         self.img_a, self.img_b = self.img[:B], self.img[B:]
         self.cls_a, self.cls_b = self.c_org[:B], self.c_org[B:]
 
+    def _begin_iteration(self):
+        self._scalars = {}          # loss name -> 0-dim device tensor (general torch formulation)
+        self._raw_used = set()      # raw loss terms written by the loss kernels (AdaINModel.SLOTS)
+
     def _loss_vector(self):
         keys = list(self._scalars)
         return keys, torch.stack([self._scalars[k].float().reshape(()) for k in keys])
+
+    def _named_losses(self, keys, values):
+        """(name, python float) pairs of the iteration's losses from the vector read back from the device"""
+        return zip(keys, values)
 
     def _run_iteration(self, body, kind='main'):
         """Run `body()` (enqueues one full training iteration and fills self._scalars with 0-dim
@@ -104,16 +112,26 @@ class Model(ABC, nn.Module):
         from ..optim import GraphHyper
         from .core import blocks
         if not self.use_graph or self.rng is not None:
-            self._scalars = {}
+            self._begin_iteration()
             body()
             keys, vec = self._loss_vector()
         elif kind not in self._graphs and self._eager_iters.get(kind, 0) < self.graph_warmup:
             self._eager_iters[kind] = self._eager_iters.get(kind, 0) + 1
-            self._scalars = {}
+            self._begin_iteration()
             body()
             keys, vec = self._loss_vector()
         else:
+            # a captured graph holds the raw addresses of the optimizers' flat buckets: if one of them was
+            # re-allocated since (load() of an optimizer checkpoint, a network moved or re-built), drop the
+            # graphs and capture again
+            gen = tuple(getattr(opt, 'generation', 0) for opt in self.optimizer.values())
+            if any(rec.get('gen') != gen for rec in self._graphs.values()):
+                self._graphs = {}
             if kind not in self._graphs:
+                for opt in self.optimizer.values():        # buckets exist (and `generation` is final) before capture
+                    if hasattr(opt, '_ensure_flat'):
+                        opt._ensure_flat()
+                gen = tuple(getattr(opt, 'generation', 0) for opt in self.optimizer.values())
                 blocks.invalidate_packs()
                 ctx = GraphHyper(self.device)
                 for opt in self.optimizer.values():
@@ -123,13 +141,14 @@ class Model(ABC, nn.Module):
                 torch.cuda.synchronize()
                 try:
                     with torch.cuda.graph(graph):
-                        self._scalars = {}
+                        self._begin_iteration()
                         body()
                         keys, vec = self._loss_vector()
                 finally:
                     for opt in self.optimizer.values():
                         opt.graph_ctx = None
-                self._graphs[kind] = dict(graph=graph, ctx=ctx, keys=keys, vec=vec, launches=ops.launches() - l0)
+                self._graphs[kind] = dict(graph=graph, ctx=ctx, keys=keys, vec=vec, launches=ops.launches() - l0,
+                                          gen=gen)
             else:
                 self._graphs[kind]['ctx'].advance()
                 ops._count(self._graphs[kind]['launches'])
@@ -137,7 +156,7 @@ class Model(ABC, nn.Module):
             g['ctx'].upload()
             g['graph'].replay()
             keys, vec = g['keys'], g['vec']
-        for k, v in zip(keys, vec.tolist()):     # the one host sync of the iteration
+        for k, v in self._named_losses(keys, vec.tolist()):     # the one host sync of the iteration
             if k == 'loss_dc':                   # reference keeps it outside self.loss (adain_model.py:142)
                 self.loss_dc = v
             else:
@@ -216,7 +235,9 @@ class Model(ABC, nn.Module):
         torch.save({opt: self.optimizer[opt].state_dict() for opt in self.optimizer}, path)
 
     def load(self, checkpoint, opt_ckpt=None):
+        # captured graphs hold packed weights and the addresses of the optimizers' buckets: start over
         self.reset_sampling_graphs()
+        self.reset_graph()
         if checkpoint is not None:
             ckpt = torch.load(checkpoint, map_location='cpu')
             for net in ckpt:

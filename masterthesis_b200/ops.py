@@ -712,9 +712,10 @@ def rgb_head_bwd(dy, y, x, w, Co):
 
 
 @_checked
-def sumsq_interior(x_pad, pad):
+def sumsq_interior(x_pad, pad, out=None):
     N, Hp, Wp, C = x_pad.shape
-    out = _T.empty((), dtype=torch.float32, device=x_pad.device)
+    if out is None:
+        out = _T.empty((), dtype=torch.float32, device=x_pad.device)
     L = _lib.lib()
     parts = L.mt_sumsq_interior_parts(N, Hp - 2 * pad, Wp - 2 * pad, C)
     scratch = _T.empty(parts, dtype=torch.float32, device=x_pad.device)
@@ -747,3 +748,170 @@ def bias_grad(dy, C, into=None):
           "colsum_into")
     _count()
     return None if into is not None else out
+
+
+# ----------------------------------------------------------------------------- small fp32 layers, heads, losses
+def _ptr_array(tensors):
+    """host array of device pointers (the `const float* const*` arguments of the C ABI)"""
+    arr = (ctypes.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+    return arr
+
+
+def _f32c(t):
+    assert t.dtype == torch.float32 and t.is_contiguous(), (t.dtype, t.is_contiguous())
+    return t
+
+
+@_checked
+def linear_fwd(x, w, b=None, act=None):
+    """nn.Linear (+ReLU): x [N, In] fp32, w [Out, In], b [Out] -> [N, Out]"""
+    _require_cuda(x)
+    N, In = x.shape
+    Out = w.shape[0]
+    y = _T.empty((N, Out), dtype=torch.float32, device=x.device)
+    check(_lib.lib().mt_linear_fwd(_p(_f32c(x)), _p(_f32c(w)), _p(b), N, In, Out, ACT[act], _p(y), _stream()),
+          "linear_fwd")
+    _count()
+    return y
+
+
+def linear_bwd(dy, y, x, w, act=None, need_dx=True, dw_into=None, db_into=None, has_bias=True, need_params=True):
+    """-> (dx | None, dw | None, db | None); dw / db are None when added into the given .grad buffers
+    (both buffers must then be given, or the layer has no bias) or when not needed"""
+    N, In = x.shape
+    Out = w.shape[0]
+    dev = x.device
+    acc = need_params and dw_into is not None and (db_into is not None or not has_bias)
+    dx = _T.empty((N, In), dtype=torch.float32, device=dev) if need_dx else None
+    dw = db = None
+    if need_params:
+        dw = dw_into if acc else _T.empty((Out, In), dtype=torch.float32, device=dev)
+        db = (db_into if acc else _T.empty((Out,), dtype=torch.float32, device=dev)) if has_bias else None
+    check(_lib.lib().mt_linear_bwd(_p(_f32c(dy)), _p(y), _p(_f32c(x)), _p(_f32c(w)), N, In, Out, ACT[act], _p(dx),
+                                   _p(dw), _p(db), int(acc), 0, _stream()), "linear_bwd")
+    _count()
+    return dx, (None if acc else dw), (None if acc or not has_bias else db)
+
+
+def style_mlp_fwd(cz, mlp, heads):
+    """mlp: [(w, b)] x 3, heads: [(w, b)] x K -> (h1, h2, s, [gb_k])   (mt_style_mlp_fwd)"""
+    _require_cuda(cz)
+    N, in_dim = cz.shape
+    hid, style_dim = mlp[0][0].shape[0], mlp[2][0].shape[0]
+    K = len(heads)
+    head_out = heads[0][0].shape[0] if K else 0
+    dev = cz.device
+    h1 = _T.empty((N, hid), dtype=torch.float32, device=dev)
+    h2 = _T.empty((N, hid), dtype=torch.float32, device=dev)
+    s = _T.empty((N, style_dim), dtype=torch.float32, device=dev)
+    gb = [_T.empty((N, head_out), dtype=torch.float32, device=dev) for _ in range(K)]
+    check(_lib.lib().mt_style_mlp_fwd(
+        _p(_f32c(cz)), N, in_dim, hid, style_dim, _ptr_array([_f32c(w) for w, _ in mlp]),
+        _ptr_array([b for _, b in mlp]), K, head_out, _ptr_array([_f32c(w) for w, _ in heads]),
+        _ptr_array([b for _, b in heads]), _p(h1), _p(h2), _p(s), _ptr_array(gb), _stream()), "style_mlp_fwd")
+    _count(3 + K)
+    return h1, h2, s, gb
+
+
+def style_mlp_bwd(cz, h1, h2, s, mlp_w, head_w, dgb, ds_in, grads_into, need_dcz):
+    """dgb: list of K tensors or None; ds_in: [N, style_dim] or None.  grads_into: None, or
+    (d_mlp_w[3], d_mlp_b[3], d_head_w[K], d_head_b[K]) .grad buffers to add into.
+    -> (dcz | None, d_mlp_w, d_mlp_b, d_head_w, d_head_b) with the gradient lists None when accumulated."""
+    N, in_dim = cz.shape
+    hid, style_dim = mlp_w[0].shape[0], mlp_w[2].shape[0]
+    K = len(head_w)
+    head_out = head_w[0].shape[0] if K else 0
+    dev = cz.device
+    acc = grads_into is not None
+    if acc:
+        d_mw, d_mb, d_hw, d_hb = grads_into
+    else:
+        d_mw = [_T.empty(tuple(w.shape), dtype=torch.float32, device=dev) for w in mlp_w]
+        d_mb = [_T.empty((w.shape[0],), dtype=torch.float32, device=dev) for w in mlp_w]
+        # a head without incoming gradient keeps a zero gradient
+        d_hw = [(_T.empty if dgb[k] is not None else torch.zeros)(tuple(w.shape), dtype=torch.float32, device=dev)
+                for k, w in enumerate(head_w)]
+        d_hb = [(_T.empty if dgb[k] is not None else torch.zeros)((w.shape[0],), dtype=torch.float32, device=dev)
+                for k, w in enumerate(head_w)]
+    ds = _T.empty((N, style_dim), dtype=torch.float32, device=dev)
+    dh2 = _T.empty((N, hid), dtype=torch.float32, device=dev)
+    dh1 = _T.empty((N, hid), dtype=torch.float32, device=dev)
+    dcz = _T.empty((N, in_dim), dtype=torch.float32, device=dev) if need_dcz else None
+    dgb = [None if g is None else _f32c(g.contiguous()) for g in (dgb or [])]
+    check(_lib.lib().mt_style_mlp_bwd(
+        _p(cz), _p(h1), _p(h2), _p(s), N, in_dim, hid, style_dim, _ptr_array(list(mlp_w)), K, head_out,
+        _ptr_array(list(head_w)), _ptr_array(dgb), _p(None if ds_in is None else _f32c(ds_in.contiguous())),
+        _ptr_array(d_mw), _ptr_array(d_mb), _ptr_array(d_hw), _ptr_array(d_hb), _p(ds), _p(dh2), _p(dh1), _p(dcz),
+        int(acc), _stream()), "style_mlp_bwd")
+    _count(3 + K)
+    if acc:
+        return dcz, None, None, None, None
+    return dcz, d_mw, d_mb, d_hw, d_hb
+
+
+@_checked
+def dis_head_fwd(h, w1, w2, C, nd):
+    """h [N,S,S,Cs] bf16 dense -> (out [N,1,S+2,S+2] fp32, cls [N,nd] fp32)   (networks.py:373-383)"""
+    N, S, S2, Cs = h.shape
+    assert S == S2 and h.is_contiguous() and tuple(w2.shape) == (nd, C, S, S), (h.shape, w2.shape)
+    out = _T.empty((N, 1, S + 2, S + 2), dtype=torch.float32, device=h.device)
+    cls = _T.empty((N, nd), dtype=torch.float32, device=h.device)
+    check(_lib.lib().mt_dis_head_fwd(_p(h), _p(_f32c(w1)), _p(_f32c(w2)), N, S, Cs, C, nd, _p(out), _p(cls),
+                                     _stream()), "dis_head_fwd")
+    _count()
+    return out, cls
+
+
+def dis_head_bwd(dout, dcls, h, w1, w2, C, nd, cls_first=0, need_dh=True, dw_into=None, need_dw=True):
+    """-> (dh | None, dw1 | None, dw2 | None); dw_into = (w1.grad, w2.grad) adds in place"""
+    N, S, _, Cs = h.shape
+    dev = h.device
+    dh = _T.empty_like(h) if need_dh else None
+    acc = dw_into is not None
+    dw1 = dw2 = None
+    if need_dw:
+        dw1, dw2 = dw_into if acc else (_T.empty((C,), dtype=torch.float32, device=dev),
+                                        _T.empty(tuple(w2.shape), dtype=torch.float32, device=dev))
+    check(_lib.lib().mt_dis_head_bwd(_p(_f32c(dout)), _p(_f32c(dcls)), _p(h), _p(w1), _p(w2), N, S, Cs, C, nd,
+                                     int(cls_first), _p(dh), _p(dw1), _p(dw2), int(acc), _stream()), "dis_head_bwd")
+    _count()
+    return dh, (None if acc else dw1), (None if acc else dw2)
+
+
+def loss_bce_logits(x, target, gscale, loss_out, want_grad=True, dx_out=None):
+    """mean BCE-with-logits of x (fp32, any shape, contiguous) against `target` (same-shape tensor or a python
+    constant); loss_out: a 1-element fp32 device view that receives the mean.  -> dx = gscale * dloss/dx
+    (written into `dx_out`, a contiguous view of x's shape, when given)"""
+    n = x.numel()
+    t_ptr, t_const = (_p(_f32c(target)), 0.0) if torch.is_tensor(target) else (None, float(target))
+    dx = (dx_out if dx_out is not None else _T.empty_like(x)) if want_grad else None
+    assert dx is None or (dx.is_contiguous() and dx.numel() == n)
+    check(_lib.lib().mt_loss_bce_logits(_p(_f32c(x)), t_ptr, t_const, n, float(gscale), _p(loss_out), _p(dx),
+                                        _stream()), "loss_bce_logits")
+    _count()
+    return dx
+
+
+def loss_l1(a, b, weight, loss_out, want_grad=True):
+    """loss_out[0] = weight * mean|a - b|; -> da = weight / n * sign(a - b)"""
+    n = a.numel()
+    assert b.numel() == n
+    L = _lib.lib()
+    parts = L.mt_loss_l1_parts(n)
+    scratch = _T.empty(parts, dtype=torch.float32, device=a.device)
+    da = _T.empty_like(a) if want_grad else None
+    check(L.mt_loss_l1(_p(_f32c(a)), _p(_f32c(b)), n, float(weight), float(weight), _p(loss_out), _p(da), _p(scratch),
+                       parts, _stream()), "loss_l1")
+    _count(2)
+    return da
+
+
+def loss_kl_normal(mu, logvar, gscale, loss_out, want_grad=True):
+    """loss_out[0] = -0.5 * sum(1 + logvar - mu^2 - exp(logvar)); -> (gscale * dloss/dmu, gscale * dloss/dlogvar)"""
+    n = mu.numel()
+    dmu = _T.empty_like(mu) if want_grad else None
+    dlv = _T.empty_like(logvar) if want_grad else None
+    check(_lib.lib().mt_loss_kl_normal(_p(_f32c(mu)), _p(_f32c(logvar)), n, float(gscale), _p(loss_out), _p(dmu), _p(dlv),
+                                       _stream()), "loss_kl_normal")
+    _count()
+    return dmu, dlv

@@ -44,9 +44,11 @@ class FlatAdam(torch.optim.Optimizer):
         params = list(params)
         defaults = dict(lr=lr, betas=(float(betas[0]), float(betas[1])), eps=eps,
                         weight_decay=weight_decay, amsgrad=False, maximize=False, foreach=None,
-                        capturable=False, differentiable=False, fused=None)
+                        capturable=False, differentiable=False, fused=None, decoupled_weight_decay=False)
         super().__init__(params, defaults)
         self._flat = None
+        self.generation = 0        # bumped whenever the flat buckets are (re)allocated: captured graphs that
+                                   # hold the old addresses must be dropped (Model._run_iteration checks it)
         self.grad_scale = 1.0      # set to 1/world by the data-parallel wrapper
         self.graph_ctx = None      # GraphHyper while an iteration is being captured
 
@@ -87,6 +89,7 @@ class FlatAdam(torch.optim.Optimizer):
             st.setdefault('step', torch.tensor(0.0))
         self._flat = dict(p=flat_p, g=flat_g, m=flat_m, v=flat_v, n=n, device=dev,
                           ptrs=[p.data_ptr() for p in ps])
+        self.generation += 1
 
     @property
     def grad_bucket(self):

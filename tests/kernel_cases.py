@@ -337,7 +337,160 @@ def big_mean_norm_case(seed=0):
     return {"fwd": rel(from_nhwc(out, C), F.instance_norm(x))}
 
 
+def module_forward_case(seed=0):
+    """The reference-compatible `forward` of the norm / noise modules on NCHW fp32 tensors (norm.py:16-21,
+    29-33, misc.py:22-26) vs torch, with gradients."""
+    from masterthesis_b200.models.core.misc import GaussianNoiseLayer
+    from masterthesis_b200.models.core.norm import AdaptiveInstanceNorm, LayerNorm
+    torch.manual_seed(seed)
+    N, C, H, W = 2, 40, 12, 20
+    r = {}
+    x = bf(torch.randn(N, C, H, W, device=DEV) * 2 + 0.3)
+    ln = LayerNorm(C).to(DEV)
+    with torch.no_grad():
+        ln.weight.copy_(torch.rand(C, 1, 1) + 0.5); ln.bias.copy_(torch.randn(C, 1, 1))
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ya = ln(xa)
+    yb = F.layer_norm(xb, xb.shape[1:], ln.weight.detach().expand(C, H, W), ln.bias.detach().expand(C, H, W))
+    g = bf(torch.randn_like(yb))
+    ya.backward(g); yb.backward(g)
+    r["ln_fwd"], r["ln_dx"] = rel(ya.detach(), yb.detach()), rel(xa.grad, xb.grad)
+    ad = AdaptiveInstanceNorm(C, 16).to(DEV)
+    s_ = torch.randn(N, 16, device=DEV)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ya = ad(xa, s_)
+    h = ad.fc(s_).detach()
+    yb = (1 + h[:, :C, None, None]) * F.instance_norm(xb) + h[:, C:, None, None]
+    ya.backward(g); yb.backward(g)
+    r["adain_fwd"], r["adain_dx"] = rel(ya.detach(), yb.detach()), rel(xa.grad, xb.grad)
+    nz = GaussianNoiseLayer().to(DEV)
+    draw = torch.randn(N, C, H, W)
+    r["noise_fwd"] = rel(nz(x, rng=lambda shape: draw), bf(x + draw.to(DEV)))
+    nz.eval()
+    r["noise_eval_identity"] = 0.0 if nz(x) is x else 1.0
+    return r
+
+
+def linear_case(N=32, In=12, Out=256, act="relu", seed=0):
+    """mt_linear_fwd / _bwd vs F.linear (+ReLU) with autograd, incl. the accumulate-into-.grad form."""
+    torch.manual_seed(seed)
+    x = torch.randn(N, In, device=DEV, requires_grad=True)
+    w = (torch.randn(Out, In, device=DEV) * 0.2).requires_grad_(True)
+    b = torch.randn(Out, device=DEV).requires_grad_(True)
+    y_ref = F.linear(x, w, b)
+    if act == "relu":
+        y_ref = F.relu(y_ref)
+    dy = torch.randn_like(y_ref)
+    y_ref.backward(dy)
+    y = ops.linear_fwd(x.detach(), w.detach(), b.detach(), act)
+    dx, dw, db = ops.linear_bwd(dy, y if act else None, x.detach(), w.detach(), act)
+    r = {"fwd": rel(y, y_ref.detach()), "dx": rel(dx, x.grad), "dw": rel(dw, w.grad), "db": rel(db, b.grad)}
+    gw, gb_ = torch.ones_like(w), torch.ones_like(b)
+    ops.linear_bwd(dy, y if act else None, x.detach(), w.detach(), act, True, gw, gb_)
+    r["into"] = max(rel(gw - 1, w.grad), rel(gb_ - 1, b.grad))
+    return r
+
+
+def style_mlp_case(N=32, K=4, C=256, seed=0):
+    """functional.StyleMLP (mt_style_mlp_fwd / _bwd) vs the nn.Sequential of the reference decoder
+    (networks.py:256-261) followed by the fc of K AdaIN blocks (norm.py:27), with autograd."""
+    from masterthesis_b200 import functional as Fn
+    torch.manual_seed(seed)
+    mlp = torch.nn.Sequential(torch.nn.Linear(12, 256), torch.nn.ReLU(), torch.nn.Linear(256, 256), torch.nn.ReLU(),
+                              torch.nn.Linear(256, C)).to(DEV)
+    fcs = [torch.nn.Linear(C, 2 * C).to(DEV) for _ in range(K)]
+    cz = torch.randn(N, 12, device=DEV, requires_grad=True)
+    s_ref = mlp(cz)
+    gb_ref = [fc(s_ref) for fc in fcs]
+    proj = [torch.randn_like(g) for g in gb_ref]
+    ps = torch.randn_like(s_ref) * (0.0 if K else 1.0)       # the AdaIN decoder uses s only through the heads
+    ((s_ref * ps).sum() + sum((g * p).sum() for g, p in zip(gb_ref, proj))).backward()
+    ref_grads = [p.grad.clone() for p in list(mlp.parameters()) + [q for fc in fcs for q in fc.parameters()]]
+    dcz_ref = cz.grad.clone()
+    for p in list(mlp.parameters()) + [q for fc in fcs for q in fc.parameters()]:
+        p.grad = None
+    cz.grad = None
+    params = [p for i in (0, 2, 4) for p in (mlp[i].weight, mlp[i].bias)] + [p for fc in fcs for p in (fc.weight, fc.bias)]
+    outs = Fn.StyleMLP.apply(cz, K, *params)
+    r = {"s": rel(outs[0].detach(), s_ref.detach()),
+         "gb": max(rel(a.detach(), b_.detach()) for a, b_ in zip(outs[1:], gb_ref))}
+    if K:
+        sum((g * p).sum() for g, p in zip(outs[1:], proj)).backward()     # s itself receives NO gradient
+    else:
+        (outs[0] * ps).sum().backward()
+    mine = [p.grad for p in list(mlp.parameters()) + [q for fc in fcs for q in fc.parameters()]]
+    r["dparams"] = max(rel(a, b_) for a, b_ in zip(mine, ref_grads))
+    r["dcz"] = rel(cz.grad, dcz_ref)
+    return r
+
+
+def dis_head_case(N=6, S=4, C=1024, nd=4, seed=0):
+    """functional.DisHead (mt_dis_head_fwd / _bwd) vs Conv2d(C,1,1,padding=1) and Conv2d(C,nd,S)+GAP."""
+    from masterthesis_b200 import functional as Fn
+    torch.manual_seed(seed)
+    h = bf(torch.randn(N, C, S, S, device=DEV))
+    w1 = (torch.randn(1, C, 1, 1, device=DEV) * 0.05).requires_grad_(True)
+    w2 = (torch.randn(nd, C, S, S, device=DEV) * 0.02).requires_grad_(True)
+    h_ref = h.clone().requires_grad_(True)
+    out_ref = F.conv2d(h_ref, w1, padding=1)
+    cls_ref = F.conv2d(h_ref, w2).mean((2, 3))
+    do, dc = torch.randn_like(out_ref), torch.randn_like(cls_ref)
+    ((out_ref * do).sum() + (cls_ref * dc).sum()).backward()
+    ref = (w1.grad.clone(), w2.grad.clone())
+    w1.grad = w2.grad = None
+    hn = to_nhwc(h).requires_grad_(True)
+    out, cls = Fn.DisHead.apply(hn, w1, w2)
+    r = {"out": rel(out.detach(), out_ref.detach()), "cls": rel(cls.detach(), cls_ref.detach())}
+    ((out * do).sum() + (cls * dc).sum()).backward()
+    r["dh"] = rel(from_nhwc(hn.grad, C), h_ref.grad)
+    r["dw1"], r["dw2"] = rel(w1.grad, ref[0]), rel(w2.grad, ref[1])
+    return r
+
+
+def loss_case(seed=0):
+    """mt_loss_bce_logits / mt_loss_l1 / mt_loss_kl_normal: value and gradient vs torch."""
+    torch.manual_seed(seed)
+    r = {}
+    buf = torch.zeros(4, device=DEV)
+    x = (torch.randn(16, 1, 6, 6, device=DEV) * 3).requires_grad_(True)
+    for name, tgt in (("bce_const1", 1.0), ("bce_const0", 0.0), ("bce_tensor", (torch.rand(16, 1, 6, 6, device=DEV) > 0.5).float())):
+        x.grad = None
+        t = torch.full_like(x, tgt) if not torch.is_tensor(tgt) else tgt
+        ref = F.binary_cross_entropy_with_logits(x, t)
+        (ref * 5.0).backward()
+        dx = ops.loss_bce_logits(x.detach(), tgt, 5.0, buf[0:1])
+        r[name] = max(rel(buf[0], ref.detach()), rel(dx, x.grad))
+    a = (torch.rand(4, 3, 64, 64, device=DEV) * 2 - 1).requires_grad_(True)
+    b = torch.rand(4, 3, 64, 64, device=DEV) * 2 - 1
+    ref = F.l1_loss(a, b) * 10.0
+    ref.backward()
+    da = ops.loss_l1(a.detach(), b, 10.0, buf[1:2])
+    r["l1"] = max(rel(buf[1], ref.detach()), rel(da, a.grad))
+    a2 = torch.randn(7, 9, device=DEV).requires_grad_(True)      # odd element count: the scalar tail
+    b2 = torch.randn(7, 9, device=DEV)
+    ref = F.l1_loss(a2, b2) * 2.0
+    ref.backward()
+    da2 = ops.loss_l1(a2.detach(), b2, 2.0, buf[1:2])
+    r["l1_tail"] = max(rel(buf[1], ref.detach()), rel(da2, a2.grad))
+    mu = torch.randn(16, 8, device=DEV).requires_grad_(True)
+    lv = (torch.randn(16, 8, device=DEV) * 0.5).requires_grad_(True)
+    ref = torch.sum(1 + lv - mu.pow(2) - lv.exp()) * (-0.5)
+    (ref * 0.01).backward()
+    dmu, dlv = ops.loss_kl_normal(mu.detach(), lv.detach(), 0.01, buf[2:3])
+    r["kl"] = max(rel(buf[2], ref.detach()), rel(dmu, mu.grad), rel(dlv, lv.grad))
+    return r
+
+
 CASES = {
+    "linear_relu": linear_case,
+    "linear_plain_n3": lambda: linear_case(3, 256, 8, None),
+    "linear_wide": lambda: linear_case(16, 256, 1024, None),
+    "style_mlp": style_mlp_case,
+    "style_mlp_base": lambda: style_mlp_case(16, 0, 1024),
+    "dis_head": dis_head_case,
+    "dis_head_s8": lambda: dis_head_case(4, 8, 128, 3),
+    "losses": loss_case,
+    "module_forwards": module_forward_case,
     "misc_ops": misc_case,
     "misc_ops_c256": lambda: misc_case(2, 256, 16, 16),
     "adam_flat": adam_case,
