@@ -110,6 +110,7 @@ class FlatAdam(torch.optim.Optimizer):
     def load_state_dict(self, state_dict):
         super().load_state_dict(state_dict)
         self._flat = None                            # rebuild views around the loaded state
+        self._steps = None                           # re-read the step count from the loaded state
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -145,8 +146,23 @@ class FlatAdam(torch.optim.Optimizer):
         return None
 
     def _step_count(self):
-        st0 = self.state[self._params()[0]]
-        return int(st0['step'].item() if torch.is_tensor(st0['step']) else st0['step'])
+        """Steps taken so far.  Kept as one python int (all parameters of a bucket step together); the
+        per-parameter `step` entries torch.optim.Adam keeps are materialised by state_dict()."""
+        if getattr(self, '_steps', None) is None:
+            st0 = self.state[self._params()[0]]
+            v = st0.get('step', 0.0)
+            self._steps = int(v.item() if torch.is_tensor(v) else v)
+        return self._steps
+
+    def state_dict(self):
+        """torch.optim.Adam's layout: every parameter gets its OWN `step` tensor (a tensor shared between
+        parameters would be incremented once per parameter by torch's foreach Adam after load_state_dict)."""
+        self._ensure_flat() if self._params()[0].is_cuda else None
+        n = float(self._step_count()) if self.state else 0.0
+        for p in self._params():
+            if p in self.state:
+                self.state[p]['step'] = torch.tensor(n)
+        return super().state_dict()
 
     def _host_advance(self):
         """Host half of one step: advance the step count and autograd's version counters (the kernel
@@ -155,9 +171,7 @@ class FlatAdam(torch.optim.Optimizer):
         ps = self._params()
         g0 = self.param_groups[0]
         step = self._step_count() + 1
-        step_t = torch.tensor(float(step))
-        for p in ps:
-            self.state[p]['step'] = step_t
+        self._steps = step
         torch._C._autograd._unsafe_set_version_counter(ps, [p._version + 1 for p in ps])
         b1, b2 = g0['betas']
         bc1 = 1.0 - b1 ** step

@@ -94,23 +94,29 @@ def convT_case(N, Cin, Cout, H, W, bias=True, act=None, seed=0):
 
 
 def norm_case(mode, N, C, H, W, act, residual=False, noise=False, seed=0):
+    """The reference runs in float64: torch's fp32 CUDA F.layer_norm backward is itself off by 40 % of the
+    gradient range at [32, 64, 256, 256] (32 rows of 4.2 M normalised elements; checked against the
+    closed-form float64 gradient in tests/tools/debug_ln.py), so it cannot be the yardstick there."""
     torch.manual_seed(seed)
     x = bf(torch.randn(N, C, H, W, device=DEV) * 2 + 0.5)
-    x_ref = x.clone().requires_grad_(True)
+    x_ref = x.double().requires_grad_(True)
     gb = lw = lb = None
     params = []
     if mode == "adain":
         gb = (torch.randn(N, 2 * C, device=DEV) * 0.5).requires_grad_(True)
         params = [gb]
-        y_ref = (1 + gb[:, :C, None, None]) * F.instance_norm(x_ref) + gb[:, C:, None, None]
+        gbd = gb.double()
+        y_ref = (1 + gbd[:, :C, None, None]) * F.instance_norm(x_ref) + gbd[:, C:, None, None]
     elif mode == "instance":
         y_ref = F.instance_norm(x_ref)
     else:
         lw = (torch.rand(C, device=DEV) + 0.5).requires_grad_(True)
         lb = torch.randn(C, device=DEV).requires_grad_(True)
         params = [lw, lb]
-        y_ref = F.layer_norm(x_ref, x_ref.shape[1:], lw.view(C, 1, 1).expand(C, H, W),
-                             lb.view(C, 1, 1).expand(C, H, W))
+        # F.layer_norm over (C,H,W) with per-channel affine (norm.py:16-21), written out in float64
+        mean = x_ref.mean((1, 2, 3), keepdim=True)
+        var = x_ref.var((1, 2, 3), unbiased=False, keepdim=True)
+        y_ref = (x_ref - mean) * (var + 1e-5).rsqrt() * lw.double().view(1, C, 1, 1) + lb.double().view(1, C, 1, 1)
     if act == "relu":
         y_ref = F.relu(y_ref)
     elif act == "lrelu":
@@ -122,8 +128,8 @@ def norm_case(mode, N, C, H, W, act, residual=False, noise=False, seed=0):
     if noise:
         nz = torch.randn(N, C, H, W, device=DEV)
         y_ref = y_ref + nz
-    g = bf(torch.randn_like(y_ref))
-    y_ref.backward(g)
+    g = bf(torch.randn(y_ref.shape, device=DEV))
+    y_ref.backward(g.double())
 
     xn = to_nhwc(x)
     stats = ops.plane_stats(xn)
@@ -412,8 +418,9 @@ def style_mlp_case(N=32, K=4, C=256, seed=0):
     cz.grad = None
     params = [p for i in (0, 2, 4) for p in (mlp[i].weight, mlp[i].bias)] + [p for fc in fcs for p in (fc.weight, fc.bias)]
     outs = Fn.StyleMLP.apply(cz, K, *params)
-    r = {"s": rel(outs[0].detach(), s_ref.detach()),
-         "gb": max(rel(a.detach(), b_.detach()) for a, b_ in zip(outs[1:], gb_ref))}
+    r = {"s": rel(outs[0].detach(), s_ref.detach())}
+    if K:
+        r["gb"] = max(rel(a.detach(), b_.detach()) for a, b_ in zip(outs[1:], gb_ref))
     if K:
         sum((g * p).sum() for g, p in zip(outs[1:], proj)).backward()     # s itself receives NO gradient
     else:

@@ -484,9 +484,9 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
     same weights, same batch, same torch seed (device Philox draws), `iters` iterations including
     the 2 eager warm-up iterations, the capture and several replays, with a changing learning rate."""
     out = {}
-    # a second eager run measures the run-to-run noise floor (fp32 atomics in the split-K weight
-    # gradients and in the plane reductions make two identical runs differ, and GAN dynamics amplify
-    # it over the iterations): the graph must stay within that floor, not within a fixed epsilon
+    # every sum of the iteration runs in a fixed order (no atomics) and the captured iteration launches the
+    # same kernels as the eager one, so the three runs must agree exactly; the second eager run separates
+    # "not reproducible" from "graph differs from eager" if that ever breaks
     for mode in ('eager', 'eager2', 'graph'):
         m, _ = make_model(dim, size, B, nd, seed, **flags)
         m.use_graph = mode == 'graph'
@@ -506,12 +506,12 @@ def graph_vs_eager(dim=8, size=64, B=2, nd=4, seed=3, iters=6, **flags):
     r = {}
     for it, (he, h2, hg) in enumerate(zip(out['eager'][0], out['eager2'][0], out['graph'][0])):
         for k in he:
-            scale = max(1.0, abs(he[k]))
-            r[f'loss_it{it}.{k}'] = max(0.0, abs(he[k] - hg[k]) / scale - 3.0 * abs(he[k] - h2[k]) / scale)
+            scale = max(1e-6, abs(he[k]))
+            r[f'loss_it{it}.{k}'] = abs(he[k] - hg[k]) / scale
+            r[f'eager_rerun_it{it}.{k}'] = abs(he[k] - h2[k]) / scale
     for n in out['eager'][1]:
-        r[f'cos_params.{n}'] = cos(out['graph'][1][n] - 0, out['eager'][1][n])
-        r[f'params.{n}'] = max(0.0, rel(out['graph'][1][n], out['eager'][1][n])
-                               - 3.0 * rel(out['eager2'][1][n], out['eager'][1][n]))
+        r[f'params.{n}'] = rel(out['graph'][1][n], out['eager'][1][n])
+        r[f'eager_rerun_params.{n}'] = rel(out['eager2'][1][n], out['eager'][1][n])
     return r
 
 

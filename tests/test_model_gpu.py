@@ -54,6 +54,59 @@ def test_training_step_vs_reference_golden():
             assert v >= 0.8 and v >= emu_v - 0.05, (k, v, emu_v)
 
 
+def test_training_step_at_the_benchmarked_geometry_vs_reference_golden():
+    """BASELINE config 3 — dim 64, 256x256, batch 8 (16 / 32 images per call: the persistent conv kernel walks
+    3.5 - 7 work items per CTA pair, split-K weight gradients over 16 / 32 images, the stacked 32-image
+    decoder calls) — two iterations of optimize_parameters with the reference's replayed draws against the
+    values the unmodified REFERENCE recorded on the CPU (tests/golden/step_dim64_256_B8.npz):
+      * every loss of the first iteration within 1e-2 relative (measured <= 1.3e-3), of the second within
+        1e-2 except kl_zs (a 0.03-sized sum over 128 values one sign-like Adam step later: <= 3e-2, measured 1.2e-2);
+      * the gradients handed to each optimizer step vs the reference's recorded samples: discriminators,
+        style encoder and the decoder's first step cosine >= 0.999, the decoder's second step >= 0.985
+        (measured 0.994 - 0.996);
+        the content encoder >= 0.9 AND no worse than the bf16-storage-emulated oracle minus 0.02 — its
+        gradient is chaotic in the forward rounding: rounding ONLY the GEMM weights of the fp32 oracle to bf16
+        already drops its cosine to 0.95-0.96 and keeping every gradient in fp32 does not help
+        (tests/tools/precision_experiment.py, DESIGN.md section 4);
+      * the worst single parameter tensor >= 0.9."""
+    from tests.model_cases import step_vs_golden
+    res = step_vs_golden('step_dim64_256_B8')
+    for k, v in res.items():
+        if k.startswith('loss_it0.'):
+            assert v <= 1e-2, (k, v)
+        elif k.startswith('loss_it1.'):
+            assert v <= (3e-2 if k.endswith('kl_zs') else 1e-2), (k, v)
+        elif k.startswith('cosrefmin_'):
+            assert v >= 0.9, (k, v, res['_worst_tensors'])
+        elif k.startswith('cosref_'):
+            if 'content_encoder' in k:
+                emu_v = res['emucos_' + k[len('cosref_'):]]
+                assert v >= 0.9 and v >= emu_v - 0.02, (k, v, emu_v)
+            elif k == 'cosref_step6_decoder':
+                assert v >= 0.985, (k, v)
+            else:
+                assert v >= 0.999, (k, v)
+
+
+def test_iteration_is_reproducible_bit_for_bit_at_the_benchmarked_geometry():
+    """dim 64, 256x256, batch 8: two eager runs and the CUDA-graph run of the same three iterations agree in
+    every loss and every parameter BIT FOR BIT (fixed-order sums everywhere: no atomics in the statistics,
+    the norm backward, the split-K weight gradients or the loss layer; the captured iteration launches the
+    same kernels with the same host-computed Adam scalars as the eager one)."""
+    from tests.model_cases import determinism
+    res = determinism()
+    assert all(v == 0.0 for v in res.values()), res
+
+
+def test_sampling_at_config2_batch_vs_oracle():
+    """BASELINE config 2: forward_reference / forward_random at N = 8, 256x256 vs the fp32 oracle, bounded
+    like test_sampling_vs_oracle."""
+    from tests.model_cases import sampling_vs_oracle
+    res = sampling_vs_oracle(N=8)
+    for k in ('forward_reference', 'forward_random'):
+        assert res[k] <= 1e-1 and res[k] <= max(2e-2, 1.5 * res['emu_' + k]), res
+
+
 def test_sampling_vs_oracle():
     """forward_reference / forward_random at 256x256 (config 2 shape) vs the fp32 oracle: the chain
     Ec -> Es -> G (25 layers) with variance-preserving synthetic weights; bounded by 1.5x the
@@ -64,14 +117,16 @@ def test_sampling_vs_oracle():
         assert res[k] <= 1e-1 and res[k] <= max(2e-2, 1.5 * res['emu_' + k]), res
 
 
+def _exact(res):
+    bad = {k: v for k, v in res.items() if v != 0.0}
+    assert not bad, f"graph replay / eager re-run differ: {bad}"
+
+
 def test_cuda_graph_iteration_matches_eager():
-    """6 iterations (2 eager warm-up, capture, replays; learning rate changed every iteration):
-    the graph-replayed losses and final weights match the eager launch sequence.  Not bit-exact
-    because the weight-gradient split-K uses fp32 atomics (order varies run to run): the bound is
-    5e-3 beyond three times the difference between two eager runs of the same sequence."""
+    """6 iterations (2 eager warm-up, capture, replays; learning rate changed every iteration): the
+    graph-replayed losses and final weights equal the eager launch sequence exactly."""
     from tests.model_cases import graph_vs_eager
-    res = graph_vs_eager()
-    _check(res, 5e-3, 0.9999)
+    _exact(graph_vs_eager())
 
 
 def test_base_nets_vs_reference_golden():
@@ -99,25 +154,38 @@ def test_flagged_training_steps_vs_reference_golden(name):
     every loss of every iteration within 1e-2 of the reference's recorded value."""
     from tests.model_cases import flag_step_vs_golden
     res = flag_step_vs_golden(name)
-    over = None
+    over = {}
+    # the second iteration's kl_zs (0.005-sized, one sign-like Adam step after the first): 3e-2
+    over.update({k: 3e-2 for k in res if k.startswith('loss_it') and not k.startswith('loss_it0') and k.endswith('kl_zs')})
+    if name in ('step_hinge_dim8_64', 'step_wgangp_dim8_64'):
+        # hinge / wgangp adversarial terms are SIGNED MEANS of raw logits (differences of means near zero for
+        # wgangp): a relative error is ill-conditioned there; bounded by 6e-2 (absolute errors <= 1e-3)
+        over.update({k: 6e-2 for k in res if k.split('.')[-1] in ('d_adv', 'd_total', 'g_adv', 'gan2')})
     if name == 'step_norms_dim8_128':
         # --dis_norm instance: un-affine InstanceNorm on the discriminator's small feature planes makes
         # the class logits (weighted x5 in g_cls / gan2_cls) the most rounding-sensitive outputs: the
         # bf16-storage-emulated ORACLE (tests/emu.py) is itself 0.74e-2 / 0.98e-2 away from the fp32
         # reference on gan2_cls here, so these keys are bounded by 2e-2
-        over = {k: 2e-2 for k in res if k.endswith('_cls')}
+        over.update({k: 2e-2 for k in res if k.endswith('_cls')})
         # ... and 5e-2 in the SECOND iteration, which runs on weights after one Adam step (a sign-like
         # step of size lr whatever |grad|, so rounding noise in tiny gradients moves weights as far as
         # signal does): measured 1.7e-2 .. 2.2e-2 over repeated runs (the weight-gradient split-K uses
         # fp32 atomics, so the second iteration is not bit-reproducible run to run)
         over.update({k: 5e-2 for k in res if k.startswith('loss_it1.') and k.endswith('_cls')})
     _check(res, 1e-2, 0.0, over)
+    # gradients of the first iteration's optimizer steps vs the reference's recorded samples (dim = 8 toys:
+    # the chained generator phases are dominated by bf16 rounding noise there, see the dim-64 test)
+    for k, v in res.items():
+        if k.startswith('cosref_'):
+            assert v >= (0.99 if 'discriminator' in k else 0.7), (k, v)
 
 
 def test_base_default_training_step_vs_oracle():
-    """BaseModel default flags (StyleEncoder + Decoder): losses of 2 iterations within 1e-2 of the oracle."""
+    """BaseModel default flags (StyleEncoder + Decoder): losses of 2 iterations within 1e-2 of the oracle
+    (second-iteration kl_zs = 0.01 * mean(z_s^2), a 1e-4-sized value after one Adam step: 3e-2)."""
     from tests.model_cases import base_default_step_vs_oracle
-    _check(base_default_step_vs_oracle(), 1e-2, 0.0)
+    res = base_default_step_vs_oracle()
+    _check(res, 1e-2, 0.0, {k: 3e-2 for k in res if k.startswith('loss_it1') and k.endswith('kl_zs')})
 
 
 def test_base_sampling_vs_oracle():
@@ -133,14 +201,14 @@ def test_cuda_graph_with_content_discriminator_schedule():
     """--use_dis_content alternates two iteration kinds (d_iter = 3): each is captured in its own CUDA
     graph; 10 iterations (warm-up, both captures, replays) match the eager launch sequence."""
     from tests.model_cases import graph_vs_eager
-    _check(graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True), 5e-3, 0.9999)
+    _exact(graph_vs_eager(size=256, B=1, iters=10, use_dis_content=True))
 
 
 def test_cuda_graph_with_spectral_norm_and_nearest_upsampling():
     """--dis_sn (power iteration + W / sigma inside the captured iteration, u / v buffers advancing on
     every replay) and --up_type nearest: graph replays match the eager launch sequence."""
     from tests.model_cases import graph_vs_eager
-    _check(graph_vs_eager(dis_sn=True, up_type='nearest'), 5e-3, 0.9999)
+    _exact(graph_vs_eager(dis_sn=True, up_type='nearest'))
 
 
 def test_sampling_graph_matches_eager():

@@ -170,6 +170,11 @@ def run_ckpt():
     dif = max(float((a.detach() - c.detach().cpu()).abs().max()) for a, c in
               zip(rm.model.decoder.parameters(), ours.model.decoder.parameters()))
     out['step_after_load.rel_to_update'] = dif / max(upd, 1e-30)
+    worst = max(zip(rm.model.decoder.named_parameters(), ours.model.decoder.parameters(), before),
+                key=lambda t: float((t[0][1].detach() - t[1].detach().cpu()).abs().max()))
+    out['step_after_load.debug'] = [worst[0][0], float((worst[0][1].detach() - worst[2]).abs().max()),
+                                    float((worst[1].detach().cpu() - worst[2]).abs().max()),
+                                    str(ours.optimizer.decoder.param_groups[0]['lr']), str(rm.optimizer.decoder.param_groups[0]['lr'])]
     # ---- the reference saves (model.py:70-82); we load it, plain and with DataParallel's `module.` prefix
     rm.args.checkpoint_dir = tmp
     rm.save(7)
