@@ -15,82 +15,125 @@
 namespace mt {
 
 // ---------------------------------------------------------------- nn.Linear
-// y[n][o] = act(sum_i x[n][i] * w[o][i] + b[o]).  One warp per output column o: the lanes split the input
-// dimension (coalesced reads of the weight row), x comes from L1/L2 (N*In floats, shared by all warps),
-// NT rows are accumulated at a time in registers and reduced by shuffles.
-template <int NT>
+// These layers are a few MFLOP on <= 64 rows: what matters is that no thread walks a long chain of
+// dependent global loads.  Shapes: N rows, In <= ~1024, Out <= ~1024.
+constexpr int LIN_ROWS = 8;     // rows of x (or g) a block keeps in shared memory / a thread in registers
+
+// y[n][o] = act(sum_i x[n][i] * w[o][i] + b[o]).  Block = 8 warps = 8 output columns x LIN_ROWS rows; the
+// rows of x are staged in shared memory once per block, a warp splits the input dimension over its lanes
+// (coalesced reads of the weight row) and reduces by shuffles.  grid = (Out / 8, N / LIN_ROWS).
 __global__ void __launch_bounds__(256)
 linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                   int N, int In, int Out, int act, float* __restrict__ y) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= Out) return;
-  const float* wr = w + (size_t)warp * In;
-  const float bias = b ? __ldg(b + warp) : 0.f;
-  for (int n0 = 0; n0 < N; n0 += NT) {
-    float acc[NT];
+  extern __shared__ float xs[];               // [LIN_ROWS][In]
+  const int n0 = blockIdx.y * LIN_ROWS, rows = min(LIN_ROWS, N - n0);
+  for (int t = threadIdx.x; t < rows * In; t += blockDim.x) xs[t] = __ldg(x + (size_t)n0 * In + t);
+  __syncthreads();
+  const int o = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (o >= Out) return;
+  const float* wr = w + (size_t)o * In;
+  float acc[LIN_ROWS];
 #pragma unroll
-    for (int j = 0; j < NT; ++j) acc[j] = 0.f;
-    for (int i = lane; i < In; i += 32) {
-      const float wv = __ldg(wr + i);
+  for (int j = 0; j < LIN_ROWS; ++j) acc[j] = 0.f;
+  for (int i = lane; i < In; i += 32) {
+    const float wv = __ldg(wr + i);
 #pragma unroll
-      for (int j = 0; j < NT; ++j)
-        if (n0 + j < N) acc[j] = fmaf(__ldg(x + (size_t)(n0 + j) * In + i), wv, acc[j]);
-    }
+    for (int j = 0; j < LIN_ROWS; ++j)
+      if (j < rows) acc[j] = fmaf(xs[j * In + i], wv, acc[j]);
+  }
+  const float bias = b ? __ldg(b + o) : 0.f;
 #pragma unroll
-    for (int j = 0; j < NT; ++j) {
-      float s = acc[j];
-      for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (lane == 0 && n0 + j < N) {
-        s += bias;
-        if (act == MT_ACT_RELU) s = fmaxf(s, 0.f);
-        y[(size_t)(n0 + j) * Out + warp] = s;
-      }
+  for (int j = 0; j < LIN_ROWS; ++j) {
+    float s = acc[j];
+    for (int k = 16; k; k >>= 1) s += __shfl_xor_sync(0xffffffffu, s, k);
+    if (lane == 0 && j < rows) {
+      s += bias;
+      if (act == MT_ACT_RELU) s = fmaxf(s, 0.f);
+      y[(size_t)(n0 + j) * Out + o] = s;
     }
   }
 }
 
-// Backward.  g[n][o] = dy[n][o] * act'(y[n][o]).  Two roles in one launch:
-//   blocks [0, gw): dW[o][i] (+)= sum_n g[n][o] x[n][i], db[o] (+)= sum_n g[n][o]   thread = (o, i), i fastest
-//   blocks [gw, ..): dx[n][i] (+)= sum_o g[n][o] w[o][i]                              thread = (n, i), i fastest
-// Sums run in index order (reproducible).
+// Backward, g[n][o] = dy[n][o] * act'(y[n][o]).  Two roles in one launch, both with fixed-order sums:
+//   blocks [0, gw): dW[o][i] (+)= sum_n g[n][o] x[n][i], db[o] (+)= sum_n g[n][o]; thread = (o, i), i fastest:
+//     the N-long loop reads g[n][o] as a warp broadcast and x[n][i] coalesced (independent loads).
+//   blocks [gw, ..): dx[n][i] (+)= sum_o g[n][o] w[o][i] for LIN_ROWS rows per block: the masked gradient rows
+//     are staged in shared memory, block = 64 columns i x 4 slices of the o loop (each thread walks Out / 4
+//     rows of w, coalesced), the four slices are combined in index order.
 __global__ void __launch_bounds__(256)
 linear_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, const float* __restrict__ x,
                   const float* __restrict__ w, int N, int In, int Out, int act, float* __restrict__ dx,
-                  float* __restrict__ dw, float* __restrict__ db, int acc_param, int acc_dx, int gw) {
+                  float* __restrict__ dw, float* __restrict__ db, int acc_param, int acc_dx, int gw, int gxi) {
+  extern __shared__ float sm[];
   if ((int)blockIdx.x < gw) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= Out * In) return;
     const int o = t / In, i = t - o * In;
-    float s = 0.f, sb = 0.f;
-    for (int n = 0; n < N; ++n) {
-      float g = __ldg(dy + (size_t)n * Out + o);
-      if (act == MT_ACT_RELU && __ldg(y + (size_t)n * Out + o) <= 0.f) g = 0.f;
-      s = fmaf(g, __ldg(x + (size_t)n * In + i), s);
-      sb += g;
+    float s0 = 0.f, s1 = 0.f, sb = 0.f;
+    int n = 0;
+    for (; n + 1 < N; n += 2) {
+      float g0 = __ldg(dy + (size_t)n * Out + o), g1 = __ldg(dy + (size_t)(n + 1) * Out + o);
+      if (act == MT_ACT_RELU) {
+        if (__ldg(y + (size_t)n * Out + o) <= 0.f) g0 = 0.f;
+        if (__ldg(y + (size_t)(n + 1) * Out + o) <= 0.f) g1 = 0.f;
+      }
+      s0 = fmaf(g0, __ldg(x + (size_t)n * In + i), s0);
+      s1 = fmaf(g1, __ldg(x + (size_t)(n + 1) * In + i), s1);
+      sb += g0; sb += g1;
     }
+    if (n < N) {
+      float g0 = __ldg(dy + (size_t)n * Out + o);
+      if (act == MT_ACT_RELU && __ldg(y + (size_t)n * Out + o) <= 0.f) g0 = 0.f;
+      s0 = fmaf(g0, __ldg(x + (size_t)n * In + i), s0);
+      sb += g0;
+    }
+    const float s = s0 + s1;
     if (dw) dw[t] = acc_param ? dw[t] + s : s;
     if (db && i == 0) db[o] = acc_param ? db[o] + sb : sb;
-  } else {
-    if (!dx) return;
-    const int t = (blockIdx.x - gw) * blockDim.x + threadIdx.x;
-    if (t >= N * In) return;
-    const int n = t / In, i = t - n * In;
-    float s = 0.f;
-    for (int o = 0; o < Out; ++o) {
-      float g = __ldg(dy + (size_t)n * Out + o);
-      if (act == MT_ACT_RELU && __ldg(y + (size_t)n * Out + o) <= 0.f) g = 0.f;
-      s = fmaf(g, __ldg(w + (size_t)o * In + i), s);
-    }
-    dx[t] = acc_dx ? dx[t] + s : s;
+    return;
   }
+  // ---- dx role
+  const int bid = blockIdx.x - gw;
+  const int it = bid % gxi, nb = bid / gxi;             // column tile, row block
+  const int n0 = nb * LIN_ROWS, rows = min(LIN_ROWS, N - n0);
+  float* gs = sm;                                        // [LIN_ROWS][Out] masked gradient rows
+  float* part = sm + LIN_ROWS * Out;                     // [4][LIN_ROWS][64]
+  for (int t = threadIdx.x; t < rows * Out; t += blockDim.x) {
+    float g = __ldg(dy + (size_t)n0 * Out + t);
+    if (act == MT_ACT_RELU && __ldg(y + (size_t)n0 * Out + t) <= 0.f) g = 0.f;
+    gs[t] = g;
+  }
+  __syncthreads();
+  const int il = threadIdx.x & 63, sl = threadIdx.x >> 6;
+  const int i = it * 64 + il;
+  float acc[LIN_ROWS];
+#pragma unroll
+  for (int j = 0; j < LIN_ROWS; ++j) acc[j] = 0.f;
+  if (i < In)
+    for (int o = sl; o < Out; o += 4) {
+      const float wv = __ldg(w + (size_t)o * In + i);
+#pragma unroll
+      for (int j = 0; j < LIN_ROWS; ++j)
+        if (j < rows) acc[j] = fmaf(gs[j * Out + o], wv, acc[j]);
+    }
+#pragma unroll
+  for (int j = 0; j < LIN_ROWS; ++j) part[(sl * LIN_ROWS + j) * 64 + il] = acc[j];
+  __syncthreads();
+  if (sl == 0 && i < In)
+    for (int j = 0; j < rows; ++j) {
+      const float s = (part[(0 * LIN_ROWS + j) * 64 + il] + part[(1 * LIN_ROWS + j) * 64 + il]) +
+                      (part[(2 * LIN_ROWS + j) * 64 + il] + part[(3 * LIN_ROWS + j) * 64 + il]);
+      float* q = dx + (size_t)(n0 + j) * In + i;
+      *q = acc_dx ? *q + s : s;
+    }
 }
 
 static int launch_linear_fwd(const float* x, const float* w, const float* b, int N, int In, int Out, int act,
                              float* y, cudaStream_t st) {
   if (N < 1 || In < 1 || Out < 1 || (act != MT_ACT_NONE && act != MT_ACT_RELU)) return -1005;
-  const int blocks = (Out * 32 + 255) / 256;
-  if (N <= 8) linear_fwd_kernel<8><<<blocks, 256, 0, st>>>(x, w, b, N, In, Out, act, y);
-  else linear_fwd_kernel<16><<<blocks, 256, 0, st>>>(x, w, b, N, In, Out, act, y);
+  const size_t smem = (size_t)LIN_ROWS * In * sizeof(float);
+  if (smem > 48 * 1024) return -1005;                    // In <= 1536
+  linear_fwd_kernel<<<dim3((Out + 7) / 8, (N + LIN_ROWS - 1) / LIN_ROWS), 256, smem, st>>>(x, w, b, N, In, Out, act, y);
   return cuda_rc();
 }
 static int launch_linear_bwd(const float* dy, const float* y, const float* x, const float* w, int N, int In,
@@ -100,16 +143,20 @@ static int launch_linear_bwd(const float* dy, const float* y, const float* x, co
   if (act == MT_ACT_RELU && !y) return -1008;
   if ((long long)Out * In >= (1ll << 31) || (long long)N * In >= (1ll << 31)) return -1005;
   const int gw = (dw || db) ? (Out * In + 255) / 256 : 0;
-  const int gx = dx ? (N * In + 255) / 256 : 0;
+  const int gxi = (In + 63) / 64;
+  const int gx = dx ? gxi * ((N + LIN_ROWS - 1) / LIN_ROWS) : 0;
   if (gw + gx == 0) return 0;
-  linear_bwd_kernel<<<gw + gx, 256, 0, st>>>(dy, y, x, w, N, In, Out, act, dx, dw, db, acc_param, acc_dx, gw);
+  const size_t smem = dx ? ((size_t)LIN_ROWS * Out + 4 * LIN_ROWS * 64) * sizeof(float) : 0;
+  if (smem > 48 * 1024) return -1005;                    // Out <= 1280
+  linear_bwd_kernel<<<gw + gx, 256, smem, st>>>(dy, y, x, w, N, In, Out, act, dx, dw, db, acc_param, acc_dx, gw, gxi);
   return cuda_rc();
 }
 
 // ---------------------------------------------------------------- discriminator heads
 // h [N][S][S][Cs] bf16 (C valid channels) -> out [N][S+2][S+2] fp32 (1x1 conv with padding 1: exact-zero
 // border) and cls [N][nd] (k x k conv with k == S, i.e. a full contraction, + global average of one value).
-// One block per image; thread = channel slice; block-level tree reduction in a fixed order.
+// One block per image; thread = channel slice: h is read coalesced over the channels, the thread's
+// w2[d][c][0..SS) rows are contiguous; block-level tree reduction in a fixed order.
 __global__ void __launch_bounds__(256)
 dis_head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w1,
                     const float* __restrict__ w2, int SS, int Cs, int C, int nd, int S,
@@ -120,10 +167,22 @@ dis_head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict
   for (int k = 0; k < NV; ++k) mine[k] = 0.f;
   for (int c = tid; c < C; c += blockDim.x) {
     const float a1 = __ldg(w1 + c);
-    for (int p = 0; p < SS; ++p) {
-      const float v = __bfloat162float(h[((size_t)n * SS + p) * Cs + c]);
-      mine[p] = fmaf(v, a1, mine[p]);
-      for (int d = 0; d < nd; ++d) mine[SS + d] = fmaf(v, __ldg(w2 + ((size_t)d * C + c) * SS + p), mine[SS + d]);
+    for (int p0 = 0; p0 < SS; p0 += 16) {             // 16 positions at a time: independent loads first
+      float v[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        v[k] = p0 + k < SS ? __bfloat162float(h[((size_t)n * SS + p0 + k) * Cs + c]) : 0.f;
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        if (p0 + k < SS) mine[p0 + k] = fmaf(v[k], a1, mine[p0 + k]);
+      for (int d = 0; d < nd; ++d) {
+        const float* wr = w2 + ((size_t)d * C + c) * SS + p0;     // this thread's contiguous filter row
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          if (p0 + k < SS) acc = fmaf(v[k], __ldg(wr + k), acc);
+        mine[SS + d] += acc;
+      }
     }
   }
   __syncthreads();
@@ -142,16 +201,17 @@ dis_head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict
 }
 
 // Backward of the heads.  dout [N][S+2][S+2] (border ignored), dcls [N][nd] (images n < cls_first carry no
-// class gradient: the fake half of a discriminator batch, adain_model.py:213-216).
-//   blocks [0, ga): dh[n][p][c] = dout[n][p] w1[c] + sum_d dcls[n][d] w2[d][c][p]        thread = (n, p, c)
-//   blocks [ga, ..): dw1[c] (+)= sum_{n,p} dout[n][p] h[n][p][c]; dw2[d][c][p] (+)= sum_n dcls[n][d] h[n][p][c]
-//                                                                                           thread = channel c
+// class gradient: the fake half of a discriminator batch, adain_model.py:213-216).  Three roles:
+//   blocks [0, ga):      dh[n][p][c] = dout[n][p] w1[c] + sum_d dcls[n][d] w2[d][c][p]     thread = (n, p, c)
+//   blocks [ga, ga+gb):  dw2[d][c][p] (+)= sum_n dcls[n][d] h[n][p][c]                     thread = (p, c), c fastest
+//   blocks [ga+gb, ..):  dw1[c] (+)= sum_{n,p} dout[n][p] h[n][p][c]       block = 32 channels x 8 groups of
+//                        (n, p) pairs, combined in index order
 __global__ void __launch_bounds__(256)
 dis_head_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ dcls,
                     const __nv_bfloat16* __restrict__ h, const float* __restrict__ w1,
                     const float* __restrict__ w2, int N, int SS, int Cs, int C, int nd, int S,
                     __nv_bfloat16* __restrict__ dh, float* __restrict__ dw1, float* __restrict__ dw2,
-                    int accumulate, int ga, int cls_first) {
+                    int accumulate, int ga, int gb, int cls_first) {
   const int So = S + 2;
   if ((int)blockIdx.x < ga) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -167,31 +227,44 @@ dis_head_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ dc
           v = fmaf(__ldg(dcls + (size_t)n * nd + d), __ldg(w2 + ((size_t)d * C + c) * SS + p), v);
     }
     dh[t] = __float2bfloat16(v);
-  } else {
-    const int c = (blockIdx.x - ga) * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    float a1 = 0.f;
-    for (int p = 0; p < SS; ++p) {
-      float a2[8];
+  } else if ((int)blockIdx.x < ga + gb) {
+    const int t = (blockIdx.x - ga) * blockDim.x + threadIdx.x;
+    if (t >= SS * C) return;
+    const int p = t / C, c = t - p * C;
+    float a2[8];
 #pragma unroll
-      for (int d = 0; d < 8; ++d) a2[d] = 0.f;
-      for (int n = 0; n < N; ++n) {
-        const float v = __bfloat162float(h[((size_t)n * SS + p) * Cs + c]);
-        a1 = fmaf(__ldg(dout + (size_t)n * So * So + (p / S + 1) * So + (p % S + 1)), v, a1);
-        if (n >= cls_first) {
-#pragma unroll
-          for (int d = 0; d < 8; ++d)
-            if (d < nd) a2[d] = fmaf(__ldg(dcls + (size_t)n * nd + d), v, a2[d]);
-        }
-      }
+    for (int d = 0; d < 8; ++d) a2[d] = 0.f;
+    for (int n = cls_first; n < N; ++n) {
+      const float v = __bfloat162float(h[((size_t)n * SS + p) * Cs + c]);
 #pragma unroll
       for (int d = 0; d < 8; ++d)
-        if (d < nd) {
-          float* q = dw2 + ((size_t)d * C + c) * SS + p;
-          *q = accumulate ? *q + a2[d] : a2[d];
-        }
+        if (d < nd) a2[d] = fmaf(__ldg(dcls + (size_t)n * nd + d), v, a2[d]);
     }
-    dw1[c] = accumulate ? dw1[c] + a1 : a1;
+#pragma unroll
+    for (int d = 0; d < 8; ++d)
+      if (d < nd) {
+        float* q = dw2 + ((size_t)d * C + c) * SS + p;
+        *q = accumulate ? *q + a2[d] : a2[d];
+      }
+  } else {
+    __shared__ float sm1[8][33];
+    const int cl = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int c = (blockIdx.x - ga - gb) * 32 + cl;
+    float a = 0.f;
+    if (c < C)
+      for (int k = g; k < N * SS; k += 8) {
+        const int n = k / SS, p = k - n * SS;
+        a = fmaf(__ldg(dout + (size_t)n * So * So + (p / S + 1) * So + (p % S + 1)),
+                 __bfloat162float(h[(size_t)k * Cs + c]), a);
+      }
+    sm1[g][cl] = a;
+    __syncthreads();
+    if (g == 0 && c < C) {
+      float v = sm1[0][cl];
+#pragma unroll
+      for (int k = 1; k < 8; ++k) v += sm1[k][cl];
+      dw1[c] = accumulate ? dw1[c] + v : v;
+    }
   }
 }
 
@@ -359,10 +432,13 @@ extern "C" int mt_dis_head_bwd(const float* dout, const float* dcls, const void*
   const long long tot = (long long)N * S * S * Cs;
   if (tot >= (1ll << 31)) return -1005;
   const int ga = dh ? (int)((tot + 255) / 256) : 0;
-  const int gb = (dw1 && dw2) ? (C + 255) / 256 : 0;
-  if (ga + gb == 0) return 0;
-  dis_head_bwd_kernel<<<ga + gb, 256, 0, ST(stream)>>>(dout, dcls, (const __nv_bfloat16*)h, w1, w2, N, S * S, Cs, C,
-                                                      nd, S, (__nv_bfloat16*)dh, dw1, dw2, accumulate, ga, cls_first);
+  const bool params = dw1 && dw2;
+  const int gb = params ? (S * S * C + 255) / 256 : 0;
+  const int gc = params ? (C + 31) / 32 : 0;
+  if (ga + gb + gc == 0) return 0;
+  dis_head_bwd_kernel<<<ga + gb + gc, 256, 0, ST(stream)>>>(dout, dcls, (const __nv_bfloat16*)h, w1, w2, N, S * S, Cs,
+                                                           C, nd, S, (__nv_bfloat16*)dh, dw1, dw2, accumulate, ga, gb,
+                                                           cls_first);
   return cuda_rc();
 }
 

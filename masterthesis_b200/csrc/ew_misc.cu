@@ -350,21 +350,33 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restri
   }
 }
 // db[c] (+)= sum over the rows of stats[row][c][0]  (column sums of a dense tensor from the per-chunk
-// partial sums of mt_plane_stats; rows added in index order)
-__global__ void __launch_bounds__(128) colsum_finalize_kernel(const float* __restrict__ stats, int rows, int C,
+// partial sums of mt_plane_stats).  Block = 32 channels x 8 row groups: a thread adds the rows r = g (mod 8)
+// with four loads in flight, the eight groups are then combined in index order (a fixed summation order;
+// one thread walking all rows was a chain of ~300 dependent L2 round trips: 36 us for a 2 us job).
+__global__ void __launch_bounds__(256) colsum_finalize_kernel(const float* __restrict__ stats, int rows, int C,
                                                               int Cv, float* __restrict__ db, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= Cv) return;
+  __shared__ float sm[8][33];
+  const int cl = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
   float a[4] = {0.f, 0.f, 0.f, 0.f};
-  int i = 0;
-  for (; i + 3 < rows; i += 4) {
+  if (c < Cv) {
+    int i = g;
+    for (; i + 24 < rows; i += 32) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u) a[u] += stats[((size_t)(i + u) * C + c) * 2];
+      for (int u = 0; u < 4; ++u) a[u] += stats[((size_t)(i + 8 * u) * C + c) * 2];
+    }
+    for (; i < rows; i += 8) a[0] += stats[((size_t)i * C + c) * 2];
   }
-  for (; i < rows; ++i) a[0] += stats[((size_t)i * C + c) * 2];
-  const float v = (a[0] + a[1]) + (a[2] + a[3]);
-  db[c] = accumulate ? db[c] + v : v;
+  sm[g][cl] = (a[0] + a[1]) + (a[2] + a[3]);
+  __syncthreads();
+  if (g == 0 && c < Cv) {
+    float v = sm[0][cl];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) v += sm[k][cl];
+    db[c] = accumulate ? db[c] + v : v;
+  }
 }
+
 // dx_pad = scale[0] * x_pad on the interior, 0 on the border
 __global__ void __launch_bounds__(256)
 scale_interior_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale, int N,
@@ -544,7 +556,7 @@ extern "C" int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, 
 extern "C" int mt_colsum_into(const float* stats, int rows, int C, int C_valid, float* db, int accumulate,
                               void* stream) {
   if (rows < 1 || C_valid < 1 || C_valid > C) return -1005;
-  colsum_finalize_kernel<<<(C_valid + 127) / 128, 128, 0, ST(stream)>>>(stats, rows, C, C_valid, db, accumulate);
+  colsum_finalize_kernel<<<(C_valid + 31) / 32, 256, 0, ST(stream)>>>(stats, rows, C, C_valid, db, accumulate);
   return cuda_rc();
 }
 extern "C" int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C,

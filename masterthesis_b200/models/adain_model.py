@@ -264,18 +264,41 @@ class AdaINModel(Model):
         # The two discriminator updates are independent (separate networks, optimizers and inputs) and
         # their tail layers leave most SMs idle: D1 runs on an auxiliary stream next to D2.  Host
         # order is the reference's (D1 then D2), so self.loss ends up with D2's values as there.
+        # Their optimizer steps (gradient all-reduce over NVLink under data parallelism, fused Adam, bf16
+        # weight re-packs) leave the critical path: nothing reads the discriminators' weights before the
+        # adversarial branch of the generator phase (`_wait_d_steps`), so both steps run on a third stream
+        # under the generator's Ec / Es / G forward.
         aux, cur = self._aux_stream(), torch.cuda.current_stream()
         if aux is not None:
             aux.wait_stream(cur)
         with (torch.cuda.stream(aux) if aux is not None else contextlib.nullcontext()):
             self.optimizer.discriminator1.zero_grad()
             self.backward_discriminator(self.model.discriminator1, img, img_fake, c_org)
-            self._step('discriminator1')
+            if aux is None:
+                self._step('discriminator1')
         self.optimizer.discriminator2.zero_grad()
         self.backward_discriminator(self.model.discriminator2, img, img_random, c_org)
-        self._step('discriminator2')
-        if aux is not None:
-            cur.wait_stream(aux)
+        if aux is None:
+            self._step('discriminator2')
+            return
+        # D1's backward read tensors that belong to the main stream (img_fake ...): join before they are freed
+        cur.wait_stream(aux)
+        comm = self._comm_stream()
+        comm.wait_stream(cur)
+        with torch.cuda.stream(comm):
+            self._step('discriminator1')
+            self._step('discriminator2')
+
+    def _comm_stream(self):
+        if getattr(self, '_comm', None) is None:
+            self._comm = torch.cuda.Stream()
+        return self._comm
+
+    def _wait_d_steps(self):
+        """the current stream waits for the discriminators' optimizer steps issued by update_discriminator
+        (called in front of every use of their weights; a no-op once joined)"""
+        if getattr(self, '_comm', None) is not None:
+            torch.cuda.current_stream().wait_stream(self._comm)
 
     def _fork(self, fn_main, fn_aux):
         """(fn_main(), fn_aux()) with fn_aux on the auxiliary stream.  For INDEPENDENT networks only
@@ -394,6 +417,7 @@ class AdaINModel(Model):
     def _g_adv_fast(self, netD, fake, c_org, adv_slot, cls_slot):
         """generator-side adversarial + classification terms as (roots, gradients): BCE(D(fake), 1) and
         lambda_cls_G * BCE(cls(fake), c_org), losses written to their slots"""
+        self._wait_d_steps()
         pred, pred_cls = netD.run(fake)
         g_a = ops.loss_bce_logits(pred.detach(), 1.0, 1.0, self._slot(adv_slot))
         g_c = ops.loss_bce_logits(pred_cls.detach(), c_org, self.args.lambda_cls_G, self._slot(cls_slot))
@@ -403,6 +427,7 @@ class AdaINModel(Model):
         """generator-side adversarial + classification loss.  `real` / `netD_real`: the relativistic
         branch (--use_ragan, :286-292 and :360-366) also scores the real images, in phase G2 with
         the OTHER discriminator (discriminator2 for the reals, discriminator1 for the fakes)."""
+        self._wait_d_steps()
         if self.args.ms_dis:
             adv, cls = 0, 0
             for pred_fake, pred_fake_cls in netD.run(fake):
@@ -558,6 +583,7 @@ class AdaINModel(Model):
         blocks.prepack(*self.model.values())
         self.update_discriminator(self.img, self.c_org)
         self.update_generator(self.img, self.c_org)
+        self._wait_d_steps()
         blocks.join_prepack()
 
     def _content_iteration(self):

@@ -57,3 +57,24 @@ def test_checkpoint_interchange_with_the_reference():
         assert r[f'ref_to_ours.{tag}.adam_step'] == 7.0, r
     assert r['load_after_capture.captured_before'] and r['load_after_capture.recaptured'], r
     assert r['load_after_capture.weights_moved'] and r['load_after_capture.finite'], r
+
+
+def test_data_parallel_gradients_equal_single_gpu():
+    """SURVEY.md 8e on hardware (skipped below 2 GPUs): one iteration on 2 ranks (NCCL all-reduce of the flat
+    buckets, KL pre-scale, 1/world in Adam) vs the same global batch on one GPU: gradient buckets at all seven
+    optimizer steps cosine >= 0.9999, losses within 1e-3."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2; log committed as profiles/r2_dp_equality_2gpu.txt)")
+    p = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2',
+                        '--master-addr', '127.0.0.1', '--master-port', '29613',
+                        os.path.join(ROOT, 'tests', 'tools', 'dp_equality.py'), '16', '64', '4'],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT)
+    lines = [l for l in p.stdout.splitlines() if l.startswith('RESULT ')]
+    assert lines, f"rc={p.returncode}\n{p.stdout[-2000:]}\n{p.stderr[-3000:]}"
+    r = json.loads(lines[0][7:])
+    for k, v in r.items():
+        if k.startswith('cos_'):
+            assert v >= 0.9999, (k, v, r)
+        elif k.startswith('loss.'):
+            assert v <= 1e-3, (k, v, r)
