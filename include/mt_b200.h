@@ -6,8 +6,17 @@
  * for. All pointers are DEVICE pointers unless a name ends in _host; all activation
  * tensors are NHWC bf16 ("stored" channel counts are multiples of 8); `stream` is a
  * cudaStream_t passed as void*. Every function returns 0 on success or a negative error
- * code (-cudaError_t, or <= -1000 for argument errors) and never allocates or
- * synchronises. There is no CPU fallback: without a CUDA device every call fails.
+ * code (-cudaError_t, or <= -1000 for argument errors) and never allocates device memory: every
+ * buffer, scratch included, is the caller's (the *_parts / *_splits / *_elems queries size them).
+ * Host-side state the library keeps, all created lazily and documented here:
+ *   - per (device, caller stream): three auxiliary streams and four events with which the sub-pixel phases /
+ *     row parities of stride-2 data gradients and transposed convolutions run side by side (forked from and
+ *     joined back into `stream` before the call returns: plain stream semantics for the caller, graph edges
+ *     under capture; MT_PHASE_FORK=0 disables);
+ *   - ONE cudaStreamSynchronize + 8-byte cudaMemcpyFromSymbol at the first implicit-GEMM launch of the
+ *     process outside stream capture (self check that the kernels' shared-memory ring sits at the offset
+ *     their constant descriptors assume; error -1011 otherwise).  No other call synchronises.
+ * Entry points are re-entrant per stream.  There is no CPU fallback: without a CUDA device every call fails.
  */
 #ifndef MT_B200_H
 #define MT_B200_H
@@ -113,6 +122,11 @@ int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd, con
                         void* y, float* stats, int parts, void* stream);
 /* d(loss)/d(input buffer), including the reflection border rows/cols (folded later) */
 int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx, void* stream);
+/* accumulate != 0: dx += d(loss)/d(input buffer) (the epilogue's TMA store becomes a reduce-add; every element
+ * is added exactly once): the residual fan-in `x + block(x)` of ResnetBlock / AdaINResnetBlock
+ * (blocks.py:137,166) without a separate add pass — dx then already holds the gradient of the skip path */
+int mt_conv2d_dgrad_acc(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx, int accumulate,
+                        void* stream);
 /* d(loss)/d(weight) as split-K partial results: fp32 dw_packed[splits][taps][Cout][Cin_s] (window mode:
  * [splits][kh][Cout][64]), splits = mt_conv2d_wgrad_splits(d), mt_packed_wgrad_elems() elements per split.
  * Every split stores its own slab (no zeroing by the caller, no atomics); mt_unpack_conv_wgrad adds the

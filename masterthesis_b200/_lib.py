@@ -40,9 +40,25 @@ def _stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every CUDA source for sm_100a into one shared library, in-tree."""
+    """Compile every CUDA source for sm_100a into one shared library, in-tree.  Safe across processes (N ranks
+    of a torchrun job on a fresh checkout): an exclusive file lock serialises the builders, and a rank that
+    waited finds the library fresh and returns."""
     if not force and not _stale():
         return LIB_PATH
+    import fcntl
+    build_dir = PKG_DIR / "build"
+    build_dir.mkdir(exist_ok=True)
+    with open(build_dir / ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():        # another process built it while this one waited
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> Path:
     nvcc = os.environ.get("NVCC", "nvcc")
     objs = []
     procs = []
@@ -62,7 +78,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             raise RuntimeError(f"nvcc failed on {src.name}:\n{out.decode()}")
         if verbose and out:
             print(out.decode())
-    tmp = LIB_PATH.with_suffix(".so.tmp")
+    tmp = LIB_PATH.with_suffix(f".so.tmp{os.getpid()}")
     cmd = [nvcc, "-shared", "-o", str(tmp)] + [str(o) for o in objs]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode != 0:

@@ -6,7 +6,9 @@
 #include <cudaTypedefs.h>
 #include <stdlib.h>
 #include <string.h>
+#include <map>
 #include <mutex>
+#include <utility>
 
 #include "../../include/mt_b200.h"
 #include "igemm.cuh"
@@ -57,6 +59,7 @@ struct ConvLike {
   int act; float slope; const float* bias; void* out;
   float* stats;             // optional fused plane statistics [Nt][stat_parts][n_store][2]
   int stat_parts, stat_part0;
+  int accumulate;           // out += result
 };
 
 static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
@@ -91,6 +94,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   p.out_n_stride = c.out_n_stride; p.out_h_stride = c.out_h_stride;
   p.out_w_stride = c.out_w_stride; p.out_off = c.out_off;
   p.act = c.act; p.slope = c.slope; p.bias = c.bias;
+  p.accumulate = c.accumulate;
   p.out = reinterpret_cast<__nv_bfloat16*>(c.out);
 
   CUtensorMap tmA, tmB;
@@ -258,24 +262,37 @@ extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void*
 struct PhaseFork {
   cudaStream_t aux[3];
   cudaEvent_t fork, join[3];
-  bool ok = false, tried = false;
-  int max_ctas = 1 << 30;     // fork when no phase uses more CTAs than this (MT_PHASE_FORK, 0 = never);
-                              // measured: forking always wins (CTA-level interleaving hides the tails)
+  bool ok = false;
 };
-static PhaseFork g_fork;
-static bool phase_fork_ready() {
-  if (g_fork.tried) return g_fork.ok;
-  g_fork.tried = true;
-  const char* e = getenv("MT_PHASE_FORK");
-  if (e) g_fork.max_ctas = atoi(e);
-  if (g_fork.max_ctas <= 0) return false;
-  if (cudaEventCreateWithFlags(&g_fork.fork, cudaEventDisableTiming) != cudaSuccess) return false;
-  for (int i = 0; i < 3; ++i) {
-    if (cudaStreamCreateWithFlags(&g_fork.aux[i], cudaStreamNonBlocking) != cudaSuccess) return false;
-    if (cudaEventCreateWithFlags(&g_fork.join[i], cudaEventDisableTiming) != cudaSuccess) return false;
+// One set of auxiliary streams / events per (device, caller stream), created at the first forked call of
+// that stream (these are the only CUDA objects the library creates; nothing is ever allocated on the device):
+// two caller streams — e.g. the two discriminator updates running side by side — never share fork / join
+// events, so neither gets a false dependency on the other.  MT_PHASE_FORK = 0 disables forking; a value
+// N > 0 forks only launches of at most N CTAs per phase.
+static std::mutex g_fork_mu;
+static std::map<std::pair<int, cudaStream_t>, PhaseFork> g_forks;
+static int g_fork_max_ctas = -1;
+static PhaseFork* phase_fork(cudaStream_t stream) {
+  std::lock_guard<std::mutex> lk(g_fork_mu);
+  if (g_fork_max_ctas < 0) {
+    const char* e = getenv("MT_PHASE_FORK");
+    g_fork_max_ctas = e ? atoi(e) : (1 << 30);
+    if (g_fork_max_ctas < 0) g_fork_max_ctas = 0;
   }
-  g_fork.ok = true;
-  return true;
+  if (g_fork_max_ctas == 0) return nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  auto key = std::make_pair(dev, stream);
+  auto it = g_forks.find(key);
+  if (it != g_forks.end()) return it->second.ok ? &it->second : nullptr;
+  PhaseFork f;
+  bool ok = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; i < 3 && ok; ++i)
+    ok = cudaStreamCreateWithFlags(&f.aux[i], cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
+  f.ok = ok;
+  auto& slot = g_forks[key] = f;
+  return ok ? &slot : nullptr;
 }
 static int phase_work_items(const ConvLike& q) {
   int tw, th, tn;
@@ -310,7 +327,8 @@ static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, lo
       if (ctas > max_ctas) max_ctas = ctas;
       qs[n++] = q;
     }
-  const bool fork = n > 1 && phase_fork_ready() && max_ctas <= g_fork.max_ctas;
+  PhaseFork* pf = n > 1 ? phase_fork(stream) : nullptr;
+  const bool fork = pf != nullptr && max_ctas <= g_fork_max_ctas;
   if (!fork) {
     for (int i = 0; i < n; ++i) {
       int rc = run_conv_like(qs[i], stream);
@@ -318,6 +336,7 @@ static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, lo
     }
     return 0;
   }
+  PhaseFork& g_fork = *pf;
   if (cudaEventRecord(g_fork.fork, stream) != cudaSuccess) return -1013;
   int rc = 0;
   for (int i = 1; i < n && !rc; ++i) {
@@ -334,10 +353,12 @@ static int run_phases(ConvLike c, int kh, int kw, int zp, int OutH, int OutW, lo
 
 // the two row-parity launches of a merged-parity operation, side by side (qs[0] on an auxiliary stream)
 static int run_pair(const ConvLike* qs, cudaStream_t st) {
-  if (!phase_fork_ready()) {
+  PhaseFork* pf = phase_fork(st);
+  if (!pf) {
     const int rc = run_conv_like(qs[0], st);
     return rc ? rc : run_conv_like(qs[1], st);
   }
+  PhaseFork& g_fork = *pf;
   if (cudaEventRecord(g_fork.fork, st) != cudaSuccess) return -1013;
   int rc = 0;
   if (cudaStreamWaitEvent(g_fork.aux[0], g_fork.fork, 0) != cudaSuccess) rc = -1013;
@@ -371,10 +392,16 @@ extern "C" int mt_conv_s1_dgrad_pair_mode(int kh, int kw, int stride, int zpad, 
 
 extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
                                void* stream) {
+  return mt_conv2d_dgrad_acc(d, dy, w_bwd, dx, 0, stream);
+}
+
+extern "C" int mt_conv2d_dgrad_acc(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,
+                                   int accumulate, void* stream) {
   int rc = check_desc(d);
   if (rc) return rc;
   ConvLike c;
   memset(&c, 0, sizeof(c));
+  c.accumulate = accumulate ? 1 : 0;
   // A = dy [N, Hout, Wout, Cout_s] (dense: the producer of dy writes an unpadded buffer)
   c.a = dy; c.An = d->N; c.Ah = d->Hout; c.Aw = d->Wout; c.Ac = d->Cout; c.Ac_s = d->Cout_s;
   c.a_mul = 1; c.window = false;

@@ -34,6 +34,7 @@ struct IgemmParams {
   long long out_n_stride, out_h_stride, out_w_stride, out_off;  // elements
   int act;
   float slope;
+  int accumulate;      // 1: out += result (TMA reduce-add store) instead of out = result
   const float* bias;
   __nv_bfloat16* out;
   float* stats;        // optional fused plane statistics: [N][stat_parts][n_stat_c][2] fp32 partial

@@ -368,7 +368,8 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         fence_proxy_async();
         named_bar_sync(1 + grp, 128);
         if (tt == 0) {
-          tma_store_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
+          if (p.accumulate) tma_reduce_add_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
+          else tma_store_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
           bulk_commit();
         }
         if (SW == 64 && p.stats != nullptr && wc.n0 < p.Nt) slab_stats(p, stage_buf, tt, c_glob, wc.n0, wc.part);

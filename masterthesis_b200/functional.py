@@ -14,6 +14,12 @@ from torch.autograd import Function
 from . import ops
 
 
+import os as _os
+# residual blocks: the skip-path gradient is added by the data-gradient conv's epilogue (MT_FUSE_RES_GRAD=0:
+# separate mt_add_interior pass, the round-1 form)
+FUSE_RESIDUAL_GRAD = _os.environ.get('MT_FUSE_RES_GRAD', '1') == '1'
+
+
 def _c(t):
     return t if t is None or t.is_contiguous() else t.contiguous()
 
@@ -211,13 +217,19 @@ class ResBlock(Function):
         dw1 = _wgrad(ctx.w1, x, dy1, g, ctx.needs_input_grad[1])
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = ops.conv_dgrad(dy1, wb1, g, x.shape[1], x.shape[2])
-            if op == 1:
+            if op == 1 and FUSE_RESIDUAL_GRAD:
                 # residual path: out_pad = pad(x_int + h) and x is padded like out, so adding the PADDED
-                # dout is the same as adding fold(dout) to the interior once x's producer folds dx
-                ops.add_interior_(dx, dout, 0)
+                # dout is the same as adding fold(dout) to the interior once x's producer folds dx.  The
+                # data-gradient conv adds its result straight onto dout (TMA reduce-add epilogue): dout is
+                # this node's own incoming gradient buffer (produced by the next block's backward or by
+                # autograd's accumulation), nothing else reads it afterwards
+                dx = ops.conv_dgrad(dy1, wb1, g, x.shape[1], x.shape[2], add_into=dout)
             else:
-                ops.add_interior_(dx, ops.reflect_fold(dout, op), 1)
+                dx = ops.conv_dgrad(dy1, wb1, g, x.shape[1], x.shape[2])
+                if op == 1:
+                    ops.add_interior_(dx, dout, 0)
+                else:
+                    ops.add_interior_(dx, ops.reflect_fold(dout, op), 1)
         dgb = (dgb1 + dgb2) if mode == "adain" else None
         return dx, dw1, dw2, None, None, None, None, None, None, dgb, None, None, None
 
@@ -379,7 +391,7 @@ class ResidualPad(Function):
                 dx = torch.zeros(xshape, dtype=G.dtype, device=G.device)
                 ops.add_interior_(dx, G, x_pad)
             else:
-                dx = G
+                dx = G.clone()      # never hand ONE buffer to two producers: a fused ResBlock adds into its gradient
         return dx, G, None, None, None
 
 

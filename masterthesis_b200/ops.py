@@ -333,13 +333,23 @@ def conv_fwd_stats(x, wf, bias, g: ConvGeom):
 
 
 @_checked
-def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win):
-    """dy: dense [N,Ho,Wo,Cout_s] -> dx [N,Hin,Win,Cin_s] (gradient of the padded input buffer)."""
+def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win, add_into=None):
+    """dy: dense [N,Ho,Wo,Cout_s] -> dx [N,Hin,Win,Cin_s] (gradient of the padded input buffer).
+    add_into: a buffer of dx's shape that the result is ADDED to in place (and returned): the skip-path
+    gradient of a residual block, so that no separate add pass runs (stride-1 Conv2d only)."""
     _require_cuda(dy)
     N = dy.shape[0]
     assert dy.is_contiguous() and dy.shape[3] == g.Cout_s
     d = g.desc(N, Hin, Win)
     assert (d.Hout, d.Wout) == tuple(dy.shape[1:3]), (d.Hout, d.Wout, dy.shape)
+    if add_into is not None:
+        assert not g.transposed and g.stride == 1 and not g.pair_s1_dgrad
+        assert tuple(add_into.shape) == (N, Hin, Win, g.Cin_s) and add_into.is_contiguous()
+        with _timed("dgrad", g, N, Hin, Win):
+            check(_lib.lib().mt_conv2d_dgrad_acc(ctypes.byref(d), _p(dy), _p(wb), _p(add_into), 1, _stream()),
+                  "conv_dgrad_acc")
+        _count()
+        return add_into
     dx = empty_act(N, Hin, Win, g.Cin_s, dy.device)
     fn = _lib.lib().mt_conv_transpose2d_dgrad if g.transposed else _lib.lib().mt_conv2d_dgrad
     with _timed("dgrad", g, N, Hin, Win):

@@ -308,6 +308,22 @@ def misc_case(N=3, C=72, H=12, W=20, p=1, seed=0):
     return r
 
 
+def dgrad_acc_case(N=3, C=256, H=20, W=24, seed=0):
+    """mt_conv2d_dgrad_acc: dx += dgrad (the epilogue's TMA reduce-add store) vs dgrad followed by a bf16 add."""
+    torch.manual_seed(seed)
+    g = ConvGeom(C, C, 3, 3, 1, 0)
+    w = bf(torch.randn(C, C, 3, 3, device=DEV) * 0.05)
+    _, wb = ops.pack_weight(w, g)
+    dy = to_nhwc(bf(torch.randn(N, C, H, W, device=DEV)))
+    base = to_nhwc(bf(torch.randn(N, C, H + 2, W + 2, device=DEV)))
+    plain = ops.conv_dgrad(dy, wb, g, H + 2, W + 2)
+    ref = (plain.float() + base.float()).to(torch.bfloat16)
+    acc = base.clone()
+    out = ops.conv_dgrad(dy, wb, g, H + 2, W + 2, add_into=acc)
+    return {"same_buffer": 0.0 if out.data_ptr() == acc.data_ptr() else 1.0,
+            "exact": 0.0 if torch.equal(out, ref) else rel(out, ref)}
+
+
 def adam_case(n=10007, steps=3, seed=0):
     """FlatAdam (mt_adam_flat) vs torch.optim.Adam with coupled weight decay (adain_model.py:58-61)."""
     from masterthesis_b200.optim import FlatAdam
@@ -500,6 +516,12 @@ CASES = {
     "module_forwards": module_forward_case,
     "misc_ops": misc_case,
     "misc_ops_c256": lambda: misc_case(2, 256, 16, 16),
+    # the warp-tiled RGB head (C / 8 in {4, 8, 16}); 12 x 20 planes: a warp's 32 pixels straddle two images
+    "misc_ops_c64": lambda: misc_case(3, 64, 12, 20),
+    "misc_ops_c32": lambda: misc_case(2, 32, 10, 14),
+    "misc_ops_c128": lambda: misc_case(2, 128, 16, 16),
+    # the residual blocks' skip-path gradient added by the data-gradient conv (TMA reduce-add epilogue)
+    "dgrad_accumulate": lambda: dgrad_acc_case(),
     "adam_flat": adam_case,
     "in_big_mean": big_mean_norm_case,
     # ---- the launches of the benchmarked configuration (BASELINE config 3: dim 64, 256x256, batch 8):
