@@ -58,8 +58,8 @@ linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
 //   blocks [0, gw): dW[o][i] (+)= sum_n g[n][o] x[n][i], db[o] (+)= sum_n g[n][o]; thread = (o, i), i fastest:
 //     the N-long loop reads g[n][o] as a warp broadcast and x[n][i] coalesced (independent loads).
 //   blocks [gw, ..): dx[n][i] (+)= sum_o g[n][o] w[o][i] for LIN_ROWS rows per block: the masked gradient rows
-//     are staged in shared memory, block = 64 columns i x 4 slices of the o loop (each thread walks Out / 4
-//     rows of w, coalesced), the four slices are combined in index order.
+//     are staged in shared memory, block = 32 columns i x 8 slices of the o loop (each thread walks Out / 8
+//     rows of w, coalesced, four loads in flight), the eight slices are combined in index order.
 __global__ void __launch_bounds__(256)
 linear_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, const float* __restrict__ x,
                   const float* __restrict__ w, int N, int In, int Out, int act, float* __restrict__ dx,
@@ -97,35 +97,38 @@ linear_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, con
   const int it = bid % gxi, nb = bid / gxi;             // column tile, row block
   const int n0 = nb * LIN_ROWS, rows = min(LIN_ROWS, N - n0);
   float* gs = sm;                                        // [LIN_ROWS][Out] masked gradient rows
-  float* part = sm + LIN_ROWS * Out;                     // [4][LIN_ROWS][64]
+  float* part = sm + LIN_ROWS * Out;                     // [8][LIN_ROWS][32]
   for (int t = threadIdx.x; t < rows * Out; t += blockDim.x) {
     float g = __ldg(dy + (size_t)n0 * Out + t);
     if (act == MT_ACT_RELU && __ldg(y + (size_t)n0 * Out + t) <= 0.f) g = 0.f;
     gs[t] = g;
   }
   __syncthreads();
-  const int il = threadIdx.x & 63, sl = threadIdx.x >> 6;
-  const int i = it * 64 + il;
+  const int il = threadIdx.x & 31, sl = threadIdx.x >> 5;       // 32 columns x 8 slices of the o loop
+  const int i = it * 32 + il;
   float acc[LIN_ROWS];
 #pragma unroll
   for (int j = 0; j < LIN_ROWS; ++j) acc[j] = 0.f;
-  if (i < In)
-    for (int o = sl; o < Out; o += 4) {
+  if (i < In) {
+#pragma unroll 4
+    for (int o = sl; o < Out; o += 8) {
       const float wv = __ldg(w + (size_t)o * In + i);
 #pragma unroll
       for (int j = 0; j < LIN_ROWS; ++j)
         if (j < rows) acc[j] = fmaf(gs[j * Out + o], wv, acc[j]);
     }
+  }
 #pragma unroll
-  for (int j = 0; j < LIN_ROWS; ++j) part[(sl * LIN_ROWS + j) * 64 + il] = acc[j];
+  for (int j = 0; j < LIN_ROWS; ++j) part[(sl * LIN_ROWS + j) * 32 + il] = acc[j];
   __syncthreads();
-  if (sl == 0 && i < In)
-    for (int j = 0; j < rows; ++j) {
-      const float s = (part[(0 * LIN_ROWS + j) * 64 + il] + part[(1 * LIN_ROWS + j) * 64 + il]) +
-                      (part[(2 * LIN_ROWS + j) * 64 + il] + part[(3 * LIN_ROWS + j) * 64 + il]);
-      float* q = dx + (size_t)(n0 + j) * In + i;
-      *q = acc_dx ? *q + s : s;
-    }
+  if (sl < rows && i < In) {                                    // warp j combines row j, slices in index order
+    const int j = sl;
+    float s = part[j * 32 + il];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) s += part[(k * LIN_ROWS + j) * 32 + il];
+    float* q = dx + (size_t)(n0 + j) * In + i;
+    *q = acc_dx ? *q + s : s;
+  }
 }
 
 static int launch_linear_fwd(const float* x, const float* w, const float* b, int N, int In, int Out, int act,
@@ -143,10 +146,10 @@ static int launch_linear_bwd(const float* dy, const float* y, const float* x, co
   if (act == MT_ACT_RELU && !y) return -1008;
   if ((long long)Out * In >= (1ll << 31) || (long long)N * In >= (1ll << 31)) return -1005;
   const int gw = (dw || db) ? (Out * In + 255) / 256 : 0;
-  const int gxi = (In + 63) / 64;
+  const int gxi = (In + 31) / 32;
   const int gx = dx ? gxi * ((N + LIN_ROWS - 1) / LIN_ROWS) : 0;
   if (gw + gx == 0) return 0;
-  const size_t smem = dx ? ((size_t)LIN_ROWS * Out + 4 * LIN_ROWS * 64) * sizeof(float) : 0;
+  const size_t smem = dx ? ((size_t)LIN_ROWS * Out + 8 * LIN_ROWS * 32) * sizeof(float) : 0;
   if (smem > 48 * 1024) return -1005;                    // Out <= 1280
   linear_bwd_kernel<<<gw + gx, 256, smem, st>>>(dy, y, x, w, N, In, Out, act, dx, dw, db, acc_param, acc_dx, gw, gxi);
   return cuda_rc();

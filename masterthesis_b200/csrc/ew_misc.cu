@@ -298,10 +298,10 @@ rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
 // as one coalesced 128-byte row per plane (lane = pixel), shuffled between the two lane mappings.  The
 // thread-per-pixel kernels above moved 134 MB at 1.8 - 2.1 TB/s (16-byte loads 128 bytes apart, scattered
 // 4-byte plane accesses); they remain the fallback for other channel counts.
-template <int V>
+template <int V, int Co>
 __global__ void __launch_bounds__(256)
 rgb_head_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, long long total,
-                         int HW, int Co, float* __restrict__ y) {
+                         int HW, float* __restrict__ y) {
   constexpr int C = V * 8, P = 32 / V;
   const int lane = threadIdx.x & 31, v = lane % V, q = lane / V;
   float4 wq[8];
@@ -326,19 +326,25 @@ rgb_head_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const float* __res
       cvt8(xr[s], f);
       float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        a0 = fmaf(f[j], wq[j].x, a0); a1 = fmaf(f[j], wq[j].y, a1);
-        a2 = fmaf(f[j], wq[j].z, a2); a3 = fmaf(f[j], wq[j].w, a3);
+      for (int j = 0; j < 8; ++j) {        // Co is a template constant: the FMA pipe, not HBM, bounds this loop
+        a0 = fmaf(f[j], wq[j].x, a0);
+        if (Co > 1) a1 = fmaf(f[j], wq[j].y, a1);
+        if (Co > 2) a2 = fmaf(f[j], wq[j].z, a2);
+        if (Co > 3) a3 = fmaf(f[j], wq[j].w, a3);
       }
 #pragma unroll
       for (int o = 1; o < V; o <<= 1) {
-        a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
-        a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+        a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+        if (Co > 1) a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+        if (Co > 2) a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+        if (Co > 3) a3 += __shfl_xor_sync(0xffffffffu, a3, o);
       }
       // pixel (s * P + q) of the warp's 32 belongs to lane s * P + q: fetch it from the group's first lane
       const int src = (lane % P) * V;
-      const float t0 = __shfl_sync(0xffffffffu, a0, src), t1 = __shfl_sync(0xffffffffu, a1, src);
-      const float t2 = __shfl_sync(0xffffffffu, a2, src), t3 = __shfl_sync(0xffffffffu, a3, src);
+      float t0 = __shfl_sync(0xffffffffu, a0, src), t1 = 0.f, t2 = 0.f, t3 = 0.f;
+      if (Co > 1) t1 = __shfl_sync(0xffffffffu, a1, src);
+      if (Co > 2) t2 = __shfl_sync(0xffffffffu, a2, src);
+      if (Co > 3) t3 = __shfl_sync(0xffffffffu, a3, src);
       if (lane / P == s) { r0 = t0; r1 = t1; r2 = t2; r3 = t3; }
     }
     const long long pix = base + lane;
@@ -353,23 +359,19 @@ rgb_head_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const float* __res
   }
 }
 
-template <int V>
-__global__ void __launch_bounds__(256)
+template <int V, int Co>
+__global__ void __launch_bounds__(256, 2)      // 2 CTAs / SM: 16 warps to cover the load latency
 rgb_head_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                          const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, long long total,
-                         int HW, int Co, __nv_bfloat16* __restrict__ dx, float* __restrict__ dwp) {
+                         int HW, __nv_bfloat16* __restrict__ dx, float* __restrict__ dwp) {
   constexpr int C = V * 8, P = 32 / V;
   extern __shared__ float red[];               // [256 / V][V][32]
   const int lane = threadIdx.x & 31, v = lane % V, q = lane / V;
-  float4 wq[8];
+  float wq[8][Co], acc[8][Co];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float* wr = wgt + (v * 8 + j) * Co;
-    wq[j] = make_float4(__ldg(wr), Co > 1 ? __ldg(wr + 1) : 0.f, Co > 2 ? __ldg(wr + 2) : 0.f, Co > 3 ? __ldg(wr + 3) : 0.f);
-  }
-  float acc[8][4];
+  for (int j = 0; j < 8; ++j)
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+    for (int o = 0; o < Co; ++o) { wq[j][o] = __ldg(wgt + (v * 8 + j) * Co + o); acc[j][o] = 0.f; }
   const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
   for (long long base = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 32; base < total;
        base += warps * 32) {
@@ -395,18 +397,21 @@ rgb_head_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__
 #pragma unroll
     for (int s = 0; s < V; ++s) {
       const int src = s * P + q;               // the lane that holds this step's pixel
-      float g[4];
+      float g[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int o = 0; o < 4; ++o) g[o] = __shfl_sync(0xffffffffu, G[o], src);
+      for (int o = 0; o < Co; ++o) g[o] = __shfl_sync(0xffffffffu, G[o], src);
       const long long pix = base + s * P + q;
       if (pix < total) {
         float f[8], d[8];
         cvt8(xr[s], f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          d[j] = g[0] * wq[j].x + g[1] * wq[j].y + g[2] * wq[j].z + g[3] * wq[j].w;
-          acc[j][0] = fmaf(f[j], g[0], acc[j][0]); acc[j][1] = fmaf(f[j], g[1], acc[j][1]);
-          acc[j][2] = fmaf(f[j], g[2], acc[j][2]); acc[j][3] = fmaf(f[j], g[3], acc[j][3]);
+        for (int j = 0; j < 8; ++j) {      // 2 * Co FMAs per element: the FMA pipe, not HBM, bounds this loop
+          float dj = g[0] * wq[j][0];
+#pragma unroll
+          for (int o = 1; o < Co; ++o) dj = fmaf(g[o], wq[j][o], dj);
+          d[j] = dj;
+#pragma unroll
+          for (int o = 0; o < Co; ++o) acc[j][o] = fmaf(f[j], g[o], acc[j][o]);
         }
         store8(dx + pix * C + v * 8, d);
       }
@@ -416,7 +421,7 @@ rgb_head_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__
 #pragma unroll
   for (int j = 0; j < 8; ++j)
 #pragma unroll
-    for (int o = 0; o < 4; ++o) red[(pl * V + v) * 32 + j * 4 + o] = acc[j][o];
+    for (int o = 0; o < 4; ++o) red[(pl * V + v) * 32 + j * 4 + o] = o < Co ? acc[j][o < Co ? o : 0] : 0.f;
   __syncthreads();
   for (int t = threadIdx.x; t < V * 32; t += blockDim.x) {
     float s = 0.f;
@@ -426,19 +431,31 @@ rgb_head_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__
   }
 }
 
+// dw[c][o] = sum over the per-block partials, block = 32 (c, o) columns x 8 groups of partials, the groups
+// combined in index order (fixed summation order)
 __global__ void __launch_bounds__(256)
 rgb_head_dw_reduce_kernel(const float* __restrict__ dwp, int parts, int C, int Co, float* __restrict__ dw) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;     // (c, o) with o < 4
-  if (t >= C * 4) return;
+  __shared__ float sm[8][33];
+  const int cl = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int t = blockIdx.x * 32 + cl;                      // (c, o) with o < 4
   float a[4] = {0.f, 0.f, 0.f, 0.f};
-  int i = 0;
-  for (; i + 3 < parts; i += 4) {
+  if (t < C * 4) {
+    int i = g;
+    for (; i + 24 < parts; i += 32) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u) a[u] += dwp[(size_t)(i + u) * C * 4 + t];
+      for (int u = 0; u < 4; ++u) a[u] += dwp[(size_t)(i + 8 * u) * C * 4 + t];
+    }
+    for (; i < parts; i += 8) a[0] += dwp[(size_t)i * C * 4 + t];
   }
-  for (; i < parts; ++i) a[0] += dwp[(size_t)i * C * 4 + t];
-  const int c = t >> 2, o = t & 3;
-  if (o < Co) dw[c * Co + o] = (a[0] + a[1]) + (a[2] + a[3]);
+  sm[g][cl] = (a[0] + a[1]) + (a[2] + a[3]);
+  __syncthreads();
+  if (g == 0 && t < C * 4) {
+    float v = sm[0][cl];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) v += sm[k][cl];
+    const int c = t >> 2, o = t & 3;
+    if (o < Co) dw[c * Co + o] = v;
+  }
 }
 
 // sum of squares over the interior of a padded buffer (per-block partial sums, added in block order by
@@ -658,12 +675,16 @@ extern "C" int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int
   if (C % 8 || Co > 4 || Co < 1) return -1003;
   const long long total = (long long)N * HW;
   const int wgrid = grid_for((total + 255) / 256, 1, 16);     // 8 warps x 32 pixels per block and pass
-  switch (C / 8) {
-    case 4: rgb_head_fwd_warp_kernel<4><<<wgrid, 256, 0, ST(stream)>>>(CBF(x), w, total, HW, Co, y); return cuda_rc();
-    case 8: rgb_head_fwd_warp_kernel<8><<<wgrid, 256, 0, ST(stream)>>>(CBF(x), w, total, HW, Co, y); return cuda_rc();
-    case 16: rgb_head_fwd_warp_kernel<16><<<wgrid, 256, 0, ST(stream)>>>(CBF(x), w, total, HW, Co, y); return cuda_rc();
+#define MT_RGB_F(V_, CO_) rgb_head_fwd_warp_kernel<V_, CO_><<<wgrid, 256, 0, ST(stream)>>>(CBF(x), w, total, HW, y); return cuda_rc()
+  switch ((C / 8) * 10 + Co) {
+    case 43: MT_RGB_F(4, 3);   case 83: MT_RGB_F(8, 3);   case 163: MT_RGB_F(16, 3);
+    case 41: MT_RGB_F(4, 1);   case 81: MT_RGB_F(8, 1);   case 161: MT_RGB_F(16, 1);
+    case 44: MT_RGB_F(4, 4);
+    case 84: MT_RGB_F(8, 4);
+    case 164: MT_RGB_F(16, 4);
     default: break;
   }
+#undef MT_RGB_F
   rgb_head_fwd_kernel<<<grid_for((long long)N * HW, 256), 256, (size_t)C * 4 * sizeof(float),
                         ST(stream)>>>(CBF(x), w, N, HW, C, Co, y);
   return cuda_rc();
@@ -683,14 +704,18 @@ extern "C" int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, c
   if (parts != grid || !dw_parts) return -1012;
   const long long total = (long long)N * HW;
   const size_t wsmem = (size_t)256 * 32 * sizeof(float);
-  switch (V) {
-    case 4: rgb_head_bwd_warp_kernel<4><<<grid, 256, wsmem, ST(stream)>>>(dy, y, CBF(x), w, total, HW, Co, BF(dx), dw_parts); break;
-    case 8: rgb_head_bwd_warp_kernel<8><<<grid, 256, wsmem, ST(stream)>>>(dy, y, CBF(x), w, total, HW, Co, BF(dx), dw_parts); break;
-    case 16: rgb_head_bwd_warp_kernel<16><<<grid, 256, wsmem, ST(stream)>>>(dy, y, CBF(x), w, total, HW, Co, BF(dx), dw_parts); break;
+#define MT_RGB_B(V_, CO_) rgb_head_bwd_warp_kernel<V_, CO_><<<grid, 256, wsmem, ST(stream)>>>(dy, y, CBF(x), w, total, HW, BF(dx), dw_parts); break
+  switch (V * 10 + Co) {
+    case 43: MT_RGB_B(4, 3);   case 83: MT_RGB_B(8, 3);   case 163: MT_RGB_B(16, 3);
+    case 41: MT_RGB_B(4, 1);   case 81: MT_RGB_B(8, 1);   case 161: MT_RGB_B(16, 1);
+    case 44: MT_RGB_B(4, 4);
+    case 84: MT_RGB_B(8, 4);
+    case 164: MT_RGB_B(16, 4);
     default:
       rgb_head_bwd_kernel<<<grid, 256, smem, ST(stream)>>>(dy, y, CBF(x), w, N, HW, C, Co, BF(dx), dw_parts);
   }
-  rgb_head_dw_reduce_kernel<<<(C * 4 + 255) / 256, 256, 0, ST(stream)>>>(dw_parts, parts, C, Co, dw);
+#undef MT_RGB_B
+  rgb_head_dw_reduce_kernel<<<(C * 4 + 31) / 32, 256, 0, ST(stream)>>>(dw_parts, parts, C, Co, dw);
   return cuda_rc();
 }
 extern "C" int mt_sumsq_interior_parts(int N, int H, int W, int C) {
