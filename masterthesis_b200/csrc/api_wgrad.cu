@@ -5,6 +5,7 @@
 
 #include "../../include/mt_b200.h"
 #include "igemm.cuh"
+#include "ew_common.cuh"
 
 namespace mt {
 
@@ -99,6 +100,7 @@ __device__ __forceinline__ unsigned w_index(unsigned co, unsigned ci, unsigned r
 __global__ void pack_weight_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh_, int kw_,
                                    int transposed, int window, __nv_bfloat16* __restrict__ wf,
                                    __nv_bfloat16* __restrict__ wb) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned nf = window ? kh * Cout * 64 : kh * kw * Cout * Cin_s;
@@ -142,6 +144,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Cout_, int C
 __global__ void __launch_bounds__(256)
 pack_weight_pairs_kernel(const float* __restrict__ w, int Cout_, int Cin_, int T_, int transposed,
                          __nv_bfloat16* __restrict__ wf, __nv_bfloat16* __restrict__ wb) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, T = T_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned n0 = wf ? Cout * Cin_s : 0, n1 = wb ? Cin * Cout_s : 0;
@@ -173,6 +176,7 @@ __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int splits, uns
                                     int Cout_, int Cin_, int kh_, int kw_,
                                     int transposed, int window, int accumulate,
                                     float* __restrict__ dw) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned n = Cout * Cin * kh * kw;
@@ -200,6 +204,7 @@ __global__ void unpack_wgrad_kernel(const float* __restrict__ g, int splits, uns
 // (0,0) -> 1, (1,0) -> 2, (1,1) -> 0, (0,1) -> none (zero block).  Source W[ci][co][r][s].
 __global__ void __launch_bounds__(256)
 pack_convT3x3s2_kernel(const float* __restrict__ w, int Cout_, int Cin_, __nv_bfloat16* __restrict__ wf) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned rows = 2 * Cout_s, per_tap = rows * Cin_s, n = 6 * per_tap;
@@ -224,6 +229,7 @@ pack_convT3x3s2_kernel(const float* __restrict__ w, int Cout_, int Cin_, __nv_bf
 __global__ void __launch_bounds__(256)
 pack_conv_s2_dgrad_kernel(const float* __restrict__ w, int Cout_, int Cin_, int k_,
                           __nv_bfloat16* __restrict__ wb) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, k = k_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned nr0 = (k + 1) / 2, nr1 = k / 2;
@@ -246,6 +252,7 @@ pack_conv_s2_dgrad_kernel(const float* __restrict__ w, int Cout_, int Cin_, int 
 __global__ void __launch_bounds__(256)
 pack_window_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh_, int kw_, int stride_,
                         __nv_bfloat16* __restrict__ wf) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_, stride = stride_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned n = kh * 2 * Cout_s * 64;
@@ -267,6 +274,7 @@ pack_window_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int kh
 __global__ void __launch_bounds__(256)
 pack_conv_s1_dgrad_pair_kernel(const float* __restrict__ w, int Cout_, int Cin_, int k_,
                                __nv_bfloat16* __restrict__ wb) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, k = k_;
   const unsigned Cout_s = (Cout + 7) & ~7u;
   const unsigned per_tap = 16 * Cout_s, n = k * (k + 1) * per_tap;
@@ -288,6 +296,7 @@ __global__ void unpack_window_pair_wgrad_kernel(const float* __restrict__ g, int
                                                 int Cout_, int Cin_, int kh_,
                                                 int kw_, int stride_, int accumulate,
                                                 float* __restrict__ dw) {
+  pdl_wait(); pdl_launch();
   const unsigned Cout = Cout_, Cin = Cin_, kh = kh_, kw = kw_, stride = stride_;
   const unsigned Cin_s = (Cin + 7) & ~7u, Cout_s = (Cout + 7) & ~7u;
   const unsigned n = Cout * Cin * kh * kw;
@@ -317,7 +326,7 @@ extern "C" int mt_pack_conv_s1_dgrad_pair_weight(const float* w, int Cout, int C
   if (n >= (1ll << 31) || Cin > 8) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_conv_s1_dgrad_pair_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, k,
+  launch_pdl(pack_conv_s1_dgrad_pair_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, Cout, Cin, k,
                                                                            (__nv_bfloat16*)w_bwd);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
@@ -330,7 +339,7 @@ extern "C" int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int spli
   if (n >= (1ll << 31) || per >= (1ll << 31) || splits < 1) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  unpack_window_pair_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, splits, (unsigned)per,
+  launch_plain(unpack_window_pair_wgrad_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, dw_packed, splits, (unsigned)per,
                                                                             Cout, Cin, kh, kw, stride,
                                                                             accumulate, dw);
   cudaError_t e = cudaGetLastError();
@@ -346,7 +355,7 @@ extern "C" int mt_pack_conv_window_pair_weight(const float* w, int Cout, int Cin
   if (n >= (1ll << 31)) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_window_pair_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, kh, kw, stride,
+  launch_pdl(pack_window_pair_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, Cout, Cin, kh, kw, stride,
                                                                     (__nv_bfloat16*)w_fwd);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
@@ -361,7 +370,7 @@ extern "C" int mt_pack_conv_s2_dgrad_weight(const float* w, int Cout, int Cin, i
   if (n >= (1ll << 31) || (k != 3 && k != 4)) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_conv_s2_dgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, k, (__nv_bfloat16*)w_bwd);
+  launch_pdl(pack_conv_s2_dgrad_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, Cout, Cin, k, (__nv_bfloat16*)w_bwd);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
 }
@@ -374,7 +383,7 @@ extern "C" int mt_pack_convT3x3s2_weight(const float* w, int Cout, int Cin, void
   if (n >= (1ll << 31)) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_convT3x3s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, (__nv_bfloat16*)w_fwd);
+  launch_pdl(pack_convT3x3s2_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, Cout, Cin, (__nv_bfloat16*)w_fwd);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
 }
@@ -398,14 +407,14 @@ extern "C" int mt_pack_conv_weight(const float* w, int Cout, int Cin, int kh, in
     int pb = (int)((pairs + 255) / 256);
     if (pb > 148 * 16) pb = 148 * 16;
     if (pb < 1) pb = 1;
-    pack_weight_pairs_kernel<<<pb, 256, 0, (cudaStream_t)stream>>>(
+    launch_pdl(pack_weight_pairs_kernel, dim3(pb), dim3(256), 0, (cudaStream_t)stream, 
         w, Cout, Cin, kh * kw, transposed, (__nv_bfloat16*)w_fwd, (__nv_bfloat16*)w_bwd);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
   }
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  pack_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+  launch_pdl(pack_weight_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, 
       w, Cout, Cin, kh, kw, transposed, window, (__nv_bfloat16*)w_fwd, (__nv_bfloat16*)w_bwd);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
@@ -425,7 +434,7 @@ extern "C" int mt_unpack_conv_wgrad(const float* dw_packed, int splits, int Cout
   if (n >= (1ll << 31) || per >= (1ll << 31) || splits < 1) return -1005;
   int blocks = (int)((n + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  unpack_wgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dw_packed, splits, (unsigned)per, Cout, Cin,
+  launch_plain(unpack_wgrad_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, dw_packed, splits, (unsigned)per, Cout, Cin,
                                                                 kh, kw, transposed, window, accumulate, dw);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;

@@ -4,8 +4,42 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
 
 namespace mt {
+
+// ---- programmatic dependent launch (PDL).  A kernel launched with the attribute may start (prologue, block
+// scheduling) while its predecessor in the stream is still draining; it must execute pdl_wait() before its
+// first access to global memory (the wait returns once the predecessor has completed and its writes are
+// visible).  pdl_launch() lets the NEXT kernel's blocks be scheduled from that point on.  Both are no-ops for
+// a kernel launched without the attribute.  MT_PDL=0 launches everything with plain stream ordering.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+static inline bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MT_PDL"); v = e ? (atoi(e) != 0) : 1; }
+  return v != 0;
+}
+template <bool PDL = true, typename K, typename... Args>
+static inline cudaError_t launch_pdl(K kern, dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = (PDL && pdl_enabled()) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+// plain stream ordering for a kernel that follows a LONG kernel on a side stream (the weight-gradient
+// unpack behind igemm_wgrad_kernel): launched early, its grid of up to 2 368 CTAs would sit resident in
+// griddepcontrol.wait for the whole weight-gradient kernel and take the thread slots the main stream's
+// norm kernels run in (measured: the gain of PDL on the main chain disappeared)
+template <typename K, typename... Args>
+static inline cudaError_t launch_plain(K kern, dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  return launch_pdl<false>(kern, grid, block, smem, st, args...);
+}
 
 static constexpr int NUM_SMS = 148;
 

@@ -25,6 +25,7 @@ constexpr int LIN_ROWS = 8;     // rows of x (or g) a block keeps in shared memo
 __global__ void __launch_bounds__(256)
 linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                   int N, int In, int Out, int act, float* __restrict__ y) {
+  pdl_wait(); pdl_launch();
   extern __shared__ float xs[];               // [LIN_ROWS][In]
   const int n0 = blockIdx.y * LIN_ROWS, rows = min(LIN_ROWS, N - n0);
   for (int t = threadIdx.x; t < rows * In; t += blockDim.x) xs[t] = __ldg(x + (size_t)n0 * In + t);
@@ -64,6 +65,7 @@ __global__ void __launch_bounds__(256)
 linear_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, const float* __restrict__ x,
                   const float* __restrict__ w, int N, int In, int Out, int act, float* __restrict__ dx,
                   float* __restrict__ dw, float* __restrict__ db, int acc_param, int acc_dx, int gw, int gxi) {
+  pdl_wait(); pdl_launch();
   extern __shared__ float sm[];
   if ((int)blockIdx.x < gw) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -136,7 +138,7 @@ static int launch_linear_fwd(const float* x, const float* w, const float* b, int
   if (N < 1 || In < 1 || Out < 1 || (act != MT_ACT_NONE && act != MT_ACT_RELU)) return -1005;
   const size_t smem = (size_t)LIN_ROWS * In * sizeof(float);
   if (smem > 48 * 1024) return -1005;                    // In <= 1536
-  linear_fwd_kernel<<<dim3((Out + 7) / 8, (N + LIN_ROWS - 1) / LIN_ROWS), 256, smem, st>>>(x, w, b, N, In, Out, act, y);
+  launch_pdl(linear_fwd_kernel, dim3(dim3((Out + 7) / 8, (N + LIN_ROWS - 1) / LIN_ROWS)), dim3(256), smem, st, x, w, b, N, In, Out, act, y);
   return cuda_rc();
 }
 static int launch_linear_bwd(const float* dy, const float* y, const float* x, const float* w, int N, int In,
@@ -151,7 +153,7 @@ static int launch_linear_bwd(const float* dy, const float* y, const float* x, co
   if (gw + gx == 0) return 0;
   const size_t smem = dx ? ((size_t)LIN_ROWS * Out + 8 * LIN_ROWS * 32) * sizeof(float) : 0;
   if (smem > 48 * 1024) return -1005;                    // Out <= 1280
-  linear_bwd_kernel<<<gw + gx, 256, smem, st>>>(dy, y, x, w, N, In, Out, act, dx, dw, db, acc_param, acc_dx, gw, gxi);
+  launch_pdl(linear_bwd_kernel, dim3(gw + gx), dim3(256), smem, st, dy, y, x, w, N, In, Out, act, dx, dw, db, acc_param, acc_dx, gw, gxi);
   return cuda_rc();
 }
 
@@ -164,6 +166,7 @@ __global__ void __launch_bounds__(256)
 dis_head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w1,
                     const float* __restrict__ w2, int SS, int Cs, int C, int nd, int S,
                     float* __restrict__ out, float* __restrict__ cls) {
+  pdl_wait(); pdl_launch();
   extern __shared__ float red[];            // [256][SS + nd]
   const int n = blockIdx.x, tid = threadIdx.x, NV = SS + nd;
   float* mine = red + tid * NV;
@@ -215,6 +218,7 @@ dis_head_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ dc
                     const float* __restrict__ w2, int N, int SS, int Cs, int C, int nd, int S,
                     __nv_bfloat16* __restrict__ dh, float* __restrict__ dw1, float* __restrict__ dw2,
                     int accumulate, int ga, int gb, int cls_first) {
+  pdl_wait(); pdl_launch();
   const int So = S + 2;
   if ((int)blockIdx.x < ga) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -291,6 +295,7 @@ __device__ __forceinline__ float block_sum_256(float v, float* sm) {
 __global__ void __launch_bounds__(256)
 bce_logits_kernel(const float* __restrict__ x, const float* __restrict__ target, float tconst, int n,
                   float gscale, float* __restrict__ loss_out, float* __restrict__ dx) {
+  pdl_wait(); pdl_launch();
   __shared__ float sm[8];
   float s = 0.f;
   const float inv = 1.f / (float)n;
@@ -308,6 +313,7 @@ bce_logits_kernel(const float* __restrict__ x, const float* __restrict__ target,
 __global__ void __launch_bounds__(256)
 l1_partial_kernel(const float* __restrict__ a, const float* __restrict__ b, long long n, float gscale,
                   float* __restrict__ part, float* __restrict__ da) {
+  pdl_wait(); pdl_launch();
   __shared__ float sm[8];
   float s = 0.f;
   const float k = gscale / (float)n;
@@ -331,6 +337,7 @@ l1_partial_kernel(const float* __restrict__ a, const float* __restrict__ b, long
 }
 __global__ void __launch_bounds__(256)
 scaled_sum_kernel(const float* __restrict__ part, int parts, float scale, float* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   __shared__ float sm[8];
   float s = 0.f;
   for (int i = threadIdx.x; i < parts; i += blockDim.x) s += part[i];
@@ -343,6 +350,7 @@ scaled_sum_kernel(const float* __restrict__ part, int parts, float scale, float*
 __global__ void __launch_bounds__(256)
 kl_normal_kernel(const float* __restrict__ mu, const float* __restrict__ logvar, int n, float gscale,
                  float* __restrict__ loss_out, float* __restrict__ dmu, float* __restrict__ dlogvar) {
+  pdl_wait(); pdl_launch();
   __shared__ float sm[8];
   float s = 0.f;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -425,7 +433,7 @@ extern "C" int mt_dis_head_fwd(const void* h, const float* w1, const float* w2, 
     if (e != cudaSuccess) return -(int)e;
     attr_set = true;
   }
-  dis_head_fwd_kernel<<<N, 256, smem, ST(stream)>>>((const __nv_bfloat16*)h, w1, w2, S * S, Cs, C, nd, S, out, cls);
+  launch_pdl(dis_head_fwd_kernel, dim3(N), dim3(256), smem, ST(stream), (const __nv_bfloat16*)h, w1, w2, S * S, Cs, C, nd, S, out, cls);
   return cuda_rc();
 }
 extern "C" int mt_dis_head_bwd(const float* dout, const float* dcls, const void* h, const float* w1,
@@ -439,7 +447,7 @@ extern "C" int mt_dis_head_bwd(const float* dout, const float* dcls, const void*
   const int gb = params ? (S * S * C + 255) / 256 : 0;
   const int gc = params ? (C + 31) / 32 : 0;
   if (ga + gb + gc == 0) return 0;
-  dis_head_bwd_kernel<<<ga + gb + gc, 256, 0, ST(stream)>>>(dout, dcls, (const __nv_bfloat16*)h, w1, w2, N, S * S, Cs,
+  launch_pdl(dis_head_bwd_kernel, dim3(ga + gb + gc), dim3(256), 0, ST(stream), dout, dcls, (const __nv_bfloat16*)h, w1, w2, N, S * S, Cs,
                                                            C, nd, S, (__nv_bfloat16*)dh, dw1, dw2, accumulate, ga, gb,
                                                            cls_first);
   return cuda_rc();
@@ -448,7 +456,7 @@ extern "C" int mt_dis_head_bwd(const float* dout, const float* dcls, const void*
 extern "C" int mt_loss_bce_logits(const float* x, const float* target, float target_const, int n, float gscale,
                                   float* loss, float* dx, void* stream) {
   if (n < 1 || !loss) return -1005;
-  bce_logits_kernel<<<1, 256, 0, ST(stream)>>>(x, target, target_const, n, gscale, loss, dx);
+  launch_pdl(bce_logits_kernel, dim3(1), dim3(256), 0, ST(stream), x, target, target_const, n, gscale, loss, dx);
   return cuda_rc();
 }
 extern "C" int mt_loss_l1_parts(long long n) { return n < 1 ? 0 : grid_for((n + 3) / 4, 256, 2); }
@@ -457,13 +465,13 @@ extern "C" int mt_loss_l1(const float* a, const float* b, long long n, float wei
   if (n < 1 || !loss) return -1005;
   if (parts != mt_loss_l1_parts(n) || !partials) return -1012;
   if ((((uintptr_t)a | (uintptr_t)b | (uintptr_t)da) & 15) != 0) return -1005;
-  l1_partial_kernel<<<parts, 256, 0, ST(stream)>>>(a, b, n, gscale, partials, da);
-  scaled_sum_kernel<<<1, 256, 0, ST(stream)>>>(partials, parts, weight / (float)n, loss);
+  launch_pdl(l1_partial_kernel, dim3(parts), dim3(256), 0, ST(stream), a, b, n, gscale, partials, da);
+  launch_pdl(scaled_sum_kernel, dim3(1), dim3(256), 0, ST(stream), partials, parts, weight / (float)n, loss);
   return cuda_rc();
 }
 extern "C" int mt_loss_kl_normal(const float* mu, const float* logvar, int n, float gscale, float* loss,
                                  float* dmu, float* dlogvar, void* stream) {
   if (n < 1 || !loss || ((dmu == nullptr) != (dlogvar == nullptr))) return -1005;
-  kl_normal_kernel<<<1, 256, 0, ST(stream)>>>(mu, logvar, n, gscale, loss, dmu, dlogvar);
+  launch_pdl(kl_normal_kernel, dim3(1), dim3(256), 0, ST(stream), mu, logvar, n, gscale, loss, dmu, dlogvar);
   return cuda_rc();
 }

@@ -10,6 +10,7 @@ namespace mt {
 __global__ void image_to_nhwc_kernel(const float* __restrict__ img, const float* __restrict__ onehot,
                                      int N, int Ci, int nd, int H, int W, int p, int Cs,
                                      __nv_bfloat16* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = Cs / 8;
   const long long total = (long long)N * Hp * Wp * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -33,6 +34,7 @@ __global__ void image_to_nhwc_kernel(const float* __restrict__ img, const float*
 // Adjoint: dpad [N,H+2p,W+2p,Cs] bf16 -> dimg [N,Ci,H,W] fp32 (border folded onto interior).
 __global__ void image_grad_kernel(const __nv_bfloat16* __restrict__ dpad, int N, int Ci, int H,
                                   int W, int p, int Cs, float* __restrict__ dimg) {
+  pdl_wait(); pdl_launch();
   const int Wp = W + 2 * p, Hp = H + 2 * p;
   const long long total = (long long)N * H * W;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -55,6 +57,7 @@ __global__ void image_grad_kernel(const __nv_bfloat16* __restrict__ dpad, int N,
 // Fill the reflection border of buf [N,H+2p,W+2p,C] from its interior, in place.
 __global__ void reflect_border_kernel(__nv_bfloat16* __restrict__ buf, int N, int H, int W, int C,
                                       int p) {
+  pdl_wait(); pdl_launch();
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const int border_px = Hp * Wp - H * W;
   const long long total = (long long)N * border_px * V;
@@ -81,6 +84,7 @@ __global__ void reflect_border_kernel(__nv_bfloat16* __restrict__ buf, int N, in
 // dense[n,h,w,:] = sum of dpad over the padded positions that mirrored (h,w)
 __global__ void reflect_fold_kernel(const __nv_bfloat16* __restrict__ dpad, int N, int H, int W,
                                     int C, int p, __nv_bfloat16* __restrict__ dense) {
+  pdl_wait(); pdl_launch();
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const long long total = (long long)N * H * W * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -105,6 +109,7 @@ __global__ void reflect_fold_kernel(const __nv_bfloat16* __restrict__ dpad, int 
 // dpad[n, h+p, w+p, :] += dense[n,h,w,:]
 __global__ void add_interior_kernel(__nv_bfloat16* __restrict__ dpad, const __nv_bfloat16* dense,
                                     int N, int H, int W, int C, int p) {
+  pdl_wait(); pdl_launch();
   const int Hp = H + 2 * p, Wp = W + 2 * p, V = C / 8;
   const long long total = (long long)N * H * W * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -130,14 +135,14 @@ extern "C" int mt_image_to_nhwc(const float* img, const float* onehot, int N, in
                                 int W, int pad, int Cs, void* out, void* stream) {
   if (Cs % 8 || Ci + nd > Cs) return -1003;
   const long long total = (long long)N * (H + 2 * pad) * (W + 2 * pad) * (Cs / 8);
-  image_to_nhwc_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
+  launch_pdl(image_to_nhwc_kernel, dim3(grid_for(total, 256)), dim3(256), 0, ST(stream), 
       img, onehot, N, Ci, onehot ? nd : 0, H, W, pad, Cs, (__nv_bfloat16*)out);
   return cuda_rc();
 }
 extern "C" int mt_image_grad_from_nhwc(const void* dpad, int N, int Ci, int H, int W, int pad,
                                        int Cs, float* dimg, void* stream) {
   if (Cs != 8 || Ci > 8) return -1003;
-  image_grad_kernel<<<grid_for((long long)N * H * W, 256), 256, 0, ST(stream)>>>(
+  launch_pdl(image_grad_kernel, dim3(grid_for((long long)N * H * W, 256)), dim3(256), 0, ST(stream), 
       (const __nv_bfloat16*)dpad, N, Ci, H, W, pad, Cs, dimg);
   return cuda_rc();
 }
@@ -147,7 +152,7 @@ extern "C" int mt_reflect_border(void* buf, int N, int H, int W, int C, int pad,
   if (pad >= H || pad >= W) return -1007;
   const long long total =
       (long long)N * ((H + 2 * pad) * (W + 2 * pad) - H * W) * (C / 8);
-  reflect_border_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((__nv_bfloat16*)buf, N, H,
+  launch_pdl(reflect_border_kernel, dim3(grid_for(total, 256)), dim3(256), 0, ST(stream), (__nv_bfloat16*)buf, N, H,
                                                                        W, C, pad);
   return cuda_rc();
 }
@@ -155,7 +160,7 @@ extern "C" int mt_reflect_fold(const void* dpad, int N, int H, int W, int C, int
                                void* stream) {
   if (C % 8) return -1003;
   const long long total = (long long)N * H * W * (C / 8);
-  reflect_fold_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
+  launch_pdl(reflect_fold_kernel, dim3(grid_for(total, 256)), dim3(256), 0, ST(stream), 
       (const __nv_bfloat16*)dpad, N, H, W, C, pad, (__nv_bfloat16*)dense);
   return cuda_rc();
 }
@@ -163,7 +168,7 @@ extern "C" int mt_add_interior(void* dpad, const void* dense, int N, int H, int 
                                void* stream) {
   if (C % 8) return -1003;
   const long long total = (long long)N * H * W * (C / 8);
-  add_interior_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>(
+  launch_pdl(add_interior_kernel, dim3(grid_for(total, 256)), dim3(256), 0, ST(stream), 
       (__nv_bfloat16*)dpad, (const __nv_bfloat16*)dense, N, H, W, C, pad);
   return cuda_rc();
 }

@@ -10,6 +10,7 @@ namespace mt {
 __global__ void __launch_bounds__(256)
 avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int p, int N, int H, int W, int C,
                     __nv_bfloat16* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * Ho * Wo * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -36,6 +37,7 @@ avgpool2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int p, int N, int H, in
 __global__ void __launch_bounds__(256)
 avgpool2_bwd_add_kernel(const __nv_bfloat16* __restrict__ dpo, __nv_bfloat16* __restrict__ dpad,
                         int p, int N, int H, int W, int C) {
+  pdl_wait(); pdl_launch();
   const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * H * W * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -58,6 +60,7 @@ __global__ void __launch_bounds__(256)
 pool_add_act_fwd_kernel(const __nv_bfloat16* __restrict__ c, const __nv_bfloat16* __restrict__ d,
                         int N, int H, int W, int C, int act, float slope,
                         __nv_bfloat16* __restrict__ out, int po) {
+  pdl_wait(); pdl_launch();
   const int Ho = H / 2, Wo = W / 2, V = C / 8;
   const long long total = (long long)N * Ho * Wo * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -87,6 +90,7 @@ __global__ void __launch_bounds__(256)
 pool_add_act_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
                         int N, int H, int W, int C, int po, int act, float slope,
                         __nv_bfloat16* __restrict__ dd, __nv_bfloat16* __restrict__ dc) {
+  pdl_wait(); pdl_launch();
   const int Ho = H / 2, Wo = W / 2, V = C / 8, Hp = Ho + 2 * po, Wp = Wo + 2 * po;
   const long long total = (long long)N * Ho * Wo * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -121,6 +125,7 @@ pool_add_act_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
 // nn.AdaptiveAvgPool2d(1): x [N,HW,C] bf16 -> out [N,C] fp32
 __global__ void __launch_bounds__(256)
 gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C, float* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   extern __shared__ float red[];
   const int V = C / 8, lanes = blockDim.x / V, n = blockIdx.x;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
@@ -144,6 +149,7 @@ gap_fwd_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C, float* __rest
 }
 __global__ void __launch_bounds__(256)
 gap_bwd_kernel(const float* __restrict__ dout, int N, int HW, int C, __nv_bfloat16* __restrict__ dx) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8;
   const long long total = (long long)N * HW * V;
   const float inv = 1.f / (float)HW;
@@ -162,6 +168,7 @@ gap_bwd_kernel(const float* __restrict__ dout, int N, int HW, int C, __nv_bfloat
 __global__ void __launch_bounds__(256)
 rgb_head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, int N,
                     int HW, int C, int Co, float* __restrict__ y) {
+  pdl_wait(); pdl_launch();
   extern __shared__ float ws[];  // [C][4]
   for (int i = threadIdx.x; i < C * 4; i += blockDim.x)
     ws[i] = (i & 3) < Co ? wgt[(i >> 2) * Co + (i & 3)] : 0.f;
@@ -191,6 +198,7 @@ __global__ void __launch_bounds__(256)
 rgb_head_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, int N,
                     int HW, int C, int Co, __nv_bfloat16* __restrict__ dx, float* __restrict__ dwp) {
+  pdl_wait(); pdl_launch();
   extern __shared__ float sm[];  // ws[C*4] | red[lanes*V*32]
   float* ws = sm;
   float* red = sm + C * 4;
@@ -302,6 +310,7 @@ template <int V, int Co>
 __global__ void __launch_bounds__(256)
 rgb_head_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, long long total,
                          int HW, float* __restrict__ y) {
+  pdl_wait(); pdl_launch();
   constexpr int C = V * 8, P = 32 / V;
   const int lane = threadIdx.x & 31, v = lane % V, q = lane / V;
   float4 wq[8];
@@ -364,6 +373,7 @@ __global__ void __launch_bounds__(256, 2)      // 2 CTAs / SM: 16 warps to cover
 rgb_head_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                          const __nv_bfloat16* __restrict__ x, const float* __restrict__ wgt, long long total,
                          int HW, __nv_bfloat16* __restrict__ dx, float* __restrict__ dwp) {
+  pdl_wait(); pdl_launch();
   constexpr int C = V * 8, P = 32 / V;
   extern __shared__ float red[];               // [256 / V][V][32]
   const int lane = threadIdx.x & 31, v = lane % V, q = lane / V;
@@ -435,6 +445,7 @@ rgb_head_bwd_warp_kernel(const float* __restrict__ dy, const float* __restrict__
 // combined in index order (fixed summation order)
 __global__ void __launch_bounds__(256)
 rgb_head_dw_reduce_kernel(const float* __restrict__ dwp, int parts, int C, int Co, float* __restrict__ dw) {
+  pdl_wait(); pdl_launch();
   __shared__ float sm[8][33];
   const int cl = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int t = blockIdx.x * 32 + cl;                      // (c, o) with o < 4
@@ -463,6 +474,7 @@ rgb_head_dw_reduce_kernel(const float* __restrict__ dwp, int parts, int C, int C
 __global__ void __launch_bounds__(256)
 sumsq_interior_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, int C, int p,
                       float* __restrict__ part) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * H * W * V;
   float s = 0.f;
@@ -489,6 +501,7 @@ sumsq_interior_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, 
 // fixed shuffle / shared-memory tree)
 __global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restrict__ part, int n,
                                                            float* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   float s = 0.f;
   for (int i = threadIdx.x; i < n; i += 256) s += part[i];
   for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -507,6 +520,7 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restri
 // one thread walking all rows was a chain of ~300 dependent L2 round trips: 36 us for a 2 us job).
 __global__ void __launch_bounds__(256) colsum_finalize_kernel(const float* __restrict__ stats, int rows, int C,
                                                               int Cv, float* __restrict__ db, int accumulate) {
+  pdl_wait(); pdl_launch();
   __shared__ float sm[8][33];
   const int cl = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + cl;
@@ -533,6 +547,7 @@ __global__ void __launch_bounds__(256) colsum_finalize_kernel(const float* __res
 __global__ void __launch_bounds__(256)
 scale_interior_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ scale, int N,
                       int H, int W, int C, int p, __nv_bfloat16* __restrict__ dx) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8, Hp = H + 2 * p, Wp = W + 2 * p;
   const long long total = (long long)N * Hp * Wp * V;
   const float sc = __ldg(scale);
@@ -557,6 +572,7 @@ scale_interior_kernel(const __nv_bfloat16* __restrict__ x, const float* __restri
 __global__ void __launch_bounds__(256)
 upsample2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, int C,
                      __nv_bfloat16* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8, Ho = 2 * H, Wo = 2 * W;
   const long long total = (long long)N * Ho * Wo * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -572,6 +588,7 @@ upsample2_fwd_kernel(const __nv_bfloat16* __restrict__ x, int N, int H, int W, i
 __global__ void __launch_bounds__(256)
 upsample2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int N, int H, int W, int C,
                      __nv_bfloat16* __restrict__ dx) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8, Wo = 2 * W;
   const long long total = (long long)N * H * W * V;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -593,6 +610,7 @@ upsample2_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int N, int H, int W, 
 __global__ void __launch_bounds__(256)
 mul_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ m, long long nvec,
            __nv_bfloat16* __restrict__ out) {
+  pdl_wait(); pdl_launch();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
        i += (long long)gridDim.x * blockDim.x) {
     const uint4 rx = ldg16(x + i * 8), rm = ldg16(m + i * 8);
@@ -613,60 +631,57 @@ using namespace mt;
 
 extern "C" int mt_upsample2_fwd(const void* x, int N, int H, int W, int C, void* out, void* stream) {
   if (C % 8) return -1003;
-  upsample2_fwd_kernel<<<grid_for((long long)N * H * W * 4 * (C / 8), 256), 256, 0, ST(stream)>>>(
+  launch_pdl(upsample2_fwd_kernel, dim3(grid_for((long long)N * H * W * 4 * (C / 8), 256)), dim3(256), 0, ST(stream), 
       CBF(x), N, H, W, C, BF(out));
   return cuda_rc();
 }
 extern "C" int mt_upsample2_bwd(const void* dy, int N, int H, int W, int C, void* dx, void* stream) {
   if (C % 8) return -1003;
-  upsample2_bwd_kernel<<<grid_for((long long)N * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
+  launch_pdl(upsample2_bwd_kernel, dim3(grid_for((long long)N * H * W * (C / 8), 256)), dim3(256), 0, ST(stream), 
       CBF(dy), N, H, W, C, BF(dx));
   return cuda_rc();
 }
 extern "C" int mt_mul(const void* x, const void* m, long long n, void* out, void* stream) {
   if (n % 8) return -1003;
-  mul_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(x), CBF(m), n / 8, BF(out));
+  launch_pdl(mul_kernel, dim3(grid_for(n / 8, 256)), dim3(256), 0, ST(stream), CBF(x), CBF(m), n / 8, BF(out));
   return cuda_rc();
 }
 extern "C" int mt_avgpool2_fwd(const void* x_pad, int pad, int N, int H, int W, int C, void* out,
                                void* stream) {
   if (C % 8) return -1003;
-  avgpool2_fwd_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256), 256, 0,
-                        ST(stream)>>>(CBF(x_pad), pad, N, H, W, C, BF(out));
+  launch_pdl(avgpool2_fwd_kernel, dim3(grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256)), dim3(256), 0, ST(stream), CBF(x_pad), pad, N, H, W, C, BF(out));
   return cuda_rc();
 }
 extern "C" int mt_avgpool2_bwd_add(const void* dpooled, void* dpad, int pad, int N, int H, int W,
                                    int C, void* stream) {
   if (C % 8) return -1003;
-  avgpool2_bwd_add_kernel<<<grid_for((long long)N * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
+  launch_pdl(avgpool2_bwd_add_kernel, dim3(grid_for((long long)N * H * W * (C / 8), 256)), dim3(256), 0, ST(stream), 
       CBF(dpooled), BF(dpad), pad, N, H, W, C);
   return cuda_rc();
 }
 extern "C" int mt_pool_add_act_fwd(const void* c, const void* d, int N, int H, int W, int C,
                                    int act, float slope, void* out_pad, int out_p, void* stream) {
   if (C % 8) return -1003;
-  pool_add_act_fwd_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256), 256, 0,
-                            ST(stream)>>>(CBF(c), CBF(d), N, H, W, C, act, slope, BF(out_pad), out_p);
+  launch_pdl(pool_add_act_fwd_kernel, dim3(grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256)), dim3(256), 0, ST(stream), CBF(c), CBF(d), N, H, W, C, act, slope, BF(out_pad), out_p);
   return cuda_rc();
 }
 extern "C" int mt_pool_add_act_bwd(const void* dout_pad, const void* out_pad, int N, int H, int W,
                                    int C, int out_p, int act, float slope, void* dd, void* dc,
                                    void* stream) {
   if (C % 8) return -1003;
-  pool_add_act_bwd_kernel<<<grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256), 256, 0,
-                            ST(stream)>>>(CBF(dout_pad), CBF(out_pad), N, H, W, C, out_p, act, slope,
+  launch_pdl(pool_add_act_bwd_kernel, dim3(grid_for((long long)N * (H / 2) * (W / 2) * (C / 8), 256)), dim3(256), 0, ST(stream), CBF(dout_pad), CBF(out_pad), N, H, W, C, out_p, act, slope,
                                           BF(dd), BF(dc));
   return cuda_rc();
 }
 extern "C" int mt_gap_fwd(const void* x, int N, int HW, int C, float* out, void* stream) {
   if (C % 8 || C / 8 > 256) return -1003;
   const int lanes = 256 / (C / 8);
-  gap_fwd_kernel<<<N, 256, (size_t)lanes * C * sizeof(float), ST(stream)>>>(CBF(x), HW, C, out);
+  launch_pdl(gap_fwd_kernel, dim3(N), dim3(256), (size_t)lanes * C * sizeof(float), ST(stream), CBF(x), HW, C, out);
   return cuda_rc();
 }
 extern "C" int mt_gap_bwd(const float* dout, int N, int HW, int C, void* dx, void* stream) {
   if (C % 8) return -1003;
-  gap_bwd_kernel<<<grid_for((long long)N * HW * (C / 8), 256), 256, 0, ST(stream)>>>(dout, N, HW, C,
+  launch_pdl(gap_bwd_kernel, dim3(grid_for((long long)N * HW * (C / 8), 256)), dim3(256), 0, ST(stream), dout, N, HW, C,
                                                                                      BF(dx));
   return cuda_rc();
 }
@@ -675,7 +690,7 @@ extern "C" int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int
   if (C % 8 || Co > 4 || Co < 1) return -1003;
   const long long total = (long long)N * HW;
   const int wgrid = grid_for((total + 255) / 256, 1, 16);     // 8 warps x 32 pixels per block and pass
-#define MT_RGB_F(V_, CO_) rgb_head_fwd_warp_kernel<V_, CO_><<<wgrid, 256, 0, ST(stream)>>>(CBF(x), w, total, HW, y); return cuda_rc()
+#define MT_RGB_F(V_, CO_) launch_pdl(rgb_head_fwd_warp_kernel<V_, CO_>, dim3(wgrid), dim3(256), 0, ST(stream), CBF(x), w, total, HW, y); return cuda_rc()
   switch ((C / 8) * 10 + Co) {
     case 43: MT_RGB_F(4, 3);   case 83: MT_RGB_F(8, 3);   case 163: MT_RGB_F(16, 3);
     case 41: MT_RGB_F(4, 1);   case 81: MT_RGB_F(8, 1);   case 161: MT_RGB_F(16, 1);
@@ -685,8 +700,7 @@ extern "C" int mt_rgb_head_fwd(const void* x, const float* w, int N, int HW, int
     default: break;
   }
 #undef MT_RGB_F
-  rgb_head_fwd_kernel<<<grid_for((long long)N * HW, 256), 256, (size_t)C * 4 * sizeof(float),
-                        ST(stream)>>>(CBF(x), w, N, HW, C, Co, y);
+  launch_pdl(rgb_head_fwd_kernel, dim3(grid_for((long long)N * HW, 256)), dim3(256), (size_t)C * 4 * sizeof(float), ST(stream), CBF(x), w, N, HW, C, Co, y);
   return cuda_rc();
 }
 extern "C" int mt_rgb_head_bwd_parts(int N, int HW, int C) {
@@ -704,7 +718,7 @@ extern "C" int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, c
   if (parts != grid || !dw_parts) return -1012;
   const long long total = (long long)N * HW;
   const size_t wsmem = (size_t)256 * 32 * sizeof(float);
-#define MT_RGB_B(V_, CO_) rgb_head_bwd_warp_kernel<V_, CO_><<<grid, 256, wsmem, ST(stream)>>>(dy, y, CBF(x), w, total, HW, BF(dx), dw_parts); break
+#define MT_RGB_B(V_, CO_) launch_pdl(rgb_head_bwd_warp_kernel<V_, CO_>, dim3(grid), dim3(256), wsmem, ST(stream), dy, y, CBF(x), w, total, HW, BF(dx), dw_parts); break
   switch (V * 10 + Co) {
     case 43: MT_RGB_B(4, 3);   case 83: MT_RGB_B(8, 3);   case 163: MT_RGB_B(16, 3);
     case 41: MT_RGB_B(4, 1);   case 81: MT_RGB_B(8, 1);   case 161: MT_RGB_B(16, 1);
@@ -712,10 +726,10 @@ extern "C" int mt_rgb_head_bwd(const float* dy, const float* y, const void* x, c
     case 84: MT_RGB_B(8, 4);
     case 164: MT_RGB_B(16, 4);
     default:
-      rgb_head_bwd_kernel<<<grid, 256, smem, ST(stream)>>>(dy, y, CBF(x), w, N, HW, C, Co, BF(dx), dw_parts);
+      launch_pdl(rgb_head_bwd_kernel, dim3(grid), dim3(256), smem, ST(stream), dy, y, CBF(x), w, N, HW, C, Co, BF(dx), dw_parts);
   }
 #undef MT_RGB_B
-  rgb_head_dw_reduce_kernel<<<(C * 4 + 31) / 32, 256, 0, ST(stream)>>>(dw_parts, parts, C, Co, dw);
+  launch_pdl(rgb_head_dw_reduce_kernel, dim3((C * 4 + 31) / 32), dim3(256), 0, ST(stream), dw_parts, parts, C, Co, dw);
   return cuda_rc();
 }
 extern "C" int mt_sumsq_interior_parts(int N, int H, int W, int C) {
@@ -725,20 +739,19 @@ extern "C" int mt_sumsq_interior(const void* x_pad, int N, int H, int W, int C, 
                                  float* partials, int parts, void* stream) {
   if (C % 8) return -1003;
   if (parts != mt_sumsq_interior_parts(N, H, W, C) || !partials) return -1012;
-  sumsq_interior_kernel<<<parts, 256, 0, ST(stream)>>>(CBF(x_pad), N, H, W, C, pad, partials);
-  sum_partials_kernel<<<1, 256, 0, ST(stream)>>>(partials, parts, out);
+  launch_pdl(sumsq_interior_kernel, dim3(parts), dim3(256), 0, ST(stream), CBF(x_pad), N, H, W, C, pad, partials);
+  launch_pdl(sum_partials_kernel, dim3(1), dim3(256), 0, ST(stream), partials, parts, out);
   return cuda_rc();
 }
 extern "C" int mt_colsum_into(const float* stats, int rows, int C, int C_valid, float* db, int accumulate,
                               void* stream) {
   if (rows < 1 || C_valid < 1 || C_valid > C) return -1005;
-  colsum_finalize_kernel<<<(C_valid + 31) / 32, 256, 0, ST(stream)>>>(stats, rows, C, C_valid, db, accumulate);
+  launch_pdl(colsum_finalize_kernel, dim3((C_valid + 31) / 32), dim3(256), 0, ST(stream), stats, rows, C, C_valid, db, accumulate);
   return cuda_rc();
 }
 extern "C" int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C,
                                  int pad, void* dx_pad, void* stream) {
   if (C % 8) return -1003;
-  scale_interior_kernel<<<grid_for((long long)N * (H + 2 * pad) * (W + 2 * pad) * (C / 8), 256), 256,
-                          0, ST(stream)>>>(CBF(x_pad), scale, N, H, W, C, pad, BF(dx_pad));
+  launch_pdl(scale_interior_kernel, dim3(grid_for((long long)N * (H + 2 * pad) * (W + 2 * pad) * (C / 8), 256)), dim3(256), 0, ST(stream), CBF(x_pad), scale, N, H, W, C, pad, BF(dx_pad));
   return cuda_rc();
 }

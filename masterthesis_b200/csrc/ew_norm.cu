@@ -50,6 +50,7 @@ plane_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
                     const float* __restrict__ ss, int H, int W, FastDiv divW, int C, int gp, int chunks,
                     float slope, float* __restrict__ out) {
   extern __shared__ float red[];  // [lanes][V*16]
+  pdl_wait(); pdl_launch();
   const int V = C / 8, HW = H * W;
   const int lanes = blockDim.x / V;
   const int n = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
@@ -199,6 +200,7 @@ norm_finalize_kernel(const float* __restrict__ stats, int parts, int mode, int N
                      float* __restrict__ csum) {
   extern __shared__ float tot_c[];   // [channels of this block][2]
   __shared__ float2 part_sm[1024];
+  pdl_wait(); pdl_launch();
   const int n = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
   const int cb = gridDim.y > 1 ? blockIdx.y * FIN_CSPLIT : 0;           // first channel of the block
   const int Cb = gridDim.y > 1 ? min(FIN_CSPLIT, C - cb) : C;           // channels of the block
@@ -261,6 +263,7 @@ __global__ void __launch_bounds__(256, 2)
 affine_act_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ss, int H, int W,
                       FastDiv divW, int C, float slope, const __nv_bfloat16* __restrict__ res, int pr,
                       const float* __restrict__ noise, __nv_bfloat16* __restrict__ out, int po) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8, lanes = blockDim.x / V;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   if (pl >= lanes) return;
@@ -347,6 +350,7 @@ norm_bwd_finalize_kernel(const float* __restrict__ sums, int parts, const float*
   __shared__ float2 part_sm[1024];
   __shared__ float tot[2];
   __shared__ float r0[32], r1[32];
+  pdl_wait(); pdl_launch();
   const int n = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
   const int cb = gridDim.y > 1 ? blockIdx.y * FIN_CSPLIT : 0;
   const int Cb = gridDim.y > 1 ? min(FIN_CSPLIT, C - cb) : C;
@@ -415,6 +419,7 @@ __global__ void norm_bwd_params_kernel(const float* __restrict__ red, const floa
                                        const float* __restrict__ csum, int N, int C, int Cv, int HW,
                                        float* __restrict__ dln_w, float* __restrict__ dln_b,
                                        float* __restrict__ dbias, int accumulate) {
+  pdl_wait(); pdl_launch();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= Cv) return;
   float sw = 0.f, sb = 0.f, sd = 0.f;
@@ -435,6 +440,7 @@ __global__ void __launch_bounds__(256, 2)
 norm_bwd_apply_kernel(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
                       const float* __restrict__ ss, const float* __restrict__ coef, int H, int W,
                       FastDiv divW, int C, int gp, float slope, __nv_bfloat16* __restrict__ dx) {
+  pdl_wait(); pdl_launch();
   const int V = C / 8, lanes = blockDim.x / V, HW = H * W;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   if (pl >= lanes) return;
@@ -505,6 +511,7 @@ act_bwd_fold_kernel(const __nv_bfloat16* __restrict__ dpad, const __nv_bfloat16*
                     int H, int W, FastDiv divW, int C, int p, float slope,
                     __nv_bfloat16* __restrict__ dy) {
   // per-plane layout as norm_bwd_apply_kernel: grid (pixel chunks, N), thread = channel vector x lane
+  pdl_wait(); pdl_launch();
   const int V = C / 8, lanes = blockDim.x / V, HW = H * W;
   const int v = threadIdx.x % V, pl = threadIdx.x / V;
   if (pl >= lanes) return;
@@ -599,8 +606,8 @@ static int reduce_launch(bool bwd, const void* x, const void* g, const float* ss
     const int chunks = plane_chunks(N, HW, C, resident_ctas(plane_reduce_kernel<B, A, G>, smem)); \
     if (parts == 0) return chunks;                                                                \
     if (parts != chunks) return -1012;                                                            \
-    plane_reduce_kernel<B, A, G><<<N * chunks, 256, smem, st>>>(                                  \
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out); \
+    launch_pdl(plane_reduce_kernel<B, A, G>, dim3(N * chunks), dim3(256), smem, st,              \
+               (const __nv_bfloat16*)x, (const __nv_bfloat16*)g, ss, H, W, dw, C, gp, chunks, slope, out); \
   } while (0)
 #define MT_RED_G(A) do { if (gp) MT_RED(true, A, true); else MT_RED(true, A, false); } while (0)
   if (!bwd) MT_RED(false, 0, false);
@@ -629,7 +636,7 @@ extern "C" int mt_norm_finalize(const float* stats, int parts, int mode, int N, 
   if (C_valid <= 0 || C_valid > C || parts < 1) return -1005;
   const int threads = parts > 1 ? 1024 : 256;
   const int splits = (parts > 1 && mode != MT_NORM_LAYER && C > FIN_CSPLIT) ? (C + FIN_CSPLIT - 1) / FIN_CSPLIT : 1;
-  norm_finalize_kernel<<<dim3(N, splits), threads, (size_t)C * 2 * sizeof(float), ST(stream)>>>(stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr, csum);
+  launch_pdl(norm_finalize_kernel, dim3(N, splits), dim3(threads), (size_t)C * 2 * sizeof(float), ST(stream), stats, parts, mode, N, C, C_valid, HW, eps, gb, ln_w, ln_b, ss, mr, csum);
   return cuda_rc();
 }
 extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, int W, int C,
@@ -639,10 +646,10 @@ extern "C" int mt_affine_act_fwd(const void* x, const float* ss, int N, int H, i
   if (!image_fits(H, W, C, res_p > out_p ? res_p : out_p)) return -1005;
   const FastDiv dw = make_fastdiv(W);
 #define MT_AFF3(A, R, Z)                                                                          \
-  affine_act_fwd_kernel<A, R, Z><<<plane_grid(N, H * W, C, resident_ctas(affine_act_fwd_kernel<A, R, Z>, 0)), \
-                                   256, 0, ST(stream)>>>(                                         \
-      (const __nv_bfloat16*)x, ss, H, W, dw, C, slope, (const __nv_bfloat16*)res_pad, res_p, noise, \
-      (__nv_bfloat16*)out_pad, out_p)
+  launch_pdl(affine_act_fwd_kernel<A, R, Z>, plane_grid(N, H * W, C, resident_ctas(affine_act_fwd_kernel<A, R, Z>, 0)), \
+             dim3(256), 0, ST(stream),                                                            \
+             (const __nv_bfloat16*)x, ss, H, W, dw, C, slope, (const __nv_bfloat16*)res_pad, res_p, noise, \
+             (__nv_bfloat16*)out_pad, out_p)
 #define MT_AFF(A)                                                                                 \
   do {                                                                                            \
     if (res_pad && noise) MT_AFF3(A, true, true);                                                 \
@@ -676,8 +683,8 @@ extern "C" int mt_norm_bwd_finalize(const float* sums, int parts, const float* m
   if (C_valid <= 0 || C_valid > C || parts < 1) return -1005;
   const int threads = parts > 1 ? 1024 : 256;
   const int splits = (parts > 1 && mode != MT_NORM_LAYER && C > FIN_CSPLIT) ? (C + FIN_CSPLIT - 1) / FIN_CSPLIT : 1;
-  norm_bwd_finalize_kernel<<<dim3(N, splits), threads, (size_t)C * 2 * sizeof(float), ST(stream)>>>(
-      sums, parts, mr, mode, N, C, C_valid, HW, gb, ln_w, coef, dgb, red);
+  launch_pdl(norm_bwd_finalize_kernel, dim3(N, splits), dim3(threads), (size_t)C * 2 * sizeof(float), ST(stream),
+             sums, parts, mr, mode, N, C, C_valid, HW, gb, ln_w, coef, dgb, red);
   return cuda_rc();
 }
 extern "C" int mt_norm_bwd_params(const float* red, const float* coef, const float* csum, int N, int C,
@@ -687,8 +694,8 @@ extern "C" int mt_norm_bwd_params(const float* red, const float* coef, const flo
   if ((dln_w == nullptr) != (dln_b == nullptr)) return -1008;
   if (dbias && (!coef || !csum)) return -1008;
   if (!dln_w && !dbias) return 0;
-  norm_bwd_params_kernel<<<(C_valid + 127) / 128, 128, 0, ST(stream)>>>(red, coef, csum, N, C, C_valid, HW,
-                                                                        dln_w, dln_b, dbias, accumulate);
+  launch_pdl(norm_bwd_params_kernel, dim3((C_valid + 127) / 128), dim3(128), 0, ST(stream), red, coef, csum, N, C,
+             C_valid, HW, dln_w, dln_b, dbias, accumulate);
   return cuda_rc();
 }
 extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss,
@@ -698,9 +705,9 @@ extern "C" int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const 
   if (!image_fits(H, W, C, g_pad)) return -1005;
   const FastDiv dw = make_fastdiv(W);
 #define MT_APP2(A, G)                                                                             \
-  norm_bwd_apply_kernel<A, G><<<plane_grid(N, H * W, C, resident_ctas(norm_bwd_apply_kernel<A, G>, 0)), 256, 0, \
-                                ST(stream)>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, H, \
-                                              W, dw, C, g_pad, slope, (__nv_bfloat16*)dx)
+  launch_pdl(norm_bwd_apply_kernel<A, G>, plane_grid(N, H * W, C, resident_ctas(norm_bwd_apply_kernel<A, G>, 0)), \
+             dim3(256), 0, ST(stream), (const __nv_bfloat16*)g, (const __nv_bfloat16*)x, ss, coef, H, \
+             W, dw, C, g_pad, slope, (__nv_bfloat16*)dx)
 #define MT_APP(A) do { if (g_pad) MT_APP2(A, true); else MT_APP2(A, false); } while (0)
   if (act == MT_ACT_RELU) MT_APP(1);
   else if (act == MT_ACT_LRELU) MT_APP(2);
@@ -715,9 +722,9 @@ extern "C" int mt_act_bwd_fold(const void* dpad, const void* out_pad, int N, int
   if (!image_fits(H, W, C, pad)) return -1005;
   const FastDiv dw = make_fastdiv(W);
 #define MT_ABF(A)                                                                                 \
-  act_bwd_fold_kernel<A><<<plane_grid(N, H * W, C, resident_ctas(act_bwd_fold_kernel<A>, 0)), 256, 0, \
-                           ST(stream)>>>((const __nv_bfloat16*)dpad, (const __nv_bfloat16*)out_pad, H, W, \
-                                         dw, C, pad, slope, (__nv_bfloat16*)dy)
+  launch_pdl(act_bwd_fold_kernel<A>, plane_grid(N, H * W, C, resident_ctas(act_bwd_fold_kernel<A>, 0)), dim3(256), 0, \
+             ST(stream), (const __nv_bfloat16*)dpad, (const __nv_bfloat16*)out_pad, H, W, \
+             dw, C, pad, slope, (__nv_bfloat16*)dy)
   if (act == MT_ACT_RELU) MT_ABF(1);
   else if (act == MT_ACT_LRELU) MT_ABF(2);
   else MT_ABF(0);

@@ -10,6 +10,7 @@ __global__ void __launch_bounds__(256)
 adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                  float* __restrict__ v, long long n, float lr_over_bc1, float inv_sqrt_bc2, float b1,
                  float b2, float eps, float wd, float gscale) {
+  pdl_wait(); pdl_launch();
   const long long n4 = n / 4;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -46,6 +47,7 @@ adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
 __global__ void __launch_bounds__(256)
 adam_flat_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                      float* __restrict__ v, long long n, const float* __restrict__ hyper) {
+  pdl_wait(); pdl_launch();
   const float lr_over_bc1 = __ldg(hyper + 0), inv_sqrt_bc2 = __ldg(hyper + 1), b1 = __ldg(hyper + 2),
               b2 = __ldg(hyper + 3), eps = __ldg(hyper + 4), wd = __ldg(hyper + 5),
               gscale = __ldg(hyper + 6);
@@ -86,7 +88,7 @@ extern "C" int mt_adam_flat_dev(float* p, const float* g, float* m, float* v, lo
                                 const float* hyper, void* stream) {
   if (n < 0 || !hyper) return -1005;
   if (n == 0) return 0;
-  mt::adam_flat_dev_kernel<<<mt::grid_for(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
+  mt::launch_pdl(mt::adam_flat_dev_kernel, dim3(mt::grid_for(n / 4 + 1, 256)), dim3(256), 0, (cudaStream_t)stream, 
       p, g, m, v, n, hyper);
   return mt::cuda_rc();
 }
@@ -98,7 +100,7 @@ extern "C" int mt_adam_flat(float* p, const float* g, float* m, float* v, long l
   if (n == 0) return 0;
   const double bc1 = 1.0 - pow((double)beta1, step);
   const double bc2 = 1.0 - pow((double)beta2, step);
-  mt::adam_flat_kernel<<<mt::grid_for(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(
+  mt::launch_pdl(mt::adam_flat_kernel, dim3(mt::grid_for(n / 4 + 1, 256)), dim3(256), 0, (cudaStream_t)stream, 
       p, g, m, v, n, (float)(lr / bc1), (float)(1.0 / sqrt(bc2)), beta1, beta2, eps, wd, gscale);
   return mt::cuda_rc();
 }

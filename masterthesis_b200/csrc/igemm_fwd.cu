@@ -240,6 +240,10 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (CG == 2) cluster_sync_all();     // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  // everything above (barriers, TMEM, tensor-map prefetch, cluster sync) touched no global data: under a
+  // programmatic dependent launch it overlapped the previous kernel's tail; from here on its results are needed
+  griddep_wait();
+  griddep_launch();
   if (stamp && warp == 0) g_ts[7] = clock64() - T0;
 
   if (warp == 0) {
@@ -429,10 +433,14 @@ static cudaError_t launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, co
   cfg.blockDim = dim3(NUM_THREADS, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  static int pdl = -1;
+  if (pdl < 0) { const char* e = getenv("MT_PDL"); pdl = e ? (atoi(e) != 0) : 1; }
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
   return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
 }
 

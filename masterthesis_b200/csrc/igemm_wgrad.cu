@@ -9,6 +9,8 @@
 // weight gradients are reproducible bit for bit.
 // Replaces autograd's Conv2d/ConvTranspose2d weight gradients (reference: the .backward() calls
 // of src/models/adain_model.py:219,316,391).
+#include <stdlib.h>
+#include <string.h>
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -135,6 +137,8 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
+  griddep_wait();        // programmatic dependent launch: the set-up above overlapped the previous kernel's tail
+  griddep_launch();
 
   WgCtx c;
   c.bar_full = smem_u32(&bar_full[0]); c.bar_empty = smem_u32(&bar_empty[0]);
@@ -196,8 +200,17 @@ static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& t
     attr_set = true;
   }
   const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;
-  kern<<<(unsigned)grid, 192, kSmem, stream>>>(tmP, tmQ, p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)grid, 1, 1); cfg.blockDim = dim3(192, 1, 1);
+  cfg.dynamicSmemBytes = kSmem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  static int pdl = -1;
+  if (pdl < 0) { const char* e = getenv("MT_PDL"); pdl = e ? (atoi(e) != 0) : 1; }
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, tmP, tmQ, p);
 }
 
 int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradParams& p,
