@@ -80,6 +80,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.t0 = None          # start of the timed region (rows before it are warm-up samples)
 
     def start(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -94,18 +95,33 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def mark(self):
+        """the timed region starts now (the sampler itself is started before the warm-up: nvidia-smi needs a
+        few hundred ms to deliver its first row, longer than a short timed region)"""
+        self.t0 = time.perf_counter()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
+        timed = [r for t, r in self.rows if self.t0 is None or t >= self.t0]
+        # a timed region shorter than the sampling period: fall back to the last rows under load (warm-up
+        # iterations of the same workload immediately before it)
+        note = None
+        if len(timed) < 2:
+            timed, note = [r for _, r in self.rows[-5:]], "timed region shorter than the sampling period: last warm-up samples"
+        self.rows = timed
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        out = {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+               "reasons": reasons, "samples": len(sm)}
+        if note:
+            out["note"] = note
+        return out
 
 
 # ------------------------------------------------------------------------------- CPU / GPU baselines
@@ -369,12 +385,13 @@ def run_ours(a):
         torch.cuda.synchronize()
 
     # ---- device-resident throughput
+    clocks = ClockSampler(dev_index)
+    clocks.start()
     model.set_inputs(resident)
     for _ in range(a.warmup):
         model.optimize_parameters(0)
     sync()
-    clocks = ClockSampler(dev_index)
-    clocks.start()
+    clocks.mark()
     l0 = ops.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
