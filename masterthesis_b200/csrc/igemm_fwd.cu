@@ -349,8 +349,10 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int sl = NSLAB == 1 ? 0 : grp; sl < NSLAB; sl += 2) {
         const int c_glob = wc.n_tile * BN + sl * SW;
         if (c_glob >= p.n_store) break;                       // team-uniform
+        if (stamp && warp == 2 && tile_i == 2) g_ts[40] = clock64() - T0;
         if (tt == 0) bulk_wait_read0();                       // previous store has left the box
         named_bar_sync(1 + grp, 128);
+        if (stamp && warp == 2 && tile_i == 2) g_ts[41] = clock64() - T0;
 #define MT_EPI(A, B) epilogue_slab<A, B, SW>(p, tmem_row + sl * SW, stage_row, m & 7, row_ok, c_glob)
         switch (p.act) {
           case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
@@ -359,24 +361,30 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           default:        if (hb) MT_EPI(ACT_NONE, true);  else MT_EPI(ACT_NONE, false);  break;
         }
 #undef MT_EPI
+        if (stamp && warp == 2 && tile_i == 2) g_ts[42] = clock64() - T0;
         if (sl + 2 >= NSLAB || c_glob + 2 * SW >= p.n_store) {
           // last TMEM read of this warp for the tile: hand the accumulator back right away
           tc_fence_before();
           __syncwarp();
           if (lane == 0) {
-            if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
-            else mbar_arrive(smem_u32(&bar_tempty[acc]));
+            if (CG == 2) {
+              if (p.dbg & 64) mbar_arrive_cluster_gpu_fence(smem_u32(&bar_tempty[acc]), 0);
+              else mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
+            } else mbar_arrive(smem_u32(&bar_tempty[acc]));
           }
           released = true;
         }
         fence_proxy_async();
         named_bar_sync(1 + grp, 128);
+        if (stamp && warp == 2 && tile_i == 2) g_ts[43] = clock64() - T0;
         if (tt == 0) {
           if (p.accumulate) tma_reduce_add_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
           else tma_store_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
           bulk_commit();
         }
+        if (stamp && warp == 2 && tile_i == 2) g_ts[44] = clock64() - T0;
         if (SW == 64 && p.stats != nullptr && wc.n0 < p.Nt) slab_stats(p, stage_buf, tt, c_glob, wc.n0, wc.part);
+        if (stamp && warp == 2 && tile_i == 2) g_ts[45] = clock64() - T0;
       }
       if (!released) {                 // a team without slabs in this tile
         tc_fence_before();

@@ -203,8 +203,20 @@ __device__ __forceinline__ void cluster_sync_all() {
 }
 // shared::cta address of this CTA -> the same offset in the pair's leader (even) CTA
 static constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;
-// arrive on the mbarrier at the same offset in CTA `rank` of the cluster
+// arrive on the mbarrier at the same offset in CTA `rank` of the cluster.  Default semantics (.release at
+// CTA scope): the `.release.cluster` form compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive, which
+// cost ~1 900 cycles per tile in the epilogue of every CTA-pair kernel (tools/conv_timeline.py).  What this
+// signal orders are the tcgen05.ld reads of the accumulator, which tcgen05.wait::ld +
+// tcgen05.fence::before_thread_sync in the caller already order before the arrive.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar), "r"(rank)
+      : "memory");
+}
+// the heavy form, kept for A/B measurements (MT_IGEMM_DBG & 64)
+__device__ __forceinline__ void mbar_arrive_cluster_gpu_fence(uint32_t bar, uint32_t rank) {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"

@@ -41,4 +41,5 @@ print(f"shape={os.environ.get('MT_SHAPE')} dbg={os.environ.get('MT_IGEMM_DBG')} 
 print("setup", t[7], "| producer done", t[6], "| kernel end", t[0])
 for i in range(8):
     print(f"tile {i}: mma {t[8+2*i]:7d} .. {t[9+2*i]:7d} ({t[9+2*i]-t[8+2*i]:6d})   epilogue {t[24+2*i]:7d} .. {t[25+2*i]:7d} ({t[25+2*i]-t[24+2*i]:6d})")
+print("epilogue of tile 2, warp 2 (last slab): enter", t[40], "| box free", t[41], "| slab in smem", t[42], "| barrier", t[43], "| store issued", t[44], "| stats", t[45])
 print("ring offset flag (negative = mismatch):", t[63])
