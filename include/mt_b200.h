@@ -303,6 +303,18 @@ int mt_loss_bce_logits(const float* x, const float* target, float target_const, 
 int mt_loss_l1_parts(long long n);
 int mt_loss_l1(const float* a, const float* b, long long n, float weight, float gscale, float* loss,
                float* da, float* partials, int parts, void* stream);
+/* mt_loss_l1 for callers that cannot allocate (code under CUDA graph capture, serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arithmetic, same kernels and the same result as mt_loss_l1, but the per-block partial sums live in a
+ * file-scope `static __device__` array of 512 floats (2 KiB, held by every GPU that loads the library until
+ * exit) instead of a caller buffer; the entry point calls no cudaMalloc / cudaFree / allocating routine.
+ * Limit: n <= mt_loss_l1_static_max_n() = 2^30 elements (error -1016 beyond it).  The array is shared by
+ * every call on the device and keeps the last call's contents (nothing needs zeroing: every slot read was
+ * written by the same call); two calls that OVERLAP on the GPU (streams with no ordering between them) race —
+ * order them, or use mt_loss_l1 with separate scratch buffers. */
+long long mt_loss_l1_static_max_n(void);
+int mt_loss_l1_static(const float* a, const float* b, long long n, float weight, float gscale, float* loss,
+                      float* da, void* stream);
 /* -0.5 * sum(1 + logvar - mu^2 - exp(logvar)) over n elements (adain_model.py:313-314);
  * dmu = gscale * mu, dlogvar = gscale * 0.5 * (exp(logvar) - 1) (both or neither) */
 int mt_loss_kl_normal(const float* mu, const float* logvar, int n, float gscale, float* loss,

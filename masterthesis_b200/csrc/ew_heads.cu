@@ -9,6 +9,8 @@
 //   * the loss layer with its gradients in the same pass: BCE-with-logits (loss.py:52-64,
 //     adain_model.py:213-216), L1 (adain_model.py:303-306), the reparameterisation KL (adain_model.py:313-314).
 // Everything is fixed-order (no atomics): results are reproducible bit for bit.
+#include <map>
+#include <mutex>
 #include "../../include/mt_b200.h"
 #include "ew_common.cuh"
 
@@ -467,6 +469,53 @@ extern "C" int mt_loss_l1(const float* a, const float* b, long long n, float wei
   if ((((uintptr_t)a | (uintptr_t)b | (uintptr_t)da) & 15) != 0) return -1005;
   launch_pdl(l1_partial_kernel, dim3(parts), dim3(256), 0, ST(stream), a, b, n, gscale, partials, da);
   launch_pdl(scaled_sum_kernel, dim3(1), dim3(256), 0, ST(stream), partials, parts, weight / (float)n, loss);
+  return cuda_rc();
+}
+// ---- mt_loss_l1 without caller scratch: the per-block partial sums live in a file-scope device array.
+// No counterpart in the reference; added for callers that cannot
+// allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the
+// library holds the MT_LOSS_L1_STATIC_MAX_PARTS * 4 = 2 KiB array until exit.  In host code the array's name is
+// only a stand-in: the device address comes from cudaGetSymbolAddress, once per device, with that device
+// current.  Every slot that the sum kernel reads was written by the partial kernel of the same call, so
+// nothing has to start at zero; all calls on one device share the array, so two calls that overlap on the GPU
+// (different streams without an ordering between them) race.
+#define MT_LOSS_L1_STATIC_MAX_PARTS 512
+#define MT_LOSS_L1_STATIC_MAX_N (1ll << 30)
+static __device__ __align__(256) float g_l1_static_parts[MT_LOSS_L1_STATIC_MAX_PARTS];
+
+static int l1_static_scratch(float** out) {
+  static std::mutex mu;
+  static std::map<int, float*> by_device;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return -(int)e;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = by_device.find(dev);
+  if (it == by_device.end()) {
+    float* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_l1_static_parts);     // `dev` is the current device
+    if (e != cudaSuccess) return -(int)e;
+    if (!ptr) return -1016;
+    it = by_device.emplace(dev, ptr).first;
+  }
+  *out = it->second;
+  return 0;
+}
+
+extern "C" long long mt_loss_l1_static_max_n(void) { return MT_LOSS_L1_STATIC_MAX_N; }
+extern "C" int mt_loss_l1_static(const float* a, const float* b, long long n, float weight, float gscale,
+                                 float* loss, float* da, void* stream) {
+  if (n < 1 || !loss || !a || !b) return -1005;
+  if (n > MT_LOSS_L1_STATIC_MAX_N) return -1016;
+  const int parts = mt_loss_l1_parts(n);
+  if (parts < 1 || parts > MT_LOSS_L1_STATIC_MAX_PARTS) return -1016;
+  if ((((uintptr_t)a | (uintptr_t)b | (uintptr_t)da) & 15) != 0) return -1005;
+  float* partials = nullptr;
+  const int rc = l1_static_scratch(&partials);
+  if (rc) return rc;
+  launch_pdl(l1_partial_kernel, dim3(parts), dim3(256), 0, ST(stream), a, b, n, gscale, partials, da);
+  launch_pdl(scaled_sum_kernel, dim3(1), dim3(256), 0, ST(stream), (const float*)partials, parts,
+             weight / (float)n, loss);
   return cuda_rc();
 }
 extern "C" int mt_loss_kl_normal(const float* mu, const float* logvar, int n, float gscale, float* loss,

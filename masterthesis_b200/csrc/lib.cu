@@ -21,6 +21,7 @@ extern "C" const char* mt_error_string(int code) {
     case -1013: return "stream fork/join of the sub-pixel phases failed";
     case -1014: return "merged-parity / paired-pixel conv modes need even extents: set MtConv2d.single = 1 for odd sizes (and pack the plain operand layouts)";
     case -1015: return "weight gradient: `splits` does not match mt_conv2d_wgrad_splits() / mt_conv_transpose2d_wgrad_splits()";
+    case -1016: return "mt_loss_l1_static: n exceeds mt_loss_l1_static_max_n() (the built-in scratch array), or the array's device address is unavailable";
     case -1012: return "`parts` does not match the *_parts() query of this entry point for this shape";
     case -1011: return "implicit-GEMM shared-memory ring is not at the expected offset";
     case -1009: return "row-window mode requested for an ineligible convolution";
