@@ -39,7 +39,12 @@ static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   if (splits < 1) splits = 1;
   const int per = cdiv(total_kt, splits);
   p.splits = cdiv(total_kt, per);
-  const int stage_bytes = (2 + p.BN / 64) * 8192;
+  // CTA pairs (one M = 256 MMA for two M tiles, half of the Q slab staged per CTA) wherever there are two
+  // M tiles to pair and the Q slab is wide enough to be worth halving; MT_WGRAD_CG=1 keeps single CTAs
+  static int force_cg = -1;
+  if (force_cg < 0) { const char* e = getenv("MT_WGRAD_CG"); force_cg = e ? atoi(e) : 0; }
+  p.cg = (p.m_tiles % 2 == 0 && p.BN >= 128 && force_cg != 1) ? 2 : 1;
+  const int stage_bytes = (2 + p.BN / p.cg / 64) * 8192;
   p.stages = (200 * 1024) / stage_bytes;
   if (p.stages > 8) p.stages = 8;
   p.tmem_cols = pow2_cols(p.BN);

@@ -50,6 +50,7 @@ struct WgradParams {
   int mul_h, mul_w, off_h, off_w, step_h, step_w;  // X coord = pix*mul + off + tap*step
   int m_tiles, n_tiles;           // Cout tiles of 128, Cin tiles of BN
   int BN;
+  int cg;                         // 1: one CTA per (tap, M tile, N tile, split); 2: CTA pair over two M tiles
   int splits;                     // split-K factor over pixel tiles
   int stages;
   int tmem_cols;

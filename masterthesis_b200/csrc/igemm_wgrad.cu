@@ -29,13 +29,14 @@ __device__ __forceinline__ void st_v4(float* addr, float a, float b, float c, fl
 // with it every shared-memory descriptor is a constant (MMA issue-rate rule, see igemm_fwd.cu).
 struct WgCtx {
   uint32_t bar_full, bar_empty, smem_base, tmem_base, phase_bits;
-  int iters, kt_begin, m_tile, n_tile, r, s;
+  int iters, kt_begin, m_tile, n_tile, r, s, rank;
 };
 
-template <int BN, int S, int STAGE>
+template <int CG, int BN, int S, int STAGE>
 __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const CUtensorMap* tmQ,
                                                  const WgradParams& p, WgCtx& c, int kb) {
-  constexpr uint32_t STAGE_BYTES = (2 + BN / 64) * WG_CHUNK;
+  constexpr int B_CHUNKS = BN / CG / 64;                      // 64-channel slabs of Q staged by this CTA
+  constexpr uint32_t STAGE_BYTES = (2 + B_CHUNKS) * WG_CHUNK;
   if constexpr (STAGE < S) {
     if (kb + STAGE < c.iters) {
       int kt = c.kt_begin + kb + STAGE;
@@ -45,28 +46,40 @@ __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const C
       const int w0 = tw * p.TW, h0 = th * p.TH, n0 = tn * p.TN;
       mbar_wait(c.bar_empty + 8 * STAGE, ((c.phase_bits >> STAGE) & 1) ^ 1);
       c.phase_bits ^= 1u << STAGE;
-      const uint32_t full = c.bar_full + 8 * STAGE;
       const uint32_t a_dst = c.smem_base + STAGE * STAGE_BYTES;
       const uint32_t b_dst = a_dst + 2 * WG_CHUNK;
-      mbar_expect_tx(full, STAGE_BYTES);
-      tma_load_4d(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
-      tma_load_4d(a_dst + WG_CHUNK, tmP, full, c.m_tile * WG_BM + 64, w0, h0, n0);
       const int qw = w0 * p.mul_w + p.off_w + c.s * p.step_w;
       const int qh = h0 * p.mul_h + p.off_h + c.r * p.step_h;
+      if (CG == 2) {
+        // the leader's barrier counts the bytes of both CTAs of the pair
+        const uint32_t full = (c.bar_full + 8 * STAGE) & PEER_BIT_MASK;
+        if (c.rank == 0) mbar_expect_tx(full, 2 * STAGE_BYTES);
+        tma_load_4d_2sm(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
+        tma_load_4d_2sm(a_dst + WG_CHUNK, tmP, full, c.m_tile * WG_BM + 64, w0, h0, n0);
 #pragma unroll
-      for (int ch = 0; ch < BN / 64; ++ch)
-        tma_load_4d(b_dst + ch * WG_CHUNK, tmQ, full, c.n_tile * BN + ch * 64, qw, qh, n0);
+        for (int ch = 0; ch < B_CHUNKS; ++ch)
+          tma_load_4d_2sm(b_dst + ch * WG_CHUNK, tmQ, full, c.n_tile * BN + c.rank * (BN / 2) + ch * 64, qw, qh,
+                          n0);
+      } else {
+        const uint32_t full = c.bar_full + 8 * STAGE;
+        mbar_expect_tx(full, STAGE_BYTES);
+        tma_load_4d(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
+        tma_load_4d(a_dst + WG_CHUNK, tmP, full, c.m_tile * WG_BM + 64, w0, h0, n0);
+#pragma unroll
+        for (int ch = 0; ch < B_CHUNKS; ++ch)
+          tma_load_4d(b_dst + ch * WG_CHUNK, tmQ, full, c.n_tile * BN + ch * 64, qw, qh, n0);
+      }
     }
-    wg_produce_round<BN, S, STAGE + 1>(tmP, tmQ, p, c, kb);
+    wg_produce_round<CG, BN, S, STAGE + 1>(tmP, tmQ, p, c, kb);
   }
 }
 
-template <int BN, int S, int STAGE>
+template <int CG, int BN, int S, int STAGE>
 __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
-  constexpr uint32_t STAGE_BYTES = (2 + BN / 64) * WG_CHUNK;
+  constexpr uint32_t STAGE_BYTES = (2 + BN / CG / 64) * WG_CHUNK;
   constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                              (static_cast<uint32_t>(BN >> 3) << 17) |
-                             (static_cast<uint32_t>(WG_BM >> 4) << 24);
+                             (static_cast<uint32_t>((WG_BM * CG) >> 4) << 24);
   if constexpr (STAGE < S) {
     if (kb + STAGE < c.iters) {
       mbar_wait(c.bar_full + 8 * STAGE, (c.phase_bits >> STAGE) & 1);
@@ -80,17 +93,24 @@ __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
         const uint64_t ad = const_smem_desc(a_off + k * 2048, WG_CHUNK, 1024);
         const uint64_t bd = const_smem_desc(b_off + k * 2048, WG_CHUNK, 1024);
         const uint32_t acc = (STAGE > 0 || k > 0) ? 1u : (kb != 0 ? 1u : 0u);
-        umma_bf16(c.tmem_base, ad, bd, IDESC, acc);
+        if (CG == 2) umma_bf16_2sm(c.tmem_base, ad, bd, IDESC, acc);
+        else umma_bf16(c.tmem_base, ad, bd, IDESC, acc);
       }
-      umma_commit(c.bar_empty + 8 * STAGE);
+      if (CG == 2) umma_commit_2sm(c.bar_empty + 8 * STAGE);
+      else umma_commit(c.bar_empty + 8 * STAGE);
     }
-    wg_mma_round<BN, S, STAGE + 1>(c, kb);
+    wg_mma_round<CG, BN, S, STAGE + 1>(c, kb);
   }
 }
 
 __device__ long long g_wg_flag;   // < 0: shared-memory ring not at SMEM_RING (checked by the launcher)
 
-template <int BN, int S>
+// CG = 2: a CTA pair owns two neighbouring 128-row tiles of M (output channels of P) and one N tile; each
+// CTA stages its own 128 x 64-pixel slab of P and HALF of the Q slab, the leader issues one cta_group::2
+// M = 256 MMA for both (as in igemm_fwd.cu).  Per CTA and 64-pixel block that is 16 + BN/2 * 128 B instead of
+// 16 KiB + BN * 128 B through L2 and shared memory: the 256 x 256 weight gradient moves 32 KiB per 512 MMA
+// cycles instead of 48.
+template <int CG, int BN, int S>
 __global__ void __launch_bounds__(192, 1)
 igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ,
                    const WgradParams p) {
@@ -102,24 +122,26 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   if ((smem_base & 0x3FFFFu) != SMEM_RING) {
     if (threadIdx.x == 0) g_wg_flag = -(long long)(smem_base & 0x3FFFFu);
     return;
   }
 
-  // ---- work item
-  int item = blockIdx.x;
+  // ---- work item (the same for both CTAs of a pair, except the M tile)
+  int item = blockIdx.x / CG;
   const int split = item % p.splits; item /= p.splits;
   const int n_tile = item % p.n_tiles; item /= p.n_tiles;
-  const int m_tile = item % p.m_tiles; item /= p.m_tiles;
+  const int m_groups = p.m_tiles / CG;
+  const int m_tile = (item % m_groups) * CG + rank; item /= m_groups;
   const int tap = item;
   const int r = tap / p.kw, s = tap % p.kw;
   const int total_kt = p.tiles_w * p.tiles_h * p.tiles_n;
   const int per = (total_kt + p.splits - 1) / p.splits;
   const int kt_begin = split * per;
   const int kt_end = min(total_kt, kt_begin + per);
-  if (kt_begin >= kt_end) return;  // uniform across the CTA
+  if (kt_begin >= kt_end) return;  // uniform across the CTA (and the pair)
   const int iters = kt_end - kt_begin;
 
   if (warp == 0 && lane == 0) {
@@ -132,9 +154,13 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
     mbar_init(smem_u32(&bar_tmem_full), 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+  if (warp == 1) {
+    if (CG == 2) tmem_alloc_2sm(smem_u32(&tmem_base_slot), p.tmem_cols);
+    else tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+  }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();     // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
   griddep_wait();        // programmatic dependent launch: the set-up above overlapped the previous kernel's tail
@@ -143,15 +169,16 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   WgCtx c;
   c.bar_full = smem_u32(&bar_full[0]); c.bar_empty = smem_u32(&bar_empty[0]);
   c.smem_base = smem_base; c.tmem_base = tmem_base; c.phase_bits = 0;
-  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.r = r; c.s = s;
+  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.r = r; c.s = s; c.rank = rank;
   if (warp == 0) {
     if (lane == 0)
-      for (int kb = 0; kb < iters; kb += S) wg_produce_round<BN, S, 0>(&tmP, &tmQ, p, c, kb);
+      for (int kb = 0; kb < iters; kb += S) wg_produce_round<CG, BN, S, 0>(&tmP, &tmQ, p, c, kb);
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      for (int kb = 0; kb < iters; kb += S) wg_mma_round<BN, S, 0>(c, kb);
-      umma_commit(smem_u32(&bar_tmem_full));
+    if (lane == 0 && rank == 0) {
+      for (int kb = 0; kb < iters; kb += S) wg_mma_round<CG, BN, S, 0>(c, kb);
+      if (CG == 2) umma_commit_2sm(smem_u32(&bar_tmem_full));
+      else umma_commit(smem_u32(&bar_tmem_full));
     }
     __syncwarp();
   } else {
@@ -182,17 +209,21 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+  if (CG == 2) cluster_sync_all();     // the leader's MMAs read the peer's smem / write its TMEM
+  if (warp == 1) {
+    if (CG == 2) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
+  }
 }
 
-template <int BN>
+template <int CG, int BN>
 static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& tmQ,
                                     const WgradParams& p, cudaStream_t stream) {
-  constexpr int kStageBytes = (2 + BN / 64) * WG_CHUNK;
+  constexpr int kStageBytes = (2 + BN / CG / 64) * WG_CHUNK;
   constexpr int kFit = (200 * 1024) / kStageBytes;
   constexpr int kStages = kFit > 8 ? 8 : kFit;
   constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024;
-  auto* kern = igemm_wgrad_kernel<BN, kStages>;
+  auto* kern = igemm_wgrad_kernel<CG, BN, kStages>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
@@ -204,12 +235,14 @@ static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& t
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)grid, 1, 1); cfg.blockDim = dim3(192, 1, 1);
   cfg.dynamicSmemBytes = kSmem; cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   static int pdl = -1;
   if (pdl < 0) { const char* e = getenv("MT_PDL"); pdl = e ? (atoi(e) != 0) : 1; }
-  cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
   return cudaLaunchKernelEx(&cfg, kern, tmP, tmQ, p);
 }
 
@@ -217,11 +250,14 @@ int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradPara
                  cudaStream_t stream) {
   const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;
   if (grid <= 0 || grid > 0x7fffffffLL) return -1000;
+  if (p.cg == 2 && (p.m_tiles % 2 || p.BN < 128)) return -1010;
   cudaError_t e;
-  switch (p.BN) {
-    case 256: e = launch_wgrad_cfg<256>(tmP, tmQ, p, stream); break;
-    case 128: e = launch_wgrad_cfg<128>(tmP, tmQ, p, stream); break;
-    case 64: e = launch_wgrad_cfg<64>(tmP, tmQ, p, stream); break;
+  switch (p.cg * 1000 + p.BN) {
+    case 2256: e = launch_wgrad_cfg<2, 256>(tmP, tmQ, p, stream); break;
+    case 2128: e = launch_wgrad_cfg<2, 128>(tmP, tmQ, p, stream); break;
+    case 1256: e = launch_wgrad_cfg<1, 256>(tmP, tmQ, p, stream); break;
+    case 1128: e = launch_wgrad_cfg<1, 128>(tmP, tmQ, p, stream); break;
+    case 1064: e = launch_wgrad_cfg<1, 64>(tmP, tmQ, p, stream); break;
     default: return -1010;
   }
   if (e != cudaSuccess) return -(int)e;
