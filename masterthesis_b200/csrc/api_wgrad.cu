@@ -30,8 +30,14 @@ static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   p.BN = n_logical >= 256 ? 256 : (n_logical > 64 ? 128 : 64);
   p.m_tiles = cdiv(c.Pc, 128);
   p.n_tiles = cdiv(n_logical, p.BN);
+  // narrow 3x3 layers: three taps (one filter row) per work item share the un-shifted operand's slab
+  // (igemm_wgrad.cu); MT_WGRAD_TAPS=1 keeps one tap per work item
+  static int force_taps = -1;
+  if (force_taps < 0) { const char* e = getenv("MT_WGRAD_TAPS"); force_taps = e ? atoi(e) : 0; }
+  p.tap_group = (!c.window && p.kh * p.kw == 9 && p.BN <= 128 && force_taps != 1) ? 3 : 1;
+  p.tap_groups = cdiv(p.kh * p.kw, p.tap_group);
   const int total_kt = p.tiles_w * p.tiles_h * p.tiles_n;
-  const int items = p.kh * p.kw * p.m_tiles * p.n_tiles;
+  const int items = p.tap_groups * p.m_tiles * p.n_tiles;
   // one wave of CTAs: every split pays a full fp32 red.add epilogue, so prefer long main loops
   int splits = 148 / items;
   const int max_splits = cdiv(total_kt, 8);   // at least 8 pixel tiles per split
@@ -44,10 +50,10 @@ static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   static int force_cg = -1;
   if (force_cg < 0) { const char* e = getenv("MT_WGRAD_CG"); force_cg = e ? atoi(e) : 0; }
   p.cg = (p.m_tiles % 2 == 0 && p.BN >= 128 && force_cg != 1) ? 2 : 1;
-  const int stage_bytes = (2 + p.BN / p.cg / 64) * 8192;
+  const int stage_bytes = (2 + p.tap_group * (p.BN / p.cg / 64)) * 8192;
   p.stages = (200 * 1024) / stage_bytes;
   if (p.stages > 8) p.stages = 8;
-  p.tmem_cols = pow2_cols(p.BN);
+  p.tmem_cols = pow2_cols(p.tap_group * p.BN);
   p.M_valid = c.Pc;
   p.N_valid = c.N_store;
   p.out_m_stride = c.N_store;

@@ -29,14 +29,14 @@ __device__ __forceinline__ void st_v4(float* addr, float a, float b, float c, fl
 // with it every shared-memory descriptor is a constant (MMA issue-rate rule, see igemm_fwd.cu).
 struct WgCtx {
   uint32_t bar_full, bar_empty, smem_base, tmem_base, phase_bits;
-  int iters, kt_begin, m_tile, n_tile, r, s, rank;
+  int iters, kt_begin, m_tile, n_tile, tap0, n_taps, rank;
 };
 
-template <int CG, int BN, int S, int STAGE>
+template <int CG, int BN, int G, int S, int STAGE>
 __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const CUtensorMap* tmQ,
                                                  const WgradParams& p, WgCtx& c, int kb) {
-  constexpr int B_CHUNKS = BN / CG / 64;                      // 64-channel slabs of Q staged by this CTA
-  constexpr uint32_t STAGE_BYTES = (2 + B_CHUNKS) * WG_CHUNK;
+  constexpr int B_CHUNKS = BN / CG / 64;                      // 64-channel slabs of Q staged by this CTA, per tap
+  constexpr uint32_t STAGE_BYTES = (2 + G * B_CHUNKS) * WG_CHUNK;
   if constexpr (STAGE < S) {
     if (kb + STAGE < c.iters) {
       int kt = c.kt_begin + kb + STAGE;
@@ -48,35 +48,42 @@ __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const C
       c.phase_bits ^= 1u << STAGE;
       const uint32_t a_dst = c.smem_base + STAGE * STAGE_BYTES;
       const uint32_t b_dst = a_dst + 2 * WG_CHUNK;
-      const int qw = w0 * p.mul_w + p.off_w + c.s * p.step_w;
-      const int qh = h0 * p.mul_h + p.off_h + c.r * p.step_h;
+      const uint32_t bytes = (2 + c.n_taps * B_CHUNKS) * WG_CHUNK;
+      const uint32_t full = CG == 2 ? ((c.bar_full + 8 * STAGE) & PEER_BIT_MASK) : (c.bar_full + 8 * STAGE);
+      // CG == 2: the leader's barrier counts the bytes of both CTAs of the pair
+      if (CG == 1 || c.rank == 0) mbar_expect_tx(full, CG * bytes);
       if (CG == 2) {
-        // the leader's barrier counts the bytes of both CTAs of the pair
-        const uint32_t full = (c.bar_full + 8 * STAGE) & PEER_BIT_MASK;
-        if (c.rank == 0) mbar_expect_tx(full, 2 * STAGE_BYTES);
         tma_load_4d_2sm(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
         tma_load_4d_2sm(a_dst + WG_CHUNK, tmP, full, c.m_tile * WG_BM + 64, w0, h0, n0);
-#pragma unroll
-        for (int ch = 0; ch < B_CHUNKS; ++ch)
-          tma_load_4d_2sm(b_dst + ch * WG_CHUNK, tmQ, full, c.n_tile * BN + c.rank * (BN / 2) + ch * 64, qw, qh,
-                          n0);
       } else {
-        const uint32_t full = c.bar_full + 8 * STAGE;
-        mbar_expect_tx(full, STAGE_BYTES);
         tma_load_4d(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
         tma_load_4d(a_dst + WG_CHUNK, tmP, full, c.m_tile * WG_BM + 64, w0, h0, n0);
+      }
+      const int qw0 = w0 * p.mul_w + p.off_w, qh0 = h0 * p.mul_h + p.off_h;
+      const int ch0 = c.n_tile * BN + c.rank * (BN / CG);
 #pragma unroll
-        for (int ch = 0; ch < B_CHUNKS; ++ch)
-          tma_load_4d(b_dst + ch * WG_CHUNK, tmQ, full, c.n_tile * BN + ch * 64, qw, qh, n0);
+      for (int g = 0; g < G; ++g) {
+        if (g < c.n_taps) {
+          const int tap = c.tap0 + g;
+          const int r = tap / p.kw, s = tap - r * p.kw;
+          const int qw = qw0 + s * p.step_w, qh = qh0 + r * p.step_h;
+#pragma unroll
+          for (int ch = 0; ch < B_CHUNKS; ++ch) {
+            const uint32_t dst = b_dst + (g * B_CHUNKS + ch) * WG_CHUNK;
+            if (CG == 2) tma_load_4d_2sm(dst, tmQ, full, ch0 + ch * 64, qw, qh, n0);
+            else tma_load_4d(dst, tmQ, full, ch0 + ch * 64, qw, qh, n0);
+          }
+        }
       }
     }
-    wg_produce_round<CG, BN, S, STAGE + 1>(tmP, tmQ, p, c, kb);
+    wg_produce_round<CG, BN, G, S, STAGE + 1>(tmP, tmQ, p, c, kb);
   }
 }
 
-template <int CG, int BN, int S, int STAGE>
+template <int CG, int BN, int G, int S, int STAGE>
 __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
-  constexpr uint32_t STAGE_BYTES = (2 + BN / CG / 64) * WG_CHUNK;
+  constexpr int B_CHUNKS = BN / CG / 64;
+  constexpr uint32_t STAGE_BYTES = (2 + G * B_CHUNKS) * WG_CHUNK;
   constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                              (static_cast<uint32_t>(BN >> 3) << 17) |
                              (static_cast<uint32_t>((WG_BM * CG) >> 4) << 24);
@@ -87,19 +94,25 @@ __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
       tc_fence_after();
       constexpr uint32_t a_off = SMEM_RING + STAGE * STAGE_BYTES;
       constexpr uint32_t b_off = a_off + 2 * WG_CHUNK;
+      // the taps of the group share the P slab of this stage: one accumulator of BN columns per tap
 #pragma unroll
-      for (int k = 0; k < WG_BK / 16; ++k) {
-        // 16 pixels = two 8-row groups of 1024 B; chunks of 64 channels are WG_CHUNK apart.
-        const uint64_t ad = const_smem_desc(a_off + k * 2048, WG_CHUNK, 1024);
-        const uint64_t bd = const_smem_desc(b_off + k * 2048, WG_CHUNK, 1024);
-        const uint32_t acc = (STAGE > 0 || k > 0) ? 1u : (kb != 0 ? 1u : 0u);
-        if (CG == 2) umma_bf16_2sm(c.tmem_base, ad, bd, IDESC, acc);
-        else umma_bf16(c.tmem_base, ad, bd, IDESC, acc);
+      for (int g = 0; g < G; ++g) {
+        if (g < c.n_taps) {
+#pragma unroll
+          for (int k = 0; k < WG_BK / 16; ++k) {
+            // 16 pixels = two 8-row groups of 1024 B; chunks of 64 channels are WG_CHUNK apart.
+            const uint64_t ad = const_smem_desc(a_off + k * 2048, WG_CHUNK, 1024);
+            const uint64_t bd = const_smem_desc(b_off + g * B_CHUNKS * WG_CHUNK + k * 2048, WG_CHUNK, 1024);
+            const uint32_t acc = (STAGE > 0 || k > 0) ? 1u : (kb != 0 ? 1u : 0u);
+            if (CG == 2) umma_bf16_2sm(c.tmem_base + g * BN, ad, bd, IDESC, acc);
+            else umma_bf16(c.tmem_base + g * BN, ad, bd, IDESC, acc);
+          }
+        }
       }
       if (CG == 2) umma_commit_2sm(c.bar_empty + 8 * STAGE);
       else umma_commit(c.bar_empty + 8 * STAGE);
     }
-    wg_mma_round<CG, BN, S, STAGE + 1>(c, kb);
+    wg_mma_round<CG, BN, G, S, STAGE + 1>(c, kb);
   }
 }
 
@@ -110,7 +123,12 @@ __device__ long long g_wg_flag;   // < 0: shared-memory ring not at SMEM_RING (c
 // M = 256 MMA for both (as in igemm_fwd.cu).  Per CTA and 64-pixel block that is 16 + BN/2 * 128 B instead of
 // 16 KiB + BN * 128 B through L2 and shared memory: the 256 x 256 weight gradient moves 32 KiB per 512 MMA
 // cycles instead of 48.
-template <int CG, int BN, int S>
+//
+// G > 1: a work item covers G consecutive filter taps.  Their GEMMs share the P operand (dy of the un-shifted
+// pixel block) and differ in the shifted Q slab, so a stage holds one P slab + G Q slabs and feeds G
+// accumulators of BN columns in TMEM: the P slab crosses L2 -> SM once per G taps.  Used for the narrow
+// layers (BN <= 128), which are bound by that stream and not by the tensor pipe.
+template <int CG, int BN, int G, int S>
 __global__ void __launch_bounds__(192, 1)
 igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ,
                    const WgradParams p) {
@@ -135,8 +153,8 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   const int n_tile = item % p.n_tiles; item /= p.n_tiles;
   const int m_groups = p.m_tiles / CG;
   const int m_tile = (item % m_groups) * CG + rank; item /= m_groups;
-  const int tap = item;
-  const int r = tap / p.kw, s = tap % p.kw;
+  const int tap0 = item * G;
+  const int n_taps = min(G, p.kh * p.kw - tap0);
   const int total_kt = p.tiles_w * p.tiles_h * p.tiles_n;
   const int per = (total_kt + p.splits - 1) / p.splits;
   const int kt_begin = split * per;
@@ -169,14 +187,14 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   WgCtx c;
   c.bar_full = smem_u32(&bar_full[0]); c.bar_empty = smem_u32(&bar_empty[0]);
   c.smem_base = smem_base; c.tmem_base = tmem_base; c.phase_bits = 0;
-  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.r = r; c.s = s; c.rank = rank;
+  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.tap0 = tap0; c.n_taps = n_taps; c.rank = rank;
   if (warp == 0) {
     if (lane == 0)
-      for (int kb = 0; kb < iters; kb += S) wg_produce_round<CG, BN, S, 0>(&tmP, &tmQ, p, c, kb);
+      for (int kb = 0; kb < iters; kb += S) wg_produce_round<CG, BN, G, S, 0>(&tmP, &tmQ, p, c, kb);
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
-      for (int kb = 0; kb < iters; kb += S) wg_mma_round<CG, BN, S, 0>(c, kb);
+      for (int kb = 0; kb < iters; kb += S) wg_mma_round<CG, BN, G, S, 0>(c, kb);
       if (CG == 2) umma_commit_2sm(smem_u32(&bar_tmem_full));
       else umma_commit(smem_u32(&bar_tmem_full));
     }
@@ -185,23 +203,25 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
     const int q = warp & 3;
     const int m = m_tile * WG_BM + q * 32 + lane;
     const bool row_ok = m < p.M_valid;
-    float* orow = p.out + (long long)split * p.out_split_stride + (long long)tap * p.out_tap_stride +
-                  (long long)m * p.out_m_stride;
     const int n_base = n_tile * BN;
     mbar_wait(smem_u32(&bar_tmem_full), 0);
     tc_fence_after();
-    for (int c0 = 0; c0 < BN; c0 += 16) {
-      if (n_base + c0 >= p.N_valid) break;
-      uint32_t v[16];
-      tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
-      tmem_ld_wait();
-      if (row_ok) {
+    for (int g = 0; g < n_taps; ++g) {
+      float* orow = p.out + (long long)split * p.out_split_stride + (long long)(tap0 + g) * p.out_tap_stride +
+                    (long long)m * p.out_m_stride;
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        if (n_base + c0 >= p.N_valid) break;
+        uint32_t v[16];
+        tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + g * BN + c0, v);
+        tmem_ld_wait();
+        if (row_ok) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int n = n_base + c0 + g * 4;
-          if (n < p.N_valid)
-            st_v4(orow + n, __uint_as_float(v[g * 4 + 0]), __uint_as_float(v[g * 4 + 1]),
-                  __uint_as_float(v[g * 4 + 2]), __uint_as_float(v[g * 4 + 3]));
+          for (int j = 0; j < 4; ++j) {
+            const int n = n_base + c0 + j * 4;
+            if (n < p.N_valid)
+              st_v4(orow + n, __uint_as_float(v[j * 4 + 0]), __uint_as_float(v[j * 4 + 1]),
+                    __uint_as_float(v[j * 4 + 2]), __uint_as_float(v[j * 4 + 3]));
+          }
         }
       }
     }
@@ -216,21 +236,21 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   }
 }
 
-template <int CG, int BN>
+template <int CG, int BN, int G>
 static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& tmQ,
                                     const WgradParams& p, cudaStream_t stream) {
-  constexpr int kStageBytes = (2 + BN / CG / 64) * WG_CHUNK;
+  constexpr int kStageBytes = (2 + G * (BN / CG / 64)) * WG_CHUNK;
   constexpr int kFit = (200 * 1024) / kStageBytes;
   constexpr int kStages = kFit > 8 ? 8 : kFit;
   constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024;
-  auto* kern = igemm_wgrad_kernel<CG, BN, kStages>;
+  auto* kern = igemm_wgrad_kernel<CG, BN, G, kStages>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;
+  const long long grid = (long long)p.tap_groups * p.m_tiles * p.n_tiles * p.splits;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)grid, 1, 1); cfg.blockDim = dim3(192, 1, 1);
@@ -248,16 +268,20 @@ static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& t
 
 int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradParams& p,
                  cudaStream_t stream) {
-  const long long grid = (long long)p.kh * p.kw * p.m_tiles * p.n_tiles * p.splits;
+  const long long grid = (long long)p.tap_groups * p.m_tiles * p.n_tiles * p.splits;
   if (grid <= 0 || grid > 0x7fffffffLL) return -1000;
   if (p.cg == 2 && (p.m_tiles % 2 || p.BN < 128)) return -1010;
   cudaError_t e;
-  switch (p.cg * 1000 + p.BN) {
-    case 2256: e = launch_wgrad_cfg<2, 256>(tmP, tmQ, p, stream); break;
-    case 2128: e = launch_wgrad_cfg<2, 128>(tmP, tmQ, p, stream); break;
-    case 1256: e = launch_wgrad_cfg<1, 256>(tmP, tmQ, p, stream); break;
-    case 1128: e = launch_wgrad_cfg<1, 128>(tmP, tmQ, p, stream); break;
-    case 1064: e = launch_wgrad_cfg<1, 64>(tmP, tmQ, p, stream); break;
+  if (p.tap_group * p.tap_groups < p.kh * p.kw || p.tap_group * p.BN > 512) return -1010;
+  switch (p.tap_group * 10000 + p.cg * 1000 + p.BN) {
+    case 12256: e = launch_wgrad_cfg<2, 256, 1>(tmP, tmQ, p, stream); break;
+    case 12128: e = launch_wgrad_cfg<2, 128, 1>(tmP, tmQ, p, stream); break;
+    case 11256: e = launch_wgrad_cfg<1, 256, 1>(tmP, tmQ, p, stream); break;
+    case 11128: e = launch_wgrad_cfg<1, 128, 1>(tmP, tmQ, p, stream); break;
+    case 11064: e = launch_wgrad_cfg<1, 64, 1>(tmP, tmQ, p, stream); break;
+    case 32128: e = launch_wgrad_cfg<2, 128, 3>(tmP, tmQ, p, stream); break;
+    case 31128: e = launch_wgrad_cfg<1, 128, 3>(tmP, tmQ, p, stream); break;
+    case 31064: e = launch_wgrad_cfg<1, 64, 3>(tmP, tmQ, p, stream); break;
     default: return -1010;
   }
   if (e != cudaSuccess) return -(int)e;
