@@ -93,6 +93,23 @@ int mt_conv_s1_dgrad_pair_mode(int kh, int kw, int stride, int zpad, int Cin_s);
 long long mt_packed_conv_s1_dgrad_pair_elems(int Cout, int k);
 int mt_pack_conv_s1_dgrad_pair_weight(const float* w, int Cout, int Cin, int k, void* w_bwd, void* stream);
 
+/* Rows-in-K data gradient for a stride-1 un-padded conv with many taps into <= 4 channels, i.e. the image
+ * gradient of the 7x7 stems (networks.py:30: 49 taps, 3 channels): one implicit-GEMM launch over (output row,
+ * dy column) whose K runs over the kh filter rows (dy rows h' - r) and whose columns are (filter column s,
+ * channel c); the epilogue adds the kw shifted columns, per-tile partial rows go to `scratch` and a second
+ * kernel adds neighbouring tiles in a fixed order (no atomics).  dy crosses L2 kh times instead of
+ * kh*(kw+1)/2 times.  When mt_conv_rowk_dgrad_mode(kh, kw, stride, zpad, Cin, Cout_s) is 1 the caller may use
+ * mt_conv2d_dgrad_rowk instead of mt_conv2d_dgrad: w_rowk = [kh][32][Cout_s] bf16 from
+ * mt_pack_conv_rowk_weight, scratch = mt_conv_rowk_scratch_elems(d) fp32 (caller-owned, needs no zeroing),
+ * dx = [N, Hin, Win, 8] bf16 as from mt_conv2d_dgrad.  No even-extent requirement.  MT_DGRAD_ROWK=0 turns the
+ * predicate off. */
+int mt_conv_rowk_dgrad_mode(int kh, int kw, int stride, int zpad, int Cin, int Cout_s);
+long long mt_packed_conv_rowk_elems(int Cout, int kh);
+int mt_pack_conv_rowk_weight(const float* w, int Cout, int Cin, int kh, int kw, void* w_rowk, void* stream);
+long long mt_conv_rowk_scratch_elems(const MtConv2d* d);
+int mt_conv2d_dgrad_rowk(const MtConv2d* d, const void* dy, const void* w_rowk, float* scratch, void* dx,
+                         void* stream);
+
 /* Row-window stems (mt_conv_window_mode) whose 64-element window also covers the next output pixel
  * ((kw + stride) * Cin_s <= 64: the 7x7 image stems networks.py:30,76 and the stride-2 stems
  * networks.py:117,361) compute two adjacent output pixels per GEMM row when

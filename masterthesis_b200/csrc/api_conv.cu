@@ -12,6 +12,7 @@
 
 #include "../../include/mt_b200.h"
 #include "igemm.cuh"
+#include "ew_common.cuh"
 
 namespace mt {
 
@@ -60,6 +61,8 @@ struct ConvLike {
   float* stats;             // optional fused plane statistics [Nt][stat_parts][n_store][2]
   int stat_parts, stat_part0;
   int accumulate;           // out += result
+  int rowk_kw, rowk_c, rowk_win;   // rows-in-K data gradient (IgemmParams::rowk_*), 0: off
+  float* rowk_out;
 };
 
 static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
@@ -96,6 +99,8 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   p.act = c.act; p.slope = c.slope; p.bias = c.bias;
   p.accumulate = c.accumulate;
   p.out = reinterpret_cast<__nv_bfloat16*>(c.out);
+  p.rowk_kw = c.rowk_kw; p.rowk_c = c.rowk_c; p.rowk_win = c.rowk_win; p.rowk_out = c.rowk_out;
+  if (p.rowk_kw > 0 && (p.BN != 32 || p.cg != 1 || p.rowk_kw * p.rowk_c > 24)) return -1014;
 
   CUtensorMap tmA, tmB;
   int rc;
@@ -147,6 +152,45 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     p.stat_parts = c.stat_parts; p.stat_part0 = c.stat_part0;
   }
   return launch_igemm(tmA, tmB, tmC, p, stream);
+}
+
+// ---- rows-in-K data gradient of a many-tap stride-1 conv into <= 4 channels (mt_conv2d_dgrad_rowk)
+// fp32 OIHW master -> bf16 [kh][32][Cout_s]: row (s * Cin + c) of tap r holds W[:, c, r, s]
+__global__ void pack_rowk_kernel(const float* __restrict__ w, int Cout, int Cin, int kh, int kw, int Cout_s,
+                                 __nv_bfloat16* __restrict__ out) {
+  pdl_wait(); pdl_launch();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= kh * 32 * Cout_s) return;
+  const int co = i % Cout_s, row = (i / Cout_s) % 32, r = i / (Cout_s * 32);
+  float v = 0.f;
+  if (co < Cout && row < kw * Cin) {
+    const int s = row / Cin, c = row - s * Cin;
+    v = w[(((long long)co * Cin + c) * kh + r) * kw + s];
+  }
+  out[i] = __float2bfloat16(v);
+}
+
+// dx[n, h, w, 0..7] (bf16) = sum of the tile slots that cover column w, lowest tile first
+__global__ void rowk_gather_kernel(const float* __restrict__ part, __nv_bfloat16* __restrict__ dx, long long pixels,
+                                   int Win, int tiles_w, int TW, int ow) {
+  pdl_wait(); pdl_launch();
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= pixels) return;
+  const int w = (int)(i % Win);
+  const long long row = i / Win;                               // n * Hin + h
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  int t = (w - (ow - 1) + TW - 1) / TW;                        // first tile with w - t * TW <= ow - 1
+  if (w - (ow - 1) < 0) t = 0;
+  for (; t < tiles_w && t * TW <= w; ++t) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(part + ((row * tiles_w + t) * ow + (w - t * TW)) * 4));
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  bf16x8 o;
+  o.v[0] = __floats2bfloat162_rn(a.x, a.y);
+  o.v[1] = __floats2bfloat162_rn(a.z, a.w);
+  o.v[2] = __floats2bfloat162_rn(0.f, 0.f);
+  o.v[3] = o.v[2];
+  *reinterpret_cast<bf16x8*>(dx + i * 8) = o;
 }
 
 static int check_desc(const MtConv2d* d) {
@@ -388,6 +432,66 @@ extern "C" int mt_conv_s1_dgrad_pair_mode(int kh, int kw, int stride, int zpad, 
   static int off = -1;
   if (off < 0) { const char* e = getenv("MT_DGRAD_PAIR"); off = (e && atoi(e) == 0) ? 1 : 0; }
   return (!off && stride == 1 && zpad == 0 && kh == kw && Cin_s == 8) ? 1 : 0;
+}
+
+// Data gradient of a stride-1, un-padded, many-tap conv into <= 4 channels (the image gradient of the 7x7
+// stems, networks.py:30) with the filter ROWS in K and the filter COLUMNS in N: one launch of the implicit
+// GEMM over (output row h', dy column w) with kh k-blocks (dy rows h' - r) and columns (s, c); its epilogue
+// adds the kw shifted columns (epilogue_rowk).  dy crosses L2 -> SM kh times instead of kh * (kw + 1) / 2.
+extern "C" int mt_conv_rowk_dgrad_mode(int kh, int kw, int stride, int zpad, int Cin, int Cout_s) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("MT_DGRAD_ROWK"); off = (e && atoi(e) == 0) ? 1 : 0; }
+  return (!off && stride == 1 && zpad == 0 && Cin <= 4 && kw * Cin <= 24 && kh * kw >= 16 && Cout_s % 8 == 0) ? 1 : 0;
+}
+extern "C" long long mt_packed_conv_rowk_elems(int Cout, int kh) { return (long long)kh * 32 * round_up(Cout, 8); }
+extern "C" int mt_pack_conv_rowk_weight(const float* w, int Cout, int Cin, int kh, int kw, void* w_rowk,
+                                        void* stream) {
+  if (kw * Cin > 24) return -1005;
+  const int Cout_s = round_up(Cout, 8), n = kh * 32 * Cout_s;
+  cudaError_t e = launch_pdl(pack_rowk_kernel, dim3(cdiv(n, 256)), dim3(256), 0, (cudaStream_t)stream, w, Cout, Cin,
+                             kh, kw, Cout_s, reinterpret_cast<__nv_bfloat16*>(w_rowk));
+  return e == cudaSuccess ? 0 : -(int)e;
+}
+static void rowk_tile(const MtConv2d* d, int* TW, int* tiles_w) {
+  int TH, TN;
+  pick_tile(128, d->Wout, d->Hin, d->N, 1, TW, &TH, &TN);      // the tile run_conv_like picks for this launch
+  *tiles_w = cdiv(d->Wout, *TW);
+}
+extern "C" long long mt_conv_rowk_scratch_elems(const MtConv2d* d) {
+  if (!d) return 0;
+  int TW, tiles_w;
+  rowk_tile(d, &TW, &tiles_w);
+  return (long long)d->N * d->Hin * tiles_w * (TW + d->kw - 1) * 4;
+}
+extern "C" int mt_conv2d_dgrad_rowk(const MtConv2d* d, const void* dy, const void* w_rowk, float* scratch,
+                                    void* dx, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  if (!dy || !w_rowk || !scratch || !dx) return -1002;
+  if (!mt_conv_rowk_dgrad_mode(d->kh, d->kw, d->stride, d->zpad, d->Cin, d->Cout_s) || d->Cin_s != 8 ||
+      d->Hin != d->Hout + d->kh - 1 || d->Win != d->Wout + d->kw - 1)
+    return -1014;
+  ConvLike c;
+  memset(&c, 0, sizeof(c));
+  c.a = dy; c.An = d->N; c.Ah = d->Hout; c.Aw = d->Wout; c.Ac = d->Cout; c.Ac_s = d->Cout_s;
+  c.a_mul = 1; c.window = false;
+  c.b = w_rowk; c.taps_total = d->kh; c.Bn = 32; c.Bk = d->Cout; c.Bk_s = d->Cout_s;
+  c.Wt = d->Wout; c.Ht = d->Hin; c.Nt = d->N;
+  c.kh = d->kh; c.kw = 1; c.off_h = 0; c.off_w = 0; c.step_h = -1; c.step_w = 0;
+  c.w_base = 0; c.w_step_r = 1; c.w_step_s = 0;
+  c.n_store = 8; c.n_bias = 0; c.bias = nullptr; c.act = MT_ACT_NONE;
+  c.out = dx;                          // only to form a valid (unused) output map
+  c.out_w_stride = 8; c.out_h_stride = (long long)d->Win * 8; c.out_n_stride = (long long)d->Hin * d->Win * 8;
+  c.rowk_kw = d->kw; c.rowk_c = d->Cin; c.rowk_win = d->Win; c.rowk_out = scratch;
+  rc = run_conv_like(c, (cudaStream_t)stream);
+  if (rc) return rc;
+  int TW, tiles_w;
+  rowk_tile(d, &TW, &tiles_w);
+  const long long pixels = (long long)d->N * d->Hin * d->Win;
+  cudaError_t e = launch_pdl(rowk_gather_kernel, dim3((unsigned)((pixels + 255) / 256)), dim3(256), 0,
+                             (cudaStream_t)stream, (const float*)scratch, reinterpret_cast<__nv_bfloat16*>(dx),
+                             pixels, d->Win, tiles_w, TW, TW + d->kw - 1);
+  return e == cudaSuccess ? 0 : -(int)e;
 }
 
 extern "C" int mt_conv2d_dgrad(const MtConv2d* d, const void* dy, const void* w_bwd, void* dx,

@@ -40,6 +40,11 @@ struct IgemmParams {
   float* stats;        // optional fused plane statistics: [N][stat_parts][n_stat_c][2] fp32 partial
   int n_stat_c;        // (sum, sumsq) per pixel tile; this launch fills slots stat_part0 + tile index
   int stat_parts, stat_part0;
+  // "rows in K, columns in N" data gradient into <= 4 channels (BN == 32 only, see epilogue_rowk in igemm_fwd.cu):
+  // GEMM column (s, c) holds tap column s of input channel c; the epilogue adds the kw shifted columns and
+  // writes fp32 partial rows to rowk_out instead of storing the tile.  rowk_kw == 0: off.
+  int rowk_kw, rowk_c, rowk_win;
+  float* rowk_out;     // [Nt][Ht][tiles_w][TW + kw - 1][4]
 };
 
 // dW_tap[Cout, Cin] = sum_pixels dY[pix, Cout]^T * X_tap[pix, Cin]   (both operands MN-major)

@@ -146,6 +146,47 @@ __device__ __forceinline__ WorkCoord decode_work(const IgemmParams& p, int item,
   return c;
 }
 
+// Epilogue of the rows-in-K data gradient (IgemmParams::rowk_*): the accumulator row of dy pixel (h, w) holds
+// Z[(s, c)] = sum_r dy[h' - r, w, :] . W[:, c, r, s] for the output row h' of this tile; the gradient is
+// dx[h', w + s, c] = sum_s Z(w)[(s, c)].  The team stages Z as fp32 in its box (row stride 25 words: the 32
+// rows a warp writes land in 32 banks), then thread o adds the <= kw shifted entries of output column o of a
+// tile row and stores the partial sum to this tile's slot (plain stores; a gather kernel adds the slots of
+// neighbouring tiles in a fixed order).
+__device__ __forceinline__ void epilogue_rowk(const IgemmParams& p, uint32_t tmem_addr, float* Z, int m, int tt,
+                                              int bar_id, uint32_t bar_tempty, const WorkCoord& wc, int tile_col) {
+  constexpr int ZS = 25;
+  uint32_t v[32];
+  tmem_ld32(tmem_addr, v);
+  tmem_ld_wait();
+  tc_fence_before();
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar_tempty);      // accumulator stage free (BN == 32 runs with CG == 1)
+  const int nz = p.rowk_kw * p.rowk_c;
+#pragma unroll
+  for (int j = 0; j < 24; ++j)
+    if (j < nz) Z[m * ZS + j] = __uint_as_float(v[j]);
+  named_bar_sync(bar_id, 128);
+  const int ow = p.TW + p.rowk_kw - 1;                       // output columns one tile row contributes to
+  const int total = p.TN * p.TH * ow;
+  for (int o = tt; o < total; o += 128) {
+    const int j = o % ow, row = o / ow;                      // row = n_i * TH + h_i
+    const int h_i = row % p.TH, n_i = row / p.TH;
+    if (wc.n0 + n_i >= p.Nt || wc.h0 + h_i >= p.Ht || wc.w0 + j >= p.rowk_win) continue;
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < p.rowk_kw; ++s) {
+      const int w_i = j - s;
+      if (w_i < 0 || w_i >= p.TW) continue;
+      const float* z = Z + (row * p.TW + w_i) * ZS + s * p.rowk_c;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (c < p.rowk_c) a[c] += z[c];
+    }
+    float* dst = p.rowk_out +
+                 ((((long long)(wc.n0 + n_i) * p.Ht + (wc.h0 + h_i)) * p.tiles_w + tile_col) * ow + j) * 4;
+    *reinterpret_cast<float4*>(dst) = make_float4(a[0], a[1], a[2], a[3]);
+  }
+}
+
 // 4 MMAs = one 64-wide K block of ring stage STAGE into the accumulator at column ACC_OFF.
 template <int CG, int STAGE, uint32_t STAGE_BYTES, int ACC_OFF>
 __device__ __forceinline__ void mma_kblock(uint32_t tmem_base, uint32_t idesc, uint32_t acc_first) {
@@ -345,6 +386,14 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tc_fence_after();
       if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
       const uint32_t tmem_row = tmem_base + acc * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
+      if constexpr (BN == 32 && CG == 1) {
+        if (p.rowk_kw > 0) {
+          named_bar_sync(1 + grp, 128);       // the team has finished reading Z of its previous tile
+          epilogue_rowk(p, tmem_row, reinterpret_cast<float*>(smem_raw + (stage_buf - smem_u32(smem_raw))), m, tt,
+                        1 + grp, smem_u32(&bar_tempty[acc]), wc, wc.w0 / p.TW);
+          continue;
+        }
+      }
       bool released = false;
       for (int sl = NSLAB == 1 ? 0 : grp; sl < NSLAB; sl += 2) {
         const int c_glob = wc.n_tile * BN + sl * SW;

@@ -195,10 +195,17 @@ class ConvGeom:
                     _lib.lib().mt_conv_window_pair_mode(self.Cin_s, self.kw, self.stride))
 
     @property
+    def rowk_dgrad(self) -> bool:
+        """many-tap stride-1 conv into <= 4 channels (7x7 image stems): data gradient with the filter rows in K
+        and the filter columns in N (include/mt_b200.h).  Takes precedence over pair_s1_dgrad."""
+        return bool(not self.transposed and _lib.lib().mt_conv_rowk_dgrad_mode(
+            self.kh, self.kw, self.stride, self.zpad, self.Cin, self.Cout_s))
+
+    @property
     def pair_s1_dgrad(self) -> bool:
         """stride-1 conv into <= 8 channels whose data gradient computes pixel pairs (include/mt_b200.h)"""
-        return bool(not self.transposed and not self.single and _lib.lib().mt_conv_s1_dgrad_pair_mode(
-            self.kh, self.kw, self.stride, self.zpad, self.Cin_s))
+        return bool(not self.transposed and not self.single and not self.rowk_dgrad and
+                    _lib.lib().mt_conv_s1_dgrad_pair_mode(self.kh, self.kw, self.stride, self.zpad, self.Cin_s))
 
     @property
     def merged_s2_dgrad(self) -> bool:
@@ -231,6 +238,22 @@ def pack_weight(w: torch.Tensor, g: ConvGeom):
     _require_cuda(w)
     L = _lib.lib()
     w = w.detach().contiguous().float()
+    if g.rowk_dgrad:
+        # the data-gradient operand is the rows-in-K pack; the forward operand follows the usual rules
+        if g.window_pair:
+            wf = _T.empty(L.mt_packed_conv_window_pair_elems(g.Cout, g.kh), dtype=torch.bfloat16, device=w.device)
+            check(L.mt_pack_conv_window_pair_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, g.stride, _p(wf), _stream()),
+                  "mt_pack_conv_window_pair_weight")
+        else:
+            wf = _T.empty(L.mt_packed_weight_elems(g.Cout, g.Cin, g.kh, g.kw, int(g.window), 0),
+                          dtype=torch.bfloat16, device=w.device)
+            check(L.mt_pack_conv_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, 0, int(g.window), _p(wf), None,
+                                        _stream()), "mt_pack_conv_weight")
+        wb = _T.empty(L.mt_packed_conv_rowk_elems(g.Cout, g.kh), dtype=torch.bfloat16, device=w.device)
+        check(L.mt_pack_conv_rowk_weight(_p(w), g.Cout, g.Cin, g.kh, g.kw, _p(wb), _stream()),
+              "mt_pack_conv_rowk_weight")
+        _count(2)
+        return wf, wb
     if g.window_pair:
         # paired row-window stem: its own forward operand; the data-gradient operand by the usual rules
         wf = _T.empty(L.mt_packed_conv_window_pair_elems(g.Cout, g.kh), dtype=torch.bfloat16, device=w.device)
@@ -351,6 +374,14 @@ def conv_dgrad(dy, wb, g: ConvGeom, Hin, Win, add_into=None):
         _count()
         return add_into
     dx = empty_act(N, Hin, Win, g.Cin_s, dy.device)
+    if g.rowk_dgrad:
+        L = _lib.lib()
+        scratch = _T.empty(L.mt_conv_rowk_scratch_elems(ctypes.byref(d)), dtype=torch.float32, device=dy.device)
+        with _timed("dgrad", g, N, Hin, Win):
+            check(L.mt_conv2d_dgrad_rowk(ctypes.byref(d), _p(dy), _p(wb), _p(scratch), _p(dx), _stream()),
+                  "conv_dgrad_rowk")
+        _count(2)
+        return dx
     fn = _lib.lib().mt_conv_transpose2d_dgrad if g.transposed else _lib.lib().mt_conv2d_dgrad
     with _timed("dgrad", g, N, Hin, Win):
         check(fn(ctypes.byref(d), _p(dy), _p(wb), _p(dx), _stream()), "conv_dgrad")

@@ -561,6 +561,9 @@ CASES = {
     "conv3x3_s2": lambda: conv_case(2, 64, 128, 64, 64, 3, 2, 1),
     "conv3x3_s2_act_pad": lambda: conv_case(2, 64, 128, 32, 32, 3, 2, 1, act="lrelu", out_pad=1),
     "stem7x7": lambda: conv_case(2, 3, 64, 64, 64, 7, 1, 3, stem=True),
+    # extents that are no multiple of any pixel tile of the rows-in-K data gradient (narrow tiles: the gather
+    # adds more than two tile slots per column)
+    "stem7x7_ragged": lambda: conv_case(3, 3, 64, 60, 44, 7, 1, 3, stem=True),
     "stem4x4_s2": lambda: conv_case(2, 7, 64, 64, 64, 4, 2, 1, stem=True),
     "stem3x3_s2": lambda: conv_case(2, 3, 64, 64, 64, 3, 2, 1, stem=True),
     "c3_generic": lambda: conv_case(2, 3, 64, 32, 32, 3, 2, 1),

@@ -1,0 +1,6 @@
+timeout 600 python -m pytest tests/test_kernels_gpu.py -x -q -k "stem" 2>&1 | tail -5
+for T in 1 0; do echo "MT_DGRAD_ROWK=$T"; MT_DGRAD_ROWK=$T MT_SHAPE=3,64,7,1,262,dgrad timeout 300 python tools/conv_timeline.py 2>&1 | grep "back-to-back"; done
+timeout 900 python -m pytest tests/test_kernels_gpu.py -x -q 2>&1 | tail -3
+for D in 1 0 1 0; do
+MT_DGRAD_ROWK=$D timeout 600 python bench.py --steps 20 --warmup 5 --no-baselines 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('rowk=$D', d['value'], d['ms_per_step'], d['e2e']['value'], d['clocks']['sm_mhz'], d['roofline']['achieved'])"; done
