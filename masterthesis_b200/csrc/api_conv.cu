@@ -102,9 +102,46 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   p.rowk_kw = c.rowk_kw; p.rowk_c = c.rowk_c; p.rowk_win = c.rowk_win; p.rowk_out = c.rowk_out;
   if (p.rowk_kw > 0 && (p.BN != 32 || p.cg != 1 || p.rowk_kw * p.rowk_c > 24)) return -1014;
 
+  // Halo variant (igemm_fwd.cu: igemm_halo_kernel) for narrow stride-1 tap grids: one activation box per
+  // K chunk serves all taps, the weight operand stays resident.  MT_HALO=0 keeps the tap-by-tap kernel.
+  bool halo = false;
+  {
+    static int halo_off = -1;
+    if (halo_off < 0) { const char* e = getenv("MT_HALO"); halo_off = (e && atoi(e) == 0) ? 1 : 0; }
+    const bool unit_steps = (c.kh == 1 || c.step_h == 1 || c.step_h == -1) &&
+                            (c.kw == 1 || c.step_w == 1 || c.step_w == -1);
+    if (!halo_off && !c.window && c.a_mul == 1 && c.a_mul_w <= 1 && unit_steps && p.n_tiles == 1 &&
+        p.rowk_kw == 0 && c.Wt >= 8 && c.Ht >= 16 && igemm_halo_supported(2, p.BN, c.kh, c.kw, p.k_chunks)) {
+      const int tw = cdiv(c.Wt, 8), th = cdiv(c.Ht, 16);
+      // fused statistics: the caller sized its slots for the default tiling (mt_conv_stats_parts)
+      if (tw * th * c.Nt >= 8 && (!c.stats || (p.TN == 1 && tw * th == p.tiles_w * p.tiles_h))) halo = true;
+    }
+  }
+  if (halo) {
+    p.TW = 8; p.TH = 16; p.TN = 1;
+    p.tiles_w = cdiv(c.Wt, 8); p.tiles_h = cdiv(c.Ht, 16); p.tiles_n = c.Nt;
+    p.cg = 2;
+    p.work_items = cdiv(p.tiles_w * p.tiles_h * p.tiles_n, 2);
+    // box origin = the smallest tap offset; taps are walked in increasing offset order, the weight tap index
+    // follows through the (possibly negated) affine map
+    const bool neg_h = c.kh > 1 && c.step_h < 0, neg_w = c.kw > 1 && c.step_w < 0;
+    p.off_h = c.off_h - (neg_h ? c.kh - 1 : 0);
+    p.off_w = c.off_w - (neg_w ? c.kw - 1 : 0);
+    p.w_base = c.w_base + (neg_h ? (c.kh - 1) * c.w_step_r : 0) + (neg_w ? (c.kw - 1) * c.w_step_s : 0);
+    p.w_step_r = neg_h ? -c.w_step_r : c.w_step_r;
+    p.w_step_s = neg_w ? -c.w_step_s : c.w_step_s;
+  }
+
   CUtensorMap tmA, tmB;
   int rc;
-  if (!c.window) {
+  if (halo) {
+    uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
+    uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
+                       (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
+    uint32_t box[4] = {64, (uint32_t)(8 + c.kw - 1), (uint32_t)(16 + c.kh - 1), 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    rc = make_tmap(&tmA, c.a, 4, dims, str, box, es);
+  } else if (!c.window) {
     uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
     uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
                        (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
@@ -151,7 +188,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     p.stats = c.stats; p.n_stat_c = c.n_store;
     p.stat_parts = c.stat_parts; p.stat_part0 = c.stat_part0;
   }
-  return launch_igemm(tmA, tmB, tmC, p, stream);
+  return halo ? launch_igemm_halo(tmA, tmB, tmC, p, stream) : launch_igemm(tmA, tmB, tmC, p, stream);
 }
 
 // ---- rows-in-K data gradient of a many-tap stride-1 conv into <= 4 channels (mt_conv2d_dgrad_rowk)

@@ -73,6 +73,9 @@ int make_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
 
 int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                  const IgemmParams& p, cudaStream_t stream);
+int igemm_halo_supported(int cg, int BN, int kh, int kw, int k_chunks);
+int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                      const IgemmParams& p, cudaStream_t stream);
 int launch_wgrad(const CUtensorMap& tmA, const CUtensorMap& tmB, const WgradParams& p,
                  cudaStream_t stream);
 

@@ -228,6 +228,105 @@ __device__ __forceinline__ void mma_round(MmaCtx& c, int kb) {
   }
 }
 
+// The epilogue role (warps 2-9) of the implicit-GEMM kernels, shared by igemm_conv_kernel and
+// igemm_halo_kernel: `stage_area` = shared address of the two 16 KiB staging boxes.
+template <int CG, int BN>
+__device__ __forceinline__ void epilogue_role(const IgemmParams& p, const CUtensorMap* tmC_p, uint8_t* smem_raw,
+                                              uint32_t stage_area, uint64_t* bar_tfull, uint64_t* bar_tempty,
+                                              uint32_t tmem_base, int cluster_id, int n_clusters, int rank,
+                                              int warp, int lane, bool stamp, long long T0) {
+  constexpr int ACC_COLS = BN < 32 ? 32 : BN;
+  const CUtensorMap& tmC = *tmC_p;
+  {
+  // ========== epilogue: TMEM -> regs -> bias/act -> bf16 -> smem box -> TMA store ==========
+  // Two teams of four warps (one warp per TMEM lane quadrant); team g takes the 64-column slabs
+  // g, g+2, ... of the tile and owns one 16 KiB staging box behind the operand ring.  Tiles of a
+  // single slab (BN <= 64) alternate between the teams instead (team = accumulator stage), so
+  // that both stay busy where the epilogue, not the MMA, is the limiter.
+  constexpr int SW = BN < 64 ? BN : 64;
+  constexpr int NSLAB = BN / SW;
+  const int q = warp & 3;            // TMEM lane quadrant this warp may access
+  const int grp = (warp - 2) >> 2;   // team
+  const int m = q * 32 + lane;       // accumulator row = pixel of the tile
+  const int tt = ((warp - 2) & 3) * 32 + lane;
+  const uint32_t stage_buf = stage_area + grp * (BM * 128);
+  const uint32_t stage_row = stage_buf + m * (SW * 2);
+  const int w_i = m % p.TW, h_i = (m / p.TW) % p.TH, n_i = m / (p.TW * p.TH);
+  const bool hb = p.n_bias > 0;
+  int tile_i = 0;
+  for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
+    const int acc = tile_i & 1;
+    if (NSLAB == 1 && acc != grp) continue;
+    const WorkCoord wc = decode_work<CG>(p, item, rank);
+    const uint32_t acc_ph = (tile_i >> 1) & 1;
+    const bool row_ok = (wc.w0 + w_i < p.Wt) && (wc.h0 + h_i < p.Ht) && (wc.n0 + n_i < p.Nt);
+    mbar_wait(smem_u32(&bar_tfull[acc]), acc_ph);
+    tc_fence_after();
+    if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
+    const uint32_t tmem_row = tmem_base + acc * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
+    if constexpr (BN == 32 && CG == 1) {
+      if (p.rowk_kw > 0) {
+        named_bar_sync(1 + grp, 128);       // the team has finished reading Z of its previous tile
+        epilogue_rowk(p, tmem_row, reinterpret_cast<float*>(smem_raw + (stage_buf - smem_u32(smem_raw))), m, tt,
+                      1 + grp, smem_u32(&bar_tempty[acc]), wc, wc.w0 / p.TW);
+        continue;
+      }
+    }
+    bool released = false;
+    for (int sl = NSLAB == 1 ? 0 : grp; sl < NSLAB; sl += 2) {
+      const int c_glob = wc.n_tile * BN + sl * SW;
+      if (c_glob >= p.n_store) break;                       // team-uniform
+      if (stamp && warp == 2 && tile_i == 2) g_ts[40] = clock64() - T0;
+      if (tt == 0) bulk_wait_read0();                       // previous store has left the box
+      named_bar_sync(1 + grp, 128);
+      if (stamp && warp == 2 && tile_i == 2) g_ts[41] = clock64() - T0;
+#define MT_EPI(A, B) epilogue_slab<A, B, SW>(p, tmem_row + sl * SW, stage_row, m & 7, row_ok, c_glob)
+      switch (p.act) {
+        case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
+        case ACT_LRELU: if (hb) MT_EPI(ACT_LRELU, true); else MT_EPI(ACT_LRELU, false); break;
+        case ACT_TANH:  if (hb) MT_EPI(ACT_TANH, true);  else MT_EPI(ACT_TANH, false);  break;
+        default:        if (hb) MT_EPI(ACT_NONE, true);  else MT_EPI(ACT_NONE, false);  break;
+      }
+#undef MT_EPI
+      if (stamp && warp == 2 && tile_i == 2) g_ts[42] = clock64() - T0;
+      if (sl + 2 >= NSLAB || c_glob + 2 * SW >= p.n_store) {
+        // last TMEM read of this warp for the tile: hand the accumulator back right away
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (CG == 2) {
+            if (p.dbg & 64) mbar_arrive_cluster_gpu_fence(smem_u32(&bar_tempty[acc]), 0);
+            else mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
+          } else mbar_arrive(smem_u32(&bar_tempty[acc]));
+        }
+        released = true;
+      }
+      fence_proxy_async();
+      named_bar_sync(1 + grp, 128);
+      if (stamp && warp == 2 && tile_i == 2) g_ts[43] = clock64() - T0;
+      if (tt == 0) {
+        if (p.accumulate) tma_reduce_add_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
+        else tma_store_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
+        bulk_commit();
+      }
+      if (stamp && warp == 2 && tile_i == 2) g_ts[44] = clock64() - T0;
+      if (SW == 64 && p.stats != nullptr && wc.n0 < p.Nt) slab_stats(p, stage_buf, tt, c_glob, wc.n0, wc.part);
+      if (stamp && warp == 2 && tile_i == 2) g_ts[45] = clock64() - T0;
+    }
+    if (!released) {                 // a team without slabs in this tile
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
+        else mbar_arrive(smem_u32(&bar_tempty[acc]));
+      }
+    }
+    if (stamp && warp == 2 && tile_i < 8) g_ts[25 + 2 * tile_i] = clock64() - T0;
+  }
+  if (tt == 0) bulk_wait0();         // the stores are complete before the CTA retires
+  }
+}
+
 template <int CG, int BN, int S>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -360,98 +459,214 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     __syncwarp();
   } else {
-    // ========== epilogue: TMEM -> regs -> bias/act -> bf16 -> smem box -> TMA store ==========
-    // Two teams of four warps (one warp per TMEM lane quadrant); team g takes the 64-column slabs
-    // g, g+2, ... of the tile and owns one 16 KiB staging box behind the operand ring.  Tiles of a
-    // single slab (BN <= 64) alternate between the teams instead (team = accumulator stage), so
-    // that both stay busy where the epilogue, not the MMA, is the limiter.
-    constexpr int SW = BN < 64 ? BN : 64;
-    constexpr int NSLAB = BN / SW;
-    const int q = warp & 3;            // TMEM lane quadrant this warp may access
-    const int grp = (warp - 2) >> 2;   // team
-    const int m = q * 32 + lane;       // accumulator row = pixel of the tile
-    const int tt = ((warp - 2) & 3) * 32 + lane;
-    const uint32_t stage_buf = smem_base + S * STAGE_BYTES + grp * (BM * 128);
-    const uint32_t stage_row = stage_buf + m * (SW * 2);
-    const int w_i = m % p.TW, h_i = (m / p.TW) % p.TH, n_i = m / (p.TW * p.TH);
-    const bool hb = p.n_bias > 0;
-    int tile_i = 0;
-    for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
-      const int acc = tile_i & 1;
-      if (NSLAB == 1 && acc != grp) continue;
-      const WorkCoord wc = decode_work<CG>(p, item, rank);
-      const uint32_t acc_ph = (tile_i >> 1) & 1;
-      const bool row_ok = (wc.w0 + w_i < p.Wt) && (wc.h0 + h_i < p.Ht) && (wc.n0 + n_i < p.Nt);
-      mbar_wait(smem_u32(&bar_tfull[acc]), acc_ph);
-      tc_fence_after();
-      if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
-      const uint32_t tmem_row = tmem_base + acc * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
-      if constexpr (BN == 32 && CG == 1) {
-        if (p.rowk_kw > 0) {
-          named_bar_sync(1 + grp, 128);       // the team has finished reading Z of its previous tile
-          epilogue_rowk(p, tmem_row, reinterpret_cast<float*>(smem_raw + (stage_buf - smem_u32(smem_raw))), m, tt,
-                        1 + grp, smem_u32(&bar_tempty[acc]), wc, wc.w0 / p.TW);
-          continue;
-        }
-      }
-      bool released = false;
-      for (int sl = NSLAB == 1 ? 0 : grp; sl < NSLAB; sl += 2) {
-        const int c_glob = wc.n_tile * BN + sl * SW;
-        if (c_glob >= p.n_store) break;                       // team-uniform
-        if (stamp && warp == 2 && tile_i == 2) g_ts[40] = clock64() - T0;
-        if (tt == 0) bulk_wait_read0();                       // previous store has left the box
-        named_bar_sync(1 + grp, 128);
-        if (stamp && warp == 2 && tile_i == 2) g_ts[41] = clock64() - T0;
-#define MT_EPI(A, B) epilogue_slab<A, B, SW>(p, tmem_row + sl * SW, stage_row, m & 7, row_ok, c_glob)
-        switch (p.act) {
-          case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
-          case ACT_LRELU: if (hb) MT_EPI(ACT_LRELU, true); else MT_EPI(ACT_LRELU, false); break;
-          case ACT_TANH:  if (hb) MT_EPI(ACT_TANH, true);  else MT_EPI(ACT_TANH, false);  break;
-          default:        if (hb) MT_EPI(ACT_NONE, true);  else MT_EPI(ACT_NONE, false);  break;
-        }
-#undef MT_EPI
-        if (stamp && warp == 2 && tile_i == 2) g_ts[42] = clock64() - T0;
-        if (sl + 2 >= NSLAB || c_glob + 2 * SW >= p.n_store) {
-          // last TMEM read of this warp for the tile: hand the accumulator back right away
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) {
-            if (CG == 2) {
-              if (p.dbg & 64) mbar_arrive_cluster_gpu_fence(smem_u32(&bar_tempty[acc]), 0);
-              else mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
-            } else mbar_arrive(smem_u32(&bar_tempty[acc]));
-          }
-          released = true;
-        }
-        fence_proxy_async();
-        named_bar_sync(1 + grp, 128);
-        if (stamp && warp == 2 && tile_i == 2) g_ts[43] = clock64() - T0;
-        if (tt == 0) {
-          if (p.accumulate) tma_reduce_add_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
-          else tma_store_4d(&tmC, stage_buf, c_glob, wc.w0, wc.h0, wc.n0);
-          bulk_commit();
-        }
-        if (stamp && warp == 2 && tile_i == 2) g_ts[44] = clock64() - T0;
-        if (SW == 64 && p.stats != nullptr && wc.n0 < p.Nt) slab_stats(p, stage_buf, tt, c_glob, wc.n0, wc.part);
-        if (stamp && warp == 2 && tile_i == 2) g_ts[45] = clock64() - T0;
-      }
-      if (!released) {                 // a team without slabs in this tile
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          if (CG == 2) mbar_arrive_cluster(smem_u32(&bar_tempty[acc]), 0);
-          else mbar_arrive(smem_u32(&bar_tempty[acc]));
-        }
-      }
-      if (stamp && warp == 2 && tile_i < 8) g_ts[25 + 2 * tile_i] = clock64() - T0;
-    }
-    if (tt == 0) bulk_wait0();         // the stores are complete before the CTA retires
+    epilogue_role<CG, BN>(p, &tmC, smem_raw, smem_base + S * STAGE_BYTES, bar_tfull, bar_tempty, tmem_base, cluster_id,
+                          n_clusters, rank, warp, lane, stamp, T0);
   }
 
   // ---- teardown
   tc_fence_before();
   __syncthreads();
   if (CG == 2) cluster_sync_all();     // the leader's MMAs read the peer's smem / write its TMEM
+  if (warp == 1) {
+    if (CG == 2) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+  if (stamp && warp == 0) g_ts[0] = clock64() - T0;
+}
+
+// ===================================================================================================
+// Halo variant for narrow stride-1 tap grids (3x3, 2x2, 1x2 shifts over the same pixel grid).
+// The layers it serves (Cout tile of 128 columns, K <= 128) are bound by the L2 -> SM operand stream of the
+// kernel above: one 16 KiB A tile and one weight tile per filter tap.  Here
+//   * ONE activation box of (16 + KH - 1) x (8 + KW - 1) pixels x 64 channels is loaded per 64-channel chunk
+//     of K and serves every tap: the pixel tile is 8 wide and 16 high, so the 8-row core matrices of the
+//     K-major SWIZZLE_128B operand are 8 consecutive pixels of one image row and the stride between them
+//     (descriptor SBO) is the box pitch; tap (r, s) starts (r * pitch + s) rows into the box.  The swizzle of
+//     tcgen05.mma operands is a function of the shared-memory ADDRESS (tools/micro/halo_desc.cu: any 128-byte
+//     row offset and any SBO read back what TMA wrote), so no re-layout is needed;
+//   * the whole weight operand of the CTA (KC * KH * KW tiles) is loaded once and stays resident.
+// Per 128-pixel tile and K chunk the SM then receives 23 KiB (3x3) instead of 9 x 24 KiB.
+// Everything else (work items, CTA pairs, TMEM double buffer, epilogue) is the kernel above.
+static constexpr int HALO_TW = 8, HALO_TH = 16, HALO_SA = 4;
+
+template <int CG, int BN, int KH, int KW, int KC>
+struct HaloCfg {
+  static constexpr int PW = HALO_TW + KW - 1, PH = HALO_TH + KH - 1, T = KH * KW;
+  static constexpr uint32_t A_BOX = PH * PW * 128;                       // bytes one TMA box delivers
+  static constexpr uint32_t A_STAGE = (A_BOX + 1023u) & ~1023u;
+  static constexpr int B_ROWS = BN / CG;
+  static constexpr uint32_t B_TILE = B_ROWS * 128;
+  static constexpr uint32_t B_OFF = HALO_SA * A_STAGE;
+  static constexpr uint32_t B_BYTES = KC * T * B_TILE;
+  static constexpr uint32_t EPI_OFF = B_OFF + B_BYTES;
+  static constexpr size_t kSmem = (size_t)EPI_OFF + 2 * BM * 128 + 1024;
+  static constexpr int GROUPS = HALO_SA / KC;                            // work items per trip round the A ring
+};
+
+// MMAs of one work item: KC boxes (ring stages STAGE0 ..), KH*KW taps each, into accumulator ACC_OFF
+template <int CG, int BN, int KH, int KW, int KC, int STAGE0, int ACC_OFF>
+__device__ __forceinline__ void halo_mma_item(uint32_t bar_afull, uint32_t bar_aempty, uint32_t tmem_base,
+                                              uint32_t& phase_bits) {
+  using C = HaloCfg<CG, BN, KH, KW, KC>;
+  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
+                             (static_cast<uint32_t>((BM * CG) >> 4) << 24);
+#pragma unroll
+  for (int kc = 0; kc < KC; ++kc) {
+    const int stage = STAGE0 + kc;
+    mbar_wait(bar_afull + 8 * stage, (phase_bits >> stage) & 1);
+    phase_bits ^= 1u << stage;
+    tc_fence_after();
+#pragma unroll
+    for (int tap = 0; tap < C::T; ++tap) {
+#pragma unroll
+      for (int k = 0; k < BK / 16; ++k) {
+        const uint32_t a_off = SMEM_RING + (STAGE0 + kc) * C::A_STAGE + ((tap / KW) * C::PW + (tap % KW)) * 128 + k * 32;
+        const uint32_t b_off = SMEM_RING + C::B_OFF + (kc * C::T + tap) * C::B_TILE + k * 32;
+        const uint64_t ad = const_smem_desc(a_off, 16, C::PW * 128);
+        const uint64_t bd = const_smem_desc(b_off, 16, 1024);
+        const uint32_t acc = (kc | tap | k) != 0 ? 1u : 0u;
+        if (CG == 2) umma_bf16_2sm(tmem_base + ACC_OFF, ad, bd, IDESC, acc);
+        else umma_bf16(tmem_base + ACC_OFF, ad, bd, IDESC, acc);
+      }
+    }
+    if (CG == 2) umma_commit_2sm(bar_aempty + 8 * stage);
+    else umma_commit(bar_aempty + 8 * stage);
+  }
+}
+template <int CG, int BN, int KH, int KW, int KC, int G>
+__device__ __forceinline__ void halo_mma_dispatch(int grp, int acc, uint32_t bar_afull, uint32_t bar_aempty,
+                                                  uint32_t tmem_base, uint32_t& phase_bits) {
+  constexpr int ACC_COLS = BN < 32 ? 32 : BN;
+  if constexpr (G < HaloCfg<CG, BN, KH, KW, KC>::GROUPS) {
+    if (grp == G) {
+      if (acc == 0) halo_mma_item<CG, BN, KH, KW, KC, G * KC, 0>(bar_afull, bar_aempty, tmem_base, phase_bits);
+      else halo_mma_item<CG, BN, KH, KW, KC, G * KC, ACC_COLS>(bar_afull, bar_aempty, tmem_base, phase_bits);
+    } else {
+      halo_mma_dispatch<CG, BN, KH, KW, KC, G + 1>(grp, acc, bar_afull, bar_aempty, tmem_base, phase_bits);
+    }
+  }
+}
+
+template <int CG, int BN, int KH, int KW, int KC>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+igemm_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ CUtensorMap tmC, const IgemmParams p) {
+  using C = HaloCfg<CG, BN, KH, KW, KC>;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_afull[HALO_SA];
+  __shared__ __align__(8) uint64_t bar_aempty[HALO_SA];
+  __shared__ __align__(8) uint64_t bar_b;
+  __shared__ __align__(8) uint64_t bar_tfull[2];
+  __shared__ __align__(8) uint64_t bar_tempty[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
+  const int cluster_id = blockIdx.x / CG;
+  const int n_clusters = gridDim.x / CG;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  if ((smem_base & 0x3FFFFu) != SMEM_RING) {            // const_smem_desc() relies on this offset
+    if (threadIdx.x == 0) g_ts[63] = -(long long)(smem_base & 0x3FFFFu);
+    return;
+  }
+  const bool stamp = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
+  const long long T0 = clock64();
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmC);
+    for (int i = 0; i < HALO_SA; ++i) {
+      mbar_init(smem_u32(&bar_afull[i]), 1);
+      mbar_init(smem_u32(&bar_aempty[i]), 1);
+    }
+    mbar_init(smem_u32(&bar_b), 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&bar_tfull[i]), 1);
+      mbar_init(smem_u32(&bar_tempty[i]), BN <= 64 ? CG * (NUM_EPI_WARPS / 2) : CG * NUM_EPI_WARPS);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    if (CG == 2) tmem_alloc_2sm(smem_u32(&tmem_base_slot), p.tmem_cols);
+    else tmem_alloc(smem_u32(&tmem_base_slot), p.tmem_cols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (CG == 2) cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  griddep_wait();
+  griddep_launch();
+  if (stamp && warp == 0) g_ts[7] = clock64() - T0;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      // the CTA's weight operand, once: tile (kc, tap) = rows [rank * B_ROWS, +B_ROWS) of tap p.w_base + r*.. + s*..
+      {
+        const uint32_t bb = CG == 2 ? (smem_u32(&bar_b) & PEER_BIT_MASK) : smem_u32(&bar_b);
+        if (CG == 1 || rank == 0) mbar_expect_tx(bb, CG * C::B_BYTES);
+        for (int kc = 0; kc < KC; ++kc)
+          for (int tap = 0; tap < C::T; ++tap) {
+            const int widx = p.w_base + (tap / KW) * p.w_step_r + (tap % KW) * p.w_step_s;
+            const uint32_t dst = smem_base + C::B_OFF + (kc * C::T + tap) * C::B_TILE;
+            if (CG == 2) tma_load_3d_2sm(dst, &tmB, bb, kc * BK, rank * C::B_ROWS, widx);
+            else tma_load_3d(dst, &tmB, bb, kc * BK, 0, widx);
+          }
+      }
+      uint32_t phase_bits = 0;
+      int tile_i = 0;
+      for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
+        const WorkCoord wc = decode_work<CG>(p, item, rank);
+        const int stage0 = (tile_i % C::GROUPS) * KC;
+        for (int kc = 0; kc < KC; ++kc) {
+          const int stage = stage0 + kc;
+          mbar_wait(smem_u32(&bar_aempty[stage]), ((phase_bits >> stage) & 1) ^ 1);
+          phase_bits ^= 1u << stage;
+          const uint32_t dst = smem_base + stage * C::A_STAGE;
+          if (CG == 2) {
+            const uint32_t full = smem_u32(&bar_afull[stage]) & PEER_BIT_MASK;
+            if (rank == 0) mbar_expect_tx(full, 2 * C::A_BOX);
+            tma_load_4d_2sm(dst, &tmA, full, kc * BK, wc.w0 + p.off_w, wc.h0 + p.off_h, wc.n0);
+          } else {
+            const uint32_t full = smem_u32(&bar_afull[stage]);
+            mbar_expect_tx(full, C::A_BOX);
+            tma_load_4d(dst, &tmA, full, kc * BK, wc.w0 + p.off_w, wc.h0 + p.off_h, wc.n0);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================= MMA issuer (one thread of the leader CTA) =================
+    if (rank == 0 && lane == 0) {
+      uint32_t phase_bits = 0;
+      mbar_wait(smem_u32(&bar_b), 0);
+      tc_fence_after();
+      int tile_i = 0;
+      for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
+        const int acc = tile_i & 1;
+        mbar_wait(smem_u32(&bar_tempty[acc]), ((tile_i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        if (stamp && tile_i < 8) g_ts[8 + 2 * tile_i] = clock64() - T0;
+        halo_mma_dispatch<CG, BN, KH, KW, KC, 0>(tile_i % C::GROUPS, acc, smem_u32(&bar_afull[0]),
+                                                 smem_u32(&bar_aempty[0]), tmem_base, phase_bits);
+        if (CG == 2) umma_commit_2sm(smem_u32(&bar_tfull[acc]));
+        else umma_commit(smem_u32(&bar_tfull[acc]));
+        if (stamp && tile_i < 8) g_ts[9 + 2 * tile_i] = clock64() - T0;
+      }
+    }
+    __syncwarp();
+  } else {
+    epilogue_role<CG, BN>(p, &tmC, smem_raw, smem_base + C::EPI_OFF, bar_tfull, bar_tempty, tmem_base, cluster_id,
+                          n_clusters, rank, warp, lane, stamp, T0);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (CG == 2) cluster_sync_all();
   if (warp == 1) {
     if (CG == 2) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
     else tmem_dealloc(tmem_base, p.tmem_cols);
@@ -499,6 +714,67 @@ static cudaError_t launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, co
   if (pdl < 0) { const char* e = getenv("MT_PDL"); pdl = e ? (atoi(e) != 0) : 1; }
   cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
   return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
+}
+
+template <int CG, int BN, int KH, int KW, int KC>
+static cudaError_t launch_halo_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                                   const IgemmParams& p, cudaStream_t stream) {
+  using C = HaloCfg<CG, BN, KH, KW, KC>;
+  static_assert(C::kSmem <= 227 * 1024, "halo configuration does not fit in shared memory");
+  static_assert(HALO_SA % KC == 0, "the A ring holds a whole number of work items");
+  auto* kern = igemm_halo_kernel<CG, BN, KH, KW, KC>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  int clusters = g_num_sms / CG;
+  if (clusters > p.work_items) clusters = p.work_items;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(clusters * CG), 1, 1);
+  cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = C::kSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  static int pdl = -1;
+  if (pdl < 0) { const char* e = getenv("MT_PDL"); pdl = e ? (atoi(e) != 0) : 1; }
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
+}
+
+// 1 if launch_igemm_halo has an instantiation for this shape (the host checks the other conditions)
+int igemm_halo_supported(int cg, int BN, int kh, int kw, int k_chunks) {
+  if (cg != 2 || BN != 128) return 0;
+  return (kh == 3 && kw == 3 && k_chunks == 1) || (kh == 2 && kw == 2 && k_chunks == 2) ||
+         (kh == 1 && kw == 2 && k_chunks == 2);
+}
+
+int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                      const IgemmParams& p_in, cudaStream_t stream) {
+  IgemmParams p = p_in;
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("MT_IGEMM_DBG"); dbg = e ? atoi(e) : 0; }
+  p.dbg = dbg;
+  if (p.work_items <= 0 || p.TW != HALO_TW || p.TH != HALO_TH || p.TN != 1) return -1000;
+  if (!igemm_halo_supported(p.cg, p.BN, p.kh, p.kw, p.k_chunks)) return -1010;
+  cudaError_t e;
+  if (p.kh == 3) e = launch_halo_cfg<2, 128, 3, 3, 1>(tmA, tmB, tmC, p, stream);
+  else if (p.kh == 2) e = launch_halo_cfg<2, 128, 2, 2, 2>(tmA, tmB, tmC, p, stream);
+  else e = launch_halo_cfg<2, 128, 1, 2, 2>(tmA, tmB, tmC, p, stream);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : -(int)e;
 }
 
 int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
