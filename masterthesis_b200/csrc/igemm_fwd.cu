@@ -487,7 +487,7 @@ igemm_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 //   * the whole weight operand of the CTA (KC * KH * KW tiles) is loaded once and stays resident.
 // Per 128-pixel tile and K chunk the SM then receives 23 KiB (3x3) instead of 9 x 24 KiB.
 // Everything else (work items, CTA pairs, TMEM double buffer, epilogue) is the kernel above.
-static constexpr int HALO_TW = 8, HALO_TH = 16, HALO_SA = 4;
+static constexpr int HALO_TW = 8, HALO_TH = 16;
 
 template <int CG, int BN, int KH, int KW, int KC>
 struct HaloCfg {
@@ -496,11 +496,15 @@ struct HaloCfg {
   static constexpr uint32_t A_STAGE = (A_BOX + 1023u) & ~1023u;
   static constexpr int B_ROWS = BN / CG;
   static constexpr uint32_t B_TILE = B_ROWS * 128;
-  static constexpr uint32_t B_OFF = HALO_SA * A_STAGE;
   static constexpr uint32_t B_BYTES = KC * T * B_TILE;
+  // A ring: as many boxes as fit beside the resident weights and the staging boxes (227 KiB per CTA, minus the
+  // alignment slack and the static / reserved 2 KiB), at most 4, a whole number of work items (multiple of KC)
+  static constexpr int FIT = (int)((227u * 1024 - 1024 - 2048 - 2 * BM * 128 - B_BYTES) / A_STAGE);
+  static constexpr int SA = ((FIT > 4 ? 4 : FIT) / KC) * KC;
+  static constexpr uint32_t B_OFF = SA * A_STAGE;
   static constexpr uint32_t EPI_OFF = B_OFF + B_BYTES;
   static constexpr size_t kSmem = (size_t)EPI_OFF + 2 * BM * 128 + 1024;
-  static constexpr int GROUPS = HALO_SA / KC;                            // work items per trip round the A ring
+  static constexpr int GROUPS = SA / KC;                            // work items per trip round the A ring
 };
 
 // MMAs of one work item: KC boxes (ring stages STAGE0 ..), KH*KW taps each, into accumulator ACC_OFF
@@ -553,8 +557,8 @@ igemm_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                   const __grid_constant__ CUtensorMap tmC, const IgemmParams p) {
   using C = HaloCfg<CG, BN, KH, KW, KC>;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_afull[HALO_SA];
-  __shared__ __align__(8) uint64_t bar_aempty[HALO_SA];
+  __shared__ __align__(8) uint64_t bar_afull[C::SA];
+  __shared__ __align__(8) uint64_t bar_aempty[C::SA];
   __shared__ __align__(8) uint64_t bar_b;
   __shared__ __align__(8) uint64_t bar_tfull[2];
   __shared__ __align__(8) uint64_t bar_tempty[2];
@@ -577,7 +581,7 @@ igemm_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmC);
-    for (int i = 0; i < HALO_SA; ++i) {
+    for (int i = 0; i < C::SA; ++i) {
       mbar_init(smem_u32(&bar_afull[i]), 1);
       mbar_init(smem_u32(&bar_aempty[i]), 1);
     }
@@ -721,7 +725,7 @@ static cudaError_t launch_halo_cfg(const CUtensorMap& tmA, const CUtensorMap& tm
                                    const IgemmParams& p, cudaStream_t stream) {
   using C = HaloCfg<CG, BN, KH, KW, KC>;
   static_assert(C::kSmem <= 227 * 1024, "halo configuration does not fit in shared memory");
-  static_assert(HALO_SA % KC == 0, "the A ring holds a whole number of work items");
+  static_assert(C::SA >= KC && C::SA % KC == 0, "the A ring holds a whole number of work items");
   auto* kern = igemm_halo_kernel<CG, BN, KH, KW, KC>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -750,9 +754,13 @@ static cudaError_t launch_halo_cfg(const CUtensorMap& tmA, const CUtensorMap& tm
 
 // 1 if launch_igemm_halo has an instantiation for this shape (the host checks the other conditions)
 int igemm_halo_supported(int cg, int BN, int kh, int kw, int k_chunks) {
-  if (cg != 2 || BN != 128) return 0;
-  return (kh == 3 && kw == 3 && k_chunks == 1) || (kh == 2 && kw == 2 && k_chunks == 2) ||
-         (kh == 1 && kw == 2 && k_chunks == 2);
+  if (cg != 2) return 0;
+  switch (BN * 1000 + kh * 100 + kw * 10 + k_chunks) {
+    case 128331: case 128332: case 128222: case 128122:
+    case 64331: case 64332:
+      return 1;
+  }
+  return 0;
 }
 
 int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
@@ -770,9 +778,15 @@ int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUte
   if (p.work_items <= 0 || p.TW != HALO_TW || p.TH != HALO_TH || p.TN != 1) return -1000;
   if (!igemm_halo_supported(p.cg, p.BN, p.kh, p.kw, p.k_chunks)) return -1010;
   cudaError_t e;
-  if (p.kh == 3) e = launch_halo_cfg<2, 128, 3, 3, 1>(tmA, tmB, tmC, p, stream);
-  else if (p.kh == 2) e = launch_halo_cfg<2, 128, 2, 2, 2>(tmA, tmB, tmC, p, stream);
-  else e = launch_halo_cfg<2, 128, 1, 2, 2>(tmA, tmB, tmC, p, stream);
+  switch (p.BN * 1000 + p.kh * 100 + p.kw * 10 + p.k_chunks) {
+    case 128331: e = launch_halo_cfg<2, 128, 3, 3, 1>(tmA, tmB, tmC, p, stream); break;
+    case 128332: e = launch_halo_cfg<2, 128, 3, 3, 2>(tmA, tmB, tmC, p, stream); break;
+    case 128222: e = launch_halo_cfg<2, 128, 2, 2, 2>(tmA, tmB, tmC, p, stream); break;
+    case 128122: e = launch_halo_cfg<2, 128, 1, 2, 2>(tmA, tmB, tmC, p, stream); break;
+    case 64331: e = launch_halo_cfg<2, 64, 3, 3, 1>(tmA, tmB, tmC, p, stream); break;
+    case 64332: e = launch_halo_cfg<2, 64, 3, 3, 2>(tmA, tmB, tmC, p, stream); break;
+    default: return -1010;
+  }
   if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? 0 : -(int)e;
 }

@@ -543,6 +543,13 @@ CASES = {
     "dis_l5_n32": lambda: conv_case(32, 512, 1024, 16, 16, 3, 2, 1),
     "dis_l6_n32": lambda: conv_case(32, 1024, 1024, 8, 8, 3, 2, 1),
     "es_conv_n16": lambda: conv_case(16, 64, 128, 128, 128, 3, 1, 1),
+    # the other 3x3 stride-1 convs of the style encoder's DownResnetBlocks (blocks.py:108-111): halo kernel with
+    # 64-column CTA pairs / two K chunks; and extents that are no multiple of its 8 x 16 pixel tile
+    "es_conv64_n16": lambda: conv_case(16, 64, 64, 128, 128, 3, 1, 1),
+    "es_conv128_n16": lambda: conv_case(16, 128, 128, 64, 64, 3, 1, 1),
+    "halo_ragged_64": lambda: conv_case(3, 64, 64, 36, 20, 3, 1, 1),
+    "halo_ragged_128": lambda: conv_case(3, 128, 128, 20, 44, 3, 1, 1, act="relu"),
+    "halo_ragged_64_128": lambda: conv_case(2, 64, 128, 52, 28, 3, 1, 1),
     "adain_res_n32": lambda: norm_case("adain", 32, 256, 64, 64, None, residual=True),
     "in_relu_n16": lambda: norm_case("instance", 16, 256, 64, 64, "relu"),
     "ln_relu_n32": lambda: norm_case("layer", 32, 64, 256, 256, "relu"),

@@ -35,6 +35,10 @@ CLASSES = [
     ("down 3x3 s2 128->256 @128->64", "fwd", 128, 256, 128, 128, 3, 2, 1, False, False),
     ("down 3x3 s2 128->256 @128->64", "dgrad", 128, 256, 128, 128, 3, 2, 1, False, False),
     ("down 3x3 s2 128->256 @128->64", "wgrad", 128, 256, 128, 128, 3, 2, 1, False, False),
+    ("Es 3x3 64->64 @128", "fwd", 64, 64, 128, 128, 3, 1, 1, False, False),
+    ("Es 3x3 64->64 @128", "dgrad", 64, 64, 128, 128, 3, 1, 1, False, False),
+    ("Es 3x3 128->128 @64", "fwd", 128, 128, 64, 64, 3, 1, 1, False, False),
+    ("Es 3x3 128->128 @64", "dgrad", 128, 128, 64, 64, 3, 1, 1, False, False),
     ("stem 7x7 3->64 @256", "fwd", 3, 64, 256, 256, 7, 1, 3, True, False),
     ("stem 7x7 3->64 @256", "dgrad", 3, 64, 256, 256, 7, 1, 3, True, False),
     ("stem 7x7 3->64 @256", "wgrad", 3, 64, 256, 256, 7, 1, 3, True, False),

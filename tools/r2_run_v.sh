@@ -1,5 +1,5 @@
 timeout 900 python -m pytest tests/test_kernels_gpu.py -x -q 2>&1 | tail -5
-for C in 1 0; do echo "MT_HALO=$C"; MT_HALO=$C timeout 600 python tools/ncu_conv_classes.py 2>&1 | grep -v wgrad | grep "Es 3x3\|convT 3x3 s2 128\|down 3x3 s2 64"; done
+for C in 1 0; do echo "MT_HALO=$C"; MT_HALO=$C timeout 600 python tools/ncu_conv_classes.py 2>&1 | grep -v wgrad | grep "Es 3x3"; done
 for C in 1 0 1 0; do
 MT_HALO=$C timeout 600 python bench.py --steps 20 --warmup 5 --no-baselines 2>/dev/null | python -c "
 import json,sys; d=json.loads(sys.stdin.read()); print('halo=$C', d['value'], d['ms_per_step'], d['e2e']['value'], d['clocks']['sm_mhz'], d['roofline']['achieved'])"; done
