@@ -35,6 +35,9 @@ static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   static int force_taps = -1;
   if (force_taps < 0) { const char* e = getenv("MT_WGRAD_TAPS"); force_taps = e ? atoi(e) : 0; }
   p.tap_group = (!c.window && p.kh * p.kw == 9 && p.BN <= 128 && force_taps != 1) ? 3 : 1;
+  // 7x7 row-window stems (taps = filter rows, 64-wide windows): four rows per work item (134 -> 118 us; the
+  // 4-row stems would be left with a single group and 148 split-K slabs: 38 -> 46 us, not used there)
+  if (c.window && p.BN == 64 && p.kh * p.kw >= 6 && force_taps != 1) p.tap_group = 4;
   p.tap_groups = cdiv(p.kh * p.kw, p.tap_group);
   const int total_kt = p.tiles_w * p.tiles_h * p.tiles_n;
   const int items = p.tap_groups * p.m_tiles * p.n_tiles;

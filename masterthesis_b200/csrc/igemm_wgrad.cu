@@ -282,6 +282,7 @@ int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradPara
     case 32128: e = launch_wgrad_cfg<2, 128, 3>(tmP, tmQ, p, stream); break;
     case 31128: e = launch_wgrad_cfg<1, 128, 3>(tmP, tmQ, p, stream); break;
     case 31064: e = launch_wgrad_cfg<1, 64, 3>(tmP, tmQ, p, stream); break;
+    case 41064: e = launch_wgrad_cfg<1, 64, 4>(tmP, tmQ, p, stream); break;
     default: return -1010;
   }
   if (e != cudaSuccess) return -(int)e;
