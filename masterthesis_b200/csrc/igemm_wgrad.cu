@@ -29,7 +29,7 @@ __device__ __forceinline__ void st_v4(float* addr, float a, float b, float c, fl
 // with it every shared-memory descriptor is a constant (MMA issue-rate rule, see igemm_fwd.cu).
 struct WgCtx {
   uint32_t bar_full, bar_empty, smem_base, tmem_base, phase_bits;
-  int iters, kt_begin, m_tile, n_tile, tap0, n_taps, rank;
+  int iters, kt_begin, m_tile, n_tile, tap0, n_taps, rank, dbg;
 };
 
 template <int CG, int BN, int G, int S, int STAGE>
@@ -51,6 +51,11 @@ __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const C
       const uint32_t bytes = (2 + c.n_taps * B_CHUNKS) * WG_CHUNK;
       const uint32_t full = CG == 2 ? ((c.bar_full + 8 * STAGE) & PEER_BIT_MASK) : (c.bar_full + 8 * STAGE);
       // CG == 2: the leader's barrier counts the bytes of both CTAs of the pair
+      if ((p.dbg & 1) && kb >= S) {            // debug: handshake only, no TMA traffic (stale operands)
+        if (CG == 1 || c.rank == 0) mbar_arrive(full);
+        wg_produce_round<CG, BN, G, S, STAGE + 1>(tmP, tmQ, p, c, kb);
+        return;
+      }
       if (CG == 1 || c.rank == 0) mbar_expect_tx(full, CG * bytes);
       if (CG == 2) {
         tma_load_4d_2sm(a_dst, tmP, full, c.m_tile * WG_BM, w0, h0, n0);
@@ -97,7 +102,7 @@ __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
       // the taps of the group share the P slab of this stage: one accumulator of BN columns per tap
 #pragma unroll
       for (int g = 0; g < G; ++g) {
-        if (g < c.n_taps) {
+        if (g < c.n_taps && !(c.dbg & 2)) {
 #pragma unroll
           for (int k = 0; k < WG_BK / 16; ++k) {
             // 16 pixels = two 8-row groups of 1024 B; chunks of 64 channels are WG_CHUNK apart.
@@ -187,7 +192,7 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   WgCtx c;
   c.bar_full = smem_u32(&bar_full[0]); c.bar_empty = smem_u32(&bar_empty[0]);
   c.smem_base = smem_base; c.tmem_base = tmem_base; c.phase_bits = 0;
-  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.tap0 = tap0; c.n_taps = n_taps; c.rank = rank;
+  c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.tap0 = tap0; c.n_taps = n_taps; c.rank = rank; c.dbg = p.dbg;
   if (warp == 0) {
     if (lane == 0)
       for (int kb = 0; kb < iters; kb += S) wg_produce_round<CG, BN, G, S, 0>(&tmP, &tmQ, p, c, kb);
@@ -214,7 +219,7 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
         uint32_t v[16];
         tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + g * BN + c0, v);
         tmem_ld_wait();
-        if (row_ok) {
+        if (row_ok && !(p.dbg & 4)) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int n = n_base + c0 + j * 4;
@@ -266,8 +271,12 @@ static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& t
   return cudaLaunchKernelEx(&cfg, kern, tmP, tmQ, p);
 }
 
-int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradParams& p,
+int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradParams& p_in,
                  cudaStream_t stream) {
+  WgradParams p = p_in;
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("MT_IGEMM_DBG"); dbg = e ? atoi(e) : 0; }
+  p.dbg = dbg;
   const long long grid = (long long)p.tap_groups * p.m_tiles * p.n_tiles * p.splits;
   if (grid <= 0 || grid > 0x7fffffffLL) return -1000;
   if (p.cg == 2 && (p.m_tiles % 2 || p.BN < 128)) return -1010;
