@@ -28,13 +28,25 @@ static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   p.off_h = c.off_h; p.off_w = c.off_w; p.step_h = c.step_h; p.step_w = c.step_w;
   const int n_logical = c.window ? 64 : c.Qc;
   p.BN = n_logical >= 256 ? 256 : (n_logical > 64 ? 128 : 64);
+  // box mode: stride-1 3x3 (the residual trunk, the style encoder's blocks): one filter row per work item, its
+  // three taps read one (8 + 2) x 8 pixel box of the shifted operand; Cin tile of at most 128 so that the
+  // three accumulators fit in TMEM.  MT_WGRAD_BOX=0 turns it off.
+  static int box_off = -1;
+  if (box_off < 0) { const char* e = getenv("MT_WGRAD_BOX"); box_off = (e && atoi(e) == 0) ? 1 : 0; }
+  p.box = (!box_off && !c.window && c.q_mul == 1 && c.kh == 3 && c.kw == 3 && c.step_w == 1 && c.step_h == 1 &&
+           c.Pw >= 8 && c.Ph >= 8) ? 1 : 0;
+  if (p.box) {
+    p.TW = 8; p.TH = 8; p.TN = 1;
+    p.tiles_w = cdiv(c.Pw, 8); p.tiles_h = cdiv(c.Ph, 8); p.tiles_n = c.Pn;
+    if (p.BN > 128) p.BN = 128;
+  }
   p.m_tiles = cdiv(c.Pc, 128);
   p.n_tiles = cdiv(n_logical, p.BN);
   // narrow 3x3 layers: three taps (one filter row) per work item share the un-shifted operand's slab
   // (igemm_wgrad.cu); MT_WGRAD_TAPS=1 keeps one tap per work item
   static int force_taps = -1;
   if (force_taps < 0) { const char* e = getenv("MT_WGRAD_TAPS"); force_taps = e ? atoi(e) : 0; }
-  p.tap_group = (!c.window && p.kh * p.kw == 9 && p.BN <= 128 && force_taps != 1) ? 3 : 1;
+  p.tap_group = (!c.window && p.kh * p.kw == 9 && p.BN <= 128 && (force_taps != 1 || p.box)) ? 3 : 1;
   // 7x7 row-window stems (taps = filter rows, 64-wide windows): four rows per work item (134 -> 118 us; the
   // 4-row stems would be left with a single group and 148 split-K slabs: 38 -> 46 us, not used there)
   if (c.window && p.BN == 64 && p.kh * p.kw >= 6 && force_taps != 1) p.tap_group = 4;
@@ -53,7 +65,7 @@ static void plan_wgrad(const WgradLike& c, WgradParams& p) {
   static int force_cg = -1;
   if (force_cg < 0) { const char* e = getenv("MT_WGRAD_CG"); force_cg = e ? atoi(e) : 0; }
   p.cg = (p.m_tiles % 2 == 0 && p.BN >= 128 && force_cg != 1) ? 2 : 1;
-  const int stage_bytes = (2 + p.tap_group * (p.BN / p.cg / 64)) * 8192;
+  const int stage_bytes = p.box ? 2 * 8192 + (p.BN / p.cg / 64) * 10240 : (2 + p.tap_group * (p.BN / p.cg / 64)) * 8192;
   p.stages = (200 * 1024) / stage_bytes;
   if (p.stages > 8) p.stages = 8;
   p.tmem_cols = pow2_cols(p.tap_group * p.BN);
@@ -84,7 +96,7 @@ static int run_wgrad_like(const WgradLike& c, int splits, cudaStream_t stream) {
     uint64_t dims[4] = {(uint64_t)c.Qc, (uint64_t)c.Qw, (uint64_t)c.Qh, (uint64_t)c.Qn};
     uint64_t str[3] = {(uint64_t)c.Qc_s * 2, (uint64_t)c.Qw * c.Qc_s * 2,
                        (uint64_t)c.Qh * c.Qw * c.Qc_s * 2};
-    uint32_t box[4] = {64, (uint32_t)(p.TW * c.q_mul), (uint32_t)(p.TH * c.q_mul), (uint32_t)p.TN};
+    uint32_t box[4] = {64, (uint32_t)(p.box ? 10 : p.TW * c.q_mul), (uint32_t)(p.TH * c.q_mul), (uint32_t)p.TN};
     uint32_t es[4] = {1, (uint32_t)c.q_mul, (uint32_t)c.q_mul, 1};
     int rc = make_tmap(&tmQ, c.q, 4, dims, str, box, es);
     if (rc) return rc;

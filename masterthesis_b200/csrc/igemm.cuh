@@ -57,6 +57,7 @@ struct WgradParams {
   int BN;
   int cg;                         // 1: one CTA per (tap, M tile, N tile, split); 2: CTA pair over two M tiles
   int dbg;                        // debug (MT_IGEMM_DBG): 1 = no TMA traffic after the first ring round, 2 = no MMAs
+  int box;                        // 1: box mode (igemm_wgrad.cu): 8 x 8 pixel tiles, one halo'd box of Q per filter row
   int tap_group, tap_groups;      // filter taps per work item (they share the P slab) and number of such groups
   int splits;                     // split-K factor over pixel tiles
   int stages;

@@ -19,6 +19,18 @@ namespace mt {
 static constexpr int WG_BM = 128;
 static constexpr int WG_BK = 64;           // pixels per stage
 static constexpr int WG_CHUNK = 64 * 128;  // one (64 ch x 64 pix) slab in bytes
+// Box mode (G = 3 taps of one filter row, stride-1 traversal): the pixel tile is 8 x 8 and ONE (8 + 2) x 8 pixel
+// box of the shifted operand serves the three taps: the 8-pixel K groups of the MN-major SWIZZLE_128B operand
+// are then `WG_BOX_PITCH` rows apart (descriptor SBO) and tap s starts s rows into the box (the swizzle is a
+// function of the shared-memory address, tools/micro/halo_desc.cu).  2.4x fewer bytes of that operand.
+static constexpr int WG_BOX_PITCH = 10;
+static constexpr int WG_BOX_CHUNK = WG_BOX_PITCH * 8 * 128;   // 10 KiB per 64-channel chunk
+template <int CG, int BN, int G, bool BOX>
+struct WgStage {
+  static constexpr int B_CHUNKS = BN / CG / 64;
+  static constexpr uint32_t B_CHUNK_BYTES = BOX ? WG_BOX_CHUNK : WG_CHUNK;
+  static constexpr uint32_t BYTES = 2 * WG_CHUNK + (BOX ? 1 : G) * B_CHUNKS * B_CHUNK_BYTES;
+};
 
 __device__ __forceinline__ void st_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
@@ -32,11 +44,11 @@ struct WgCtx {
   int iters, kt_begin, m_tile, n_tile, tap0, n_taps, rank, dbg;
 };
 
-template <int CG, int BN, int G, int S, int STAGE>
+template <int CG, int BN, int G, bool BOX, int S, int STAGE>
 __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const CUtensorMap* tmQ,
                                                  const WgradParams& p, WgCtx& c, int kb) {
   constexpr int B_CHUNKS = BN / CG / 64;                      // 64-channel slabs of Q staged by this CTA, per tap
-  constexpr uint32_t STAGE_BYTES = (2 + G * B_CHUNKS) * WG_CHUNK;
+  constexpr uint32_t STAGE_BYTES = WgStage<CG, BN, G, BOX>::BYTES;
   if constexpr (STAGE < S) {
     if (kb + STAGE < c.iters) {
       int kt = c.kt_begin + kb + STAGE;
@@ -48,12 +60,12 @@ __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const C
       c.phase_bits ^= 1u << STAGE;
       const uint32_t a_dst = c.smem_base + STAGE * STAGE_BYTES;
       const uint32_t b_dst = a_dst + 2 * WG_CHUNK;
-      const uint32_t bytes = (2 + c.n_taps * B_CHUNKS) * WG_CHUNK;
+      const uint32_t bytes = BOX ? STAGE_BYTES : (2 + c.n_taps * B_CHUNKS) * WG_CHUNK;
       const uint32_t full = CG == 2 ? ((c.bar_full + 8 * STAGE) & PEER_BIT_MASK) : (c.bar_full + 8 * STAGE);
       // CG == 2: the leader's barrier counts the bytes of both CTAs of the pair
       if ((p.dbg & 1) && kb >= S) {            // debug: handshake only, no TMA traffic (stale operands)
         if (CG == 1 || c.rank == 0) mbar_arrive(full);
-        wg_produce_round<CG, BN, G, S, STAGE + 1>(tmP, tmQ, p, c, kb);
+        wg_produce_round<CG, BN, G, BOX, S, STAGE + 1>(tmP, tmQ, p, c, kb);
         return;
       }
       if (CG == 1 || c.rank == 0) mbar_expect_tx(full, CG * bytes);
@@ -66,8 +78,18 @@ __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const C
       }
       const int qw0 = w0 * p.mul_w + p.off_w, qh0 = h0 * p.mul_h + p.off_h;
       const int ch0 = c.n_tile * BN + c.rank * (BN / CG);
+      if (BOX) {
+        // one box per chunk: origin = tap column 0 of the group's filter row
+        const int r = c.tap0 / p.kw;
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
+        for (int ch = 0; ch < B_CHUNKS; ++ch) {
+          const uint32_t dst = b_dst + ch * WG_BOX_CHUNK;
+          if (CG == 2) tma_load_4d_2sm(dst, tmQ, full, ch0 + ch * 64, qw0, qh0 + r * p.step_h, n0);
+          else tma_load_4d(dst, tmQ, full, ch0 + ch * 64, qw0, qh0 + r * p.step_h, n0);
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < (BOX ? 0 : G); ++g) {
         if (g < c.n_taps) {
           const int tap = c.tap0 + g;
           const int r = tap / p.kw, s = tap - r * p.kw;
@@ -81,14 +103,14 @@ __device__ __forceinline__ void wg_produce_round(const CUtensorMap* tmP, const C
         }
       }
     }
-    wg_produce_round<CG, BN, G, S, STAGE + 1>(tmP, tmQ, p, c, kb);
+    wg_produce_round<CG, BN, G, BOX, S, STAGE + 1>(tmP, tmQ, p, c, kb);
   }
 }
 
-template <int CG, int BN, int G, int S, int STAGE>
+template <int CG, int BN, int G, bool BOX, int S, int STAGE>
 __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
   constexpr int B_CHUNKS = BN / CG / 64;
-  constexpr uint32_t STAGE_BYTES = (2 + G * B_CHUNKS) * WG_CHUNK;
+  constexpr uint32_t STAGE_BYTES = WgStage<CG, BN, G, BOX>::BYTES;
   constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                              (static_cast<uint32_t>(BN >> 3) << 17) |
                              (static_cast<uint32_t>((WG_BM * CG) >> 4) << 24);
@@ -107,7 +129,10 @@ __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
           for (int k = 0; k < WG_BK / 16; ++k) {
             // 16 pixels = two 8-row groups of 1024 B; chunks of 64 channels are WG_CHUNK apart.
             const uint64_t ad = const_smem_desc(a_off + k * 2048, WG_CHUNK, 1024);
-            const uint64_t bd = const_smem_desc(b_off + g * B_CHUNKS * WG_CHUNK + k * 2048, WG_CHUNK, 1024);
+            // box mode: tap g starts g pixel rows into the box, 8-pixel K groups are one box row apart
+            const uint64_t bd = BOX ? const_smem_desc(b_off + g * 128 + k * 2 * WG_BOX_PITCH * 128, WG_BOX_CHUNK,
+                                                      WG_BOX_PITCH * 128)
+                                    : const_smem_desc(b_off + g * B_CHUNKS * WG_CHUNK + k * 2048, WG_CHUNK, 1024);
             const uint32_t acc = (STAGE > 0 || k > 0) ? 1u : (kb != 0 ? 1u : 0u);
             if (CG == 2) umma_bf16_2sm(c.tmem_base + g * BN, ad, bd, IDESC, acc);
             else umma_bf16(c.tmem_base + g * BN, ad, bd, IDESC, acc);
@@ -117,7 +142,7 @@ __device__ __forceinline__ void wg_mma_round(WgCtx& c, int kb) {
       if (CG == 2) umma_commit_2sm(c.bar_empty + 8 * STAGE);
       else umma_commit(c.bar_empty + 8 * STAGE);
     }
-    wg_mma_round<CG, BN, G, S, STAGE + 1>(c, kb);
+    wg_mma_round<CG, BN, G, BOX, S, STAGE + 1>(c, kb);
   }
 }
 
@@ -133,7 +158,7 @@ __device__ long long g_wg_flag;   // < 0: shared-memory ring not at SMEM_RING (c
 // pixel block) and differ in the shifted Q slab, so a stage holds one P slab + G Q slabs and feeds G
 // accumulators of BN columns in TMEM: the P slab crosses L2 -> SM once per G taps.  Used for the narrow
 // layers (BN <= 128), which are bound by that stream and not by the tensor pipe.
-template <int CG, int BN, int G, int S>
+template <int CG, int BN, int G, bool BOX, int S>
 __global__ void __launch_bounds__(192, 1)
 igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmQ,
                    const WgradParams p) {
@@ -195,11 +220,11 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   c.iters = iters; c.kt_begin = kt_begin; c.m_tile = m_tile; c.n_tile = n_tile; c.tap0 = tap0; c.n_taps = n_taps; c.rank = rank; c.dbg = p.dbg;
   if (warp == 0) {
     if (lane == 0)
-      for (int kb = 0; kb < iters; kb += S) wg_produce_round<CG, BN, G, S, 0>(&tmP, &tmQ, p, c, kb);
+      for (int kb = 0; kb < iters; kb += S) wg_produce_round<CG, BN, G, BOX, S, 0>(&tmP, &tmQ, p, c, kb);
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
-      for (int kb = 0; kb < iters; kb += S) wg_mma_round<CG, BN, G, S, 0>(c, kb);
+      for (int kb = 0; kb < iters; kb += S) wg_mma_round<CG, BN, G, BOX, S, 0>(c, kb);
       if (CG == 2) umma_commit_2sm(smem_u32(&bar_tmem_full));
       else umma_commit(smem_u32(&bar_tmem_full));
     }
@@ -241,14 +266,14 @@ igemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constan
   }
 }
 
-template <int CG, int BN, int G>
+template <int CG, int BN, int G, bool BOX = false>
 static cudaError_t launch_wgrad_cfg(const CUtensorMap& tmP, const CUtensorMap& tmQ,
                                     const WgradParams& p, cudaStream_t stream) {
-  constexpr int kStageBytes = (2 + G * (BN / CG / 64)) * WG_CHUNK;
+  constexpr int kStageBytes = WgStage<CG, BN, G, BOX>::BYTES;
   constexpr int kFit = (200 * 1024) / kStageBytes;
   constexpr int kStages = kFit > 8 ? 8 : kFit;
   constexpr size_t kSmem = (size_t)kStages * kStageBytes + 1024;
-  auto* kern = igemm_wgrad_kernel<CG, BN, G, kStages>;
+  auto* kern = igemm_wgrad_kernel<CG, BN, G, BOX, kStages>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
@@ -282,6 +307,15 @@ int launch_wgrad(const CUtensorMap& tmP, const CUtensorMap& tmQ, const WgradPara
   if (p.cg == 2 && (p.m_tiles % 2 || p.BN < 128)) return -1010;
   cudaError_t e;
   if (p.tap_group * p.tap_groups < p.kh * p.kw || p.tap_group * p.BN > 512) return -1010;
+  if (p.box) {
+    if (p.tap_group != 3 || p.TW != 8 || p.TH != 8 || p.TN != 1 || p.kw != 3) return -1010;
+    switch (p.cg * 1000 + p.BN) {
+      case 2128: e = launch_wgrad_cfg<2, 128, 3, true>(tmP, tmQ, p, stream); break;
+      case 1128: e = launch_wgrad_cfg<1, 128, 3, true>(tmP, tmQ, p, stream); break;
+      case 1064: e = launch_wgrad_cfg<1, 64, 3, true>(tmP, tmQ, p, stream); break;
+      default: return -1010;
+    }
+  } else
   switch (p.tap_group * 10000 + p.cg * 1000 + p.BN) {
     case 12256: e = launch_wgrad_cfg<2, 256, 1>(tmP, tmQ, p, stream); break;
     case 12128: e = launch_wgrad_cfg<2, 128, 1>(tmP, tmQ, p, stream); break;
