@@ -110,7 +110,8 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     if (halo_off < 0) { const char* e = getenv("MT_HALO"); halo_off = (e && atoi(e) == 0) ? 1 : 0; }
     const bool unit_steps = (c.kh == 1 || c.step_h == 1 || c.step_h == -1) &&
                             (c.kw == 1 || c.step_w == 1 || c.step_w == -1);
-    if (!halo_off && !c.window && c.a_mul == 1 && c.a_mul_w <= 1 && unit_steps && p.n_tiles == 1 &&
+    // (row-window stems qualify too: a "pixel" of their tensor map is a window start, the taps are filter rows)
+    if (!halo_off && c.a_mul == 1 && c.a_mul_w <= 1 && unit_steps && p.n_tiles == 1 &&
         p.rowk_kw == 0 && c.Wt >= 8 && c.Ht >= 16 && igemm_halo_supported(2, p.BN, c.kh, c.kw, p.k_chunks)) {
       const int tw = cdiv(c.Wt, 8), th = cdiv(c.Ht, 16);
       // fused statistics: the caller sized its slots for the default tiling (mt_conv_stats_parts)
@@ -138,6 +139,10 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
     uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
                        (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
+    if (c.window) {                    // dim0: 64-element window starting at pixel (w * win_stride)
+      dims[0] = 64; dims[1] = (uint64_t)c.win_cols;
+      str[0] = (uint64_t)c.win_stride * c.Ac_s * 2;
+    }
     uint32_t box[4] = {64, (uint32_t)(8 + c.kw - 1), (uint32_t)(16 + c.kh - 1), 1};
     uint32_t es[4] = {1, 1, 1, 1};
     rc = make_tmap(&tmA, c.a, 4, dims, str, box, es);

@@ -758,6 +758,7 @@ int igemm_halo_supported(int cg, int BN, int kh, int kw, int k_chunks) {
   switch (BN * 1000 + kh * 100 + kw * 10 + k_chunks) {
     case 128331: case 128332: case 128222: case 128122:
     case 64331: case 64332:
+    case 128711:                      // 7-row window stems (paired pixels: 128 columns)
       return 1;
   }
   return 0;
@@ -785,6 +786,7 @@ int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUte
     case 128122: e = launch_halo_cfg<2, 128, 1, 2, 2>(tmA, tmB, tmC, p, stream); break;
     case 64331: e = launch_halo_cfg<2, 64, 3, 3, 1>(tmA, tmB, tmC, p, stream); break;
     case 64332: e = launch_halo_cfg<2, 64, 3, 3, 2>(tmA, tmB, tmC, p, stream); break;
+    case 128711: e = launch_halo_cfg<2, 128, 7, 1, 1>(tmA, tmB, tmC, p, stream); break;
     default: return -1010;
   }
   if (e == cudaSuccess) e = cudaGetLastError();
