@@ -16,6 +16,7 @@
  *   - ONE cudaStreamSynchronize + 8-byte cudaMemcpyFromSymbol at the first implicit-GEMM launch of the
  *     process outside stream capture (self check that the kernels' shared-memory ring sits at the offset
  *     their constant descriptors assume; error -1011 otherwise).  No other call synchronises.
+ * Device-side state: one 2 KiB `static __device__` array per GPU, the built-in scratch of mt_loss_l1_static.
  * Entry points are re-entrant per stream.  There is no CPU fallback: without a CUDA device every call fails.
  */
 #ifndef MT_B200_H
@@ -129,6 +130,14 @@ int mt_unpack_conv_window_pair_wgrad(const float* dw_packed, int splits, int Cou
 /* nn.Conv2d forward (+bias, +activation)            blocks.py:33-36, networks.py:373-374 */
 int mt_conv2d_fwd(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,
                   void* y, void* stream);
+/* Same with a PER-IMAGE bias, bias_n[N][Cout] fp32: the first 1x1 convolution of DecResnetBlock's block1 /
+ * block2 (blocks.py:180-190,199-205) reads cat(out, z tiled over the plane); the tiled half of its K is a
+ * per-image constant, so  conv1x1(cat(out, z)) = conv1x1(out; W[:, :C]) + (W[:, C:] z_n + b)  and only the
+ * first term is a convolution.  Needs one image per pixel tile (Hout * Wout >= 128 or so: -1014 otherwise, the
+ * caller then materialises the concatenation). */
+int mt_conv2d_image_bias_ok(const MtConv2d* d);   /* 1: the launch has one image per pixel tile */
+int mt_conv2d_fwd_image_bias(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias_n,
+                             void* y, void* stream);
 /* Same, with the statistics pass of the following InstanceNorm / LayerNorm (blocks.py:38-41,
  * networks.py:470-489) fused into the conv epilogue: per-channel sum / sum of squares of the STORED
  * bf16 output of every pixel tile go to stats[N][parts][Cout_s][2] (fp32, every slot written once,
@@ -227,6 +236,9 @@ int mt_norm_bwd_params(const float* red, const float* coef, const float* csum, i
 /* db[c] (+)= sum over `rows` of stats[row][c][0], c < C_valid: column sums of a dense tensor (bias gradients,
  * blocks.py:36) from the partial sums of mt_plane_stats (rows = N * parts), added in row order */
 int mt_colsum_into(const float* stats, int rows, int C, int C_valid, float* db, int accumulate, void* stream);
+/* the same per image: out[n][c] = sum over the `parts` rows of image n (the per-image column sums of dy that the
+ * gradient of a per-image bias needs, mt_conv2d_fwd_image_bias) */
+int mt_colsum_images(const float* stats, int N, int parts, int C, int C_valid, float* out, void* stream);
 int mt_norm_bwd_apply(const void* g, int g_pad, const void* x, const float* ss, const float* coef,
                       int N, int H, int W, int C, int act, float slope, void* dx, void* stream);
 /* backward of conv+bias+activation written into a padded buffer: fold + act' */

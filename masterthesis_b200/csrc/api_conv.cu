@@ -61,6 +61,7 @@ struct ConvLike {
   float* stats;             // optional fused plane statistics [Nt][stat_parts][n_store][2]
   int stat_parts, stat_part0;
   int accumulate;           // out += result
+  long long bias_n_stride;  // > 0: per-image bias rows (needs one image per tile)
   int rowk_kw, rowk_c, rowk_win;   // rows-in-K data gradient (IgemmParams::rowk_*), 0: off
   float* rowk_out;
 };
@@ -96,7 +97,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
   p.tmem_cols = pow2_cols(2 * p.acc_cols);
   p.out_n_stride = c.out_n_stride; p.out_h_stride = c.out_h_stride;
   p.out_w_stride = c.out_w_stride; p.out_off = c.out_off;
-  p.act = c.act; p.slope = c.slope; p.bias = c.bias;
+  p.act = c.act; p.slope = c.slope; p.bias = c.bias; p.bias_n_stride = c.bias ? c.bias_n_stride : 0;
   p.accumulate = c.accumulate;
   p.out = reinterpret_cast<__nv_bfloat16*>(c.out);
   p.rowk_kw = c.rowk_kw; p.rowk_c = c.rowk_c; p.rowk_win = c.rowk_win; p.rowk_out = c.rowk_out;
@@ -193,6 +194,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     p.stats = c.stats; p.n_stat_c = c.n_store;
     p.stat_parts = c.stat_parts; p.stat_part0 = c.stat_part0;
   }
+  if (p.bias_n_stride > 0 && p.TN != 1) return -1014;     // a tile would span images
   return halo ? launch_igemm_halo(tmA, tmB, tmC, p, stream) : launch_igemm(tmA, tmB, tmC, p, stream);
 }
 
@@ -299,9 +301,30 @@ extern "C" int mt_conv_stats_parts(const MtConv2d* d, int transposed) {
   return tn == 1 ? cdiv(d->Wout, tw) * cdiv(d->Hout, th) : 0;
 }
 
+static int conv2d_fwd_impl(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,
+                           long long bias_n_stride, void* y, float* stats, int parts, void* stream);
 extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void* w_fwd,
                                    const float* bias, void* y, float* stats, int parts,
                                    void* stream) {
+  return conv2d_fwd_impl(d, x, w_fwd, bias, 0, y, stats, parts, stream);
+}
+// 1 if the pixel tile the library picks for this forward launch holds pixels of ONE image (what the per-image
+// bias of mt_conv2d_fwd_image_bias needs)
+extern "C" int mt_conv2d_image_bias_ok(const MtConv2d* d) {
+  if (check_desc(d) || d->window) return 0;
+  int tw, th, tn;
+  pick_tile(128, d->Wout, d->Hout, d->N, d->stride, &tw, &th, &tn);
+  return tn == 1 ? 1 : 0;
+}
+// per-image bias: bias_n[N][Cout] fp32 (see the header)
+extern "C" int mt_conv2d_fwd_image_bias(const MtConv2d* d, const void* x, const void* w_fwd,
+                                        const float* bias_n, void* y, void* stream) {
+  if (!bias_n) return -1002;
+  if (d && d->window) return -1014;
+  return conv2d_fwd_impl(d, x, w_fwd, bias_n, d ? d->Cout : 0, y, nullptr, 0, stream);
+}
+static int conv2d_fwd_impl(const MtConv2d* d, const void* x, const void* w_fwd, const float* bias,
+                           long long bias_n_stride, void* y, float* stats, int parts, void* stream) {
   int rc = check_desc(d);
   if (rc) return rc;
   ConvLike c;
@@ -327,6 +350,7 @@ extern "C" int mt_conv2d_fwd_stats(const MtConv2d* d, const void* x, const void*
   c.out_n_stride = (long long)d->out_H * d->out_W * d->Cout_s;
   c.out_off = ((long long)d->out_pad * d->out_W + d->out_pad) * d->Cout_s;
   c.act = d->act; c.slope = d->slope; c.bias = bias; c.out = y;
+  c.bias_n_stride = bias_n_stride;
   c.stats = stats; c.stat_parts = parts; c.stat_part0 = 0;
   if (win && !d->single && mt_conv_window_pair_mode(d->Cin_s, d->kw, d->stride)) {
     if (d->Wout & 1) return -1014;

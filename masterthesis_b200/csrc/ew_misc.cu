@@ -524,6 +524,9 @@ __global__ void __launch_bounds__(256) colsum_finalize_kernel(const float* __res
   __shared__ float sm[8][33];
   const int cl = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + cl;
+  // blockIdx.y: independent group of `rows` rows with its own output row (mt_colsum_images: one per image)
+  stats += (size_t)blockIdx.y * rows * C * 2;
+  db += (size_t)blockIdx.y * Cv;
   float a[4] = {0.f, 0.f, 0.f, 0.f};
   if (c < Cv) {
     int i = g;
@@ -747,6 +750,13 @@ extern "C" int mt_colsum_into(const float* stats, int rows, int C, int C_valid, 
                               void* stream) {
   if (rows < 1 || C_valid < 1 || C_valid > C) return -1005;
   launch_pdl(colsum_finalize_kernel, dim3((C_valid + 31) / 32), dim3(256), 0, ST(stream), stats, rows, C, C_valid, db, accumulate);
+  return cuda_rc();
+}
+extern "C" int mt_colsum_images(const float* stats, int N, int parts, int C, int C_valid, float* out,
+                                void* stream) {
+  if (N < 1 || parts < 1 || C_valid < 1 || C_valid > C) return -1005;
+  launch_pdl(colsum_finalize_kernel, dim3((C_valid + 31) / 32, N), dim3(256), 0, ST(stream), stats, parts, C, C_valid,
+             out, 0);
   return cuda_rc();
 }
 extern "C" int mt_scale_interior(const void* x_pad, const float* scale, int N, int H, int W, int C,

@@ -36,6 +36,7 @@ struct IgemmParams {
   float slope;
   int accumulate;      // 1: out += result (TMA reduce-add store) instead of out = result
   const float* bias;
+  long long bias_n_stride;   // > 0: image n of a tile (TN == 1) reads bias + n * bias_n_stride (per-image bias)
   __nv_bfloat16* out;
   float* stats;        // optional fused plane statistics: [N][stat_parts][n_stat_c][2] fp32 partial
   int n_stat_c;        // (sum, sumsq) per pixel tile; this launch fills slots stat_part0 + tile index

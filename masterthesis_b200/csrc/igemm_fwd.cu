@@ -44,8 +44,9 @@ __device__ long long g_ts[64];   // debug timestamps of CTA 0 (MT_IGEMM_DBG & 32
 // different lines per instruction.  Rows outside the valid pixel range are staged as zeros (the
 // store clips them; the fused plane statistics must not see them).
 template <int ACT, bool BIAS, int SW>
-__device__ __forceinline__ void epilogue_slab(const IgemmParams& p, uint32_t tmem_addr,
-                                              uint32_t stage_row, int r7, bool row_ok, int c_glob) {
+__device__ __forceinline__ void epilogue_slab(const IgemmParams& p, const float* __restrict__ bias,
+                                              uint32_t tmem_addr, uint32_t stage_row, int r7, bool row_ok,
+                                              int c_glob) {
   constexpr int LD = SW < 32 ? 32 : SW;
   uint32_t v[LD];
   {
@@ -66,14 +67,14 @@ __device__ __forceinline__ void epilogue_slab(const IgemmParams& p, uint32_t tme
     if (BIAS) {
       const int cb = (p.bias_wrap > 0 && c >= p.bias_wrap) ? c - p.bias_wrap : c;   // wrap is a multiple of 8
       if (cb + 8 <= p.n_bias) {
-        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + cb));
-        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + cb + 4));
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + cb));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + cb + 4));
         f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
         f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
       } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (cb + j < p.n_bias) f[j] += __ldg(p.bias + cb + j);
+          if (cb + j < p.n_bias) f[j] += __ldg(bias + cb + j);
       }
     }
 #pragma unroll
@@ -264,6 +265,7 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, const CUtens
     tc_fence_after();
     if (stamp && warp == 2 && tile_i < 8) g_ts[24 + 2 * tile_i] = clock64() - T0;
     const uint32_t tmem_row = tmem_base + acc * ACC_COLS + (static_cast<uint32_t>(q * 32) << 16);
+    const float* bias_item = p.bias + (long long)wc.n0 * p.bias_n_stride;      // per-image bias: TN == 1
     if constexpr (BN == 32 && CG == 1) {
       if (p.rowk_kw > 0) {
         named_bar_sync(1 + grp, 128);       // the team has finished reading Z of its previous tile
@@ -280,7 +282,7 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, const CUtens
       if (tt == 0) bulk_wait_read0();                       // previous store has left the box
       named_bar_sync(1 + grp, 128);
       if (stamp && warp == 2 && tile_i == 2) g_ts[41] = clock64() - T0;
-#define MT_EPI(A, B) epilogue_slab<A, B, SW>(p, tmem_row + sl * SW, stage_row, m & 7, row_ok, c_glob)
+#define MT_EPI(A, B) epilogue_slab<A, B, SW>(p, bias_item, tmem_row + sl * SW, stage_row, m & 7, row_ok, c_glob)
       switch (p.act) {
         case ACT_RELU:  if (hb) MT_EPI(ACT_RELU, true);  else MT_EPI(ACT_RELU, false);  break;
         case ACT_LRELU: if (hb) MT_EPI(ACT_LRELU, true); else MT_EPI(ACT_LRELU, false); break;
@@ -680,6 +682,24 @@ igemm_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
 static int g_num_sms = 0;
 
+// One-time self check of the shared-memory layout assumption behind const_smem_desc(): the kernels report a
+// ring that is not at SMEM_RING through g_ts[63] and compute nothing.  Synchronises once per process, outside
+// stream capture, after the first launch of either implicit-GEMM kernel family.
+static int check_ring_once(cudaStream_t stream) {
+  static bool ring_checked = false;
+  if (ring_checked) return 0;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) {
+    long long flag = 0;
+    if (cudaStreamSynchronize(stream) != cudaSuccess) return -1011;
+    if (cudaMemcpyFromSymbol(&flag, g_ts, sizeof(flag), 63 * sizeof(long long)) != cudaSuccess) return -1011;
+    if (flag < 0) return -1011;        // operand ring is not at SMEM_RING: nothing was computed
+    ring_checked = true;
+  }
+  return 0;
+}
+
+
 template <int CG, int BN>
 struct StageCfg {
   static constexpr int kStageBytes = A_STAGE_BYTES + (BN / CG) * BK * 2;
@@ -790,7 +810,8 @@ int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUte
     default: return -1010;
   }
   if (e == cudaSuccess) e = cudaGetLastError();
-  return e == cudaSuccess ? 0 : -(int)e;
+  if (e != cudaSuccess) return -(int)e;
+  return check_ring_once(stream);
 }
 
 int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
@@ -820,20 +841,7 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorM
   }
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return -(int)e;
-  // One-time self check of the shared-memory layout assumption behind const_smem_desc().
-  static bool ring_checked = false;
-  if (!ring_checked) {
-    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone) {
-      long long flag = 0;
-      if (cudaStreamSynchronize(stream) != cudaSuccess) return -1011;
-      if (cudaMemcpyFromSymbol(&flag, g_ts, sizeof(flag), 63 * sizeof(long long)) != cudaSuccess)
-        return -1011;
-      if (flag < 0) return -1011;        // operand ring is not at SMEM_RING: nothing was computed
-      ring_checked = true;
-    }
-  }
-  return 0;
+  return check_ring_once(stream);
 }
 
 }  // namespace mt

@@ -97,6 +97,51 @@ class ConvAct(Function):
         return dx, dw, db, None, None, None, None, None
 
 
+class ConvZAct(Function):
+    """activation(conv1x1(cat(h, z tiled over the plane)) + b) without the concatenation: the first 1x1 conv of
+    DecResnetBlock's block1 / block2 (reference blocks.py:180-190, 199-205).  The tiled half of K is a per-image
+    constant, so the layer is a convolution of h with W[:, :Cx] plus the per-image bias W[:, Cx:] z_n + b
+    (mt_linear_fwd -> mt_conv2d_fwd_image_bias).  Backward: the usual data / weight gradient on (h, W[:, :Cx]);
+    the per-image column sums of dy (mt_colsum_images) are the gradient of the per-image bias, from which
+    dz, dW[:, Cx:] and db follow as a Linear backward."""
+
+    @staticmethod
+    def forward(ctx, h, z, weight, bias, wf_h, wb_h, geom_h, act, out_pad):
+        Cx = geom_h.Cin
+        wz = weight.detach()[:, Cx:, 0, 0].contiguous()                     # [Cout, Cv] fp32
+        bias_n = ops.linear_fwd(z.detach().float().contiguous(), wz, bias.detach() if bias is not None else None)
+        out = ops.conv_fwd_image_bias(h, wf_h, bias_n, geom_h, act=act, out_pad=out_pad)
+        ops.reflect_border_(out, out_pad)
+        ctx.geom, ctx.act, ctx.out_pad = geom_h, act, out_pad
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(h, out if (act is not None) else None, wb_h, z, wz)
+        ctx.wshape = tuple(weight.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        h, out, wb_h, z, wz = ctx.saved_tensors
+        g, act, op = ctx.geom, ctx.act, ctx.out_pad
+        dout = _c(dout)
+        dy = ops.reflect_fold(dout, op) if act is None else ops.act_bwd_fold(dout, out, op, act)
+        dh = ops.conv_dgrad(dy, wb_h, g, h.shape[1], h.shape[2]) if ctx.needs_input_grad[0] else None
+        dw = db = dz = None
+        need_w = ctx.needs_input_grad[2]
+        if need_w or ctx.needs_input_grad[1] or ctx.needs_input_grad[3]:
+            cs = ops.colsum_images(dy, g.Cout)                                 # d(per-image bias) [N, Cout]
+            dz, dwz, db = ops.linear_bwd(cs, None, z.float().contiguous(), wz, act=None,
+                                         need_dx=ctx.needs_input_grad[1], has_bias=ctx.has_bias,
+                                         need_params=need_w or ctx.needs_input_grad[3])
+            if need_w:
+                dwh = ops.conv_wgrad(h, dy, g)                                 # [Cout, Cx, 1, 1]
+                dw = torch.cat((dwh.view(g.Cout, g.Cin), dwz), dim=1).view(ctx.wshape)
+            if not ctx.needs_input_grad[3]:
+                db = None
+            if dz is not None:
+                dz = dz.to(z.dtype)
+        return dh, dz, dw, db, None, None, None, None, None
+
+
 class ConvNormAct(Function):
     """conv -> {InstanceNorm | AdaIN | LayerNorm} -> activation (-> + noise) -> padded output
     (ConvBlock with norm: blocks.py:38-42; UpsampleBlock: blocks.py:82-90)."""

@@ -22,6 +22,8 @@ from .norm import AdaptiveInstanceNorm, LayerNorm
 
 # ------------------------------------------------------------------------- parameter holders
 _PACK_EPOCH = [0]
+# DecResnetBlock: fold the tiled-z half of its 1x1 convs into a per-image bias (MT_FOLD_Z=0: materialise the concat)
+FOLD_TILED_Z = os.environ.get('MT_FOLD_Z', '1') != '0'
 
 
 def invalidate_packs():
@@ -551,10 +553,31 @@ class DecResnetBlock(nn.Module):
         self._dropout, self._stride = dropout, stride
         self.n_channel = n_channel
 
+    def _packed_h(self, m):
+        """bf16 operands of W[:, :n_channel] of a 1x1 conv over cat(h, z): the part that multiplies h"""
+        w = m.weight
+        key = (w._version, w.data_ptr(), _PACK_EPOCH[0])
+        cache = self.__dict__.setdefault('_h_packs', {})
+        rec = cache.get(id(m))
+        if rec is None or rec[0] != key:
+            g = ConvGeom(self.n_channel, m.out_channels, 1, 1, 1, 0)
+            rec = cache[id(m)] = (key, g, ops.pack_weight(w.detach()[:, :self.n_channel].contiguous(), g))
+        return rec[1], rec[2]
+
     def _half(self, x, z, conv, block, out_pad):
         c = conv.conv
         wf, wb = c.packed()
         h = Fn.ConvNormAct.apply(x, c.weight, c.bias, wf, wb, c.geom(), 'instance', None, None, None, 0, None)
+        m = block[0]
+        N, H, W, _ = h.shape
+        if FOLD_TILED_Z and not m.spectral and m.kernel_size == 1 and self._stride == 1:
+            # the tiled-z half of K folded into a per-image bias (Fn.ConvZAct): no concatenated tensor
+            gh, (wf, wb) = self._packed_h(m)
+            if ops.image_bias_ok(gh, N, H, W):
+                h = Fn.ConvZAct.apply(h, z, m.weight, m.bias, wf, wb, gh, 'relu', 0)
+                m = block[2]
+                wf, wb = m.packed()
+                return Fn.ConvAct.apply(h, m.weight, m.bias, wf, wb, m.geom(), 'relu', out_pad)
         h = Fn.ConcatChannels.apply(h, z, self.n_channel, 0)
         for i, pad in ((0, 0), (2, out_pad)):
             m = block[i]

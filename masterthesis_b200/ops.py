@@ -777,6 +777,38 @@ def scale_interior(x_pad, scale, pad):
     return dx
 
 
+@_checked
+def conv_fwd_image_bias(x, wf, bias_n, g: ConvGeom, act=None, out_pad=0):
+    """conv_fwd with a per-image bias bias_n [N, Cout] fp32 (mt_conv2d_fwd_image_bias); raises _lib.MtError
+    -1014 when a pixel tile would span images (tiny planes)"""
+    _require_cuda(x)
+    N, Hin, Win, C = x.shape
+    assert C == g.Cin_s and x.dtype == torch.bfloat16 and x.is_contiguous()
+    assert tuple(bias_n.shape) == (N, g.Cout)
+    d = g.desc(N, Hin, Win, out_pad, act)
+    out = empty_act(N, d.out_H, d.out_W, g.Cout_s, x.device)
+    check(_lib.lib().mt_conv2d_fwd_image_bias(ctypes.byref(d), _p(x), _p(wf), _p(_f32c(bias_n)), _p(out), _stream()),
+          "conv_fwd_image_bias")
+    _count()
+    return out
+
+
+def image_bias_ok(g: ConvGeom, N, Hin, Win):
+    """whether mt_conv2d_fwd_image_bias can run this launch (one image per pixel tile)"""
+    d = g.desc(N, Hin, Win)
+    return bool(_lib.lib().mt_conv2d_image_bias_ok(ctypes.byref(d)))
+
+
+def colsum_images(dy, C):
+    """per-image column sums of a dense bf16 tensor [N,H,W,C_s] -> fp32 [N, C] (mt_plane_stats + mt_colsum_images)"""
+    st = plane_stats(dy)
+    N, parts, Cs, _ = st.shape
+    out = _T.empty((N, C), dtype=torch.float32, device=dy.device)
+    check(_lib.lib().mt_colsum_images(_p(st), N, parts, Cs, C, _p(out), _stream()), "colsum_images")
+    _count()
+    return out
+
+
 def bias_grad(dy, C, into=None):
     """sum over (n, h, w) of a dense bf16 tensor [N,H,W,C_s] -> its first C channels (the bias gradient of
     the convolution that produced the tensor dy is the gradient of, blocks.py:36): per-chunk column sums

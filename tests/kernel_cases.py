@@ -413,6 +413,50 @@ def linear_case(N=32, In=12, Out=256, act="relu", seed=0):
     return r
 
 
+def conv_z_case(N=4, Cx=256, Cv=256, Cout=512, H=16, W=16, seed=0):
+    """functional.ConvZAct (mt_linear_fwd + mt_conv2d_fwd_image_bias; backward through mt_colsum_images and
+    mt_linear_bwd) vs the reference's formulation act(conv1x1(cat(h, z tiled), W) + b) (blocks.py:180-190,
+    199-205) in fp32 with autograd: output, dh, dz, dW (both halves), db.  Gradients are compared for the
+    activation-free form and for ReLU with the mask our forward produced (a pre-activation within bf16 rounding
+    of zero may land on either side; a single flipped unit is a 5-10 % max-norm error in dh, which says nothing
+    about the kernels)."""
+    from masterthesis_b200 import functional as Fn
+    torch.manual_seed(seed)
+    h = bf(torch.randn(N, Cx, H, W, device=DEV))
+    z = torch.randn(N, Cv, device=DEV)
+    w = bf(torch.randn(Cout, Cx + Cv, 1, 1, device=DEV) * 0.05)
+    b = torch.randn(Cout, device=DEV) * 0.1
+    g = ConvGeom(Cx, Cout, 1, 1, 1, 0)
+    assert ops.image_bias_ok(g, N, H, W)
+    wf, wb = ops.pack_weight(w[:, :Cx].contiguous(), g)
+    res = {}
+    for act in (None, 'relu'):
+        h_ref, z_ref = h.clone().requires_grad_(True), z.clone().requires_grad_(True)
+        w_ref, b_ref = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+        cat = torch.cat((h_ref, z_ref[:, :, None, None].expand(N, Cv, H, W)), 1)
+        pre = F.conv2d(cat, w_ref, b_ref)
+        hn = to_nhwc(h).requires_grad_(True)
+        zz = z.clone().requires_grad_(True)
+        ww, bb = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+        y = Fn.ConvZAct.apply(hn, zz, ww, bb, wf, wb, g, act, 0)
+        yo = from_nhwc(y.detach(), Cout)
+        if act is None:
+            y_ref = pre
+        else:
+            res["fwd_relu_vs_fp32"] = rel(yo, F.relu(pre).detach())
+            y_ref = pre * (yo > 0).float()
+        dy = bf(torch.randn_like(y_ref))
+        y_ref.backward(dy)
+        y.backward(to_nhwc(dy))
+        ops.join_side()
+        torch.cuda.synchronize()
+        t = "" if act is None else "_relu"
+        res.update({"fwd" + t: rel(yo, y_ref.detach()), "dh" + t: rel(from_nhwc(hn.grad, Cx), h_ref.grad),
+                    "dz" + t: rel(zz.grad, z_ref.grad), "dw_h" + t: rel(ww.grad[:, :Cx], w_ref.grad[:, :Cx]),
+                    "dw_z" + t: rel(ww.grad[:, Cx:], w_ref.grad[:, Cx:]), "db" + t: rel(bb.grad, b_ref.grad)})
+    return res
+
+
 def style_mlp_case(N=32, K=4, C=256, seed=0):
     """functional.StyleMLP (mt_style_mlp_fwd / _bwd) vs the nn.Sequential of the reference decoder
     (networks.py:256-261) followed by the fc of K AdaIN blocks (norm.py:27), with autograd."""
@@ -507,6 +551,8 @@ def loss_case(seed=0):
 CASES = {
     "linear_relu": linear_case,
     "linear_plain_n3": lambda: linear_case(3, 256, 8, None),
+    "conv_z_fold": lambda: conv_z_case(),
+    "conv_z_fold_n16": lambda: conv_z_case(16, 256, 256, 512, 64, 64),
     "linear_wide": lambda: linear_case(16, 256, 1024, None),
     "style_mlp": style_mlp_case,
     "style_mlp_base": lambda: style_mlp_case(16, 0, 1024),
