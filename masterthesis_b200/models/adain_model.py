@@ -211,7 +211,7 @@ class AdaINModel(Model):
         the next use, on the pack stream)."""
         if self.dp is not None:
             self.dp.allreduce([self.optimizer[n] for n in nets])
-        blocks.join_prepack()              # no pack may still be reading the weights this step overwrites
+        blocks.join_prepack(self.ctx)              # no pack may still be reading the weights this step overwrites
         for n in nets:
             self.optimizer[n].step()
         if prepack:                        # the stepped weights have another consumer in this iteration
@@ -400,7 +400,7 @@ class AdaINModel(Model):
         bucket = opt.grad_bucket
         total_norm = torch.linalg.vector_norm(bucket) * opt.grad_scale
         bucket.mul_(torch.clamp(5.0 / (total_norm + 1e-6), max=1.0))
-        blocks.join_prepack()
+        blocks.join_prepack(self.ctx)
         opt.step()
 
     # ------------------------------------------------------------------ phases G1 / G2 (:225-394)
@@ -571,7 +571,7 @@ class AdaINModel(Model):
 
     # ------------------------------------------------------------------ the iteration (:421-430)
     def optimize_parameters(self, global_iter):
-        blocks.set_dropout_rng(self.rng)       # --use_dropout masks: replayed draws (parity) or device Philox
+        blocks.set_dropout_rng(self.rng, self.ctx)       # --use_dropout masks: replayed draws (parity) or device Philox
         if self.args.use_dis_content and global_iter % self.args.d_iter != 0:
             self._run_iteration(self._content_iteration, 'content')
         else:
@@ -584,12 +584,12 @@ class AdaINModel(Model):
         self.update_discriminator(self.img, self.c_org)
         self.update_generator(self.img, self.c_org)
         self._wait_d_steps()
-        blocks.join_prepack()
+        blocks.join_prepack(self.ctx)
 
     def _content_iteration(self):
         blocks.prepack(self.model.content_encoder, self.model.content_discriminator)
         self.update_content_discriminator(self.img, self.c_org)
-        blocks.join_prepack()
+        blocks.join_prepack(self.ctx)
 
     def compute_visuals(self):
         B = self.args.batch_size

@@ -21,16 +21,42 @@ from .norm import AdaptiveInstanceNorm, LayerNorm
 
 
 # ------------------------------------------------------------------------- parameter holders
-_PACK_EPOCH = [0]
+class HostContext:
+    """Host-side state of ONE model instance: the pack epoch (bumped before a CUDA-graph capture so that every
+    weight is re-packed inside it), the stream on which weights are packed ahead of use, and the replayed
+    dropout draws of the parity harness.  `Model` owns one and binds it to the modules of its networks
+    (`bind_context`); modules used on their own share `_DEFAULT_CTX`.  (Round 1 kept these as module globals,
+    so two models in one process shared them.)"""
+
+    def __init__(self):
+        self.pack_epoch = 0
+        self.pack_streams = {}
+        self.dropout_rng = None
+
+
+_DEFAULT_CTX = HostContext()
+
+
+def context_of(module) -> HostContext:
+    return module.__dict__.get('_mt_ctx') or _DEFAULT_CTX
+
+
+def bind_context(ctx: HostContext, *nets):
+    """make every module of `nets` use `ctx` (Model.initialize)"""
+    for net in nets:
+        for m in net.modules():
+            m.__dict__['_mt_ctx'] = ctx
+
+
 # DecResnetBlock: fold the tiled-z half of its 1x1 convs into a per-image bias (MT_FOLD_Z=0: materialise the concat)
 FOLD_TILED_Z = os.environ.get('MT_FOLD_Z', '1') != '0'
 
 
-def invalidate_packs():
-    """Drop every cached bf16 weight pack (Model does this before capturing an iteration in a CUDA
-    graph: a replayed iteration must re-pack every weight at its first use, because the weights were
-    stepped by the previous replay)."""
-    _PACK_EPOCH[0] += 1
+def invalidate_packs(ctx: HostContext = None):
+    """Drop every cached bf16 weight pack of the context's modules (Model does this before capturing an
+    iteration in a CUDA graph: a replayed iteration must re-pack every weight at its first use, because the
+    weights were stepped by the previous replay)."""
+    (ctx or _DEFAULT_CTX).pack_epoch += 1
 
 
 # Weight packs ahead of their first use.  A pack is a ~8 us, 64-block kernel: at its point of use it sits
@@ -39,13 +65,12 @@ def invalidate_packs():
 # separate stream instead, layer by layer in module order, each pack followed by an event that the
 # consuming convolution waits for: the packs of the later layers run under the earlier layers' work.
 PREPACK = os.environ.get('MT_PREPACK', '1') == '1'
-_pack_streams = {}
 
 
-def _pack_stream(device):
-    s = _pack_streams.get(device)
+def _pack_stream(ctx, device):
+    s = ctx.pack_streams.get(device)
     if s is None:
-        s = _pack_streams[device] = torch.cuda.Stream(device=device)
+        s = ctx.pack_streams[device] = torch.cuda.Stream(device=device)
     return s
 
 
@@ -55,18 +80,20 @@ def prepack(*nets):
     if not PREPACK or ops.POISON or ops.PROFILE is not None:
         return
     todo = []
+    ctx = None
     for net in nets:
         for m in net.modules():
             if isinstance(m, _ConvParams) and not m.spectral and m._pack is not None:
                 w = m.weight
+                ctx = context_of(m)
                 (_, _, zpad, stem, single, _), _ = m._pack
-                key = (w._version, w.data_ptr(), zpad, stem, single, _PACK_EPOCH[0])
+                key = (w._version, w.data_ptr(), zpad, stem, single, ctx.pack_epoch)
                 if m._pack[0] != key:
                     todo.append((m, key, zpad, stem, single))
     if not todo:
         return
     cur = torch.cuda.current_stream()
-    side = _pack_stream(todo[0][0].weight.device)
+    side = _pack_stream(ctx, todo[0][0].weight.device)
     side.wait_stream(cur)
     with torch.cuda.stream(side):
         for m, key, zpad, stem, single in todo:
@@ -76,10 +103,10 @@ def prepack(*nets):
             m._pack_event = ev
 
 
-def join_prepack():
+def join_prepack(ctx: HostContext = None):
     """current stream waits for every pack issued so far (before the packed weights are overwritten by
     the next optimizer step, and at the end of an iteration so that a captured graph has no open branch)"""
-    for dev, s in _pack_streams.items():
+    for dev, s in (ctx or _DEFAULT_CTX).pack_streams.items():
         torch.cuda.current_stream(dev).wait_stream(s)
 
 
@@ -114,7 +141,7 @@ class _ConvParams(nn.Module):
     def packed(self, zpad=0, stem=False, single=False):
         """bf16 GEMM operands of the fp32 master weight, refreshed when the weight changes."""
         w = self.weight
-        key = (w._version, w.data_ptr(), zpad, stem, single, _PACK_EPOCH[0])
+        key = (w._version, w.data_ptr(), zpad, stem, single, context_of(self).pack_epoch)
         if self._pack is None or self._pack[0] != key:
             self._pack = (key, ops.pack_weight(w, self.geom(zpad, stem, single)))
             self._pack_event = None
@@ -187,19 +214,15 @@ class ConvTranspose2d(_ConvParams):
 
 
 # ------------------------------------------------------------------------- dropout masks
-_DROPOUT_RNG = [None]
-
-
-def set_dropout_rng(rng):
+def set_dropout_rng(rng, ctx: HostContext = None):
     """rng(shape_nchw) -> N(0,1) CPU tensor: replayed draws of the parity harness (keep = draw > 0,
     the rule oracle/make_golden.py installs in the reference); None: device Philox (torch.rand)."""
-    _DROPOUT_RNG[0] = rng
+    (ctx or _DEFAULT_CTX).dropout_rng = rng
 
 
-def dropout_mask(x, C, p):
+def dropout_mask(x, C, p, rng=None):
     """bf16 mask of x's NHWC shape holding 0 or 1/(1-p)   (nn.Dropout(p), blocks.py:133-134,152,190)"""
     N, H, W, Cs = x.shape
-    rng = _DROPOUT_RNG[0]
     if rng is not None:
         keep = torch.zeros((N, H, W, Cs), dtype=torch.bool, device=x.device)
         keep[..., :C] = (rng((N, C, H, W)) > 0).to(x.device).permute(0, 2, 3, 1)
@@ -212,7 +235,7 @@ def apply_dropout(h, C, module):
     """h: dense NHWC bf16; module: the block's nn.Dropout (identity in eval mode)"""
     if not module.training or module.p == 0:
         return h
-    return Fn.MaskMul.apply(h, dropout_mask(h, C, module.p))
+    return Fn.MaskMul.apply(h, dropout_mask(h, C, module.p, context_of(module).dropout_rng))
 
 
 # ------------------------------------------------------------------------- layout edges
@@ -556,7 +579,7 @@ class DecResnetBlock(nn.Module):
     def _packed_h(self, m):
         """bf16 operands of W[:, :n_channel] of a 1x1 conv over cat(h, z): the part that multiplies h"""
         w = m.weight
-        key = (w._version, w.data_ptr(), _PACK_EPOCH[0])
+        key = (w._version, w.data_ptr(), context_of(self).pack_epoch)
         cache = self.__dict__.setdefault('_h_packs', {})
         rec = cache.get(id(m))
         if rec is None or rec[0] != key:

@@ -56,6 +56,8 @@ class Model(ABC, nn.Module):
         self._graphs = {}        # iteration kind ('main' / 'content') -> captured graph record
         self._eager_iters = {}
         self._scalars = {}
+        from .core.blocks import HostContext
+        self.ctx = HostContext()     # pack epoch / pack stream / dropout replay of THIS model (core/blocks.py)
 
     @abstractmethod
     def set_inputs(self, inputs):
@@ -132,7 +134,7 @@ class Model(ABC, nn.Module):
                     if hasattr(opt, '_ensure_flat'):
                         opt._ensure_flat()
                 gen = tuple(getattr(opt, 'generation', 0) for opt in self.optimizer.values())
-                blocks.invalidate_packs()
+                blocks.invalidate_packs(self.ctx)
                 ctx = GraphHyper(self.device)
                 for opt in self.optimizer.values():
                     opt.graph_ctx = ctx
@@ -203,6 +205,8 @@ class Model(ABC, nn.Module):
             self.model[net] = init_net(self.model[net], init_type=init_type,
                                        init_gain=getattr(self.args, 'init_gain', 0.02),
                                        gpu_ids=self.args.gpu_ids, device=self.device)
+        from .core import blocks
+        blocks.bind_context(self.ctx, *self.model.values())
         if 'train' in self.args.mode:
             self.args.last_iter = -1 if self.args.resume_opt is None else self.args.last_iter
             self.init_scheduler()

@@ -60,12 +60,11 @@ def test_spectral_norm_changes_the_discriminator_state_dict_like_the_reference()
 
 def test_dropout_mask_replays_the_reference_rule():
     draws_a, draws_b = synth.Draws(7), synth.Draws(7)
-    blocks.set_dropout_rng(draws_a)
-    try:
-        x = torch.zeros(2, 4, 6, 16, dtype=torch.bfloat16)             # NHWC, 12 logical of 16 stored channels
-        m = blocks.dropout_mask(x, 12, 0.5)
-    finally:
-        blocks.set_dropout_rng(None)
+    ctx = blocks.HostContext()                                         # per-model host state: not a module global
+    blocks.set_dropout_rng(draws_a, ctx)
+    x = torch.zeros(2, 4, 6, 16, dtype=torch.bfloat16)                 # NHWC, 12 logical of 16 stored channels
+    m = blocks.dropout_mask(x, 12, 0.5, ctx.dropout_rng)
+    assert blocks.context_of(torch.nn.Dropout(0.5)).dropout_rng is None    # other models are not affected
     want = (draws_b((2, 12, 4, 6)) > 0).permute(0, 2, 3, 1)
     assert m.dtype == torch.bfloat16 and m.shape == x.shape
     assert torch.equal(m[..., :12].float(), want.float() * 2.0)
