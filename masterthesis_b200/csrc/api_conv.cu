@@ -119,6 +119,24 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
       if (tw * th * c.Nt >= 8 && (!c.stats || (p.TN == 1 && tw * th == p.tiles_w * p.tiles_h))) halo = true;
     }
   }
+  // stride-2 3x3 variant (igemm_halo_s2_kernel): parity-class boxes; K = 64, 128-column CTA pairs, weights resident
+  bool halo_s2 = false;
+  {
+    static int off2 = -1;
+    if (off2 < 0) { const char* e = getenv("MT_HALO_S2"); off2 = (e && atoi(e) == 0) ? 1 : 0; }
+    if (!halo && !off2 && !c.window && c.a_mul == 2 && c.a_mul_w <= 0 && c.kh == 3 && c.kw == 3 && c.step_h == 1 &&
+        c.step_w == 1 && p.k_chunks == 1 && p.BN == 128 && p.n_tiles == 1 && p.rowk_kw == 0 && c.Wt >= 8 &&
+        c.Ht >= 16) {
+      const int tw = cdiv(c.Wt, 8), th = cdiv(c.Ht, 16);
+      if (tw * th * c.Nt >= 8 && (!c.stats || (p.TN == 1 && tw * th == p.tiles_w * p.tiles_h))) halo_s2 = true;
+    }
+  }
+  if (halo_s2) {
+    p.TW = 8; p.TH = 16; p.TN = 1;
+    p.tiles_w = cdiv(c.Wt, 8); p.tiles_h = cdiv(c.Ht, 16); p.tiles_n = c.Nt;
+    p.cg = 2;
+    p.work_items = cdiv(p.tiles_w * p.tiles_h * p.tiles_n, 2);
+  }
   if (halo) {
     p.TW = 8; p.TH = 16; p.TN = 1;
     p.tiles_w = cdiv(c.Wt, 8); p.tiles_h = cdiv(c.Ht, 16); p.tiles_n = c.Nt;
@@ -136,7 +154,14 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
 
   CUtensorMap tmA, tmB;
   int rc;
-  if (halo) {
+  if (halo_s2) {
+    uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
+    uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
+                       (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
+    uint32_t box[4] = {64, 9 * 2, 17 * 2, 1};        // 9 x 17 pixels of one parity class (element strides 2)
+    uint32_t es[4] = {1, 2, 2, 1};
+    rc = make_tmap(&tmA, c.a, 4, dims, str, box, es);
+  } else if (halo) {
     uint64_t dims[4] = {(uint64_t)c.Ac, (uint64_t)c.Aw, (uint64_t)c.Ah, (uint64_t)c.An};
     uint64_t str[3] = {(uint64_t)c.Ac_s * 2, (uint64_t)c.Aw * c.Ac_s * 2,
                        (uint64_t)c.Ah * c.Aw * c.Ac_s * 2};
@@ -195,6 +220,7 @@ static int run_conv_like(const ConvLike& c, cudaStream_t stream) {
     p.stat_parts = c.stat_parts; p.stat_part0 = c.stat_part0;
   }
   if (p.bias_n_stride > 0 && p.TN != 1) return -1014;     // a tile would span images
+  if (halo_s2) return launch_igemm_halo_s2(tmA, tmB, tmC, p, stream);
   return halo ? launch_igemm_halo(tmA, tmB, tmC, p, stream) : launch_igemm(tmA, tmB, tmC, p, stream);
 }
 

@@ -79,6 +79,8 @@ int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorM
 int igemm_halo_supported(int cg, int BN, int kh, int kw, int k_chunks);
 int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                       const IgemmParams& p, cudaStream_t stream);
+int launch_igemm_halo_s2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                         const IgemmParams& p, cudaStream_t stream);
 int launch_wgrad(const CUtensorMap& tmA, const CUtensorMap& tmB, const WgradParams& p,
                  cudaStream_t stream);
 

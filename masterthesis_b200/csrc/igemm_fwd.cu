@@ -680,6 +680,167 @@ igemm_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (stamp && warp == 0) g_ts[0] = clock64() - T0;
 }
 
+// ===================================================================================================
+// Halo variant for STRIDE-2 3x3 tap grids (the down-sampling convs forward, the data gradient of the
+// transposed convs): tap (r, s) reads input pixel (2h + r, 2w + s), so taps of equal parity (r & 1, s & 1) read
+// the same sub-sampled pixel grid shifted by (r >> 1, s >> 1).  One box of 17 x 9 sub-sampled pixels (TMA
+// element strides 2) per parity class serves its 4 / 2 / 2 / 1 taps through row-shifted descriptors; the four
+// class boxes are the four stages of the A ring (stage = class: compile-time), so the next tile's class-c box
+// loads as soon as this tile's class-c taps have issued.  Weights resident as in igemm_halo_kernel.
+// 78 KiB per tile and CTA instead of 9 x 24 KiB.  CTA pairs, Cout tile 128, K = 64 (one chunk).
+struct HaloS2Cfg {
+  static constexpr int BN = 128, CG = 2, PW = HALO_TW + 1, PH = HALO_TH + 1, T = 9;
+  static constexpr uint32_t A_BOX = PH * PW * 128;
+  static constexpr uint32_t A_STAGE = (A_BOX + 1023u) & ~1023u;
+  static constexpr int B_ROWS = BN / CG;
+  static constexpr uint32_t B_TILE = B_ROWS * 128;
+  static constexpr uint32_t B_OFF = 4 * A_STAGE;
+  static constexpr uint32_t B_BYTES = T * B_TILE;
+  static constexpr uint32_t EPI_OFF = B_OFF + B_BYTES;
+  static constexpr size_t kSmem = (size_t)EPI_OFF + 2 * BM * 128 + 1024;
+};
+
+// MMAs of parity class CLS = 2 * (r & 1) + (s & 1) of one work item into accumulator ACC_OFF
+template <int CLS, int ACC_OFF>
+__device__ __forceinline__ void halo_s2_class(uint32_t bar_afull, uint32_t bar_aempty, uint32_t tmem_base,
+                                              uint32_t& phase_bits) {
+  using C = HaloS2Cfg;
+  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(C::BN >> 3) << 17) |
+                             (static_cast<uint32_t>((BM * C::CG) >> 4) << 24);
+  constexpr int PR = CLS >> 1, PS = CLS & 1;
+  mbar_wait(bar_afull + 8 * CLS, (phase_bits >> CLS) & 1);
+  phase_bits ^= 1u << CLS;
+  tc_fence_after();
+#pragma unroll
+  for (int r = PR; r < 3; r += 2) {
+#pragma unroll
+    for (int s = PS; s < 3; s += 2) {
+#pragma unroll
+      for (int k = 0; k < BK / 16; ++k) {
+        const uint32_t a_off = SMEM_RING + CLS * C::A_STAGE + ((r >> 1) * C::PW + (s >> 1)) * 128 + k * 32;
+        const uint32_t b_off = SMEM_RING + C::B_OFF + (r * 3 + s) * C::B_TILE + k * 32;
+        const uint32_t acc = (CLS | (r >> 1) | (s >> 1) | k) != 0 ? 1u : 0u;
+        umma_bf16_2sm(tmem_base + ACC_OFF, const_smem_desc(a_off, 16, C::PW * 128), const_smem_desc(b_off, 16, 1024),
+                      IDESC, acc);
+      }
+    }
+  }
+  umma_commit_2sm(bar_aempty + 8 * CLS);
+}
+template <int ACC_OFF>
+__device__ __forceinline__ void halo_s2_item(uint32_t bar_afull, uint32_t bar_aempty, uint32_t tmem_base,
+                                             uint32_t& phase_bits) {
+  halo_s2_class<0, ACC_OFF>(bar_afull, bar_aempty, tmem_base, phase_bits);
+  halo_s2_class<1, ACC_OFF>(bar_afull, bar_aempty, tmem_base, phase_bits);
+  halo_s2_class<2, ACC_OFF>(bar_afull, bar_aempty, tmem_base, phase_bits);
+  halo_s2_class<3, ACC_OFF>(bar_afull, bar_aempty, tmem_base, phase_bits);
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+igemm_halo_s2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmC, const IgemmParams p) {
+  using C = HaloS2Cfg;
+  constexpr int CG = C::CG, BN = C::BN;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_afull[4];
+  __shared__ __align__(8) uint64_t bar_aempty[4];
+  __shared__ __align__(8) uint64_t bar_b;
+  __shared__ __align__(8) uint64_t bar_tfull[2];
+  __shared__ __align__(8) uint64_t bar_tempty[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+  const int cluster_id = blockIdx.x / CG;
+  const int n_clusters = gridDim.x / CG;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  if ((smem_base & 0x3FFFFu) != SMEM_RING) {
+    if (threadIdx.x == 0) g_ts[63] = -(long long)(smem_base & 0x3FFFFu);
+    return;
+  }
+  const bool stamp = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
+  const long long T0 = clock64();
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmC);
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(smem_u32(&bar_afull[i]), 1);
+      mbar_init(smem_u32(&bar_aempty[i]), 1);
+    }
+    mbar_init(smem_u32(&bar_b), 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&bar_tfull[i]), 1);
+      mbar_init(smem_u32(&bar_tempty[i]), CG * NUM_EPI_WARPS);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_2sm(smem_u32(&tmem_base_slot), p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  griddep_wait();
+  griddep_launch();
+  if (stamp && warp == 0) g_ts[7] = clock64() - T0;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      {
+        const uint32_t bb = smem_u32(&bar_b) & PEER_BIT_MASK;
+        if (rank == 0) mbar_expect_tx(bb, CG * C::B_BYTES);
+        for (int tap = 0; tap < C::T; ++tap) {
+          const int widx = p.w_base + (tap / 3) * p.w_step_r + (tap % 3) * p.w_step_s;
+          tma_load_3d_2sm(smem_base + C::B_OFF + tap * C::B_TILE, &tmB, bb, 0, rank * C::B_ROWS, widx);
+        }
+      }
+      uint32_t phase_bits = 0;
+      for (int item = cluster_id; item < p.work_items; item += n_clusters) {
+        const WorkCoord wc = decode_work<CG>(p, item, rank);
+        for (int cls = 0; cls < 4; ++cls) {
+          mbar_wait(smem_u32(&bar_aempty[cls]), ((phase_bits >> cls) & 1) ^ 1);
+          phase_bits ^= 1u << cls;
+          const uint32_t full = smem_u32(&bar_afull[cls]) & PEER_BIT_MASK;
+          if (rank == 0) mbar_expect_tx(full, 2 * C::A_BOX);
+          tma_load_4d_2sm(smem_base + cls * C::A_STAGE, &tmA, full, 0, 2 * wc.w0 + p.off_w + (cls & 1),
+                          2 * wc.h0 + p.off_h + (cls >> 1), wc.n0);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (rank == 0 && lane == 0) {
+      uint32_t phase_bits = 0;
+      mbar_wait(smem_u32(&bar_b), 0);
+      tc_fence_after();
+      int tile_i = 0;
+      for (int item = cluster_id; item < p.work_items; item += n_clusters, ++tile_i) {
+        const int acc = tile_i & 1;
+        mbar_wait(smem_u32(&bar_tempty[acc]), ((tile_i >> 1) & 1) ^ 1);
+        tc_fence_after();
+        if (stamp && tile_i < 8) g_ts[8 + 2 * tile_i] = clock64() - T0;
+        if (acc == 0) halo_s2_item<0>(smem_u32(&bar_afull[0]), smem_u32(&bar_aempty[0]), tmem_base, phase_bits);
+        else halo_s2_item<BN>(smem_u32(&bar_afull[0]), smem_u32(&bar_aempty[0]), tmem_base, phase_bits);
+        umma_commit_2sm(smem_u32(&bar_tfull[acc]));
+        if (stamp && tile_i < 8) g_ts[9 + 2 * tile_i] = clock64() - T0;
+      }
+    }
+    __syncwarp();
+  } else {
+    epilogue_role<CG, BN>(p, &tmC, smem_raw, smem_base + C::EPI_OFF, bar_tfull, bar_tempty, tmem_base, cluster_id,
+                          n_clusters, rank, warp, lane, stamp, T0);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_2sm(tmem_base, p.tmem_cols);
+  if (stamp && warp == 0) g_ts[0] = clock64() - T0;
+}
+
 static int g_num_sms = 0;
 
 // One-time self check of the shared-memory layout assumption behind const_smem_desc(): the kernels report a
@@ -809,6 +970,52 @@ int launch_igemm_halo(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUte
     case 128711: e = launch_halo_cfg<2, 128, 7, 1, 1>(tmA, tmB, tmC, p, stream); break;
     default: return -1010;
   }
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) return -(int)e;
+  return check_ring_once(stream);
+}
+
+int launch_igemm_halo_s2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                         const IgemmParams& p_in, cudaStream_t stream) {
+  IgemmParams p = p_in;
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("MT_IGEMM_DBG"); dbg = e ? atoi(e) : 0; }
+  p.dbg = dbg;
+  if (p.work_items <= 0 || p.TW != HALO_TW || p.TH != HALO_TH || p.TN != 1 || p.cg != 2 || p.BN != 128 ||
+      p.kh != 3 || p.kw != 3 || p.k_chunks != 1 || p.n_tiles != 1)
+    return -1010;
+  using C = HaloS2Cfg;
+  static_assert(C::kSmem <= 227 * 1024, "stride-2 halo configuration does not fit in shared memory");
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(igemm_halo_s2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)C::kSmem);
+    if (e != cudaSuccess) return -(int)e;
+    attr_set = true;
+  }
+  int clusters = g_num_sms / 2;
+  if (clusters > p.work_items) clusters = p.work_items;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(clusters * 2), 1, 1);
+  cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = C::kSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  static int pdl = -1;
+  if (pdl < 0) { const char* e = getenv("MT_PDL"); pdl = e ? (atoi(e) != 0) : 1; }
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, igemm_halo_s2_kernel, tmA, tmB, tmC, p);
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return -(int)e;
   return check_ring_once(stream);
